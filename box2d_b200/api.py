@@ -1,0 +1,242 @@
+"""Host-side mirror of the reference's Box2D.API surface for the step path, over the C-ABI.
+
+Names and argument meaning follow the C# facade (api/World.cs, api/Body.cs, api/Shape.cs, api/Joint.cs):
+``WorldAPI.CreateWorld/Step/GetContactEvents``, ``BodyAPI.CreateBody/SetTransform/...``,
+``ShapeAPI.CreatePolygonShape/...``, ``JointAPI.CreateRevoluteJoint``. Errors from the library raise
+``B2Error`` (the C# shim would throw likewise); unsupported features fail loudly at the call that needs them.
+
+``World`` is backend-agnostic: it is handed a bound function table (see capi.bind). ``CudaBackend`` binds the
+product library; the oracle is bound only by tests/ (never from this package).
+"""
+import ctypes as C
+import numpy as np
+from . import capi
+from .capi import (Vec2, Rot, Transform, WorldDef, BodyDef, ShapeDef, Geometry, RevoluteJointDef, BodyRead, ContactRead,
+                   ContactTouchEvent, ContactHitEvent, JointRead, ShapeRead, Counters, Profile)
+
+STATIC_BODY, KINEMATIC_BODY, DYNAMIC_BODY = 0, 1, 2
+FLT_MAX = 3.4028234663852886e38
+
+
+class B2Error(RuntimeError):
+    pass
+
+
+def default_world_def():
+    """include/Types.cs:75-144"""
+    d = WorldDef()
+    d.gravity = Vec2(0.0, -10.0)
+    d.restitutionThreshold = 1.0
+    d.hitEventThreshold = 1.0
+    d.contactHertz = 30.0
+    d.contactDampingRatio = 10.0
+    d.contactSpeed = 3.0
+    d.maximumLinearSpeed = 400.0
+    d.enableSleep = 1
+    d.enableContinuous = 1
+    d.enableContactSoftening = 0
+    return d
+
+
+def default_body_def():
+    """include/Types.cs:170-223"""
+    d = BodyDef()
+    d.type = STATIC_BODY
+    d.rotation = Rot(1.0, 0.0)
+    d.gravityScale = 1.0
+    d.sleepThreshold = 0.05
+    d.enableSleep = 1
+    d.isAwake = 1
+    d.isEnabled = 1
+    return d
+
+
+def default_shape_def():
+    """include/Types.cs:285-344"""
+    d = ShapeDef()
+    d.friction = 0.6
+    d.density = 1.0
+    d.categoryBits = 0xFFFFFFFFFFFFFFFF
+    d.maskBits = 0xFFFFFFFFFFFFFFFF
+    d.invokeContactCreation = 1
+    d.updateBodyMass = 1
+    return d
+
+
+def default_revolute_joint_def():
+    """include/Types.cs:431-456,569-597"""
+    d = RevoluteJointDef()
+    d.bodyIdA = -1
+    d.bodyIdB = -1
+    d.localFrameA = Transform(Vec2(0, 0), Rot(1, 0))
+    d.localFrameB = Transform(Vec2(0, 0), Rot(1, 0))
+    d.forceThreshold = FLT_MAX
+    d.torqueThreshold = FLT_MAX
+    d.constraintHertz = 60.0
+    d.constraintDampingRatio = 2.0
+    d.drawScale = 1.0
+    return d
+
+
+class Backend:
+    """A bound C-ABI: fns (common entry points), create(def)->handle, last_error(handle)."""
+
+    def __init__(self, fns, create, last_error, name):
+        self.fns, self.create, self.last_error, self.name = fns, create, last_error, name
+
+
+_cuda_backend = None
+
+
+def CudaBackend(device=0):
+    """Binds libb2cuda.so. Raises if the library (the CUDA extension) is missing: there is no fallback."""
+    global _cuda_backend
+    path = capi.product_library_path()
+    try:
+        lib = C.CDLL(path)
+    except OSError as e:
+        raise B2Error(f"libb2cuda.so not built/loadable at {path}: {e}. Run __graft_entry__.build().") from e
+    fns = capi.bind(lib, "b2cuda_")
+    extra = {}
+    for name, (args, res) in capi.PRODUCT_ONLY.items():
+        f = getattr(lib, "b2cuda_" + name)
+        f.argtypes, f.restype = args, res
+        extra[name] = f
+    fns.update(extra)
+
+    def create(wdef):
+        h = C.c_void_p()
+        rc = extra["world_create"](C.byref(wdef), device, C.byref(h))
+        if rc != 0:
+            raise B2Error(f"b2cuda_world_create failed rc={rc}: {extra['last_error']().decode()}")
+        return h
+
+    return Backend(fns, create, lambda h: extra["last_error"]().decode(), "cuda")
+
+
+class World:
+    """WorldAPI + BodyAPI + ShapeAPI + JointAPI for one world (api/World.cs:7-113 etc.)."""
+
+    def __init__(self, backend, world_def=None):
+        self.backend = backend
+        self.fns = backend.fns
+        self.handle = backend.create(world_def if world_def is not None else default_world_def())
+
+    def _check(self, rc):
+        if rc != 0:
+            raise B2Error(f"{self.backend.name} rc={rc}: {self.backend.last_error(self.handle)}")
+
+    # --- BodyAPI ---
+    def CreateBody(self, body_def):
+        out = C.c_int32(-1)
+        self._check(self.fns["create_body"](self.handle, C.byref(body_def), C.byref(out)))
+        return out.value
+
+    def SetTransform(self, body_id, position, rotation=(1.0, 0.0)):
+        self._check(self.fns["body_set_transform"](self.handle, body_id, Vec2(*position), Rot(*rotation)))
+
+    def SetLinearVelocity(self, body_id, v):
+        self._check(self.fns["body_set_linear_velocity"](self.handle, body_id, Vec2(*v)))
+
+    def SetAngularVelocity(self, body_id, w):
+        self._check(self.fns["body_set_angular_velocity"](self.handle, body_id, float(w)))
+
+    def ApplyForceToCenter(self, body_id, f, wake=True):
+        self._check(self.fns["body_apply_force_to_center"](self.handle, body_id, Vec2(*f), int(wake)))
+
+    def ApplyTorque(self, body_id, t, wake=True):
+        self._check(self.fns["body_apply_torque"](self.handle, body_id, float(t), int(wake)))
+
+    def ApplyLinearImpulseToCenter(self, body_id, i, wake=True):
+        self._check(self.fns["body_apply_linear_impulse_to_center"](self.handle, body_id, Vec2(*i), int(wake)))
+
+    # --- ShapeAPI ---
+    def CreateShape(self, body_id, shape_def, geometry):
+        out = C.c_int32(-1)
+        self._check(self.fns["create_shape"](self.handle, body_id, C.byref(shape_def), C.byref(geometry), C.byref(out)))
+        return out.value
+
+    CreatePolygonShape = CreateCircleShape = CreateCapsuleShape = CreateSegmentShape = CreateShape
+
+    # --- JointAPI ---
+    def CreateRevoluteJoint(self, joint_def):
+        out = C.c_int32(-1)
+        self._check(self.fns["create_revolute_joint"](self.handle, C.byref(joint_def), C.byref(out)))
+        return out.value
+
+    # --- WorldAPI ---
+    def SetGravity(self, g):
+        self._check(self.fns["world_set_gravity"](self.handle, Vec2(*g)))
+
+    def EnableWarmStarting(self, flag):
+        self._check(self.fns["world_enable_warm_starting"](self.handle, int(flag)))
+
+    def EnableSpeculative(self, flag):
+        self._check(self.fns["world_enable_speculative"](self.handle, int(flag)))
+
+    def EnableContinuous(self, flag):
+        self._check(self.fns["world_enable_continuous"](self.handle, int(flag)))
+
+    def SetContactTuning(self, hertz, damping, push):
+        self._check(self.fns["world_set_contact_tuning"](self.handle, hertz, damping, push))
+
+    def Step(self, time_step, sub_step_count):
+        self._check(self.fns["world_step"](self.handle, float(time_step), int(sub_step_count)))
+
+    def Synchronize(self):
+        self._check(self.fns["world_synchronize"](self.handle))
+
+    def Destroy(self):
+        if self.handle is not None:
+            self.fns["world_destroy"](self.handle)
+            self.handle = None
+
+    def GetCounters(self):
+        c = Counters()
+        self._check(self.fns["world_get_counters"](self.handle, C.byref(c)))
+        return c
+
+    def GetProfile(self):
+        p = Profile()
+        self._check(self.fns["world_get_profile"](self.handle, C.byref(p)))
+        return p
+
+    def GetContactEvents(self):
+        """Returns (begin, end, hit) as numpy structured arrays (copies)."""
+        b, e, h = C.POINTER(ContactTouchEvent)(), C.POINTER(ContactTouchEvent)(), C.POINTER(ContactHitEvent)()
+        nb, ne, nh = C.c_int32(), C.c_int32(), C.c_int32()
+        self._check(self.fns["world_get_contact_events"](self.handle, C.byref(b), C.byref(nb), C.byref(e), C.byref(ne), C.byref(h), C.byref(nh)))
+
+        def grab(ptr, n, ty):
+            if n == 0:
+                return np.zeros(0, dtype=np.dtype(ty))
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ty * n)).contents).copy() if False else \
+                np.frombuffer(C.string_at(ptr, n * C.sizeof(ty)), dtype=np.dtype(ty)).copy()
+        return grab(b, nb.value, ContactTouchEvent), grab(e, ne.value, ContactTouchEvent), grab(h, nh.value, ContactHitEvent)
+
+    def GetJointEvents(self):
+        p, n = C.POINTER(C.c_int32)(), C.c_int32()
+        self._check(self.fns["world_get_joint_events"](self.handle, C.byref(p), C.byref(n)))
+        return np.array([p[i] for i in range(n.value)], dtype=np.int32)
+
+    def _read(self, name, ty, hint):
+        n = C.c_int32()
+        cap = max(hint, 16)
+        while True:
+            buf = (ty * cap)()
+            self._check(self.fns[name](self.handle, buf, cap, C.byref(n)))
+            if n.value <= cap:
+                return np.frombuffer(buf, dtype=np.dtype(ty), count=n.value).copy()
+            cap = n.value
+
+    def ReadBodies(self):
+        return self._read("world_read_bodies", BodyRead, self.GetCounters().bodyCount + 16)
+
+    def ReadContacts(self):
+        return self._read("world_read_contacts", ContactRead, self.GetCounters().contactCount + 16)
+
+    def ReadJoints(self):
+        return self._read("world_read_joints", JointRead, self.GetCounters().jointCount + 16)
+
+    def ReadShapes(self):
+        return self._read("world_read_shapes", ShapeRead, self.GetCounters().shapeCount + 16)

@@ -1,0 +1,172 @@
+"""ctypes mirror of include/b2cuda.h (POD structs + function prototypes).
+
+The same prototypes are bound twice: on libb2cuda.so with prefix ``b2cuda_`` (the product) and — by the
+tests only — on the oracle library with prefix ``b2o_``. Nothing in this package loads the oracle.
+"""
+import ctypes as C
+import os
+
+MAX_POLY = 8
+
+
+class Vec2(C.Structure):
+    _fields_ = [("x", C.c_float), ("y", C.c_float)]
+
+
+class Rot(C.Structure):
+    _fields_ = [("c", C.c_float), ("s", C.c_float)]
+
+
+class Transform(C.Structure):
+    _fields_ = [("p", Vec2), ("q", Rot)]
+
+
+class WorldDef(C.Structure):
+    _fields_ = [("gravity", Vec2), ("restitutionThreshold", C.c_float), ("hitEventThreshold", C.c_float),
+                ("contactHertz", C.c_float), ("contactDampingRatio", C.c_float), ("contactSpeed", C.c_float),
+                ("maximumLinearSpeed", C.c_float), ("enableSleep", C.c_int32), ("enableContinuous", C.c_int32),
+                ("enableContactSoftening", C.c_int32), ("bodyCapacity", C.c_int32), ("shapeCapacity", C.c_int32),
+                ("contactCapacity", C.c_int32), ("jointCapacity", C.c_int32)]
+
+
+class BodyDef(C.Structure):
+    _fields_ = [("type", C.c_int32), ("position", Vec2), ("rotation", Rot), ("linearVelocity", Vec2),
+                ("angularVelocity", C.c_float), ("linearDamping", C.c_float), ("angularDamping", C.c_float),
+                ("gravityScale", C.c_float), ("sleepThreshold", C.c_float), ("userData", C.c_uint64),
+                ("lockLinearX", C.c_int32), ("lockLinearY", C.c_int32), ("lockAngularZ", C.c_int32),
+                ("enableSleep", C.c_int32), ("isAwake", C.c_int32), ("isBullet", C.c_int32), ("isEnabled", C.c_int32),
+                ("allowFastRotation", C.c_int32)]
+
+
+class ShapeDef(C.Structure):
+    _fields_ = [("userData", C.c_uint64), ("friction", C.c_float), ("restitution", C.c_float),
+                ("rollingResistance", C.c_float), ("tangentSpeed", C.c_float), ("userMaterialId", C.c_uint64),
+                ("density", C.c_float), ("groupIndex", C.c_int32), ("categoryBits", C.c_uint64), ("maskBits", C.c_uint64),
+                ("enableCustomFiltering", C.c_int32), ("isSensor", C.c_int32), ("enableSensorEvents", C.c_int32),
+                ("enableContactEvents", C.c_int32), ("enableHitEvents", C.c_int32), ("enablePreSolveEvents", C.c_int32),
+                ("invokeContactCreation", C.c_int32), ("updateBodyMass", C.c_int32)]
+
+
+class Geometry(C.Structure):
+    _fields_ = [("type", C.c_int32), ("count", C.c_int32), ("radius", C.c_float), ("v", Vec2 * MAX_POLY),
+                ("n", Vec2 * MAX_POLY), ("centroid", Vec2)]
+
+
+class RevoluteJointDef(C.Structure):
+    _fields_ = [("bodyIdA", C.c_int32), ("bodyIdB", C.c_int32), ("localFrameA", Transform), ("localFrameB", Transform),
+                ("forceThreshold", C.c_float), ("torqueThreshold", C.c_float), ("constraintHertz", C.c_float),
+                ("constraintDampingRatio", C.c_float), ("drawScale", C.c_float), ("collideConnected", C.c_int32),
+                ("userData", C.c_uint64), ("targetAngle", C.c_float), ("enableSpring", C.c_int32), ("hertz", C.c_float),
+                ("dampingRatio", C.c_float), ("enableLimit", C.c_int32), ("lowerAngle", C.c_float), ("upperAngle", C.c_float),
+                ("enableMotor", C.c_int32), ("maxMotorTorque", C.c_float), ("motorSpeed", C.c_float)]
+
+
+class BodyRead(C.Structure):
+    _fields_ = [("transform", Transform), ("center", Vec2), ("linearVelocity", Vec2), ("angularVelocity", C.c_float),
+                ("flags", C.c_uint32)]
+
+
+class ManifoldPointRead(C.Structure):
+    _fields_ = [("point", Vec2), ("anchorA", Vec2), ("anchorB", Vec2), ("separation", C.c_float),
+                ("normalImpulse", C.c_float), ("tangentImpulse", C.c_float), ("totalNormalImpulse", C.c_float),
+                ("normalVelocity", C.c_float), ("id", C.c_uint32), ("persisted", C.c_uint32)]
+
+
+class ContactRead(C.Structure):
+    _fields_ = [("contactId", C.c_int32), ("shapeIdA", C.c_int32), ("shapeIdB", C.c_int32), ("colorIndex", C.c_int32),
+                ("flags", C.c_uint32), ("pointCount", C.c_int32), ("normal", Vec2), ("rollingImpulse", C.c_float),
+                ("friction", C.c_float), ("restitution", C.c_float), ("rollingResistance", C.c_float),
+                ("tangentSpeed", C.c_float), ("points", ManifoldPointRead * 2)]
+
+
+class ContactTouchEvent(C.Structure):
+    _fields_ = [("shapeIdA", C.c_int32), ("shapeIdB", C.c_int32), ("contactId", C.c_int32), ("contactGeneration", C.c_uint32)]
+
+
+class ContactHitEvent(C.Structure):
+    _fields_ = [("shapeIdA", C.c_int32), ("shapeIdB", C.c_int32), ("point", Vec2), ("normal", Vec2), ("approachSpeed", C.c_float)]
+
+
+class JointRead(C.Structure):
+    _fields_ = [("jointId", C.c_int32), ("colorIndex", C.c_int32), ("linearImpulse", Vec2), ("springImpulse", C.c_float),
+                ("motorImpulse", C.c_float), ("lowerImpulse", C.c_float), ("upperImpulse", C.c_float)]
+
+
+class ShapeRead(C.Structure):
+    _fields_ = [("aabbLo", Vec2), ("aabbHi", Vec2), ("fatLo", Vec2), ("fatHi", Vec2), ("proxyKey", C.c_int32), ("enlarged", C.c_int32)]
+
+
+class Counters(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("bodyCount", "awakeBodyCount", "shapeCount", "contactCount", "touchingContactCount",
+                                         "jointCount", "contactIdCapacity", "activeColorCount", "moveCount", "newPairCount",
+                                         "toiCandidates", "unsupportedCount", "stepCount", "errorFlags")] + \
+               [("colorCounts", C.c_int32 * 24)]
+
+
+class Profile(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("step", "pairs", "collide", "solve", "prepareStages", "solveConstraints",
+                                         "prepareConstraints", "integrateVelocities", "warmStart", "solveImpulses",
+                                         "integratePositions", "relaxImpulses", "applyRestitution", "storeImpulses",
+                                         "transforms", "refit", "readback")]
+
+
+# name -> (argtypes after the world handle, has world handle)
+_W = C.c_void_p
+PROTOS = {
+    "create_body": [_W, C.POINTER(BodyDef), C.POINTER(C.c_int32)],
+    "create_shape": [_W, C.c_int32, C.POINTER(ShapeDef), C.POINTER(Geometry), C.POINTER(C.c_int32)],
+    "create_revolute_joint": [_W, C.POINTER(RevoluteJointDef), C.POINTER(C.c_int32)],
+    "body_set_transform": [_W, C.c_int32, Vec2, Rot],
+    "body_set_linear_velocity": [_W, C.c_int32, Vec2],
+    "body_set_angular_velocity": [_W, C.c_int32, C.c_float],
+    "body_apply_force_to_center": [_W, C.c_int32, Vec2, C.c_int32],
+    "body_apply_torque": [_W, C.c_int32, C.c_float, C.c_int32],
+    "body_apply_linear_impulse_to_center": [_W, C.c_int32, Vec2, C.c_int32],
+    "world_set_gravity": [_W, Vec2],
+    "world_enable_warm_starting": [_W, C.c_int32],
+    "world_enable_speculative": [_W, C.c_int32],
+    "world_enable_continuous": [_W, C.c_int32],
+    "world_set_contact_tuning": [_W, C.c_float, C.c_float, C.c_float],
+    "world_step": [_W, C.c_float, C.c_int32],
+    "world_synchronize": [_W],
+    "world_destroy": [_W],
+    "world_get_contact_events": [_W, C.POINTER(C.POINTER(ContactTouchEvent)), C.POINTER(C.c_int32),
+                                 C.POINTER(C.POINTER(ContactTouchEvent)), C.POINTER(C.c_int32),
+                                 C.POINTER(C.POINTER(ContactHitEvent)), C.POINTER(C.c_int32)],
+    "world_get_joint_events": [_W, C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32)],
+    "world_read_bodies": [_W, C.POINTER(BodyRead), C.c_int32, C.POINTER(C.c_int32)],
+    "world_read_contacts": [_W, C.POINTER(ContactRead), C.c_int32, C.POINTER(C.c_int32)],
+    "world_read_joints": [_W, C.POINTER(JointRead), C.c_int32, C.POINTER(C.c_int32)],
+    "world_read_shapes": [_W, C.POINTER(ShapeRead), C.c_int32, C.POINTER(C.c_int32)],
+    "world_get_counters": [_W, C.POINTER(Counters)],
+}
+# symbols only the product exports (declared in include/b2cuda.h)
+PRODUCT_ONLY = {
+    "last_error": ([], C.c_char_p),
+    "default_world_def": ([C.POINTER(WorldDef)], C.c_int32),
+    "default_body_def": ([C.POINTER(BodyDef)], C.c_int32),
+    "default_shape_def": ([C.POINTER(ShapeDef)], C.c_int32),
+    "default_revolute_joint_def": ([C.POINTER(RevoluteJointDef)], C.c_int32),
+    "world_create": ([C.POINTER(WorldDef), C.c_int32, C.POINTER(_W)], C.c_int32),
+    "world_get_profile": ([_W, C.POINTER(Profile)], C.c_int32),
+}
+
+
+def bind(lib, prefix):
+    """Attach argtypes/restype for every common entry point; returns {name: function}."""
+    fns = {}
+    for name, args in PROTOS.items():
+        f = getattr(lib, prefix + name)
+        f.argtypes = args
+        f.restype = C.c_int32
+        fns[name] = f
+    return fns
+
+
+def product_library_path():
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libb2cuda.so")
+
+
+def exported_symbols():
+    """Every symbol include/b2cuda.h declares (used by the CPU-side export test)."""
+    return ["b2cuda_" + n for n in list(PROTOS) + list(PRODUCT_ONLY)]

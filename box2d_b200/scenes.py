@@ -1,0 +1,197 @@
+"""Scene builders for BASELINE.json's configs, written against the Box2D.API mirror (api.World).
+
+The reference ships no samples (README.md:4); these definitions are ours and are used
+identically for the oracle and the CUDA library. All coordinates are exactly representable or pass
+through np.float32 so both sides receive bit-identical inputs.
+"""
+import numpy as np
+from . import api, geometry as geo
+
+f32 = np.float32
+
+
+def splitmix64(state):
+    state = (state + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+    z = state
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    return state, z ^ (z >> 31)
+
+
+def _uniform(state, lo, hi):
+    state, z = splitmix64(state)
+    u = (z >> 11) / float(1 << 53)
+    return state, float(f32(lo + (hi - lo) * u))
+
+
+def world_def(enable_sleep=False, enable_continuous=True, **kw):
+    d = api.default_world_def()
+    d.enableSleep = int(enable_sleep)
+    d.enableContinuous = int(enable_continuous)
+    for k, v in kw.items():
+        setattr(d, k, v)
+    return d
+
+
+def _shape_def(events=True, **kw):
+    sd = api.default_shape_def()
+    sd.enableContactEvents = int(events)
+    for k, v in kw.items():
+        setattr(sd, k, v)
+    return sd
+
+
+def _dynamic_body(world, x, y, **kw):
+    bd = api.default_body_def()
+    bd.type = api.DYNAMIC_BODY
+    bd.position = api.Vec2(float(f32(x)), float(f32(y)))
+    for k, v in kw.items():
+        setattr(bd, k, v)
+    return world.CreateBody(bd)
+
+
+def add_pyramid(world, rows, origin=(0.0, 0.0), ground_half_width=None, jitter_seed=None, jitter=0.0):
+    """Static ground box with its top at origin.y, then `rows` rows of unit boxes (row i has rows-i boxes)."""
+    ox, oy = origin
+    bd = api.default_body_def()
+    bd.position = api.Vec2(float(f32(ox)), float(f32(oy)))
+    ground = world.CreateBody(bd)
+    ghw = ground_half_width if ground_half_width is not None else float(rows)
+    world.CreatePolygonShape(ground, _shape_def(), geo.MakeOffsetBox(ghw, 1.0, (0.0, -1.0)))
+    box = geo.MakeBox(0.5, 0.5)
+    sd = _shape_def()
+    bodies = []
+    state = jitter_seed if jitter_seed is not None else 0
+    for i in range(rows):
+        count = rows - i
+        for j in range(count):
+            x = ox + (j - (count - 1) * 0.5) * 1.0
+            if jitter_seed is not None:
+                state, dx = _uniform(state, -jitter, jitter)
+                x += dx
+            y = oy + 0.5 + i * 1.0
+            b = _dynamic_body(world, x, y)
+            world.CreatePolygonShape(b, sd, box)
+            bodies.append(b)
+    return ground, bodies
+
+
+def large_pyramid(world, rows=100):
+    return add_pyramid(world, rows)
+
+
+def many_pyramids(world, nx=20, ny=20, rows=10, pitch=15.0):
+    out = []
+    for gy in range(ny):
+        for gx in range(nx):
+            out.append(add_pyramid(world, rows, origin=(gx * pitch, gy * pitch), ground_half_width=6.0))
+    return out
+
+
+def tumbler(world, n=20000, half=25.0, pitch=0.3, seed=12345, angular_velocity=0.7853981852531433):
+    """Kinematic rotating container with n mixed circles/capsules/boxes on a jittered lattice."""
+    bd = api.default_body_def()
+    bd.type = api.KINEMATIC_BODY
+    bd.angularVelocity = angular_velocity      # 0.25*pi as fp32
+    container = world.CreateBody(bd)
+    sd = _shape_def()
+    t = 0.5
+    for (hx, hy, c) in [(t, half + t, (half, 0.0)), (t, half + t, (-half, 0.0)), (half + t, t, (0.0, half)), (half + t, t, (0.0, -half))]:
+        world.CreatePolygonShape(container, sd, geo.MakeOffsetBox(hx, hy, c))
+    cols = int(np.ceil(np.sqrt(n)))
+    state = seed
+    bodies = []
+    circle = geo.Circle((0.0, 0.0), 0.1)
+    capsule = geo.Capsule((-0.05, 0.0), (0.05, 0.0), 0.075)
+    box = geo.MakeBox(0.1, 0.1)
+    for k in range(n):
+        i, j = k % cols, k // cols
+        state, dx = _uniform(state, -0.01, 0.01)
+        state, dy = _uniform(state, -0.01, 0.01)
+        x = (i - (cols - 1) * 0.5) * pitch + dx
+        y = (j - (cols - 1) * 0.5) * pitch + dy
+        b = _dynamic_body(world, x, y)
+        world.CreateShape(b, sd, (circle, capsule, box)[k % 3])
+        bodies.append(b)
+    return container, bodies
+
+
+def joint_grid(world, n=100, with_ground=True):
+    """n x n circles on a 1 m lattice, revolute joints to the right and lower neighbour, top row pinned."""
+    bd = api.default_body_def()
+    anchor = world.CreateBody(bd)
+    sd = _shape_def()
+    if with_ground:
+        ground = world.CreateBody(bd)
+        world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(float(n), 1.0, (0.5 * (n - 1), -(n - 1) - 0.6 - 1.0)))
+    circle = geo.Circle((0.0, 0.0), 0.4)
+    ids = [[None] * n for _ in range(n)]
+    for j in range(n):          # row j (0 = top), y = -j
+        for i in range(n):
+            b = _dynamic_body(world, float(i), float(-j))
+            world.CreateCircleShape(b, sd, circle)
+            ids[j][i] = b
+    joints = []
+    for j in range(n):
+        for i in range(n):
+            if j == 0:
+                jd = api.default_revolute_joint_def()
+                jd.bodyIdA, jd.bodyIdB = anchor, ids[j][i]
+                jd.localFrameA.p = api.Vec2(float(i), 0.5)
+                jd.localFrameB.p = api.Vec2(0.0, 0.5)
+                joints.append(world.CreateRevoluteJoint(jd))
+            if i + 1 < n:
+                jd = api.default_revolute_joint_def()
+                jd.bodyIdA, jd.bodyIdB = ids[j][i], ids[j][i + 1]
+                jd.localFrameA.p = api.Vec2(0.5, 0.0)
+                jd.localFrameB.p = api.Vec2(-0.5, 0.0)
+                joints.append(world.CreateRevoluteJoint(jd))
+            if j + 1 < n:
+                jd = api.default_revolute_joint_def()
+                jd.bodyIdA, jd.bodyIdB = ids[j][i], ids[j + 1][i]
+                jd.localFrameA.p = api.Vec2(0.0, -0.5)
+                jd.localFrameB.p = api.Vec2(0.0, 0.5)
+                joints.append(world.CreateRevoluteJoint(jd))
+    return ids, joints
+
+
+def mixed_drop(world, n=120, seed=7):
+    """Small scene touching every manifold pair type the step path supports: static segments + a static rounded
+    box as terrain, a kinematic paddle, and dynamic circles / capsules / boxes / rounded boxes / 3-gons dropped on it."""
+    bd = api.default_body_def()
+    ground = world.CreateBody(bd)
+    sd = _shape_def()
+    world.CreateSegmentShape(ground, sd, geo.Segment((-12.0, 0.0), (12.0, 0.0)))
+    world.CreateSegmentShape(ground, sd, geo.Segment((-12.0, 0.0), (-14.0, 6.0)))
+    world.CreateSegmentShape(ground, sd, geo.Segment((12.0, 0.0), (14.0, 6.0)))
+    world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(2.0, 0.25, (0.0, 0.25)))
+    kd = api.default_body_def()
+    kd.type = api.KINEMATIC_BODY
+    kd.position = api.Vec2(-5.0, 1.5)
+    kd.angularVelocity = 1.0
+    paddle = world.CreateBody(kd)
+    world.CreatePolygonShape(paddle, sd, geo.MakeBox(1.5, 0.1))
+    world.CreateCapsuleShape(paddle, sd, geo.Capsule((0.0, -0.6), (0.0, 0.6), 0.1))
+    shapes = [geo.Circle((0.0, 0.0), 0.2), geo.Capsule((-0.2, 0.0), (0.2, 0.0), 0.12), geo.MakeBox(0.2, 0.15),
+              geo.MakeRoundedBox(0.15, 0.15, 0.05), geo.Circle((0.1, 0.0), 0.15)]
+    state = seed
+    bodies = []
+    cols = 12
+    for k in range(n):
+        i, j = k % cols, k // cols
+        state, dx = _uniform(state, -0.05, 0.05)
+        b = _dynamic_body(world, (i - 5.5) * 0.9 + dx, 1.2 + j * 0.6)
+        world.CreateShape(b, sd, shapes[k % len(shapes)])
+        if k % 7 == 0:      # a second shape on some bodies (multi-shape mass + shape-list order)
+            world.CreateCircleShape(b, sd, geo.Circle((0.0, 0.2), 0.1))
+        bodies.append(b)
+    return ground, paddle, bodies
+
+
+SCENES = {
+    "large_pyramid": large_pyramid,
+    "many_pyramids": many_pyramids,
+    "tumbler": tumbler,
+    "joint_grid": joint_grid,
+    "mixed_drop": mixed_drop,
+}

@@ -1,0 +1,170 @@
+/* libb2cuda.so — C-ABI of the B200-native rigid-body step for the Box2D 3 C# port (MWstudios/Box2D).
+ *
+ * The reference has no FFI seam today (no DllImport/LibraryImport anywhere); the seam this library
+ * introduces is the static Box2D.API surface. Each entry point below names the reference method whose
+ * body a [LibraryImport("b2cuda")] stub replaces (see INTEGRATION.md and csharp/Box2D.Cuda/).
+ *
+ * Conventions: every function returns int32 status (0 = B2C_OK, <0 = error); no exceptions cross the
+ * ABI; b2cuda_last_error() returns a library-owned UTF-8 string. Ids are the reference's raw ints
+ * (BodyID.index1 - 1 etc., include/ID.cs:4-49); the library owns the id pools and reproduces the
+ * reference's LIFO recycling (src/IDPool.cs). A world is not re-entrant (api/World.cs:36-37).
+ * All state that the step touches lives in device memory; there is no CPU fallback: if no CUDA device
+ * is usable b2cuda_world_create fails with B2C_E_NO_DEVICE.
+ */
+#ifndef B2CUDA_H
+#define B2CUDA_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2C_OK 0
+#define B2C_E_INVALID (-1)       /* bad handle / id / argument */
+#define B2C_E_UNSUPPORTED (-2)   /* feature of the reference that this build does not cover (never silent) */
+#define B2C_E_NO_DEVICE (-3)
+#define B2C_E_CUDA (-4)
+#define B2C_E_CAPACITY (-5)      /* a device buffer overflowed (contacts, pairs, events) */
+#define B2C_E_LOCKED (-6)
+
+typedef struct B2CVec2 { float x, y; } B2CVec2;
+typedef struct B2CRot { float c, s; } B2CRot;
+typedef struct B2CTransform { B2CVec2 p; B2CRot q; } B2CTransform;
+
+/* WorldDef POD — include/Types.cs:75-144 (callbacks/task system are not representable: default mixers only) */
+typedef struct B2CWorldDef {
+  B2CVec2 gravity;
+  float restitutionThreshold, hitEventThreshold, contactHertz, contactDampingRatio, contactSpeed, maximumLinearSpeed;
+  int32_t enableSleep, enableContinuous, enableContactSoftening;
+  int32_t bodyCapacity, shapeCapacity, contactCapacity, jointCapacity;   /* hints, 0 = default; buffers grow between steps */
+} B2CWorldDef;
+
+/* BodyDef POD — include/Types.cs:170-223 */
+typedef struct B2CBodyDef {
+  int32_t type;                  /* 0 static, 1 kinematic, 2 dynamic (include/Types.cs:147) */
+  B2CVec2 position; B2CRot rotation; B2CVec2 linearVelocity;
+  float angularVelocity, linearDamping, angularDamping, gravityScale, sleepThreshold;
+  uint64_t userData;
+  int32_t lockLinearX, lockLinearY, lockAngularZ, enableSleep, isAwake, isBullet, isEnabled, allowFastRotation;
+} B2CBodyDef;
+
+/* ShapeDef POD — include/Types.cs:285-344 */
+typedef struct B2CShapeDef {
+  uint64_t userData;
+  float friction, restitution, rollingResistance, tangentSpeed;
+  uint64_t userMaterialId;
+  float density;
+  int32_t groupIndex;
+  uint64_t categoryBits, maskBits;
+  int32_t enableCustomFiltering, isSensor, enableSensorEvents, enableContactEvents, enableHitEvents,
+          enablePreSolveEvents, invokeContactCreation, updateBodyMass;
+} B2CShapeDef;
+
+/* Geometry POD — include/Collision.cs:65,184,376,632. type: 0 circle, 1 capsule, 2 segment, 3 polygon.
+ * circle: v[0]=center; capsule: v[0],v[1]=centers; segment: v[0],v[1]; polygon: count<=8 vertices+normals
+ * (built host-side by the unchanged C# Geometry.MakeBox/MakePolygon, src/Geometry.cs). */
+#define B2C_MAX_POLYGON_VERTICES 8
+typedef struct B2CGeometry {
+  int32_t type, count;
+  float radius;
+  B2CVec2 v[B2C_MAX_POLYGON_VERTICES], n[B2C_MAX_POLYGON_VERTICES];
+  B2CVec2 centroid;
+} B2CGeometry;
+
+/* RevoluteJointDef POD — include/Types.cs:431-456,569-597 */
+typedef struct B2CRevoluteJointDef {
+  int32_t bodyIdA, bodyIdB;
+  B2CTransform localFrameA, localFrameB;
+  float forceThreshold, torqueThreshold, constraintHertz, constraintDampingRatio, drawScale;
+  int32_t collideConnected;
+  uint64_t userData;
+  float targetAngle; int32_t enableSpring; float hertz, dampingRatio;
+  int32_t enableLimit; float lowerAngle, upperAngle;
+  int32_t enableMotor; float maxMotorTorque, motorSpeed;
+} B2CRevoluteJointDef;
+
+/* Read-back records */
+typedef struct B2CBodyRead {      /* BodyAPI.GetTransform/GetLinearVelocity/GetAngularVelocity... api/Body.cs:282-357 */
+  B2CTransform transform; B2CVec2 center; B2CVec2 linearVelocity; float angularVelocity; uint32_t flags;
+} B2CBodyRead;
+typedef struct B2CManifoldPointRead {   /* include/Collision.cs:916-945 */
+  B2CVec2 point, anchorA, anchorB;
+  float separation, normalImpulse, tangentImpulse, totalNormalImpulse, normalVelocity;
+  uint32_t id, persisted;
+} B2CManifoldPointRead;
+typedef struct B2CContactRead {         /* ContactAPI.GetData api/Contact.cs + graph color (Counters) */
+  int32_t contactId, shapeIdA, shapeIdB, colorIndex;
+  uint32_t flags;                        /* bit0 touching */
+  int32_t pointCount;
+  B2CVec2 normal; float rollingImpulse, friction, restitution, rollingResistance, tangentSpeed;
+  B2CManifoldPointRead points[2];
+} B2CContactRead;
+typedef struct B2CContactTouchEvent { int32_t shapeIdA, shapeIdB, contactId; uint32_t contactGeneration; } B2CContactTouchEvent; /* include/Types.cs:697-730 */
+typedef struct B2CContactHitEvent { int32_t shapeIdA, shapeIdB; B2CVec2 point, normal; float approachSpeed; } B2CContactHitEvent;
+typedef struct B2CJointRead { int32_t jointId, colorIndex; B2CVec2 linearImpulse; float springImpulse, motorImpulse, lowerImpulse, upperImpulse; } B2CJointRead;
+typedef struct B2CShapeRead { B2CVec2 aabbLo, aabbHi, fatLo, fatHi; int32_t proxyKey, enlarged; } B2CShapeRead;
+typedef struct B2CCounters {            /* WorldAPI.GetCounters api/World.cs:817-834 */
+  int32_t bodyCount, awakeBodyCount, shapeCount, contactCount, touchingContactCount, jointCount, contactIdCapacity,
+          activeColorCount, moveCount, newPairCount, toiCandidates, unsupportedCount, stepCount, errorFlags;
+  int32_t colorCounts[24];
+} B2CCounters;
+typedef struct B2CProfile {             /* WorldAPI.GetProfile api/World.cs:814; fields of include/Types.cs:378-403 (ms, CUDA events) */
+  float step, pairs, collide, solve, prepareStages, solveConstraints, prepareConstraints, integrateVelocities, warmStart,
+        solveImpulses, integratePositions, relaxImpulses, applyRestitution, storeImpulses, transforms, refit, readback;
+} B2CProfile;
+
+typedef struct B2CWorld B2CWorld;
+
+const char* b2cuda_last_error(void);
+int32_t b2cuda_default_world_def(B2CWorldDef* def);       /* include/Types.cs:75-144 defaults */
+int32_t b2cuda_default_body_def(B2CBodyDef* def);         /* :170-223 */
+int32_t b2cuda_default_shape_def(B2CShapeDef* def);       /* :285-344 */
+int32_t b2cuda_default_revolute_joint_def(B2CRevoluteJointDef* def);   /* :431-456,569-597 */
+
+/* WorldAPI.CreateWorld / DestroyWorld — api/World.cs:12-18, src/World.cs:183-260 */
+int32_t b2cuda_world_create(const B2CWorldDef* def, int32_t device, B2CWorld** out);
+int32_t b2cuda_world_destroy(B2CWorld* world);
+/* BodyAPI.CreateBody — api/Body.cs:16-105 */
+int32_t b2cuda_create_body(B2CWorld* world, const B2CBodyDef* def, int32_t* bodyId);
+/* ShapeAPI.CreateCircleShape/CreateCapsuleShape/CreateSegmentShape/CreatePolygonShape — api/Shape.cs:8-33 */
+int32_t b2cuda_create_shape(B2CWorld* world, int32_t bodyId, const B2CShapeDef* def, const B2CGeometry* geometry, int32_t* shapeId);
+/* JointAPI.CreateRevoluteJoint — api/Joint.cs:555, src/joints/RevoluteJoint.cs:32-56 */
+int32_t b2cuda_create_revolute_joint(B2CWorld* world, const B2CRevoluteJointDef* def, int32_t* jointId);
+/* BodyAPI.SetTransform :293 / SetLinearVelocity :359 / SetAngularVelocity :369 / ApplyForceToCenter :457 /
+ * ApplyTorque :469 / ApplyLinearImpulseToCenter :531 — api/Body.cs */
+int32_t b2cuda_body_set_transform(B2CWorld* world, int32_t bodyId, B2CVec2 position, B2CRot rotation);
+int32_t b2cuda_body_set_linear_velocity(B2CWorld* world, int32_t bodyId, B2CVec2 v);
+int32_t b2cuda_body_set_angular_velocity(B2CWorld* world, int32_t bodyId, float w);
+int32_t b2cuda_body_apply_force_to_center(B2CWorld* world, int32_t bodyId, B2CVec2 force, int32_t wake);
+int32_t b2cuda_body_apply_torque(B2CWorld* world, int32_t bodyId, float torque, int32_t wake);
+int32_t b2cuda_body_apply_linear_impulse_to_center(B2CWorld* world, int32_t bodyId, B2CVec2 impulse, int32_t wake);
+/* WorldAPI.SetGravity :698 / EnableWarmStarting :801 / EnableSpeculative :941 / EnableContinuous :654 / SetContactTuning :780 */
+int32_t b2cuda_world_set_gravity(B2CWorld* world, B2CVec2 gravity);
+int32_t b2cuda_world_enable_warm_starting(B2CWorld* world, int32_t flag);
+int32_t b2cuda_world_enable_speculative(B2CWorld* world, int32_t flag);
+int32_t b2cuda_world_enable_continuous(B2CWorld* world, int32_t flag);
+int32_t b2cuda_world_set_contact_tuning(B2CWorld* world, float hertz, float dampingRatio, float pushSpeed);
+
+/* WorldAPI.Step — api/World.cs:31-113. Asynchronous on the world's stream; read-backs synchronise. */
+int32_t b2cuda_world_step(B2CWorld* world, float timeStep, int32_t subStepCount);
+int32_t b2cuda_world_synchronize(B2CWorld* world);
+
+/* WorldAPI.GetContactEvents — api/World.cs:302-312. Pointers into library-owned pinned host memory, valid until
+ * the next step ("transient, do not store"). End events are the reference's double-buffered previous set. */
+int32_t b2cuda_world_get_contact_events(B2CWorld* world, const B2CContactTouchEvent** begin, int32_t* beginCount,
+                                        const B2CContactTouchEvent** end, int32_t* endCount,
+                                        const B2CContactHitEvent** hit, int32_t* hitCount);
+/* WorldAPI.GetJointEvents — api/World.cs:314-319: joint ids whose reaction exceeded a threshold */
+int32_t b2cuda_world_get_joint_events(B2CWorld* world, const int32_t** jointIds, int32_t* count);
+/* WorldAPI.GetBodyEvents / BodyAPI getters in bulk: record i = bodyId i (free slots zeroed) */
+int32_t b2cuda_world_read_bodies(B2CWorld* world, B2CBodyRead* dst, int32_t capacity, int32_t* count);
+/* ContactAPI.GetData for every live contact in ascending contactId */
+int32_t b2cuda_world_read_contacts(B2CWorld* world, B2CContactRead* dst, int32_t capacity, int32_t* count);
+int32_t b2cuda_world_read_joints(B2CWorld* world, B2CJointRead* dst, int32_t capacity, int32_t* count);
+int32_t b2cuda_world_read_shapes(B2CWorld* world, B2CShapeRead* dst, int32_t capacity, int32_t* count);
+int32_t b2cuda_world_get_counters(B2CWorld* world, B2CCounters* out);
+int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

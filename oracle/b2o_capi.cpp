@@ -1,0 +1,186 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see b2o_math.h header). Parity unpinned by the reference.
+// C entry points with the same shapes as include/b2cuda.h (prefix b2o_) so the same scene script can
+// drive the oracle and the product. Uses the product header for POD layouts only.
+#include "../include/b2cuda.h"
+#include "b2o_world.h"
+#include <cstring>
+#include <algorithm>
+
+using namespace b2o;
+
+static inline Vec2 V(B2CVec2 v) { return {v.x, v.y}; }
+static inline B2CVec2 CV(Vec2 v) { return {v.x, v.y}; }
+static inline Rot R(B2CRot r) { Rot q; q.c = r.c; q.s = r.s; return q; }
+static inline Transform T(B2CTransform t) { Transform x; x.p = V(t.p); x.q = R(t.q); return x; }
+
+extern "C" {
+
+int32_t b2o_world_create(const B2CWorldDef* d, World** out) {
+  WorldDef def; def.gravity = V(d->gravity); def.restitutionThreshold = d->restitutionThreshold; def.hitEventThreshold = d->hitEventThreshold;
+  def.contactHertz = d->contactHertz; def.contactDampingRatio = d->contactDampingRatio; def.contactSpeed = d->contactSpeed;
+  def.maximumLinearSpeed = d->maximumLinearSpeed; def.enableSleep = d->enableSleep != 0; def.enableContinuous = d->enableContinuous != 0;
+  def.enableContactSoftening = d->enableContactSoftening != 0;
+  *out = new World(def);
+  return 0;
+}
+int32_t b2o_world_destroy(World* w) { delete w; return 0; }
+int32_t b2o_create_body(World* w, const B2CBodyDef* d, int32_t* bodyId) {
+  BodyDef def; def.type = d->type; def.position = V(d->position); def.rotation = R(d->rotation); def.linearVelocity = V(d->linearVelocity);
+  def.angularVelocity = d->angularVelocity; def.linearDamping = d->linearDamping; def.angularDamping = d->angularDamping;
+  def.gravityScale = d->gravityScale; def.sleepThreshold = d->sleepThreshold; def.userData = d->userData;
+  def.lockLinearX = d->lockLinearX; def.lockLinearY = d->lockLinearY; def.lockAngularZ = d->lockAngularZ; def.enableSleep = d->enableSleep;
+  def.isAwake = d->isAwake; def.isBullet = d->isBullet; def.isEnabled = d->isEnabled; def.allowFastRotation = d->allowFastRotation;
+  *bodyId = w->CreateBody(def);
+  return 0;
+}
+int32_t b2o_create_shape(World* w, int32_t bodyId, const B2CShapeDef* d, const B2CGeometry* g, int32_t* shapeId) {
+  ShapeDef def; def.userData = d->userData; def.material.friction = d->friction; def.material.restitution = d->restitution;
+  def.material.rollingResistance = d->rollingResistance; def.material.tangentSpeed = d->tangentSpeed; def.material.userMaterialId = d->userMaterialId;
+  def.density = d->density; def.filter.categoryBits = d->categoryBits; def.filter.maskBits = d->maskBits; def.filter.groupIndex = d->groupIndex;
+  def.enableCustomFiltering = d->enableCustomFiltering; def.isSensor = d->isSensor; def.enableSensorEvents = d->enableSensorEvents;
+  def.enableContactEvents = d->enableContactEvents; def.enableHitEvents = d->enableHitEvents; def.enablePreSolveEvents = d->enablePreSolveEvents;
+  def.invokeContactCreation = d->invokeContactCreation; def.updateBodyMass = d->updateBodyMass;
+  Geom geom; geom.type = g->type; geom.count = g->count; geom.radius = g->radius; geom.centroid = V(g->centroid);
+  for (int i = 0; i < kMaxPolygonVertices; i++) { geom.v[i] = V(g->v[i]); geom.n[i] = V(g->n[i]); }
+  *shapeId = w->CreateShape(bodyId, def, geom);
+  return 0;
+}
+int32_t b2o_create_revolute_joint(World* w, const B2CRevoluteJointDef* d, int32_t* jointId) {
+  RevoluteJointDef def; def.bodyIdA = d->bodyIdA; def.bodyIdB = d->bodyIdB; def.localFrameA = T(d->localFrameA); def.localFrameB = T(d->localFrameB);
+  def.forceThreshold = d->forceThreshold; def.torqueThreshold = d->torqueThreshold; def.constraintHertz = d->constraintHertz;
+  def.constraintDampingRatio = d->constraintDampingRatio; def.collideConnected = d->collideConnected; def.userData = d->userData;
+  def.targetAngle = d->targetAngle; def.enableSpring = d->enableSpring; def.hertz = d->hertz; def.dampingRatio = d->dampingRatio;
+  def.enableLimit = d->enableLimit; def.lowerAngle = d->lowerAngle; def.upperAngle = d->upperAngle; def.enableMotor = d->enableMotor;
+  def.maxMotorTorque = d->maxMotorTorque; def.motorSpeed = d->motorSpeed;
+  *jointId = w->CreateRevoluteJoint(def);
+  return 0;
+}
+int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
+int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }
+int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAngularVelocity(id, x); return 0; }
+int32_t b2o_body_apply_force_to_center(World* w, int32_t id, B2CVec2 f, int32_t) { w->ApplyForceToCenter(id, V(f)); return 0; }
+int32_t b2o_body_apply_torque(World* w, int32_t id, float t, int32_t) { w->ApplyTorque(id, t); return 0; }
+int32_t b2o_body_apply_linear_impulse_to_center(World* w, int32_t id, B2CVec2 i, int32_t) { w->ApplyLinearImpulseToCenter(id, V(i)); return 0; }
+int32_t b2o_world_set_gravity(World* w, B2CVec2 g) { w->gravity = V(g); return 0; }
+int32_t b2o_world_enable_warm_starting(World* w, int32_t f) { w->enableWarmStarting = f != 0; return 0; }
+int32_t b2o_world_enable_speculative(World* w, int32_t f) { w->enableSpeculative = f != 0; return 0; }
+int32_t b2o_world_enable_continuous(World* w, int32_t f) { w->enableContinuous = f != 0; return 0; }
+int32_t b2o_world_set_contact_tuning(World* w, float hertz, float damping, float pushSpeed) {   // api/World.cs:780-787
+  w->contactHertz = netClamp(hertz, 0, FLT_MAX); w->contactDampingRatio = netClamp(damping, 0, FLT_MAX); w->contactSpeed = netClamp(pushSpeed, 0, FLT_MAX);
+  return 0;
+}
+int32_t b2o_world_step(World* w, float dt, int32_t sub) { w->Step(dt, sub); return 0; }
+int32_t b2o_world_synchronize(World*) { return 0; }
+
+static thread_local std::vector<B2CContactTouchEvent> tBegin, tEnd;
+static thread_local std::vector<B2CContactHitEvent> tHit;
+int32_t b2o_world_get_contact_events(World* w, const B2CContactTouchEvent** begin, int32_t* beginCount, const B2CContactTouchEvent** end,
+                                     int32_t* endCount, const B2CContactHitEvent** hit, int32_t* hitCount) {
+  tBegin.clear(); tEnd.clear(); tHit.clear();
+  for (auto& e : w->contactBeginEvents) tBegin.push_back({e.shapeIdA, e.shapeIdB, e.contactId, e.contactGeneration});
+  for (auto& e : w->contactEndEvents[1 - w->endEventArrayIndex]) tEnd.push_back({e.shapeIdA, e.shapeIdB, e.contactId, e.contactGeneration});
+  for (auto& e : w->contactHitEvents) tHit.push_back({e.shapeIdA, e.shapeIdB, CV(e.point), CV(e.normal), e.approachSpeed});
+  *begin = tBegin.data(); *beginCount = (int)tBegin.size(); *end = tEnd.data(); *endCount = (int)tEnd.size();
+  *hit = tHit.data(); *hitCount = (int)tHit.size();
+  return 0;
+}
+int32_t b2o_world_get_joint_events(World* w, const int32_t** ids, int32_t* count) { *ids = w->jointEvents.data(); *count = (int)w->jointEvents.size(); return 0; }
+int32_t b2o_world_read_bodies(World* w, B2CBodyRead* dst, int32_t capacity, int32_t* count) {
+  int n = (int)w->bodies.size(); *count = n;
+  for (int i = 0; i < n && i < capacity; i++) {
+    B2CBodyRead r; memset(&r, 0, sizeof(r));
+    const Body& b = w->bodies[i];
+    if (b.id != -1) {
+      const BodySim& s = w->GetBodySim(b);
+      r.transform.p = CV(s.transform.p); r.transform.q = {s.transform.q.c, s.transform.q.s}; r.center = CV(s.center); r.flags = s.flags;
+      if (const BodyState* st = w->GetBodyState(b)) { r.linearVelocity = CV(st->linearVelocity); r.angularVelocity = st->angularVelocity; }
+    }
+    dst[i] = r;
+  }
+  return 0;
+}
+static void FillPoint(B2CManifoldPointRead& o, const ManifoldPoint& p) {
+  o.point = CV(p.point); o.anchorA = CV(p.anchorA); o.anchorB = CV(p.anchorB); o.separation = p.separation; o.normalImpulse = p.normalImpulse;
+  o.tangentImpulse = p.tangentImpulse; o.totalNormalImpulse = p.totalNormalImpulse; o.normalVelocity = p.normalVelocity; o.id = p.id; o.persisted = p.persisted;
+}
+int32_t b2o_world_read_contacts(World* w, B2CContactRead* dst, int32_t capacity, int32_t* count) {
+  int n = 0;
+  for (size_t i = 0; i < w->contacts.size(); i++) {
+    const Contact& c = w->contacts[i];
+    if (c.contactId == -1) continue;
+    if (n < capacity) {
+      const ContactSim& s = w->GetContactSim(c);
+      B2CContactRead r; memset(&r, 0, sizeof(r));
+      r.contactId = c.contactId; r.shapeIdA = c.shapeIdA; r.shapeIdB = c.shapeIdB; r.colorIndex = c.colorIndex;
+      r.flags = (c.flags & kContactTouching) ? 1u : 0u; r.pointCount = s.manifold.pointCount; r.normal = CV(s.manifold.normal);
+      r.rollingImpulse = s.manifold.rollingImpulse; r.friction = s.friction; r.restitution = s.restitution;
+      r.rollingResistance = s.rollingResistance; r.tangentSpeed = s.tangentSpeed;
+      FillPoint(r.points[0], s.manifold.point0); FillPoint(r.points[1], s.manifold.point1);
+      dst[n] = r;
+    }
+    n++;
+  }
+  *count = n;
+  return 0;
+}
+int32_t b2o_world_read_joints(World* w, B2CJointRead* dst, int32_t capacity, int32_t* count) {
+  int n = 0;
+  for (size_t i = 0; i < w->joints.size(); i++) {
+    const Joint& j = w->joints[i];
+    if (j.jointId == -1 || j.colorIndex == -1) continue;
+    if (n < capacity) {
+      const JointSim& s = w->GetJointSim(j);
+      dst[n] = {j.jointId, j.colorIndex, CV(s.linearImpulse), s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse};
+    }
+    n++;
+  }
+  *count = n;
+  return 0;
+}
+int32_t b2o_world_read_shapes(World* w, B2CShapeRead* dst, int32_t capacity, int32_t* count) {
+  int n = (int)w->shapes.size(); *count = n;
+  for (int i = 0; i < n && i < capacity; i++) {
+    const Shape& s = w->shapes[i];
+    dst[i] = {CV(s.aabb.lo), CV(s.aabb.hi), CV(s.fatAABB.lo), CV(s.fatAABB.hi), s.proxyKey, s.enlargedAABB ? 1 : 0};
+  }
+  return 0;
+}
+int32_t b2o_world_get_counters(World* w, B2CCounters* out) {
+  memset(out, 0, sizeof(*out));
+  out->bodyCount = w->bodyIdPool.GetIdCount(); out->awakeBodyCount = (int)w->awakeSet.bodySims.size(); out->shapeCount = w->shapeIdPool.GetIdCount();
+  out->contactCount = w->contactIdPool.GetIdCount(); out->jointCount = w->jointIdPool.GetIdCount(); out->contactIdCapacity = w->contactIdPool.GetIdCapacity();
+  int touching = 0, active = 0;
+  for (int i = 0; i < kGraphColorCount; i++) {
+    out->colorCounts[i] = (int)(w->colors[i].contactSims.size() + w->colors[i].jointSims.size()); touching += (int)w->colors[i].contactSims.size();
+    if (i < kOverflowIndex && out->colorCounts[i] > 0) active++;
+  }
+  out->touchingContactCount = touching; out->activeColorCount = active; out->moveCount = (int)w->moveArray.size();
+  out->newPairCount = (int)w->lastNewPairKeys.size(); out->toiCandidates = w->counters.toiCandidates; out->unsupportedCount = w->counters.unsupported;
+  out->stepCount = (int)w->stepIndex;
+  return 0;
+}
+// pair keys created by the last step, in the reference's creation order (ordering rule A.3-2)
+int32_t b2o_world_get_new_pairs(World* w, uint64_t* dst, int32_t capacity, int32_t* count) {
+  *count = (int)w->lastNewPairKeys.size();
+  for (int i = 0; i < *count && i < capacity; i++) dst[i] = w->lastNewPairKeys[i];
+  return 0;
+}
+// DFS leaf rank (child2 first, src/DynamicTree.cs:539,552) of every proxy of one tree; -1 for non-leaves
+int32_t b2o_world_get_tree_ranks(World* w, int32_t treeType, int32_t* dst, int32_t capacity, int32_t* nodeCapacity) {
+  const DynamicTree& t = w->trees[treeType];
+  *nodeCapacity = (int)t.nodes.size();
+  for (int i = 0; i < capacity; i++) dst[i] = -1;
+  if (t.root == -1) return 0;
+  std::vector<int> stack{t.root}; int rank = 0;
+  while (!stack.empty()) {
+    int id = stack.back(); stack.pop_back();
+    const TreeNode& n = t.nodes[id];
+    if (n.flags & kNodeLeaf) { if (id < capacity) dst[id] = rank; rank++; }
+    else { stack.push_back(n.child1); stack.push_back(n.child2); }
+  }
+  return 0;
+}
+int32_t b2o_world_get_profile_ms(World* w, double* out8) { for (int i = 0; i < 8; i++) out8[i] = w->profileMs[i]; return 0; }
+const char* b2o_last_error(World* w) { return w->lastError.c_str(); }
+
+}  // extern "C"

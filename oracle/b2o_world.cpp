@@ -1,0 +1,291 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see b2o_math.h header). Parity unpinned by the reference.
+// Part 1: world construction, body/shape/joint creation, mass data, setters.
+#include "b2o_world.h"
+#include <cassert>
+#include <cstring>
+
+namespace b2o {
+
+static inline int ProxyType(int key) { return key & 3; }        // src/BroadPhase.cs:30-32
+static inline int ProxyId(int key) { return key >> 2; }
+static inline int ProxyKey(int id, int type) { return (id << 2) | type; }
+static inline uint64_t ShapePairKey(uint64_t k1, uint64_t k2) { return k1 < k2 ? (k1 << 32 | k2) : (k2 << 32 | k1); }  // src/Contact.cs:126
+
+World::World(const WorldDef& def) {      // src/World.cs:183-226, src/ConstraintGraph.cs:73-83
+  gravity = def.gravity; hitEventThreshold = def.hitEventThreshold; restitutionThreshold = def.restitutionThreshold;
+  maxLinearSpeed = def.maximumLinearSpeed; contactSpeed = def.contactSpeed; contactHertz = def.contactHertz;
+  contactDampingRatio = def.contactDampingRatio; enableSleep = def.enableSleep;
+  enableContactSoftening = def.enableContactSoftening; enableContinuous = def.enableContinuous;
+  for (int i = 0; i < kGraphColorCount - 1; i++) colors[i].bodySet.SetBitCountAndClear(16);
+  if (enableSleep) { counters.unsupported++; lastError = "oracle: enableSleep=true (islands/sleep) is not restated"; }
+}
+
+int World::CreateBody(const BodyDef& def) {     // api/Body.cs:16-105
+  if (!def.isEnabled || def.isBullet || !(def.isAwake || !def.enableSleep)) { counters.unsupported++; lastError = "oracle: disabled/bullet/asleep bodies not restated"; }
+  int setId = def.type == kStaticBody ? kStaticSet : kAwakeSet;
+  int bodyId = bodyIdPool.AllocId();
+  uint32_t lockFlags = (def.lockLinearX ? kLockLinearX : 0) | (def.lockLinearY ? kLockLinearY : 0) | (def.lockAngularZ ? kLockAngularZ : 0) |
+                       (def.isBullet ? kIsBullet : 0) | (def.allowFastRotation ? kAllowFastRotation : 0);
+  SolverSet& set = setId == kStaticSet ? staticSet : awakeSet;
+  BodySim sim;
+  sim.transform.p = def.position; sim.transform.q = def.rotation; sim.center = def.position; sim.rotation0 = def.rotation;
+  sim.center0 = def.position; sim.minExtent = kHuge; sim.maxExtent = 0; sim.linearDamping = def.linearDamping;
+  sim.angularDamping = def.angularDamping; sim.gravityScale = def.gravityScale; sim.bodyId = bodyId;
+  sim.flags = lockFlags | (def.type == kDynamicBody ? kDynamicFlag : 0);
+  set.bodySims.push_back(sim);
+  if (setId == kAwakeSet) {
+    BodyState st; st.linearVelocity = def.linearVelocity; st.angularVelocity = def.angularVelocity; st.flags = sim.flags;
+    set.bodyStates.push_back(st);
+  }
+  if (bodyId == (int)bodies.size()) bodies.emplace_back();
+  Body& body = bodies[bodyId];
+  uint16_t gen = body.generation;
+  body = Body();
+  body.generation = (uint16_t)(gen + 1);
+  body.userData = def.userData; body.setIndex = setId; body.localIndex = (int)set.bodySims.size() - 1;
+  body.id = bodyId; body.sleepThreshold = def.sleepThreshold; body.type = def.type; body.flags = sim.flags; body.enableSleep = def.enableSleep;
+  return bodyId;
+}
+
+int World::BroadPhaseCreateProxy(int proxyType, const AABB& aabb, uint64_t categoryBits, int shapeIndex, bool forcePairCreation) {
+  // src/BroadPhase.cs:71-79
+  int proxyId = trees[proxyType].CreateProxy(aabb, categoryBits, (uint64_t)shapeIndex);
+  int proxyKey = ProxyKey(proxyId, proxyType);
+  if (proxyType != kStaticBody || forcePairCreation) BufferMove(proxyKey);
+  return proxyKey;
+}
+
+void World::UpdateShapeAABBs(Shape& s, const Transform& xf, int proxyType) {    // src/Shape.cs:64-75
+  AABB aabb = ComputeAABB(s.geom, xf);
+  aabb.lo.x -= kSpeculativeDistance; aabb.lo.y -= kSpeculativeDistance; aabb.hi.x += kSpeculativeDistance; aabb.hi.y += kSpeculativeDistance;
+  s.aabb = aabb;
+  float margin = proxyType == kStaticBody ? kSpeculativeDistance : kAABBMargin;
+  s.fatAABB = {{aabb.lo.x - margin, aabb.lo.y - margin}, {aabb.hi.x + margin, aabb.hi.y + margin}};
+}
+
+int World::CreateShape(int bodyId, const ShapeDef& def, const Geom& geom) {     // api/Shape.cs:8-24, src/Shape.cs:171-218
+  if (def.isSensor || geom.type == kChainSegment) { counters.unsupported++; lastError = "oracle: sensors/chain segments not restated"; }
+  Body& body = bodies[bodyId];
+  Transform transform = GetBodySim(body).transform;
+  int shapeId = shapeIdPool.AllocId();
+  if (shapeId == (int)shapes.size()) shapes.emplace_back();
+  Shape& shape = shapes[shapeId];
+  uint16_t gen = shape.generation;
+  shape = Shape();
+  shape.generation = (uint16_t)(gen + 1);
+  shape.geom = geom; shape.id = shapeId; shape.bodyId = body.id; shape.density = def.density; shape.material = def.material;
+  shape.filter = def.filter; shape.userData = def.userData; shape.enableSensorEvents = def.enableSensorEvents;
+  shape.enableContactEvents = def.enableContactEvents; shape.enableCustomFiltering = def.enableCustomFiltering;
+  shape.enableHitEvents = def.enableHitEvents; shape.enablePreSolveEvents = def.enablePreSolveEvents;
+  shape.localCentroid = GetCentroid(geom);
+  {
+    int proxyType = body.type;     // src/Shape.cs:126-131
+    UpdateShapeAABBs(shape, transform, proxyType);
+    shape.proxyKey = BroadPhaseCreateProxy(proxyType, shape.fatAABB, shape.filter.categoryBits, shapeId, def.invokeContactCreation || def.isSensor);
+  }
+  if (body.headShapeId != -1) shapes[body.headShapeId].prevShapeId = shapeId;
+  shape.prevShapeId = -1; shape.nextShapeId = body.headShapeId; body.headShapeId = shapeId; body.shapeCount++;
+  shape.sensorIndex = -1;
+  if (def.updateBodyMass) UpdateBodyMassData(body);
+  return shapeId;
+}
+
+void World::UpdateBodyMassData(Body& body) {      // src/Body.cs:255-353
+  BodySim& bodySim = GetBodySim(body);
+  body.mass = 0; body.inertia = 0; bodySim.invMass = 0; bodySim.invInertia = 0; bodySim.localCenter = {0, 0};
+  bodySim.minExtent = kHuge; bodySim.maxExtent = 0;
+  if (body.type != kDynamicBody) {
+    bodySim.center = bodySim.transform.p; bodySim.center0 = bodySim.center;
+    if (body.type == kKinematicBody) {
+      int shapeId = body.headShapeId;
+      while (shapeId != -1) {
+        const Shape& s = shapes[shapeId];
+        ShapeExtent extent = ComputeExtent(s.geom, {0, 0});
+        bodySim.minExtent = netMin(bodySim.minExtent, extent.minExtent);
+        bodySim.maxExtent = netMax(bodySim.maxExtent, extent.maxExtent);
+        shapeId = s.nextShapeId;
+      }
+    }
+    return;
+  }
+  int shapeCount = body.shapeCount;
+  std::vector<MassData> masses(shapeCount);
+  Vec2 localCenter = {0, 0};
+  int shapeIndex = 0;
+  int shapeId = body.headShapeId;
+  while (shapeId != -1) {
+    const Shape& s = shapes[shapeId];
+    shapeId = s.nextShapeId;
+    if (s.density == 0) { masses[shapeIndex] = MassData(); continue; }
+    MassData massData = ComputeMass(s.geom, s.density);
+    body.mass += massData.mass;
+    localCenter = MulAdd(localCenter, massData.mass, massData.center);
+    masses[shapeIndex] = massData;
+    shapeIndex++;
+  }
+  if (body.mass > 0) { bodySim.invMass = 1 / body.mass; localCenter = bodySim.invMass * localCenter; }
+  for (shapeIndex = 0; shapeIndex < shapeCount; shapeIndex++) {
+    MassData massData = masses[shapeIndex];
+    if (massData.mass == 0) continue;
+    Vec2 offset = localCenter - massData.center;
+    float inertia = massData.rotationalInertia + massData.mass * Dot(offset, offset);
+    body.inertia += inertia;
+  }
+  if (body.inertia > 0) bodySim.invInertia = 1 / body.inertia; else { body.inertia = 0; bodySim.invInertia = 0; }
+  Vec2 oldCenter = bodySim.center;
+  bodySim.localCenter = localCenter;
+  bodySim.center = TransformPoint(bodySim.transform, bodySim.localCenter);
+  bodySim.center0 = bodySim.center;
+  BodyState* state = GetBodyState(body);
+  if (state) { Vec2 deltaLinear = CrossSV(state->angularVelocity, bodySim.center - oldCenter); state->linearVelocity = state->linearVelocity + deltaLinear; }
+  shapeId = body.headShapeId;
+  while (shapeId != -1) {
+    const Shape& s = shapes[shapeId];
+    ShapeExtent extent = ComputeExtent(s.geom, localCenter);
+    bodySim.minExtent = netMin(bodySim.minExtent, extent.minExtent);
+    bodySim.maxExtent = netMax(bodySim.maxExtent, extent.maxExtent);
+    shapeId = s.nextShapeId;
+  }
+}
+
+bool World::ShouldBodiesCollide(const Body& bodyA, const Body& bodyB) const {   // src/Body.cs:354-371
+  if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) return false;
+  int jointKey, otherBodyId;
+  if (bodyA.jointCount < bodyB.jointCount) { jointKey = bodyA.headJointKey; otherBodyId = bodyB.id; }
+  else { jointKey = bodyB.headJointKey; otherBodyId = bodyA.id; }
+  while (jointKey != -1) {
+    int jointId = jointKey >> 1, edgeIndex = jointKey & 1, otherEdgeIndex = edgeIndex ^ 1;
+    const Joint& joint = joints[jointId];
+    if (!joint.collideConnected && (otherEdgeIndex == 1 ? joint.edge1.bodyId : joint.edge0.bodyId) == otherBodyId) return false;
+    jointKey = edgeIndex == 1 ? joint.edge1.nextKey : joint.edge0.nextKey;
+  }
+  return true;
+}
+
+int World::AssignJointColor(int bodyIdA, int bodyIdB, int typeA, int typeB) {   // src/ConstraintGraph.cs:91-128
+  if (typeA != kStaticBody && typeB != kStaticBody) {
+    for (int i = 0; i < kDynamicColorCount; i++) {
+      GraphColor& color = colors[i];
+      if (color.bodySet.GetBit(bodyIdA) || color.bodySet.GetBit(bodyIdB)) continue;
+      if (typeA == kDynamicBody) color.bodySet.SetBitGrow(bodyIdA);
+      if (typeB == kDynamicBody) color.bodySet.SetBitGrow(bodyIdB);
+      return i;
+    }
+  } else if (typeA == kDynamicBody) {
+    for (int i = kGraphColorCount - 2; i >= 1; i--) {
+      GraphColor& color = colors[i];
+      if (color.bodySet.GetBit(bodyIdA)) continue;
+      color.bodySet.SetBitGrow(bodyIdA); return i;
+    }
+  } else if (typeB == kDynamicBody) {
+    for (int i = kGraphColorCount - 2; i >= 1; i--) {
+      GraphColor& color = colors[i];
+      if (color.bodySet.GetBit(bodyIdB)) continue;
+      color.bodySet.SetBitGrow(bodyIdB); return i;
+    }
+  }
+  return kOverflowIndex;
+}
+
+int World::CreateRevoluteJoint(const RevoluteJointDef& def) {    // src/joints/RevoluteJoint.cs:32-56, src/Joint.cs:181-296
+  Body& bodyA = bodies[def.bodyIdA]; Body& bodyB = bodies[def.bodyIdB];
+  int bodyIdA = bodyA.id, bodyIdB = bodyB.id;
+  int jointId = jointIdPool.AllocId();
+  if (jointId == (int)joints.size()) joints.emplace_back();
+  Joint& joint = joints[jointId];
+  uint16_t gen = joint.generation;
+  joint = Joint();
+  joint.generation = (uint16_t)(gen + 1);
+  joint.jointId = jointId; joint.userData = def.userData; joint.type = 4; joint.collideConnected = def.collideConnected;
+  joint.edge0.bodyId = bodyIdA; joint.edge0.prevKey = -1; joint.edge0.nextKey = bodyA.headJointKey;
+  int keyA = jointId << 1;
+  if (bodyA.headJointKey != -1) {
+    Joint& jointA = joints[bodyA.headJointKey >> 1];
+    if (bodyA.headJointKey & 1) jointA.edge1.prevKey = keyA; else jointA.edge0.prevKey = keyA;
+  }
+  bodyA.headJointKey = keyA; bodyA.jointCount++;
+  joint.edge1.bodyId = bodyIdB; joint.edge1.prevKey = -1; joint.edge1.nextKey = bodyB.headJointKey;
+  int keyB = (jointId << 1) | 1;
+  if (bodyB.headJointKey != -1) {
+    Joint& jointB = joints[bodyB.headJointKey >> 1];
+    if (bodyA.headJointKey & 1) jointB.edge1.prevKey = keyB; else jointB.edge0.prevKey = keyB;   // Q11: tests bodyA's key
+  }
+  bodyB.headJointKey = keyB; bodyB.jointCount++;
+  if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) { counters.unsupported++; lastError = "oracle: joint between two non-dynamic bodies (static set) not restated"; return jointId; }
+  joint.setIndex = kAwakeSet;
+  int colorIndex = AssignJointColor(bodyIdA, bodyIdB, bodyA.type, bodyB.type);   // src/ConstraintGraph.cs:242-251
+  JointSim sim; sim.jointId = jointId; sim.bodyIdA = bodyIdA; sim.bodyIdB = bodyIdB;
+  sim.localFrameA = def.localFrameA; sim.localFrameB = def.localFrameB; sim.type = 4;
+  sim.constraintHertz = def.constraintHertz; sim.constraintDampingRatio = def.constraintDampingRatio;
+  sim.constraintSoftness.biasRate = 0; sim.constraintSoftness.massScale = 1; sim.constraintSoftness.impulseScale = 0;
+  sim.forceThreshold = def.forceThreshold; sim.torqueThreshold = def.torqueThreshold;
+  sim.targetAngle = netClamp(def.targetAngle, -kPi, kPi); sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio;
+  sim.lowerAngle = def.lowerAngle; sim.upperAngle = def.upperAngle; sim.maxMotorTorque = def.maxMotorTorque; sim.motorSpeed = def.motorSpeed;
+  sim.enableSpring = def.enableSpring; sim.enableLimit = def.enableLimit; sim.enableMotor = def.enableMotor;
+  colors[colorIndex].jointSims.push_back(sim);
+  joint.colorIndex = colorIndex; joint.localIndex = (int)colors[colorIndex].jointSims.size() - 1;
+  if (!def.collideConnected) DestroyContactsBetweenBodies(bodyA, bodyB);
+  return jointId;
+}
+
+void World::DestroyContactsBetweenBodies(Body& bodyA, Body& bodyB) {    // src/Joint.cs:155-180
+  int contactKey, otherBodyId;
+  if (bodyA.contactCount < bodyB.contactCount) { contactKey = bodyA.headContactKey; otherBodyId = bodyB.id; }
+  else { contactKey = bodyB.headContactKey; otherBodyId = bodyA.id; }
+  while (contactKey != -1) {
+    int contactId = contactKey >> 1, edgeIndex = contactKey & 1;
+    Contact& contact = contacts[contactId];
+    contactKey = edgeIndex == 1 ? contact.edge1.nextKey : contact.edge0.nextKey;
+    int otherEdgeIndex = edgeIndex ^ 1;
+    if ((otherEdgeIndex == 1 ? contact.edge1.bodyId : contact.edge0.bodyId) == otherBodyId) DestroyContact(contact);
+  }
+}
+
+void World::SetTransform(int bodyId, Vec2 position, Rot rotation) {      // api/Body.cs:293-325
+  Body& body = bodies[bodyId];
+  BodySim& bodySim = GetBodySim(body);
+  bodySim.transform.p = position; bodySim.transform.q = rotation;
+  bodySim.center = TransformPoint(bodySim.transform, bodySim.localCenter);
+  bodySim.rotation0 = bodySim.transform.q; bodySim.center0 = bodySim.center;
+  Transform transform = bodySim.transform;
+  int shapeId = body.headShapeId;
+  while (shapeId != -1) {
+    Shape& shape = shapes[shapeId];
+    AABB aabb = ComputeAABB(shape.geom, transform);
+    aabb.lo.x -= kSpeculativeDistance; aabb.lo.y -= kSpeculativeDistance; aabb.hi.x += kSpeculativeDistance; aabb.hi.y += kSpeculativeDistance;
+    shape.aabb = aabb;
+    if (!Contains(shape.fatAABB, aabb)) {
+      AABB fat = {{aabb.lo.x - kAABBMargin, aabb.lo.y - kAABBMargin}, {aabb.hi.x + kAABBMargin, aabb.hi.y + kAABBMargin}};
+      shape.fatAABB = fat;
+      if (shape.proxyKey != -1) { trees[ProxyType(shape.proxyKey)].MoveProxy(ProxyId(shape.proxyKey), fat); BufferMove(shape.proxyKey); }   // src/BroadPhase.cs:89-95
+    }
+    shapeId = shape.nextShapeId;
+  }
+}
+void World::SetLinearVelocity(int bodyId, Vec2 v) {       // api/Body.cs:359-367
+  Body& body = bodies[bodyId]; if (body.type == kStaticBody) return;
+  if (BodyState* s = GetBodyState(body)) s->linearVelocity = v;
+}
+void World::SetAngularVelocity(int bodyId, float w) {     // api/Body.cs:369-377
+  Body& body = bodies[bodyId]; if (body.type == kStaticBody) return;
+  if (BodyState* s = GetBodyState(body)) s->angularVelocity = w;
+}
+void World::ApplyForceToCenter(int bodyId, Vec2 force) {  // api/Body.cs:457-467
+  Body& body = bodies[bodyId]; if (body.type != kDynamicBody) return;
+  if (body.setIndex == kAwakeSet) { BodySim& sim = GetBodySim(body); sim.force = sim.force + force; }
+}
+void World::ApplyTorque(int bodyId, float torque) {       // api/Body.cs:469-479 (assigns, port quirk)
+  Body& body = bodies[bodyId]; if (body.type != kDynamicBody) return;
+  if (body.setIndex == kAwakeSet) GetBodySim(body).torque = torque;
+}
+void World::ApplyLinearImpulseToCenter(int bodyId, Vec2 impulse) {   // api/Body.cs:531-545, src/Body.cs:131-135
+  Body& body = bodies[bodyId]; if (body.type != kDynamicBody) return;
+  if (body.setIndex == kAwakeSet) {
+    BodyState& st = awakeSet.bodyStates[body.localIndex]; const BodySim& sim = awakeSet.bodySims[body.localIndex];
+    st.linearVelocity = MulAdd(st.linearVelocity, sim.invMass, impulse);
+    float v2 = LengthSquared(st.linearVelocity);
+    if (v2 > maxLinearSpeed * maxLinearSpeed) st.linearVelocity = st.linearVelocity * (maxLinearSpeed / sqrtf(v2));
+  }
+}
+
+}  // namespace b2o
