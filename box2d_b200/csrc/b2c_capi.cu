@@ -1,0 +1,95 @@
+// libb2cuda — C-ABI entry points declared in include/b2cuda.h. No exceptions cross the ABI; every call returns a status.
+#include "b2c_host.cuh"
+#include <cstring>
+#include <new>
+
+using namespace b2c;
+
+struct B2CWorld { World* w; };
+static thread_local std::string g_lastError;
+static int done(B2CWorld* h, int rc) { if (rc != B2C_OK && h && h->w) g_lastError = h->w->error; return rc; }
+#define CHECK_HANDLE(h) do { if (!(h) || !(h)->w) { g_lastError = "null world handle"; return B2C_E_INVALID; } } while (0)
+
+extern "C" {
+
+const char* b2cuda_last_error(void) { return g_lastError.c_str(); }
+
+int32_t b2cuda_default_world_def(B2CWorldDef* d) {          // include/Types.cs:75-144
+  if (!d) return B2C_E_INVALID;
+  memset(d, 0, sizeof(*d));
+  d->gravity = {0.0f, -10.0f}; d->restitutionThreshold = 1.0f; d->hitEventThreshold = 1.0f; d->contactHertz = 30.0f;
+  d->contactDampingRatio = 10.0f; d->contactSpeed = 3.0f; d->maximumLinearSpeed = 400.0f;
+  d->enableSleep = 1; d->enableContinuous = 1; d->enableContactSoftening = 0;
+  return B2C_OK;
+}
+int32_t b2cuda_default_body_def(B2CBodyDef* d) {            // include/Types.cs:170-223
+  if (!d) return B2C_E_INVALID;
+  memset(d, 0, sizeof(*d));
+  d->type = 0; d->rotation = {1.0f, 0.0f}; d->gravityScale = 1.0f; d->sleepThreshold = 0.05f; d->enableSleep = 1; d->isAwake = 1; d->isEnabled = 1;
+  return B2C_OK;
+}
+int32_t b2cuda_default_shape_def(B2CShapeDef* d) {          // include/Types.cs:285-344
+  if (!d) return B2C_E_INVALID;
+  memset(d, 0, sizeof(*d));
+  d->friction = 0.6f; d->density = 1.0f; d->categoryBits = ~0ull; d->maskBits = ~0ull; d->invokeContactCreation = 1; d->updateBodyMass = 1;
+  return B2C_OK;
+}
+int32_t b2cuda_default_revolute_joint_def(B2CRevoluteJointDef* d) {   // include/Types.cs:431-456,569-597
+  if (!d) return B2C_E_INVALID;
+  memset(d, 0, sizeof(*d));
+  d->bodyIdA = -1; d->bodyIdB = -1; d->localFrameA.q = {1.0f, 0.0f}; d->localFrameB.q = {1.0f, 0.0f};
+  d->forceThreshold = FLT_MAX; d->torqueThreshold = FLT_MAX; d->constraintHertz = 60.0f; d->constraintDampingRatio = 2.0f; d->drawScale = 1.0f;
+  return B2C_OK;
+}
+
+int32_t b2cuda_world_create(const B2CWorldDef* def, int32_t device, B2CWorld** out) {
+  if (!def || !out) { g_lastError = "null argument"; return B2C_E_INVALID; }
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) { g_lastError = std::string("no usable CUDA device: ") + cudaGetErrorString(e) + " (libb2cuda has no CPU fallback)"; return B2C_E_NO_DEVICE; }
+  if (device < 0 || device >= count) { g_lastError = "device index out of range"; return B2C_E_NO_DEVICE; }
+  if (def->enableSleep) { g_lastError = "enableSleep=1 (islands/sleep, src/Island.cs) is not supported in this build; set enableSleep=0"; return B2C_E_UNSUPPORTED; }
+  B2CWorld* h = new (std::nothrow) B2CWorld();
+  if (!h) return B2C_E_INVALID;
+  h->w = new (std::nothrow) World(*def, device);
+  if (!h->w) { delete h; return B2C_E_INVALID; }
+  *out = h;
+  return B2C_OK;
+}
+int32_t b2cuda_world_destroy(B2CWorld* h) { if (!h) return B2C_E_INVALID; delete h->w; delete h; return B2C_OK; }
+
+int32_t b2cuda_create_body(B2CWorld* h, const B2CBodyDef* def, int32_t* bodyId) { CHECK_HANDLE(h); if (!def || !bodyId) return B2C_E_INVALID; return done(h, h->w->createBody(*def, bodyId)); }
+int32_t b2cuda_create_shape(B2CWorld* h, int32_t bodyId, const B2CShapeDef* def, const B2CGeometry* g, int32_t* shapeId) {
+  CHECK_HANDLE(h); if (!def || !g || !shapeId) return B2C_E_INVALID; return done(h, h->w->createShape(bodyId, *def, *g, shapeId));
+}
+int32_t b2cuda_create_revolute_joint(B2CWorld* h, const B2CRevoluteJointDef* def, int32_t* jointId) { CHECK_HANDLE(h); if (!def || !jointId) return B2C_E_INVALID; return done(h, h->w->createRevoluteJoint(*def, jointId)); }
+int32_t b2cuda_body_set_transform(B2CWorld* h, int32_t id, B2CVec2 p, B2CRot q) { CHECK_HANDLE(h); return done(h, h->w->setTransform(id, mk(p.x, p.y), mkRot(q.c, q.s))); }
+int32_t b2cuda_body_set_linear_velocity(B2CWorld* h, int32_t id, B2CVec2 v) { CHECK_HANDLE(h); return done(h, h->w->setLinearVelocity(id, mk(v.x, v.y))); }
+int32_t b2cuda_body_set_angular_velocity(B2CWorld* h, int32_t id, float w) { CHECK_HANDLE(h); return done(h, h->w->setAngularVelocity(id, w)); }
+int32_t b2cuda_body_apply_force_to_center(B2CWorld* h, int32_t id, B2CVec2 f, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyForceToCenter(id, mk(f.x, f.y))); }
+int32_t b2cuda_body_apply_torque(B2CWorld* h, int32_t id, float t, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyTorque(id, t)); }
+int32_t b2cuda_body_apply_linear_impulse_to_center(B2CWorld* h, int32_t id, B2CVec2 i, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyLinearImpulseToCenter(id, mk(i.x, i.y))); }
+int32_t b2cuda_world_set_gravity(B2CWorld* h, B2CVec2 g) { CHECK_HANDLE(h); h->w->gravity = mk(g.x, g.y); return B2C_OK; }
+int32_t b2cuda_world_enable_warm_starting(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableWarmStarting = f != 0; return B2C_OK; }
+int32_t b2cuda_world_enable_speculative(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableSpeculative = f != 0; return B2C_OK; }
+int32_t b2cuda_world_enable_continuous(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableContinuous = f != 0; return B2C_OK; }
+int32_t b2cuda_world_set_contact_tuning(B2CWorld* h, float hertz, float damping, float push) {   // api/World.cs:780-787
+  CHECK_HANDLE(h);
+  h->w->contactHertz = netClamp(hertz, 0.0f, FLT_MAX); h->w->contactDampingRatio = netClamp(damping, 0.0f, FLT_MAX); h->w->contactSpeed = netClamp(push, 0.0f, FLT_MAX);
+  return B2C_OK;
+}
+int32_t b2cuda_world_step(B2CWorld* h, float dt, int32_t sub) { CHECK_HANDLE(h); return done(h, h->w->step(dt, sub)); }
+int32_t b2cuda_world_synchronize(B2CWorld* h) { CHECK_HANDLE(h); return done(h, h->w->synchronize()); }
+int32_t b2cuda_world_get_contact_events(B2CWorld* h, const B2CContactTouchEvent** b, int32_t* nb, const B2CContactTouchEvent** e, int32_t* ne, const B2CContactHitEvent** hit, int32_t* nh) {
+  CHECK_HANDLE(h); return done(h, h->w->getContactEvents(b, nb, e, ne, hit, nh));
+}
+int32_t b2cuda_world_get_joint_events(B2CWorld* h, const int32_t** ids, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->getJointEvents(ids, n)); }
+int32_t b2cuda_world_read_bodies(B2CWorld* h, B2CBodyRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readBodies(dst, cap, n)); }
+int32_t b2cuda_world_read_contacts(B2CWorld* h, B2CContactRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readContacts(dst, cap, n)); }
+int32_t b2cuda_world_read_joints(B2CWorld* h, B2CJointRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readJoints(dst, cap, n)); }
+int32_t b2cuda_world_read_shapes(B2CWorld* h, B2CShapeRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readShapes(dst, cap, n)); }
+int32_t b2cuda_world_get_counters(B2CWorld* h, B2CCounters* out) { CHECK_HANDLE(h); return done(h, h->w->getCounters(out)); }
+int32_t b2cuda_world_get_profile(B2CWorld* h, B2CProfile* out) { CHECK_HANDLE(h); return done(h, h->w->getProfile(out)); }
+
+}  // extern "C"

@@ -1,0 +1,691 @@
+// libb2cuda — host-side creation API, device upload and read-back (see b2c_host.cuh).
+// Mirrors api/Body.cs:16-105 (CreateBody), src/Shape.cs:171-218 (CreateShapeInternal), src/Body.cs:255-353
+// (UpdateBodyMassData), src/joints/RevoluteJoint.cs:32-56 + src/Joint.cs:181-296 (CreateJoint),
+// src/ConstraintGraph.cs:91-128 (AssignJointColor). None of this is on the step path.
+#include "b2c_host.cuh"
+#include <cstring>
+#include <cstdio>
+#include <algorithm>
+
+namespace b2c {
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(B2C_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+static inline int proxyKeyOf(int id, int type) { return (id << 2) | type; }
+
+// ---- mass / extent (include/Collision.cs:82-92,205-228,431-497,649-653) ----
+struct MassData { float mass; V2 center; float rotationalInertia; };
+static MassData circleMass(V2 center, float radius, float density) {
+  float rr = radius * radius, mass = density * kPi * rr;
+  MassData m; m.mass = mass; m.center = center; m.rotationalInertia = mass * 0.5f * rr; return m;
+}
+static MassData capsuleMass(V2 p1, V2 p2, float radius, float density) {
+  float rr = radius * radius;
+  float ll = distSq(p1, p2), len = sqrtf(ll);
+  float circleM = density * (kPi * radius * radius);
+  float boxM = density * (2.0f * radius * radius);
+  MassData m; m.mass = circleM + boxM; m.center = mk(0.5f * (p1.x + p2.x), 0.5f * (p1.y + p2.y));
+  float lc = 4.0f * radius / (3.0f * kPi);
+  float h = 0.5f * len;
+  float circleInertia = circleM * (0.5f * rr + h * h + 2.0f * h * lc);
+  float boxInertia = boxM * (4.0f * rr + ll) / 12.0f;
+  m.rotationalInertia = circleInertia + boxInertia;
+  return m;
+}
+static MassData geomMass(const Geom& g, float density) {
+  MassData zero; zero.mass = 0; zero.center = mk(0, 0); zero.rotationalInertia = 0;
+  if (g.type == kCircle) return circleMass(g.v[0], g.radius, density);
+  if (g.type == kCapsule) return capsuleMass(g.v[0], g.v[1], g.radius, density);
+  if (g.type != kPolygon) return zero;
+  if (g.count == 1) return circleMass(g.v[0], g.radius, density);
+  if (g.count == 2) return capsuleMass(g.v[0], g.v[1], g.radius, density);
+  V2 verts[kMaxPolygonVertices];
+  if (g.radius > 0.0f) {
+    const float sqrt2 = 1.4142135623730950488016887242097f;
+    for (int i = 0, j = g.count - 1; i < g.count; j = i++) {
+      V2 mid = normalize(g.n[j] + g.n[i]);
+      verts[i] = mulAdd(g.v[i], sqrt2 * g.radius, mid);
+    }
+  } else for (int i = 0; i < g.count; i++) verts[i] = g.v[i];
+  V2 center = mk(0, 0);
+  float area = 0, rotationalInertia = 0;
+  V2 r = verts[0];
+  const float inv3 = 1.0f / 3.0f;
+  for (int i = 1; i < g.count - 1; i++) {
+    V2 e1 = verts[i] - r, e2 = verts[i + 1] - r;
+    float D = cross(e1, e2);
+    float triArea = 0.5f * D;
+    area += triArea;
+    center = mulAdd(center, triArea * inv3, e1 + e2);
+    float intx2 = e1.x * e1.x + e2.x * e1.x + e2.x * e2.x;
+    float inty2 = e1.y * e1.y + e2.y * e1.y + e2.y * e2.y;
+    rotationalInertia += 0.25f * inv3 * D * (intx2 + inty2);
+  }
+  float invArea = 1.0f / area;
+  center.x *= invArea; center.y *= invArea;
+  MassData m;
+  m.mass = density * area;
+  m.center = r + center;
+  m.rotationalInertia = density * rotationalInertia - density * area * dot(center, center);
+  return m;
+}
+static void geomExtent(const Geom& g, V2 localCenter, float* minExtent, float* maxExtent) {
+  if (g.type == kCircle) { *minExtent = g.radius; *maxExtent = dist(g.v[0], localCenter) + g.radius; }
+  else if (g.type == kCapsule) { *minExtent = g.radius; *maxExtent = sqrtf(netMax(distSq(g.v[0], localCenter), distSq(g.v[1], localCenter))) + g.radius; }
+  else if (g.type == kSegment) { *minExtent = 0; *maxExtent = sqrtf(netMax(distSq(g.v[0], localCenter), distSq(g.v[1], localCenter))); }
+  else {
+    float mn = kHuge, mxSq = 0;
+    for (int i = 0; i < g.count; i++) {
+      float planeOffset = dot(g.n[i], g.v[i] - g.centroid);
+      mn = netMin(mn, planeOffset);
+      mxSq = netMax(mxSq, distSq(g.v[i], localCenter));
+    }
+    *minExtent = mn + g.radius; *maxExtent = sqrtf(mxSq) + g.radius;
+  }
+}
+
+World::World(const B2CWorldDef& def, int device) : device_(device) {
+  gravity = mk(def.gravity.x, def.gravity.y);
+  restitutionThreshold = def.restitutionThreshold; hitEventThreshold = def.hitEventThreshold; contactHertz = def.contactHertz;
+  contactDampingRatio = def.contactDampingRatio; contactSpeed = def.contactSpeed; maxLinearSpeed = def.maximumLinearSpeed;
+  enableSleep = def.enableSleep != 0; enableContinuous = def.enableContinuous != 0; enableContactSoftening = def.enableContactSoftening != 0;
+  capHintBody = def.bodyCapacity; capHintShape = def.shapeCapacity; capHintContact = def.contactCapacity; capHintJoint = def.jointCapacity;
+  moved_.resize(3);
+  colorJoints_.resize(kGraphColorCount);
+}
+
+World::~World() { freeDevice(); }
+
+void World::freeDevice() {
+  if (device_ >= 0) cudaSetDevice(device_);
+  for (void* p : allocs_) cudaFree(p);
+  allocs_.clear();
+  if (hostScalars_) cudaFreeHost(hostScalars_);
+  if (hBegin_) cudaFreeHost(hBegin_);
+  if (hEnd_) cudaFreeHost(hEnd_);
+  if (hHit_) cudaFreeHost(hHit_);
+  if (hJointEvents_) cudaFreeHost(hJointEvents_);
+  hostScalars_ = nullptr; hBegin_ = hEnd_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
+  for (auto& e : ev_) if (e) { cudaEventDestroy(e); e = nullptr; }
+  if (stream_) { cudaStreamDestroy(stream_); stream_ = nullptr; }
+}
+
+void World::bufferMove(int key) {                 // src/BroadPhase.cs:56-59
+  int type = key & 3, id = key >> 2;
+  auto& m = moved_[type];
+  if ((int)m.size() <= id) m.resize(id + 1, 0);
+  if (!m[id]) { m[id] = 1; moveArray_.push_back(key); }
+}
+
+int World::createBody(const B2CBodyDef& def, int* bodyId) {
+  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_body after the first step is not supported in this build");
+  if (!def.isEnabled || def.isBullet || !(def.isAwake || !def.enableSleep))
+    return fail(B2C_E_UNSUPPORTED, "disabled / bullet / initially-asleep bodies are not supported");
+  int id = bodyIds_.alloc();
+  if (id == (int)bodies_.size()) bodies_.emplace_back();
+  HBody& b = bodies_[id];
+  uint16_t gen = b.generation;
+  b = HBody();
+  b.generation = (uint16_t)(gen + 1);
+  b.id = id; b.type = def.type; b.userData = def.userData; b.sleepThreshold = def.sleepThreshold; b.enableSleep = def.enableSleep != 0;
+  b.flags = (def.lockLinearX ? kLockLinearX : 0) | (def.lockLinearY ? kLockLinearY : 0) | (def.lockAngularZ ? kLockAngularZ : 0) |
+            (def.allowFastRotation ? kAllowFastRotation : 0) | (def.type == kDynamicBody ? kDynamicFlag : 0);
+  b.xf.p = mk(def.position.x, def.position.y); b.xf.q = mkRot(def.rotation.c, def.rotation.s);
+  b.center = b.xf.p; b.center0 = b.xf.p; b.rot0 = b.xf.q; b.localCenter = mk(0, 0); b.force = mk(0, 0);
+  b.linearDamping = def.linearDamping; b.angularDamping = def.angularDamping; b.gravityScale = def.gravityScale;
+  b.v = mk(def.linearVelocity.x, def.linearVelocity.y); b.w = def.angularVelocity;
+  if (def.type != kStaticBody) { b.simIndex = (int)awakeOrder_.size(); awakeOrder_.push_back(id); }
+  if ((int)colorMask_.size() <= id) colorMask_.resize(id + 1, 0);
+  colorMask_[id] = 0;
+  *bodyId = id;
+  return B2C_OK;
+}
+
+void World::updateShapeAABBs(HShape& s, Xf xf, int proxyType) {   // src/Shape.cs:64-75
+  Box aabb = boxGrow(geomAABB(s.geom, xf), kSpeculativeDistance);
+  s.aabb = aabb;
+  s.fat = boxGrow(aabb, proxyType == kStaticBody ? kSpeculativeDistance : kAABBMargin);
+}
+
+int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId) {
+  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_shape after the first step is not supported in this build");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  if (def.isSensor) return fail(B2C_E_UNSUPPORTED, "sensor shapes are not supported (src/Sensor.cs is out of scope)");
+  if (def.enableCustomFiltering || def.enablePreSolveEvents) return fail(B2C_E_UNSUPPORTED, "managed callbacks (custom filter / preSolve) cannot run on the device");
+  if (g.type < 0 || g.type > kPolygon) return fail(B2C_E_UNSUPPORTED, "chain segments are not supported");
+  if (g.type == kPolygon && (g.count < 1 || g.count > kMaxPolygonVertices)) return fail(B2C_E_UNSUPPORTED, "polygon vertex count must be 1..8");
+  HBody& body = bodies_[bodyId];
+  int id = shapeIds_.alloc();
+  if (id == (int)shapes_.size()) shapes_.emplace_back();
+  HShape& s = shapes_[id];
+  uint16_t gen = s.generation;
+  s = HShape();
+  s.generation = (uint16_t)(gen + 1);
+  s.id = id; s.bodyId = bodyId;
+  memset(&s.geom, 0, sizeof(Geom));
+  s.geom.type = g.type; s.geom.count = g.count; s.geom.radius = g.radius; s.geom.centroid = mk(g.centroid.x, g.centroid.y);
+  for (int i = 0; i < kMaxPolygonVertices; i++) { s.geom.v[i] = mk(g.v[i].x, g.v[i].y); s.geom.n[i] = mk(g.n[i].x, g.n[i].y); }
+  s.friction = def.friction; s.restitution = def.restitution; s.rollingResistance = def.rollingResistance; s.tangentSpeed = def.tangentSpeed;
+  s.density = def.density; s.categoryBits = def.categoryBits; s.maskBits = def.maskBits; s.groupIndex = def.groupIndex; s.userData = def.userData;
+  s.flags = (def.enableContactEvents ? SF_CONTACT_EVENTS : 0) | (def.enableHitEvents ? SF_HIT_EVENTS : 0);
+  int proxyType = body.type;
+  updateShapeAABBs(s, body.xf, proxyType);
+  {                                               // src/BroadPhase.cs:71-79
+    int proxyId = trees_[proxyType].createProxy(s.fat, s.categoryBits, id);
+    s.proxyKey = proxyKeyOf(proxyId, proxyType);
+    if (proxyType != kStaticBody || def.invokeContactCreation) bufferMove(s.proxyKey);
+  }
+  if (body.headShapeId != -1) shapes_[body.headShapeId].prevShapeId = id;
+  s.prevShapeId = -1; s.nextShapeId = body.headShapeId; body.headShapeId = id; body.shapeCount++;
+  if (def.updateBodyMass) updateBodyMassData(body);
+  *shapeId = id;
+  return B2C_OK;
+}
+
+void World::updateBodyMassData(HBody& body) {     // src/Body.cs:255-353
+  body.mass = 0; body.inertia = 0; body.invMass = 0; body.invInertia = 0; body.localCenter = mk(0, 0);
+  body.minExtent = kHuge; body.maxExtent = 0;
+  if (body.type != kDynamicBody) {
+    body.center = body.xf.p; body.center0 = body.center;
+    if (body.type == kKinematicBody) {
+      for (int sid = body.headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) {
+        float mn, mx; geomExtent(shapes_[sid].geom, mk(0, 0), &mn, &mx);
+        body.minExtent = netMin(body.minExtent, mn); body.maxExtent = netMax(body.maxExtent, mx);
+      }
+    }
+    return;
+  }
+  std::vector<MassData> masses(body.shapeCount);
+  for (auto& m : masses) { m.mass = 0; m.center = mk(0, 0); m.rotationalInertia = 0; }
+  V2 localCenter = mk(0, 0);
+  int shapeIndex = 0;
+  for (int sid = body.headShapeId; sid != -1;) {
+    const HShape& s = shapes_[sid];
+    sid = s.nextShapeId;
+    if (s.density == 0.0f) continue;              // :291 (the C# `continue` skips the index increment too)
+    MassData md = geomMass(s.geom, s.density);
+    body.mass += md.mass;
+    localCenter = mulAdd(localCenter, md.mass, md.center);
+    masses[shapeIndex] = md;
+    shapeIndex++;
+  }
+  if (body.mass > 0.0f) { body.invMass = 1.0f / body.mass; localCenter = body.invMass * localCenter; }
+  for (shapeIndex = 0; shapeIndex < body.shapeCount; shapeIndex++) {
+    MassData md = masses[shapeIndex];
+    if (md.mass == 0.0f) continue;
+    V2 offset = localCenter - md.center;
+    float inertia = md.rotationalInertia + md.mass * dot(offset, offset);
+    body.inertia += inertia;
+  }
+  if (body.inertia > 0.0f) body.invInertia = 1.0f / body.inertia; else { body.inertia = 0; body.invInertia = 0; }
+  V2 oldCenter = body.center;
+  body.localCenter = localCenter;
+  body.center = xfPoint(body.xf, localCenter);
+  body.center0 = body.center;
+  body.v = body.v + crossSV(body.w, body.center - oldCenter);
+  for (int sid = body.headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) {
+    float mn, mx; geomExtent(shapes_[sid].geom, localCenter, &mn, &mx);
+    body.minExtent = netMin(body.minExtent, mn); body.maxExtent = netMax(body.maxExtent, mx);
+  }
+}
+
+int World::assignJointColor(int bodyIdA, int bodyIdB, int typeA, int typeB) {   // src/ConstraintGraph.cs:91-128
+  uint32_t& mA = colorMask_[bodyIdA]; uint32_t& mB = colorMask_[bodyIdB];
+  if (typeA != kStaticBody && typeB != kStaticBody) {
+    for (int i = 0; i < kDynamicColorCount; i++) {
+      if (((mA >> i) & 1u) || ((mB >> i) & 1u)) continue;
+      if (typeA == kDynamicBody) mA |= 1u << i;
+      if (typeB == kDynamicBody) mB |= 1u << i;
+      return i;
+    }
+  } else if (typeA == kDynamicBody) {
+    for (int i = kGraphColorCount - 2; i >= 1; i--) { if ((mA >> i) & 1u) continue; mA |= 1u << i; return i; }
+  } else if (typeB == kDynamicBody) {
+    for (int i = kGraphColorCount - 2; i >= 1; i--) { if ((mB >> i) & 1u) continue; mB |= 1u << i; return i; }
+  }
+  return kOverflowIndex;
+}
+
+int World::createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId) {
+  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_revolute_joint after the first step is not supported in this build");
+  int nb = (int)bodies_.size();
+  if (def.bodyIdA < 0 || def.bodyIdA >= nb || def.bodyIdB < 0 || def.bodyIdB >= nb) return fail(B2C_E_INVALID, "bad body id");
+  HBody& bodyA = bodies_[def.bodyIdA]; HBody& bodyB = bodies_[def.bodyIdB];
+  if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) return fail(B2C_E_UNSUPPORTED, "joint between two non-dynamic bodies (static set) is not supported");
+  int id = jointIds_.alloc();
+  if (id == (int)joints_.size()) joints_.emplace_back();
+  HJoint& j = joints_[id];
+  uint16_t gen = j.generation;
+  j = HJoint();
+  j.generation = (uint16_t)(gen + 1);
+  j.id = id; j.collideConnected = def.collideConnected != 0;
+  j.bodyIdA = bodyA.id; j.prevKeyA = -1; j.nextKeyA = bodyA.headJointKey;      // src/Joint.cs:208-236
+  bodyA.headJointKey = id << 1; bodyA.jointCount++;
+  j.bodyIdB = bodyB.id; j.prevKeyB = -1; j.nextKeyB = bodyB.headJointKey;
+  bodyB.headJointKey = (id << 1) | 1; bodyB.jointCount++;
+  int color = assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type);
+  if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
+  JointDev& s = j.sim;
+  memset(&s, 0, sizeof(s));
+  s.jointId = id; s.bodyIdA = bodyA.id; s.bodyIdB = bodyB.id; s.colorIndex = color;
+  auto T = [](B2CTransform t) { return mkXf(mk(t.p.x, t.p.y), mkRot(t.q.c, t.q.s)); };
+  s.localFrameA = T(def.localFrameA); s.localFrameB = T(def.localFrameB);
+  s.constraintHertz = def.constraintHertz; s.constraintDampingRatio = def.constraintDampingRatio;
+  s.forceThreshold = def.forceThreshold; s.torqueThreshold = def.torqueThreshold;
+  s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.targetAngle = netClamp(def.targetAngle, -kPi, kPi);
+  s.maxMotorTorque = def.maxMotorTorque; s.motorSpeed = def.motorSpeed; s.lowerAngle = def.lowerAngle; s.upperAngle = def.upperAngle;
+  s.enableSpring = def.enableSpring != 0; s.enableMotor = def.enableMotor != 0; s.enableLimit = def.enableLimit != 0;
+  s.constraintSoftness.biasRate = 0; s.constraintSoftness.massScale = 1; s.constraintSoftness.impulseScale = 0;
+  colorJoints_[color].push_back(id);
+  // DestroyContactsBetweenBodies (src/Joint.cs:155-180): no contacts exist before the first step.
+  *jointId = id;
+  return B2C_OK;
+}
+
+int World::setTransform(int bodyId, V2 p, Rot q) {          // api/Body.cs:293-325
+  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "body_set_transform after the first step is not supported in this build");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  b.xf.p = p; b.xf.q = q;
+  b.center = xfPoint(b.xf, b.localCenter);
+  b.rot0 = q; b.center0 = b.center;
+  for (int sid = b.headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) {
+    HShape& s = shapes_[sid];
+    Box aabb = boxGrow(geomAABB(s.geom, b.xf), kSpeculativeDistance);
+    s.aabb = aabb;
+    if (!boxContains(s.fat, aabb)) {
+      s.fat = boxGrow(aabb, kAABBMargin);
+      if (s.proxyKey != -1) { trees_[s.proxyKey & 3].moveProxy(s.proxyKey >> 2, s.fat); bufferMove(s.proxyKey); }
+    }
+  }
+  return B2C_OK;
+}
+
+template <class T> T* World::dalloc(size_t n) {
+  void* p = nullptr;
+  if (n == 0) n = 1;
+  if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+  cudaMemsetAsync(p, 0, n * sizeof(T), stream_);
+  allocs_.push_back(p);
+  return (T*)p;
+}
+
+#define UP(dst, vec) do { if (!(vec).empty()) CK(cudaMemcpyAsync((dst), (vec).data(), (vec).size() * sizeof((vec)[0]), cudaMemcpyHostToDevice, stream_)); } while (0)
+#define DA(ptr, T, n) do { (ptr) = dalloc<T>(n); if (!(ptr)) return fail(B2C_E_CUDA, "cudaMalloc failed for " #ptr); } while (0)
+
+int World::upload() {
+  CK(cudaSetDevice(device_));
+  CK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  for (auto& e : ev_) CK(cudaEventCreate(&e));
+  CK(cudaHostAlloc((void**)&hostScalars_, sizeof(Scalars), cudaHostAllocDefault));
+  memset(hostScalars_, 0, sizeof(Scalars));
+  WorldDev& d = d_;
+  const int nBody = (int)bodies_.size(), nAwake = (int)awakeOrder_.size(), nShape = (int)shapes_.size(), nJoint = (int)joints_.size();
+  d.awakeCount = nAwake; d.bodyCapacity = nBody; d.shapeCapacity = nShape; d.jointCapacity = nJoint;
+  // ---- bodies ----
+  std::vector<float4> st0(nAwake), st1(nAwake), simMass(nAwake), simForce(nAwake), simPose(nAwake), simLocal(nAwake), simPose0(nAwake);
+  std::vector<uint32_t> simFlags(nAwake); std::vector<int> simBodyId(nAwake);
+  for (int i = 0; i < nAwake; i++) {
+    const HBody& b = bodies_[awakeOrder_[i]];
+    uint32_t fl = b.flags;
+    st0[i] = make_float4(b.v.x, b.v.y, b.w, __builtin_bit_cast(float, fl));
+    st1[i] = make_float4(0, 0, 1, 0);
+    simMass[i] = make_float4(b.invMass, b.invInertia, b.linearDamping, b.angularDamping);
+    simForce[i] = make_float4(b.force.x, b.force.y, b.torque, b.gravityScale);
+    simPose[i] = make_float4(b.center.x, b.center.y, b.xf.q.c, b.xf.q.s);
+    simLocal[i] = make_float4(b.localCenter.x, b.localCenter.y, b.minExtent, b.maxExtent);
+    simPose0[i] = make_float4(b.center0.x, b.center0.y, b.rot0.c, b.rot0.s);
+    simFlags[i] = fl; simBodyId[i] = b.id;
+  }
+  DA(d.st0, float4, nAwake); DA(d.st1, float4, nAwake); DA(d.simMass, float4, nAwake); DA(d.simForce, float4, nAwake);
+  DA(d.simPose, float4, nAwake); DA(d.simLocal, float4, nAwake); DA(d.simPose0, float4, nAwake); DA(d.simFlags, uint32_t, nAwake); DA(d.simBodyId, int, nAwake);
+  UP(d.st0, st0); UP(d.st1, st1); UP(d.simMass, simMass); UP(d.simForce, simForce); UP(d.simPose, simPose); UP(d.simLocal, simLocal);
+  UP(d.simPose0, simPose0); UP(d.simFlags, simFlags); UP(d.simBodyId, simBodyId);
+  std::vector<float4> bodyXf(nBody), bodyMass(nBody); std::vector<float2> bodyCenter(nBody);
+  std::vector<int> bodySim(nBody), bodyType(nBody), bodyHeadShape(nBody), bodyHeadJoint(nBody), bodyJointCount(nBody);
+  std::vector<float> bodySleep(nBody); std::vector<uint32_t> bodyFlags(nBody);
+  for (int i = 0; i < nBody; i++) {
+    const HBody& b = bodies_[i];
+    bodyXf[i] = make_float4(b.xf.p.x, b.xf.p.y, b.xf.q.c, b.xf.q.s);
+    bodyMass[i] = make_float4(b.invMass, b.invInertia, b.localCenter.x, b.localCenter.y);
+    bodyCenter[i] = make_float2(b.center.x, b.center.y);
+    bodySim[i] = b.simIndex; bodyType[i] = b.type; bodyHeadShape[i] = b.headShapeId; bodyHeadJoint[i] = b.headJointKey; bodyJointCount[i] = b.jointCount;
+    bodySleep[i] = b.sleepThreshold; bodyFlags[i] = b.flags;
+  }
+  colorMask_.resize(nBody, 0);
+  DA(d.bodyXf, float4, nBody); DA(d.bodyMass, float4, nBody); DA(d.bodyCenter, float2, nBody); DA(d.bodySim, int, nBody); DA(d.bodyType, int, nBody);
+  DA(d.bodyHeadShape, int, nBody); DA(d.bodyHeadJoint, int, nBody); DA(d.bodyJointCount, int, nBody); DA(d.bodyColorMask, uint32_t, nBody);
+  DA(d.bodyMinOp, int, nBody); DA(d.bodySleepThreshold, float, nBody); DA(d.bodyFlags, uint32_t, nBody);
+  UP(d.bodyXf, bodyXf); UP(d.bodyMass, bodyMass); UP(d.bodyCenter, bodyCenter); UP(d.bodySim, bodySim); UP(d.bodyType, bodyType);
+  UP(d.bodyHeadShape, bodyHeadShape); UP(d.bodyHeadJoint, bodyHeadJoint); UP(d.bodyJointCount, bodyJointCount); UP(d.bodyColorMask, colorMask_);
+  UP(d.bodySleepThreshold, bodySleep); UP(d.bodyFlags, bodyFlags);
+  CK(cudaMemsetAsync(d.bodyMinOp, 0x7f, sizeof(int) * (size_t)std::max(nBody, 1), stream_));
+  // ---- shapes ----
+  std::vector<ShapeDev> sh(nShape); std::vector<float4> shAABB(nShape), shFat(nShape);
+  for (int i = 0; i < nShape; i++) {
+    const HShape& s = shapes_[i]; ShapeDev& o = sh[i];
+    memset(&o, 0, sizeof(o));
+    o.geom = s.geom; o.material = make_float4(s.friction, s.restitution, s.rollingResistance, s.tangentSpeed);
+    o.categoryBits = s.categoryBits; o.maskBits = s.maskBits; o.groupIndex = s.groupIndex; o.bodyId = s.bodyId; o.nextShapeId = s.nextShapeId;
+    o.proxyKey = s.proxyKey; o.flags = s.flags; o.sensorIndex = -1;
+    shAABB[i] = make_float4(s.aabb.lo.x, s.aabb.lo.y, s.aabb.hi.x, s.aabb.hi.y);
+    shFat[i] = make_float4(s.fat.lo.x, s.fat.lo.y, s.fat.hi.x, s.fat.hi.y);
+  }
+  DA(d.shapes, ShapeDev, nShape); DA(d.shapeAABB, float4, nShape); DA(d.shapeFat, float4, nShape);
+  UP(d.shapes, sh); UP(d.shapeAABB, shAABB); UP(d.shapeFat, shFat);
+  // ---- joints ----
+  std::vector<JointDev> jd(nJoint); std::vector<int4> je(nJoint); std::vector<int> jc(nJoint), jsorted;
+  for (int i = 0; i < nJoint; i++) {
+    const HJoint& j = joints_[i];
+    jd[i] = j.sim; je[i] = make_int4(j.bodyIdA, j.nextKeyA, j.bodyIdB, j.nextKeyB); jc[i] = j.collideConnected ? 1 : 0;
+  }
+  d.jointColorStart[0] = 0;
+  for (int c = 0; c < kGraphColorCount; c++) {
+    for (int id : colorJoints_[c]) jsorted.push_back(id);
+    d.jointColorStart[c + 1] = (int)jsorted.size();
+  }
+  DA(d.joints, JointDev, nJoint); DA(d.jointEdges, int4, nJoint); DA(d.jointCollide, int, nJoint); DA(d.jointSorted, int, nJoint); DA(d.jointEventFlag, uint8_t, nJoint);
+  UP(d.joints, jd); UP(d.jointEdges, je); UP(d.jointCollide, jc); UP(d.jointSorted, jsorted);
+  // ---- trees ----
+  int totalProxies = 0;
+  for (int t = 0; t < 3; t++) {
+    HostTree& h = trees_[t]; TreeDev& td = d.trees[t];
+    int cap = h.capacity();
+    td.capacity = cap; td.stackCapacity = 16384;
+    DA(td.aabb, float4, cap); DA(td.child, int2, cap); DA(td.parent, int, cap); DA(td.hf, uint32_t, cap); DA(td.cat, uint64_t, cap);
+    DA(td.user, int, cap); DA(td.moved, uint8_t, cap); DA(td.meta, int, 4); DA(td.leafIdx, int, cap); DA(td.leafCtr, float2, cap); DA(td.stack, int, td.stackCapacity);
+    UP(td.aabb, h.aabb); UP(td.child, h.child); UP(td.parent, h.parent); UP(td.hf, h.hf); UP(td.cat, h.cat); UP(td.user, h.user);
+    std::vector<uint8_t> mv(cap, 0);
+    for (size_t k = 0; k < moved_[t].size() && k < (size_t)cap; k++) mv[k] = moved_[t][k];
+    UP(td.moved, mv);
+    int meta[4] = {h.root, h.nodeCount, h.freeList, h.proxyCount};
+    CK(cudaMemcpyAsync(td.meta, meta, sizeof(meta), cudaMemcpyHostToDevice, stream_));
+    CK(cudaStreamSynchronize(stream_));
+    totalProxies += h.proxyCount;
+  }
+  d.moveCapacity = std::max(totalProxies, 16);
+  int contactCap = capHintContact > 0 ? capHintContact : std::max(4096, 12 * nShape);
+  d.contactCapacity = contactCap; d.pairCapacity = contactCap; d.eventCapacity = contactCap;
+  d.constraintCapacity = contactCap + 32 * kGraphColorCount;
+  int tableSize = 1; while (tableSize < 4 * contactCap) tableSize <<= 1;
+  d.pairTableSize = tableSize;
+  DA(d.moveArray, int, d.moveCapacity); DA(d.moveHitCount, int, d.moveCapacity + 1); DA(d.movePairs, int2, d.pairCapacity);
+  DA(d.pairTable, unsigned long long, tableSize);
+  UP(d.moveArray, moveArray_);
+  DA(d.cShape, int2, contactCap); DA(d.cBody, int2, contactCap); DA(d.cFlags, uint32_t, contactCap); DA(d.cColor, int, contactCap); DA(d.cGen, uint32_t, contactCap);
+  DA(d.cMat, float4, contactCap); DA(d.cMass, float4, contactCap); DA(d.cSim, int2, contactCap);
+  DA(d.mN, float4, contactCap); DA(d.mA0, float4, contactCap); DA(d.mA1, float4, contactCap); DA(d.mB0, float4, contactCap); DA(d.mB1, float4, contactCap);
+  DA(d.mC0, float4, contactCap); DA(d.mC1, float4, contactCap); DA(d.contactFree, int, contactCap);
+  DA(d.flagScan, int4, contactCap + 1); DA(d.opList, int, contactCap); DA(d.opDone, uint8_t, contactCap);
+  int cc = d.constraintCapacity;
+  DA(d.sA, float4, cc); DA(d.sB, float4, cc); DA(d.sC, float4, cc); DA(d.sD, float4, cc); DA(d.sE, float4, cc); DA(d.sF, float4, cc);
+  DA(d.sG, float4, cc); DA(d.sH, float4, cc); DA(d.sI, float4, cc); DA(d.sJ, float4, cc); DA(d.sContact, int, cc); DA(d.cConstraint, int, contactCap);
+  DA(d.blockHist, int, (size_t)(contactCap / 256 + 2) * kGraphColorCount);
+  DA(d.beginEvents, B2CContactTouchEvent, d.eventCapacity); DA(d.endEvents[0], B2CContactTouchEvent, d.eventCapacity);
+  DA(d.endEvents[1], B2CContactTouchEvent, d.eventCapacity); DA(d.hitEvents, B2CContactHitEvent, d.eventCapacity);
+  DA(d.bodyEnlargedCount, int, nAwake + 1);
+  DA(d.sc, Scalars, 1);
+  int scanBlocks = std::max(contactCap, std::max(d.moveCapacity, nAwake)) / 1024 + 2;
+  DA(d.scanBlockSums, int, scanBlocks); DA(d.scanBlockSums4, int4, scanBlocks);
+  Scalars init; memset(&init, 0, sizeof(init));
+  init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;
+  CK(cudaMemcpyAsync(d.sc, &init, sizeof(init), cudaMemcpyHostToDevice, stream_));
+  CK(cudaHostAlloc((void**)&hBegin_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&hEnd_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&hHit_, sizeof(B2CContactHitEvent) * d.eventCapacity, cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(nJoint, 1), cudaHostAllocDefault));
+  CK(cudaStreamSynchronize(stream_));
+  onDevice_ = true;
+  return B2C_OK;
+}
+
+int World::synchronize() {
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  CK(cudaStreamSynchronize(stream_));
+  if (hostScalars_->errorFlags & ~(int)ERR_TOI_CANDIDATE) {   // TOI candidates are counted (counters.toiCandidates), the step uses the no-hit result
+    char buf[160]; snprintf(buf, sizeof(buf), "device error flags 0x%x (capacity/stack/overflow-color/TOI; see b2c_world.cuh ERR_*)", hostScalars_->errorFlags);
+    uint32_t f = (uint32_t)hostScalars_->errorFlags;
+    if (f & (ERR_CONTACT_CAPACITY | ERR_PAIR_CAPACITY | ERR_HASH_FULL | ERR_STACK_OVERFLOW)) return fail(B2C_E_CAPACITY, buf);
+    if (f & ERR_OVERFLOW_COLOR) return fail(B2C_E_UNSUPPORTED, buf);
+    return fail(B2C_E_CUDA, buf);
+  }
+  return B2C_OK;
+}
+
+// ---- mutators that patch device rows directly (api/Body.cs:359-545) ----
+int World::setLinearVelocity(int bodyId, V2 v) {
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  if (b.type == kStaticBody) return B2C_OK;
+  if (!onDevice_) { b.v = v; return B2C_OK; }
+  CK(cudaSetDevice(device_));
+  float xy[2] = {v.x, v.y};
+  CK(cudaMemcpyAsync(&d_.st0[b.simIndex], xy, sizeof(xy), cudaMemcpyHostToDevice, stream_));
+  CK(cudaStreamSynchronize(stream_));
+  return B2C_OK;
+}
+int World::setAngularVelocity(int bodyId, float w) {
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  if (b.type == kStaticBody) return B2C_OK;
+  if (!onDevice_) { b.w = w; return B2C_OK; }
+  CK(cudaSetDevice(device_));
+  CK(cudaMemcpyAsync(&d_.st0[b.simIndex].z, &w, sizeof(float), cudaMemcpyHostToDevice, stream_));
+  CK(cudaStreamSynchronize(stream_));
+  return B2C_OK;
+}
+int World::applyForceToCenter(int bodyId, V2 f) {            // api/Body.cs:457-467 (accumulates)
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  if (b.type != kDynamicBody) return B2C_OK;
+  if (!onDevice_) { b.force = b.force + f; return B2C_OK; }
+  CK(cudaSetDevice(device_));
+  float cur[2];
+  CK(cudaMemcpyAsync(cur, &d_.simForce[b.simIndex], sizeof(cur), cudaMemcpyDeviceToHost, stream_));
+  CK(cudaStreamSynchronize(stream_));
+  cur[0] = cur[0] + f.x; cur[1] = cur[1] + f.y;
+  CK(cudaMemcpyAsync(&d_.simForce[b.simIndex], cur, sizeof(cur), cudaMemcpyHostToDevice, stream_));
+  CK(cudaStreamSynchronize(stream_));
+  return B2C_OK;
+}
+int World::applyTorque(int bodyId, float t) {                 // api/Body.cs:469-479 (assigns — port quirk)
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  if (b.type != kDynamicBody) return B2C_OK;
+  if (!onDevice_) { b.torque = t; return B2C_OK; }
+  CK(cudaSetDevice(device_));
+  CK(cudaMemcpyAsync(&d_.simForce[b.simIndex].z, &t, sizeof(float), cudaMemcpyHostToDevice, stream_));
+  CK(cudaStreamSynchronize(stream_));
+  return B2C_OK;
+}
+int World::applyLinearImpulseToCenter(int bodyId, V2 imp) {   // api/Body.cs:531-545
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  if (b.type != kDynamicBody) return B2C_OK;
+  V2 v = b.v;
+  if (onDevice_) {
+    CK(cudaSetDevice(device_));
+    float cur[2];
+    CK(cudaMemcpyAsync(cur, &d_.st0[b.simIndex], sizeof(cur), cudaMemcpyDeviceToHost, stream_));
+    CK(cudaStreamSynchronize(stream_));
+    v = mk(cur[0], cur[1]);
+  }
+  v = mulAdd(v, b.invMass, imp);
+  float v2 = lengthSq(v);
+  if (v2 > maxLinearSpeed * maxLinearSpeed) v = (maxLinearSpeed / sqrtf(v2)) * v;
+  if (!onDevice_) { b.v = v; return B2C_OK; }
+  float xy[2] = {v.x, v.y};
+  CK(cudaMemcpyAsync(&d_.st0[b.simIndex], xy, sizeof(xy), cudaMemcpyHostToDevice, stream_));
+  CK(cudaStreamSynchronize(stream_));
+  return B2C_OK;
+}
+
+// ---- read-back ----
+template <class T> static int fetch(std::vector<T>& out, const T* dev, size_t n, cudaStream_t s) {
+  out.resize(n);
+  if (n == 0) return 0;
+  return cudaMemcpyAsync(out.data(), dev, n * sizeof(T), cudaMemcpyDeviceToHost, s) == cudaSuccess ? 0 : 1;
+}
+
+int World::readBodies(B2CBodyRead* dst, int capacity, int* count) {
+  int n = (int)bodies_.size();
+  *count = n;
+  if (!onDevice_) {
+    for (int i = 0; i < n && i < capacity; i++) {
+      const HBody& b = bodies_[i]; B2CBodyRead r; memset(&r, 0, sizeof(r));
+      r.transform.p = {b.xf.p.x, b.xf.p.y}; r.transform.q = {b.xf.q.c, b.xf.q.s}; r.center = {b.center.x, b.center.y};
+      r.linearVelocity = {b.v.x, b.v.y}; r.angularVelocity = b.w; r.flags = b.flags;
+      dst[i] = r;
+    }
+    return B2C_OK;
+  }
+  int rc = synchronize(); if (rc) return rc;
+  std::vector<float4> xf, st0; std::vector<float2> ctr; std::vector<uint32_t> sf;
+  if (fetch(xf, d_.bodyXf, n, stream_) | fetch(ctr, d_.bodyCenter, n, stream_) | fetch(st0, d_.st0, d_.awakeCount, stream_) | fetch(sf, d_.simFlags, d_.awakeCount, stream_))
+    return fail(B2C_E_CUDA, "read_bodies copy failed");
+  CK(cudaStreamSynchronize(stream_));
+  for (int i = 0; i < n && i < capacity; i++) {
+    const HBody& b = bodies_[i]; B2CBodyRead r; memset(&r, 0, sizeof(r));
+    if (b.id != -1) {
+      r.transform.p = {xf[i].x, xf[i].y}; r.transform.q = {xf[i].z, xf[i].w}; r.center = {ctr[i].x, ctr[i].y};
+      r.flags = b.flags;
+      if (b.simIndex >= 0) { float4 s = st0[b.simIndex]; r.linearVelocity = {s.x, s.y}; r.angularVelocity = s.z; r.flags = sf[b.simIndex]; }
+    }
+    dst[i] = r;
+  }
+  return B2C_OK;
+}
+
+int World::readContacts(B2CContactRead* dst, int capacity, int* count) {
+  *count = 0;
+  if (!onDevice_) return B2C_OK;
+  int rc = synchronize(); if (rc) return rc;
+  int n = hostScalars_->contactNext;
+  std::vector<int2> cShape; std::vector<uint32_t> cFlags; std::vector<int> cColor; std::vector<float4> cMat, mN, mA0, mA1, mB0, mB1, mC0, mC1;
+  if (fetch(cShape, d_.cShape, n, stream_) | fetch(cFlags, d_.cFlags, n, stream_) | fetch(cColor, d_.cColor, n, stream_) | fetch(cMat, d_.cMat, n, stream_) |
+      fetch(mN, d_.mN, n, stream_) | fetch(mA0, d_.mA0, n, stream_) | fetch(mA1, d_.mA1, n, stream_) | fetch(mB0, d_.mB0, n, stream_) |
+      fetch(mB1, d_.mB1, n, stream_) | fetch(mC0, d_.mC0, n, stream_) | fetch(mC1, d_.mC1, n, stream_))
+    return fail(B2C_E_CUDA, "read_contacts copy failed");
+  CK(cudaStreamSynchronize(stream_));
+  int k = 0;
+  for (int i = 0; i < n; i++) {
+    if (!(cFlags[i] & CF_ALIVE)) continue;
+    if (k < capacity) {
+      B2CContactRead r; memset(&r, 0, sizeof(r));
+      r.contactId = i; r.shapeIdA = cShape[i].x; r.shapeIdB = cShape[i].y; r.colorIndex = cColor[i];
+      r.flags = (cFlags[i] & CF_TOUCHING) ? 1u : 0u;
+      r.pointCount = __builtin_bit_cast(int, mN[i].w); r.normal = {mN[i].x, mN[i].y}; r.rollingImpulse = mN[i].z;
+      r.friction = cMat[i].x; r.restitution = cMat[i].y; r.rollingResistance = cMat[i].z; r.tangentSpeed = cMat[i].w;
+      auto fill = [](B2CManifoldPointRead& o, float4 a, float4 b, float4 c) {
+        o.anchorA = {a.x, a.y}; o.anchorB = {a.z, a.w}; o.separation = b.x; o.normalImpulse = b.y; o.tangentImpulse = b.z; o.totalNormalImpulse = b.w;
+        o.point = {c.x, c.y}; o.normalVelocity = c.z; uint32_t w = __builtin_bit_cast(uint32_t, c.w); o.id = w & 0xffffu; o.persisted = (w >> 16) & 1u;
+      };
+      fill(r.points[0], mA0[i], mB0[i], mC0[i]); fill(r.points[1], mA1[i], mB1[i], mC1[i]);
+      dst[k] = r;
+    }
+    k++;
+  }
+  *count = k;
+  return B2C_OK;
+}
+
+int World::readJoints(B2CJointRead* dst, int capacity, int* count) {
+  int n = (int)joints_.size();
+  *count = n;
+  std::vector<JointDev> jd;
+  if (onDevice_) {
+    int rc = synchronize(); if (rc) return rc;
+    if (fetch(jd, d_.joints, n, stream_)) return fail(B2C_E_CUDA, "read_joints copy failed");
+    CK(cudaStreamSynchronize(stream_));
+  } else { jd.resize(n); for (int i = 0; i < n; i++) jd[i] = joints_[i].sim; }
+  for (int i = 0; i < n && i < capacity; i++) {
+    const JointDev& s = jd[i];
+    dst[i] = {s.jointId, s.colorIndex, {s.linearImpulse.x, s.linearImpulse.y}, s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse};
+  }
+  return B2C_OK;
+}
+
+int World::readShapes(B2CShapeRead* dst, int capacity, int* count) {
+  int n = (int)shapes_.size();
+  *count = n;
+  if (!onDevice_) {
+    for (int i = 0; i < n && i < capacity; i++) {
+      const HShape& s = shapes_[i];
+      dst[i] = {{s.aabb.lo.x, s.aabb.lo.y}, {s.aabb.hi.x, s.aabb.hi.y}, {s.fat.lo.x, s.fat.lo.y}, {s.fat.hi.x, s.fat.hi.y}, s.proxyKey, 0};
+    }
+    return B2C_OK;
+  }
+  int rc = synchronize(); if (rc) return rc;
+  std::vector<float4> a, f; std::vector<ShapeDev> sh;
+  if (fetch(a, d_.shapeAABB, n, stream_) | fetch(f, d_.shapeFat, n, stream_) | fetch(sh, d_.shapes, n, stream_)) return fail(B2C_E_CUDA, "read_shapes copy failed");
+  CK(cudaStreamSynchronize(stream_));
+  for (int i = 0; i < n && i < capacity; i++)
+    dst[i] = {{a[i].x, a[i].y}, {a[i].z, a[i].w}, {f[i].x, f[i].y}, {f[i].z, f[i].w}, sh[i].proxyKey, (sh[i].flags & SF_ENLARGED) ? 1 : 0};
+  return B2C_OK;
+}
+
+int World::getCounters(B2CCounters* out) {
+  memset(out, 0, sizeof(*out));
+  out->bodyCount = bodyIds_.count(); out->awakeBodyCount = (int)awakeOrder_.size(); out->shapeCount = shapeIds_.count(); out->jointCount = jointIds_.count();
+  out->unsupportedCount = unsupported; out->stepCount = stepCount_;
+  if (!onDevice_) {
+    out->moveCount = (int)moveArray_.size();
+    for (int c = 0; c < kGraphColorCount; c++) out->colorCounts[c] = (int)colorJoints_[c].size();
+    return B2C_OK;
+  }
+  int rc = synchronize();
+  const Scalars& s = *hostScalars_;
+  out->contactCount = s.liveContactCount; out->touchingContactCount = s.touchingCount; out->contactIdCapacity = s.contactNext;
+  int active = 0;
+  for (int c = 0; c < kGraphColorCount; c++) {
+    out->colorCounts[c] = s.colorCount[c] + (d_.jointColorStart[c + 1] - d_.jointColorStart[c]);
+    if (c < kOverflowIndex && out->colorCounts[c] > 0) active++;
+  }
+  out->activeColorCount = active; out->moveCount = s.moveCount; out->newPairCount = s.newPairCount; out->toiCandidates = s.toiCandidates;
+  out->errorFlags = s.errorFlags;
+  return rc;
+}
+
+int World::getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B2CContactTouchEvent** end, int* ne, const B2CContactHitEvent** hit, int* nh) {
+  *begin = nullptr; *end = nullptr; *hit = nullptr; *nb = *ne = *nh = 0;
+  if (!onDevice_) return B2C_OK;
+  int rc = synchronize(); if (rc) return rc;
+  if (!eventsFetched_) {
+    const Scalars& s = *hostScalars_;
+    hBeginN_ = s.beginCount; hEndN_ = s.endCount[lastEndIndex_]; hHitN_ = s.hitCount;
+    if (hBeginN_) CK(cudaMemcpyAsync(hBegin_, d_.beginEvents, sizeof(B2CContactTouchEvent) * hBeginN_, cudaMemcpyDeviceToHost, stream_));
+    if (hEndN_) CK(cudaMemcpyAsync(hEnd_, d_.endEvents[lastEndIndex_], sizeof(B2CContactTouchEvent) * hEndN_, cudaMemcpyDeviceToHost, stream_));
+    if (hHitN_) CK(cudaMemcpyAsync(hHit_, d_.hitEvents, sizeof(B2CContactHitEvent) * hHitN_, cudaMemcpyDeviceToHost, stream_));
+    CK(cudaStreamSynchronize(stream_));
+    eventsFetched_ = true;
+  }
+  *begin = hBegin_; *nb = hBeginN_; *end = hEnd_; *ne = hEndN_; *hit = hHit_; *nh = hHitN_;
+  return B2C_OK;
+}
+
+int World::getJointEvents(const int** ids, int* count) {
+  *ids = hJointEvents_; *count = 0;
+  if (!onDevice_ || joints_.empty()) return B2C_OK;
+  int rc = synchronize(); if (rc) return rc;
+  std::vector<uint8_t> flags;
+  if (fetch(flags, d_.jointEventFlag, joints_.size(), stream_)) return fail(B2C_E_CUDA, "joint event copy failed");
+  CK(cudaStreamSynchronize(stream_));
+  int n = 0;
+  for (size_t i = 0; i < flags.size(); i++) if (flags[i]) hJointEvents_[n++] = (int)i;
+  *count = n;
+  return B2C_OK;
+}
+
+int World::getProfile(B2CProfile* out) {
+  memset(out, 0, sizeof(*out));
+  if (!onDevice_ || !profileValid_) return B2C_OK;
+  int rc = synchronize(); if (rc) return rc;
+  float pairs = 0, collide = 0, solve = 0, fin = 0, total = 0;
+  cudaEventElapsedTime(&pairs, ev_[0], ev_[1]); cudaEventElapsedTime(&collide, ev_[1], ev_[2]); cudaEventElapsedTime(&solve, ev_[2], ev_[3]);
+  cudaEventElapsedTime(&fin, ev_[3], ev_[4]); cudaEventElapsedTime(&total, ev_[0], ev_[4]);
+  out->step = total; out->pairs = pairs; out->collide = collide; out->solve = solve + fin; out->solveConstraints = solve; out->transforms = fin; out->refit = fin;
+  return B2C_OK;
+}
+
+}  // namespace b2c

@@ -1,0 +1,137 @@
+// libb2cuda — host-side creation bookkeeping (the part of Box2D.API that is NOT on the step path:
+// id pools, body/shape/joint creation, mass data, proxy insertion into the SAH tree, joint coloring).
+// It only builds the arrays that are uploaded to the device; it contains no step code — the step
+// runs exclusively on the GPU (b2c_step.cu) and there is no CPU fallback.
+#pragma once
+#include <vector>
+#include <string>
+#include "b2c_world.cuh"
+
+namespace b2c {
+
+struct IdPool {                 // src/IDPool.cs (LIFO recycling)
+  std::vector<int> freeArray; int nextIndex = 0;
+  int alloc() { if (!freeArray.empty()) { int id = freeArray.back(); freeArray.pop_back(); return id; } return nextIndex++; }
+  void release(int id) { freeArray.push_back(id); }
+  int capacity() const { return nextIndex; }
+  int count() const { return nextIndex - (int)freeArray.size(); }
+};
+
+// Host replica of the reference's incremental tree, used at creation time only (src/DynamicTree.cs:36-480).
+struct HostTree {
+  std::vector<float4> aabb; std::vector<int2> child; std::vector<int> parent; std::vector<uint32_t> hf;
+  std::vector<uint64_t> cat; std::vector<int> user;
+  int root = -1, nodeCount = 0, freeList = 0, proxyCount = 0;
+  HostTree();
+  int capacity() const { return (int)aabb.size(); }
+  int createProxy(Box box, uint64_t categoryBits, int userData);
+  void moveProxy(int id, Box box);
+ private:
+  int allocNode();
+  void freeNode(int id);
+  int findBestSibling(Box boxD);
+  void rotate(int iA);
+  void applyRot(int iA, int iInner, int iMove, int iUp, int iStay, bool aChild1, bool innerChild1, Box box);
+  void insertLeaf(int leaf, bool shouldRotate);
+  void removeLeaf(int leaf);
+  Box box(int i) const { float4 a = aabb[i]; Box b; b.lo = mk(a.x, a.y); b.hi = mk(a.z, a.w); return b; }
+  void setBox(int i, Box b) { aabb[i] = make_float4(b.lo.x, b.lo.y, b.hi.x, b.hi.y); }
+  int height(int i) const { return (int)(hf[i] & 0xffffu); }
+  uint32_t flags(int i) const { return hf[i] >> 16; }
+  void setHeight(int i, int h) { hf[i] = (hf[i] & 0xffff0000u) | (uint32_t)h; }
+  void orFlags(int i, uint32_t f) { hf[i] |= f << 16; }
+};
+
+struct HBody {                  // src/Body.cs:35-93 Body + BodySim + BodyState at creation time
+  int id = -1, type = kStaticBody, simIndex = -1;
+  int headShapeId = -1, shapeCount = 0, headJointKey = -1, jointCount = 0;
+  float mass = 0, inertia = 0, sleepThreshold = 0.05f;
+  uint32_t flags = 0; uint16_t generation = 0; uint64_t userData = 0; bool enableSleep = true;
+  Xf xf; V2 center, center0, localCenter, force; Rot rot0;
+  float torque = 0, invMass = 0, invInertia = 0, minExtent = kHuge, maxExtent = 0, linearDamping = 0, angularDamping = 0, gravityScale = 1;
+  V2 v; float w = 0;
+};
+struct HShape {
+  int id = -1, bodyId = -1, prevShapeId = -1, nextShapeId = -1, proxyKey = -1;
+  Geom geom; float friction = 0.6f, restitution = 0, rollingResistance = 0, tangentSpeed = 0, density = 1;
+  uint64_t categoryBits = ~0ull, maskBits = ~0ull; int groupIndex = 0; uint32_t flags = 0; uint16_t generation = 0;
+  Box aabb, fat; uint64_t userData = 0;
+};
+struct HJoint {
+  int id = -1; uint16_t generation = 0; bool collideConnected = false;
+  int bodyIdA = -1, nextKeyA = -1, prevKeyA = -1, bodyIdB = -1, nextKeyB = -1, prevKeyB = -1;
+  JointDev sim;
+};
+
+class World {
+ public:
+  explicit World(const B2CWorldDef& def, int device);
+  ~World();
+  // --- creation API (host) ---
+  int createBody(const B2CBodyDef& def, int* bodyId);
+  int createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId);
+  int createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId);
+  int setTransform(int bodyId, V2 p, Rot q);
+  int setLinearVelocity(int bodyId, V2 v);
+  int setAngularVelocity(int bodyId, float w);
+  int applyForceToCenter(int bodyId, V2 f);
+  int applyTorque(int bodyId, float t);
+  int applyLinearImpulseToCenter(int bodyId, V2 i);
+  // --- step + readback (device) ---
+  int step(float dt, int subSteps);
+  int synchronize();
+  int readBodies(B2CBodyRead* dst, int capacity, int* count);
+  int readContacts(B2CContactRead* dst, int capacity, int* count);
+  int readJoints(B2CJointRead* dst, int capacity, int* count);
+  int readShapes(B2CShapeRead* dst, int capacity, int* count);
+  int getCounters(B2CCounters* out);
+  int getProfile(B2CProfile* out);
+  int getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B2CContactTouchEvent** end, int* ne, const B2CContactHitEvent** hit, int* nh);
+  int getJointEvents(const int** ids, int* count);
+
+  // tunables (api/World.cs setters)
+  V2 gravity; float restitutionThreshold, hitEventThreshold, contactHertz, contactDampingRatio, contactSpeed, maxLinearSpeed;
+  bool enableSleep, enableContinuous, enableContactSoftening, enableWarmStarting = true, enableSpeculative = true;
+  std::string error;
+  int unsupported = 0;
+  int capHintBody, capHintShape, capHintContact, capHintJoint;
+
+ private:
+  void updateBodyMassData(HBody& body);
+  void updateShapeAABBs(HShape& s, Xf xf, int proxyType);
+  int assignJointColor(int bodyIdA, int bodyIdB, int typeA, int typeB);
+  void bufferMove(int key);
+  int upload();                 // host arrays -> device (first step)
+  void freeDevice();
+  int fail(int code, const std::string& msg) { error = msg; return code; }
+  template <class T> T* dalloc(size_t n);
+
+  int device_;
+  cudaStream_t stream_ = nullptr;
+  bool onDevice_ = false;
+  // host creation state
+  IdPool bodyIds_, shapeIds_, jointIds_;
+  std::vector<HBody> bodies_; std::vector<HShape> shapes_; std::vector<HJoint> joints_;
+  std::vector<int> awakeOrder_;        // bodyId per awake sim index
+  HostTree trees_[3];
+  std::vector<int> moveArray_; std::vector<std::vector<uint8_t>> moved_;
+  std::vector<uint32_t> colorMask_;    // per bodyId
+  std::vector<std::vector<int>> colorJoints_;
+  // device state
+  WorldDev d_{};
+  std::vector<void*> allocs_;
+  Scalars* hostScalars_ = nullptr;     // pinned
+  int endIndex_ = 0;
+  int stepCount_ = 0;
+  bool eventsFetched_ = false;
+  B2CContactTouchEvent *hBegin_ = nullptr, *hEnd_ = nullptr; B2CContactHitEvent* hHit_ = nullptr; int* hJointEvents_ = nullptr;
+  int hBeginN_ = 0, hEndN_ = 0, hHitN_ = 0, hJointN_ = 0;
+  int lastEndIndex_ = 0;
+  cudaEvent_t ev_[8] = {};
+  B2CProfile profile_{};
+  bool profileValid_ = false;
+  int coopBlocks_ = 0;
+  friend struct StepLauncher;
+};
+
+}  // namespace b2c

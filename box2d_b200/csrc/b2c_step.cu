@@ -1,0 +1,1356 @@
+// libb2cuda — the rigid-body step on the device (WorldAPI.Step, api/World.cs:31-113).
+// Every kernel is grid-strided over a count that lives in device memory (Scalars), so the whole step is a fixed
+// sequence of launches with no host read-back: UpdateBroadPhasePairs -> Collide -> Solve -> Finalize/refit.
+// Serial, order-defining parts of the reference (contact id allocation, begin/end processing in ascending contactId,
+// greedy graph coloring, move-array order) are reproduced with ordered compaction (prefix sums) and priority rounds,
+// so ids, colors and event streams are bit-identical to the single-threaded C# step.
+#include "b2c_host.cuh"
+#include "b2c_manifold.cuh"
+#include <cooperative_groups.h>
+#include <cstdio>
+#include <algorithm>
+
+namespace cg = cooperative_groups;
+
+namespace b2c {
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(B2C_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+constexpr int kThreads = 256;
+constexpr int kScanChunk = 1024;
+
+__device__ __forceinline__ int gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
+__device__ __forceinline__ int gsize() { return gridDim.x * blockDim.x; }
+__device__ __forceinline__ Box toBox(float4 a) { Box b; b.lo = mk(a.x, a.y); b.hi = mk(a.z, a.w); return b; }
+__device__ __forceinline__ float4 fromBox(Box b) { return make_float4(b.lo.x, b.lo.y, b.hi.x, b.hi.y); }
+__device__ __forceinline__ Xf toXf(float4 a) { return mkXf(mk(a.x, a.y), mkRot(a.z, a.w)); }
+__device__ __forceinline__ unsigned long long pairKey(int a, int b) {   // src/Contact.cs:126
+  unsigned long long k1 = (unsigned long long)(unsigned)a, k2 = (unsigned long long)(unsigned)b;
+  return k1 < k2 ? (k1 << 32 | k2) : (k2 << 32 | k1);
+}
+__device__ __forceinline__ unsigned hashKey(unsigned long long k) {
+  k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33; return (unsigned)k;
+}
+constexpr unsigned long long kEmptyKey = ~0ull;
+
+// ------------------------------------------------------------------------------------------------------------
+// generic chunked exclusive scan: pass 1 scans 1024-element chunks in place and records chunk totals, pass 2 scans the
+// chunk totals; consumers read data[i] + sums[i >> 10].
+// ------------------------------------------------------------------------------------------------------------
+template <class T> __device__ __forceinline__ T zeroOf();
+template <> __device__ __forceinline__ int zeroOf<int>() { return 0; }
+template <> __device__ __forceinline__ int4 zeroOf<int4>() { return make_int4(0, 0, 0, 0); }
+__device__ __forceinline__ int addT(int a, int b) { return a + b; }
+__device__ __forceinline__ int4 addT(int4 a, int4 b) { return make_int4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ int make_neg(int v) { return -v; }
+__device__ __forceinline__ int4 make_neg(int4 v) { return make_int4(-v.x, -v.y, -v.z, -v.w); }
+__device__ __forceinline__ int shflUp(int v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
+__device__ __forceinline__ int4 shflUp(int4 v, int d) {
+  return make_int4(__shfl_up_sync(0xffffffffu, v.x, d), __shfl_up_sync(0xffffffffu, v.y, d), __shfl_up_sync(0xffffffffu, v.z, d), __shfl_up_sync(0xffffffffu, v.w, d));
+}
+// block-wide inclusive scan for 1024 threads; returns inclusive value, total via shared
+template <class T> __device__ __forceinline__ T blockInclusive(T v, T* warpSums, T* total) {
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int d = 1; d < 32; d <<= 1) { T n = shflUp(v, d); if (lane >= d) v = addT(v, n); }
+  if (lane == 31) warpSums[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    T w = lane < (int)(blockDim.x >> 5) ? warpSums[lane] : zeroOf<T>();
+    for (int d = 1; d < 32; d <<= 1) { T n = shflUp(w, d); if (lane >= d) w = addT(w, n); }
+    warpSums[lane] = w;
+  }
+  __syncthreads();
+  if (warp > 0) v = addT(v, warpSums[warp - 1]);
+  *total = warpSums[(blockDim.x >> 5) - 1];
+  __syncthreads();
+  return v;
+}
+template <class T> __global__ void __launch_bounds__(kScanChunk) k_scan_chunks(T* data, T* sums, const int* nPtr) {
+  __shared__ T warpSums[32];
+  int n = *nPtr;
+  int chunks = (n + kScanChunk - 1) / kScanChunk;
+  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+    int i = c * kScanChunk + threadIdx.x;
+    T v = i < n ? data[i] : zeroOf<T>();
+    T total;
+    T inc = blockInclusive(v, warpSums, &total);
+    if (i < n) data[i] = addT(inc, make_neg(v));
+    if (threadIdx.x == 0) sums[c] = total;
+  }
+}
+template <class T> __global__ void __launch_bounds__(kScanChunk) k_scan_sums(T* sums, const int* nPtr, T* totalOut) {
+  __shared__ T warpSums[32];
+  int n = *nPtr;
+  int chunks = (n + kScanChunk - 1) / kScanChunk;
+  T carry = zeroOf<T>();
+  for (int base = 0; base < chunks; base += kScanChunk) {
+    int i = base + threadIdx.x;
+    T v = i < chunks ? sums[i] : zeroOf<T>();
+    T total;
+    T inc = blockInclusive(v, warpSums, &total);
+    if (i < chunks) sums[i] = addT(carry, addT(inc, make_neg(v)));
+    carry = addT(carry, total);
+  }
+  if (threadIdx.x == 0) *totalOut = carry;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Phase 0: UpdateBroadPhasePairs (src/BroadPhase.cs:137-268)
+// ------------------------------------------------------------------------------------------------------------
+__global__ void k_pair_insert(WorldDev d) {
+  if (d.sc->moveCount == 0) return;
+  int n = d.sc->contactNext;
+  unsigned mask = (unsigned)d.pairTableSize - 1u;
+  for (int i = gtid(); i < n; i += gsize()) {
+    if (!(d.cFlags[i] & CF_ALIVE)) continue;
+    int2 s = d.cShape[i];
+    unsigned long long key = pairKey(s.x, s.y);
+    unsigned h = hashKey(key) & mask;
+    for (int probe = 0; probe < d.pairTableSize; probe++) {
+      unsigned long long old = atomicCAS(&d.pairTable[h], kEmptyKey, key);
+      if (old == kEmptyKey || old == key) break;
+      h = (h + 1) & mask;
+    }
+  }
+}
+__device__ __forceinline__ bool pairSetContains(const WorldDev& d, unsigned long long key) {
+  unsigned mask = (unsigned)d.pairTableSize - 1u;
+  unsigned h = hashKey(key) & mask;
+  for (int probe = 0; probe < d.pairTableSize; probe++) {
+    unsigned long long v = d.pairTable[h];
+    if (v == key) return true;
+    if (v == kEmptyKey) return false;
+    h = (h + 1) & mask;
+  }
+  return false;
+}
+__device__ __forceinline__ bool shouldShapesCollide(const ShapeDev& a, const ShapeDev& b) {   // src/Shape.cs:56-61
+  if (a.groupIndex == b.groupIndex && a.groupIndex != 0) return a.groupIndex > 0;
+  return (a.maskBits & b.categoryBits) != 0 && (a.categoryBits & b.maskBits) != 0;
+}
+__device__ inline bool shouldBodiesCollide(const WorldDev& d, int bodyIdA, int bodyIdB) {     // src/Body.cs:354-371
+  if (d.bodyType[bodyIdA] != kDynamicBody && d.bodyType[bodyIdB] != kDynamicBody) return false;
+  int jointKey, otherBodyId;
+  if (d.bodyJointCount[bodyIdA] < d.bodyJointCount[bodyIdB]) { jointKey = d.bodyHeadJoint[bodyIdA]; otherBodyId = bodyIdB; }
+  else { jointKey = d.bodyHeadJoint[bodyIdB]; otherBodyId = bodyIdA; }
+  while (jointKey != -1) {
+    int jointId = jointKey >> 1, edge = jointKey & 1;
+    int4 e = d.jointEdges[jointId];
+    int otherBody = edge == 1 ? e.x : e.z;      // the edge opposite to ours
+    if (!d.jointCollide[jointId] && otherBody == otherBodyId) return false;
+    jointKey = edge == 1 ? e.w : e.y;
+  }
+  return true;
+}
+
+constexpr int kQueryStack = 128;
+
+// PairQueryCallback (:137-196) for one leaf hit. Returns true when the pair must become a contact.
+__device__ __forceinline__ bool acceptPair(const WorldDev& d, int queryKey, int queryType, int queryShape, int hitProxyId, int treeType, int hitShape,
+                                           int* shapeIdA, int* shapeIdB) {
+  int proxyKey = (hitProxyId << 2) | treeType;
+  if (proxyKey == queryKey) return false;
+  if (queryType == kDynamicBody) {
+    if (treeType == kDynamicBody && proxyKey < queryKey && d.trees[treeType].moved[hitProxyId]) return false;
+  } else if (d.trees[treeType].moved[hitProxyId]) return false;
+  if (pairSetContains(d, pairKey(hitShape, queryShape))) return false;
+  int a, b;
+  if (proxyKey < queryKey) { a = hitShape; b = queryShape; } else { a = queryShape; b = hitShape; }
+  const ShapeDev& sa = d.shapes[a]; const ShapeDev& sb = d.shapes[b];
+  if (sa.bodyId == sb.bodyId) return false;
+  if (sa.sensorIndex != -1 || sb.sensorIndex != -1) return false;
+  if (!shouldShapesCollide(sa, sb)) return false;
+  if (!shouldBodiesCollide(d, sa.bodyId, sb.bodyId)) return false;
+  if (!pairSupported(sa.geom.type, sb.geom.type)) return false;   // Contact.CreateContact returns early (src/Contact.cs:137-139)
+  *shapeIdA = a; *shapeIdB = b;
+  return true;
+}
+
+// DynamicTree.Query (src/DynamicTree.cs:531-557): explicit stack, child1 pushed first so child2 is visited first.
+template <bool FILL> __device__ inline int queryTree(const WorldDev& d, int treeType, Box fat, int queryKey, int queryType, int queryShape, int hitBase, int2* out, int outLast) {
+  const TreeDev& t = d.trees[treeType];
+  int root = t.meta[0];
+  if (t.meta[1] == 0 || root == -1) return 0;
+  int stack[kQueryStack];
+  int sp = 0, hits = 0;
+  stack[sp++] = root;
+  while (sp > 0) {
+    int id = stack[--sp];
+    Box nb = toBox(t.aabb[id]);
+    if (!boxOverlaps(nb, fat)) continue;        // maskBits == DEFAULT_MASK_BITS: the category test always passes for non-zero categories
+    if (t.cat[id] == 0) continue;
+    uint32_t hf = t.hf[id];
+    if ((hf >> 16) & NODE_LEAF) {
+      int a, b;
+      if (acceptPair(d, queryKey, queryType, queryShape, id, treeType, t.user[id], &a, &b)) {
+        if (FILL) out[outLast - (hitBase + hits)] = make_int2(a, b);
+        hits++;
+      }
+    } else {
+      int2 c = t.child[id];
+      if (sp + 2 > kQueryStack) { atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); continue; }
+      stack[sp++] = c.x; stack[sp++] = c.y;
+    }
+  }
+  return hits;
+}
+
+// FindPairsTask (:197-232). FILL=false counts accepted hits per move entry; FILL=true writes them in contact-creation
+// order: move index ascending, within a query the REVERSE of the hit order (the C# result list is LIFO, :193-194,:251-262).
+template <bool FILL> __global__ void __launch_bounds__(kThreads) k_find_pairs(WorldDev d) {
+  int n = d.sc->moveCount;
+  for (int i = gtid(); i < n; i += gsize()) {
+    int queryKey = d.moveArray[i];
+    int count = 0;
+    if (queryKey != -1) {
+      int type = queryKey & 3, id = queryKey >> 2;
+      Box fat = toBox(d.trees[type].aabb[id]);
+      int queryShape = d.trees[type].user[id];
+      int2* out = nullptr; int outLast = 0;
+      if (FILL) {
+        int begin = d.moveHitCount[i] + d.scanBlockSums[i >> 10];
+        int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) >> 10] : d.sc->newPairCount;
+        if (end > d.pairCapacity) { atomicOr(&d.sc->errorFlags, (int)ERR_PAIR_CAPACITY); continue; }
+        out = d.movePairs; outLast = end - 1;
+      }
+      if (type == kDynamicBody) {
+        count += queryTree<FILL>(d, kKinematicBody, fat, queryKey, type, queryShape, count, out, outLast);
+        count += queryTree<FILL>(d, kStaticBody, fat, queryKey, type, queryShape, count, out, outLast);
+      }
+      count += queryTree<FILL>(d, kDynamicBody, fat, queryKey, type, queryShape, count, out, outLast);
+    }
+    if (!FILL) d.moveHitCount[i] = count;
+  }
+}
+
+// World.CreateContact (src/Contact.cs:134-227), one thread per new pair in creation order. Ids come from the LIFO pool:
+// the r-th allocation pops freeArray[freeCount-1-r], then extends nextIndex (src/IDPool.cs:15-28).
+__global__ void __launch_bounds__(kThreads) k_create_contacts(WorldDev d) {
+  int n = d.sc->newPairCount;
+  int freeCount = d.sc->contactFreeCount, next = d.sc->contactNext;
+  for (int r = gtid(); r < n; r += gsize()) {
+    int id = r < freeCount ? d.contactFree[freeCount - 1 - r] : next + (r - freeCount);
+    if (id >= d.contactCapacity) { atomicOr(&d.sc->errorFlags, (int)ERR_CONTACT_CAPACITY); continue; }
+    int2 p = d.movePairs[r];
+    int a = p.x, b = p.y;
+    if (!pairPrimary(d.shapes[a].geom.type, d.shapes[b].geom.type)) { int t = a; a = b; b = t; }
+    const ShapeDev& sa = d.shapes[a]; const ShapeDev& sb = d.shapes[b];
+    uint32_t flags = CF_ALIVE;
+    if ((sa.flags | sb.flags) & SF_CONTACT_EVENTS) flags |= CF_ENABLE_CONTACT_EVENTS;
+    if ((sa.flags | sb.flags) & SF_HIT_EVENTS) flags |= CF_SHAPE_HIT;
+    d.cShape[id] = make_int2(a, b);
+    d.cBody[id] = make_int2(sa.bodyId, sb.bodyId);
+    d.cFlags[id] = flags;
+    d.cColor[id] = -1;
+    d.cGen[id] = d.cGen[id] + 1;
+    d.cConstraint[id] = -1;
+    float4 ma = sa.material, mb = sb.material;
+    d.cMat[id] = make_float4(sqrtf(ma.x * mb.x), netMax(ma.y, mb.y), 0.0f, 0.0f);   // src/World.cs:139-140
+    d.cMass[id] = make_float4(0, 0, 0, 0);
+    d.cSim[id] = make_int2(-1, -1);
+    float4 z = make_float4(0, 0, 0, 0);
+    d.mN[id] = z; d.mA0[id] = z; d.mA1[id] = z; d.mB0[id] = z; d.mB1[id] = z; d.mC0[id] = z; d.mC1[id] = z;
+  }
+}
+__global__ void __launch_bounds__(kThreads) k_clear_moved(WorldDev d) {
+  int n = d.sc->moveCount;
+  for (int i = gtid(); i < n; i += gsize()) {
+    int key = d.moveArray[i];
+    if (key != -1) d.trees[key & 3].moved[key >> 2] = 0;
+  }
+}
+__global__ void k_pairs_finish(WorldDev d) {
+  Scalars& s = *d.sc;
+  int n = s.newPairCount;
+  int fromFree = n < s.contactFreeCount ? n : s.contactFreeCount;
+  s.contactFreeCount -= fromFree;
+  s.contactNext += n - fromFree;
+  if (s.contactNext > d.contactCapacity) { s.contactNext = d.contactCapacity; s.errorFlags |= (int)ERR_CONTACT_CAPACITY; }
+  s.liveContactCount += n;
+  s.moveCount = 0;
+  s.beginCount = 0; s.hitCount = 0; s.jointEventCount = 0; s.anyRestitution = 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Phase 1a: BroadPhase.RebuildTrees (src/BroadPhase.cs:112-116) -> DynamicTree.Rebuild(false) (src/DynamicTree.cs:802-1000).
+// The topology this produces decides the DFS order of later queries, hence contact ids; it is reproduced step for step.
+// v1: one thread per tree walks the sequential algorithm (pyramids never enlarge; churn scenes pay for it).
+// ------------------------------------------------------------------------------------------------------------
+struct TreeRef {
+  const TreeDev& t;
+  __device__ int allocNode(Scalars* sc) {
+    int id = t.meta[2];
+    if (id == -1) { atomicOr(&sc->errorFlags, (int)ERR_TREE); return 0; }
+    t.meta[2] = t.parent[id];
+    t.aabb[id] = make_float4(0, 0, 0, 0); t.child[id] = make_int2(-1, -1); t.parent[id] = -1; t.hf[id] = (uint32_t)NODE_ALLOCATED << 16;
+    t.cat[id] = ~0ull; t.user[id] = -1;
+    t.meta[1]++;
+    return id;
+  }
+  __device__ void freeNode(int id) { t.parent[id] = t.meta[2]; t.hf[id] &= 0xffffu; t.meta[2] = id; t.meta[1]--; }
+};
+__device__ int partitionMid(int* indices, float2* centers, int count) {   // :802-847
+  if (count <= 2) return count / 2;
+  float2 lo = centers[0], hi = centers[0];
+  for (int i = 1; i < count; i++) {
+    float2 c = centers[i];
+    lo.x = lo.x < c.x ? lo.x : c.x; lo.y = lo.y < c.y ? lo.y : c.y;
+    hi.x = hi.x > c.x ? hi.x : c.x; hi.y = hi.y > c.y ? hi.y : c.y;
+  }
+  float dx = hi.x - lo.x, dy = hi.y - lo.y;
+  float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y);
+  int i1 = 0, i2 = count;
+  if (dx > dy) {
+    float pivot = cx;
+    while (i1 < i2) {
+      while (i1 < i2 && centers[i1].x < pivot) i1++;
+      while (i1 < i2 && centers[i2 - 1].x >= pivot) i2--;
+      if (i1 < i2) { int ti = indices[i1]; indices[i1] = indices[i2 - 1]; indices[i2 - 1] = ti; float2 tc = centers[i1]; centers[i1] = centers[i2 - 1]; centers[i2 - 1] = tc; i1++; i2--; }
+    }
+  } else {
+    float pivot = cy;
+    while (i1 < i2) {
+      while (i1 < i2 && centers[i1].y < pivot) i1++;
+      while (i1 < i2 && centers[i2 - 1].y >= pivot) i2--;
+      if (i1 < i2) { int ti = indices[i1]; indices[i1] = indices[i2 - 1]; indices[i2 - 1] = ti; float2 tc = centers[i1]; centers[i1] = centers[i2 - 1]; centers[i2 - 1] = tc; i1++; i2--; }
+    }
+  }
+  if (i1 > 0 && i1 < count) return i1;
+  return count / 2;
+}
+__device__ __forceinline__ void refitFromChildren(const TreeDev& t, int node) {
+  int2 c = t.child[node];
+  Box u = boxUnion(toBox(t.aabb[c.x]), toBox(t.aabb[c.y]));
+  t.aabb[node] = fromBox(u);
+  int h1 = (int)(t.hf[c.x] & 0xffffu), h2 = (int)(t.hf[c.y] & 0xffffu);
+  t.hf[node] = (t.hf[node] & 0xffff0000u) | (uint32_t)(1 + (h1 > h2 ? h1 : h2));
+  t.cat[node] = t.cat[c.x] | t.cat[c.y];
+}
+__global__ void k_tree_rebuild(WorldDev d) {
+  if (threadIdx.x != 0) return;
+  int treeType = blockIdx.x == 0 ? kDynamicBody : kKinematicBody;
+  const TreeDev& t = d.trees[treeType];
+  TreeRef tr{t};
+  int proxyCount = t.meta[3];
+  d.sc->rebuildLeafCount[treeType] = 0;
+  if (proxyCount == 0) return;
+  int root = t.meta[0];
+  if (!((t.hf[root] >> 16) & NODE_ENLARGED) || (t.hf[root] & 0xffffu) == 0) return;   // nothing flagged: Rebuild returns the same root
+  int* stack = t.stack; const int stackCap = t.stackCapacity;
+  int leafCount = 0, sp = 0;
+  int node = root;
+  while (true) {                                  // :969-993 collect leaves / untouched subtrees, free enlarged internals
+    uint32_t hf = t.hf[node];
+    if ((hf & 0xffffu) == 0 || !((hf >> 16) & NODE_ENLARGED)) {
+      t.leafIdx[leafCount] = node;
+      float4 a = t.aabb[node];
+      t.leafCtr[leafCount] = make_float2(0.5f * (a.x + a.z), 0.5f * (a.y + a.w));
+      leafCount++;
+      t.parent[node] = -1;
+    } else {
+      int doomed = node;
+      int2 c = t.child[node];
+      node = c.x;
+      if (sp >= stackCap) { atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); return; }
+      stack[sp++] = c.y;
+      tr.freeNode(doomed);
+      continue;
+    }
+    if (sp == 0) break;
+    node = stack[--sp];
+  }
+  d.sc->rebuildLeafCount[treeType] = leafCount;
+  // BuildTree :853-959 — items are (nodeIndex, childCount, startIndex, splitIndex, endIndex)
+  if (leafCount == 1) { t.parent[t.leafIdx[0]] = -1; t.meta[0] = t.leafIdx[0]; return; }
+  int* items = stack;
+  int top = 0;
+  {
+    int n = tr.allocNode(d.sc);
+    int split = partitionMid(t.leafIdx, t.leafCtr, leafCount);
+    items[0] = n; items[1] = -1; items[2] = 0; items[3] = split; items[4] = leafCount;
+  }
+  while (true) {
+    int* item = items + 5 * top;
+    item[1]++;
+    if (item[1] == 2) {
+      if (top == 0) break;
+      int doneNode = item[0];
+      top--;
+      int* parentItem = items + 5 * top;
+      if (parentItem[1] == 0) t.child[parentItem[0]].x = doneNode; else t.child[parentItem[0]].y = doneNode;
+      t.parent[doneNode] = parentItem[0];
+      refitFromChildren(t, doneNode);
+    } else {
+      int startIndex, endIndex;
+      if (item[1] == 0) { startIndex = item[2]; endIndex = item[3]; } else { startIndex = item[3]; endIndex = item[4]; }
+      int count = endIndex - startIndex;
+      if (count == 1) {
+        int childIndex = t.leafIdx[startIndex];
+        if (item[1] == 0) t.child[item[0]].x = childIndex; else t.child[item[0]].y = childIndex;
+        t.parent[childIndex] = item[0];
+      } else {
+        if (5 * (top + 2) > stackCap) { atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); return; }
+        int n = tr.allocNode(d.sc);
+        int split = startIndex + partitionMid(t.leafIdx + startIndex, t.leafCtr + startIndex, count);
+        top++;
+        int* ni = items + 5 * top;
+        ni[0] = n; ni[1] = -1; ni[2] = startIndex; ni[3] = split; ni[4] = endIndex;
+      }
+    }
+  }
+  int newRoot = items[0];
+  refitFromChildren(t, newRoot);
+  t.meta[0] = newRoot;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Phase 1b: CollideTask + UpdateContact (src/World.cs:261-310, src/Contact.cs:324-417), one thread per contact slot
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t fbits(float f) { return __float_as_uint(f); }
+__device__ __forceinline__ void loadPoint(MPoint& p, float4 a, float4 b, float4 c) {
+  p.anchorA = mk(a.x, a.y); p.anchorB = mk(a.z, a.w); p.separation = b.x; p.normalImpulse = b.y; p.tangentImpulse = b.z; p.totalNormalImpulse = b.w;
+  p.point = mk(c.x, c.y); p.normalVelocity = c.z; uint32_t w = fbits(c.w); p.id = w & 0xffffu; p.persisted = (w >> 16) & 1u;
+}
+__device__ __forceinline__ void storePoint(const MPoint& p, float4* a, float4* b, float4* c) {
+  *a = make_float4(p.anchorA.x, p.anchorA.y, p.anchorB.x, p.anchorB.y);
+  *b = make_float4(p.separation, p.normalImpulse, p.tangentImpulse, p.totalNormalImpulse);
+  *c = make_float4(p.point.x, p.point.y, p.normalVelocity, __uint_as_float((p.id & 0xffffu) | (p.persisted << 16)));
+}
+
+__global__ void __launch_bounds__(kThreads) k_collide(WorldDev d, StepParams sp) {
+  int n = d.sc->contactNext;
+  for (int i = gtid(); i < n; i += gsize()) {
+    uint32_t flags = d.cFlags[i];
+    int4 fs = make_int4(0, 0, 0, 0);
+    if (flags & CF_ALIVE) {
+      int2 sh = d.cShape[i];
+      bool overlap = boxOverlaps(toBox(d.shapeFat[sh.x]), toBox(d.shapeFat[sh.y]));
+      bool wasTouching = (flags & CF_TOUCHING) != 0;
+      bool events = (flags & CF_ENABLE_CONTACT_EVENTS) != 0;
+      if (!overlap) {
+        flags |= CF_DISJOINT;
+        fs.z = 1;                                   // destroy
+        if (wasTouching) { fs.w = 1; if (events) fs.y = 1; }     // graph removal + end event (DestroyContact :247-254)
+      } else {
+        const ShapeDev& sa = d.shapes[sh.x]; const ShapeDev& sb = d.shapes[sh.y];
+        int2 bd = d.cBody[i];
+        float4 massA = d.bodyMass[bd.x], massB = d.bodyMass[bd.y];
+        d.cSim[i] = make_int2(d.bodySim[bd.x], d.bodySim[bd.y]);
+        d.cMass[i] = make_float4(massA.x, massA.y, massB.x, massB.y);
+        Xf xfA = toXf(d.bodyXf[bd.x]), xfB = toXf(d.bodyXf[bd.y]);
+        V2 centerOffsetA = rotate(xfA.q, mk(massA.z, massA.w)), centerOffsetB = rotate(xfB.q, mk(massB.z, massB.w));
+        // UpdateContact
+        Manifold old; old.pointCount = (int)fbits(d.mN[i].w); old.rollingImpulse = d.mN[i].z;
+        loadPoint(old.p0, d.mA0[i], d.mB0[i], d.mC0[i]); loadPoint(old.p1, d.mA1[i], d.mB1[i], d.mC1[i]);
+        Manifold m = computeManifold(sa.geom, xfA, sb.geom, xfB);
+        float4 ma = sa.material, mb = sb.material;
+        float friction = sqrtf(ma.x * mb.x), restitution = netMax(ma.y, mb.y), rolling = 0.0f;
+        if (ma.z > 0.0f || mb.z > 0.0f) {
+          float rA = sa.geom.type == kSegment ? 0.0f : sa.geom.radius, rB = sb.geom.type == kSegment ? 0.0f : sb.geom.radius;
+          rolling = netMax(ma.z, mb.z) * netMax(rA, rB);
+        }
+        d.cMat[i] = make_float4(friction, restitution, rolling, ma.w + mb.w);
+        int pointCount = m.pointCount;
+        bool touching = pointCount > 0;
+        if (!sp.enableSpeculative && pointCount == 2) {            // Q7: tests point0 twice (src/Contact.cs:366,371)
+          if (m.p0.separation > 1.5f * kLinearSlop) { m.p0 = m.p1; m.pointCount = 1; }
+          pointCount = m.pointCount;
+        }
+        if (touching && (flags & CF_SHAPE_HIT)) flags |= CF_ENABLE_HIT; else flags &= ~CF_ENABLE_HIT;
+        if (pointCount > 0) m.rollingImpulse = old.rollingImpulse;
+        for (int k = 0; k < pointCount; k++) {
+          MPoint& mp2 = k == 1 ? m.p1 : m.p0;
+          mp2.anchorA = mp2.anchorA - centerOffsetA;
+          mp2.anchorB = mp2.anchorB - centerOffsetB;
+          mp2.tangentImpulse = 0; mp2.normalImpulse = 0; mp2.totalNormalImpulse = 0; mp2.normalVelocity = 0; mp2.persisted = 0;
+          for (int j = 0; j < old.pointCount; j++) {
+            MPoint& mp1 = j == 1 ? old.p1 : old.p0;
+            if (mp1.id == mp2.id) {
+              mp2.normalImpulse = mp1.normalImpulse; mp2.tangentImpulse = mp1.tangentImpulse; mp2.persisted = 1;
+              mp1.normalImpulse = 0; mp1.tangentImpulse = 0;
+              break;
+            }
+          }
+        }
+        d.mN[i] = make_float4(m.normal.x, m.normal.y, m.rollingImpulse, __uint_as_float((uint32_t)m.pointCount));
+        storePoint(m.p0, &d.mA0[i], &d.mB0[i], &d.mC0[i]); storePoint(m.p1, &d.mA1[i], &d.mB1[i], &d.mC1[i]);
+        if (touching && !wasTouching) { flags |= CF_STARTED; fs.w = 1; if (events) fs.x = 1; }
+        else if (!touching && wasTouching) { flags |= CF_STOPPED; fs.w = 1; if (events) fs.y = 1; }
+      }
+      d.cFlags[i] = flags;
+    }
+    d.flagScan[i] = fs;
+  }
+}
+
+// Serial pass of World.Collide (:382-450) as ordered compaction: events, id recycling and graph ops in ascending contactId.
+__global__ void __launch_bounds__(kThreads) k_contact_events(WorldDev d, StepParams sp) {
+  int n = d.sc->contactNext;
+  int freeCount = d.sc->contactFreeCount;
+  for (int i = gtid(); i < n; i += gsize()) {
+    uint32_t flags = d.cFlags[i];
+    if (!(flags & CF_STATE_MASK)) continue;
+    int4 rank = addT(d.flagScan[i], d.scanBlockSums4[i >> 10]);
+    int2 sh = d.cShape[i];
+    B2CContactTouchEvent ev = {sh.x, sh.y, i, d.cGen[i]};
+    if (flags & CF_DISJOINT) {
+      if ((flags & CF_TOUCHING) && (flags & CF_ENABLE_CONTACT_EVENTS)) d.endEvents[sp.endIndex][rank.y] = ev;
+      d.contactFree[freeCount + rank.z] = i;
+      if (flags & CF_TOUCHING) d.opList[rank.w] = i;
+      d.cFlags[i] = 0;                             // slot is dead; cBody/cColor stay readable for the graph op
+    } else if (flags & CF_STARTED) {
+      if (flags & CF_ENABLE_CONTACT_EVENTS) d.beginEvents[rank.x] = ev;
+      d.opList[rank.w] = i;
+      d.cFlags[i] = (flags & ~CF_STATE_MASK) | CF_TOUCHING;
+    } else {
+      if (flags & CF_ENABLE_CONTACT_EVENTS) d.endEvents[sp.endIndex][rank.y] = ev;
+      d.opList[rank.w] = i;
+      d.cFlags[i] = flags & ~(CF_STATE_MASK | CF_TOUCHING);
+    }
+  }
+}
+__global__ void k_events_finish(WorldDev d, StepParams sp, int4* totals) {
+  Scalars& s = *d.sc;
+  int4 t = *totals;
+  if (s.contactNext == 0) t = make_int4(0, 0, 0, 0);
+  s.beginCount = t.x; s.endCount[sp.endIndex] = t.y;
+  s.contactFreeCount += t.z; s.liveContactCount -= t.z;
+  s.opCount = t.w;
+  if (t.w > 0) s.graphDirty = 1;
+}
+
+// AddContactToGraph / RemoveContactFromGraph (src/ConstraintGraph.cs:135-241) in ascending contactId order.
+// An op may run once it is the lowest pending op on both of its dynamic bodies, which yields exactly the sequential result.
+__global__ void __launch_bounds__(1024) k_color_ops(WorldDev d) {
+  __shared__ int sRemaining;
+  int n = d.sc->opCount;
+  if (n == 0) return;
+  for (int k = threadIdx.x; k < n; k += blockDim.x) d.opDone[k] = 0;
+  __syncthreads();
+  int rounds = 0;
+  while (true) {
+    if (threadIdx.x == 0) sRemaining = 0;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+      if (d.opDone[k]) continue;
+      int2 b = d.cBody[d.opList[k]];
+      if (d.bodyType[b.x] == kDynamicBody) atomicMin(&d.bodyMinOp[b.x], k);
+      if (d.bodyType[b.y] == kDynamicBody) atomicMin(&d.bodyMinOp[b.y], k);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+      if (d.opDone[k]) continue;
+      int id = d.opList[k];
+      int2 b = d.cBody[id];
+      int typeA = d.bodyType[b.x], typeB = d.bodyType[b.y];
+      bool ready = (typeA != kDynamicBody || d.bodyMinOp[b.x] == k) && (typeB != kDynamicBody || d.bodyMinOp[b.y] == k);
+      if (!ready) { sRemaining = 1; continue; }
+      int color = d.cColor[id];
+      if (color == -1) {                           // add
+        uint32_t mA = d.bodyColorMask[b.x], mB = d.bodyColorMask[b.y];
+        int c = kOverflowIndex;
+        if (typeA != kStaticBody && typeB != kStaticBody) {
+          uint32_t freeBits = ~(mA | mB) & ((1u << kDynamicColorCount) - 1u);
+          if (freeBits) c = __ffs((int)freeBits) - 1;
+          if (c != kOverflowIndex) { if (typeA == kDynamicBody) mA |= 1u << c; if (typeB == kDynamicBody) mB |= 1u << c; }
+        } else if (typeA == kDynamicBody) {
+          uint32_t freeBits = ~mA & 0x007ffffeu;    // colors 22..1
+          if (freeBits) { c = 31 - __clz((int)freeBits); mA |= 1u << c; }
+        } else if (typeB == kDynamicBody) {
+          uint32_t freeBits = ~mB & 0x007ffffeu;
+          if (freeBits) { c = 31 - __clz((int)freeBits); mB |= 1u << c; }
+        }
+        if (typeA == kDynamicBody) d.bodyColorMask[b.x] = mA;
+        if (typeB == kDynamicBody) d.bodyColorMask[b.y] = mB;
+        d.cColor[id] = c;
+        if (c == kOverflowIndex) atomicOr(&d.sc->errorFlags, (int)ERR_OVERFLOW_COLOR);
+      } else {                                     // remove
+        if (color != kOverflowIndex) {
+          if (typeA == kDynamicBody) d.bodyColorMask[b.x] &= ~(1u << color);
+          if (typeB == kDynamicBody) d.bodyColorMask[b.y] &= ~(1u << color);
+        }
+        d.cColor[id] = -1;
+      }
+      d.opDone[k] = 2;                             // done this round: still has to reset its bodies below
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+      if (d.opDone[k] == 1) continue;
+      int2 b = d.cBody[d.opList[k]];
+      d.bodyMinOp[b.x] = 0x7f7f7f7f; d.bodyMinOp[b.y] = 0x7f7f7f7f;
+      if (d.opDone[k] == 2) d.opDone[k] = 1;
+    }
+    rounds++;
+    __syncthreads();
+    if (sRemaining == 0) break;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) d.sc->colorRounds = rounds;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Phase 2a: group touching contacts by color (stable in contactId) — the per-color arrays of GraphColor.contactSims.
+// Rebuilt only on steps where the graph changed.
+// ------------------------------------------------------------------------------------------------------------
+constexpr int kSortChunk = 256;
+__global__ void __launch_bounds__(kSortChunk) k_color_hist(WorldDev d) {
+  if (!d.sc->graphDirty) return;
+  __shared__ int hist[kGraphColorCount];
+  int n = d.sc->contactNext;
+  int chunks = (n + kSortChunk - 1) / kSortChunk;
+  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+    if (threadIdx.x < kGraphColorCount) hist[threadIdx.x] = 0;
+    __syncthreads();
+    int i = c * kSortChunk + threadIdx.x;
+    if (i < n && (d.cFlags[i] & CF_TOUCHING)) atomicAdd(&hist[d.cColor[i]], 1);
+    __syncthreads();
+    if (threadIdx.x < kGraphColorCount) d.blockHist[c * kGraphColorCount + threadIdx.x] = hist[threadIdx.x];
+    __syncthreads();
+  }
+}
+__global__ void k_color_offsets(WorldDev d) {
+  if (!d.sc->graphDirty) return;
+  __shared__ int counts[kGraphColorCount];
+  int n = d.sc->contactNext;
+  int chunks = (n + kSortChunk - 1) / kSortChunk;
+  int c = threadIdx.x;
+  if (c < kGraphColorCount) {
+    int run = 0;
+    for (int k = 0; k < chunks; k++) { int v = d.blockHist[k * kGraphColorCount + c]; d.blockHist[k * kGraphColorCount + c] = run; run += v; }
+    counts[c] = run;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int start = 0, touching = 0;
+    for (int k = 0; k < kGraphColorCount; k++) {
+      d.sc->colorCount[k] = counts[k]; d.sc->colorStart[k] = start;
+      start += (counts[k] + 31) & ~31;
+      touching += counts[k];
+    }
+    d.sc->constraintTotal = start;
+    d.sc->touchingCount = touching;
+  }
+}
+__global__ void __launch_bounds__(kSortChunk) k_color_scatter(WorldDev d) {
+  if (!d.sc->graphDirty) return;
+  __shared__ int warpHist[kSortChunk / 32][kGraphColorCount];
+  int n = d.sc->contactNext;
+  int chunks = (n + kSortChunk - 1) / kSortChunk;
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+    for (int k = threadIdx.x; k < (kSortChunk / 32) * kGraphColorCount; k += blockDim.x) (&warpHist[0][0])[k] = 0;
+    __syncthreads();
+    int i = c * kSortChunk + threadIdx.x;
+    int color = -1;
+    if (i < n && (d.cFlags[i] & CF_TOUCHING)) color = d.cColor[i];
+    unsigned peers = __match_any_sync(0xffffffffu, color);
+    int rankInWarp = __popc(peers & ((1u << lane) - 1u));
+    if (color >= 0 && rankInWarp == 0) warpHist[warp][color] = __popc(peers);
+    __syncthreads();
+    if (color >= 0) {
+      int before = 0;
+      for (int w = 0; w < warp; w++) before += warpHist[w][color];
+      int t = d.sc->colorStart[color] + d.blockHist[c * kGraphColorCount + color] + before + rankInWarp;
+      d.sContact[t] = i;
+      d.cConstraint[i] = t;
+    } else if (i < n) d.cConstraint[i] = -1;
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Phase 2b: solver stages (src/Solver.cs:599-727, src/ContactSolver.cs:362-1026 AVX lanes, src/joints/RevoluteJoint.cs)
+// ------------------------------------------------------------------------------------------------------------
+struct BodyW { V2 v; float w; uint32_t flags; V2 dp; Rot dq; };
+__device__ __forceinline__ BodyW gatherBody(const WorldDev& d, int index) {        // GatherBodies :415-451
+  BodyW b;
+  if (index < 0) { b.v = mk(0, 0); b.w = 0; b.flags = 0; b.dp = mk(0, 0); b.dq = mkRot(1, 0); return b; }
+  float4 a = d.st0[index], c = d.st1[index];
+  b.v = mk(a.x, a.y); b.w = a.z; b.flags = fbits(a.w); b.dp = mk(c.x, c.y); b.dq = mkRot(c.z, c.w);
+  return b;
+}
+__device__ __forceinline__ void scatterBody(const WorldDev& d, int index, const BodyW& b) {   // ScatterBodies :452-479 (v,w only change)
+  if (index >= 0 && (b.flags & kDynamicFlag)) d.st0[index] = make_float4(b.v.x, b.v.y, b.w, __uint_as_float(b.flags));
+}
+
+struct Lane {       // one constraint's read-only planes in registers
+  int indexA, indexB; float mA, mB, iA, iB; V2 n; float friction, tangentSpeed, rollingResistance, rollingMass;
+  float biasRate, massScale, impulseScale, restitution; V2 rA1, rB1, rA2, rB2; float normalMass1, tangentMass1, normalMass2, tangentMass2;
+  float baseSep1, baseSep2, relVel1, relVel2;
+};
+__device__ __forceinline__ void loadLane(const WorldDev& d, int t, Lane& c, bool anchorsOnly) {
+  float4 A = d.sA[t], B = d.sB[t], E = d.sE[t], F = d.sF[t];
+  c.indexA = (int)fbits(A.x); c.indexB = (int)fbits(A.y); c.mA = A.z; c.mB = A.w; c.iA = B.x; c.iB = B.y; c.n = mk(B.z, B.w);
+  c.rA1 = mk(E.x, E.y); c.rB1 = mk(E.z, E.w); c.rA2 = mk(F.x, F.y); c.rB2 = mk(F.z, F.w);
+  if (anchorsOnly) return;
+  float4 C = d.sC[t], D = d.sD[t], G = d.sG[t], H = d.sH[t];
+  c.friction = C.x; c.tangentSpeed = C.y; c.rollingResistance = C.z; c.rollingMass = C.w;
+  c.biasRate = D.x; c.massScale = D.y; c.impulseScale = D.z; c.restitution = D.w;
+  c.normalMass1 = G.x; c.tangentMass1 = G.y; c.normalMass2 = G.z; c.tangentMass2 = G.w;
+  c.baseSep1 = H.x; c.baseSep2 = H.y; c.relVel1 = H.z; c.relVel2 = H.w;
+}
+__device__ __forceinline__ void applyP(BodyW& bA, BodyW& bB, const Lane& c, V2 rA, V2 rB, float Px, float Py) {   // :794-805
+  bA.v.x = bA.v.x - c.mA * Px; bA.v.y = bA.v.y - c.mA * Py;
+  bA.w = bA.w - c.iA * (rA.x * Py - rA.y * Px);
+  bB.v.x = bB.v.x + c.mB * Px; bB.v.y = bB.v.y + c.mB * Py;
+  bB.w = bB.w + c.iB * (rB.x * Py - rB.y * Px);
+}
+
+// PrepareContactsTask :480-685
+__device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
+  int ci = d.sContact[t];
+  float warmStartScale = sp.enableWarmStarting ? 1.0f : 0.0f;
+  int2 idx = d.cSim[ci];
+  float4 mass = d.cMass[ci];
+  float mA = mass.x, iA = mass.y, mB = mass.z, iB = mass.w;
+  V2 vA = mk(0, 0), vB = mk(0, 0); float wA = 0, wB = 0;
+  if (idx.x != -1) { float4 s = d.st0[idx.x]; vA = mk(s.x, s.y); wA = s.z; }
+  if (idx.y != -1) { float4 s = d.st0[idx.y]; vB = mk(s.x, s.y); wB = s.z; }
+  float k = iA + iB;
+  float rollingMass = k > 0.0f ? 1.0f / k : 0.0f;
+  Softness soft = sp.contactSoftness;
+  if (idx.x == -1 || idx.y == -1) soft = sp.staticSoftness;
+  else if (sp.enableContactSoftening) {
+    float contactHertz = netMin(sp.contactHertz, 0.125f * sp.inv_h);
+    float ratio = 1.0f;
+    if (mA < mB) ratio = netMax(0.5f, mA / mB); else if (mB < mA) ratio = netMax(0.5f, mB / mA);
+    soft = makeSoft(ratio * contactHertz, ratio * sp.contactDampingRatio, sp.h);
+  }
+  float4 mn = d.mN[ci], mat = d.cMat[ci];
+  V2 normal = mk(mn.x, mn.y);
+  int pointCount = (int)fbits(mn.w);
+  V2 tangent = rightPerp(normal);
+  d.sA[t] = make_float4(__int_as_float(idx.x), __int_as_float(idx.y), mA, mB);
+  d.sB[t] = make_float4(iA, iB, normal.x, normal.y);
+  d.sC[t] = make_float4(mat.x, mat.w, mat.z, rollingMass);
+  d.sD[t] = make_float4(soft.biasRate, soft.massScale, soft.impulseScale, mat.y);
+  float4 E, F = make_float4(0, 0, 0, 0), G = make_float4(0, 0, 0, 0), H = make_float4(0, 0, 0, 0), I = make_float4(0, 0, 0, 0);
+  {
+    float4 a = d.mA0[ci], b = d.mB0[ci];
+    V2 rA = mk(a.x, a.y), rB = mk(a.z, a.w);
+    E = a;
+    H.x = b.x - dot(rB - rA, normal);
+    I.x = warmStartScale * b.y; I.y = warmStartScale * b.z;
+    float rnA = cross(rA, normal), rnB = cross(rB, normal);
+    float kNormal = mA + mB + iA * rnA * rnA + iB * rnB * rnB;
+    G.x = kNormal > 0.0f ? 1.0f / kNormal : 0.0f;
+    float rtA = cross(rA, tangent), rtB = cross(rB, tangent);
+    float kTangent = mA + mB + iA * rtA * rtA + iB * rtB * rtB;
+    G.y = kTangent > 0.0f ? 1.0f / kTangent : 0.0f;
+    V2 vrA = vA + crossSV(wA, rA), vrB = vB + crossSV(wB, rB);
+    H.z = dot(normal, vrB - vrA);
+  }
+  if (pointCount == 2) {
+    float4 a = d.mA1[ci], b = d.mB1[ci];
+    V2 rA = mk(a.x, a.y), rB = mk(a.z, a.w);
+    F = a;
+    H.y = b.x - dot(rB - rA, normal);
+    I.z = warmStartScale * b.y; I.w = warmStartScale * b.z;
+    float rnA = cross(rA, normal), rnB = cross(rB, normal);
+    float kNormal = mA + mB + iA * rnA * rnA + iB * rnB * rnB;
+    G.z = kNormal > 0.0f ? 1.0f / kNormal : 0.0f;
+    float rtA = cross(rA, tangent), rtB = cross(rB, tangent);
+    float kTangent = mA + mB + iA * rtA * rtA + iB * rtB * rtB;
+    G.w = kTangent > 0.0f ? 1.0f / kTangent : 0.0f;
+    V2 vrA = vA + crossSV(wA, rA), vrB = vB + crossSV(wB, rB);
+    H.w = dot(normal, vrB - vrA);
+  }
+  d.sE[t] = E; d.sF[t] = F; d.sG[t] = G; d.sH[t] = H; d.sI[t] = I;
+  d.sJ[t] = make_float4(0.0f, 0.0f, warmStartScale * mn.z, 0.0f);
+  if (!(mat.y == 0.0f)) d.sc->anyRestitution = 1;
+}
+
+// WarmStartContactsTask :686-744
+__device__ __forceinline__ void warmStartContact(const WorldDev& d, int t) {
+  Lane c; loadLane(d, t, c, true);
+  float4 I = d.sI[t]; float rollingImpulse = d.sJ[t].z;
+  BodyW bA = gatherBody(d, c.indexA), bB = gatherBody(d, c.indexB);
+  float tangentX = c.n.y, tangentY = 0.0f - c.n.x;
+  {
+    float Px = I.x * c.n.x + I.y * tangentX, Py = I.x * c.n.y + I.y * tangentY;
+    bA.w = bA.w - c.iA * (c.rA1.x * Py - c.rA1.y * Px);
+    bA.v.x = bA.v.x - c.mA * Px; bA.v.y = bA.v.y - c.mA * Py;
+    bB.w = bB.w + c.iB * (c.rB1.x * Py - c.rB1.y * Px);
+    bB.v.x = bB.v.x + c.mB * Px; bB.v.y = bB.v.y + c.mB * Py;
+  }
+  {
+    float Px = I.z * c.n.x + I.w * tangentX, Py = I.z * c.n.y + I.w * tangentY;
+    bA.w = bA.w - c.iA * (c.rA2.x * Py - c.rA2.y * Px);
+    bA.v.x = bA.v.x - c.mA * Px; bA.v.y = bA.v.y - c.mA * Py;
+    bB.w = bB.w + c.iB * (c.rB2.x * Py - c.rB2.y * Px);
+    bB.v.x = bB.v.x + c.mB * Px; bB.v.y = bB.v.y + c.mB * Py;
+  }
+  bA.w = bA.w - c.iA * rollingImpulse;
+  bB.w = bB.w + c.iB * rollingImpulse;
+  scatterBody(d, c.indexA, bA); scatterBody(d, c.indexB, bB);
+}
+
+__device__ __forceinline__ void solveNormalPoint(BodyW& bA, BodyW& bB, const Lane& c, V2 dp, V2 rA, V2 rB, float baseSeparation, float normalMass,
+                                                 float& normalImpulse, float& totalP, float& total, float inv_h, float contactSpeed,
+                                                 float biasRate, float massScale, float impulseScale) {   // :773-806
+  V2 rsA = rotate(bA.dq, rA), rsB = rotate(bB.dq, rB);
+  float dsx = dp.x + (rsB.x - rsA.x), dsy = dp.y + (rsB.y - rsA.y);
+  float s = (c.n.x * dsx + c.n.y * dsy) + baseSeparation;
+  bool mask = s > 0.0f;
+  float specBias = s * inv_h, softBias = avxMax(biasRate * s, contactSpeed);
+  float bias = mask ? specBias : softBias;
+  float pointMassScale = mask ? 1.0f : massScale;
+  float pointImpulseScale = mask ? 0.0f : impulseScale;
+  float dvx = (bB.v.x - bB.w * rB.y) - (bA.v.x - bA.w * rA.y);
+  float dvy = (bB.v.y + bB.w * rB.x) - (bA.v.y + bA.w * rA.x);
+  float vn = dvx * c.n.x + dvy * c.n.y;
+  float negImpulse = normalMass * (pointMassScale * vn + bias) + pointImpulseScale * normalImpulse;
+  float newImpulse = avxMax(normalImpulse - negImpulse, 0.0f);
+  float impulse = newImpulse - normalImpulse;
+  normalImpulse = newImpulse;
+  totalP = totalP + newImpulse;
+  total = total + newImpulse;
+  applyP(bA, bB, c, rA, rB, impulse * c.n.x, impulse * c.n.y);
+}
+__device__ __forceinline__ void solveFrictionPoint(BodyW& bA, BodyW& bB, const Lane& c, V2 rA, V2 rB, float tangentX, float tangentY, float tangentMass,
+                                                   float normalImpulse, float& tangentImpulse) {          // :844-871
+  float dvx = (bB.v.x - bB.w * rB.y) - (bA.v.x - bA.w * rA.y);
+  float dvy = (bB.v.y + bB.w * rB.x) - (bA.v.y + bA.w * rA.x);
+  float vt = dvx * tangentX + dvy * tangentY;
+  vt = vt - c.tangentSpeed;
+  float negImpulse = tangentMass * vt;
+  float maxFriction = c.friction * normalImpulse;
+  float newImpulse = tangentImpulse - negImpulse;
+  newImpulse = avxMax(0.0f - maxFriction, avxMin(newImpulse, maxFriction));
+  float impulse = newImpulse - tangentImpulse;
+  tangentImpulse = newImpulse;
+  applyP(bA, bB, c, rA, rB, impulse * tangentX, impulse * tangentY);
+}
+// SolveContactsTask :745-912 (useBias=true: Solve, false: Relax)
+template <bool USE_BIAS> __device__ __forceinline__ void solveContact(const WorldDev& d, const StepParams& sp, int t) {
+  Lane c; loadLane(d, t, c, false);
+  float4 I = d.sI[t], J = d.sJ[t];
+  float contactSpeed = -sp.contactSpeed;
+  BodyW bA = gatherBody(d, c.indexA), bB = gatherBody(d, c.indexB);
+  float biasRate, massScale, impulseScale;
+  if (USE_BIAS) { biasRate = c.massScale * c.biasRate; massScale = c.massScale; impulseScale = c.impulseScale; }
+  else { biasRate = 0.0f; massScale = 1.0f; impulseScale = 0.0f; }
+  float totalNormalImpulse = 0.0f;
+  V2 dp = mk(bB.dp.x - bA.dp.x, bB.dp.y - bA.dp.y);
+  solveNormalPoint(bA, bB, c, dp, c.rA1, c.rB1, c.baseSep1, c.normalMass1, I.x, J.x, totalNormalImpulse, sp.inv_h, contactSpeed, biasRate, massScale, impulseScale);
+  solveNormalPoint(bA, bB, c, dp, c.rA2, c.rB2, c.baseSep2, c.normalMass2, I.z, J.y, totalNormalImpulse, sp.inv_h, contactSpeed, biasRate, massScale, impulseScale);
+  float tangentX = c.n.y, tangentY = 0.0f - c.n.x;
+  solveFrictionPoint(bA, bB, c, c.rA1, c.rB1, tangentX, tangentY, c.tangentMass1, I.x, I.y);
+  solveFrictionPoint(bA, bB, c, c.rA2, c.rB2, tangentX, tangentY, c.tangentMass2, I.z, I.w);
+  {
+    float deltaLambda = c.rollingMass * (bA.w - bB.w);
+    float lambda = J.z;
+    float maxLambda = c.rollingResistance * totalNormalImpulse;
+    J.z = avxMax(0.0f - maxLambda, avxMin(lambda + deltaLambda, maxLambda));
+    deltaLambda = J.z - lambda;
+    bA.w = bA.w - c.iA * deltaLambda;
+    bB.w = bB.w + c.iB * deltaLambda;
+  }
+  d.sI[t] = I; d.sJ[t] = J;
+  scatterBody(d, c.indexA, bA); scatterBody(d, c.indexB, bB);
+}
+
+// ApplyRestitutionTask :913-989, with quirk Q1 (multiplies by the compare mask, not the blended mass). The reference skips an
+// 8-lane SIMD group when all its lanes have restitution 0; groups here are 8 consecutive constraints of the device's color order.
+__device__ __forceinline__ void restitutionPoint(BodyW& bA, BodyW& bB, const Lane& c, V2 rA, V2 rB, float relativeVelocity, float& normalImpulse,
+                                                 float& totalP, float threshold, bool restitutionMask) {
+  bool mask1 = (relativeVelocity + threshold) > 0.0f;
+  bool mask2 = totalP == 0.0f;
+  float mask = (mask1 || mask2 || restitutionMask) ? __uint_as_float(0xffffffffu) : 0.0f;
+  float dvx = (bB.v.x - bB.w * rB.y) - (bA.v.x - bA.w * rA.y);
+  float dvy = (bB.v.y + bB.w * rB.x) - (bA.v.y + bA.w * rA.x);
+  float vn = dvx * c.n.x + dvy * c.n.y;
+  float negImpulse = mask * (vn + c.restitution * relativeVelocity);
+  float newImpulse = avxMax(normalImpulse - negImpulse, 0.0f);
+  float deltaImpulse = newImpulse - normalImpulse;
+  normalImpulse = newImpulse;
+  totalP = totalP + deltaImpulse;
+  applyP(bA, bB, c, rA, rB, deltaImpulse * c.n.x, deltaImpulse * c.n.y);
+}
+__device__ __forceinline__ void restitutionContact(const WorldDev& d, const StepParams& sp, int t, int colorBegin, int colorEnd) {
+  int g0 = colorBegin + ((t - colorBegin) & ~7);
+  bool allZero = true;
+  for (int k = g0; k < g0 + 8 && k < colorEnd; k++) if (!(d.sD[k].w == 0.0f)) allZero = false;
+  if (allZero) return;
+  Lane c; loadLane(d, t, c, false);
+  float4 I = d.sI[t], J = d.sJ[t];
+  BodyW bA = gatherBody(d, c.indexA), bB = gatherBody(d, c.indexB);
+  bool restitutionMask = c.restitution == 0.0f;
+  restitutionPoint(bA, bB, c, c.rA1, c.rB1, c.relVel1, I.x, J.x, sp.restitutionThreshold, restitutionMask);
+  restitutionPoint(bA, bB, c, c.rA2, c.rB2, c.relVel2, I.z, J.y, sp.restitutionThreshold, restitutionMask);
+  d.sI[t] = I; d.sJ[t] = J;
+  scatterBody(d, c.indexA, bA); scatterBody(d, c.indexB, bB);
+}
+// StoreImpulsesTask :990-1025
+__device__ __forceinline__ void storeImpulses(const WorldDev& d, int t) {
+  int ci = d.sContact[t];
+  float4 I = d.sI[t], J = d.sJ[t], H = d.sH[t];
+  d.mN[ci].z = J.z;
+  float4 b0 = d.mB0[ci], b1 = d.mB1[ci];
+  b0.y = I.x; b0.z = I.y; b0.w = J.x; b1.y = I.z; b1.z = I.w; b1.w = J.y;
+  d.mB0[ci] = b0; d.mB1[ci] = b1;
+  d.mC0[ci].z = H.z; d.mC1[ci].z = H.w;
+}
+
+// ---- revolute joint (src/Joint.cs:125-130, src/joints/RevoluteJoint.cs:72-235) ----
+__device__ void prepareJoint(const WorldDev& d, const StepParams& sp, JointDev& j) {
+  float hertz = netMin(j.constraintHertz, 0.25f * sp.inv_h);
+  j.constraintSoftness = makeSoft(hertz, j.constraintDampingRatio, sp.h);
+  float4 massA = d.bodyMass[j.bodyIdA], massB = d.bodyMass[j.bodyIdB];
+  j.invMassA = massA.x; j.invIA = massA.y; j.invMassB = massB.x; j.invIB = massB.y;
+  j.indexA = d.bodySim[j.bodyIdA]; j.indexB = d.bodySim[j.bodyIdB];
+  Xf xfA = toXf(d.bodyXf[j.bodyIdA]), xfB = toXf(d.bodyXf[j.bodyIdB]);
+  j.frameA.q = mulRot(xfA.q, j.localFrameA.q);
+  j.frameA.p = rotate(xfA.q, j.localFrameA.p - mk(massA.z, massA.w));
+  j.frameB.q = mulRot(xfB.q, j.localFrameB.q);
+  j.frameB.p = rotate(xfB.q, j.localFrameB.p - mk(massB.z, massB.w));
+  float2 cA = d.bodyCenter[j.bodyIdA], cB = d.bodyCenter[j.bodyIdB];
+  j.deltaCenter = mk(cB.x, cB.y) - mk(cA.x, cA.y);
+  float k = j.invIA + j.invIB;
+  j.axialMass = k > 0.0f ? 1.0f / k : 0.0f;
+  j.springSoftness = makeSoft(j.hertz, j.dampingRatio, sp.h);
+  if (!sp.enableWarmStarting) { j.linearImpulse = mk(0, 0); j.springImpulse = 0; j.motorImpulse = 0; j.lowerImpulse = 0; j.upperImpulse = 0; }
+}
+__device__ void warmStartJoint(const WorldDev& d, JointDev& j) {
+  BodyW bA = gatherBody(d, j.indexA), bB = gatherBody(d, j.indexB);
+  V2 rA = rotate(bA.dq, j.frameA.p), rB = rotate(bB.dq, j.frameB.p);
+  float axialImpulse = j.springImpulse + j.motorImpulse + j.lowerImpulse - j.upperImpulse;
+  if (bA.flags & kDynamicFlag) {
+    bA.v = mulSub(bA.v, j.invMassA, j.linearImpulse);
+    bA.w -= j.invIA * (cross(rA, j.linearImpulse) + axialImpulse);
+  }
+  if (bB.flags & kDynamicFlag) {
+    bB.v = mulAdd(bB.v, j.invMassB, j.linearImpulse);
+    bB.w += j.invIB * (cross(rB, j.linearImpulse) + axialImpulse);
+  }
+  scatterBody(d, j.indexA, bA); scatterBody(d, j.indexB, bB);
+}
+__device__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {
+  float mA = j.invMassA, mB = j.invMassB, iA = j.invIA, iB = j.invIB;
+  BodyW bA = gatherBody(d, j.indexA), bB = gatherBody(d, j.indexB);
+  V2 vA = bA.v, vB = bB.v; float wA = bA.w, wB = bB.w;
+  Rot qA = mulRot(bA.dq, j.frameA.q), qB = mulRot(bB.dq, j.frameB.q);
+  Rot relQ = invMulRot(qA, qB);
+  bool fixedRotation = iA + iB == 0.0f;
+  if (j.enableSpring && !fixedRotation) {
+    float jointAngle = atan2f(relQ.s, relQ.c);
+    float jointAngleDelta = fmodf((jointAngle - j.targetAngle) + kPi, kTau) - kPi;
+    float bias = j.springSoftness.biasRate * jointAngleDelta;
+    float massScale = j.springSoftness.massScale, impulseScale = j.springSoftness.impulseScale;
+    float Cdot = wB - wA;
+    float impulse = -massScale * j.axialMass * (Cdot + bias) - impulseScale * j.springImpulse;
+    j.springImpulse += impulse;
+    wA -= iA * impulse; wB += iB * impulse;
+  }
+  if (j.enableMotor && !fixedRotation) {
+    float Cdot = wB - wA - j.motorSpeed;
+    float impulse = -j.axialMass * Cdot;
+    float oldImpulse = j.motorImpulse;
+    float maxImpulse = sp.h * j.maxMotorTorque;
+    j.motorImpulse = netClamp(j.motorImpulse + impulse, -maxImpulse, maxImpulse);
+    impulse = j.motorImpulse - oldImpulse;
+    wA -= iA * impulse; wB += iB * impulse;
+  }
+  if (j.enableLimit && !fixedRotation) {
+    float jointAngle = atan2f(relQ.s, relQ.c);
+    {
+      float C = jointAngle - j.lowerAngle;
+      float bias = 0.0f, massScale = 1.0f, impulseScale = 0.0f;
+      if (C > 0.0f) bias = C * sp.inv_h;
+      else if (useBias) { bias = j.constraintSoftness.biasRate * C; massScale = j.constraintSoftness.massScale; impulseScale = j.constraintSoftness.impulseScale; }
+      float Cdot = wB - wA;
+      float oldImpulse = j.lowerImpulse;
+      float impulse = -massScale * j.axialMass * (Cdot + bias) - impulseScale * oldImpulse;
+      j.lowerImpulse = netMax(oldImpulse + impulse, 0.0f);
+      impulse = j.lowerImpulse - oldImpulse;
+      wA -= iA * impulse; wB += iB * impulse;
+    }
+    {
+      float C = j.upperAngle - jointAngle;
+      float bias = 0.0f, massScale = 1.0f, impulseScale = 0.0f;
+      if (C > 0.0f) bias = C * sp.inv_h;
+      else if (useBias) { bias = j.constraintSoftness.biasRate * C; massScale = j.constraintSoftness.massScale; impulseScale = j.constraintSoftness.impulseScale; }
+      float Cdot = wA - wB;
+      float oldImpulse = j.upperImpulse;
+      float impulse = -massScale * j.axialMass * (Cdot + bias) - impulseScale * oldImpulse;
+      j.upperImpulse = netMax(oldImpulse + impulse, 0.0f);
+      impulse = j.upperImpulse - oldImpulse;
+      wA += iA * impulse; wB -= iB * impulse;
+    }
+  }
+  {
+    V2 rA = rotate(bA.dq, j.frameA.p), rB = rotate(bB.dq, j.frameB.p);
+    V2 Cdot = (vB + crossSV(wB, rB)) - (vA + crossSV(wA, rA));
+    V2 bias = mk(0, 0);
+    float massScale = 1.0f, impulseScale = 0.0f;
+    if (useBias) {
+      V2 separation = ((bB.dp - bA.dp) + (rB - rA)) + j.deltaCenter;
+      bias = j.constraintSoftness.biasRate * separation;
+      massScale = j.constraintSoftness.massScale; impulseScale = j.constraintSoftness.impulseScale;
+    }
+    float Kxx = mA + mB + rA.y * rA.y * iA + rB.y * rB.y * iB;
+    float Kxy = -rA.y * rA.x * iA - rB.y * rB.x * iB;
+    float Kyy = mA + mB + rA.x * rA.x * iA + rB.x * rB.x * iB;
+    V2 rhs = Cdot + bias;
+    float det = Kxx * Kyy - Kxy * Kxy;              // Mat22.Solve, include/MathFunctions.cs:211-215 (cx=(Kxx,Kxy), cy=(Kxy,Kyy))
+    if (det != 0.0f) det = 1.0f / det;
+    V2 b = mk(det * (Kyy * rhs.x - Kxy * rhs.y), det * (Kxx * rhs.y - Kxy * rhs.x));
+    V2 impulse = (-massScale * b) - (impulseScale * j.linearImpulse);
+    j.linearImpulse = j.linearImpulse + impulse;
+    vA = mulSub(vA, mA, impulse); wA -= iA * cross(rA, impulse);
+    vB = mulAdd(vB, mB, impulse); wB += iB * cross(rB, impulse);
+  }
+  bA.v = vA; bA.w = wA; bB.v = vB; bB.w = wB;
+  scatterBody(d, j.indexA, bA); scatterBody(d, j.indexB, bB);
+  if (useBias && (j.forceThreshold < FLT_MAX || j.torqueThreshold < FLT_MAX) && !d.jointEventFlag[j.jointId]) {   // src/Solver.cs:186-196
+    float force = length(j.linearImpulse) * sp.inv_h, torque = fabsf(j.motorImpulse + j.lowerImpulse - j.upperImpulse) * sp.inv_h;
+    if (force >= j.forceThreshold || torque >= j.torqueThreshold) d.jointEventFlag[j.jointId] = 1;
+  }
+}
+
+// IntegrateVelocitiesTask src/Solver.cs:121-160
+__device__ __forceinline__ void integrateVelocity(const WorldDev& d, const StepParams& sp, int i) {
+  float4 s = d.st0[i], m = d.simMass[i], f = d.simForce[i];
+  V2 v = mk(s.x, s.y); float w = s.z; uint32_t flags = fbits(s.w);
+  float h = sp.h;
+  float maxAngularSpeed = kMaxRotation * sp.inv_dt;
+  float maxLinSq = sp.maxLinearSpeed * sp.maxLinearSpeed, maxAngSq = maxAngularSpeed * maxAngularSpeed;
+  float linearDamping = 1.0f / (1.0f + h * m.z), angularDamping = 1.0f / (1.0f + h * m.w);
+  float gravityScale = m.x > 0.0f ? f.w : 0.0f;
+  V2 delta = ((h * m.x) * mk(f.x, f.y)) + ((h * gravityScale) * sp.gravity);
+  float angularDelta = h * m.y * f.z;
+  v = mulAdd(delta, linearDamping, v);
+  w = angularDelta + angularDamping * w;
+  uint32_t simFlags = 0;
+  if (dot(v, v) > maxLinSq) { float ratio = sp.maxLinearSpeed / length(v); v = ratio * v; simFlags |= kIsSpeedCapped; }
+  if (w * w > maxAngSq && !(d.simFlags[i] & kAllowFastRotation)) { float ratio = maxAngularSpeed / fabsf(w); w *= ratio; simFlags |= kIsSpeedCapped; }
+  if (simFlags) d.simFlags[i] |= simFlags;
+  if (flags & kLockLinearX) v.x = 0.0f;
+  if (flags & kLockLinearY) v.y = 0.0f;
+  if (flags & kLockAngularZ) w = 0.0f;
+  d.st0[i] = make_float4(v.x, v.y, w, s.w);
+}
+// IntegratePositionsTask src/Solver.cs:199-212
+__device__ __forceinline__ void integratePosition(const WorldDev& d, const StepParams& sp, int i) {
+  float4 s = d.st0[i], p = d.st1[i];
+  uint32_t flags = fbits(s.w);
+  bool locked = false;
+  if (flags & kLockLinearX) { s.x = 0.0f; locked = true; }
+  if (flags & kLockLinearY) { s.y = 0.0f; locked = true; }
+  if (flags & kLockAngularZ) { s.z = 0.0f; locked = true; }
+  if (locked) d.st0[i] = s;
+  V2 dp = mulAdd(mk(p.x, p.y), sp.h, mk(s.x, s.y));
+  Rot dq = integrateRot(mkRot(p.z, p.w), sp.h * s.z);
+  d.st1[i] = make_float4(dp.x, dp.y, dq.c, dq.s);
+}
+
+__global__ void __launch_bounds__(kThreads) k_prepare(WorldDev d, StepParams sp) {
+  const Scalars& s = *d.sc;
+  for (int c = 0; c < kOverflowIndex; c++) {
+    int begin = s.colorStart[c], end = begin + s.colorCount[c];
+    for (int t = begin + gtid(); t < end; t += gsize()) prepareContact(d, sp, t);
+  }
+  int nj = d.jointColorStart[kGraphColorCount];
+  for (int k = gtid(); k < nj; k += gsize()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
+}
+
+// SolverTask substep loop (src/Solver.cs:599-727) as one persistent cooperative kernel: a grid-wide barrier replaces the
+// reference's per-stage spin barrier; empty colors cost nothing.
+__global__ void __launch_bounds__(512) k_solver(WorldDev d, StepParams sp) {
+  cg::grid_group grid = cg::this_grid();
+  const Scalars& s = *d.sc;
+  __shared__ int sBegin[kGraphColorCount], sEnd[kGraphColorCount], sJBegin[kGraphColorCount], sJEnd[kGraphColorCount], sActive[kGraphColorCount], sActiveCount;
+  if (threadIdx.x == 0) {
+    int n = 0;
+    for (int c = 0; c < kOverflowIndex; c++) {
+      int cc = s.colorCount[c], jc = d.jointColorStart[c + 1] - d.jointColorStart[c];
+      if (cc + jc > 0) { sActive[n] = c; sBegin[n] = s.colorStart[c]; sEnd[n] = s.colorStart[c] + cc; sJBegin[n] = d.jointColorStart[c]; sJEnd[n] = d.jointColorStart[c + 1]; n++; }
+    }
+    sActiveCount = n;
+  }
+  __syncthreads();
+  const int activeCount = sActiveCount;
+  const int tid = gtid(), stride = gsize();
+  const int awake = d.awakeCount;
+  for (int sub = 0; sub < sp.subStepCount; sub++) {
+    for (int i = tid; i < awake; i += stride) integrateVelocity(d, sp, i);
+    grid.sync();
+    for (int a = 0; a < activeCount; a++) {
+      for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) warmStartJoint(d, d.joints[d.jointSorted[k]]);
+      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) warmStartContact(d, t);
+      grid.sync();
+    }
+    for (int a = 0; a < activeCount; a++) {
+      for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], true);
+      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<true>(d, sp, t);
+      grid.sync();
+    }
+    for (int i = tid; i < awake; i += stride) integratePosition(d, sp, i);
+    grid.sync();
+    for (int a = 0; a < activeCount; a++) {
+      for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], false);
+      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<false>(d, sp, t);
+      grid.sync();
+    }
+  }
+  // restitution: skipped entirely (like every AllZeroW group) when no constraint has restitution (flag set by k_prepare)
+  if (s.anyRestitution) {
+    for (int a = 0; a < activeCount; a++) {
+      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) restitutionContact(d, sp, t, sBegin[a], sEnd[a]);
+      grid.sync();
+    }
+  }
+  for (int a = 0; a < activeCount; a++)
+    for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) storeImpulses(d, t);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Phase 3: FinalizeBodiesTask (src/Solver.cs:402-503) + refit (:1191-1237, src/DynamicTree.cs:482-505)
+// ------------------------------------------------------------------------------------------------------------
+__device__ inline int countToiCandidates(const WorldDev& d, Box query, int fastShape, int fastBody) {   // ContinuousQueryCallback :224-253 (static tree)
+  const TreeDev& t = d.trees[kStaticBody];
+  int root = t.meta[0];
+  if (t.meta[1] == 0 || root == -1) return 0;
+  int stack[kQueryStack]; int sp = 0, found = 0;
+  stack[sp++] = root;
+  while (sp > 0) {
+    int id = stack[--sp];
+    if (!boxOverlaps(toBox(t.aabb[id]), query) || t.cat[id] == 0) continue;
+    if ((t.hf[id] >> 16) & NODE_LEAF) {
+      int other = t.user[id];
+      if (other == fastShape) break;
+      const ShapeDev& so = d.shapes[other];
+      if (so.bodyId == fastBody) continue;
+      if (!shouldShapesCollide(d.shapes[fastShape], so)) continue;
+      if (!shouldBodiesCollide(d, fastBody, so.bodyId)) continue;
+      found++;
+    } else if (sp + 2 <= kQueryStack) { int2 c = t.child[id]; stack[sp++] = c.x; stack[sp++] = c.y; }
+  }
+  return found;
+}
+
+__global__ void __launch_bounds__(kThreads) k_finalize(WorldDev d, StepParams sp) {
+  int n = d.awakeCount;
+  for (int i = gtid(); i < n; i += gsize()) {
+    float4 s = d.st0[i], p = d.st1[i], pose = d.simPose[i], loc = d.simLocal[i];
+    uint32_t flags = fbits(s.w);
+    if (flags & kLockLinearX) s.x = 0.0f;
+    if (flags & kLockLinearY) s.y = 0.0f;
+    if (flags & kLockAngularZ) s.z = 0.0f;
+    V2 v = mk(s.x, s.y); float w = s.z;
+    V2 center = mk(pose.x, pose.y) + mk(p.x, p.y);
+    Rot q = normalizeRot(mulRot(mkRot(p.z, p.w), mkRot(pose.z, pose.w)));
+    float maxVelocity = length(v) + fabsf(w) * loc.w;
+    d.st0[i] = s;
+    d.st1[i] = make_float4(0.0f, 0.0f, 1.0f, 0.0f);
+    V2 localCenter = mk(loc.x, loc.y);
+    Xf xf = mkXf(center - rotate(q, localCenter), q);
+    int bodyId = d.simBodyId[i];
+    d.simPose[i] = make_float4(center.x, center.y, q.c, q.s);
+    d.bodyXf[bodyId] = make_float4(xf.p.x, xf.p.y, q.c, q.s);
+    d.bodyCenter[bodyId] = make_float2(center.x, center.y);
+    float4 f = d.simForce[i];
+    d.simForce[i] = make_float4(0.0f, 0.0f, 0.0f, f.w);
+    uint32_t simFlags = d.simFlags[i];
+    d.bodyFlags[bodyId] = (d.bodyFlags[bodyId] & ~(kIsFast | kIsSpeedCapped | kHadTimeOfImpact)) | (simFlags & (kIsSpeedCapped | kHadTimeOfImpact));
+    simFlags &= ~(kIsFast | kIsSpeedCapped | kHadTimeOfImpact);
+    bool isFast = false;
+    // sleeping is disabled in this build (world creation rejects enableSleep), so the first branch of :444 always runs
+    if (d.bodyType[bodyId] == kDynamicBody && sp.enableContinuous && maxVelocity * sp.dt > 0.5f * loc.z) { simFlags |= kIsFast; isFast = true; }
+    else d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
+    int enlarged = 0;
+    if (isFast) {
+      // SolveContinuous :315-401 for a non-bullet body, no-hit result; a would-be TOI candidate is reported, never ignored
+      int candidates = 0;
+      for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+        Box box1 = toBox(d.shapeAABB[sid]);
+        Box box2 = geomAABB(d.shapes[sid].geom, xf);
+        d.shapeAABB[sid] = fromBox(box2);               // raw AABB, no speculative margin (:337-339)
+        candidates += countToiCandidates(d, boxUnion(box1, box2), sid, bodyId);
+      }
+      if (candidates) { atomicAdd(&d.sc->toiCandidates, candidates); atomicOr(&d.sc->errorFlags, (int)ERR_TOI_CANDIDATE); }
+      d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
+      for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+        Box aabb = toBox(d.shapeAABB[sid]);
+        if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
+          d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
+          d.shapes[sid].flags |= SF_ENLARGED;
+          simFlags |= kEnlargeBounds;
+          enlarged++;
+        }
+      }
+    } else {
+      for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+        Box aabb = boxGrow(geomAABB(d.shapes[sid].geom, xf), kSpeculativeDistance);
+        d.shapeAABB[sid] = fromBox(aabb);
+        if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
+          d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
+          d.shapes[sid].flags |= SF_ENLARGED;
+          enlarged++;
+        }
+      }
+    }
+    d.simFlags[i] = simFlags;
+    d.bodyEnlargedCount[i] = enlarged;
+  }
+}
+
+__device__ __forceinline__ void atomicMinF(float* addr, float v) {
+  v = v + 0.0f;
+  if (v >= 0.0f) atomicMin((int*)addr, __float_as_int(v)); else atomicMax((unsigned*)addr, __float_as_uint(v));
+}
+__device__ __forceinline__ void atomicMaxF(float* addr, float v) {
+  v = v + 0.0f;
+  if (v >= 0.0f) atomicMax((int*)addr, __float_as_int(v)); else atomicMin((unsigned*)addr, __float_as_uint(v));
+}
+// Enlarged bodies in ascending sim index, shapes in body list order: BroadPhase.EnlargeProxy + BufferMove (:1202-1233).
+// EnlargeProxy's result (ancestor boxes = union, every ancestor flagged Enlarged) does not depend on the order of the
+// calls, so it is applied with float atomics; the move array order is produced by the prefix sum.
+__global__ void __launch_bounds__(kThreads) k_refit(WorldDev d) {
+  int n = d.awakeCount;
+  for (int i = gtid(); i < n; i += gsize()) {
+    int offset = d.bodyEnlargedCount[i] + d.scanBlockSums[i >> 10];
+    int next = (i + 1 < n) ? d.bodyEnlargedCount[i + 1] + d.scanBlockSums[(i + 1) >> 10] : d.sc->moveCount;
+    if (next == offset) continue;
+    int bodyId = d.simBodyId[i];
+    for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+      ShapeDev& sh = d.shapes[sid];
+      if (!(sh.flags & SF_ENLARGED)) continue;
+      sh.flags &= ~SF_ENLARGED;
+      int key = sh.proxyKey;
+      const TreeDev& t = d.trees[key & 3];
+      int id = key >> 2;
+      float4 fat = d.shapeFat[sid];
+      t.aabb[id] = fat;
+      if (offset < d.moveCapacity) d.moveArray[offset] = key;
+      offset++;
+      t.moved[id] = 1;
+      for (int p = t.parent[id]; p != -1; p = t.parent[p]) {
+        float* a = (float*)&t.aabb[p];
+        atomicMinF(a + 0, fat.x); atomicMinF(a + 1, fat.y); atomicMaxF(a + 2, fat.z); atomicMaxF(a + 3, fat.w);
+        atomicOr(&t.hf[p], (uint32_t)NODE_ENLARGED << 16);
+      }
+    }
+  }
+}
+
+// contact hit events (src/Solver.cs:1151-1190); order within a step is not defined by this build (appended atomically)
+__global__ void __launch_bounds__(kThreads) k_hit_events(WorldDev d, StepParams sp) {
+  int n = d.sc->contactNext;
+  for (int i = gtid(); i < n; i += gsize()) {
+    uint32_t flags = d.cFlags[i];
+    if ((flags & (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) != (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) continue;
+    float4 mn = d.mN[i];
+    int pointCount = (int)fbits(mn.w);
+    float best = sp.hitEventThreshold; V2 point = mk(0, 0); bool hit = false;
+    if (pointCount > 0) { float4 b = d.mB0[i], c = d.mC0[i]; float a = -c.z; if (a > best && b.w > 0.0f) { best = a; point = mk(c.x, c.y); hit = true; } }
+    if (pointCount > 1) { float4 b = d.mB1[i], c = d.mC1[i]; float a = -c.z; if (a > best && b.w > 0.0f) { best = a; point = mk(c.x, c.y); hit = true; } }
+    if (hit) {
+      int k = atomicAdd(&d.sc->hitCount, 1);
+      if (k < d.eventCapacity) { int2 sh = d.cShape[i]; B2CContactHitEvent ev = {sh.x, sh.y, {point.x, point.y}, {mn.x, mn.y}, best}; d.hitEvents[k] = ev; }
+    }
+  }
+}
+__global__ void k_step_finish(WorldDev d, int newEndIndex) {
+  Scalars& s = *d.sc;
+  s.graphDirty = 0;
+  s.stepCount++;
+  if (s.moveCount > d.moveCapacity) { s.moveCount = d.moveCapacity; s.errorFlags |= (int)ERR_PAIR_CAPACITY; }
+  s.endCount[newEndIndex] = 0;                     // api/World.cs:106-108: swap, then clear the buffer the next step appends to
+}
+__global__ void k_zero_step(WorldDev d, int newEndIndex) { Scalars& s = *d.sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; }
+
+// ------------------------------------------------------------------------------------------------------------
+// host driver
+// ------------------------------------------------------------------------------------------------------------
+static int gridFor(int n, int threads, int maxBlocks) {
+  int b = (n + threads - 1) / threads;
+  if (b < 1) b = 1;
+  return b > maxBlocks ? maxBlocks : b;
+}
+
+int World::step(float timeStep, int subStepCount) {
+  if (enableSleep) return fail(B2C_E_UNSUPPORTED, "enableSleep=true (islands/sleep, src/Island.cs) is not supported in this build; create the world with enableSleep=0");
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }
+  CK(cudaSetDevice(device_));
+  WorldDev& d = d_;
+  eventsFetched_ = false;
+  if (timeStep == 0.0f) {                          // api/World.cs:44-51
+    lastEndIndex_ = endIndex_;
+    endIndex_ = 1 - endIndex_;
+    k_zero_step<<<1, 1, 0, stream_>>>(d, endIndex_);
+    CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
+    return B2C_OK;
+  }
+  StepParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.dt = timeStep; sp.subStepCount = subStepCount > 1 ? subStepCount : 1;
+  if (timeStep > 0.0f) { sp.inv_dt = 1.0f / timeStep; sp.h = timeStep / sp.subStepCount; sp.inv_h = sp.subStepCount * sp.inv_dt; }
+  float hz = netMin(contactHertz, 0.125f * sp.inv_h);           // api/World.cs:63-83
+  sp.contactSoftness = makeSoft(hz, contactDampingRatio, sp.h);
+  sp.staticSoftness = makeSoft(2.0f * hz, contactDampingRatio, sp.h);
+  sp.restitutionThreshold = restitutionThreshold; sp.maxLinearSpeed = maxLinearSpeed; sp.contactSpeed = contactSpeed; sp.contactHertz = contactHertz;
+  sp.contactDampingRatio = contactDampingRatio; sp.hitEventThreshold = hitEventThreshold; sp.gravity = gravity;
+  sp.enableWarmStarting = enableWarmStarting; sp.enableContactSoftening = enableContactSoftening; sp.enableContinuous = enableContinuous;
+  sp.enableSpeculative = enableSpeculative; sp.enableSleep = 0; sp.endIndex = endIndex_;
+
+  const int maxBlocks = 148 * 8;
+  const int gMove = gridFor(d.moveCapacity, kThreads, maxBlocks), gContact = gridFor(d.contactCapacity, kThreads, maxBlocks);
+  const int gBody = gridFor(d.awakeCount, kThreads, maxBlocks), gScan = 148 * 2;
+  Scalars* sc = d.sc;
+  cudaEventRecord(ev_[0], stream_);
+  // --- UpdateBroadPhasePairs ---
+  CK(cudaMemsetAsync(d.pairTable, 0xff, sizeof(unsigned long long) * (size_t)d.pairTableSize, stream_));
+  k_pair_insert<<<gContact, kThreads, 0, stream_>>>(d);
+  k_find_pairs<false><<<gMove, kThreads, 0, stream_>>>(d);
+  k_scan_chunks<int><<<gScan, kScanChunk, 0, stream_>>>(d.moveHitCount, d.scanBlockSums, &sc->moveCount);
+  k_scan_sums<int><<<1, kScanChunk, 0, stream_>>>(d.scanBlockSums, &sc->moveCount, &sc->newPairCount);
+  k_find_pairs<true><<<gMove, kThreads, 0, stream_>>>(d);
+  k_create_contacts<<<gContact, kThreads, 0, stream_>>>(d);
+  k_clear_moved<<<gMove, kThreads, 0, stream_>>>(d);
+  k_pairs_finish<<<1, 1, 0, stream_>>>(d);
+  cudaEventRecord(ev_[1], stream_);
+  // --- Collide ---
+  k_tree_rebuild<<<2, 32, 0, stream_>>>(d);
+  k_collide<<<gContact, kThreads, 0, stream_>>>(d, sp);
+  k_scan_chunks<int4><<<gScan, kScanChunk, 0, stream_>>>(d.flagScan, d.scanBlockSums4, &sc->contactNext);
+  k_scan_sums<int4><<<1, kScanChunk, 0, stream_>>>(d.scanBlockSums4, &sc->contactNext, d.flagScan + d.contactCapacity);
+  k_contact_events<<<gContact, kThreads, 0, stream_>>>(d, sp);
+  k_events_finish<<<1, 1, 0, stream_>>>(d, sp, d.flagScan + d.contactCapacity);
+  k_color_ops<<<1, 1024, 0, stream_>>>(d);
+  cudaEventRecord(ev_[2], stream_);
+  // --- Solve ---
+  int gChunks = gridFor(d.contactCapacity, kSortChunk, maxBlocks);
+  k_color_hist<<<gChunks, kSortChunk, 0, stream_>>>(d);
+  k_color_offsets<<<1, 32, 0, stream_>>>(d);
+  k_color_scatter<<<gChunks, kSortChunk, 0, stream_>>>(d);
+  k_prepare<<<gContact, kThreads, 0, stream_>>>(d, sp);
+  if (coopBlocks_ == 0) {
+    int perSm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_solver, 512, 0));
+    cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device_));
+    if (perSm < 1) return fail(B2C_E_CUDA, "k_solver cannot be made resident for a cooperative launch");
+    coopBlocks_ = prop.multiProcessorCount;       // one 512-thread CTA per SM: the barrier cost grows with CTA count
+  }
+  {
+    void* args[] = {(void*)&d, (void*)&sp};
+    CK(cudaLaunchCooperativeKernel((void*)k_solver, dim3(coopBlocks_), dim3(512), args, 0, stream_));
+  }
+  cudaEventRecord(ev_[3], stream_);
+  // --- Finalize + refit ---
+  k_finalize<<<gBody, kThreads, 0, stream_>>>(d, sp);
+  k_scan_chunks<int><<<gScan, kScanChunk, 0, stream_>>>(d.bodyEnlargedCount, d.scanBlockSums, &sc->awakeCount);
+  k_scan_sums<int><<<1, kScanChunk, 0, stream_>>>(d.scanBlockSums, &sc->awakeCount, &sc->moveCount);
+  k_refit<<<gBody, kThreads, 0, stream_>>>(d);
+  k_hit_events<<<gContact, kThreads, 0, stream_>>>(d, sp);
+  lastEndIndex_ = endIndex_;
+  endIndex_ = 1 - endIndex_;
+  k_step_finish<<<1, 1, 0, stream_>>>(d, endIndex_);
+  cudaEventRecord(ev_[4], stream_);
+  CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
+  CK(cudaGetLastError());
+  profileValid_ = true;
+  stepCount_++;
+  return B2C_OK;
+}
+
+}  // namespace b2c

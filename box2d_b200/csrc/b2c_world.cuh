@@ -1,0 +1,160 @@
+// libb2cuda — device-resident world layout (SoA, float4 rows) and the host-side world that owns it.
+// The layout is ours (B200-first), the semantics are the reference's: each array cites the C# type it replaces.
+#pragma once
+#include <cuda_runtime.h>
+#include <vector>
+#include <string>
+#include "b2c_math.cuh"
+#include "../../include/b2cuda.h"
+
+namespace b2c {
+
+// ---- contact slot flags (src/Contact.cs:6-16,66-85 merged into one word; slot index == contactId) ----
+enum : uint32_t {
+  CF_ALIVE = 1u, CF_TOUCHING = 2u, CF_ENABLE_CONTACT_EVENTS = 4u, CF_ENABLE_HIT = 8u, CF_ENABLE_PRESOLVE = 16u,
+  CF_SHAPE_HIT = 32u,            // either shape has enableHitEvents (static property of the pair)
+  CF_DISJOINT = 0x100u, CF_STARTED = 0x200u, CF_STOPPED = 0x400u, CF_STATE_MASK = 0x700u
+};
+enum : uint32_t { ERR_CONTACT_CAPACITY = 1u, ERR_STACK_OVERFLOW = 2u, ERR_OVERFLOW_COLOR = 4u, ERR_PAIR_CAPACITY = 8u,
+                  ERR_TOI_CANDIDATE = 16u, ERR_HASH_FULL = 32u, ERR_TREE = 64u };
+enum : uint16_t { NODE_ALLOCATED = 1, NODE_ENLARGED = 2, NODE_LEAF = 4 };   // src/DynamicTree.cs TreeNodeFlags
+
+// ---- dynamic AABB tree replica (src/DynamicTree.cs:11-32 TreeNode, SoA) ----
+struct TreeDev {
+  float4* aabb;        // lo.x lo.y hi.x hi.y
+  int2* child;         // child1, child2 (-1,-1 for leaves)
+  int* parent;         // parent, or next-free for nodes on the free list
+  uint32_t* hf;        // height | flags << 16
+  uint64_t* cat;       // categoryBits
+  int* user;           // leaf: shapeId
+  uint8_t* moved;      // BroadPhase.moveSet membership, indexed by proxy id
+  int* meta;           // [0] root [1] nodeCount [2] freeList [3] proxyCount
+  int* leafIdx;        // rebuild scratch (leafIndices)
+  float2* leafCtr;     // rebuild scratch (leafCenters)
+  int* stack;          // rebuild scratch: DFS stack + RebuildItem stack (5 ints each)
+  int capacity;
+  int stackCapacity;
+};
+
+struct ShapeDev {      // src/Shape.cs:25-52 (hot subset) — one AoS row per shapeId, 16-byte aligned
+  Geom geom;                         // 152 B
+  float4 material;                   // friction, restitution, rollingResistance, tangentSpeed
+  uint64_t categoryBits, maskBits;
+  int groupIndex, bodyId, nextShapeId, proxyKey;
+  uint32_t flags;                    // SF_*
+  int sensorIndex; int pad0, pad1;
+};
+enum : uint32_t { SF_CONTACT_EVENTS = 1u, SF_HIT_EVENTS = 2u, SF_PRESOLVE = 4u, SF_CUSTOM_FILTER = 8u, SF_ENLARGED = 16u };
+
+struct JointDev {      // src/Joint.cs:74-133 + src/joints/RevoluteJoint.cs:6-31
+  int jointId, bodyIdA, bodyIdB, colorIndex;
+  Xf localFrameA, localFrameB;
+  float constraintHertz, constraintDampingRatio, forceThreshold, torqueThreshold;
+  float hertz, dampingRatio, targetAngle, maxMotorTorque, motorSpeed, lowerAngle, upperAngle;
+  int enableSpring, enableMotor, enableLimit;
+  // prepared each step
+  int indexA, indexB;
+  float invMassA, invMassB, invIA, invIB;
+  Xf frameA, frameB; V2 deltaCenter; float axialMass;
+  Softness constraintSoftness, springSoftness;
+  // accumulated impulses
+  V2 linearImpulse; float springImpulse, motorImpulse, lowerImpulse, upperImpulse;
+};
+
+struct Scalars {       // device scalars, mirrored to pinned host memory at the end of each step
+  int moveCount, newPairCount, contactNext, contactFreeCount;
+  int beginCount, endCount[2], hitCount;
+  int colorCount[kGraphColorCount], colorStart[kGraphColorCount];
+  int constraintTotal, graphDirty, opCount, enlargedShapeCount;
+  int errorFlags, toiCandidates, jointEventCount, stepCount;
+  int touchingCount, liveContactCount, rebuildLeafCount[3], colorRounds;
+  int awakeCount, anyRestitution;
+};
+
+struct StepParams {    // src/Solver.cs:57-112 StepContext (scalars only)
+  float dt, inv_dt, h, inv_h;
+  int subStepCount;
+  Softness contactSoftness, staticSoftness;
+  float restitutionThreshold, maxLinearSpeed, contactSpeed, contactHertz, contactDampingRatio, hitEventThreshold;
+  V2 gravity;
+  int enableWarmStarting, enableContactSoftening, enableContinuous, enableSpeculative, enableSleep;
+  int endIndex;        // which contactEndEvents buffer this step appends to
+};
+
+struct WorldDev {
+  // --- awake body set, index = awake sim index (src/Body.cs:119-173 BodyState + BodySim) ---
+  float4* st0;         // v.x v.y w flags
+  float4* st1;         // dp.x dp.y dq.c dq.s
+  float4* simMass;     // invMass invInertia linearDamping angularDamping
+  float4* simForce;    // force.x force.y torque gravityScale
+  float4* simPose;     // center.x center.y q.c q.s
+  float4* simLocal;    // localCenter.x localCenter.y minExtent maxExtent
+  float4* simPose0;    // center0.x center0.y q0.c q0.s
+  uint32_t* simFlags;
+  int* simBodyId;
+  int awakeCount;
+  // --- per bodyId (all sets): what narrowphase / pair filtering / joints need ---
+  float4* bodyXf;      // p.x p.y q.c q.s
+  float4* bodyMass;    // invMass invInertia localCenter.x localCenter.y
+  float2* bodyCenter;  // center (static bodies keep theirs; awake bodies refreshed in finalize)
+  int* bodySim;        // awake sim index or -1
+  int* bodyType;
+  int* bodyHeadShape;
+  int* bodyHeadJoint;  // joint key (jointId<<1|edge) or -1
+  int* bodyJointCount;
+  uint32_t* bodyColorMask;   // bit c <=> colors[c].bodySet.GetBit(bodyId) (src/ConstraintGraph.cs:10-24 transposed)
+  int* bodyMinOp;      // coloring scratch
+  float* bodySleepThreshold;
+  uint32_t* bodyFlags;
+  int bodyCapacity;
+  // --- shapes ---
+  ShapeDev* shapes;
+  float4* shapeAABB;   // aabb lo/hi
+  float4* shapeFat;    // fatAABB lo/hi
+  int shapeCapacity;
+  // --- joints ---
+  JointDev* joints;
+  int4* jointEdges;    // per jointId: edge0.bodyId, edge0.nextKey, edge1.bodyId, edge1.nextKey
+  int* jointCollide;   // collideConnected
+  int* jointSorted;    // joint ids grouped by color
+  int jointColorStart[kGraphColorCount + 1];
+  uint8_t* jointEventFlag;
+  int jointCapacity;
+  // --- broadphase ---
+  TreeDev trees[3];
+  int* moveArray;      // proxy keys, BroadPhase.moveArray order
+  int* moveHitCount;   // per move entry: accepted hits, then exclusive offsets
+  int2* movePairs;     // (shapeIdA, shapeIdB) in contact-creation order
+  int moveCapacity, pairCapacity;
+  unsigned long long* pairTable;   // open-addressing set of shape pair keys (World.pairSet)
+  int pairTableSize;   // power of two
+  // --- contacts, slot == contactId (src/Contact.cs Contact + ContactSim) ---
+  int2* cShape; int2* cBody; uint32_t* cFlags; int* cColor; uint32_t* cGen;
+  float4* cMat; float4* cMass; int2* cSim;
+  float4* mN;          // normal.x normal.y rollingImpulse pointCount(bits)
+  float4* mA0; float4* mA1;   // anchorA.xy anchorB.xy
+  float4* mB0; float4* mB1;   // separation normalImpulse tangentImpulse totalNormalImpulse
+  float4* mC0; float4* mC1;   // point.xy normalVelocity (id | persisted<<16)(bits)
+  int* contactFree;    // IDPool.freeArray
+  int contactCapacity;
+  // --- per-step ordered compaction scratch ---
+  int4* flagScan;      // per contact slot: (begin, end, destroy, op) flags -> exclusive ranks
+  int* opList;         // contact ids with a graph op (add/remove), ascending
+  uint8_t* opDone;
+  // --- solver constraint planes, index = constraint (grouped by color) ---
+  float4* sA; float4* sB; float4* sC; float4* sD; float4* sE; float4* sF; float4* sG; float4* sH; float4* sI; float4* sJ;
+  int* sContact;       // contact slot of constraint t
+  int* cConstraint;    // constraint index of contact slot (or -1)
+  int constraintCapacity;
+  int* blockHist;      // color sort scratch [numChunks][24]
+  // --- events ---
+  B2CContactTouchEvent* beginEvents; B2CContactTouchEvent* endEvents[2]; B2CContactHitEvent* hitEvents;
+  int eventCapacity;
+  // --- finalize / refit scratch ---
+  int* bodyEnlargedCount;   // per awake sim: enlarged shapes, then exclusive offsets
+  Scalars* sc;
+  // generic scan scratch
+  int* scanBlockSums; int4* scanBlockSums4;
+};
+
+}  // namespace b2c

@@ -1,0 +1,92 @@
+"""Parity harness: drives the CUDA library and the CPU oracle through the same Box2D.API mirror and compares the
+reference-visible state after every step. TEST INFRASTRUCTURE (imports the oracle)."""
+import numpy as np
+from box2d_b200 import api, scenes
+from oracle_backend import OracleBackend
+
+
+def _flat(a):
+    """structured array -> dict of flat leaf arrays"""
+    out = {}
+
+    def rec(prefix, arr):
+        if arr.dtype.names:
+            for n in arr.dtype.names:
+                rec(prefix + "." + n if prefix else n, arr[n])
+        else:
+            out[prefix] = np.asarray(arr)
+    rec("", a)
+    return out
+
+
+def compare_struct(name, a, b, exact_fields=None, skip=(), report=None):
+    """Bit-exact comparison of two structured arrays; returns max relative error over float leaves."""
+    assert len(a) == len(b), f"{name}: length {len(a)} vs {len(b)}"
+    fa, fb = _flat(a), _flat(b)
+    worst = 0.0
+    for k in fa:
+        if k in skip:
+            continue
+        x, y = fa[k], fb[k]
+        if x.dtype.kind == "f":
+            same = (x.view(np.uint32) == y.view(np.uint32)) | ((x == 0) & (y == 0))
+            if not same.all():
+                denom = np.maximum(np.abs(y), 1e-6)
+                err = float(np.max(np.abs(x.astype(np.float64) - y) / denom))
+                worst = max(worst, err)
+                if report is not None:
+                    idx = np.argwhere(~same)[:3].tolist()
+                    report.append(f"{name}.{k}: {int((~same).sum())} mismatches, max rel {err:.3e}, first at {idx}")
+        else:
+            if not np.array_equal(x, y):
+                bad = np.argwhere(x != y)[:3].tolist()
+                raise AssertionError(f"{name}.{k}: integer mismatch at {bad}: {x[tuple(bad[0])]} vs {y[tuple(bad[0])]}")
+    return worst
+
+
+def snapshot(w):
+    ev = w.GetContactEvents()
+    return dict(bodies=w.ReadBodies(), contacts=w.ReadContacts(), shapes=w.ReadShapes(), joints=w.ReadJoints(),
+                begin=ev[0], end=ev[1], hit=ev[2], counters=w.GetCounters())
+
+
+def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0, verbose=False, mutate=None):
+    """Builds the same scene on both backends, steps both, compares after every step. Returns summary dict."""
+    cuda = api.World(api.CudaBackend(), world_def if world_def is not None else scenes.world_def())
+    orc = api.World(OracleBackend(), world_def if world_def is not None else scenes.world_def())
+    try:
+        build(cuda)
+        build(orc)
+        worst = 0.0
+        notes = []
+        for step in range(steps):
+            if mutate is not None:
+                mutate(cuda, step)
+                mutate(orc, step)
+            cuda.Step(dt, substeps)
+            orc.Step(dt, substeps)
+            a, b = snapshot(cuda), snapshot(orc)
+            rep = []
+            # exact: pair set / ids / colors / manifold ids / events
+            for key in ("begin", "end"):
+                compare_struct(f"step{step}.{key}", a[key], b[key], report=rep)
+            ca, cb = a["counters"], b["counters"]
+            for f in ("contactCount", "touchingContactCount", "contactIdCapacity", "activeColorCount", "moveCount", "newPairCount"):
+                assert getattr(ca, f) == getattr(cb, f), f"step{step} counters.{f}: {getattr(ca, f)} vs {getattr(cb, f)}"
+            assert list(ca.colorCounts) == list(cb.colorCounts), f"step{step} colorCounts {list(ca.colorCounts)} vs {list(cb.colorCounts)}"
+            e = compare_struct(f"step{step}.contacts", a["contacts"], b["contacts"], report=rep)
+            e = max(e, compare_struct(f"step{step}.bodies", a["bodies"], b["bodies"], report=rep))
+            e = max(e, compare_struct(f"step{step}.shapes", a["shapes"], b["shapes"], skip=("enlarged",), report=rep))
+            e = max(e, compare_struct(f"step{step}.joints", a["joints"], b["joints"], report=rep))
+            if rep and verbose:
+                print("\n".join(rep[:12]))
+            if e > tol:
+                raise AssertionError(f"step {step}: max rel err {e:.3e} > {tol}\n" + "\n".join(rep[:12]))
+            worst = max(worst, e)
+            notes.extend(rep)
+        c = cuda.GetCounters()
+        return dict(max_rel_err=worst, steps=steps, contacts=c.contactCount, touching=c.touchingContactCount, bodies=c.bodyCount,
+                    colors=c.activeColorCount, toi=c.toiCandidates)
+    finally:
+        cuda.Destroy()
+        orc.Destroy()
