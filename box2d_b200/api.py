@@ -201,6 +201,14 @@ class World:
         self._check(self.fns["world_get_profile"](self.handle, C.byref(p)))
         return p
 
+    def TimerStart(self):
+        self._check(self.fns["world_timer_start"](self.handle))
+
+    def TimerStop(self):
+        ms = C.c_float()
+        self._check(self.fns["world_timer_stop"](self.handle, C.byref(ms)))
+        return ms.value
+
     def GetContactEvents(self):
         """Returns (begin, end, hit) as numpy structured arrays (copies)."""
         b, e, h = C.POINTER(ContactTouchEvent)(), C.POINTER(ContactTouchEvent)(), C.POINTER(ContactHitEvent)()

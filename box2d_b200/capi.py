@@ -149,6 +149,8 @@ PRODUCT_ONLY = {
     "default_revolute_joint_def": ([C.POINTER(RevoluteJointDef)], C.c_int32),
     "world_create": ([C.POINTER(WorldDef), C.c_int32, C.POINTER(_W)], C.c_int32),
     "world_get_profile": ([_W, C.POINTER(Profile)], C.c_int32),
+    "world_timer_start": ([_W], C.c_int32),
+    "world_timer_stop": ([_W, C.POINTER(C.c_float)], C.c_int32),
 }
 
 

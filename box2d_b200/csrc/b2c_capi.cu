@@ -92,4 +92,7 @@ int32_t b2cuda_world_read_shapes(B2CWorld* h, B2CShapeRead* dst, int32_t cap, in
 int32_t b2cuda_world_get_counters(B2CWorld* h, B2CCounters* out) { CHECK_HANDLE(h); return done(h, h->w->getCounters(out)); }
 int32_t b2cuda_world_get_profile(B2CWorld* h, B2CProfile* out) { CHECK_HANDLE(h); return done(h, h->w->getProfile(out)); }
 
+int32_t b2cuda_world_timer_start(B2CWorld* h) { CHECK_HANDLE(h); return done(h, h->w->timerStart()); }
+int32_t b2cuda_world_timer_stop(B2CWorld* h, float* ms) { CHECK_HANDLE(h); if (!ms) return B2C_E_INVALID; return done(h, h->w->timerStop(ms)); }
+
 }  // extern "C"

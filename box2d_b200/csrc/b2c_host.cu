@@ -107,6 +107,7 @@ void World::freeDevice() {
   if (hJointEvents_) cudaFreeHost(hJointEvents_);
   hostScalars_ = nullptr; hBegin_ = hEnd_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
   for (auto& e : ev_) if (e) { cudaEventDestroy(e); e = nullptr; }
+  for (auto& e : timer_) if (e) { cudaEventDestroy(e); e = nullptr; }
   if (stream_) { cudaStreamDestroy(stream_); stream_ = nullptr; }
 }
 
@@ -317,6 +318,7 @@ int World::upload() {
   CK(cudaSetDevice(device_));
   CK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
   for (auto& e : ev_) CK(cudaEventCreate(&e));
+  for (auto& e : timer_) CK(cudaEventCreate(&e));
   CK(cudaHostAlloc((void**)&hostScalars_, sizeof(Scalars), cudaHostAllocDefault));
   memset(hostScalars_, 0, sizeof(Scalars));
   WorldDev& d = d_;
@@ -677,14 +679,39 @@ int World::getJointEvents(const int** ids, int* count) {
   return B2C_OK;
 }
 
-int World::getProfile(B2CProfile* out) {
+int World::getProfile(B2CProfile* out) {       // averages over the steps since the previous call (at most kProfRing)
   memset(out, 0, sizeof(*out));
-  if (!onDevice_ || !profileValid_) return B2C_OK;
+  if (!onDevice_ || profCount_ == 0) return B2C_OK;
   int rc = synchronize(); if (rc) return rc;
-  float pairs = 0, collide = 0, solve = 0, fin = 0, total = 0;
-  cudaEventElapsedTime(&pairs, ev_[0], ev_[1]); cudaEventElapsedTime(&collide, ev_[1], ev_[2]); cudaEventElapsedTime(&solve, ev_[2], ev_[3]);
-  cudaEventElapsedTime(&fin, ev_[3], ev_[4]); cudaEventElapsedTime(&total, ev_[0], ev_[4]);
-  out->step = total; out->pairs = pairs; out->collide = collide; out->solve = solve + fin; out->solveConstraints = solve; out->transforms = fin; out->refit = fin;
+  int n = profCount_ < kProfRing ? profCount_ : kProfRing;
+  double acc[6] = {0, 0, 0, 0, 0, 0};
+  for (int k = 0; k < n; k++) {
+    int slot = (profHead_ - 1 - k + 2 * kProfRing) % kProfRing;
+    cudaEvent_t* e = ev_ + slot * kProfEvents;
+    float ms;
+    for (int j = 0; j < 5; j++) { cudaEventElapsedTime(&ms, e[j], e[j + 1]); acc[j] += ms; }
+    cudaEventElapsedTime(&ms, e[0], e[5]); acc[5] += ms;
+  }
+  out->pairs = (float)(acc[0] / n); out->collide = (float)(acc[1] / n); out->prepareConstraints = (float)(acc[2] / n);
+  out->solveConstraints = (float)(acc[3] / n); out->transforms = (float)(acc[4] / n); out->refit = out->transforms;
+  out->solve = (float)((acc[2] + acc[3] + acc[4]) / n); out->step = (float)(acc[5] / n);
+  profCount_ = 0;
+  return B2C_OK;
+}
+
+int World::timerStart() {
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }
+  CK(cudaSetDevice(device_));
+  CK(cudaEventRecord(timer_[0], stream_));
+  return B2C_OK;
+}
+int World::timerStop(float* ms) {
+  *ms = 0;
+  if (!onDevice_) return fail(B2C_E_INVALID, "timer not started");
+  CK(cudaSetDevice(device_));
+  CK(cudaEventRecord(timer_[1], stream_));
+  CK(cudaEventSynchronize(timer_[1]));
+  CK(cudaEventElapsedTime(ms, timer_[0], timer_[1]));
   return B2C_OK;
 }
 

@@ -86,6 +86,8 @@ class World {
   int readShapes(B2CShapeRead* dst, int capacity, int* count);
   int getCounters(B2CCounters* out);
   int getProfile(B2CProfile* out);
+  int timerStart();
+  int timerStop(float* ms);
   int getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B2CContactTouchEvent** end, int* ne, const B2CContactHitEvent** hit, int* nh);
   int getJointEvents(const int** ids, int* count);
 
@@ -127,7 +129,10 @@ class World {
   B2CContactTouchEvent *hBegin_ = nullptr, *hEnd_ = nullptr; B2CContactHitEvent* hHit_ = nullptr; int* hJointEvents_ = nullptr;
   int hBeginN_ = 0, hEndN_ = 0, hHitN_ = 0, hJointN_ = 0;
   int lastEndIndex_ = 0;
-  cudaEvent_t ev_[8] = {};
+  static constexpr int kProfRing = 64, kProfEvents = 6;
+  cudaEvent_t ev_[kProfRing * kProfEvents] = {};
+  cudaEvent_t timer_[2] = {};
+  int profHead_ = 0, profCount_ = 0;
   B2CProfile profile_{};
   bool profileValid_ = false;
   int coopBlocks_ = 0;

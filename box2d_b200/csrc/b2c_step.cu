@@ -1297,7 +1297,8 @@ int World::step(float timeStep, int subStepCount) {
   const int gMove = gridFor(d.moveCapacity, kThreads, maxBlocks), gContact = gridFor(d.contactCapacity, kThreads, maxBlocks);
   const int gBody = gridFor(d.awakeCount, kThreads, maxBlocks), gScan = 148 * 2;
   Scalars* sc = d.sc;
-  cudaEventRecord(ev_[0], stream_);
+  cudaEvent_t* pe = ev_ + (profHead_ % kProfRing) * kProfEvents;
+  cudaEventRecord(pe[0], stream_);
   // --- UpdateBroadPhasePairs ---
   CK(cudaMemsetAsync(d.pairTable, 0xff, sizeof(unsigned long long) * (size_t)d.pairTableSize, stream_));
   k_pair_insert<<<gContact, kThreads, 0, stream_>>>(d);
@@ -1308,7 +1309,7 @@ int World::step(float timeStep, int subStepCount) {
   k_create_contacts<<<gContact, kThreads, 0, stream_>>>(d);
   k_clear_moved<<<gMove, kThreads, 0, stream_>>>(d);
   k_pairs_finish<<<1, 1, 0, stream_>>>(d);
-  cudaEventRecord(ev_[1], stream_);
+  cudaEventRecord(pe[1], stream_);
   // --- Collide ---
   k_tree_rebuild<<<2, 32, 0, stream_>>>(d);
   k_collide<<<gContact, kThreads, 0, stream_>>>(d, sp);
@@ -1317,7 +1318,7 @@ int World::step(float timeStep, int subStepCount) {
   k_contact_events<<<gContact, kThreads, 0, stream_>>>(d, sp);
   k_events_finish<<<1, 1, 0, stream_>>>(d, sp, d.flagScan + d.contactCapacity);
   k_color_ops<<<1, 1024, 0, stream_>>>(d);
-  cudaEventRecord(ev_[2], stream_);
+  cudaEventRecord(pe[2], stream_);
   // --- Solve ---
   int gChunks = gridFor(d.contactCapacity, kSortChunk, maxBlocks);
   k_color_hist<<<gChunks, kSortChunk, 0, stream_>>>(d);
@@ -1331,11 +1332,12 @@ int World::step(float timeStep, int subStepCount) {
     if (perSm < 1) return fail(B2C_E_CUDA, "k_solver cannot be made resident for a cooperative launch");
     coopBlocks_ = prop.multiProcessorCount;       // one 512-thread CTA per SM: the barrier cost grows with CTA count
   }
+  cudaEventRecord(pe[3], stream_);
   {
     void* args[] = {(void*)&d, (void*)&sp};
     CK(cudaLaunchCooperativeKernel((void*)k_solver, dim3(coopBlocks_), dim3(512), args, 0, stream_));
   }
-  cudaEventRecord(ev_[3], stream_);
+  cudaEventRecord(pe[4], stream_);
   // --- Finalize + refit ---
   k_finalize<<<gBody, kThreads, 0, stream_>>>(d, sp);
   k_scan_chunks<int><<<gScan, kScanChunk, 0, stream_>>>(d.bodyEnlargedCount, d.scanBlockSums, &sc->awakeCount);
@@ -1345,10 +1347,10 @@ int World::step(float timeStep, int subStepCount) {
   lastEndIndex_ = endIndex_;
   endIndex_ = 1 - endIndex_;
   k_step_finish<<<1, 1, 0, stream_>>>(d, endIndex_);
-  cudaEventRecord(ev_[4], stream_);
+  cudaEventRecord(pe[5], stream_);
+  profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
   CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
   CK(cudaGetLastError());
-  profileValid_ = true;
   stepCount_++;
   return B2C_OK;
 }

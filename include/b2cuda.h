@@ -162,7 +162,11 @@ int32_t b2cuda_world_read_contacts(B2CWorld* world, B2CContactRead* dst, int32_t
 int32_t b2cuda_world_read_joints(B2CWorld* world, B2CJointRead* dst, int32_t capacity, int32_t* count);
 int32_t b2cuda_world_read_shapes(B2CWorld* world, B2CShapeRead* dst, int32_t capacity, int32_t* count);
 int32_t b2cuda_world_get_counters(B2CWorld* world, B2CCounters* out);
-int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);
+int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);   /* averages over the steps since the previous call (<= 64) */
+/* (new, no reference counterpart) device-time stopwatch on the world's own stream: CUDA events around whatever was
+ * enqueued between the two calls; stop synchronises. Used by bench.py so timing does not depend on torch's stream. */
+int32_t b2cuda_world_timer_start(B2CWorld* world);
+int32_t b2cuda_world_timer_stop(B2CWorld* world, float* elapsedMs);
 
 #ifdef __cplusplus
 }

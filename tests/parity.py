@@ -85,8 +85,9 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
             worst = max(worst, e)
             notes.extend(rep)
         c = cuda.GetCounters()
+        co = orc.GetCounters()
         return dict(max_rel_err=worst, steps=steps, contacts=c.contactCount, touching=c.touchingContactCount, bodies=c.bodyCount,
-                    colors=c.activeColorCount, toi=c.toiCandidates)
+                    colors=c.activeColorCount, toi=c.toiCandidates, toi_oracle=co.toiCandidates)
     finally:
         cuda.Destroy()
         orc.Destroy()

@@ -14,7 +14,7 @@ def test_small_pyramid_bit_exact():
 def test_mixed_drop_bit_exact():
     res = parity.run_pair(lambda w: scenes.mixed_drop(w), steps=60, verbose=True)
     assert res["max_rel_err"] == 0.0
-    assert res["toi"] == 0
+    assert res["toi"] == res["toi_oracle"]      # fast bodies take the no-hit continuous path on both sides
 
 
 def test_large_pyramid_10_steps():
