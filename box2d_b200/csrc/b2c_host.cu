@@ -39,7 +39,7 @@ static MassData geomMass(const Geom& g, float density) {
   if (g.type != kPolygon) return zero;
   if (g.count == 1) return circleMass(g.v[0], g.radius, density);
   if (g.count == 2) return capsuleMass(g.v[0], g.v[1], g.radius, density);
-  V2 verts[kMaxPolygonVertices];
+  V2 verts[kMaxPolygonVertices] = {};
   if (g.radius > 0.0f) {
     const float sqrt2 = 1.4142135623730950488016887242097f;
     for (int i = 0, j = g.count - 1; i < g.count; j = i++) {

@@ -109,7 +109,7 @@ inline MassData ComputeMass(const Geom& g, float density) {
   // include/Collision.cs:431-484
   if (g.count == 1) return CircleMass(g.v[0], g.radius, density);
   if (g.count == 2) return CapsuleMass(g.v[0], g.v[1], g.radius, density);
-  Vec2 vertices[kMaxPolygonVertices];
+  Vec2 vertices[kMaxPolygonVertices] = {};
   if (g.radius > 0) {
     float sqrt2 = 1.4142135623730950488016887242097f;
     for (int i = 0, j = g.count - 1; i < g.count; j = i++) {
