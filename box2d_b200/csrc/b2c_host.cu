@@ -423,11 +423,15 @@ int World::upload() {
   DA(d.sA, float4, cc); DA(d.sB, float4, cc); DA(d.sC, float4, cc); DA(d.sD, float4, cc); DA(d.sE, float4, cc); DA(d.sF, float4, cc);
   DA(d.sG, float4, cc); DA(d.sH, float4, cc); DA(d.sI, float4, cc); DA(d.sJ, float4, cc); DA(d.sContact, int, cc); DA(d.cConstraint, int, contactCap);
   DA(d.blockHist, int, (size_t)(contactCap / 256 + 2) * kGraphColorCount);
+  DA(d.ufParent, int, nAwake); DA(d.rootBodyCount, int, nAwake); DA(d.rootConCount, int, nAwake); DA(d.rootColorCount, int, (size_t)nAwake * kGraphColorCount);
+  DA(d.rootInfo, int, nAwake); DA(d.rootScan, int4, nAwake + 1); DA(d.islandBodyStart, int, nAwake + 1); DA(d.islandConStart, int, nAwake + 1);
+  DA(d.islandColorOff, int, (size_t)(nAwake + 1) * (kGraphColorCount + 1)); DA(d.islandBodies, int, nAwake); DA(d.bodyLocal, int, nAwake);
+  DA(d.freeBodies, int, nAwake); DA(d.bigBodies, int, nAwake); DA(d.kinematicUsed, uint8_t, nAwake); DA(d.sLocal, int2, cc);
   DA(d.beginEvents, B2CContactTouchEvent, d.eventCapacity); DA(d.endEvents[0], B2CContactTouchEvent, d.eventCapacity);
   DA(d.endEvents[1], B2CContactTouchEvent, d.eventCapacity); DA(d.hitEvents, B2CContactHitEvent, d.eventCapacity);
   DA(d.bodyEnlargedCount, int, nAwake + 1);
   DA(d.sc, Scalars, 1);
-  int scanBlocks = std::max(contactCap, std::max(d.moveCapacity, nAwake)) / 1024 + 2;
+  int scanBlocks = std::max(contactCap, std::max(d.moveCapacity, nAwake)) / 256 + 2;
   DA(d.scanBlockSums, int, scanBlocks); DA(d.scanBlockSums4, int4, scanBlocks);
   Scalars init; memset(&init, 0, sizeof(init));
   init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;
@@ -641,7 +645,7 @@ int World::getCounters(B2CCounters* out) {
   out->contactCount = s.liveContactCount; out->touchingContactCount = s.touchingCount; out->contactIdCapacity = s.contactNext;
   int active = 0;
   for (int c = 0; c < kGraphColorCount; c++) {
-    out->colorCounts[c] = s.colorCount[c] + (d_.jointColorStart[c + 1] - d_.jointColorStart[c]);
+    out->colorCounts[c] = s.colorTotal[c] + (d_.jointColorStart[c + 1] - d_.jointColorStart[c]);
     if (c < kOverflowIndex && out->colorCounts[c] > 0) active++;
   }
   out->activeColorCount = active; out->moveCount = s.moveCount; out->newPairCount = s.newPairCount; out->toiCandidates = s.toiCandidates;

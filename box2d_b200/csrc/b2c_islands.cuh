@@ -1,0 +1,277 @@
+// libb2cuda — island partition + island-local solver (included by b2c_step.cu after the lane functions).
+// An island is a connected component of dynamic bodies under touching contacts and joints (the partition src/Island.cs
+// maintains for sleeping). Constraints of different islands never share a writable body, so each island may run the
+// reference's stage sequence on its own: colors in order, barrier between colors. A small island runs inside ONE CTA
+// with its body rows in shared memory and its constraints in registers, so the ~120 barriers of a step are
+// __syncthreads() instead of grid-wide syncs; large islands (and islands with joints or kinematic neighbours) keep the
+// grid-wide kernel. Per-body and per-constraint arithmetic is identical in both paths, hence so are the results.
+#pragma once
+
+namespace b2c {
+
+constexpr int kIslandThreads = 256;
+constexpr int kIslandMaxBodies = 256;      // body rows staged in shared memory (8 KB)
+constexpr int kIslandMaxCons = 1024;       // <= kIslandThreads: constraints live in registers; above: re-read per stage
+constexpr int kForceBig = 1 << 20;
+
+__device__ __forceinline__ int ufFind(int* parent, int x) {
+  int p = parent[x];
+  while (p != x) { int gp = parent[p]; if (gp != p) parent[x] = gp; x = p; p = gp; }   // path halving
+  return x;
+}
+__device__ __forceinline__ void ufUnion(int* parent, int a, int b) {
+  while (true) {
+    a = ufFind(parent, a); b = ufFind(parent, b);
+    if (a == b) return;
+    int hi = a > b ? a : b, lo = a > b ? b : a;
+    int old = atomicCAS(&parent[hi], hi, lo);    // hook the larger root under the smaller one
+    if (old == hi) return;
+  }
+}
+__device__ __forceinline__ bool simIsDynamic(const WorldDev& d, int sim) { return sim >= 0 && (fbits(d.st0[sim].w) & kDynamicFlag) != 0; }
+
+// grid-wide exclusive scan of int4 rows inside a cooperative kernel (chunk = blockDim.x); consumers add sums[i / blockDim.x]
+__device__ void gridScan4(cg::grid_group& grid, int4* data, int4* sums, int n, int4* totalOut) {
+  __shared__ int4 warpSums[32];
+  const int chunk = blockDim.x;
+  int chunks = (n + chunk - 1) / chunk;
+  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+    int i = c * chunk + threadIdx.x;
+    int4 v = i < n ? data[i] : make_int4(0, 0, 0, 0);
+    int4 total;
+    int4 inc = blockInclusive(v, warpSums, &total);
+    if (i < n) data[i] = addT(inc, make_neg(v));
+    if (threadIdx.x == 0) sums[c] = total;
+  }
+  grid.sync();
+  if (blockIdx.x == 0) {
+    int4 carry = make_int4(0, 0, 0, 0);
+    for (int base = 0; base < chunks; base += chunk) {
+      int i = base + threadIdx.x;
+      int4 v = i < chunks ? sums[i] : make_int4(0, 0, 0, 0);
+      int4 total;
+      int4 inc = blockInclusive(v, warpSums, &total);
+      if (i < chunks) sums[i] = addT(carry, addT(inc, make_neg(v)));
+      carry = addT(carry, total);
+    }
+    if (threadIdx.x == 0) *totalOut = carry;
+  }
+  grid.sync();
+}
+
+// Rebuilds the island partition and the constraint order [grid-path colors | island 0 | island 1 | ...] when the graph
+// changed this step; a no-op (one uniform branch) otherwise. Order inside one (group, color) bucket is arbitrary:
+// constraints of one color never share a writable body, so it does not influence any result.
+__global__ void __launch_bounds__(512) k_islands(WorldDev d) {
+  Scalars& s = *d.sc;
+  if (!s.graphDirty) return;
+  cg::grid_group grid = cg::this_grid();
+  const int tid = gtid(), stride = gsize();
+  const int awake = d.awakeCount, nContacts = s.contactNext, nJoints = d.jointColorStart[kGraphColorCount];
+  __shared__ int hist[kGraphColorCount];
+  // P0 init
+  for (int i = tid; i < awake; i += stride) { d.ufParent[i] = i; d.rootBodyCount[i] = 0; d.rootConCount[i] = 0; d.kinematicUsed[i] = 0; }
+  for (int i = tid; i < awake * kGraphColorCount; i += stride) d.rootColorCount[i] = 0;
+  if (tid < kGraphColorCount) { s.colorTotal[tid] = 0; s.bigCursor[tid] = 0; s.colorCount[tid] = 0; }
+  if (tid == 0) { s.freeBodyCount = 0; s.bigBodyCount = 0; }
+  grid.sync();
+  // P1 union
+  for (int i = tid; i < nContacts; i += stride) {
+    if (!(d.cFlags[i] & CF_TOUCHING) || d.cColor[i] >= kOverflowIndex) continue;
+    int2 sim = d.cSim[i];
+    if (simIsDynamic(d, sim.x) && simIsDynamic(d, sim.y)) ufUnion(d.ufParent, sim.x, sim.y);
+  }
+  for (int k = tid; k < nJoints; k += stride) {
+    const JointDev& j = d.joints[d.jointSorted[k]];
+    int a = d.bodySim[j.bodyIdA], b = d.bodySim[j.bodyIdB];
+    if (simIsDynamic(d, a) && simIsDynamic(d, b)) ufUnion(d.ufParent, a, b);
+  }
+  grid.sync();
+  // P2 flatten + bodies per root
+  for (int i = tid; i < awake; i += stride) { int r = ufFind(d.ufParent, i); d.ufParent[i] = r; atomicAdd(&d.rootBodyCount[r], 1); }
+  grid.sync();
+  // P3 constraints per root / color
+  if (threadIdx.x < kGraphColorCount) hist[threadIdx.x] = 0;
+  __syncthreads();
+  for (int i = tid; i < nContacts; i += stride) {
+    if (!(d.cFlags[i] & CF_TOUCHING)) continue;
+    int c = d.cColor[i];
+    atomicAdd(&hist[c], 1);
+    if (c >= kOverflowIndex) continue;
+    int2 sim = d.cSim[i];
+    bool dynA = simIsDynamic(d, sim.x), dynB = simIsDynamic(d, sim.y);
+    int r = d.ufParent[dynA ? sim.x : sim.y];
+    int add = 1;
+    if (sim.x >= 0 && !dynA) { d.kinematicUsed[sim.x] = 1; add += kForceBig; }
+    if (sim.y >= 0 && !dynB) { d.kinematicUsed[sim.y] = 1; add += kForceBig; }
+    atomicAdd(&d.rootConCount[r], add);
+    atomicAdd(&d.rootColorCount[r * kGraphColorCount + c], 1);
+  }
+  for (int k = tid; k < nJoints; k += stride) {
+    const JointDev& j = d.joints[d.jointSorted[k]];
+    int a = d.bodySim[j.bodyIdA], b = d.bodySim[j.bodyIdB];
+    bool dynA = simIsDynamic(d, a), dynB = simIsDynamic(d, b);
+    if (a >= 0 && !dynA) d.kinematicUsed[a] = 1;
+    if (b >= 0 && !dynB) d.kinematicUsed[b] = 1;
+    if (dynA || dynB) atomicAdd(&d.rootConCount[d.ufParent[dynA ? a : b]], kForceBig);
+  }
+  __syncthreads();
+  if (threadIdx.x < kGraphColorCount && hist[threadIdx.x]) atomicAdd(&s.colorTotal[threadIdx.x], hist[threadIdx.x]);
+  grid.sync();
+  // P4 classify roots
+  for (int i = tid; i < awake; i += stride) {
+    int4 in = make_int4(0, 0, 0, 0);
+    if (d.ufParent[i] == i) {
+      int bodies = d.rootBodyCount[i], cons = d.rootConCount[i];
+      if (cons == 0) d.rootInfo[i] = d.kinematicUsed[i] ? -2 : -1;
+      else if (bodies > kIslandMaxBodies || cons > kIslandMaxCons) {
+        d.rootInfo[i] = -2;
+        for (int c = 0; c < kOverflowIndex; c++) { int n = d.rootColorCount[i * kGraphColorCount + c]; if (n) atomicAdd(&s.colorCount[c], n); }
+      } else { d.rootInfo[i] = 0; in = make_int4(1, bodies, cons, 0); }
+    }
+    d.rootScan[i] = in;
+  }
+  grid.sync();
+  gridScan4(grid, d.rootScan, d.scanBlockSums4, awake, d.rootScan + awake);
+  // P6 layout of the grid-path color ranges (padded to 32) in front of the islands
+  if (tid == 0) {
+    int start = 0, touching = 0;
+    for (int c = 0; c < kGraphColorCount; c++) { s.colorStart[c] = start; start += (s.colorCount[c] + 31) & ~31; touching += s.colorTotal[c]; }
+    int4 tot = d.rootScan[awake];
+    s.smallConStart = start; s.islandCount = tot.x; s.constraintTotal = start + tot.z; s.touchingCount = touching;
+  }
+  grid.sync();
+  // P7 per island offsets
+  const int smallConStart = s.smallConStart;
+  for (int t = tid; t < smallConStart; t += stride) d.sContact[t] = -1;
+  for (int i = tid; i < awake; i += stride) {
+    if (d.ufParent[i] != i || d.rootInfo[i] < 0) continue;
+    int4 sc = addT(d.rootScan[i], d.scanBlockSums4[i / (int)blockDim.x]);
+    int id = sc.x;
+    d.rootInfo[i] = id;
+    d.islandBodyStart[id] = sc.y; d.islandBodyStart[id + 1] = sc.y + d.rootBodyCount[i];
+    d.islandConStart[id] = smallConStart + sc.z;
+    int off = 0;
+    for (int c = 0; c < kGraphColorCount; c++) { d.islandColorOff[id * (kGraphColorCount + 1) + c] = off; off += d.rootColorCount[i * kGraphColorCount + c]; d.rootColorCount[i * kGraphColorCount + c] = 0; }
+    d.islandColorOff[id * (kGraphColorCount + 1) + kGraphColorCount] = off;
+    d.rootBodyCount[i] = 0;
+  }
+  grid.sync();
+  // P8 bodies -> free list / grid-path list / island lists
+  for (int i = tid; i < awake; i += stride) {
+    int r = d.ufParent[i], info = d.rootInfo[r];
+    if (info == -1) { d.freeBodies[atomicAdd(&s.freeBodyCount, 1)] = i; d.bodyLocal[i] = -1; }
+    else if (info == -2) { d.bigBodies[atomicAdd(&s.bigBodyCount, 1)] = i; d.bodyLocal[i] = -1; }
+    else { int k = atomicAdd(&d.rootBodyCount[r], 1); d.islandBodies[d.islandBodyStart[info] + k] = i; d.bodyLocal[i] = k; }
+  }
+  grid.sync();
+  // P9 constraints -> slots
+  for (int i = tid; i < nContacts; i += stride) {
+    if (!(d.cFlags[i] & CF_TOUCHING)) { if (d.cFlags[i] & CF_ALIVE) d.cConstraint[i] = -1; continue; }
+    int c = d.cColor[i];
+    if (c >= kOverflowIndex) { d.cConstraint[i] = -1; continue; }
+    int2 sim = d.cSim[i];
+    int r = d.ufParent[simIsDynamic(d, sim.x) ? sim.x : sim.y];
+    int info = d.rootInfo[r], t;
+    if (info < 0) t = s.colorStart[c] + atomicAdd(&s.bigCursor[c], 1);
+    else t = d.islandConStart[info] + d.islandColorOff[info * (kGraphColorCount + 1) + c] + atomicAdd(&d.rootColorCount[r * kGraphColorCount + c], 1);
+    d.sContact[t] = i; d.cConstraint[i] = t;
+    d.sLocal[t] = make_int2(sim.x >= 0 ? d.bodyLocal[sim.x] : -1, sim.y >= 0 ? d.bodyLocal[sim.y] : -1);
+  }
+}
+
+
+// Bodies that no constraint touches: the four substeps are a private loop (IntegrateVelocities + IntegratePositions).
+__global__ void __launch_bounds__(kThreads) k_free_bodies(WorldDev d, StepParams sp) {
+  int n = d.sc->freeBodyCount;
+  for (int k = gtid(); k < n; k += gsize()) {
+    int i = d.freeBodies[k];
+    float4 s0 = d.st0[i], s1 = d.st1[i], m = d.simMass[i], f = d.simForce[i];
+    uint32_t sf = d.simFlags[i], sf0 = sf;
+    for (int sub = 0; sub < sp.subStepCount; sub++) { s0 = integrateVelocityRow(s0, m, f, sp, &sf); integratePositionRow(s0, s1, sp); }
+    d.st0[i] = s0; d.st1[i] = s1;
+    if (sf != sf0) d.simFlags[i] = sf;
+  }
+}
+
+// One CTA per small island: the whole SolverTask stage sequence (src/Solver.cs:599-727) with __syncthreads() as the barrier.
+template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepParams& sp, int g, float4* s0, float4* s1, int* colorOff) {
+  const int tid = threadIdx.x, T = blockDim.x;
+  const int bBegin = d.islandBodyStart[g], nb = d.islandBodyStart[g + 1] - bBegin;
+  const int cBegin = d.islandConStart[g];
+  if (tid <= kGraphColorCount) colorOff[tid] = d.islandColorOff[g * (kGraphColorCount + 1) + tid];
+  int sim = -1; float4 m = make_float4(0, 0, 0, 0), f = m; uint32_t sf = 0, sf0 = 0;
+  if (tid < nb) { sim = d.islandBodies[bBegin + tid]; s0[tid] = d.st0[sim]; s1[tid] = d.st1[sim]; m = d.simMass[sim]; f = d.simForce[sim]; sf = sf0 = d.simFlags[sim]; }
+  __syncthreads();
+  const int K = colorOff[kGraphColorCount];
+  BodyRows bs{s0, s1};
+  // register-resident constraint (CACHED): thread t owns constraint cBegin + t for the whole step
+  Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int2 loc = make_int2(-1, -1); int myColor = -1;
+  if (CACHED && tid < K) {
+    loadLane(d, cBegin + tid, c, false); I = d.sI[cBegin + tid]; J = d.sJ[cBegin + tid]; loc = d.sLocal[cBegin + tid];
+    for (int k = 0; k < kOverflowIndex; k++) if (tid >= colorOff[k] && tid < colorOff[k + 1]) myColor = k;
+  }
+  for (int sub = 0; sub < sp.subStepCount; sub++) {
+    if (tid < nb) s0[tid] = integrateVelocityRow(s0[tid], m, f, sp, &sf);
+    __syncthreads();
+    for (int k = 0; k < kOverflowIndex; k++) {
+      if (colorOff[k] == colorOff[k + 1]) continue;
+      if (CACHED) { if (myColor == k) warmStartLane(bs, c, loc.x, loc.y, I, J.z); }
+      else for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) { Lane l; loadLane(d, cBegin + t, l, true); int2 lc = d.sLocal[cBegin + t]; warmStartLane(bs, l, lc.x, lc.y, d.sI[cBegin + t], d.sJ[cBegin + t].z); }
+      __syncthreads();
+    }
+    for (int k = 0; k < kOverflowIndex; k++) {
+      if (colorOff[k] == colorOff[k + 1]) continue;
+      if (CACHED) { if (myColor == k) solveLane<true>(bs, sp, c, loc.x, loc.y, I, J); }
+      else for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) {
+        Lane l; loadLane(d, cBegin + t, l, false); int2 lc = d.sLocal[cBegin + t]; float4 li = d.sI[cBegin + t], lj = d.sJ[cBegin + t];
+        solveLane<true>(bs, sp, l, lc.x, lc.y, li, lj); d.sI[cBegin + t] = li; d.sJ[cBegin + t] = lj;
+      }
+      __syncthreads();
+    }
+    if (tid < nb) { float4 a = s0[tid], b = s1[tid]; integratePositionRow(a, b, sp); s0[tid] = a; s1[tid] = b; }
+    __syncthreads();
+    for (int k = 0; k < kOverflowIndex; k++) {
+      if (colorOff[k] == colorOff[k + 1]) continue;
+      if (CACHED) { if (myColor == k) solveLane<false>(bs, sp, c, loc.x, loc.y, I, J); }
+      else for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) {
+        Lane l; loadLane(d, cBegin + t, l, false); int2 lc = d.sLocal[cBegin + t]; float4 li = d.sI[cBegin + t], lj = d.sJ[cBegin + t];
+        solveLane<false>(bs, sp, l, lc.x, lc.y, li, lj); d.sI[cBegin + t] = li; d.sJ[cBegin + t] = lj;
+      }
+      __syncthreads();
+    }
+  }
+  if (CACHED && tid < K) { d.sI[cBegin + tid] = I; d.sJ[cBegin + tid] = J; }
+  if (d.sc->anyRestitution) {                     // ApplyRestitution per color, 8-lane groups in this island's order
+    __syncthreads();
+    for (int k = 0; k < kOverflowIndex; k++) {
+      if (colorOff[k] == colorOff[k + 1]) continue;
+      for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) {
+        int g0 = colorOff[k] + ((t - colorOff[k]) & ~7);
+        bool allZero = true;
+        for (int q = g0; q < g0 + 8 && q < colorOff[k + 1]; q++) if (!(d.sD[cBegin + q].w == 0.0f)) allZero = false;
+        if (allZero) continue;
+        Lane l; loadLane(d, cBegin + t, l, false); int2 lc = d.sLocal[cBegin + t]; float4 li = d.sI[cBegin + t], lj = d.sJ[cBegin + t];
+        restitutionLane(bs, sp, l, lc.x, lc.y, li, lj); d.sI[cBegin + t] = li; d.sJ[cBegin + t] = lj;
+      }
+      __syncthreads();
+    }
+  }
+  __syncthreads();
+  if (tid < nb) { d.st0[sim] = s0[tid]; d.st1[sim] = s1[tid]; if (sf != sf0) d.simFlags[sim] = sf; }
+  for (int t = tid; t < K; t += T) storeImpulses(d, cBegin + t);
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kIslandThreads) k_solver_islands(WorldDev d, StepParams sp) {
+  __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
+  __shared__ int colorOff[kGraphColorCount + 1];
+  int n = d.sc->islandCount;
+  for (int g = blockIdx.x; g < n; g += gridDim.x) {
+    int K = d.islandColorOff[g * (kGraphColorCount + 1) + kGraphColorCount];
+    if (K <= (int)blockDim.x) runIsland<true>(d, sp, g, s0, s1, colorOff);
+    else runIsland<false>(d, sp, g, s0, s1, colorOff);
+  }
+}
+
+}  // namespace b2c

@@ -671,6 +671,20 @@ __device__ __forceinline__ BodyW gatherBody(const WorldDev& d, int index) {     
 __device__ __forceinline__ void scatterBody(const WorldDev& d, int index, const BodyW& b) {   // ScatterBodies :452-479 (v,w only change)
   if (index >= 0 && (b.flags & kDynamicFlag)) d.st0[index] = make_float4(b.v.x, b.v.y, b.w, __uint_as_float(b.flags));
 }
+// Body-state accessors for the constraint lanes: rows in global memory (grid path) or staged in shared memory (island path).
+struct BodyRows {
+  float4* st0; float4* st1;
+  __device__ __forceinline__ BodyW load(int index) const {
+    BodyW b;
+    if (index < 0) { b.v = mk(0, 0); b.w = 0; b.flags = 0; b.dp = mk(0, 0); b.dq = mkRot(1, 0); return b; }
+    float4 a = st0[index], c = st1[index];
+    b.v = mk(a.x, a.y); b.w = a.z; b.flags = fbits(a.w); b.dp = mk(c.x, c.y); b.dq = mkRot(c.z, c.w);
+    return b;
+  }
+  __device__ __forceinline__ void store(int index, const BodyW& b) const {
+    if (index >= 0 && (b.flags & kDynamicFlag)) st0[index] = make_float4(b.v.x, b.v.y, b.w, __uint_as_float(b.flags));
+  }
+};
 
 struct Lane {       // one constraint's read-only planes in registers
   int indexA, indexB; float mA, mB, iA, iB; V2 n; float friction, tangentSpeed, rollingResistance, rollingMass;
@@ -760,10 +774,8 @@ __device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
 }
 
 // WarmStartContactsTask :686-744
-__device__ __forceinline__ void warmStartContact(const WorldDev& d, int t) {
-  Lane c; loadLane(d, t, c, true);
-  float4 I = d.sI[t]; float rollingImpulse = d.sJ[t].z;
-  BodyW bA = gatherBody(d, c.indexA), bB = gatherBody(d, c.indexB);
+__device__ __forceinline__ void warmStartLane(const BodyRows& bs, const Lane& c, int ia, int ib, float4 I, float rollingImpulse) {
+  BodyW bA = bs.load(ia), bB = bs.load(ib);
   float tangentX = c.n.y, tangentY = 0.0f - c.n.x;
   {
     float Px = I.x * c.n.x + I.y * tangentX, Py = I.x * c.n.y + I.y * tangentY;
@@ -781,7 +793,12 @@ __device__ __forceinline__ void warmStartContact(const WorldDev& d, int t) {
   }
   bA.w = bA.w - c.iA * rollingImpulse;
   bB.w = bB.w + c.iB * rollingImpulse;
-  scatterBody(d, c.indexA, bA); scatterBody(d, c.indexB, bB);
+  bs.store(ia, bA); bs.store(ib, bB);
+}
+__device__ __forceinline__ void warmStartContact(const WorldDev& d, int t) {
+  Lane c; loadLane(d, t, c, true);
+  BodyRows bs{d.st0, d.st1};
+  warmStartLane(bs, c, c.indexA, c.indexB, d.sI[t], d.sJ[t].z);
 }
 
 __device__ __forceinline__ void solveNormalPoint(BodyW& bA, BodyW& bB, const Lane& c, V2 dp, V2 rA, V2 rB, float baseSeparation, float normalMass,
@@ -821,11 +838,9 @@ __device__ __forceinline__ void solveFrictionPoint(BodyW& bA, BodyW& bB, const L
   applyP(bA, bB, c, rA, rB, impulse * tangentX, impulse * tangentY);
 }
 // SolveContactsTask :745-912 (useBias=true: Solve, false: Relax)
-template <bool USE_BIAS> __device__ __forceinline__ void solveContact(const WorldDev& d, const StepParams& sp, int t) {
-  Lane c; loadLane(d, t, c, false);
-  float4 I = d.sI[t], J = d.sJ[t];
+template <bool USE_BIAS> __device__ __forceinline__ void solveLane(const BodyRows& bs, const StepParams& sp, const Lane& c, int ia, int ib, float4& I, float4& J) {
   float contactSpeed = -sp.contactSpeed;
-  BodyW bA = gatherBody(d, c.indexA), bB = gatherBody(d, c.indexB);
+  BodyW bA = bs.load(ia), bB = bs.load(ib);
   float biasRate, massScale, impulseScale;
   if (USE_BIAS) { biasRate = c.massScale * c.biasRate; massScale = c.massScale; impulseScale = c.impulseScale; }
   else { biasRate = 0.0f; massScale = 1.0f; impulseScale = 0.0f; }
@@ -845,8 +860,14 @@ template <bool USE_BIAS> __device__ __forceinline__ void solveContact(const Worl
     bA.w = bA.w - c.iA * deltaLambda;
     bB.w = bB.w + c.iB * deltaLambda;
   }
+  bs.store(ia, bA); bs.store(ib, bB);
+}
+template <bool USE_BIAS> __device__ __forceinline__ void solveContact(const WorldDev& d, const StepParams& sp, int t) {
+  Lane c; loadLane(d, t, c, false);
+  float4 I = d.sI[t], J = d.sJ[t];
+  BodyRows bs{d.st0, d.st1};
+  solveLane<USE_BIAS>(bs, sp, c, c.indexA, c.indexB, I, J);
   d.sI[t] = I; d.sJ[t] = J;
-  scatterBody(d, c.indexA, bA); scatterBody(d, c.indexB, bB);
 }
 
 // ApplyRestitutionTask :913-989, with quirk Q1 (multiplies by the compare mask, not the blended mass). The reference skips an
@@ -866,6 +887,13 @@ __device__ __forceinline__ void restitutionPoint(BodyW& bA, BodyW& bB, const Lan
   totalP = totalP + deltaImpulse;
   applyP(bA, bB, c, rA, rB, deltaImpulse * c.n.x, deltaImpulse * c.n.y);
 }
+__device__ __forceinline__ void restitutionLane(const BodyRows& bs, const StepParams& sp, const Lane& c, int ia, int ib, float4& I, float4& J) {
+  BodyW bA = bs.load(ia), bB = bs.load(ib);
+  bool restitutionMask = c.restitution == 0.0f;
+  restitutionPoint(bA, bB, c, c.rA1, c.rB1, c.relVel1, I.x, J.x, sp.restitutionThreshold, restitutionMask);
+  restitutionPoint(bA, bB, c, c.rA2, c.rB2, c.relVel2, I.z, J.y, sp.restitutionThreshold, restitutionMask);
+  bs.store(ia, bA); bs.store(ib, bB);
+}
 __device__ __forceinline__ void restitutionContact(const WorldDev& d, const StepParams& sp, int t, int colorBegin, int colorEnd) {
   int g0 = colorBegin + ((t - colorBegin) & ~7);
   bool allZero = true;
@@ -873,12 +901,9 @@ __device__ __forceinline__ void restitutionContact(const WorldDev& d, const Step
   if (allZero) return;
   Lane c; loadLane(d, t, c, false);
   float4 I = d.sI[t], J = d.sJ[t];
-  BodyW bA = gatherBody(d, c.indexA), bB = gatherBody(d, c.indexB);
-  bool restitutionMask = c.restitution == 0.0f;
-  restitutionPoint(bA, bB, c, c.rA1, c.rB1, c.relVel1, I.x, J.x, sp.restitutionThreshold, restitutionMask);
-  restitutionPoint(bA, bB, c, c.rA2, c.rB2, c.relVel2, I.z, J.y, sp.restitutionThreshold, restitutionMask);
+  BodyRows bs{d.st0, d.st1};
+  restitutionLane(bs, sp, c, c.indexA, c.indexB, I, J);
   d.sI[t] = I; d.sJ[t] = J;
-  scatterBody(d, c.indexA, bA); scatterBody(d, c.indexB, bB);
 }
 // StoreImpulsesTask :990-1025
 __device__ __forceinline__ void storeImpulses(const WorldDev& d, int t) {
@@ -1007,9 +1032,8 @@ __device__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j,
   }
 }
 
-// IntegrateVelocitiesTask src/Solver.cs:121-160
-__device__ __forceinline__ void integrateVelocity(const WorldDev& d, const StepParams& sp, int i) {
-  float4 s = d.st0[i], m = d.simMass[i], f = d.simForce[i];
+// IntegrateVelocitiesTask src/Solver.cs:121-160 — pure row form; returns the new (v, w, flags) row, ORs IsSpeedCapped into *simFlags
+__device__ __forceinline__ float4 integrateVelocityRow(float4 s, float4 m, float4 f, const StepParams& sp, uint32_t* simFlags) {
   V2 v = mk(s.x, s.y); float w = s.z; uint32_t flags = fbits(s.w);
   float h = sp.h;
   float maxAngularSpeed = kMaxRotation * sp.inv_dt;
@@ -1020,35 +1044,40 @@ __device__ __forceinline__ void integrateVelocity(const WorldDev& d, const StepP
   float angularDelta = h * m.y * f.z;
   v = mulAdd(delta, linearDamping, v);
   w = angularDelta + angularDamping * w;
-  uint32_t simFlags = 0;
-  if (dot(v, v) > maxLinSq) { float ratio = sp.maxLinearSpeed / length(v); v = ratio * v; simFlags |= kIsSpeedCapped; }
-  if (w * w > maxAngSq && !(d.simFlags[i] & kAllowFastRotation)) { float ratio = maxAngularSpeed / fabsf(w); w *= ratio; simFlags |= kIsSpeedCapped; }
-  if (simFlags) d.simFlags[i] |= simFlags;
+  if (dot(v, v) > maxLinSq) { float ratio = sp.maxLinearSpeed / length(v); v = ratio * v; *simFlags |= kIsSpeedCapped; }
+  if (w * w > maxAngSq && !(*simFlags & kAllowFastRotation)) { float ratio = maxAngularSpeed / fabsf(w); w *= ratio; *simFlags |= kIsSpeedCapped; }
   if (flags & kLockLinearX) v.x = 0.0f;
   if (flags & kLockLinearY) v.y = 0.0f;
   if (flags & kLockAngularZ) w = 0.0f;
-  d.st0[i] = make_float4(v.x, v.y, w, s.w);
+  return make_float4(v.x, v.y, w, s.w);
 }
-// IntegratePositionsTask src/Solver.cs:199-212
+__device__ __forceinline__ void integrateVelocity(const WorldDev& d, const StepParams& sp, int i) {
+  uint32_t sf = d.simFlags[i], sf0 = sf;
+  d.st0[i] = integrateVelocityRow(d.st0[i], d.simMass[i], d.simForce[i], sp, &sf);
+  if (sf != sf0) d.simFlags[i] = sf;
+}
+// IntegratePositionsTask src/Solver.cs:199-212 — pure row form
+__device__ __forceinline__ void integratePositionRow(float4& s, float4& p, const StepParams& sp) {
+  uint32_t flags = fbits(s.w);
+  if (flags & kLockLinearX) s.x = 0.0f;
+  if (flags & kLockLinearY) s.y = 0.0f;
+  if (flags & kLockAngularZ) s.z = 0.0f;
+  V2 dp = mulAdd(mk(p.x, p.y), sp.h, mk(s.x, s.y));
+  Rot dq = integrateRot(mkRot(p.z, p.w), sp.h * s.z);
+  p = make_float4(dp.x, dp.y, dq.c, dq.s);
+}
 __device__ __forceinline__ void integratePosition(const WorldDev& d, const StepParams& sp, int i) {
   float4 s = d.st0[i], p = d.st1[i];
   uint32_t flags = fbits(s.w);
-  bool locked = false;
-  if (flags & kLockLinearX) { s.x = 0.0f; locked = true; }
-  if (flags & kLockLinearY) { s.y = 0.0f; locked = true; }
-  if (flags & kLockAngularZ) { s.z = 0.0f; locked = true; }
-  if (locked) d.st0[i] = s;
-  V2 dp = mulAdd(mk(p.x, p.y), sp.h, mk(s.x, s.y));
-  Rot dq = integrateRot(mkRot(p.z, p.w), sp.h * s.z);
-  d.st1[i] = make_float4(dp.x, dp.y, dq.c, dq.s);
+  integratePositionRow(s, p, sp);
+  if (flags & (kLockLinearX | kLockLinearY | kLockAngularZ)) d.st0[i] = s;
+  d.st1[i] = p;
 }
 
 __global__ void __launch_bounds__(kThreads) k_prepare(WorldDev d, StepParams sp) {
   const Scalars& s = *d.sc;
-  for (int c = 0; c < kOverflowIndex; c++) {
-    int begin = s.colorStart[c], end = begin + s.colorCount[c];
-    for (int t = begin + gtid(); t < end; t += gsize()) prepareContact(d, sp, t);
-  }
+  int total = s.constraintTotal;
+  for (int t = gtid(); t < total; t += gsize()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
   int nj = d.jointColorStart[kGraphColorCount];
   for (int k = gtid(); k < nj; k += gsize()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
 }
@@ -1070,9 +1099,10 @@ __global__ void __launch_bounds__(512) k_solver(WorldDev d, StepParams sp) {
   __syncthreads();
   const int activeCount = sActiveCount;
   const int tid = gtid(), stride = gsize();
-  const int awake = d.awakeCount;
+  const int awake = s.bigBodyCount;               // bodies of grid-path islands (+ kinematic bodies some constraint reads)
+  if (awake == 0 && activeCount == 0) return;     // everything lives in small islands / free bodies: no grid barrier at all
   for (int sub = 0; sub < sp.subStepCount; sub++) {
-    for (int i = tid; i < awake; i += stride) integrateVelocity(d, sp, i);
+    for (int i = tid; i < awake; i += stride) integrateVelocity(d, sp, d.bigBodies[i]);
     grid.sync();
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) warmStartJoint(d, d.joints[d.jointSorted[k]]);
@@ -1084,7 +1114,7 @@ __global__ void __launch_bounds__(512) k_solver(WorldDev d, StepParams sp) {
       for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<true>(d, sp, t);
       grid.sync();
     }
-    for (int i = tid; i < awake; i += stride) integratePosition(d, sp, i);
+    for (int i = tid; i < awake; i += stride) integratePosition(d, sp, d.bigBodies[i]);
     grid.sync();
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], false);
@@ -1102,6 +1132,10 @@ __global__ void __launch_bounds__(512) k_solver(WorldDev d, StepParams sp) {
   for (int a = 0; a < activeCount; a++)
     for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) storeImpulses(d, t);
 }
+
+}  // namespace b2c
+#include "b2c_islands.cuh"
+namespace b2c {
 
 // ------------------------------------------------------------------------------------------------------------
 // Phase 3: FinalizeBodiesTask (src/Solver.cs:402-503) + refit (:1191-1237, src/DynamicTree.cs:482-505)
@@ -1320,23 +1354,26 @@ int World::step(float timeStep, int subStepCount) {
   k_color_ops<<<1, 1024, 0, stream_>>>(d);
   cudaEventRecord(pe[2], stream_);
   // --- Solve ---
-  int gChunks = gridFor(d.contactCapacity, kSortChunk, maxBlocks);
-  k_color_hist<<<gChunks, kSortChunk, 0, stream_>>>(d);
-  k_color_offsets<<<1, 32, 0, stream_>>>(d);
-  k_color_scatter<<<gChunks, kSortChunk, 0, stream_>>>(d);
-  k_prepare<<<gContact, kThreads, 0, stream_>>>(d, sp);
   if (coopBlocks_ == 0) {
-    int perSm = 0;
+    int perSm = 0, perSm2 = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_solver, 512, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm2, k_islands, 512, 0));
     cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device_));
-    if (perSm < 1) return fail(B2C_E_CUDA, "k_solver cannot be made resident for a cooperative launch");
+    if (perSm < 1 || perSm2 < 1) return fail(B2C_E_CUDA, "cooperative kernels cannot be made resident");
     coopBlocks_ = prop.multiProcessorCount;       // one 512-thread CTA per SM: the barrier cost grows with CTA count
   }
+  {
+    void* args[] = {(void*)&d};
+    CK(cudaLaunchCooperativeKernel((void*)k_islands, dim3(coopBlocks_), dim3(512), args, 0, stream_));
+  }
+  k_prepare<<<gContact, kThreads, 0, stream_>>>(d, sp);
   cudaEventRecord(pe[3], stream_);
   {
     void* args[] = {(void*)&d, (void*)&sp};
     CK(cudaLaunchCooperativeKernel((void*)k_solver, dim3(coopBlocks_), dim3(512), args, 0, stream_));
   }
+  k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp);
+  k_free_bodies<<<gBody, kThreads, 0, stream_>>>(d, sp);
   cudaEventRecord(pe[4], stream_);
   // --- Finalize + refit ---
   k_finalize<<<gBody, kThreads, 0, stream_>>>(d, sp);

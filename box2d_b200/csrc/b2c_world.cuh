@@ -69,6 +69,8 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int errorFlags, toiCandidates, jointEventCount, stepCount;
   int touchingCount, liveContactCount, rebuildLeafCount[3], colorRounds;
   int awakeCount, anyRestitution;
+  int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
+  int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
 };
 
 struct StepParams {    // src/Solver.cs:57-112 StepContext (scalars only)
@@ -147,6 +149,20 @@ struct WorldDev {
   int* cConstraint;    // constraint index of contact slot (or -1)
   int constraintCapacity;
   int* blockHist;      // color sort scratch [numChunks][24]
+  // --- islands: connected components of dynamic bodies under touching contacts + joints (src/Island.cs keeps the same
+  //     partition for sleeping; here it only decides which solver kernel a constraint runs in) ---
+  int* ufParent;       // [awake] union-find parent, root after flatten
+  int* rootBodyCount;  // [awake] bodies per root, then body cursor
+  int* rootConCount;   // [awake] constraints per root (+ 1<<20 per joint / kinematic neighbour: forces the grid path)
+  int* rootColorCount; // [awake*24] constraints per root and color, then cursors
+  int* rootInfo;       // [awake] at roots: -1 free body, -2 grid-path island, >= 0 compact island id
+  int4* rootScan;      // [awake+1]
+  int* islandBodyStart; int* islandConStart; int* islandColorOff;   // per island id; islandColorOff is [id*25 + color]
+  int* islandBodies;   // [awake] sim indices grouped by island
+  int* bodyLocal;      // [awake] position inside its island's body list
+  int* freeBodies; int* bigBodies;   // [awake]
+  uint8_t* kinematicUsed;            // [awake] non-dynamic awake body referenced by a constraint
+  int2* sLocal;        // [constraint] island-local body indices (-1 = not in the awake set)
   // --- events ---
   B2CContactTouchEvent* beginEvents; B2CContactTouchEvent* endEvents[2]; B2CContactHitEvent* hitEvents;
   int eventCapacity;
