@@ -176,13 +176,9 @@ def b200_arm(args, rank, world_size, local_rank):
     c2 = w.GetCounters()
     if c2.errorFlags & ~16:
         raise SystemExit(f"bench.py: device error flags 0x{c2.errorFlags:x}")
-    t = torch.tensor([step_ms, warm_ms, e2e_s * 1000.0], dtype=torch.float64, device="cuda")
-    units = torch.tensor([float(bodies * SUBSTEPS * K)], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(units, op=dist.ReduceOp.SUM)
-    step_ms_max, warm_ms_max, e2e_ms_max = [float(x) for x in t.tolist()]
-    total_units = float(units.item())
+    from box2d_b200 import batch
+    (step_ms_max, warm_ms_max, e2e_ms_max), total_units = batch.reduce_timing([step_ms, warm_ms, e2e_s * 1000.0], bodies * SUBSTEPS * K, dist, "cuda")
+    stats = batch.reduce_stats(batch.batch_stats(b[b["flags"] != 0]), dist, "cuda")   # NCCL is used for batch statistics only
     if rank != 0:
         w.Destroy()
         return
@@ -208,7 +204,8 @@ def b200_arm(args, rank, world_size, local_rank):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
             "e2e": {"value": total_units / (e2e_ms_max * 1e-3), "unit": "body-substeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(d2h),
                     "note": "Step(dt,substeps) has no per-step host input; scene uploaded once at the first step; each step reads back all body transforms/velocities and contact events to host"},
-            "gpu_launches": KERNELS_PER_STEP * K, "clocks": sampler.result()}
+            "gpu_launches": KERNELS_PER_STEP * K, "clocks": sampler.result(),
+            "batch_stats": {"bodies": int(stats[0]), "sum_v2": float(stats[1]), "max_speed": float(stats[2]), "min_y": float(stats[3])}}
     if world_size == 1 and not args.no_cpu:
         v, sec, nb = cpu_oracle_run(args.workload, 20, args.cpu_steps)
         line["cpu_baseline"] = {"value": v, "unit": "body-substeps/s", "cores": 1, "kind": "port",

@@ -30,3 +30,15 @@ def test_joint_grid_small():
 def test_tumbler_small():
     res = parity.run_pair(lambda w: scenes.tumbler(w, n=600, half=6.0), steps=40, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+@pytest.mark.parametrize("name", ["pyramid10", "mixed_drop", "joint_grid8", "tumbler300"])
+def test_cuda_matches_committed_golden(name):
+    """The CUDA path against tests/golden/*.npz (bit-exact pair sets, ids, colors, feature ids, events, body states)."""
+    from box2d_b200 import api
+    from test_oracle_golden import check_against_golden
+    w = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        check_against_golden(w, name)
+    finally:
+        w.Destroy()
