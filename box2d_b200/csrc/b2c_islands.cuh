@@ -9,8 +9,8 @@
 
 namespace b2c {
 
-constexpr int kIslandThreads = 256;
-constexpr int kIslandMaxBodies = 256;      // body rows staged in shared memory (8 KB)
+constexpr int kIslandThreads = 192;
+constexpr int kIslandMaxBodies = 192;      // body rows staged in shared memory (8 KB)
 constexpr int kIslandMaxCons = 1024;       // <= kIslandThreads: constraints live in registers; above: re-read per stage
 constexpr int kForceBig = 1 << 20;
 

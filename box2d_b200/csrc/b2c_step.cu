@@ -18,6 +18,7 @@ namespace b2c {
 
 constexpr int kThreads = 256;
 constexpr int kScanChunk = 1024;
+constexpr int kCoopThreads = 512;      // block size of the cooperative phase kernels == chunk of gridScan
 
 __device__ __forceinline__ int gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
 __device__ __forceinline__ int gsize() { return gridDim.x * blockDim.x; }
@@ -34,8 +35,7 @@ __device__ __forceinline__ unsigned hashKey(unsigned long long k) {
 constexpr unsigned long long kEmptyKey = ~0ull;
 
 // ------------------------------------------------------------------------------------------------------------
-// generic chunked exclusive scan: pass 1 scans 1024-element chunks in place and records chunk totals, pass 2 scans the
-// chunk totals; consumers read data[i] + sums[i >> 10].
+// block / grid exclusive scans used by the ordered compactions
 // ------------------------------------------------------------------------------------------------------------
 template <class T> __device__ __forceinline__ T zeroOf();
 template <> __device__ __forceinline__ int zeroOf<int>() { return 0; }
@@ -65,43 +65,43 @@ template <class T> __device__ __forceinline__ T blockInclusive(T v, T* warpSums,
   __syncthreads();
   return v;
 }
-template <class T> __global__ void __launch_bounds__(kScanChunk) k_scan_chunks(T* data, T* sums, const int* nPtr) {
+// grid-wide exclusive scan inside a cooperative kernel (chunk = blockDim.x); consumers read data[i] + sums[i / blockDim.x]
+template <class T> __device__ void gridScan(cg::grid_group& grid, T* data, T* sums, int n, T* totalOut) {
   __shared__ T warpSums[32];
-  int n = *nPtr;
-  int chunks = (n + kScanChunk - 1) / kScanChunk;
+  const int chunk = blockDim.x;
+  int chunks = (n + chunk - 1) / chunk;
   for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
-    int i = c * kScanChunk + threadIdx.x;
+    int i = c * chunk + threadIdx.x;
     T v = i < n ? data[i] : zeroOf<T>();
     T total;
     T inc = blockInclusive(v, warpSums, &total);
     if (i < n) data[i] = addT(inc, make_neg(v));
     if (threadIdx.x == 0) sums[c] = total;
   }
-}
-template <class T> __global__ void __launch_bounds__(kScanChunk) k_scan_sums(T* sums, const int* nPtr, T* totalOut) {
-  __shared__ T warpSums[32];
-  int n = *nPtr;
-  int chunks = (n + kScanChunk - 1) / kScanChunk;
-  T carry = zeroOf<T>();
-  for (int base = 0; base < chunks; base += kScanChunk) {
-    int i = base + threadIdx.x;
-    T v = i < chunks ? sums[i] : zeroOf<T>();
-    T total;
-    T inc = blockInclusive(v, warpSums, &total);
-    if (i < chunks) sums[i] = addT(carry, addT(inc, make_neg(v)));
-    carry = addT(carry, total);
+  grid.sync();
+  if (blockIdx.x == 0) {
+    T carry = zeroOf<T>();
+    for (int base = 0; base < chunks; base += chunk) {
+      int i = base + threadIdx.x;
+      T v = i < chunks ? sums[i] : zeroOf<T>();
+      T total;
+      T inc = blockInclusive(v, warpSums, &total);
+      if (i < chunks) sums[i] = addT(carry, addT(inc, make_neg(v)));
+      carry = addT(carry, total);
+    }
+    if (threadIdx.x == 0) *totalOut = carry;
   }
-  if (threadIdx.x == 0) *totalOut = carry;
+  grid.sync();
 }
 
 // ------------------------------------------------------------------------------------------------------------
 // Phase 0: UpdateBroadPhasePairs (src/BroadPhase.cs:137-268)
 // ------------------------------------------------------------------------------------------------------------
-__global__ void k_pair_insert(WorldDev d) {
+__device__ void p_pair_insert(const WorldDev& d, int tid, int stride) {
   if (d.sc->moveCount == 0) return;
   int n = d.sc->contactNext;
   unsigned mask = (unsigned)d.pairTableSize - 1u;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = tid; i < n; i += stride) {
     if (!(d.cFlags[i] & CF_ALIVE)) continue;
     int2 s = d.cShape[i];
     unsigned long long key = pairKey(s.x, s.y);
@@ -197,9 +197,9 @@ template <bool FILL> __device__ inline int queryTree(const WorldDev& d, int tree
 
 // FindPairsTask (:197-232). FILL=false counts accepted hits per move entry; FILL=true writes them in contact-creation
 // order: move index ascending, within a query the REVERSE of the hit order (the C# result list is LIFO, :193-194,:251-262).
-template <bool FILL> __global__ void __launch_bounds__(kThreads) k_find_pairs(WorldDev d) {
+template <bool FILL> __device__ void p_find_pairs(const WorldDev& d, int tid, int stride) {
   int n = d.sc->moveCount;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = tid; i < n; i += stride) {
     int queryKey = d.moveArray[i];
     int count = 0;
     if (queryKey != -1) {
@@ -208,8 +208,7 @@ template <bool FILL> __global__ void __launch_bounds__(kThreads) k_find_pairs(Wo
       int queryShape = d.trees[type].user[id];
       int2* out = nullptr; int outLast = 0;
       if (FILL) {
-        int begin = d.moveHitCount[i] + d.scanBlockSums[i >> 10];
-        int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) >> 10] : d.sc->newPairCount;
+        int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) / kCoopThreads] : d.sc->newPairCount;
         if (end > d.pairCapacity) { atomicOr(&d.sc->errorFlags, (int)ERR_PAIR_CAPACITY); continue; }
         out = d.movePairs; outLast = end - 1;
       }
@@ -225,10 +224,10 @@ template <bool FILL> __global__ void __launch_bounds__(kThreads) k_find_pairs(Wo
 
 // World.CreateContact (src/Contact.cs:134-227), one thread per new pair in creation order. Ids come from the LIFO pool:
 // the r-th allocation pops freeArray[freeCount-1-r], then extends nextIndex (src/IDPool.cs:15-28).
-__global__ void __launch_bounds__(kThreads) k_create_contacts(WorldDev d) {
+__device__ void p_create_contacts(const WorldDev& d, int tid, int stride) {
   int n = d.sc->newPairCount;
   int freeCount = d.sc->contactFreeCount, next = d.sc->contactNext;
-  for (int r = gtid(); r < n; r += gsize()) {
+  for (int r = tid; r < n; r += stride) {
     int id = r < freeCount ? d.contactFree[freeCount - 1 - r] : next + (r - freeCount);
     if (id >= d.contactCapacity) { atomicOr(&d.sc->errorFlags, (int)ERR_CONTACT_CAPACITY); continue; }
     int2 p = d.movePairs[r];
@@ -237,7 +236,7 @@ __global__ void __launch_bounds__(kThreads) k_create_contacts(WorldDev d) {
     const ShapeDev& sa = d.shapes[a]; const ShapeDev& sb = d.shapes[b];
     uint32_t flags = CF_ALIVE;
     if ((sa.flags | sb.flags) & SF_CONTACT_EVENTS) flags |= CF_ENABLE_CONTACT_EVENTS;
-    if ((sa.flags | sb.flags) & SF_HIT_EVENTS) flags |= CF_SHAPE_HIT;
+    if ((sa.flags | sb.flags) & SF_HIT_EVENTS) { flags |= CF_SHAPE_HIT; d.sc->anyHitShapes = 1; }
     d.cShape[id] = make_int2(a, b);
     d.cBody[id] = make_int2(sa.bodyId, sb.bodyId);
     d.cFlags[id] = flags;
@@ -252,14 +251,14 @@ __global__ void __launch_bounds__(kThreads) k_create_contacts(WorldDev d) {
     d.mN[id] = z; d.mA0[id] = z; d.mA1[id] = z; d.mB0[id] = z; d.mB1[id] = z; d.mC0[id] = z; d.mC1[id] = z;
   }
 }
-__global__ void __launch_bounds__(kThreads) k_clear_moved(WorldDev d) {
+__device__ void p_clear_moved(const WorldDev& d, int tid, int stride) {
   int n = d.sc->moveCount;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = tid; i < n; i += stride) {
     int key = d.moveArray[i];
     if (key != -1) d.trees[key & 3].moved[key >> 2] = 0;
   }
 }
-__global__ void k_pairs_finish(WorldDev d) {
+__device__ void p_pairs_finish(const WorldDev& d) {
   Scalars& s = *d.sc;
   int n = s.newPairCount;
   int fromFree = n < s.contactFreeCount ? n : s.contactFreeCount;
@@ -326,9 +325,7 @@ __device__ __forceinline__ void refitFromChildren(const TreeDev& t, int node) {
   t.hf[node] = (t.hf[node] & 0xffff0000u) | (uint32_t)(1 + (h1 > h2 ? h1 : h2));
   t.cat[node] = t.cat[c.x] | t.cat[c.y];
 }
-__global__ void k_tree_rebuild(WorldDev d) {
-  if (threadIdx.x != 0) return;
-  int treeType = blockIdx.x == 0 ? kDynamicBody : kKinematicBody;
+__device__ void p_tree_rebuild(const WorldDev& d, int treeType) {
   const TreeDev& t = d.trees[treeType];
   TreeRef tr{t};
   int proxyCount = t.meta[3];
@@ -417,9 +414,9 @@ __device__ __forceinline__ void storePoint(const MPoint& p, float4* a, float4* b
   *c = make_float4(p.point.x, p.point.y, p.normalVelocity, __uint_as_float((p.id & 0xffffu) | (p.persisted << 16)));
 }
 
-__global__ void __launch_bounds__(kThreads) k_collide(WorldDev d, StepParams sp) {
+__device__ void p_collide(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.sc->contactNext;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = tid; i < n; i += stride) {
     uint32_t flags = d.cFlags[i];
     int4 fs = make_int4(0, 0, 0, 0);
     if (flags & CF_ALIVE) {
@@ -478,19 +475,20 @@ __global__ void __launch_bounds__(kThreads) k_collide(WorldDev d, StepParams sp)
         else if (!touching && wasTouching) { flags |= CF_STOPPED; fs.w = 1; if (events) fs.y = 1; }
       }
       d.cFlags[i] = flags;
+      if (flags & CF_STATE_MASK) d.sc->anyContactFlag = 1;
     }
     d.flagScan[i] = fs;
   }
 }
 
 // Serial pass of World.Collide (:382-450) as ordered compaction: events, id recycling and graph ops in ascending contactId.
-__global__ void __launch_bounds__(kThreads) k_contact_events(WorldDev d, StepParams sp) {
+__device__ void p_contact_events(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.sc->contactNext;
   int freeCount = d.sc->contactFreeCount;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = tid; i < n; i += stride) {
     uint32_t flags = d.cFlags[i];
     if (!(flags & CF_STATE_MASK)) continue;
-    int4 rank = addT(d.flagScan[i], d.scanBlockSums4[i >> 10]);
+    int4 rank = addT(d.flagScan[i], d.scanBlockSums4[i / kCoopThreads]);
     int2 sh = d.cShape[i];
     B2CContactTouchEvent ev = {sh.x, sh.y, i, d.cGen[i]};
     if (flags & CF_DISJOINT) {
@@ -509,7 +507,7 @@ __global__ void __launch_bounds__(kThreads) k_contact_events(WorldDev d, StepPar
     }
   }
 }
-__global__ void k_events_finish(WorldDev d, StepParams sp, int4* totals) {
+__device__ void p_events_finish(const WorldDev& d, const StepParams& sp, int4* totals) {
   Scalars& s = *d.sc;
   int4 t = *totals;
   if (s.contactNext == 0) t = make_int4(0, 0, 0, 0);
@@ -521,7 +519,7 @@ __global__ void k_events_finish(WorldDev d, StepParams sp, int4* totals) {
 
 // AddContactToGraph / RemoveContactFromGraph (src/ConstraintGraph.cs:135-241) in ascending contactId order.
 // An op may run once it is the lowest pending op on both of its dynamic bodies, which yields exactly the sequential result.
-__global__ void __launch_bounds__(1024) k_color_ops(WorldDev d) {
+__device__ void p_color_ops(const WorldDev& d) {
   __shared__ int sRemaining;
   int n = d.sc->opCount;
   if (n == 0) return;
@@ -585,76 +583,6 @@ __global__ void __launch_bounds__(1024) k_color_ops(WorldDev d) {
     __syncthreads();
   }
   if (threadIdx.x == 0) d.sc->colorRounds = rounds;
-}
-
-// ------------------------------------------------------------------------------------------------------------
-// Phase 2a: group touching contacts by color (stable in contactId) — the per-color arrays of GraphColor.contactSims.
-// Rebuilt only on steps where the graph changed.
-// ------------------------------------------------------------------------------------------------------------
-constexpr int kSortChunk = 256;
-__global__ void __launch_bounds__(kSortChunk) k_color_hist(WorldDev d) {
-  if (!d.sc->graphDirty) return;
-  __shared__ int hist[kGraphColorCount];
-  int n = d.sc->contactNext;
-  int chunks = (n + kSortChunk - 1) / kSortChunk;
-  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
-    if (threadIdx.x < kGraphColorCount) hist[threadIdx.x] = 0;
-    __syncthreads();
-    int i = c * kSortChunk + threadIdx.x;
-    if (i < n && (d.cFlags[i] & CF_TOUCHING)) atomicAdd(&hist[d.cColor[i]], 1);
-    __syncthreads();
-    if (threadIdx.x < kGraphColorCount) d.blockHist[c * kGraphColorCount + threadIdx.x] = hist[threadIdx.x];
-    __syncthreads();
-  }
-}
-__global__ void k_color_offsets(WorldDev d) {
-  if (!d.sc->graphDirty) return;
-  __shared__ int counts[kGraphColorCount];
-  int n = d.sc->contactNext;
-  int chunks = (n + kSortChunk - 1) / kSortChunk;
-  int c = threadIdx.x;
-  if (c < kGraphColorCount) {
-    int run = 0;
-    for (int k = 0; k < chunks; k++) { int v = d.blockHist[k * kGraphColorCount + c]; d.blockHist[k * kGraphColorCount + c] = run; run += v; }
-    counts[c] = run;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int start = 0, touching = 0;
-    for (int k = 0; k < kGraphColorCount; k++) {
-      d.sc->colorCount[k] = counts[k]; d.sc->colorStart[k] = start;
-      start += (counts[k] + 31) & ~31;
-      touching += counts[k];
-    }
-    d.sc->constraintTotal = start;
-    d.sc->touchingCount = touching;
-  }
-}
-__global__ void __launch_bounds__(kSortChunk) k_color_scatter(WorldDev d) {
-  if (!d.sc->graphDirty) return;
-  __shared__ int warpHist[kSortChunk / 32][kGraphColorCount];
-  int n = d.sc->contactNext;
-  int chunks = (n + kSortChunk - 1) / kSortChunk;
-  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
-    for (int k = threadIdx.x; k < (kSortChunk / 32) * kGraphColorCount; k += blockDim.x) (&warpHist[0][0])[k] = 0;
-    __syncthreads();
-    int i = c * kSortChunk + threadIdx.x;
-    int color = -1;
-    if (i < n && (d.cFlags[i] & CF_TOUCHING)) color = d.cColor[i];
-    unsigned peers = __match_any_sync(0xffffffffu, color);
-    int rankInWarp = __popc(peers & ((1u << lane) - 1u));
-    if (color >= 0 && rankInWarp == 0) warpHist[warp][color] = __popc(peers);
-    __syncthreads();
-    if (color >= 0) {
-      int before = 0;
-      for (int w = 0; w < warp; w++) before += warpHist[w][color];
-      int t = d.sc->colorStart[color] + d.blockHist[c * kGraphColorCount + color] + before + rankInWarp;
-      d.sContact[t] = i;
-      d.cConstraint[i] = t;
-    } else if (i < n) d.cConstraint[i] = -1;
-    __syncthreads();
-  }
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -1162,9 +1090,9 @@ __device__ inline int countToiCandidates(const WorldDev& d, Box query, int fastS
   return found;
 }
 
-__global__ void __launch_bounds__(kThreads) k_finalize(WorldDev d, StepParams sp) {
+__device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.awakeCount;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = tid; i < n; i += stride) {
     float4 s = d.st0[i], p = d.st1[i], pose = d.simPose[i], loc = d.simLocal[i];
     uint32_t flags = fbits(s.w);
     if (flags & kLockLinearX) s.x = 0.0f;
@@ -1225,6 +1153,7 @@ __global__ void __launch_bounds__(kThreads) k_finalize(WorldDev d, StepParams sp
     }
     d.simFlags[i] = simFlags;
     d.bodyEnlargedCount[i] = enlarged;
+    if (enlarged) atomicAdd(&d.sc->enlargedShapeCount, enlarged);
   }
 }
 
@@ -1239,11 +1168,11 @@ __device__ __forceinline__ void atomicMaxF(float* addr, float v) {
 // Enlarged bodies in ascending sim index, shapes in body list order: BroadPhase.EnlargeProxy + BufferMove (:1202-1233).
 // EnlargeProxy's result (ancestor boxes = union, every ancestor flagged Enlarged) does not depend on the order of the
 // calls, so it is applied with float atomics; the move array order is produced by the prefix sum.
-__global__ void __launch_bounds__(kThreads) k_refit(WorldDev d) {
+__device__ void p_refit(const WorldDev& d, int tid, int stride) {
   int n = d.awakeCount;
-  for (int i = gtid(); i < n; i += gsize()) {
-    int offset = d.bodyEnlargedCount[i] + d.scanBlockSums[i >> 10];
-    int next = (i + 1 < n) ? d.bodyEnlargedCount[i + 1] + d.scanBlockSums[(i + 1) >> 10] : d.sc->moveCount;
+  for (int i = tid; i < n; i += stride) {
+    int offset = d.bodyEnlargedCount[i] + d.scanBlockSums[i / kCoopThreads];
+    int next = (i + 1 < n) ? d.bodyEnlargedCount[i + 1] + d.scanBlockSums[(i + 1) / kCoopThreads] : d.sc->moveCount;
     if (next == offset) continue;
     int bodyId = d.simBodyId[i];
     for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
@@ -1268,9 +1197,9 @@ __global__ void __launch_bounds__(kThreads) k_refit(WorldDev d) {
 }
 
 // contact hit events (src/Solver.cs:1151-1190); order within a step is not defined by this build (appended atomically)
-__global__ void __launch_bounds__(kThreads) k_hit_events(WorldDev d, StepParams sp) {
+__device__ void p_hit_events(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.sc->contactNext;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = tid; i < n; i += stride) {
     uint32_t flags = d.cFlags[i];
     if ((flags & (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) != (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) continue;
     float4 mn = d.mN[i];
@@ -1284,7 +1213,7 @@ __global__ void __launch_bounds__(kThreads) k_hit_events(WorldDev d, StepParams 
     }
   }
 }
-__global__ void k_step_finish(WorldDev d, int newEndIndex) {
+__device__ void p_step_finish(const WorldDev& d, int newEndIndex) {
   Scalars& s = *d.sc;
   s.graphDirty = 0;
   s.stepCount++;
@@ -1292,6 +1221,66 @@ __global__ void k_step_finish(WorldDev d, int newEndIndex) {
   s.endCount[newEndIndex] = 0;                     // api/World.cs:106-108: swap, then clear the buffer the next step appends to
 }
 __global__ void k_zero_step(WorldDev d, int newEndIndex) { Scalars& s = *d.sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; }
+
+// ------------------------------------------------------------------------------------------------------------
+// Fused cooperative phase kernels: one launch per reference phase, grid.sync() between dependent sub-phases, and a
+// uniform early-out when the phase has nothing to do (no moved proxies / no contact state change / no enlarged proxy).
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCoopThreads) k_broadphase(WorldDev d) {      // UpdateBroadPhasePairs + RebuildTrees
+  cg::grid_group grid = cg::this_grid();
+  const int tid = gtid(), stride = gsize();
+  Scalars& s = *d.sc;
+  if (s.moveCount > 0) {
+    for (int i = tid; i < d.pairTableSize; i += stride) d.pairTable[i] = kEmptyKey;
+    grid.sync();
+    p_pair_insert(d, tid, stride);
+    grid.sync();
+    p_find_pairs<false>(d, tid, stride);
+    grid.sync();
+    gridScan<int>(grid, d.moveHitCount, d.scanBlockSums, s.moveCount, &s.newPairCount);
+    p_find_pairs<true>(d, tid, stride);
+    grid.sync();
+    p_create_contacts(d, tid, stride);
+    p_clear_moved(d, tid, stride);
+    grid.sync();
+  } else if (tid == 0) s.newPairCount = 0;
+  if (tid == 0) p_pairs_finish(d);
+  if (threadIdx.x == 0 && blockIdx.x == 1) p_tree_rebuild(d, kDynamicBody);
+  if (threadIdx.x == 0 && blockIdx.x == 2) p_tree_rebuild(d, kKinematicBody);
+}
+
+__global__ void __launch_bounds__(kCoopThreads) k_collide_phase(WorldDev d, StepParams sp) {   // World.Collide
+  cg::grid_group grid = cg::this_grid();
+  const int tid = gtid(), stride = gsize();
+  Scalars& s = *d.sc;
+  p_collide(d, sp, tid, stride);
+  grid.sync();
+  if (s.anyContactFlag == 0) {                    // no begin / end / destroy anywhere: the serial pass is empty
+    if (tid == 0) { s.beginCount = 0; s.endCount[sp.endIndex] = 0; s.opCount = 0; }
+    return;
+  }
+  gridScan<int4>(grid, d.flagScan, d.scanBlockSums4, s.contactNext, d.flagScan + d.contactCapacity);
+  p_contact_events(d, sp, tid, stride);
+  grid.sync();
+  if (tid == 0) { p_events_finish(d, sp, d.flagScan + d.contactCapacity); s.anyContactFlag = 0; }
+  grid.sync();
+  if (blockIdx.x == 0) p_color_ops(d);
+}
+
+__global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, StepParams sp, int newEndIndex) {   // FinalizeBodies + refit
+  cg::grid_group grid = cg::this_grid();
+  const int tid = gtid(), stride = gsize();
+  Scalars& s = *d.sc;
+  p_finalize(d, sp, tid, stride);
+  if (s.anyHitShapes) p_hit_events(d, sp, tid, stride);
+  grid.sync();
+  if (s.enlargedShapeCount > 0) {
+    gridScan<int>(grid, d.bodyEnlargedCount, d.scanBlockSums, d.awakeCount, &s.moveCount);
+    p_refit(d, tid, stride);
+    grid.sync();
+  } else if (tid == 0) s.moveCount = 0;
+  if (tid == 0) { s.enlargedShapeCount = 0; p_step_finish(d, newEndIndex); }
+}
 
 // ------------------------------------------------------------------------------------------------------------
 // host driver
@@ -1328,62 +1317,36 @@ int World::step(float timeStep, int subStepCount) {
   sp.enableSpeculative = enableSpeculative; sp.enableSleep = 0; sp.endIndex = endIndex_;
 
   const int maxBlocks = 148 * 8;
-  const int gMove = gridFor(d.moveCapacity, kThreads, maxBlocks), gContact = gridFor(d.contactCapacity, kThreads, maxBlocks);
-  const int gBody = gridFor(d.awakeCount, kThreads, maxBlocks), gScan = 148 * 2;
-  Scalars* sc = d.sc;
+  const int gContact = gridFor(d.contactCapacity, kThreads, maxBlocks), gBody = gridFor(d.awakeCount, kThreads, maxBlocks);
+  if (coopBlocks_ == 0) {
+    int occ[5] = {0, 0, 0, 0, 0};
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], k_solver, kCoopThreads, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], k_islands, kCoopThreads, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[2], k_broadphase, kCoopThreads, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[3], k_collide_phase, kCoopThreads, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[4], k_finalize_phase, kCoopThreads, 0));
+    for (int o : occ) if (o < 1) return fail(B2C_E_CUDA, "a cooperative phase kernel cannot be made resident");
+    cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device_));
+    coopBlocks_ = prop.multiProcessorCount;       // one 512-thread CTA per SM: the barrier cost grows with CTA count
+    if (coopBlocks_ < 3) return fail(B2C_E_CUDA, "device too small");
+  }
+  const dim3 cgrid(coopBlocks_), cblock(kCoopThreads);
   cudaEvent_t* pe = ev_ + (profHead_ % kProfRing) * kProfEvents;
   cudaEventRecord(pe[0], stream_);
-  // --- UpdateBroadPhasePairs ---
-  CK(cudaMemsetAsync(d.pairTable, 0xff, sizeof(unsigned long long) * (size_t)d.pairTableSize, stream_));
-  k_pair_insert<<<gContact, kThreads, 0, stream_>>>(d);
-  k_find_pairs<false><<<gMove, kThreads, 0, stream_>>>(d);
-  k_scan_chunks<int><<<gScan, kScanChunk, 0, stream_>>>(d.moveHitCount, d.scanBlockSums, &sc->moveCount);
-  k_scan_sums<int><<<1, kScanChunk, 0, stream_>>>(d.scanBlockSums, &sc->moveCount, &sc->newPairCount);
-  k_find_pairs<true><<<gMove, kThreads, 0, stream_>>>(d);
-  k_create_contacts<<<gContact, kThreads, 0, stream_>>>(d);
-  k_clear_moved<<<gMove, kThreads, 0, stream_>>>(d);
-  k_pairs_finish<<<1, 1, 0, stream_>>>(d);
+  { void* args[] = {(void*)&d}; CK(cudaLaunchCooperativeKernel((void*)k_broadphase, cgrid, cblock, args, 0, stream_)); }
   cudaEventRecord(pe[1], stream_);
-  // --- Collide ---
-  k_tree_rebuild<<<2, 32, 0, stream_>>>(d);
-  k_collide<<<gContact, kThreads, 0, stream_>>>(d, sp);
-  k_scan_chunks<int4><<<gScan, kScanChunk, 0, stream_>>>(d.flagScan, d.scanBlockSums4, &sc->contactNext);
-  k_scan_sums<int4><<<1, kScanChunk, 0, stream_>>>(d.scanBlockSums4, &sc->contactNext, d.flagScan + d.contactCapacity);
-  k_contact_events<<<gContact, kThreads, 0, stream_>>>(d, sp);
-  k_events_finish<<<1, 1, 0, stream_>>>(d, sp, d.flagScan + d.contactCapacity);
-  k_color_ops<<<1, 1024, 0, stream_>>>(d);
+  { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_collide_phase, cgrid, cblock, args, 0, stream_)); }
   cudaEventRecord(pe[2], stream_);
-  // --- Solve ---
-  if (coopBlocks_ == 0) {
-    int perSm = 0, perSm2 = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_solver, 512, 0));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm2, k_islands, 512, 0));
-    cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device_));
-    if (perSm < 1 || perSm2 < 1) return fail(B2C_E_CUDA, "cooperative kernels cannot be made resident");
-    coopBlocks_ = prop.multiProcessorCount;       // one 512-thread CTA per SM: the barrier cost grows with CTA count
-  }
-  {
-    void* args[] = {(void*)&d};
-    CK(cudaLaunchCooperativeKernel((void*)k_islands, dim3(coopBlocks_), dim3(512), args, 0, stream_));
-  }
+  { void* args[] = {(void*)&d}; CK(cudaLaunchCooperativeKernel((void*)k_islands, cgrid, cblock, args, 0, stream_)); }
   k_prepare<<<gContact, kThreads, 0, stream_>>>(d, sp);
   cudaEventRecord(pe[3], stream_);
-  {
-    void* args[] = {(void*)&d, (void*)&sp};
-    CK(cudaLaunchCooperativeKernel((void*)k_solver, dim3(coopBlocks_), dim3(512), args, 0, stream_));
-  }
+  { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_solver, cgrid, cblock, args, 0, stream_)); }
   k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp);
   k_free_bodies<<<gBody, kThreads, 0, stream_>>>(d, sp);
   cudaEventRecord(pe[4], stream_);
-  // --- Finalize + refit ---
-  k_finalize<<<gBody, kThreads, 0, stream_>>>(d, sp);
-  k_scan_chunks<int><<<gScan, kScanChunk, 0, stream_>>>(d.bodyEnlargedCount, d.scanBlockSums, &sc->awakeCount);
-  k_scan_sums<int><<<1, kScanChunk, 0, stream_>>>(d.scanBlockSums, &sc->awakeCount, &sc->moveCount);
-  k_refit<<<gBody, kThreads, 0, stream_>>>(d);
-  k_hit_events<<<gContact, kThreads, 0, stream_>>>(d, sp);
   lastEndIndex_ = endIndex_;
   endIndex_ = 1 - endIndex_;
-  k_step_finish<<<1, 1, 0, stream_>>>(d, endIndex_);
+  { void* args[] = {(void*)&d, (void*)&sp, (void*)&endIndex_}; CK(cudaLaunchCooperativeKernel((void*)k_finalize_phase, cgrid, cblock, args, 0, stream_)); }
   cudaEventRecord(pe[5], stream_);
   profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
   CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));

@@ -68,7 +68,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int constraintTotal, graphDirty, opCount, enlargedShapeCount;
   int errorFlags, toiCandidates, jointEventCount, stepCount;
   int touchingCount, liveContactCount, rebuildLeafCount[3], colorRounds;
-  int awakeCount, anyRestitution;
+  int awakeCount, anyRestitution, anyContactFlag, anyHitShapes;
   int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
   int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
 };
