@@ -237,6 +237,13 @@ class World:
                 return np.frombuffer(buf, dtype=np.dtype(ty), count=n.value).copy()
             cap = n.value
 
+    def GetBodyEvents(self, copy=True):
+        """WorldAPI.GetBodyEvents: one record per body id. copy=False returns a view of the library's pinned buffer (valid until the next Step)."""
+        p, n = C.POINTER(BodyRead)(), C.c_int32()
+        self._check(self.fns["world_get_body_events"](self.handle, C.byref(p), C.byref(n)))
+        arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value * C.sizeof(BodyRead),)).view(np.dtype(BodyRead))
+        return arr.copy() if copy else arr
+
     def ReadBodies(self):
         return self._read("world_read_bodies", BodyRead, self.GetCounters().bodyCount + 16)
 

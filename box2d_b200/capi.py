@@ -134,6 +134,7 @@ PROTOS = {
                                  C.POINTER(C.POINTER(ContactTouchEvent)), C.POINTER(C.c_int32),
                                  C.POINTER(C.POINTER(ContactHitEvent)), C.POINTER(C.c_int32)],
     "world_get_joint_events": [_W, C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32)],
+    "world_get_body_events": [_W, C.POINTER(C.POINTER(BodyRead)), C.POINTER(C.c_int32)],
     "world_read_bodies": [_W, C.POINTER(BodyRead), C.c_int32, C.POINTER(C.c_int32)],
     "world_read_contacts": [_W, C.POINTER(ContactRead), C.c_int32, C.POINTER(C.c_int32)],
     "world_read_joints": [_W, C.POINTER(JointRead), C.c_int32, C.POINTER(C.c_int32)],

@@ -105,6 +105,8 @@ void World::freeDevice() {
   if (hEnd_) cudaFreeHost(hEnd_);
   if (hHit_) cudaFreeHost(hHit_);
   if (hJointEvents_) cudaFreeHost(hJointEvents_);
+  if (hBodyRead_) cudaFreeHost(hBodyRead_);
+  hBodyRead_ = nullptr;
   hostScalars_ = nullptr; hBegin_ = hEnd_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
   for (auto& e : ev_) if (e) { cudaEventDestroy(e); e = nullptr; }
   for (auto& e : timer_) if (e) { cudaEventDestroy(e); e = nullptr; }
@@ -439,6 +441,8 @@ int World::upload() {
   CK(cudaHostAlloc((void**)&hBegin_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&hEnd_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&hHit_, sizeof(B2CContactHitEvent) * d.eventCapacity, cudaHostAllocDefault));
+  DA(dBodyRead_, B2CBodyRead, nBody);
+  CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(nBody, 1), cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(nJoint, 1), cudaHostAllocDefault));
   CK(cudaStreamSynchronize(stream_));
   onDevice_ = true;

@@ -81,6 +81,7 @@ class World {
   int step(float dt, int subSteps);
   int synchronize();
   int readBodies(B2CBodyRead* dst, int capacity, int* count);
+  int getBodyEvents(const B2CBodyRead** records, int* count);
   int readContacts(B2CContactRead* dst, int capacity, int* count);
   int readJoints(B2CJointRead* dst, int capacity, int* count);
   int readShapes(B2CShapeRead* dst, int capacity, int* count);
@@ -136,6 +137,7 @@ class World {
   B2CProfile profile_{};
   bool profileValid_ = false;
   int coopBlocks_ = 0;
+  B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false;
   friend struct StepLauncher;
 };
 

@@ -205,12 +205,21 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
   __syncthreads();
   const int K = colorOff[kGraphColorCount];
   BodyRows bs{s0, s1};
-  // register-resident constraint (CACHED): thread t owns constraint cBegin + t for the whole step
-  Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int2 loc = make_int2(-1, -1); int myColor = -1;
-  if (CACHED && tid < K) {
-    loadLane(d, cBegin + tid, c, false); I = d.sI[cBegin + tid]; J = d.sJ[cBegin + tid]; loc = d.sLocal[cBegin + tid];
-    for (int k = 0; k < kOverflowIndex; k++) if (tid >= colorOff[k] && tid < colorOff[k + 1]) myColor = k;
+  // PrepareContacts for this island: lanes are built straight into registers (CACHED) or into the planes (large islands).
+  // Velocities read here are the pre-step ones: nothing has integrated yet.
+  Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int2 loc = make_int2(-1, -1); int myColor = -1, myContact = -1;
+  bool anyRest = false;
+  if (CACHED) {
+    if (tid < K) {
+      myContact = d.sContact[cBegin + tid];
+      computeLane(d, sp, myContact, c, I, J); loc = d.sLocal[cBegin + tid];
+      anyRest = !(c.restitution == 0.0f);
+      for (int k = 0; k < kOverflowIndex; k++) if (tid >= colorOff[k] && tid < colorOff[k + 1]) myColor = k;
+    }
+  } else {
+    for (int t = tid; t < K; t += T) { Lane l; float4 li, lj; computeLane(d, sp, d.sContact[cBegin + t], l, li, lj); writeLane(d, cBegin + t, l, li, lj); anyRest |= !(l.restitution == 0.0f); }
   }
+  const bool islandRestitution = __syncthreads_or(anyRest);
   for (int sub = 0; sub < sp.subStepCount; sub++) {
     if (tid < nb) s0[tid] = integrateVelocityRow(s0[tid], m, f, sp, &sf);
     __syncthreads();
@@ -241,8 +250,8 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
       __syncthreads();
     }
   }
-  if (CACHED && tid < K) { d.sI[cBegin + tid] = I; d.sJ[cBegin + tid] = J; }
-  if (d.sc->anyRestitution) {                     // ApplyRestitution per color, 8-lane groups in this island's order
+  if (islandRestitution) {
+    if (CACHED && tid < K) writeLane(d, cBegin + tid, c, I, J);                     // ApplyRestitution per color, 8-lane groups in this island's order
     __syncthreads();
     for (int k = 0; k < kOverflowIndex; k++) {
       if (colorOff[k] == colorOff[k + 1]) continue;
@@ -259,11 +268,12 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
   }
   __syncthreads();
   if (tid < nb) { d.st0[sim] = s0[tid]; d.st1[sim] = s1[tid]; if (sf != sf0) d.simFlags[sim] = sf; }
-  for (int t = tid; t < K; t += T) storeImpulses(d, cBegin + t);
+  if (CACHED && !islandRestitution) { if (tid < K) storeImpulsesRegs(d, myContact, I, J, c.relVel1, c.relVel2); }
+  else for (int t = tid; t < K; t += T) storeImpulses(d, cBegin + t);
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(kIslandThreads) k_solver_islands(WorldDev d, StepParams sp) {
+__global__ void __launch_bounds__(kIslandThreads, 3) k_solver_islands(WorldDev d, StepParams sp) {
   __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
   __shared__ int colorOff[kGraphColorCount + 1];
   int n = d.sc->islandCount;

@@ -637,9 +637,8 @@ __device__ __forceinline__ void applyP(BodyW& bA, BodyW& bB, const Lane& c, V2 r
   bB.w = bB.w + c.iB * (rB.x * Py - rB.y * Px);
 }
 
-// PrepareContactsTask :480-685
-__device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
-  int ci = d.sContact[t];
+// PrepareContactsTask :480-685 — builds one constraint lane (registers) from the contact slot `ci`
+__device__ __forceinline__ void computeLane(const WorldDev& d, const StepParams& sp, int ci, Lane& c, float4& I, float4& J) {
   float warmStartScale = sp.enableWarmStarting ? 1.0f : 0.0f;
   int2 idx = d.cSim[ci];
   float4 mass = d.cMass[ci];
@@ -648,7 +647,6 @@ __device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
   if (idx.x != -1) { float4 s = d.st0[idx.x]; vA = mk(s.x, s.y); wA = s.z; }
   if (idx.y != -1) { float4 s = d.st0[idx.y]; vB = mk(s.x, s.y); wB = s.z; }
   float k = iA + iB;
-  float rollingMass = k > 0.0f ? 1.0f / k : 0.0f;
   Softness soft = sp.contactSoftness;
   if (idx.x == -1 || idx.y == -1) soft = sp.staticSoftness;
   else if (sp.enableContactSoftening) {
@@ -661,44 +659,59 @@ __device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
   V2 normal = mk(mn.x, mn.y);
   int pointCount = (int)fbits(mn.w);
   V2 tangent = rightPerp(normal);
-  d.sA[t] = make_float4(__int_as_float(idx.x), __int_as_float(idx.y), mA, mB);
-  d.sB[t] = make_float4(iA, iB, normal.x, normal.y);
-  d.sC[t] = make_float4(mat.x, mat.w, mat.z, rollingMass);
-  d.sD[t] = make_float4(soft.biasRate, soft.massScale, soft.impulseScale, mat.y);
-  float4 E, F = make_float4(0, 0, 0, 0), G = make_float4(0, 0, 0, 0), H = make_float4(0, 0, 0, 0), I = make_float4(0, 0, 0, 0);
+  c.indexA = idx.x; c.indexB = idx.y; c.mA = mA; c.mB = mB; c.iA = iA; c.iB = iB; c.n = normal;
+  c.friction = mat.x; c.tangentSpeed = mat.w; c.rollingResistance = mat.z; c.rollingMass = k > 0.0f ? 1.0f / k : 0.0f;
+  c.biasRate = soft.biasRate; c.massScale = soft.massScale; c.impulseScale = soft.impulseScale; c.restitution = mat.y;
+  c.rA2 = mk(0, 0); c.rB2 = mk(0, 0); c.normalMass2 = 0; c.tangentMass2 = 0; c.baseSep2 = 0; c.relVel2 = 0;
+  I = make_float4(0, 0, 0, 0);
   {
     float4 a = d.mA0[ci], b = d.mB0[ci];
     V2 rA = mk(a.x, a.y), rB = mk(a.z, a.w);
-    E = a;
-    H.x = b.x - dot(rB - rA, normal);
+    c.rA1 = rA; c.rB1 = rB;
+    c.baseSep1 = b.x - dot(rB - rA, normal);
     I.x = warmStartScale * b.y; I.y = warmStartScale * b.z;
     float rnA = cross(rA, normal), rnB = cross(rB, normal);
     float kNormal = mA + mB + iA * rnA * rnA + iB * rnB * rnB;
-    G.x = kNormal > 0.0f ? 1.0f / kNormal : 0.0f;
+    c.normalMass1 = kNormal > 0.0f ? 1.0f / kNormal : 0.0f;
     float rtA = cross(rA, tangent), rtB = cross(rB, tangent);
     float kTangent = mA + mB + iA * rtA * rtA + iB * rtB * rtB;
-    G.y = kTangent > 0.0f ? 1.0f / kTangent : 0.0f;
+    c.tangentMass1 = kTangent > 0.0f ? 1.0f / kTangent : 0.0f;
     V2 vrA = vA + crossSV(wA, rA), vrB = vB + crossSV(wB, rB);
-    H.z = dot(normal, vrB - vrA);
+    c.relVel1 = dot(normal, vrB - vrA);
   }
   if (pointCount == 2) {
     float4 a = d.mA1[ci], b = d.mB1[ci];
     V2 rA = mk(a.x, a.y), rB = mk(a.z, a.w);
-    F = a;
-    H.y = b.x - dot(rB - rA, normal);
+    c.rA2 = rA; c.rB2 = rB;
+    c.baseSep2 = b.x - dot(rB - rA, normal);
     I.z = warmStartScale * b.y; I.w = warmStartScale * b.z;
     float rnA = cross(rA, normal), rnB = cross(rB, normal);
     float kNormal = mA + mB + iA * rnA * rnA + iB * rnB * rnB;
-    G.z = kNormal > 0.0f ? 1.0f / kNormal : 0.0f;
+    c.normalMass2 = kNormal > 0.0f ? 1.0f / kNormal : 0.0f;
     float rtA = cross(rA, tangent), rtB = cross(rB, tangent);
     float kTangent = mA + mB + iA * rtA * rtA + iB * rtB * rtB;
-    G.w = kTangent > 0.0f ? 1.0f / kTangent : 0.0f;
+    c.tangentMass2 = kTangent > 0.0f ? 1.0f / kTangent : 0.0f;
     V2 vrA = vA + crossSV(wA, rA), vrB = vB + crossSV(wB, rB);
-    H.w = dot(normal, vrB - vrA);
+    c.relVel2 = dot(normal, vrB - vrA);
   }
-  d.sE[t] = E; d.sF[t] = F; d.sG[t] = G; d.sH[t] = H; d.sI[t] = I;
-  d.sJ[t] = make_float4(0.0f, 0.0f, warmStartScale * mn.z, 0.0f);
-  if (!(mat.y == 0.0f)) d.sc->anyRestitution = 1;
+  J = make_float4(0.0f, 0.0f, warmStartScale * mn.z, 0.0f);
+}
+__device__ __forceinline__ void writeLane(const WorldDev& d, int t, const Lane& c, float4 I, float4 J) {
+  d.sA[t] = make_float4(__int_as_float(c.indexA), __int_as_float(c.indexB), c.mA, c.mB);
+  d.sB[t] = make_float4(c.iA, c.iB, c.n.x, c.n.y);
+  d.sC[t] = make_float4(c.friction, c.tangentSpeed, c.rollingResistance, c.rollingMass);
+  d.sD[t] = make_float4(c.biasRate, c.massScale, c.impulseScale, c.restitution);
+  d.sE[t] = make_float4(c.rA1.x, c.rA1.y, c.rB1.x, c.rB1.y);
+  d.sF[t] = make_float4(c.rA2.x, c.rA2.y, c.rB2.x, c.rB2.y);
+  d.sG[t] = make_float4(c.normalMass1, c.tangentMass1, c.normalMass2, c.tangentMass2);
+  d.sH[t] = make_float4(c.baseSep1, c.baseSep2, c.relVel1, c.relVel2);
+  d.sI[t] = I; d.sJ[t] = J;
+}
+__device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
+  Lane c; float4 I, J;
+  computeLane(d, sp, d.sContact[t], c, I, J);
+  writeLane(d, t, c, I, J);
+  if (!(c.restitution == 0.0f)) d.sc->anyRestitution = 1;
 }
 
 // WarmStartContactsTask :686-744
@@ -842,6 +855,14 @@ __device__ __forceinline__ void storeImpulses(const WorldDev& d, int t) {
   b0.y = I.x; b0.z = I.y; b0.w = J.x; b1.y = I.z; b1.z = I.w; b1.w = J.y;
   d.mB0[ci] = b0; d.mB1[ci] = b1;
   d.mC0[ci].z = H.z; d.mC1[ci].z = H.w;
+}
+
+__device__ __forceinline__ void storeImpulsesRegs(const WorldDev& d, int ci, float4 I, float4 J, float relVel1, float relVel2) {
+  d.mN[ci].z = J.z;
+  float4 b0 = d.mB0[ci], b1 = d.mB1[ci];
+  b0.y = I.x; b0.z = I.y; b0.w = J.x; b1.y = I.z; b1.z = I.w; b1.w = J.y;
+  d.mB0[ci] = b0; d.mB1[ci] = b1;
+  d.mC0[ci].z = relVel1; d.mC1[ci].z = relVel2;
 }
 
 // ---- revolute joint (src/Joint.cs:125-130, src/joints/RevoluteJoint.cs:72-235) ----
@@ -1004,7 +1025,7 @@ __device__ __forceinline__ void integratePosition(const WorldDev& d, const StepP
 
 __global__ void __launch_bounds__(kThreads) k_prepare(WorldDev d, StepParams sp) {
   const Scalars& s = *d.sc;
-  int total = s.constraintTotal;
+  int total = s.smallConStart;                    // grid-path constraints only: small islands prepare their own lanes in registers
   for (int t = gtid(); t < total; t += gsize()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
   int nj = d.jointColorStart[kGraphColorCount];
   for (int k = gtid(); k < nj; k += gsize()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
@@ -1282,6 +1303,19 @@ __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, Ste
   if (tid == 0) { s.enlargedShapeCount = 0; p_step_finish(d, newEndIndex); }
 }
 
+// bodyMoveEvents equivalent: one packed record per body id (src/Solver.cs:432-438)
+__global__ void __launch_bounds__(kThreads) k_pack_bodies(WorldDev d, B2CBodyRead* out) {
+  for (int i = gtid(); i < d.bodyCapacity; i += gsize()) {
+    float4 xf = d.bodyXf[i]; float2 c = d.bodyCenter[i];
+    B2CBodyRead r;
+    r.transform.p = {xf.x, xf.y}; r.transform.q = {xf.z, xf.w}; r.center = {c.x, c.y};
+    int sim = d.bodySim[i];
+    if (sim >= 0) { float4 s = d.st0[sim]; r.linearVelocity = {s.x, s.y}; r.angularVelocity = s.z; r.flags = d.simFlags[sim]; }
+    else { r.linearVelocity = {0.0f, 0.0f}; r.angularVelocity = 0.0f; r.flags = d.bodyFlags[i]; }
+    out[i] = r;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // host driver
 // ------------------------------------------------------------------------------------------------------------
@@ -1296,7 +1330,7 @@ int World::step(float timeStep, int subStepCount) {
   if (!onDevice_) { int rc = upload(); if (rc) return rc; }
   CK(cudaSetDevice(device_));
   WorldDev& d = d_;
-  eventsFetched_ = false;
+  eventsFetched_ = false; bodiesFetched_ = false;
   if (timeStep == 0.0f) {                          // api/World.cs:44-51
     lastEndIndex_ = endIndex_;
     endIndex_ = 1 - endIndex_;
@@ -1352,6 +1386,21 @@ int World::step(float timeStep, int subStepCount) {
   CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
   CK(cudaGetLastError());
   stepCount_++;
+  return B2C_OK;
+}
+
+int World::getBodyEvents(const B2CBodyRead** records, int* count) {
+  *records = nullptr; *count = 0;
+  if (!onDevice_) return fail(B2C_E_INVALID, "get_body_events before the first step");
+  CK(cudaSetDevice(device_));
+  if (!bodiesFetched_) {
+    int n = d_.bodyCapacity;
+    k_pack_bodies<<<gridFor(n, kThreads, 148 * 8), kThreads, 0, stream_>>>(d_, dBodyRead_);
+    CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
+    bodiesFetched_ = true;
+  }
+  int rc = synchronize(); if (rc) return rc;
+  *records = hBodyRead_; *count = d_.bodyCapacity;
   return B2C_OK;
 }
 

@@ -157,6 +157,9 @@ int32_t b2cuda_world_get_contact_events(B2CWorld* world, const B2CContactTouchEv
 int32_t b2cuda_world_get_joint_events(B2CWorld* world, const int32_t** jointIds, int32_t* count);
 /* WorldAPI.GetBodyEvents / BodyAPI getters in bulk: record i = bodyId i (free slots zeroed) */
 int32_t b2cuda_world_read_bodies(B2CWorld* world, B2CBodyRead* dst, int32_t capacity, int32_t* count);
+/* WorldAPI.GetBodyEvents — api/World.cs:283-290 (bodyMoveEvents, src/Solver.cs:432-438): one record per body id, packed on the
+ * device and copied once into library-owned pinned host memory; the pointer is valid until the next step ("transient"). */
+int32_t b2cuda_world_get_body_events(B2CWorld* world, const B2CBodyRead** records, int32_t* count);
 /* ContactAPI.GetData for every live contact in ascending contactId */
 int32_t b2cuda_world_read_contacts(B2CWorld* world, B2CContactRead* dst, int32_t capacity, int32_t* count);
 int32_t b2cuda_world_read_joints(B2CWorld* world, B2CJointRead* dst, int32_t capacity, int32_t* count);

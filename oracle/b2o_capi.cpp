@@ -99,6 +99,14 @@ int32_t b2o_world_read_bodies(World* w, B2CBodyRead* dst, int32_t capacity, int3
   }
   return 0;
 }
+static thread_local std::vector<B2CBodyRead> tBodies;
+int32_t b2o_world_get_body_events(World* w, const B2CBodyRead** records, int32_t* count) {
+  int n = (int)w->bodies.size();
+  tBodies.resize(n);
+  b2o_world_read_bodies(w, tBodies.data(), n, count);
+  *records = tBodies.data();
+  return 0;
+}
 static void FillPoint(B2CManifoldPointRead& o, const ManifoldPoint& p) {
   o.point = CV(p.point); o.anchorA = CV(p.anchorA); o.anchorB = CV(p.anchorB); o.separation = p.separation; o.normalImpulse = p.normalImpulse;
   o.tangentImpulse = p.tangentImpulse; o.totalNormalImpulse = p.totalNormalImpulse; o.normalVelocity = p.normalVelocity; o.id = p.id; o.persisted = p.persisted;
