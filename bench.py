@@ -104,7 +104,7 @@ def reference_arm(args, rank):
     print(json.dumps(line), flush=True)
 
 
-KERNELS_PER_STEP = 8    # k_broadphase, k_collide_phase, k_islands, k_prepare, k_solver, k_solver_islands, k_free_bodies, k_finalize_phase
+KERNELS_PER_STEP = 3    # k_step_front (cooperative), k_solver_islands, k_finalize_phase (cooperative)
 
 
 def b200_arm(args, rank, world_size, local_rank):

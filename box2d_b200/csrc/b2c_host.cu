@@ -687,22 +687,26 @@ int World::getJointEvents(const int** ids, int* count) {
   return B2C_OK;
 }
 
-int World::getProfile(B2CProfile* out) {       // averages over the steps since the previous call (at most kProfRing)
+int World::getProfile(B2CProfile* out) {       // averages over the steps since the previous call (events: at most kProfRing steps)
   memset(out, 0, sizeof(*out));
   if (!onDevice_ || profCount_ == 0) return B2C_OK;
   int rc = synchronize(); if (rc) return rc;
   int n = profCount_ < kProfRing ? profCount_ : kProfRing;
-  double acc[6] = {0, 0, 0, 0, 0, 0};
+  double acc[4] = {0, 0, 0, 0};
   for (int k = 0; k < n; k++) {
     int slot = (profHead_ - 1 - k + 2 * kProfRing) % kProfRing;
     cudaEvent_t* e = ev_ + slot * kProfEvents;
     float ms;
-    for (int j = 0; j < 5; j++) { cudaEventElapsedTime(&ms, e[j], e[j + 1]); acc[j] += ms; }
-    cudaEventElapsedTime(&ms, e[0], e[5]); acc[5] += ms;
+    for (int j = 0; j < 3; j++) { cudaEventElapsedTime(&ms, e[j], e[j + 1]); acc[j] += ms; }
+    cudaEventElapsedTime(&ms, e[0], e[3]); acc[3] += ms;
   }
-  out->pairs = (float)(acc[0] / n); out->collide = (float)(acc[1] / n); out->prepareConstraints = (float)(acc[2] / n);
-  out->solveConstraints = (float)(acc[3] / n); out->transforms = (float)(acc[4] / n); out->refit = out->transforms;
-  out->solve = (float)((acc[2] + acc[3] + acc[4]) / n); out->step = (float)(acc[5] / n);
+  // sub-phases of the fused front kernel: %globaltimer sums kept on the device (ns), differenced against the previous call
+  double ph[4];
+  for (int k = 0; k < 4; k++) { ph[k] = (double)(hostScalars_->phaseAcc[k] - lastPhaseAcc_[k]) * 1e-6 / profCount_; lastPhaseAcc_[k] = hostScalars_->phaseAcc[k]; }
+  out->pairs = (float)ph[0]; out->collide = (float)ph[1]; out->prepareConstraints = (float)ph[2];
+  out->solveConstraints = (float)(ph[3] + acc[1] / n);          // grid-path solver + island solver kernel
+  out->transforms = (float)(acc[2] / n); out->refit = out->transforms;
+  out->solve = out->prepareConstraints + out->solveConstraints + out->transforms; out->step = (float)(acc[3] / n);
   profCount_ = 0;
   return B2C_OK;
 }

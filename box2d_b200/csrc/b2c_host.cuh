@@ -134,6 +134,7 @@ class World {
   cudaEvent_t ev_[kProfRing * kProfEvents] = {};
   cudaEvent_t timer_[2] = {};
   int profHead_ = 0, profCount_ = 0;
+  unsigned long long lastPhaseAcc_[4] = {0, 0, 0, 0};
   B2CProfile profile_{};
   bool profileValid_ = false;
   int coopBlocks_ = 0;

@@ -62,10 +62,9 @@ __device__ void gridScan4(cg::grid_group& grid, int4* data, int4* sums, int n, i
 // Rebuilds the island partition and the constraint order [grid-path colors | island 0 | island 1 | ...] when the graph
 // changed this step; a no-op (one uniform branch) otherwise. Order inside one (group, color) bucket is arbitrary:
 // constraints of one color never share a writable body, so it does not influence any result.
-__global__ void __launch_bounds__(512) k_islands(WorldDev d) {
+__device__ void phase_islands(cg::grid_group& grid, const WorldDev& d) {
   Scalars& s = *d.sc;
   if (!s.graphDirty) return;
-  cg::grid_group grid = cg::this_grid();
   const int tid = gtid(), stride = gsize();
   const int awake = d.awakeCount, nContacts = s.contactNext, nJoints = d.jointColorStart[kGraphColorCount];
   __shared__ int hist[kGraphColorCount];
@@ -182,9 +181,9 @@ __global__ void __launch_bounds__(512) k_islands(WorldDev d) {
 
 
 // Bodies that no constraint touches: the four substeps are a private loop (IntegrateVelocities + IntegratePositions).
-__global__ void __launch_bounds__(kThreads) k_free_bodies(WorldDev d, StepParams sp) {
+__device__ void freeBodies(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.sc->freeBodyCount;
-  for (int k = gtid(); k < n; k += gsize()) {
+  for (int k = tid; k < n; k += stride) {
     int i = d.freeBodies[k];
     float4 s0 = d.st0[i], s1 = d.st1[i], m = d.simMass[i], f = d.simForce[i];
     uint32_t sf = d.simFlags[i], sf0 = sf;
@@ -282,6 +281,7 @@ __global__ void __launch_bounds__(kIslandThreads, 3) k_solver_islands(WorldDev d
     if (K <= (int)blockDim.x) runIsland<true>(d, sp, g, s0, s1, colorOff);
     else runIsland<false>(d, sp, g, s0, s1, colorOff);
   }
+  freeBodies(d, sp, gtid(), gsize());
 }
 
 }  // namespace b2c

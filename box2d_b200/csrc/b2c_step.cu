@@ -1023,7 +1023,7 @@ __device__ __forceinline__ void integratePosition(const WorldDev& d, const StepP
   d.st1[i] = p;
 }
 
-__global__ void __launch_bounds__(kThreads) k_prepare(WorldDev d, StepParams sp) {
+__device__ void phase_prepare(const WorldDev& d, const StepParams& sp) {
   const Scalars& s = *d.sc;
   int total = s.smallConStart;                    // grid-path constraints only: small islands prepare their own lanes in registers
   for (int t = gtid(); t < total; t += gsize()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
@@ -1033,8 +1033,7 @@ __global__ void __launch_bounds__(kThreads) k_prepare(WorldDev d, StepParams sp)
 
 // SolverTask substep loop (src/Solver.cs:599-727) as one persistent cooperative kernel: a grid-wide barrier replaces the
 // reference's per-stage spin barrier; empty colors cost nothing.
-__global__ void __launch_bounds__(512) k_solver(WorldDev d, StepParams sp) {
-  cg::grid_group grid = cg::this_grid();
+__device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {
   const Scalars& s = *d.sc;
   __shared__ int sBegin[kGraphColorCount], sEnd[kGraphColorCount], sJBegin[kGraphColorCount], sJEnd[kGraphColorCount], sActive[kGraphColorCount], sActiveCount;
   if (threadIdx.x == 0) {
@@ -1247,8 +1246,7 @@ __global__ void k_zero_step(WorldDev d, int newEndIndex) { Scalars& s = *d.sc; s
 // Fused cooperative phase kernels: one launch per reference phase, grid.sync() between dependent sub-phases, and a
 // uniform early-out when the phase has nothing to do (no moved proxies / no contact state change / no enlarged proxy).
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kCoopThreads) k_broadphase(WorldDev d) {      // UpdateBroadPhasePairs + RebuildTrees
-  cg::grid_group grid = cg::this_grid();
+__device__ void phase_broadphase(cg::grid_group& grid, const WorldDev& d) {      // UpdateBroadPhasePairs + RebuildTrees
   const int tid = gtid(), stride = gsize();
   Scalars& s = *d.sc;
   if (s.moveCount > 0) {
@@ -1270,8 +1268,7 @@ __global__ void __launch_bounds__(kCoopThreads) k_broadphase(WorldDev d) {      
   if (threadIdx.x == 0 && blockIdx.x == 2) p_tree_rebuild(d, kKinematicBody);
 }
 
-__global__ void __launch_bounds__(kCoopThreads) k_collide_phase(WorldDev d, StepParams sp) {   // World.Collide
-  cg::grid_group grid = cg::this_grid();
+__device__ void phase_collide(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {   // World.Collide
   const int tid = gtid(), stride = gsize();
   Scalars& s = *d.sc;
   p_collide(d, sp, tid, stride);
@@ -1286,6 +1283,32 @@ __global__ void __launch_bounds__(kCoopThreads) k_collide_phase(WorldDev d, Step
   if (tid == 0) { p_events_finish(d, sp, d.flagScan + d.contactCapacity); s.anyContactFlag = 0; }
   grid.sync();
   if (blockIdx.x == 0) p_color_ops(d);
+}
+
+__device__ __forceinline__ unsigned long long globalTimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ void stamp(const WorldDev& d, int k) { if (gtid() == 0) d.sc->phaseStamp[k] = globalTimer(); }
+
+// One launch for UpdateBroadPhasePairs -> Collide -> (islands) -> PrepareContacts -> grid-path solver. Phases that have
+// nothing to do leave through a uniform branch; barriers after phases that wrote nothing are skipped.
+__global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepParams sp) {
+  cg::grid_group grid = cg::this_grid();
+  Scalars& s = *d.sc;
+  stamp(d, 0);
+  phase_broadphase(grid, d);
+  grid.sync();
+  stamp(d, 1);
+  phase_collide(grid, d, sp);
+  grid.sync();
+  stamp(d, 2);
+  const bool dirty = s.graphDirty != 0;
+  phase_islands(grid, d);
+  if (dirty) grid.sync();
+  const bool gridWork = s.smallConStart > 0 || d.jointColorStart[kGraphColorCount] > 0 || s.bigBodyCount > 0;
+  if (gridWork) { phase_prepare(d, sp); grid.sync(); }
+  stamp(d, 3);
+  if (gridWork) phase_solver_grid(grid, d, sp);
+  stamp(d, 4);
+  if (gtid() == 0) for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k];
 }
 
 __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, StepParams sp, int newEndIndex) {   // FinalizeBodies + refit
@@ -1350,15 +1373,10 @@ int World::step(float timeStep, int subStepCount) {
   sp.enableWarmStarting = enableWarmStarting; sp.enableContactSoftening = enableContactSoftening; sp.enableContinuous = enableContinuous;
   sp.enableSpeculative = enableSpeculative; sp.enableSleep = 0; sp.endIndex = endIndex_;
 
-  const int maxBlocks = 148 * 8;
-  const int gContact = gridFor(d.contactCapacity, kThreads, maxBlocks), gBody = gridFor(d.awakeCount, kThreads, maxBlocks);
   if (coopBlocks_ == 0) {
-    int occ[5] = {0, 0, 0, 0, 0};
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], k_solver, kCoopThreads, 0));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], k_islands, kCoopThreads, 0));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[2], k_broadphase, kCoopThreads, 0));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[3], k_collide_phase, kCoopThreads, 0));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[4], k_finalize_phase, kCoopThreads, 0));
+    int occ[2] = {0, 0};
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], k_step_front, kCoopThreads, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], k_finalize_phase, kCoopThreads, 0));
     for (int o : occ) if (o < 1) return fail(B2C_E_CUDA, "a cooperative phase kernel cannot be made resident");
     cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device_));
     coopBlocks_ = prop.multiProcessorCount;       // one 512-thread CTA per SM: the barrier cost grows with CTA count
@@ -1367,21 +1385,14 @@ int World::step(float timeStep, int subStepCount) {
   const dim3 cgrid(coopBlocks_), cblock(kCoopThreads);
   cudaEvent_t* pe = ev_ + (profHead_ % kProfRing) * kProfEvents;
   cudaEventRecord(pe[0], stream_);
-  { void* args[] = {(void*)&d}; CK(cudaLaunchCooperativeKernel((void*)k_broadphase, cgrid, cblock, args, 0, stream_)); }
+  { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
   cudaEventRecord(pe[1], stream_);
-  { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_collide_phase, cgrid, cblock, args, 0, stream_)); }
-  cudaEventRecord(pe[2], stream_);
-  { void* args[] = {(void*)&d}; CK(cudaLaunchCooperativeKernel((void*)k_islands, cgrid, cblock, args, 0, stream_)); }
-  k_prepare<<<gContact, kThreads, 0, stream_>>>(d, sp);
-  cudaEventRecord(pe[3], stream_);
-  { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_solver, cgrid, cblock, args, 0, stream_)); }
   k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp);
-  k_free_bodies<<<gBody, kThreads, 0, stream_>>>(d, sp);
-  cudaEventRecord(pe[4], stream_);
+  cudaEventRecord(pe[2], stream_);
   lastEndIndex_ = endIndex_;
   endIndex_ = 1 - endIndex_;
   { void* args[] = {(void*)&d, (void*)&sp, (void*)&endIndex_}; CK(cudaLaunchCooperativeKernel((void*)k_finalize_phase, cgrid, cblock, args, 0, stream_)); }
-  cudaEventRecord(pe[5], stream_);
+  cudaEventRecord(pe[3], stream_);
   profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
   CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
   CK(cudaGetLastError());

@@ -69,6 +69,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int errorFlags, toiCandidates, jointEventCount, stepCount;
   int touchingCount, liveContactCount, rebuildLeafCount[3], colorRounds;
   int awakeCount, anyRestitution, anyContactFlag, anyHitShapes;
+  unsigned long long phaseStamp[8], phaseAcc[8];   // %globaltimer stamps inside k_step_front and their per-phase sums (ns)
   int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
   int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
 };
