@@ -188,10 +188,18 @@ def mixed_drop(world, n=120, seed=7):
     return ground, paddle, bodies
 
 
+def batched_pyramids(world, n_worlds=8192, first=0, rows=10, pitch=15.0, cols=128):
+    """BASELINE.json configs[4]: `n_worlds` independent 10-row pyramids (world index first..first+n), each on its own ground,
+    x positions jittered per world by splitmix64(seed=world index) so worlds are not bit-copies."""
+    for k in range(first, first + n_worlds):
+        add_pyramid(world, rows, origin=((k % cols) * pitch, (k // cols) * pitch), ground_half_width=6.0, jitter_seed=k, jitter=0.001)
+
+
 SCENES = {
     "large_pyramid": large_pyramid,
     "many_pyramids": many_pyramids,
     "tumbler": tumbler,
     "joint_grid": joint_grid,
     "mixed_drop": mixed_drop,
+    "batched_pyramids": batched_pyramids,
 }
