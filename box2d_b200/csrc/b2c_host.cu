@@ -398,6 +398,9 @@ int World::upload() {
     td.capacity = cap; td.stackCapacity = 16384;
     DA(td.aabb, float4, cap); DA(td.child, int2, cap); DA(td.parent, int, cap); DA(td.hf, uint32_t, cap); DA(td.cat, uint64_t, cap);
     DA(td.user, int, cap); DA(td.moved, uint8_t, cap); DA(td.meta, int, 4); DA(td.leafIdx, int, cap); DA(td.leafCtr, float2, cap); DA(td.stack, int, td.stackCapacity);
+    DA(td.segStart, int, cap); DA(td.recEnd, int, cap + 1); DA(td.recNode, int, cap + 1); DA(td.recSplit, int, cap + 1); DA(td.recBox, float4, cap + 1);
+    DA(td.flagScan, int, cap + 1); DA(td.flagArr, int, cap + 1); DA(td.pairR, int, cap + 1); DA(td.freeIds, int, cap + 1); DA(td.subCount, int, cap);
+    DA(td.visit, int, cap); DA(td.serialList, int, cap + 1); DA(td.rb, int, 8);
     UP(td.aabb, h.aabb); UP(td.child, h.child); UP(td.parent, h.parent); UP(td.hf, h.hf); UP(td.cat, h.cat); UP(td.user, h.user);
     std::vector<uint8_t> mv(cap, 0);
     for (size_t k = 0; k < moved_[t].size() && k < (size_t)cap; k++) mv[k] = moved_[t][k];

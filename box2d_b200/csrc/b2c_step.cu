@@ -1242,6 +1242,10 @@ __device__ void p_step_finish(const WorldDev& d, int newEndIndex) {
 }
 __global__ void k_zero_step(WorldDev d, int newEndIndex) { Scalars& s = *d.sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; }
 
+}  // namespace b2c
+#include "b2c_rebuild.cuh"
+namespace b2c {
+
 // ------------------------------------------------------------------------------------------------------------
 // Fused cooperative phase kernels: one launch per reference phase, grid.sync() between dependent sub-phases, and a
 // uniform early-out when the phase has nothing to do (no moved proxies / no contact state change / no enlarged proxy).
@@ -1264,8 +1268,9 @@ __device__ void phase_broadphase(cg::grid_group& grid, const WorldDev& d) {     
     grid.sync();
   } else if (tid == 0) s.newPairCount = 0;
   if (tid == 0) p_pairs_finish(d);
-  if (threadIdx.x == 0 && blockIdx.x == 1) p_tree_rebuild(d, kDynamicBody);
-  if (threadIdx.x == 0 && blockIdx.x == 2) p_tree_rebuild(d, kKinematicBody);
+  grid.sync();
+  phase_rebuild(grid, d, kDynamicBody);           // BroadPhase.RebuildTrees (src/BroadPhase.cs:112-116)
+  phase_rebuild(grid, d, kKinematicBody);
 }
 
 __device__ void phase_collide(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {   // World.Collide

@@ -32,6 +32,10 @@ struct TreeDev {
   int* leafIdx;        // rebuild scratch (leafIndices)
   float2* leafCtr;     // rebuild scratch (leafCenters)
   int* stack;          // rebuild scratch: DFS stack + RebuildItem stack (5 ints each)
+  // parallel rebuild scratch (b2c_rebuild.cuh), all sized `capacity`
+  int* segStart; int* recEnd; int* recNode; int* recSplit; float4* recBox; int* flagScan; int* flagArr; int* pairR; int* freeIds;
+  int* subCount; int* visit; int* serialList;
+  int* rb;             // [0] L [1] freed internal nodes [2] node cursor [3],[4] active ranges (level parity) [5] serial ranges [6] new root
   int capacity;
   int stackCapacity;
 };
