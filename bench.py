@@ -143,7 +143,7 @@ def b200_arm(args, rank, world_size, local_rank):
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
-    step_ms, solver_ms, phases = 0.0, 0.0, [0.0] * 5
+    step_ms, solver_ms, phases = 0.0, 0.0, [0.0] * 6
     done = 0
     while done < K:
         n = min(32, K - done)
@@ -155,7 +155,7 @@ def b200_arm(args, rank, world_size, local_rank):
         p = w.GetProfile()
         step_ms += p.step * n
         solver_ms += p.solveConstraints * n
-        for i, f in enumerate(("pairs", "collide", "prepareConstraints", "solveConstraints", "transforms")):
+        for i, f in enumerate(("pairs", "collide", "prepareConstraints", "solveConstraints", "transforms", "treeRebuild")):
             phases[i] += getattr(p, f) * n
         done += n
     barrier()
@@ -203,7 +203,7 @@ def b200_arm(args, rank, world_size, local_rank):
                        "worlds_per_gpu": "20x20 independent 10-row pyramids in one device world", "parallelism": f"replicas x{world_size} (no data-path collective)",
                        "l2": "384 MB flush buffer written between timed steps; per-step CUDA-event time summed"},
             "value_l2_resident": total_units / (warm_ms_max * 1e-3), "ms_per_step_l2_resident": warm_ms_max / K,
-            "phase_ms": dict(zip(("pairs", "collide", "color_sort_prepare", "solver_kernel", "finalize_refit"), [x / K for x in phases])),
+            "phase_ms": dict(zip(("pairs", "collide", "color_sort_prepare", "solver_kernel", "finalize_refit", "tree_rebuild_in_collide"), [x / K for x in phases])),
             "roofline": {"bound": "hbm", "kernel": "k_solver", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "algorithmic_bytes_per_launch": algo_bytes, "avg_launch_ms": avg_solver_ms,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},

@@ -201,6 +201,12 @@ class World:
         self._check(self.fns["world_get_profile"](self.handle, C.byref(p)))
         return p
 
+    def DebugChecksums(self):
+        """Per-phase state checksums of the last step (zeros unless B2CUDA_DEBUG_CHECKSUMS=1 was set at the first step)."""
+        out = (C.c_uint64 * 16)()
+        self._check(self.fns["world_debug_checksums"](self.handle, out))
+        return list(out)
+
     def TimerStart(self):
         self._check(self.fns["world_timer_start"](self.handle))
 

@@ -107,7 +107,7 @@ class Profile(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("step", "pairs", "collide", "solve", "prepareStages", "solveConstraints",
                                          "prepareConstraints", "integrateVelocities", "warmStart", "solveImpulses",
                                          "integratePositions", "relaxImpulses", "applyRestitution", "storeImpulses",
-                                         "transforms", "refit", "readback")]
+                                         "transforms", "refit", "readback", "treeRebuild")]
 
 
 # name -> (argtypes after the world handle, has world handle)
@@ -152,6 +152,7 @@ PRODUCT_ONLY = {
     "world_get_profile": ([_W, C.POINTER(Profile)], C.c_int32),
     "world_timer_start": ([_W], C.c_int32),
     "world_timer_stop": ([_W, C.POINTER(C.c_float)], C.c_int32),
+    "world_debug_checksums": ([_W, C.POINTER(C.c_uint64)], C.c_int32),
 }
 
 

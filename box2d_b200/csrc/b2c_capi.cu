@@ -91,6 +91,7 @@ int32_t b2cuda_world_read_contacts(B2CWorld* h, B2CContactRead* dst, int32_t cap
 int32_t b2cuda_world_read_joints(B2CWorld* h, B2CJointRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readJoints(dst, cap, n)); }
 int32_t b2cuda_world_read_shapes(B2CWorld* h, B2CShapeRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readShapes(dst, cap, n)); }
 int32_t b2cuda_world_get_counters(B2CWorld* h, B2CCounters* out) { CHECK_HANDLE(h); return done(h, h->w->getCounters(out)); }
+int32_t b2cuda_world_debug_checksums(B2CWorld* h, uint64_t* out16) { CHECK_HANDLE(h); return done(h, h->w->debugChecksums((unsigned long long*)out16)); }
 int32_t b2cuda_world_get_profile(B2CWorld* h, B2CProfile* out) { CHECK_HANDLE(h); return done(h, h->w->getProfile(out)); }
 
 int32_t b2cuda_world_timer_start(B2CWorld* h) { CHECK_HANDLE(h); return done(h, h->w->timerStart()); }

@@ -418,6 +418,15 @@ int World::upload() {
   d.pairTableSize = tableSize;
   DA(d.moveArray, int, d.moveCapacity); DA(d.moveHitCount, int, d.moveCapacity + 1); DA(d.movePairs, int2, d.pairCapacity);
   DA(d.pairTable, unsigned long long, tableSize);
+  { int sumCap = 0; for (int t = 0; t < 3; t++) sumCap += d.trees[t].capacity;
+    d.bigScratch = std::max(1 << 21, sumCap);
+    d.bigQueryVisits = kBigQueryVisits;
+    d.islandMaxBodies = kIslandMaxBodies;
+    d.debugChecksums = getenv("B2CUDA_DEBUG_CHECKSUMS") ? 1 : 0;
+    if (const char* e = getenv("B2CUDA_ISLAND_MAX_BODIES")) { int v = atoi(e); if (v >= 0 && v <= kIslandMaxBodies) d.islandMaxBodies = v; }
+    if (const char* e = getenv("B2CUDA_BIG_QUERY_VISITS")) { int v = atoi(e); if (v > 0) d.bigQueryVisits = v; }
+    DA(d.moveBig, int, d.moveCapacity); DA(d.bigList, int, kMaxBigQueries); DA(d.bigSegStart, int, kMaxBigQueries + 1); DA(d.bigOff, int, kMaxBigQueries + 1);
+    DA(d.bigScan, int, d.bigScratch); DA(d.bigFlag, uint8_t, d.bigScratch); DA(d.bigHits, int2, d.pairCapacity); }
   UP(d.moveArray, moveArray_);
   DA(d.cShape, int2, contactCap); DA(d.cBody, int2, contactCap); DA(d.cFlags, uint32_t, contactCap); DA(d.cColor, int, contactCap); DA(d.cGen, uint32_t, contactCap);
   DA(d.cMat, float4, contactCap); DA(d.cMass, float4, contactCap); DA(d.cSim, int2, contactCap);
@@ -436,7 +445,7 @@ int World::upload() {
   DA(d.endEvents[1], B2CContactTouchEvent, d.eventCapacity); DA(d.hitEvents, B2CContactHitEvent, d.eventCapacity);
   DA(d.bodyEnlargedCount, int, nAwake + 1);
   DA(d.sc, Scalars, 1);
-  int scanBlocks = std::max(contactCap, std::max(d.moveCapacity, nAwake)) / 256 + 2;
+  int scanBlocks = std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, nAwake)) / 256 + 2;
   DA(d.scanBlockSums, int, scanBlocks); DA(d.scanBlockSums4, int4, scanBlocks);
   Scalars init; memset(&init, 0, sizeof(init));
   init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;
@@ -704,13 +713,21 @@ int World::getProfile(B2CProfile* out) {       // averages over the steps since 
     cudaEventElapsedTime(&ms, e[0], e[3]); acc[3] += ms;
   }
   // sub-phases of the fused front kernel: %globaltimer sums kept on the device (ns), differenced against the previous call
-  double ph[4];
-  for (int k = 0; k < 4; k++) { ph[k] = (double)(hostScalars_->phaseAcc[k] - lastPhaseAcc_[k]) * 1e-6 / profCount_; lastPhaseAcc_[k] = hostScalars_->phaseAcc[k]; }
-  out->pairs = (float)ph[0]; out->collide = (float)ph[1]; out->prepareConstraints = (float)ph[2];
+  double ph[5];
+  for (int k = 0; k < 5; k++) { ph[k] = (double)(hostScalars_->phaseAcc[k] - lastPhaseAcc_[k]) * 1e-6 / profCount_; lastPhaseAcc_[k] = hostScalars_->phaseAcc[k]; }
+  out->pairs = (float)ph[0]; out->collide = (float)ph[1]; out->treeRebuild = (float)ph[4]; out->prepareConstraints = (float)ph[2];
   out->solveConstraints = (float)(ph[3] + acc[1] / n);          // grid-path solver + island solver kernel
   out->transforms = (float)(acc[2] / n); out->refit = out->transforms;
   out->solve = out->prepareConstraints + out->solveConstraints + out->transforms; out->step = (float)(acc[3] / n);
   profCount_ = 0;
+  return B2C_OK;
+}
+
+int World::debugChecksums(unsigned long long* out16) {
+  for (int k = 0; k < 16; k++) out16[k] = 0;
+  if (!onDevice_) return B2C_OK;
+  int rc = synchronize(); if (rc) return rc;
+  for (int k = 0; k < 16; k++) out16[k] = hostScalars_->dbg[k];
   return B2C_OK;
 }
 

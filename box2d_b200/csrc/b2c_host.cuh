@@ -87,6 +87,7 @@ class World {
   int readShapes(B2CShapeRead* dst, int capacity, int* count);
   int getCounters(B2CCounters* out);
   int getProfile(B2CProfile* out);
+  int debugChecksums(unsigned long long* out16);
   int timerStart();
   int timerStop(float* ms);
   int getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B2CContactTouchEvent** end, int* ne, const B2CContactHitEvent** hit, int* nh);
@@ -134,7 +135,7 @@ class World {
   cudaEvent_t ev_[kProfRing * kProfEvents] = {};
   cudaEvent_t timer_[2] = {};
   int profHead_ = 0, profCount_ = 0;
-  unsigned long long lastPhaseAcc_[4] = {0, 0, 0, 0};
+  unsigned long long lastPhaseAcc_[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   B2CProfile profile_{};
   bool profileValid_ = false;
   int coopBlocks_ = 0;

@@ -10,13 +10,19 @@
 namespace b2c {
 
 constexpr int kIslandThreads = 192;
-constexpr int kIslandMaxBodies = 192;      // body rows staged in shared memory (8 KB)
 constexpr int kIslandMaxCons = 1024;       // <= kIslandThreads: constraints live in registers; above: re-read per stage
 constexpr int kForceBig = 1 << 20;
 
 __device__ __forceinline__ int ufFind(int* parent, int x) {
   int p = parent[x];
   while (p != x) { int gp = parent[p]; if (gp != p) parent[x] = gp; x = p; p = gp; }   // path halving
+  return x;
+}
+// Read-only find for the flatten pass: path halving there would let a slow thread overwrite an already flattened entry
+// with an older, higher ancestor (the forest stays valid but is no longer flat, and every later phase assumes flat).
+__device__ __forceinline__ int ufFindReadOnly(const int* parent, int x) {
+  int p = parent[x];
+  while (p != x) { x = p; p = parent[x]; }
   return x;
 }
 __device__ __forceinline__ void ufUnion(int* parent, int a, int b) {
@@ -87,7 +93,7 @@ __device__ void phase_islands(cg::grid_group& grid, const WorldDev& d) {
   }
   grid.sync();
   // P2 flatten + bodies per root
-  for (int i = tid; i < awake; i += stride) { int r = ufFind(d.ufParent, i); d.ufParent[i] = r; atomicAdd(&d.rootBodyCount[r], 1); }
+  for (int i = tid; i < awake; i += stride) { int r = ufFindReadOnly(d.ufParent, i); d.ufParent[i] = r; atomicAdd(&d.rootBodyCount[r], 1); }
   grid.sync();
   // P3 constraints per root / color
   if (threadIdx.x < kGraphColorCount) hist[threadIdx.x] = 0;
@@ -123,7 +129,7 @@ __device__ void phase_islands(cg::grid_group& grid, const WorldDev& d) {
     if (d.ufParent[i] == i) {
       int bodies = d.rootBodyCount[i], cons = d.rootConCount[i];
       if (cons == 0) d.rootInfo[i] = d.kinematicUsed[i] ? -2 : -1;
-      else if (bodies > kIslandMaxBodies || cons > kIslandMaxCons) {
+      else if (bodies > d.islandMaxBodies || cons > kIslandMaxCons) {
         d.rootInfo[i] = -2;
         for (int c = 0; c < kOverflowIndex; c++) { int n = d.rootColorCount[i * kGraphColorCount + c]; if (n) atomicAdd(&s.colorCount[c], n); }
       } else { d.rootInfo[i] = 0; in = make_int4(1, bodies, cons, 0); }

@@ -42,8 +42,12 @@ __device__ void rbWalkUp(const TreeDev& t, int cur) {
 // sequential BuildTree (:853-959) for a small range whose root node is already allocated and linked to its parent
 __device__ void rbBuildSerial(const TreeDev& t, int s, int e, int rootNode) {
   int items[5 * (kSerialRange + 2)];
+  int li[kSerialRange]; float2 lc[kSerialRange];      // the range is worked on in thread-local (L1-resident) copies
+  const int base = s;
+  for (int k = 0; k < e - s; k++) { li[k] = t.leafIdx[s + k]; lc[k] = t.leafCtr[s + k]; }
+  e -= s; s = 0;
   int top = 0;
-  items[0] = rootNode; items[1] = -1; items[2] = s; items[3] = s + partitionMid(t.leafIdx + s, t.leafCtr + s, e - s); items[4] = e;
+  items[0] = rootNode; items[1] = -1; items[2] = s; items[3] = s + partitionMid(li + s, lc + s, e - s); items[4] = e;
   while (true) {
     int* item = items + 5 * top;
     item[1]++;
@@ -60,21 +64,20 @@ __device__ void rbBuildSerial(const TreeDev& t, int s, int e, int rootNode) {
       if (item[1] == 0) { startIndex = item[2]; endIndex = item[3]; } else { startIndex = item[3]; endIndex = item[4]; }
       int count = endIndex - startIndex;
       if (count == 1) {
-        int childIndex = t.leafIdx[startIndex];
+        int childIndex = li[startIndex];
         if (item[1] == 0) t.child[item[0]].x = childIndex; else t.child[item[0]].y = childIndex;
         t.parent[childIndex] = item[0];
       } else {
         int n = rbAllocNode(t);
-        int split = startIndex + partitionMid(t.leafIdx + startIndex, t.leafCtr + startIndex, count);
+        int split = startIndex + partitionMid(li + startIndex, lc + startIndex, count);
         top++;
         int* ni = items + 5 * top;
         ni[0] = n; ni[1] = -1; ni[2] = startIndex; ni[3] = split; ni[4] = endIndex;
       }
     }
   }
-  int keepParent = t.parent[rootNode];
   refitFromChildren(t, rootNode);
-  t.parent[rootNode] = keepParent;
+  for (int k = 0; k < e; k++) { t.leafIdx[base + k] = li[k]; t.leafCtr[base + k] = lc[k]; }
 }
 
 // is `n` a frontier node of the rebuild (a "leaf" of BuildTree)?  :973-978

@@ -17,7 +17,6 @@ namespace b2c {
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(B2C_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
 constexpr int kThreads = 256;
-constexpr int kScanChunk = 1024;
 constexpr int kCoopThreads = 512;      // block size of the cooperative phase kernels == chunk of gridScan
 
 __device__ __forceinline__ int gtid() { return blockIdx.x * blockDim.x + threadIdx.x; }
@@ -167,7 +166,8 @@ __device__ __forceinline__ bool acceptPair(const WorldDev& d, int queryKey, int 
 }
 
 // DynamicTree.Query (src/DynamicTree.cs:531-557): explicit stack, child1 pushed first so child2 is visited first.
-template <bool FILL> __device__ inline int queryTree(const WorldDev& d, int treeType, Box fat, int queryKey, int queryType, int queryShape, int hitBase, int2* out, int outLast) {
+// BUDGET: give up (return -1) after kBigQueryVisits node visits — the query is then answered by the leaf sweep below.
+template <bool FILL, bool BUDGET> __device__ inline int queryTree(const WorldDev& d, int treeType, Box fat, int queryKey, int queryType, int queryShape, int hitBase, int2* out, int outLast, int& visits) {
   const TreeDev& t = d.trees[treeType];
   int root = t.meta[0];
   if (t.meta[1] == 0 || root == -1) return 0;
@@ -176,6 +176,7 @@ template <bool FILL> __device__ inline int queryTree(const WorldDev& d, int tree
   stack[sp++] = root;
   while (sp > 0) {
     int id = stack[--sp];
+    if (BUDGET && ++visits > d.bigQueryVisits) return -1;
     Box nb = toBox(t.aabb[id]);
     if (!boxOverlaps(nb, fat)) continue;        // maskBits == DEFAULT_MASK_BITS: the category test always passes for non-zero categories
     if (t.cat[id] == 0) continue;
@@ -194,6 +195,15 @@ template <bool FILL> __device__ inline int queryTree(const WorldDev& d, int tree
   }
   return hits;
 }
+template <bool FILL, bool BUDGET> __device__ inline int queryTrees(const WorldDev& d, Box fat, int queryKey, int type, int queryShape, int2* out, int outLast) {
+  int count = 0, visits = 0, h;
+  if (type == kDynamicBody) {
+    h = queryTree<FILL, BUDGET>(d, kKinematicBody, fat, queryKey, type, queryShape, count, out, outLast, visits); if (h < 0) return -1; count += h;
+    h = queryTree<FILL, BUDGET>(d, kStaticBody, fat, queryKey, type, queryShape, count, out, outLast, visits); if (h < 0) return -1; count += h;
+  }
+  h = queryTree<FILL, BUDGET>(d, kDynamicBody, fat, queryKey, type, queryShape, count, out, outLast, visits); if (h < 0) return -1; count += h;
+  return count;
+}
 
 // FindPairsTask (:197-232). FILL=false counts accepted hits per move entry; FILL=true writes them in contact-creation
 // order: move index ascending, within a query the REVERSE of the hit order (the C# result list is LIFO, :193-194,:251-262).
@@ -202,22 +212,26 @@ template <bool FILL> __device__ void p_find_pairs(const WorldDev& d, int tid, in
   for (int i = tid; i < n; i += stride) {
     int queryKey = d.moveArray[i];
     int count = 0;
+    if (FILL && d.moveBig[i] >= 0) continue;    // wide query: p_big_fill copies its hits
     if (queryKey != -1) {
       int type = queryKey & 3, id = queryKey >> 2;
       Box fat = toBox(d.trees[type].aabb[id]);
       int queryShape = d.trees[type].user[id];
-      int2* out = nullptr; int outLast = 0;
       if (FILL) {
         int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) / kCoopThreads] : d.sc->newPairCount;
         if (end > d.pairCapacity) { atomicOr(&d.sc->errorFlags, (int)ERR_PAIR_CAPACITY); continue; }
-        out = d.movePairs; outLast = end - 1;
+        queryTrees<true, false>(d, fat, queryKey, type, queryShape, d.movePairs, end - 1);
+      } else {
+        int big = -1;
+        count = queryTrees<false, true>(d, fat, queryKey, type, queryShape, nullptr, 0);
+        if (count < 0) {
+          int slot = atomicAdd(&d.sc->bigQueryCount, 1);
+          if (slot < kMaxBigQueries) { d.bigList[slot] = i; big = slot; count = 0; }
+          else count = queryTrees<false, false>(d, fat, queryKey, type, queryShape, nullptr, 0);
+        }
+        d.moveBig[i] = big;
       }
-      if (type == kDynamicBody) {
-        count += queryTree<FILL>(d, kKinematicBody, fat, queryKey, type, queryShape, count, out, outLast);
-        count += queryTree<FILL>(d, kStaticBody, fat, queryKey, type, queryShape, count, out, outLast);
-      }
-      count += queryTree<FILL>(d, kDynamicBody, fat, queryKey, type, queryShape, count, out, outLast);
-    }
+    } else if (!FILL) d.moveBig[i] = -1;
     if (!FILL) d.moveHitCount[i] = count;
   }
 }
@@ -266,28 +280,15 @@ __device__ void p_pairs_finish(const WorldDev& d) {
   s.contactNext += n - fromFree;
   if (s.contactNext > d.contactCapacity) { s.contactNext = d.contactCapacity; s.errorFlags |= (int)ERR_CONTACT_CAPACITY; }
   s.liveContactCount += n;
-  s.moveCount = 0;
+  s.moveCount = 0; s.bigQueryCount = 0;
   s.beginCount = 0; s.hitCount = 0; s.jointEventCount = 0; s.anyRestitution = 0;
 }
 
 // ------------------------------------------------------------------------------------------------------------
 // Phase 1a: BroadPhase.RebuildTrees (src/BroadPhase.cs:112-116) -> DynamicTree.Rebuild(false) (src/DynamicTree.cs:802-1000).
 // The topology this produces decides the DFS order of later queries, hence contact ids; it is reproduced step for step.
-// v1: one thread per tree walks the sequential algorithm (pyramids never enlarge; churn scenes pay for it).
+// The parallel, bit-exact version lives in b2c_rebuild.cuh; PartitionMid and the child refit below are shared with it.
 // ------------------------------------------------------------------------------------------------------------
-struct TreeRef {
-  const TreeDev& t;
-  __device__ int allocNode(Scalars* sc) {
-    int id = t.meta[2];
-    if (id == -1) { atomicOr(&sc->errorFlags, (int)ERR_TREE); return 0; }
-    t.meta[2] = t.parent[id];
-    t.aabb[id] = make_float4(0, 0, 0, 0); t.child[id] = make_int2(-1, -1); t.parent[id] = -1; t.hf[id] = (uint32_t)NODE_ALLOCATED << 16;
-    t.cat[id] = ~0ull; t.user[id] = -1;
-    t.meta[1]++;
-    return id;
-  }
-  __device__ void freeNode(int id) { t.parent[id] = t.meta[2]; t.hf[id] &= 0xffffu; t.meta[2] = id; t.meta[1]--; }
-};
 __device__ int partitionMid(int* indices, float2* centers, int count) {   // :802-847
   if (count <= 2) return count / 2;
   float2 lo = centers[0], hi = centers[0];
@@ -324,80 +325,6 @@ __device__ __forceinline__ void refitFromChildren(const TreeDev& t, int node) {
   int h1 = (int)(t.hf[c.x] & 0xffffu), h2 = (int)(t.hf[c.y] & 0xffffu);
   t.hf[node] = (t.hf[node] & 0xffff0000u) | (uint32_t)(1 + (h1 > h2 ? h1 : h2));
   t.cat[node] = t.cat[c.x] | t.cat[c.y];
-}
-__device__ void p_tree_rebuild(const WorldDev& d, int treeType) {
-  const TreeDev& t = d.trees[treeType];
-  TreeRef tr{t};
-  int proxyCount = t.meta[3];
-  d.sc->rebuildLeafCount[treeType] = 0;
-  if (proxyCount == 0) return;
-  int root = t.meta[0];
-  if (!((t.hf[root] >> 16) & NODE_ENLARGED) || (t.hf[root] & 0xffffu) == 0) return;   // nothing flagged: Rebuild returns the same root
-  int* stack = t.stack; const int stackCap = t.stackCapacity;
-  int leafCount = 0, sp = 0;
-  int node = root;
-  while (true) {                                  // :969-993 collect leaves / untouched subtrees, free enlarged internals
-    uint32_t hf = t.hf[node];
-    if ((hf & 0xffffu) == 0 || !((hf >> 16) & NODE_ENLARGED)) {
-      t.leafIdx[leafCount] = node;
-      float4 a = t.aabb[node];
-      t.leafCtr[leafCount] = make_float2(0.5f * (a.x + a.z), 0.5f * (a.y + a.w));
-      leafCount++;
-      t.parent[node] = -1;
-    } else {
-      int doomed = node;
-      int2 c = t.child[node];
-      node = c.x;
-      if (sp >= stackCap) { atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); return; }
-      stack[sp++] = c.y;
-      tr.freeNode(doomed);
-      continue;
-    }
-    if (sp == 0) break;
-    node = stack[--sp];
-  }
-  d.sc->rebuildLeafCount[treeType] = leafCount;
-  // BuildTree :853-959 — items are (nodeIndex, childCount, startIndex, splitIndex, endIndex)
-  if (leafCount == 1) { t.parent[t.leafIdx[0]] = -1; t.meta[0] = t.leafIdx[0]; return; }
-  int* items = stack;
-  int top = 0;
-  {
-    int n = tr.allocNode(d.sc);
-    int split = partitionMid(t.leafIdx, t.leafCtr, leafCount);
-    items[0] = n; items[1] = -1; items[2] = 0; items[3] = split; items[4] = leafCount;
-  }
-  while (true) {
-    int* item = items + 5 * top;
-    item[1]++;
-    if (item[1] == 2) {
-      if (top == 0) break;
-      int doneNode = item[0];
-      top--;
-      int* parentItem = items + 5 * top;
-      if (parentItem[1] == 0) t.child[parentItem[0]].x = doneNode; else t.child[parentItem[0]].y = doneNode;
-      t.parent[doneNode] = parentItem[0];
-      refitFromChildren(t, doneNode);
-    } else {
-      int startIndex, endIndex;
-      if (item[1] == 0) { startIndex = item[2]; endIndex = item[3]; } else { startIndex = item[3]; endIndex = item[4]; }
-      int count = endIndex - startIndex;
-      if (count == 1) {
-        int childIndex = t.leafIdx[startIndex];
-        if (item[1] == 0) t.child[item[0]].x = childIndex; else t.child[item[0]].y = childIndex;
-        t.parent[childIndex] = item[0];
-      } else {
-        if (5 * (top + 2) > stackCap) { atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); return; }
-        int n = tr.allocNode(d.sc);
-        int split = startIndex + partitionMid(t.leafIdx + startIndex, t.leafCtr + startIndex, count);
-        top++;
-        int* ni = items + 5 * top;
-        ni[0] = n; ni[1] = -1; ni[2] = startIndex; ni[3] = split; ni[4] = endIndex;
-      }
-    }
-  }
-  int newRoot = items[0];
-  refitFromChildren(t, newRoot);
-  t.meta[0] = newRoot;
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -1035,12 +962,12 @@ __device__ void phase_prepare(const WorldDev& d, const StepParams& sp) {
 // reference's per-stage spin barrier; empty colors cost nothing.
 __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {
   const Scalars& s = *d.sc;
-  __shared__ int sBegin[kGraphColorCount], sEnd[kGraphColorCount], sJBegin[kGraphColorCount], sJEnd[kGraphColorCount], sActive[kGraphColorCount], sActiveCount;
+  __shared__ int sBegin[kGraphColorCount], sEnd[kGraphColorCount], sJBegin[kGraphColorCount], sJEnd[kGraphColorCount], sActiveCount;
   if (threadIdx.x == 0) {
     int n = 0;
     for (int c = 0; c < kOverflowIndex; c++) {
       int cc = s.colorCount[c], jc = d.jointColorStart[c + 1] - d.jointColorStart[c];
-      if (cc + jc > 0) { sActive[n] = c; sBegin[n] = s.colorStart[c]; sEnd[n] = s.colorStart[c] + cc; sJBegin[n] = d.jointColorStart[c]; sJEnd[n] = d.jointColorStart[c + 1]; n++; }
+      if (cc + jc > 0) { sBegin[n] = s.colorStart[c]; sEnd[n] = s.colorStart[c] + cc; sJBegin[n] = d.jointColorStart[c]; sJEnd[n] = d.jointColorStart[c + 1]; n++; }
     }
     sActiveCount = n;
   }
@@ -1209,8 +1136,13 @@ __device__ void p_refit(const WorldDev& d, int tid, int stride) {
       t.moved[id] = 1;
       for (int p = t.parent[id]; p != -1; p = t.parent[p]) {
         float* a = (float*)&t.aabb[p];
-        atomicMinF(a + 0, fat.x); atomicMinF(a + 1, fat.y); atomicMaxF(a + 2, fat.z); atomicMaxF(a + 3, fat.w);
-        atomicOr(&t.hf[p], (uint32_t)NODE_ENLARGED << 16);
+        const volatile float* av = a;                     // most ancestors already contain the box: test before the atomic
+        float4 cur = make_float4(av[0], av[1], av[2], av[3]);
+        if (fat.x < cur.x) atomicMinF(a + 0, fat.x);
+        if (fat.y < cur.y) atomicMinF(a + 1, fat.y);
+        if (fat.z > cur.z) atomicMaxF(a + 2, fat.z);
+        if (fat.w > cur.w) atomicMaxF(a + 3, fat.w);
+        if (!((*(volatile uint32_t*)&t.hf[p] >> 16) & NODE_ENLARGED)) atomicOr(&t.hf[p], (uint32_t)NODE_ENLARGED << 16);
       }
     }
   }
@@ -1244,6 +1176,7 @@ __global__ void k_zero_step(WorldDev d, int newEndIndex) { Scalars& s = *d.sc; s
 
 }  // namespace b2c
 #include "b2c_rebuild.cuh"
+#include "b2c_bigquery.cuh"
 namespace b2c {
 
 // ------------------------------------------------------------------------------------------------------------
@@ -1260,17 +1193,16 @@ __device__ void phase_broadphase(cg::grid_group& grid, const WorldDev& d) {     
     grid.sync();
     p_find_pairs<false>(d, tid, stride);
     grid.sync();
+    phase_big_queries(grid, d);
     gridScan<int>(grid, d.moveHitCount, d.scanBlockSums, s.moveCount, &s.newPairCount);
     p_find_pairs<true>(d, tid, stride);
+    p_big_fill(d, tid, stride);
     grid.sync();
     p_create_contacts(d, tid, stride);
     p_clear_moved(d, tid, stride);
     grid.sync();
   } else if (tid == 0) s.newPairCount = 0;
   if (tid == 0) p_pairs_finish(d);
-  grid.sync();
-  phase_rebuild(grid, d, kDynamicBody);           // BroadPhase.RebuildTrees (src/BroadPhase.cs:112-116)
-  phase_rebuild(grid, d, kKinematicBody);
 }
 
 __device__ void phase_collide(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {   // World.Collide
@@ -1290,6 +1222,101 @@ __device__ void phase_collide(cg::grid_group& grid, const WorldDev& d, const Ste
   if (blockIdx.x == 0) p_color_ops(d);
 }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// Debug aid (B2CUDA_DEBUG_CHECKSUMS=1): order-independent checksums of the state between phases, so that two runs of
+// the same scene can be compared phase by phase (scripts/gpu_determinism.py). Off by default: one uniform branch.
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) { x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33; return x; }
+__device__ __forceinline__ unsigned long long hf4(unsigned long long h, float4 v) {
+  h = mix64(h + (((unsigned long long)fbits(v.x) << 32) | fbits(v.y)));
+  return mix64(h + (((unsigned long long)fbits(v.z) << 32) | fbits(v.w)));
+}
+__device__ void dbgAdd(const WorldDev& d, int slot, unsigned long long sum) {
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0 && sum) atomicAdd(&d.sc->dbg[slot], sum);
+}
+__device__ void dbgBodies(const WorldDev& d, int slot) {
+  if (!d.debugChecksums) return;
+  unsigned long long sum = 0;
+  for (int i = gtid(); i < d.awakeCount; i += gsize()) sum += hf4(hf4(mix64(i + 1), d.st0[i]), d.st1[i]);
+  dbgAdd(d, slot, sum);
+}
+__device__ void dbgContacts(const WorldDev& d, int slot) {
+  if (!d.debugChecksums) return;
+  unsigned long long sum = 0;
+  int n = d.sc->contactNext;
+  for (int i = gtid(); i < n; i += gsize()) {
+    if (!(d.cFlags[i] & CF_ALIVE)) continue;
+    unsigned long long h = mix64(i + 1);
+    int2 sh = d.cShape[i], sm = d.cSim[i];
+    h = mix64(h + d.cFlags[i]); h = mix64(h + (unsigned)d.cColor[i]); h = mix64(h + (((unsigned long long)(unsigned)sh.x << 32) | (unsigned)sh.y));
+    h = mix64(h + (((unsigned long long)(unsigned)sm.x << 32) | (unsigned)sm.y));
+    h = hf4(h, d.cMass[i]); h = hf4(h, d.cMat[i]); h = hf4(h, d.mN[i]); h = hf4(h, d.mA0[i]); h = hf4(h, d.mB0[i]); h = hf4(h, d.mC0[i]);
+    if (fbits(d.mN[i].w) > 1) { h = hf4(h, d.mA1[i]); h = hf4(h, d.mB1[i]); h = hf4(h, d.mC1[i]); }
+    sum += h;
+  }
+  dbgAdd(d, slot, sum);
+}
+__device__ void dbgLanes(const WorldDev& d, int slot, bool all) {
+  if (!d.debugChecksums) return;
+  unsigned long long sum = 0;
+  int n = d.sc->smallConStart;
+  for (int t = gtid(); t < n; t += gsize()) {
+    int ci = d.sContact[t];
+    if (ci < 0) continue;
+    unsigned long long h = mix64(ci + 1);
+    if (all) { h = hf4(h, d.sB[t]); h = hf4(h, d.sC[t]); h = hf4(h, d.sD[t]); h = hf4(h, d.sE[t]); h = hf4(h, d.sF[t]); h = hf4(h, d.sG[t]); h = hf4(h, d.sH[t]);
+               float4 A = d.sA[t]; h = hf4(h, make_float4(0, 0, A.z, A.w)); }
+    h = hf4(h, d.sI[t]); h = hf4(h, d.sJ[t]);
+    sum += h;
+  }
+  dbgAdd(d, slot, sum);
+}
+
+// debug: number of (color, dynamic body) pairs claimed by more than one touching constraint (must be 0), and the same
+// test on the solver's own arrangement (slot -> contact -> bodies)
+__device__ void dbgColorConflicts(cg::grid_group& grid, const WorldDev& d, int slot) {
+  if (!d.debugChecksums) return;
+  const int awake = d.awakeCount, n = d.sc->contactNext;
+  grid.sync();
+  for (int i = gtid(); i < awake * kGraphColorCount; i += gsize()) d.rootColorCount[i] = 0;
+  grid.sync();
+  unsigned long long bad = 0;
+  for (int i = gtid(); i < n; i += gsize()) {
+    if (!(d.cFlags[i] & CF_TOUCHING)) continue;
+    int c = d.cColor[i];
+    if (c < 0 || c >= kOverflowIndex) { bad += 1000000; continue; }
+    if (d.cConstraint[i] < 0 || d.sContact[d.cConstraint[i]] != i) bad += 1000;
+    int2 sim = d.cSim[i];
+    if (sim.x >= 0 && (fbits(d.st0[sim.x].w) & kDynamicFlag) && atomicAdd(&d.rootColorCount[sim.x * kGraphColorCount + c], 1) > 0) bad++;
+    if (sim.y >= 0 && (fbits(d.st0[sim.y].w) & kDynamicFlag) && atomicAdd(&d.rootColorCount[sim.y * kGraphColorCount + c], 1) > 0) bad++;
+  }
+  dbgAdd(d, slot, bad);
+  // partition: both dynamic bodies of a touching contact share a root; roots are fixed points; a small island's constraint
+  // indexes its own bodies; a body with a constraint is never on the free list
+  unsigned long long bad2 = 0;
+  for (int i = gtid(); i < awake; i += gsize()) { int r = d.ufParent[i]; if (r < 0 || r >= awake || d.ufParent[r] != r) bad2 += 1; }
+  for (int i = gtid(); i < n; i += gsize()) {
+    if (!(d.cFlags[i] & CF_TOUCHING)) continue;
+    int2 sim = d.cSim[i];
+    bool dynA = sim.x >= 0 && (fbits(d.st0[sim.x].w) & kDynamicFlag), dynB = sim.y >= 0 && (fbits(d.st0[sim.y].w) & kDynamicFlag);
+    if (dynA && dynB && d.ufParent[sim.x] != d.ufParent[sim.y]) bad2 += 1000;
+    int r = d.ufParent[dynA ? sim.x : sim.y], info = d.rootInfo[r];
+    if (info == -1) bad2 += 1000000;
+    int t = d.cConstraint[i];
+    if (info >= 0 && t >= 0) {
+      int2 lc = d.sLocal[t];
+      int b0 = d.islandBodyStart[info], nb = d.islandBodyStart[info + 1] - b0;
+      if (dynA && (lc.x < 0 || lc.x >= nb || d.islandBodies[b0 + lc.x] != sim.x)) bad2 += 1000000000ull;
+      if (dynB && (lc.y < 0 || lc.y >= nb || d.islandBodies[b0 + lc.y] != sim.y)) bad2 += 1000000000ull;
+      if (t < d.islandConStart[info] || t >= d.islandConStart[info] + d.islandColorOff[info * (kGraphColorCount + 1) + kGraphColorCount]) bad2 += 1000000000000ull;
+    }
+  }
+  dbgAdd(d, slot + 1, bad2);
+  grid.sync();
+}
+
 __device__ __forceinline__ unsigned long long globalTimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ void stamp(const WorldDev& d, int k) { if (gtid() == 0) d.sc->phaseStamp[k] = globalTimer(); }
 
@@ -1299,27 +1326,37 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   cg::grid_group grid = cg::this_grid();
   Scalars& s = *d.sc;
   stamp(d, 0);
+  if (gtid() < 16) s.dbg[gtid()] = 0;
   phase_broadphase(grid, d);
   grid.sync();
   stamp(d, 1);
+  dbgContacts(d, 0); dbgBodies(d, 1);
+  phase_rebuild(grid, d, kDynamicBody);           // BroadPhase.RebuildTrees (src/BroadPhase.cs:112-116), part of Collide in the reference
+  phase_rebuild(grid, d, kKinematicBody);
+  stamp(d, 5);
   phase_collide(grid, d, sp);
   grid.sync();
   stamp(d, 2);
+  dbgContacts(d, 2);
   const bool dirty = s.graphDirty != 0;
   phase_islands(grid, d);
   if (dirty) grid.sync();
   const bool gridWork = s.smallConStart > 0 || d.jointColorStart[kGraphColorCount] > 0 || s.bigBodyCount > 0;
   if (gridWork) { phase_prepare(d, sp); grid.sync(); }
   stamp(d, 3);
+  dbgLanes(d, 3, true); dbgBodies(d, 4); dbgColorConflicts(grid, d, 10);
+  if (d.debugChecksums) grid.sync();
   if (gridWork) phase_solver_grid(grid, d, sp);
   stamp(d, 4);
-  if (gtid() == 0) for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k];
+  if (d.debugChecksums) { grid.sync(); dbgBodies(d, 5); dbgLanes(d, 6, false); dbgContacts(d, 7); }
+  if (gtid() == 0) { for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k]; s.phaseAcc[4] += s.phaseStamp[5] - s.phaseStamp[1]; }
 }
 
 __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, StepParams sp, int newEndIndex) {   // FinalizeBodies + refit
   cg::grid_group grid = cg::this_grid();
   const int tid = gtid(), stride = gsize();
   Scalars& s = *d.sc;
+  if (d.debugChecksums) { dbgBodies(d, 8); dbgContacts(d, 9); grid.sync(); }
   p_finalize(d, sp, tid, stride);
   if (s.anyHitShapes) p_hit_events(d, sp, tid, stride);
   grid.sync();

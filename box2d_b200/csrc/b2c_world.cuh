@@ -76,6 +76,9 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   unsigned long long phaseStamp[8], phaseAcc[8];   // %globaltimer stamps inside k_step_front and their per-phase sums (ns)
   int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
   int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
+  int bigQueryCount, bigHitTotal, bigGroupTotal, staticRanksValid;   // wide broadphase queries (b2c_bigquery.cuh)
+  int rebuildLevels[3], pad0;
+  unsigned long long dbg[16];           // order-independent state checksums per phase (B2CUDA_DEBUG_CHECKSUMS=1; b2cuda_world_debug_checksums)
 };
 
 struct StepParams {    // src/Solver.cs:57-112 StepContext (scalars only)
@@ -133,6 +136,17 @@ struct WorldDev {
   int* moveHitCount;   // per move entry: accepted hits, then exclusive offsets
   int2* movePairs;     // (shapeIdA, shapeIdB) in contact-creation order
   int moveCapacity, pairCapacity;
+  // wide queries (a moved proxy whose fat box overlaps a large part of a tree) are answered by a grid-wide sweep over the
+  // tree's leaves in DFS order instead of a one-thread traversal (b2c_bigquery.cuh)
+  int* moveBig;        // per move entry: slot in bigList or -1
+  int* bigList;        // [kMaxBigQueries] move indices
+  int* bigSegStart;    // [kMaxBigQueries+1] start of each wide query's leaf segment in the sweep
+  int* bigOff;         // [kMaxBigQueries+1] start of each wide query's hits in bigHits
+  int* bigScan;        // [bigScratch] sweep flags -> exclusive ranks
+  uint8_t* bigFlag;    // [bigScratch]
+  int2* bigHits;       // [pairCapacity] accepted pairs in hit order
+  int bigScratch;
+  int bigQueryVisits;  // node-visit budget of a one-thread query (kBigQueryVisits; B2CUDA_BIG_QUERY_VISITS overrides it for tests)
   unsigned long long* pairTable;   // open-addressing set of shape pair keys (World.pairSet)
   int pairTableSize;   // power of two
   // --- contacts, slot == contactId (src/Contact.cs Contact + ContactSim) ---
@@ -168,6 +182,8 @@ struct WorldDev {
   int* freeBodies; int* bigBodies;   // [awake]
   uint8_t* kinematicUsed;            // [awake] non-dynamic awake body referenced by a constraint
   int2* sLocal;        // [constraint] island-local body indices (-1 = not in the awake set)
+  int debugChecksums;
+  int islandMaxBodies; // kIslandMaxBodies; B2CUDA_ISLAND_MAX_BODIES=0 sends every island down the grid path (tests)
   // --- events ---
   B2CContactTouchEvent* beginEvents; B2CContactTouchEvent* endEvents[2]; B2CContactHitEvent* hitEvents;
   int eventCapacity;

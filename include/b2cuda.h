@@ -109,7 +109,8 @@ typedef struct B2CCounters {            /* WorldAPI.GetCounters api/World.cs:817
 } B2CCounters;
 typedef struct B2CProfile {             /* WorldAPI.GetProfile api/World.cs:814; fields of include/Types.cs:378-403 (ms, CUDA events) */
   float step, pairs, collide, solve, prepareStages, solveConstraints, prepareConstraints, integrateVelocities, warmStart,
-        solveImpulses, integratePositions, relaxImpulses, applyRestitution, storeImpulses, transforms, refit, readback;
+        solveImpulses, integratePositions, relaxImpulses, applyRestitution, storeImpulses, transforms, refit, readback,
+        treeRebuild;        /* BroadPhase.RebuildTrees: inside `collide` as in the reference (src/World.cs:313), also reported alone */
 } B2CProfile;
 
 typedef struct B2CWorld B2CWorld;
@@ -165,6 +166,9 @@ int32_t b2cuda_world_read_contacts(B2CWorld* world, B2CContactRead* dst, int32_t
 int32_t b2cuda_world_read_joints(B2CWorld* world, B2CJointRead* dst, int32_t capacity, int32_t* count);
 int32_t b2cuda_world_read_shapes(B2CWorld* world, B2CShapeRead* dst, int32_t capacity, int32_t* count);
 int32_t b2cuda_world_get_counters(B2CWorld* world, B2CCounters* out);
+/* Debug aid, no reference counterpart: with B2CUDA_DEBUG_CHECKSUMS=1 in the environment at world upload, out16 receives
+   order-independent checksums of the device state between the phases of the last step (scripts/gpu_determinism.py). */
+int32_t b2cuda_world_debug_checksums(B2CWorld* world, uint64_t* out16);
 int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);   /* averages over the steps since the previous call (<= 64) */
 /* (new, no reference counterpart) device-time stopwatch on the world's own stream: CUDA events around whatever was
  * enqueued between the two calls; stop synchronises. Used by bench.py so timing does not depend on torch's stream. */
