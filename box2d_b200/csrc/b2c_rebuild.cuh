@@ -3,7 +3,7 @@
 // reference's DFS order (child1 first) with subtree counts + per-node rank walks instead of a stack; (2) BuildTree's top-down
 // median split runs level by level over all ranges at once — PartitionMid's two-pointer swap loop has the closed form
 // "k-th misplaced element from the left swaps with the k-th misplaced element from the right", evaluated with one prefix sum
-// per level; ranges of <= kSerialRange leaves are finished by one thread each with the sequential code; (3) boxes, heights
+// per level; ranges of <= kSerialRange leaves are finished by one warp each, in registers; (3) boxes, heights
 // and category bits of the new internal nodes are filled bottom-up (second arrival computes). Which free node id an internal
 // node receives is not reproduced (ids of internal nodes are not observable; leaves keep their proxy ids).
 #pragma once
@@ -39,45 +39,98 @@ __device__ void rbWalkUp(const TreeDev& t, int cur) {
   }
 }
 
-// sequential BuildTree (:853-959) for a small range whose root node is already allocated and linked to its parent
-__device__ void rbBuildSerial(const TreeDev& t, int s, int e, int rootNode) {
-  int items[5 * (kSerialRange + 2)];
-  int li[kSerialRange]; float2 lc[kSerialRange];      // the range is worked on in thread-local (L1-resident) copies
-  const int base = s;
-  for (int k = 0; k < e - s; k++) { li[k] = t.leafIdx[s + k]; lc[k] = t.leafCtr[s + k]; }
-  e -= s; s = 0;
-  int top = 0;
-  items[0] = rootNode; items[1] = -1; items[2] = s; items[3] = s + partitionMid(li + s, lc + s, e - s); items[4] = e;
-  while (true) {
-    int* item = items + 5 * top;
-    item[1]++;
-    if (item[1] == 2) {
-      if (top == 0) break;
-      int doneNode = item[0];
-      top--;
-      int* parentItem = items + 5 * top;
-      if (parentItem[1] == 0) t.child[parentItem[0]].x = doneNode; else t.child[parentItem[0]].y = doneNode;
-      t.parent[doneNode] = parentItem[0];
-      refitFromChildren(t, doneNode);
-    } else {
-      int startIndex, endIndex;
-      if (item[1] == 0) { startIndex = item[2]; endIndex = item[3]; } else { startIndex = item[3]; endIndex = item[4]; }
-      int count = endIndex - startIndex;
-      if (count == 1) {
-        int childIndex = li[startIndex];
-        if (item[1] == 0) t.child[item[0]].x = childIndex; else t.child[item[0]].y = childIndex;
-        t.parent[childIndex] = item[0];
-      } else {
-        int n = rbAllocNode(t);
-        int split = startIndex + partitionMid(li + startIndex, lc + startIndex, count);
-        top++;
-        int* ni = items + 5 * top;
-        ni[0] = n; ni[1] = -1; ni[2] = startIndex; ni[3] = split; ni[4] = endIndex;
-      }
+// BuildTree (:853-959) for a range of <= 32 frontier nodes whose root node is already allocated and linked to its parent,
+// by ONE WARP with the range in registers (lane p = position p). Every level all ranges split at once: the center bounds
+// are a segmented reduction over lanes, PartitionMid's swaps (k-th misplaced-left with k-th misplaced-right, counted
+// with ballots) are two shuffles, child ids come from a block of free ids reserved with a single atomic. Boxes, heights
+// and category bits of the new nodes are computed after the last level from the final arrangement: the node whose split
+// falls before position j is finished by lane j (each internal node of a binary tree over a sequence has its own split).
+// No load in here depends on an earlier store, unlike the one-thread version this replaces.
+__device__ void rbBuildWarp(const TreeDev& t, int rs, int re, int rootNode) {
+  const unsigned lane = threadIdx.x & 31u, full = 0xffffffffu;
+  const int count = re - rs;
+  const bool in = (int)lane < count;
+  int idx = in ? t.leafIdx[rs + lane] : -1;
+  float2 c = in ? t.leafCtr[rs + lane] : make_float2(0.0f, 0.0f);
+  int base = 0;
+  if (lane == 0 && count > 2) base = atomicAdd(&t.rb[2], count - 2);
+  base = __shfl_sync(full, base, 0);
+  const int myFree = ((int)lane < count - 2) ? t.freeIds[base + lane] : -1;    // lane k holds the k-th reserved id
+  int nextFree = 0;                                                            // warp-uniform
+  int s = in ? 0 : (int)lane, e = in ? count : (int)lane;                      // current range of this lane (empty for idle lanes)
+  int node = rootNode, depth = 0, leafDepth = 0;
+  int recS = 0, recE = 0, recId = -1, recDepth = 0;                            // the internal node this lane finishes
+  while (__ballot_sync(full, e - s > 1)) {
+    const int n = e - s;
+    // center bounds of the range (:804-809)
+    float lox = c.x, loy = c.y, hix = c.x, hiy = c.y;
+    for (int j = 0; j < 32; j++) {
+      float cx = __shfl_sync(full, c.x, j), cy = __shfl_sync(full, c.y, j);
+      if (j >= s && j < e) { lox = lox < cx ? lox : cx; loy = loy < cy ? loy : cy; hix = hix > cx ? hix : cx; hiy = hiy > cy ? hiy : cy; }
+    }
+    bool f = false;
+    if (n > 2) { float dx = hix - lox, dy = hiy - loy; f = dx > dy ? (c.x < 0.5f * (lox + hix)) : (c.y < 0.5f * (loy + hiy)); }
+    const unsigned R = (e >= 32 ? full : ((1u << e) - 1u)) & ~((1u << s) - 1u);
+    const unsigned F = __ballot_sync(full, f) & R;
+    const int m = __popc(F);
+    int split = s + n / 2;
+    int partner = lane;
+    if (n > 2 && m > 0 && m < n) {
+      split = s + m;
+      const unsigned leftRegion = R & ((1u << split) - 1u);
+      const unsigned ML = ~F & leftRegion, MR = F & ~leftRegion;       // misplaced on the left / on the right
+      const unsigned me = 1u << lane;
+      if (ML & me) { int k = __popc(ML & (me - 1u)); unsigned x = MR; for (int i = 0; i < k; i++) x &= ~(1u << (31 - __clz(x))); partner = 31 - __clz(x); }
+      else if (MR & me) { int k = __popc(MR & ~(me | (me - 1u))); unsigned x = ML; for (int i = 0; i < k; i++) x &= x - 1u; partner = __ffs(x) - 1; }
+    }
+    idx = __shfl_sync(full, idx, partner); c.x = __shfl_sync(full, c.x, partner); c.y = __shfl_sync(full, c.y, partner);
+    // children (:905-930): a single element becomes the child itself, a longer range gets one of the reserved ids
+    const bool owner = n > 1 && (int)lane == s;
+    const bool needL = owner && split - s > 1, needR = owner && e - split > 1;
+    const unsigned BL = __ballot_sync(full, needL), BR = __ballot_sync(full, needR);
+    const unsigned below = (1u << lane) - 1u;
+    const int slotL = nextFree + __popc(BL & below) + __popc(BR & below), slotR = slotL + (needL ? 1 : 0);
+    nextFree += __popc(BL) + __popc(BR);
+    int newL = -1, newR = -1;
+    for (int j = 0; j < 32; j++) {                 // fetch reserved ids from the lanes that hold them
+      int wantL = __shfl_sync(full, needL ? slotL : -1, j), wantR = __shfl_sync(full, needR ? slotR : -1, j);
+      int gotL = __shfl_sync(full, myFree, wantL < 0 ? 0 : wantL), gotR = __shfl_sync(full, myFree, wantR < 0 ? 0 : wantR);
+      if ((int)lane == j) { newL = gotL; newR = gotR; }
+    }
+    const int idxAtSplit = __shfl_sync(full, idx, split < 32 ? split : 0);
+    int leftId = needL ? newL : idx, rightId = needR ? newR : idxAtSplit;
+    if (owner) { t.child[node] = make_int2(leftId, rightId); t.parent[leftId] = node; t.parent[rightId] = node; }
+    leftId = __shfl_sync(full, leftId, s < 32 ? s : 0); rightId = __shfl_sync(full, rightId, s < 32 ? s : 0);
+    if (n > 1) {
+      if ((int)lane == split) { recS = s; recE = e; recId = node; recDepth = depth; }
+      if ((int)lane < split) { e = split; node = leftId; } else { s = split; node = rightId; }
+      depth++;
+      if (e - s == 1) leafDepth = depth;
     }
   }
-  refitFromChildren(t, rootNode);
-  for (int k = 0; k < e; k++) { t.leafIdx[base + k] = li[k]; t.leafCtr[base + k] = lc[k]; }
+  // finish the new nodes from the final arrangement
+  float4 box = make_float4(0, 0, 0, 0); int h = 0; unsigned catLo = 0, catHi = 0;
+  if (in) { box = t.aabb[idx]; h = (int)(t.hf[idx] & 0xffffu); unsigned long long ct = t.cat[idx]; catLo = (unsigned)ct; catHi = (unsigned)(ct >> 32); }
+  Box acc; acc.lo = mk(0, 0); acc.hi = mk(0, 0); int accH = 0; unsigned accLo = 0, accHi = 0; bool first = true;
+  for (int j = 0; j < 32; j++) {
+    float4 bj = make_float4(__shfl_sync(full, box.x, j), __shfl_sync(full, box.y, j), __shfl_sync(full, box.z, j), __shfl_sync(full, box.w, j));
+    int hj = __shfl_sync(full, h, j) + __shfl_sync(full, leafDepth, j);
+    unsigned cl = __shfl_sync(full, catLo, j), ch = __shfl_sync(full, catHi, j);
+    if (recId >= 0 && j >= recS && j < recE) {
+      Box b = toBox(bj);
+      acc = first ? b : boxUnion(acc, b); first = false;
+      int hh = hj - recDepth; accH = accH > hh ? accH : hh;
+      accLo |= cl; accHi |= ch;
+    }
+  }
+  if (recId >= 0) {
+    t.aabb[recId] = fromBox(acc); t.hf[recId] = ((uint32_t)NODE_ALLOCATED << 16) | (uint32_t)accH;
+    t.cat[recId] = ((unsigned long long)accHi << 32) | accLo; t.user[recId] = -1;
+    if (recId != rootNode) t.visit[recId] = 0;
+  }
+  if (in) { t.leafIdx[rs + lane] = idx; t.leafCtr[rs + lane] = c; }
+  __threadfence();
+  __syncwarp();
 }
 
 // is `n` a frontier node of the rebuild (a "leaf" of BuildTree)?  :973-978
@@ -148,14 +201,30 @@ __device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeT
   }
   grid.sync();
   int level = 0;
+  unsigned long long tLoop = 0;
+  if (d.debugChecksums && tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tLoop));
   while (t.rb[3 + (level & 1)] > 0) {
     const int nextSlot = 3 + ((level + 1) & 1);
     // A: elements move to their (possibly new) range; bounds of the centers per active range  :804-809
-    for (int p = tid; p < L; p += stride) {
-      int s = t.segStart[p], e = t.recEnd[s];
-      if (p >= e) { s = e; t.segStart[p] = s; e = t.recEnd[s]; }
-      if (e - s > kSerialRange && t.recNode[s] >= 0) {
-        float2 c = t.leafCtr[p]; float* b = (float*)&t.recBox[s];
+    for (int p0 = tid - (tid & 31); p0 < L; p0 += stride) {      // warp-uniform trip count: the body uses warp votes
+      const int p = p0 + (tid & 31);
+      int s = -1; bool act = false; float2 c = make_float2(0.0f, 0.0f);
+      if (p < L) {
+        s = t.segStart[p]; int e = t.recEnd[s];
+        if (p >= e) { s = e; t.segStart[p] = s; e = t.recEnd[s]; }
+        act = e - s > kSerialRange && t.recNode[s] >= 0;
+        if (act) c = t.leafCtr[p];
+      }
+      const int s0 = __shfl_sync(0xffffffffu, s, 0);
+      if (__all_sync(0xffffffffu, act && s == s0)) {             // whole warp inside one range: one set of atomics per warp
+        float lx = c.x, ly = c.y, hx = c.x, hy = c.y;
+        for (int o = 16; o > 0; o >>= 1) {
+          float a = __shfl_xor_sync(0xffffffffu, lx, o); lx = lx < a ? lx : a; a = __shfl_xor_sync(0xffffffffu, ly, o); ly = ly < a ? ly : a;
+          a = __shfl_xor_sync(0xffffffffu, hx, o); hx = hx > a ? hx : a; a = __shfl_xor_sync(0xffffffffu, hy, o); hy = hy > a ? hy : a;
+        }
+        if ((tid & 31) == 0) { float* b = (float*)&t.recBox[s]; rbAtomicMinF(b + 0, lx); rbAtomicMinF(b + 1, ly); rbAtomicMaxF(b + 2, hx); rbAtomicMaxF(b + 3, hy); }
+      } else if (act) {
+        float* b = (float*)&t.recBox[s];
         rbAtomicMinF(b + 0, c.x); rbAtomicMinF(b + 1, c.y); rbAtomicMaxF(b + 2, c.x); rbAtomicMaxF(b + 3, c.y);
       }
     }
@@ -233,13 +302,17 @@ __device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeT
     grid.sync();
     level++;
   }
+  if (d.debugChecksums && tid == 0 && treeType == kDynamicBody) {
+    unsigned long long now; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+    d.sc->dbg[12] = level; d.sc->dbg[13] = L; d.sc->dbg[14] = now - tLoop; d.sc->dbg[15] = t.rb[5];
+  }
   // small ranges: sequential BuildTree, one thread per range, then completion upward
   const int nSerial = t.rb[5];
-  for (int k = tid; k < nSerial; k += stride) {
+  for (int k = tid >> 5; k < nSerial; k += stride >> 5) {       // one warp per range
     int s = t.serialList[k];
     int node = t.recNode[s];
-    rbBuildSerial(t, s, t.recEnd[s], node);
-    rbWalkUp(t, node);
+    rbBuildWarp(t, s, t.recEnd[s], node);
+    if ((threadIdx.x & 31) == 0) rbWalkUp(t, node);
   }
   if (tid == 0) t.meta[0] = t.rb[6];
 }

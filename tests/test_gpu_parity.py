@@ -84,4 +84,4 @@ def test_island_partition_valid_and_run_to_run_deterministic(monkeypatch):
     assert any(any(row) for row in a), "debug checksums not enabled"
     for step, (ra, rb) in enumerate(zip(a, b)):
         assert ra[10] == 0 and ra[11] == 0, f"step {step}: colour conflicts {ra[10]} partition errors {ra[11]}"
-        assert ra == rb, f"step {step}: phase checksums differ between two runs: slots {[k for k in range(16) if ra[k] != rb[k]]}"
+        assert ra[:12] == rb[:12], f"step {step}: phase checksums differ between two runs: slots {[k for k in range(12) if ra[k] != rb[k]]}"   # 12..15 hold timings
