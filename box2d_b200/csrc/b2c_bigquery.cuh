@@ -115,7 +115,7 @@ __device__ void phase_big_queries(cg::grid_group& grid, const WorldDev& d) {
       BigItem it = bigDecode(d, g0, g1, base + e);
       const TreeDev& t = d.trees[it.treeType];
       int a, b2;
-      bool f = boxOverlaps(toBox(t.aabb[it.leaf]), it.fat) && t.cat[it.leaf] != 0 &&
+      bool f = boxOverlaps(toBox(t.aabb[it.leaf]), it.fat) &&
                acceptPair(d, it.queryKey, it.queryKey & 3, it.queryShape, it.leaf, it.treeType, t.user[it.leaf], &a, &b2);
       d.bigFlag[e] = f ? 1 : 0; d.bigScan[e] = f ? 1 : 0;
     }

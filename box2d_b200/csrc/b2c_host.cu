@@ -425,7 +425,7 @@ int World::upload() {
     d.debugChecksums = getenv("B2CUDA_DEBUG_CHECKSUMS") ? 1 : 0;
     if (const char* e = getenv("B2CUDA_ISLAND_MAX_BODIES")) { int v = atoi(e); if (v >= 0 && v <= kIslandMaxBodies) d.islandMaxBodies = v; }
     if (const char* e = getenv("B2CUDA_BIG_QUERY_VISITS")) { int v = atoi(e); if (v > 0) d.bigQueryVisits = v; }
-    DA(d.moveBig, int, d.moveCapacity); DA(d.bigList, int, kMaxBigQueries); DA(d.bigSegStart, int, kMaxBigQueries + 1); DA(d.bigOff, int, kMaxBigQueries + 1);
+    DA(d.moveBig, int, d.moveCapacity); DA(d.moveHitBuf, int2, (size_t)d.moveCapacity * 4); DA(d.bigList, int, kMaxBigQueries); DA(d.bigSegStart, int, kMaxBigQueries + 1); DA(d.bigOff, int, kMaxBigQueries + 1);
     DA(d.bigScan, int, d.bigScratch); DA(d.bigFlag, uint8_t, d.bigScratch); DA(d.bigHits, int2, d.pairCapacity); }
   UP(d.moveArray, moveArray_);
   DA(d.cShape, int2, contactCap); DA(d.cBody, int2, contactCap); DA(d.cFlags, uint32_t, contactCap); DA(d.cColor, int, contactCap); DA(d.cGen, uint32_t, contactCap);

@@ -167,7 +167,12 @@ __device__ __forceinline__ bool acceptPair(const WorldDev& d, int queryKey, int 
 
 // DynamicTree.Query (src/DynamicTree.cs:531-557): explicit stack, child1 pushed first so child2 is visited first.
 // BUDGET: give up (return -1) after kBigQueryVisits node visits — the query is then answered by the leaf sweep below.
-template <bool FILL, bool BUDGET> __device__ inline int queryTree(const WorldDev& d, int treeType, Box fat, int queryKey, int queryType, int queryShape, int hitBase, int2* out, int outLast, int& visits) {
+constexpr int kHitBuf = 4;     // accepted hits kept from the count pass; queries with more re-traverse in the fill pass
+struct HitSink {               // where accepted hits of one query go
+  int2* out; int outLast;      // FILL: movePairs and the query's last slot (hits are written in reverse)
+  int2* buf;                   // count pass: first kHitBuf hits in hit order
+};
+template <bool FILL, bool BUDGET> __device__ inline int queryTree(const WorldDev& d, int treeType, Box fat, int queryKey, int queryType, int queryShape, int hitBase, const HitSink& sink, int& visits) {
   const TreeDev& t = d.trees[treeType];
   int root = t.meta[0];
   if (t.meta[1] == 0 || root == -1) return 0;
@@ -177,36 +182,38 @@ template <bool FILL, bool BUDGET> __device__ inline int queryTree(const WorldDev
   while (sp > 0) {
     int id = stack[--sp];
     if (BUDGET && ++visits > d.bigQueryVisits) return -1;
-    Box nb = toBox(t.aabb[id]);
-    if (!boxOverlaps(nb, fat)) continue;        // maskBits == DEFAULT_MASK_BITS: the category test always passes for non-zero categories
-    if (t.cat[id] == 0) continue;
-    uint32_t hf = t.hf[id];
-    if ((hf >> 16) & NODE_LEAF) {
+    float4 nb = t.aabb[id]; int2 c = t.child[id];      // independent loads; leaves have child (-1,-1)
+    if (!boxOverlaps(toBox(nb), fat)) continue;
+    // The reference also tests (categoryBits & maskBits) with maskBits = DEFAULT_MASK_BITS (:541): that only rejects
+    // category 0, and a category-0 leaf is rejected by shouldShapesCollide below, so the hit list is the same.
+    if (c.x == -1) {
       int a, b;
       if (acceptPair(d, queryKey, queryType, queryShape, id, treeType, t.user[id], &a, &b)) {
-        if (FILL) out[outLast - (hitBase + hits)] = make_int2(a, b);
+        int h = hitBase + hits;
+        if (FILL) sink.out[sink.outLast - h] = make_int2(a, b);
+        else if (h < kHitBuf) sink.buf[h] = make_int2(a, b);
         hits++;
       }
     } else {
-      int2 c = t.child[id];
       if (sp + 2 > kQueryStack) { atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); continue; }
       stack[sp++] = c.x; stack[sp++] = c.y;
     }
   }
   return hits;
 }
-template <bool FILL, bool BUDGET> __device__ inline int queryTrees(const WorldDev& d, Box fat, int queryKey, int type, int queryShape, int2* out, int outLast) {
+template <bool FILL, bool BUDGET> __device__ inline int queryTrees(const WorldDev& d, Box fat, int queryKey, int type, int queryShape, const HitSink& sink) {
   int count = 0, visits = 0, h;
   if (type == kDynamicBody) {
-    h = queryTree<FILL, BUDGET>(d, kKinematicBody, fat, queryKey, type, queryShape, count, out, outLast, visits); if (h < 0) return -1; count += h;
-    h = queryTree<FILL, BUDGET>(d, kStaticBody, fat, queryKey, type, queryShape, count, out, outLast, visits); if (h < 0) return -1; count += h;
+    h = queryTree<FILL, BUDGET>(d, kKinematicBody, fat, queryKey, type, queryShape, count, sink, visits); if (h < 0) return -1; count += h;
+    h = queryTree<FILL, BUDGET>(d, kStaticBody, fat, queryKey, type, queryShape, count, sink, visits); if (h < 0) return -1; count += h;
   }
-  h = queryTree<FILL, BUDGET>(d, kDynamicBody, fat, queryKey, type, queryShape, count, out, outLast, visits); if (h < 0) return -1; count += h;
+  h = queryTree<FILL, BUDGET>(d, kDynamicBody, fat, queryKey, type, queryShape, count, sink, visits); if (h < 0) return -1; count += h;
   return count;
 }
 
-// FindPairsTask (:197-232). FILL=false counts accepted hits per move entry; FILL=true writes them in contact-creation
-// order: move index ascending, within a query the REVERSE of the hit order (the C# result list is LIFO, :193-194,:251-262).
+// FindPairsTask (:197-232). FILL=false counts accepted hits per move entry (keeping the first kHitBuf); FILL=true writes
+// them in contact-creation order: move index ascending, within a query the REVERSE of the hit order (the C# result list
+// is LIFO, :193-194,:251-262). Accepted hits are NEW pairs only, so most queries have none and few have more than kHitBuf.
 template <bool FILL> __device__ void p_find_pairs(const WorldDev& d, int tid, int stride) {
   int n = d.sc->moveCount;
   for (int i = tid; i < n; i += stride) {
@@ -215,19 +222,25 @@ template <bool FILL> __device__ void p_find_pairs(const WorldDev& d, int tid, in
     if (FILL && d.moveBig[i] >= 0) continue;    // wide query: p_big_fill copies its hits
     if (queryKey != -1) {
       int type = queryKey & 3, id = queryKey >> 2;
-      Box fat = toBox(d.trees[type].aabb[id]);
-      int queryShape = d.trees[type].user[id];
+      HitSink sink; sink.out = d.movePairs; sink.outLast = 0; sink.buf = d.moveHitBuf + (size_t)i * kHitBuf;
       if (FILL) {
+        int begin = d.moveHitCount[i] + d.scanBlockSums[i / kCoopThreads];
         int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) / kCoopThreads] : d.sc->newPairCount;
+        if (end == begin) continue;
         if (end > d.pairCapacity) { atomicOr(&d.sc->errorFlags, (int)ERR_PAIR_CAPACITY); continue; }
-        queryTrees<true, false>(d, fat, queryKey, type, queryShape, d.movePairs, end - 1);
+        sink.outLast = end - 1;
+        if (end - begin <= kHitBuf) { for (int h = 0; h < end - begin; h++) d.movePairs[end - 1 - h] = sink.buf[h]; continue; }
+        Box fat = toBox(d.trees[type].aabb[id]);
+        queryTrees<true, false>(d, fat, queryKey, type, d.trees[type].user[id], sink);
       } else {
+        Box fat = toBox(d.trees[type].aabb[id]);
+        int queryShape = d.trees[type].user[id];
         int big = -1;
-        count = queryTrees<false, true>(d, fat, queryKey, type, queryShape, nullptr, 0);
+        count = queryTrees<false, true>(d, fat, queryKey, type, queryShape, sink);
         if (count < 0) {
           int slot = atomicAdd(&d.sc->bigQueryCount, 1);
           if (slot < kMaxBigQueries) { d.bigList[slot] = i; big = slot; count = 0; }
-          else count = queryTrees<false, false>(d, fat, queryKey, type, queryShape, nullptr, 0);
+          else count = queryTrees<false, false>(d, fat, queryKey, type, queryShape, sink);
         }
         d.moveBig[i] = big;
       }

@@ -139,6 +139,7 @@ struct WorldDev {
   // wide queries (a moved proxy whose fat box overlaps a large part of a tree) are answered by a grid-wide sweep over the
   // tree's leaves in DFS order instead of a one-thread traversal (b2c_bigquery.cuh)
   int* moveBig;        // per move entry: slot in bigList or -1
+  int2* moveHitBuf;    // [moveCapacity * kHitBuf] first accepted hits of each query, kept from the count pass
   int* bigList;        // [kMaxBigQueries] move indices
   int* bigSegStart;    // [kMaxBigQueries+1] start of each wide query's leaf segment in the sweep
   int* bigOff;         // [kMaxBigQueries+1] start of each wide query's hits in bigHits
