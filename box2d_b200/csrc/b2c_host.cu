@@ -102,12 +102,12 @@ void World::freeDevice() {
   allocs_.clear();
   if (hostScalars_) cudaFreeHost(hostScalars_);
   if (hBegin_) cudaFreeHost(hBegin_);
-  if (hEnd_) cudaFreeHost(hEnd_);
+  for (auto& e : hEnd_) { if (e) cudaFreeHost(e); e = nullptr; }
   if (hHit_) cudaFreeHost(hHit_);
   if (hJointEvents_) cudaFreeHost(hJointEvents_);
   if (hBodyRead_) cudaFreeHost(hBodyRead_);
   hBodyRead_ = nullptr;
-  hostScalars_ = nullptr; hBegin_ = hEnd_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
+  hostScalars_ = nullptr; hBegin_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
   for (auto& e : ev_) if (e) { cudaEventDestroy(e); e = nullptr; }
   for (auto& e : timer_) if (e) { cudaEventDestroy(e); e = nullptr; }
   if (stream_) { cudaStreamDestroy(stream_); stream_ = nullptr; }
@@ -432,7 +432,10 @@ int World::upload() {
   DA(d.cMat, float4, contactCap); DA(d.cMass, float4, contactCap); DA(d.cSim, int2, contactCap);
   DA(d.mN, float4, contactCap); DA(d.mA0, float4, contactCap); DA(d.mA1, float4, contactCap); DA(d.mB0, float4, contactCap); DA(d.mB1, float4, contactCap);
   DA(d.mC0, float4, contactCap); DA(d.mC1, float4, contactCap); DA(d.contactFree, int, contactCap);
-  DA(d.flagScan, int4, contactCap + 1); DA(d.opList, int, contactCap); DA(d.opDone, uint8_t, contactCap);
+  DA(d.flagScan, int4, contactCap + 1); DA(d.opList, int, contactCap); DA(d.opDone, uint8_t, contactCap); DA(d.opOv, uint8_t, contactCap);
+  d.ovCapacity = contactCap / 4 + 1024;
+  DA(d.ovList, int, d.ovCapacity); DA(d.cOvIndex, int, contactCap); DA(d.ovCons, OvConstraint, d.ovCapacity);
+  CK(cudaMemsetAsync(d.cOvIndex, 0xff, sizeof(int) * (size_t)contactCap, stream_));
   int cc = d.constraintCapacity;
   DA(d.sA, float4, cc); DA(d.sB, float4, cc); DA(d.sC, float4, cc); DA(d.sD, float4, cc); DA(d.sE, float4, cc); DA(d.sF, float4, cc);
   DA(d.sG, float4, cc); DA(d.sH, float4, cc); DA(d.sI, float4, cc); DA(d.sJ, float4, cc); DA(d.sContact, int, cc); DA(d.cConstraint, int, contactCap);
@@ -441,8 +444,6 @@ int World::upload() {
   DA(d.rootInfo, int, nAwake); DA(d.rootScan, int4, nAwake + 1); DA(d.islandBodyStart, int, nAwake + 1); DA(d.islandConStart, int, nAwake + 1);
   DA(d.islandColorOff, int, (size_t)(nAwake + 1) * (kGraphColorCount + 1)); DA(d.islandBodies, int, nAwake); DA(d.bodyLocal, int, nAwake);
   DA(d.freeBodies, int, nAwake); DA(d.bigBodies, int, nAwake); DA(d.kinematicUsed, uint8_t, nAwake); DA(d.sLocal, int2, cc);
-  DA(d.beginEvents, B2CContactTouchEvent, d.eventCapacity); DA(d.endEvents[0], B2CContactTouchEvent, d.eventCapacity);
-  DA(d.endEvents[1], B2CContactTouchEvent, d.eventCapacity); DA(d.hitEvents, B2CContactHitEvent, d.eventCapacity);
   DA(d.bodyEnlargedCount, int, nAwake + 1);
   DA(d.sc, Scalars, 1);
   int scanBlocks = std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, nAwake)) / 256 + 2;
@@ -450,9 +451,14 @@ int World::upload() {
   Scalars init; memset(&init, 0, sizeof(init));
   init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;
   CK(cudaMemcpyAsync(d.sc, &init, sizeof(init), cudaMemcpyHostToDevice, stream_));
-  CK(cudaHostAlloc((void**)&hBegin_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocDefault));
-  CK(cudaHostAlloc((void**)&hEnd_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocDefault));
-  CK(cudaHostAlloc((void**)&hHit_, sizeof(B2CContactHitEvent) * d.eventCapacity, cudaHostAllocDefault));
+  // contact events are written by the kernels straight into mapped pinned host memory (few per step; no copy, no extra sync)
+  CK(cudaHostAlloc((void**)&hBegin_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocMapped));
+  for (auto& e : hEnd_) CK(cudaHostAlloc((void**)&e, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocMapped));
+  CK(cudaHostAlloc((void**)&hHit_, sizeof(B2CContactHitEvent) * d.eventCapacity, cudaHostAllocMapped));
+  CK(cudaHostGetDevicePointer((void**)&d.beginEvents, hBegin_, 0));
+  for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.endEvents[k], hEnd_[k], 0));
+  CK(cudaHostGetDevicePointer((void**)&d.hitEvents, hHit_, 0));
+  d.bodyOut = nullptr;
   DA(dBodyRead_, B2CBodyRead, nBody);
   CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(nBody, 1), cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(nJoint, 1), cudaHostAllocDefault));
@@ -676,13 +682,12 @@ int World::getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B
   if (!eventsFetched_) {
     const Scalars& s = *hostScalars_;
     hBeginN_ = s.beginCount; hEndN_ = s.endCount[lastEndIndex_]; hHitN_ = s.hitCount;
-    if (hBeginN_) CK(cudaMemcpyAsync(hBegin_, d_.beginEvents, sizeof(B2CContactTouchEvent) * hBeginN_, cudaMemcpyDeviceToHost, stream_));
-    if (hEndN_) CK(cudaMemcpyAsync(hEnd_, d_.endEvents[lastEndIndex_], sizeof(B2CContactTouchEvent) * hEndN_, cudaMemcpyDeviceToHost, stream_));
-    if (hHitN_) CK(cudaMemcpyAsync(hHit_, d_.hitEvents, sizeof(B2CContactHitEvent) * hHitN_, cudaMemcpyDeviceToHost, stream_));
-    CK(cudaStreamSynchronize(stream_));
+    if (hBeginN_ > d_.eventCapacity) hBeginN_ = d_.eventCapacity;
+    if (hEndN_ > d_.eventCapacity) hEndN_ = d_.eventCapacity;
+    if (hHitN_ > d_.eventCapacity) hHitN_ = d_.eventCapacity;
     eventsFetched_ = true;
   }
-  *begin = hBegin_; *nb = hBeginN_; *end = hEnd_; *ne = hEndN_; *hit = hHit_; *nh = hHitN_;
+  *begin = hBegin_; *nb = hBeginN_; *end = hEnd_[lastEndIndex_]; *ne = hEndN_; *hit = hHit_; *nh = hHitN_;
   return B2C_OK;
 }
 

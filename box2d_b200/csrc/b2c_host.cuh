@@ -128,7 +128,7 @@ class World {
   int endIndex_ = 0;
   int stepCount_ = 0;
   bool eventsFetched_ = false;
-  B2CContactTouchEvent *hBegin_ = nullptr, *hEnd_ = nullptr; B2CContactHitEvent* hHit_ = nullptr; int* hJointEvents_ = nullptr;
+  B2CContactTouchEvent *hBegin_ = nullptr, *hEnd_[2] = {nullptr, nullptr}; B2CContactHitEvent* hHit_ = nullptr; int* hJointEvents_ = nullptr;   // event arrays: mapped pinned host memory the kernels write into
   int hBeginN_ = 0, hEndN_ = 0, hHitN_ = 0, hJointN_ = 0;
   int lastEndIndex_ = 0;
   static constexpr int kProfRing = 64, kProfEvents = 6;
@@ -139,7 +139,7 @@ class World {
   B2CProfile profile_{};
   bool profileValid_ = false;
   int coopBlocks_ = 0;
-  B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false;
+  B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false; bool streamBodies_ = false;   // streamBodies_: every step packs + copies the body records (set by the first GetBodyEvents)
   friend struct StepLauncher;
 };
 

@@ -82,7 +82,7 @@ __device__ void phase_islands(cg::grid_group& grid, const WorldDev& d) {
   grid.sync();
   // P1 union
   for (int i = tid; i < nContacts; i += stride) {
-    if (!(d.cFlags[i] & CF_TOUCHING) || d.cColor[i] >= kOverflowIndex) continue;
+    if (!(d.cFlags[i] & CF_TOUCHING)) continue;
     int2 sim = d.cSim[i];
     if (simIsDynamic(d, sim.x) && simIsDynamic(d, sim.y)) ufUnion(d.ufParent, sim.x, sim.y);
   }
@@ -102,10 +102,15 @@ __device__ void phase_islands(cg::grid_group& grid, const WorldDev& d) {
     if (!(d.cFlags[i] & CF_TOUCHING)) continue;
     int c = d.cColor[i];
     atomicAdd(&hist[c], 1);
-    if (c >= kOverflowIndex) continue;
     int2 sim = d.cSim[i];
     bool dynA = simIsDynamic(d, sim.x), dynB = simIsDynamic(d, sim.y);
     int r = d.ufParent[dynA ? sim.x : sim.y];
+    if (c >= kOverflowIndex) {                       // overflow constraints are solved serially by the grid path (b2c_overflow.cuh)
+      if (sim.x >= 0 && !dynA) d.kinematicUsed[sim.x] = 1;
+      if (sim.y >= 0 && !dynB) d.kinematicUsed[sim.y] = 1;
+      atomicAdd(&d.rootConCount[r], kForceBig);
+      continue;
+    }
     int add = 1;
     if (sim.x >= 0 && !dynA) { d.kinematicUsed[sim.x] = 1; add += kForceBig; }
     if (sim.y >= 0 && !dynB) { d.kinematicUsed[sim.y] = 1; add += kForceBig; }

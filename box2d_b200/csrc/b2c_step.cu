@@ -457,13 +457,19 @@ __device__ void p_events_finish(const WorldDev& d, const StepParams& sp, int4* t
   if (t.w > 0) s.graphDirty = 1;
 }
 
+}  // namespace b2c
+#include "b2c_overflow.cuh"
+namespace b2c {
+
 // AddContactToGraph / RemoveContactFromGraph (src/ConstraintGraph.cs:135-241) in ascending contactId order.
 // An op may run once it is the lowest pending op on both of its dynamic bodies, which yields exactly the sequential result.
 __device__ void p_color_ops(const WorldDev& d) {
   __shared__ int sRemaining;
   int n = d.sc->opCount;
   if (n == 0) return;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) d.opDone[k] = 0;
+  for (int k = threadIdx.x; k < n; k += blockDim.x) { d.opDone[k] = 0; d.opOv[k] = 0; }
+  __shared__ int sAnyOv;
+  if (threadIdx.x == 0) sAnyOv = 0;
   __syncthreads();
   int rounds = 0;
   while (true) {
@@ -500,8 +506,9 @@ __device__ void p_color_ops(const WorldDev& d) {
         if (typeA == kDynamicBody) d.bodyColorMask[b.x] = mA;
         if (typeB == kDynamicBody) d.bodyColorMask[b.y] = mB;
         d.cColor[id] = c;
-        if (c == kOverflowIndex) atomicOr(&d.sc->errorFlags, (int)ERR_OVERFLOW_COLOR);
+        if (c == kOverflowIndex) { d.opOv[k] = 1; sAnyOv = 1; }
       } else {                                     // remove
+        if (color == kOverflowIndex) { d.opOv[k] = 2; sAnyOv = 1; }
         if (color != kOverflowIndex) {
           if (typeA == kDynamicBody) d.bodyColorMask[b.x] &= ~(1u << color);
           if (typeB == kDynamicBody) d.bodyColorMask[b.y] &= ~(1u << color);
@@ -522,7 +529,7 @@ __device__ void p_color_ops(const WorldDev& d) {
     if (sRemaining == 0) break;
     __syncthreads();
   }
-  if (threadIdx.x == 0) d.sc->colorRounds = rounds;
+  if (threadIdx.x == 0) { d.sc->colorRounds = rounds; if (sAnyOv) ovReplayOps(d, n); }
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -969,6 +976,8 @@ __device__ void phase_prepare(const WorldDev& d, const StepParams& sp) {
   for (int t = gtid(); t < total; t += gsize()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
   int nj = d.jointColorStart[kGraphColorCount];
   for (int k = gtid(); k < nj; k += gsize()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
+  int nov = s.ovCount;
+  for (int k = gtid(); k < nov; k += gsize()) ovPrepare(d, sp, k);
 }
 
 // SolverTask substep loop (src/Solver.cs:599-727) as one persistent cooperative kernel: a grid-wide barrier replaces the
@@ -989,14 +998,17 @@ __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const
   const int tid = gtid(), stride = gsize();
   const int awake = s.bigBodyCount;               // bodies of grid-path islands (+ kinematic bodies some constraint reads)
   if (awake == 0 && activeCount == 0) return;     // everything lives in small islands / free bodies: no grid barrier at all
+  const int nov = s.ovCount;                      // overflow colour: one thread, array order, before the colours of each stage (:633-670)
   for (int sub = 0; sub < sp.subStepCount; sub++) {
     for (int i = tid; i < awake; i += stride) integrateVelocity(d, sp, d.bigBodies[i]);
     grid.sync();
+    if (nov > 0) { if (tid == 0) ovWarmStart(d, nov); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) warmStartJoint(d, d.joints[d.jointSorted[k]]);
       for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) warmStartContact(d, t);
       grid.sync();
     }
+    if (nov > 0) { if (tid == 0) ovSolve(d, sp, nov, true); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], true);
       for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<true>(d, sp, t);
@@ -1004,6 +1016,7 @@ __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const
     }
     for (int i = tid; i < awake; i += stride) integratePosition(d, sp, d.bigBodies[i]);
     grid.sync();
+    if (nov > 0) { if (tid == 0) ovSolve(d, sp, nov, true); grid.sync(); }      // Q4: the relax pass of the overflow colour keeps useBias
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], false);
       for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<false>(d, sp, t);
@@ -1012,6 +1025,7 @@ __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const
   }
   // restitution: skipped entirely (like every AllZeroW group) when no constraint has restitution (flag set by k_prepare)
   if (s.anyRestitution) {
+    if (nov > 0) { if (tid == 0) ovRestitution(d, sp, nov); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) restitutionContact(d, sp, t, sBegin[a], sEnd[a]);
       grid.sync();
@@ -1019,6 +1033,7 @@ __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const
   }
   for (int a = 0; a < activeCount; a++)
     for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) storeImpulses(d, t);
+  for (int k = tid; k < nov; k += stride) ovStoreImpulses(d, k);
 }
 
 }  // namespace b2c
@@ -1112,6 +1127,12 @@ __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int
       }
     }
     d.simFlags[i] = simFlags;
+    if (d.bodyOut) {                               // bodyMoveEvents (src/Solver.cs:432-438): one packed record per body
+      B2CBodyRead r;
+      r.transform.p = {xf.p.x, xf.p.y}; r.transform.q = {q.c, q.s}; r.center = {center.x, center.y};
+      r.linearVelocity = {s.x, s.y}; r.angularVelocity = s.z; r.flags = simFlags;
+      d.bodyOut[bodyId] = r;
+    }
     d.bodyEnlargedCount[i] = enlarged;
     if (enlarged) atomicAdd(&d.sc->enlargedShapeCount, enlarged);
   }
@@ -1299,7 +1320,8 @@ __device__ void dbgColorConflicts(cg::grid_group& grid, const WorldDev& d, int s
   for (int i = gtid(); i < n; i += gsize()) {
     if (!(d.cFlags[i] & CF_TOUCHING)) continue;
     int c = d.cColor[i];
-    if (c < 0 || c >= kOverflowIndex) { bad += 1000000; continue; }
+    if (c == kOverflowIndex) continue;             // solved serially, shares bodies by design
+    if (c < 0 || c > kOverflowIndex) { bad += 1000000; continue; }
     if (d.cConstraint[i] < 0 || d.sContact[d.cConstraint[i]] != i) bad += 1000;
     int2 sim = d.cSim[i];
     if (sim.x >= 0 && (fbits(d.st0[sim.x].w) & kDynamicFlag) && atomicAdd(&d.rootColorCount[sim.x * kGraphColorCount + c], 1) > 0) bad++;
@@ -1450,6 +1472,10 @@ int World::step(float timeStep, int subStepCount) {
   cudaEventRecord(pe[3], stream_);
   profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
   CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
+  if (streamBodies_) {                             // the caller reads body records every step: the copy rides behind the step
+    CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)d.bodyCapacity, cudaMemcpyDeviceToHost, stream_));
+    bodiesFetched_ = true;
+  }
   CK(cudaGetLastError());
   stepCount_++;
   return B2C_OK;
@@ -1464,6 +1490,7 @@ int World::getBodyEvents(const B2CBodyRead** records, int* count) {
     k_pack_bodies<<<gridFor(n, kThreads, 148 * 8), kThreads, 0, stream_>>>(d_, dBodyRead_);
     CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
     bodiesFetched_ = true;
+    streamBodies_ = true; d_.bodyOut = dBodyRead_;   // from now on FinalizeBodies keeps the records current and step() copies them
   }
   int rc = synchronize(); if (rc) return rc;
   *records = hBodyRead_; *count = d_.bodyCapacity;

@@ -65,6 +65,13 @@ struct JointDev {      // src/Joint.cs:74-133 + src/joints/RevoluteJoint.cs:6-31
   V2 linearImpulse; float springImpulse, motorImpulse, lowerImpulse, upperImpulse;
 };
 
+// scalar overflow constraint (src/ContactSolver.cs:9-37)
+struct OvPoint { V2 anchorA, anchorB; float baseSeparation, relativeVelocity, normalImpulse, tangentImpulse, totalNormalImpulse, normalMass, tangentMass; };
+struct OvConstraint {
+  int indexA, indexB; OvPoint p0, p1; V2 normal; float invMassA, invMassB, invIA, invIB;
+  float friction, restitution, tangentSpeed, rollingResistance, rollingMass, rollingImpulse; Softness softness; int pointCount;
+};
+
 struct Scalars {       // device scalars, mirrored to pinned host memory at the end of each step
   int moveCount, newPairCount, contactNext, contactFreeCount;
   int beginCount, endCount[2], hitCount;
@@ -77,7 +84,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
   int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
   int bigQueryCount, bigHitTotal, bigGroupTotal, staticRanksValid;   // wide broadphase queries (b2c_bigquery.cuh)
-  int rebuildLevels[3], pad0;
+  int rebuildLevels[3], ovCount;        // ovCount: contacts in the overflow colour
   unsigned long long dbg[16];           // order-independent state checksums per phase (B2CUDA_DEBUG_CHECKSUMS=1; b2cuda_world_debug_checksums)
 };
 
@@ -163,6 +170,10 @@ struct WorldDev {
   int4* flagScan;      // per contact slot: (begin, end, destroy, op) flags -> exclusive ranks
   int* opList;         // contact ids with a graph op (add/remove), ascending
   uint8_t* opDone;
+  uint8_t* opOv;       // per op: 1 = added to the overflow colour, 2 = removed from it
+  int* ovList;         // contact ids of the overflow colour in the reference's array order
+  int* cOvIndex;       // per contact slot: position in ovList (Contact.localIndex for that colour) or -1
+  OvConstraint* ovCons; int ovCapacity;
   // --- solver constraint planes, index = constraint (grouped by color) ---
   float4* sA; float4* sB; float4* sC; float4* sD; float4* sE; float4* sF; float4* sG; float4* sH; float4* sI; float4* sJ;
   int* sContact;       // contact slot of constraint t
@@ -188,6 +199,7 @@ struct WorldDev {
   // --- events ---
   B2CContactTouchEvent* beginEvents; B2CContactTouchEvent* endEvents[2]; B2CContactHitEvent* hitEvents;
   int eventCapacity;
+  B2CBodyRead* bodyOut;   // when set, FinalizeBodies also writes the packed per-body record (bodyMoveEvents equivalent)
   // --- finalize / refit scratch ---
   int* bodyEnlargedCount;   // per awake sim: enlarged shapes, then exclusive offsets
   Scalars* sc;

@@ -188,6 +188,28 @@ def mixed_drop(world, n=120, seed=7):
     return ground, paddle, bodies
 
 
+def overflow_plank(world, n=26):
+    """A long dynamic plank resting on n small dynamic boxes: the plank needs more than the 20 dynamic colours, so some
+    contacts land in the overflow colour (src/ConstraintGraph.cs:140) and are solved by the scalar overflow path."""
+    bd = api.default_body_def()
+    ground = world.CreateBody(bd)
+    sd = _shape_def()
+    half = 0.5 * n * 0.6 + 2.0
+    world.CreateSegmentShape(ground, sd, geo.Segment((-half, 0.0), (half, 0.0)))
+    bodies = []
+    for i in range(n):
+        b = _dynamic_body(world, (i - 0.5 * (n - 1)) * 0.6, 0.25)
+        world.CreatePolygonShape(b, sd, geo.MakeBox(0.25, 0.25))
+        bodies.append(b)
+    plank = _dynamic_body(world, 0.0, 0.62)
+    world.CreatePolygonShape(plank, sd, geo.MakeBox(0.5 * n * 0.6, 0.1))
+    for i in range(0, n, 3):        # a few circles dropped on the plank keep contacts changing
+        c = _dynamic_body(world, (i - 0.5 * (n - 1)) * 0.6, 1.2 + 0.05 * (i % 4))
+        world.CreateCircleShape(c, sd, geo.Circle((0.0, 0.0), 0.15))
+        bodies.append(c)
+    return ground, plank, bodies
+
+
 def batched_pyramids(world, n_worlds=8192, first=0, rows=10, pitch=15.0, cols=128):
     """BASELINE.json configs[4]: `n_worlds` independent 10-row pyramids (world index first..first+n), each on its own ground,
     x positions jittered per world by splitmix64(seed=world index) so worlds are not bit-copies."""
@@ -201,5 +223,6 @@ SCENES = {
     "tumbler": tumbler,
     "joint_grid": joint_grid,
     "mixed_drop": mixed_drop,
+    "overflow_plank": overflow_plank,
     "batched_pyramids": batched_pyramids,
 }

@@ -59,6 +59,7 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
         build(orc)
         worst = 0.0
         notes = []
+        max_overflow = 0
         for step in range(steps):
             if mutate is not None:
                 mutate(cuda, step)
@@ -71,6 +72,7 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
             for key in ("begin", "end"):
                 compare_struct(f"step{step}.{key}", a[key], b[key], report=rep)
             ca, cb = a["counters"], b["counters"]
+            max_overflow = max(max_overflow, ca.colorCounts[23])
             for f in ("contactCount", "touchingContactCount", "contactIdCapacity", "activeColorCount", "moveCount", "newPairCount"):
                 assert getattr(ca, f) == getattr(cb, f), f"step{step} counters.{f}: {getattr(ca, f)} vs {getattr(cb, f)}"
             assert list(ca.colorCounts) == list(cb.colorCounts), f"step{step} colorCounts {list(ca.colorCounts)} vs {list(cb.colorCounts)}"
@@ -87,7 +89,7 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
         c = cuda.GetCounters()
         co = orc.GetCounters()
         return dict(max_rel_err=worst, steps=steps, contacts=c.contactCount, touching=c.touchingContactCount, bodies=c.bodyCount,
-                    colors=c.activeColorCount, toi=c.toiCandidates, toi_oracle=co.toiCandidates)
+                    colors=c.activeColorCount, toi=c.toiCandidates, toi_oracle=co.toiCandidates, max_overflow=max_overflow)
     finally:
         cuda.Destroy()
         orc.Destroy()

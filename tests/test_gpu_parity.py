@@ -85,3 +85,17 @@ def test_island_partition_valid_and_run_to_run_deterministic(monkeypatch):
     for step, (ra, rb) in enumerate(zip(a, b)):
         assert ra[10] == 0 and ra[11] == 0, f"step {step}: colour conflicts {ra[10]} partition errors {ra[11]}"
         assert ra[:12] == rb[:12], f"step {step}: phase checksums differ between two runs: slots {[k for k in range(12) if ra[k] != rb[k]]}"   # 12..15 hold timings
+
+
+def test_overflow_colour_bit_exact():
+    """A body with more than 20 dynamic contacts: some land in the overflow colour and take the scalar, serial solver
+    (quirks Q2-Q4 included), then leave it again (swap-remove order of the overflow array)."""
+    res = parity.run_pair(lambda w: scenes.overflow_plank(w), steps=45, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    assert res["max_overflow"] > 0, "scene did not reach the overflow colour"
+
+
+def test_tumbler_dense_pile_long():
+    """Long enough for the pile to compact (contacts churn, colours fill up)."""
+    res = parity.run_pair(lambda w: scenes.tumbler(w, n=1500, half=5.0, pitch=0.22), steps=160, verbose=False)
+    assert res["max_rel_err"] == 0.0
