@@ -220,9 +220,10 @@ def b200_arm(args, rank, world_size, local_rank):
             "gpu_launches": KERNELS_PER_STEP * K, "clocks": sampler.result(),
             "batch_stats": {"bodies": int(stats[0]), "sum_v2": float(stats[1]), "max_speed": float(stats[2]), "min_y": float(stats[3])}}
     if world_size == 1 and not args.no_cpu:
-        v, sec, nb = cpu_oracle_run(args.workload, 20, args.cpu_steps)
+        cpu_warm = min(W, 60)
+        v, sec, nb = cpu_oracle_run(args.workload, cpu_warm, args.cpu_steps)
         line["cpu_baseline"] = {"value": v, "unit": "body-substeps/s", "cores": 1, "kind": "port",
-                                "sample": f"{args.cpu_steps} steps of {args.workload} ({nb} bodies) after 20 warm-up steps, 1 thread, {sec:.1f} s"}
+                                "sample": f"{args.cpu_steps} steps of {args.workload} ({nb} bodies) after {cpu_warm} warm-up steps, 1 thread, {sec:.1f} s"}
     print(json.dumps(line), flush=True)
     w.Destroy()
 

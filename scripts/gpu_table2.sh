@@ -1,6 +1,6 @@
 cd /root/repo
 wl=tumbler
-timeout 900 python bench.py --workload $wl --steps 60 --warmup 20 --cpu-steps 20 2>&1 | tail -1 > gpurun_out/table_$wl.json
+timeout 900 python bench.py --workload $wl --steps 200 --warmup 60 --cpu-steps 20 2>&1 | tail -1 > gpurun_out/table_$wl.json
 python -c "
 import json,sys
 d=json.load(open('gpurun_out/table_$wl.json'))
