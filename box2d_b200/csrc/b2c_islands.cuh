@@ -215,17 +215,26 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
   __syncthreads();
   const int K = colorOff[kGraphColorCount];
   BodyRows bs{s0, s1};
+  // active colours of this island, kept in registers: the stage loops below touch no memory for the loop control
+  int nActive = 0, myActive = -1;
+  for (int k = 0; k < kOverflowIndex; k++) {
+    int b = colorOff[k], e = colorOff[k + 1];
+    if (b == e) continue;
+    if (tid >= b && tid < e) myActive = nActive;
+    if (!CACHED && tid == 0) { colorOff[kGraphColorCount + 1 + 2 * nActive] = b; colorOff[kGraphColorCount + 2 + 2 * nActive] = e; }
+    nActive++;
+  }
+  const int* act = colorOff + kGraphColorCount + 1;          // (begin, end) per active colour, for islands too large for registers
   // PrepareContacts for this island: lanes are built straight into registers (CACHED) or into the planes (large islands).
   // Velocities read here are the pre-step ones: nothing has integrated yet.
-  Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int2 loc = make_int2(-1, -1); int myColor = -1, myContact = -1;
+  Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int2 loc = make_int2(-1, -1); int myContact = -1;
   bool anyRest = false;
   if (CACHED) {
     if (tid < K) {
       myContact = d.sContact[cBegin + tid];
       computeLane(d, sp, myContact, c, I, J); loc = d.sLocal[cBegin + tid];
       anyRest = !(c.restitution == 0.0f);
-      for (int k = 0; k < kOverflowIndex; k++) if (tid >= colorOff[k] && tid < colorOff[k + 1]) myColor = k;
-    }
+    } else myActive = -1;
   } else {
     for (int t = tid; t < K; t += T) { Lane l; float4 li, lj; computeLane(d, sp, d.sContact[cBegin + t], l, li, lj); writeLane(d, cBegin + t, l, li, lj); anyRest |= !(l.restitution == 0.0f); }
   }
@@ -233,16 +242,14 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
   for (int sub = 0; sub < sp.subStepCount; sub++) {
     if (tid < nb) s0[tid] = integrateVelocityRow(s0[tid], m, f, sp, &sf);
     __syncthreads();
-    for (int k = 0; k < kOverflowIndex; k++) {
-      if (colorOff[k] == colorOff[k + 1]) continue;
-      if (CACHED) { if (myColor == k) warmStartLane(bs, c, loc.x, loc.y, I, J.z); }
-      else for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) { Lane l; loadLane(d, cBegin + t, l, true); int2 lc = d.sLocal[cBegin + t]; warmStartLane(bs, l, lc.x, lc.y, d.sI[cBegin + t], d.sJ[cBegin + t].z); }
+    for (int a = 0; a < nActive; a++) {
+      if (CACHED) { if (myActive == a) warmStartLane(bs, c, loc.x, loc.y, I, J.z); }
+      else for (int t = act[2 * a] + tid; t < act[2 * a + 1]; t += T) { Lane l; loadLane(d, cBegin + t, l, true); int2 lc = d.sLocal[cBegin + t]; warmStartLane(bs, l, lc.x, lc.y, d.sI[cBegin + t], d.sJ[cBegin + t].z); }
       __syncthreads();
     }
-    for (int k = 0; k < kOverflowIndex; k++) {
-      if (colorOff[k] == colorOff[k + 1]) continue;
-      if (CACHED) { if (myColor == k) solveLane<true>(bs, sp, c, loc.x, loc.y, I, J); }
-      else for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) {
+    for (int a = 0; a < nActive; a++) {
+      if (CACHED) { if (myActive == a) solveLane<true>(bs, sp, c, loc.x, loc.y, I, J); }
+      else for (int t = act[2 * a] + tid; t < act[2 * a + 1]; t += T) {
         Lane l; loadLane(d, cBegin + t, l, false); int2 lc = d.sLocal[cBegin + t]; float4 li = d.sI[cBegin + t], lj = d.sJ[cBegin + t];
         solveLane<true>(bs, sp, l, lc.x, lc.y, li, lj); d.sI[cBegin + t] = li; d.sJ[cBegin + t] = lj;
       }
@@ -250,10 +257,9 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
     }
     if (tid < nb) { float4 a = s0[tid], b = s1[tid]; integratePositionRow(a, b, sp); s0[tid] = a; s1[tid] = b; }
     __syncthreads();
-    for (int k = 0; k < kOverflowIndex; k++) {
-      if (colorOff[k] == colorOff[k + 1]) continue;
-      if (CACHED) { if (myColor == k) solveLane<false>(bs, sp, c, loc.x, loc.y, I, J); }
-      else for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) {
+    for (int a = 0; a < nActive; a++) {
+      if (CACHED) { if (myActive == a) solveLane<false>(bs, sp, c, loc.x, loc.y, I, J); }
+      else for (int t = act[2 * a] + tid; t < act[2 * a + 1]; t += T) {
         Lane l; loadLane(d, cBegin + t, l, false); int2 lc = d.sLocal[cBegin + t]; float4 li = d.sI[cBegin + t], lj = d.sJ[cBegin + t];
         solveLane<false>(bs, sp, l, lc.x, lc.y, li, lj); d.sI[cBegin + t] = li; d.sJ[cBegin + t] = lj;
       }
@@ -285,7 +291,7 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
 
 __global__ void __launch_bounds__(kIslandThreads, 3) k_solver_islands(WorldDev d, StepParams sp) {
   __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
-  __shared__ int colorOff[kGraphColorCount + 1];
+  __shared__ int colorOff[kGraphColorCount + 1 + 2 * kGraphColorCount];   // colour offsets, then (begin, end) of the active colours
   int n = d.sc->islandCount;
   for (int g = blockIdx.x; g < n; g += gridDim.x) {
     int K = d.islandColorOff[g * (kGraphColorCount + 1) + kGraphColorCount];
