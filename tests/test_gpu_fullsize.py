@@ -1,0 +1,109 @@
+"""-m gpu: BASELINE.json configurations at FULL size, CUDA vs oracle through the C-ABI.
+
+north_star: pair sets, colours, manifold point counts / feature ids and begin/end event streams bit-exact over the first 10
+steps; transforms and velocities within 1e-5 relative after 1 step (here: bit-exact every step); kinetic energy and resting
+configuration within 1 % over 600 steps. Plus edge cases (empty world, static-only world, dt = 0, single free body)."""
+import numpy as np
+import pytest
+import parity
+from box2d_b200 import api, scenes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name,steps", [("many_pyramids", 10), ("large_pyramid", 10), ("joint_grid", 10), ("tumbler", 10)])
+def test_baseline_config_first_steps_bit_exact(name, steps):
+    res = parity.run_pair(lambda w: scenes.SCENES[name](w), steps=steps, tol=1e-5 if name == "joint_grid" else 0.0)
+    assert res["max_rel_err"] <= (1e-5 if name == "joint_grid" else 0.0)     # joint_grid: atan2f in the revolute spring/limit path
+    assert res["bodies"] >= 5000
+
+
+def test_batched_worlds_1024_bit_exact():
+    res = parity.run_pair(lambda w: scenes.batched_pyramids(w, n_worlds=1024), steps=6)
+    assert res["max_rel_err"] == 0.0
+
+
+def _kinetic_energy(bodies):
+    v = bodies["linearVelocity"]
+    return float(np.sum(v["x"].astype(np.float64) ** 2 + v["y"].astype(np.float64) ** 2) + np.sum(bodies["angularVelocity"].astype(np.float64) ** 2))
+
+
+def test_resting_pyramid_600_steps_energy_and_configuration():
+    """600 steps of a 20-row pyramid on both backends: the CUDA state must stay the oracle's state (bit-exact), hence kinetic
+    energy and the resting configuration agree to far better than the 1 % the north star asks for."""
+    from oracle_backend import OracleBackend
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    orc = api.World(OracleBackend(), scenes.world_def())
+    try:
+        scenes.large_pyramid(cuda, 20)
+        scenes.large_pyramid(orc, 20)
+        for step in range(600):
+            cuda.Step(1.0 / 60.0, 4)
+            orc.Step(1.0 / 60.0, 4)
+            if step % 100 == 99:
+                a, b = cuda.ReadBodies(), orc.ReadBodies()
+                assert a.tobytes() == b.tobytes(), f"step {step}: body state differs"
+        a, b = cuda.ReadBodies(), orc.ReadBodies()
+        ka, kb = _kinetic_energy(a), _kinetic_energy(b)
+        assert abs(ka - kb) <= 0.01 * max(kb, 1e-12)
+        pa, pb = a["transform"]["p"], b["transform"]["p"]
+        assert np.max(np.abs(pa["y"] - pb["y"])) <= 0.01 * 0.5 and np.max(np.abs(pa["x"] - pb["x"])) <= 0.01 * 0.5
+        assert ka < 1e-2, f"pyramid did not come to rest: kinetic measure {ka}"
+    finally:
+        cuda.Destroy()
+        orc.Destroy()
+
+
+def test_empty_world_and_static_only_world_step():
+    w = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        for _ in range(3):
+            w.Step(1.0 / 60.0, 4)
+        c = w.GetCounters()
+        assert c.bodyCount == 0 and c.contactCount == 0 and c.errorFlags == 0
+        b, e, h = w.GetContactEvents()
+        assert len(b) == 0 and len(e) == 0 and len(h) == 0
+    finally:
+        w.Destroy()
+    res = parity.run_pair(lambda wd: wd.CreateSegmentShape(wd.CreateBody(api.default_body_def()), scenes._shape_def(), __import__("box2d_b200").geometry.Segment((-5.0, 0.0), (5.0, 0.0))), steps=3)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_zero_dt_step_swaps_end_event_buffers_only():
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 6), steps=12, dt=1.0 / 60.0,
+                          mutate=None)
+    assert res["max_rel_err"] == 0.0
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        scenes.add_pyramid(cuda, 6)
+        cuda.Step(1.0 / 60.0, 4)
+        before = cuda.ReadBodies().tobytes()
+        cuda.Step(0.0, 4)
+        assert cuda.ReadBodies().tobytes() == before
+        b, e, h = cuda.GetContactEvents()
+        assert len(b) == 0
+    finally:
+        cuda.Destroy()
+
+
+def test_single_free_body_matches_closed_form():
+    """Free fall under the soft-step integrator: v_n = v_{n-1} + h g, p_n = p_{n-1} + h v_n (fp32, no damping)."""
+    w = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        b = scenes._dynamic_body(w, 0.0, 100.0)
+        w.CreateCircleShape(b, scenes._shape_def(), __import__("box2d_b200").geometry.Circle((0.0, 0.0), 0.5))
+        steps, sub = 30, 4
+        h = np.float32(np.float32(1.0 / 60.0) / np.float32(sub))
+        v, y = np.float32(0.0), np.float32(100.0)
+        for _ in range(steps):
+            w.Step(1.0 / 60.0, sub)
+            dy = np.float32(0.0)
+            for _ in range(sub):
+                v = np.float32(v + np.float32(h * np.float32(-10.0)))
+                dy = np.float32(dy + np.float32(h * v))
+            y = np.float32(y + dy)
+        body = w.ReadBodies()[b]
+        assert abs(float(body["linearVelocity"]["y"]) - float(v)) <= 1e-5 * abs(float(v))
+        assert abs(float(body["transform"]["p"]["y"]) - float(y)) <= 1e-5 * abs(float(y))
+    finally:
+        w.Destroy()
