@@ -970,9 +970,9 @@ __device__ __forceinline__ void integratePosition(const WorldDev& d, const StepP
   d.st1[i] = p;
 }
 
-__device__ void phase_prepare(const WorldDev& d, const StepParams& sp) {
+__device__ void phase_prepare(const WorldDev& d, const StepParams& sp, bool contactLanes) {
   const Scalars& s = *d.sc;
-  int total = s.smallConStart;                    // grid-path constraints only: small islands prepare their own lanes in registers
+  int total = contactLanes ? s.smallConStart : 0; // grid-path constraints only (and only when they do not fit one per thread): small islands prepare their own lanes in registers
   for (int t = gtid(); t < total; t += gsize()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
   int nj = d.jointColorStart[kGraphColorCount];
   for (int k = gtid(); k < nj; k += gsize()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
@@ -982,7 +982,9 @@ __device__ void phase_prepare(const WorldDev& d, const StepParams& sp) {
 
 // SolverTask substep loop (src/Solver.cs:599-727) as one persistent cooperative kernel: a grid-wide barrier replaces the
 // reference's per-stage spin barrier; empty colors cost nothing.
-__device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {
+// CACHED: the grid-path constraints fit one per thread, so each thread builds its lane in registers (PrepareContacts fused in,
+// as in the island kernel) and keeps it there for the whole step: a stage then loads only the two body rows after the barrier.
+template <bool CACHED> __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {
   const Scalars& s = *d.sc;
   __shared__ int sBegin[kGraphColorCount], sEnd[kGraphColorCount], sJBegin[kGraphColorCount], sJEnd[kGraphColorCount], sActiveCount;
   if (threadIdx.x == 0) {
@@ -999,19 +1001,32 @@ __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const
   const int awake = s.bigBodyCount;               // bodies of grid-path islands (+ kinematic bodies some constraint reads)
   if (awake == 0 && activeCount == 0) return;     // everything lives in small islands / free bodies: no grid barrier at all
   const int nov = s.ovCount;                      // overflow colour: one thread, array order, before the colours of each stage (:633-670)
+  Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int myA = -1, myContact = -1;
+  const BodyRows bs{d.st0, d.st1};
+  if (CACHED) {
+    if (tid < s.smallConStart) myContact = d.sContact[tid];
+    if (myContact >= 0) {
+      computeLane(d, sp, myContact, c, I, J);      // reads pre-step velocities: the barrier below keeps IntegrateVelocities behind it
+      if (!(c.restitution == 0.0f)) d.sc->anyRestitution = 1;
+      for (int a = 0; a < activeCount; a++) if (tid >= sBegin[a] && tid < sEnd[a]) myA = a;
+    }
+    grid.sync();
+  }
   for (int sub = 0; sub < sp.subStepCount; sub++) {
     for (int i = tid; i < awake; i += stride) integrateVelocity(d, sp, d.bigBodies[i]);
     grid.sync();
     if (nov > 0) { if (tid == 0) ovWarmStart(d, nov); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) warmStartJoint(d, d.joints[d.jointSorted[k]]);
-      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) warmStartContact(d, t);
+      if (CACHED) { if (myA == a) warmStartLane(bs, c, c.indexA, c.indexB, I, J.z); }
+      else for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) warmStartContact(d, t);
       grid.sync();
     }
     if (nov > 0) { if (tid == 0) ovSolve(d, sp, nov, true); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], true);
-      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<true>(d, sp, t);
+      if (CACHED) { if (myA == a) solveLane<true>(bs, sp, c, c.indexA, c.indexB, I, J); }
+      else for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<true>(d, sp, t);
       grid.sync();
     }
     for (int i = tid; i < awake; i += stride) integratePosition(d, sp, d.bigBodies[i]);
@@ -1019,19 +1034,22 @@ __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const
     if (nov > 0) { if (tid == 0) ovSolve(d, sp, nov, true); grid.sync(); }      // Q4: the relax pass of the overflow colour keeps useBias
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], false);
-      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<false>(d, sp, t);
+      if (CACHED) { if (myA == a) solveLane<false>(bs, sp, c, c.indexA, c.indexB, I, J); }
+      else for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) solveContact<false>(d, sp, t);
       grid.sync();
     }
   }
   // restitution: skipped entirely (like every AllZeroW group) when no constraint has restitution (flag set by k_prepare)
   if (s.anyRestitution) {
+    if (CACHED) { if (myContact >= 0) writeLane(d, tid, c, I, J); grid.sync(); }      // restitution works on 8-lane groups of the planes
     if (nov > 0) { if (tid == 0) ovRestitution(d, sp, nov); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) restitutionContact(d, sp, t, sBegin[a], sEnd[a]);
       grid.sync();
     }
   }
-  for (int a = 0; a < activeCount; a++)
+  if (CACHED && !s.anyRestitution) { if (myContact >= 0) storeImpulsesRegs(d, myContact, I, J, c.relVel1, c.relVel2); }
+  else for (int a = 0; a < activeCount; a++)
     for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) storeImpulses(d, t);
   for (int k = tid; k < nov; k += stride) ovStoreImpulses(d, k);
 }
@@ -1377,11 +1395,12 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   phase_islands(grid, d);
   if (dirty) grid.sync();
   const bool gridWork = s.smallConStart > 0 || d.jointColorStart[kGraphColorCount] > 0 || s.bigBodyCount > 0;
-  if (gridWork) { phase_prepare(d, sp); grid.sync(); }
+  const bool cachedLanes = s.smallConStart <= gsize();   // one grid-path constraint per thread: lanes stay in registers
+  if (gridWork) { phase_prepare(d, sp, !cachedLanes); if (!cachedLanes) grid.sync(); }
   stamp(d, 3);
   dbgLanes(d, 3, true); dbgBodies(d, 4); dbgColorConflicts(grid, d, 10);
   if (d.debugChecksums) grid.sync();
-  if (gridWork) phase_solver_grid(grid, d, sp);
+  if (gridWork) { if (cachedLanes) phase_solver_grid<true>(grid, d, sp); else phase_solver_grid<false>(grid, d, sp); }
   stamp(d, 4);
   if (d.debugChecksums) { grid.sync(); dbgBodies(d, 5); dbgLanes(d, 6, false); dbgContacts(d, 7); }
   if (gtid() == 0) { for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k]; s.phaseAcc[4] += s.phaseStamp[5] - s.phaseStamp[1]; }
