@@ -139,7 +139,7 @@ class World {
   B2CProfile profile_{};
   bool profileValid_ = false;
   int coopBlocks_ = 0;
-  B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false; bool streamBodies_ = false;   // streamBodies_: every step packs + copies the body records (set by the first GetBodyEvents)
+  B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false; bool streamBodies_ = false; int islandMode_ = 0;   // 0 auto, 1 CTA per island, 2 warp per island   // streamBodies_: every step packs + copies the body records (set by the first GetBodyEvents)
   friend struct StepLauncher;
 };
 

@@ -289,11 +289,17 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(kIslandThreads, 3) k_solver_islands(WorldDev d, StepParams sp) {
+}  // namespace b2c
+#include "b2c_islands_warp.cuh"
+namespace b2c {
+
+// skipWarpEligible: this step's small islands are solved by k_solver_islands_warp; only the ones that do not fit a slice stay here
+__global__ void __launch_bounds__(kIslandThreads, 3) k_solver_islands(WorldDev d, StepParams sp, int skipWarpEligible) {
   __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
   __shared__ int colorOff[kGraphColorCount + 1 + 2 * kGraphColorCount];   // colour offsets, then (begin, end) of the active colours
   int n = d.sc->islandCount;
   for (int g = blockIdx.x; g < n; g += gridDim.x) {
+    if (skipWarpEligible && warpIslandEligible(d, g)) continue;
     int K = d.islandColorOff[g * (kGraphColorCount + 1) + kGraphColorCount];
     if (K <= (int)blockDim.x) runIsland<true>(d, sp, g, s0, s1, colorOff);
     else runIsland<false>(d, sp, g, s0, s1, colorOff);

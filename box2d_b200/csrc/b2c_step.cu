@@ -1476,6 +1476,8 @@ int World::step(float timeStep, int subStepCount) {
     for (int o : occ) if (o < 1) return fail(B2C_E_CUDA, "a cooperative phase kernel cannot be made resident");
     cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device_));
     coopBlocks_ = prop.multiProcessorCount;       // one 512-thread CTA per SM: the barrier cost grows with CTA count
+    CK(cudaFuncSetAttribute(k_solver_islands_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kWarpIslandsPerCta * sizeof(WarpIslandSlice))));
+    if (const char* e = getenv("B2CUDA_ISLAND_MODE")) islandMode_ = !strcmp(e, "cta") ? 1 : !strcmp(e, "warp") ? 2 : 0;   // tests force a variant
     if (coopBlocks_ < 3) return fail(B2C_E_CUDA, "device too small");
   }
   const dim3 cgrid(coopBlocks_), cblock(kCoopThreads);
@@ -1483,7 +1485,11 @@ int World::step(float timeStep, int subStepCount) {
   cudaEventRecord(pe[0], stream_);
   { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
   cudaEventRecord(pe[1], stream_);
-  k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp);
+  // few islands: one CTA each (shortest stage chain); thousands (batched worlds): one warp each (b2c_islands_warp.cuh).
+  // The count comes from the last step whose scalars reached the host; either variant is correct for any count.
+  int warpMode = islandMode_ == 2 || (islandMode_ == 0 && hostScalars_->islandCount >= 8 * coopBlocks_);
+  if (warpMode) k_solver_islands_warp<<<coopBlocks_, 32 * kWarpIslandsPerCta, kWarpIslandsPerCta * sizeof(WarpIslandSlice), stream_>>>(d, sp);
+  k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp, warpMode);
   cudaEventRecord(pe[2], stream_);
   lastEndIndex_ = endIndex_;
   endIndex_ = 1 - endIndex_;

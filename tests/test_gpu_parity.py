@@ -99,3 +99,14 @@ def test_tumbler_dense_pile_long():
     """Long enough for the pile to compact (contacts churn, colours fill up)."""
     res = parity.run_pair(lambda w: scenes.tumbler(w, n=1500, half=5.0, pitch=0.22), steps=160, verbose=False)
     assert res["max_rel_err"] == 0.0
+
+
+@pytest.mark.parametrize("scene,steps", [("pyramids", 25), ("mixed", 60), ("tumbler", 40)])
+def test_warp_per_island_variant_bit_exact(scene, steps, monkeypatch):
+    """Force the throughput variant of the island solver (one warp per island, lanes in shared memory)."""
+    monkeypatch.setenv("B2CUDA_ISLAND_MODE", "warp")
+    build = {"pyramids": lambda w: scenes.batched_pyramids(w, n_worlds=64),
+             "mixed": lambda w: scenes.mixed_drop(w),
+             "tumbler": lambda w: scenes.tumbler(w, n=600, half=6.0)}[scene]
+    res = parity.run_pair(build, steps=steps, verbose=True)
+    assert res["max_rel_err"] == 0.0
