@@ -354,13 +354,31 @@ __device__ __forceinline__ void storePoint(const MPoint& p, float4* a, float4* b
   *c = make_float4(p.point.x, p.point.y, p.normalVelocity, __uint_as_float((p.id & 0xffffu) | (p.persisted << 16)));
 }
 
+__device__ __forceinline__ void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 __device__ void p_collide(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.sc->contactNext;
+  // A thread that owns several slots (batched worlds: ~16 per thread) walks a chain of dependent loads per slot
+  // (slot -> shape ids -> fat boxes / shape rows / body rows). The ids of the NEXT slot are loaded one iteration early and
+  // everything they point to is requested from L2 while the current manifold is computed.
+  uint32_t nextFlags = 0; int2 nextSh = make_int2(0, 0), nextBd = make_int2(0, 0);
+  if (tid < n) { nextFlags = d.cFlags[tid]; nextSh = d.cShape[tid]; nextBd = d.cBody[tid]; }
   for (int i = tid; i < n; i += stride) {
-    uint32_t flags = d.cFlags[i];
+    uint32_t flags = nextFlags;
+    const int2 curSh = nextSh, curBd = nextBd;
+    const int j = i + stride;
+    if (j < n) {
+      nextFlags = d.cFlags[j]; nextSh = d.cShape[j]; nextBd = d.cBody[j];
+      if (nextFlags & CF_ALIVE) {
+        prefetchL2(&d.shapeFat[nextSh.x]); prefetchL2(&d.shapeFat[nextSh.y]);
+        prefetchL2(&d.shapes[nextSh.x]); prefetchL2((const char*)&d.shapes[nextSh.x] + 128);
+        prefetchL2(&d.shapes[nextSh.y]); prefetchL2((const char*)&d.shapes[nextSh.y] + 128);
+        prefetchL2(&d.bodyXf[nextBd.x]); prefetchL2(&d.bodyXf[nextBd.y]); prefetchL2(&d.bodyMass[nextBd.x]); prefetchL2(&d.bodyMass[nextBd.y]);
+        prefetchL2(&d.mN[j]); prefetchL2(&d.mA0[j]); prefetchL2(&d.mA1[j]); prefetchL2(&d.mB0[j]); prefetchL2(&d.mB1[j]); prefetchL2(&d.mC0[j]); prefetchL2(&d.mC1[j]);
+      }
+    }
     int4 fs = make_int4(0, 0, 0, 0);
     if (flags & CF_ALIVE) {
-      int2 sh = d.cShape[i];
+      int2 sh = curSh;
       bool overlap = boxOverlaps(toBox(d.shapeFat[sh.x]), toBox(d.shapeFat[sh.y]));
       bool wasTouching = (flags & CF_TOUCHING) != 0;
       bool events = (flags & CF_ENABLE_CONTACT_EVENTS) != 0;
@@ -370,7 +388,7 @@ __device__ void p_collide(const WorldDev& d, const StepParams& sp, int tid, int 
         if (wasTouching) { fs.w = 1; if (events) fs.y = 1; }     // graph removal + end event (DestroyContact :247-254)
       } else {
         const ShapeDev& sa = d.shapes[sh.x]; const ShapeDev& sb = d.shapes[sh.y];
-        int2 bd = d.cBody[i];
+        int2 bd = curBd;
         float4 massA = d.bodyMass[bd.x], massB = d.bodyMass[bd.y];
         d.cSim[i] = make_int2(d.bodySim[bd.x], d.bodySim[bd.y]);
         d.cMass[i] = make_float4(massA.x, massA.y, massB.x, massB.y);
