@@ -401,6 +401,7 @@ int World::upload() {
     DA(td.segStart, int, cap); DA(td.recEnd, int, cap + 1); DA(td.recNode, int, cap + 1); DA(td.recSplit, int, cap + 1); DA(td.recBox, float4, cap + 1);
     DA(td.flagScan, int, cap + 1); DA(td.flagArr, int, cap + 1); DA(td.pairR, int, cap + 1); DA(td.freeIds, int, cap + 1); DA(td.subCount, int, cap);
     DA(td.visit, int, cap); DA(td.serialList, int, cap + 1); DA(td.rb, int, 8);
+    DA(td.recEnd2, int, cap + 1); DA(td.recNode2, int, cap + 1); DA(td.recBox2, float4, cap + 1); DA(td.recM, int, cap + 1); DA(td.serEnd, int, cap + 1); DA(td.serNode, int, cap + 1);
     UP(td.aabb, h.aabb); UP(td.child, h.child); UP(td.parent, h.parent); UP(td.hf, h.hf); UP(td.cat, h.cat); UP(td.user, h.user);
     std::vector<uint8_t> mv(cap, 0);
     for (size_t k = 0; k < moved_[t].size() && k < (size_t)cap; k++) mv[k] = moved_[t][k];

@@ -28,7 +28,7 @@ __device__ __forceinline__ int rbAllocNode(const TreeDev& t) { int id = t.freeId
 
 // bottom-up completion: called once per finished child; the second arrival at a node computes it and continues upward
 __device__ void rbWalkUp(const TreeDev& t, int cur) {
-  while (true) {
+  for (int guard = 0; guard < 4096; guard++) {     // a tree is never this deep; the bound turns a corrupted parent chain into a stop, not a hang
     int p = t.parent[cur];
     if (p == -1) return;
     __threadfence();
@@ -60,7 +60,7 @@ __device__ void rbBuildWarp(const TreeDev& t, int rs, int re, int rootNode) {
   int s = in ? 0 : (int)lane, e = in ? count : (int)lane;                      // current range of this lane (empty for idle lanes)
   int node = rootNode, depth = 0, leafDepth = 0;
   int recS = 0, recE = 0, recId = -1, recDepth = 0;                            // the internal node this lane finishes
-  while (__ballot_sync(full, e - s > 1)) {
+  for (int guard = 0; guard < 32 && __ballot_sync(full, e - s > 1); guard++) {     // <= 31 levels for 32 elements
     const int n = e - s;
     // center bounds of the range (:804-809)
     float lox = c.x, loy = c.y, hix = c.x, hiy = c.y;
@@ -157,6 +157,7 @@ __device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeT
   // R0
   for (int n = tid; n < cap; n += stride) { t.visit[n] = 0; t.subCount[n] = 0; }
   if (tid < 8) t.rb[tid] = 0;
+  if (tid == 0) t.recBox[0] = make_float4(FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX);
   grid.sync();
   // R1: doomed internal nodes -> freeIds; frontier subtree counts bottom-up
   for (int n = tid; n < cap; n += stride) {
@@ -186,118 +187,123 @@ __device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeT
     while (true) { int p = t.parent[cur]; if (p == -1) break; int2 c = t.child[p]; if (c.y == cur) r += t.subCount[c.x]; cur = p; }
     t.leafIdx[r] = n;
     float4 a = t.aabb[n];
-    t.leafCtr[r] = make_float2(0.5f * (a.x + a.z), 0.5f * (a.y + a.w));
+    float2 ctr = make_float2(0.5f * (a.x + a.z), 0.5f * (a.y + a.w));
+    t.leafCtr[r] = ctr;
     t.segStart[r] = 0;
+    float* b = (float*)&t.recBox[0];               // center bounds of the root range (first level's pivot)
+    rbAtomicMinF(b + 0, ctr.x); rbAtomicMinF(b + 1, ctr.y); rbAtomicMaxF(b + 2, ctr.x); rbAtomicMaxF(b + 3, ctr.y);
   }
   grid.sync();
   if (t.rb[1] != L - 1) { if (tid == 0) atomicOr(&d.sc->errorFlags, (int)ERR_TREE); return; }
   // R3: root range; the doomed nodes become the pool of new internal nodes
+  int* const recEndP[2] = {t.recEnd, t.recEnd2}; int* const recNodeP[2] = {t.recNode, t.recNode2}; float4* const recBoxP[2] = {t.recBox, t.recBox2};
   if (tid == 0) {
     d.sc->rebuildLeafCount[treeType] = L;
     int node0 = rbAllocNode(t);
     t.rb[6] = node0;
-    t.recEnd[0] = L; t.recNode[0] = node0; t.recBox[0] = make_float4(FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX);
-    if (L > kSerialRange) t.rb[3] = 1; else { t.serialList[0] = 0; t.rb[5] = 1; }
+    t.recEnd[0] = L; t.recNode[0] = node0;
+    if (L > kSerialRange) t.rb[3] = 1; else { t.serialList[0] = 0; t.serEnd[0] = L; t.serNode[0] = node0; t.rb[5] = 1; }
   }
   grid.sync();
+  // Level loop, 4 grid barriers per level. Range records (end, node, center bounds) are double-buffered by level parity,
+  // keyed by the range's first position; segStart[p] is the range an element is in, or -1 once its range is final
+  // (a single element, or <= kSerialRange elements that a warp finishes later).
   int level = 0;
   unsigned long long tLoop = 0;
   if (d.debugChecksums && tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tLoop));
+  __shared__ int rbWarpSums[32];
   while (t.rb[3 + (level & 1)] > 0) {
-    const int nextSlot = 3 + ((level + 1) & 1);
-    // A: elements move to their (possibly new) range; bounds of the centers per active range  :804-809
-    for (int p0 = tid - (tid & 31); p0 < L; p0 += stride) {      // warp-uniform trip count: the body uses warp votes
-      const int p = p0 + (tid & 31);
-      int s = -1; bool act = false; float2 c = make_float2(0.0f, 0.0f);
-      if (p < L) {
-        s = t.segStart[p]; int e = t.recEnd[s];
-        if (p >= e) { s = e; t.segStart[p] = s; e = t.recEnd[s]; }
-        act = e - s > kSerialRange && t.recNode[s] >= 0;
-        if (act) c = t.leafCtr[p];
-      }
-      const int s0 = __shfl_sync(0xffffffffu, s, 0);
-      if (__all_sync(0xffffffffu, act && s == s0)) {             // whole warp inside one range: one set of atomics per warp
-        float lx = c.x, ly = c.y, hx = c.x, hy = c.y;
-        for (int o = 16; o > 0; o >>= 1) {
-          float a = __shfl_xor_sync(0xffffffffu, lx, o); lx = lx < a ? lx : a; a = __shfl_xor_sync(0xffffffffu, ly, o); ly = ly < a ? ly : a;
-          a = __shfl_xor_sync(0xffffffffu, hx, o); hx = hx > a ? hx : a; a = __shfl_xor_sync(0xffffffffu, hy, o); hy = hy > a ? hy : a;
+    const int par = level & 1, nxt = par ^ 1, nextSlot = 3 + nxt;
+    const int* recEnd = recEndP[par]; const int* recNode = recNodeP[par]; const float4* recBox = recBoxP[par];
+    // P1: "< pivot" flag of every element (:810-845), fused into the first pass of the prefix sum
+    {
+      const int chunk = blockDim.x, chunks = (L + chunk - 1) / chunk;
+      for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+        int i = c * chunk + threadIdx.x, f = 0;
+        if (i < L) {
+          int sg = t.segStart[i];
+          if (sg >= 0) {
+            float4 b = recBox[sg]; float2 ctr = t.leafCtr[i];
+            float dx = b.z - b.x, dy = b.w - b.y;
+            f = dx > dy ? (ctr.x < 0.5f * (b.x + b.z)) : (ctr.y < 0.5f * (b.y + b.w));
+          }
+          t.flagArr[i] = f;
         }
-        if ((tid & 31) == 0) { float* b = (float*)&t.recBox[s]; rbAtomicMinF(b + 0, lx); rbAtomicMinF(b + 1, ly); rbAtomicMaxF(b + 2, hx); rbAtomicMaxF(b + 3, hy); }
-      } else if (act) {
-        float* b = (float*)&t.recBox[s];
-        rbAtomicMinF(b + 0, c.x); rbAtomicMinF(b + 1, c.y); rbAtomicMaxF(b + 2, c.x); rbAtomicMaxF(b + 3, c.y);
+        int total, inc = blockInclusive(f, rbWarpSums, &total);
+        if (i < L) t.flagScan[i] = inc - f;
+        if (threadIdx.x == 0) d.scanBlockSums[c] = total;
       }
-    }
-    if (tid == 0) t.rb[nextSlot] = 0;
-    grid.sync();
-    // B1: "< pivot" flags  :810-845
-    for (int p = tid; p < L; p += stride) {
-      int s = t.segStart[p], e = t.recEnd[s], f = 0;
-      if (e - s > kSerialRange && t.recNode[s] >= 0) {
-        float4 b = t.recBox[s]; float2 c = t.leafCtr[p];
-        float dx = b.z - b.x, dy = b.w - b.y;
-        f = dx > dy ? (c.x < 0.5f * (b.x + b.z)) : (c.y < 0.5f * (b.y + b.w));
+      if (tid == 0) t.rb[nextSlot] = 0;
+      grid.sync();
+      if (blockIdx.x == 0) {
+        int carry = 0;
+        for (int base = 0; base < chunks; base += chunk) {
+          int i = base + threadIdx.x, v = i < chunks ? d.scanBlockSums[i] : 0;
+          int total, inc = blockInclusive(v, rbWarpSums, &total);
+          if (i < chunks) d.scanBlockSums[i] = carry + inc - v;
+          carry += total;
+        }
+        if (threadIdx.x == 0) t.flagScan[cap] = carry;
       }
-      t.flagScan[p] = f; t.flagArr[p] = f;
+      grid.sync();
     }
-    grid.sync();
-    gridScan<int>(grid, t.flagScan, d.scanBlockSums, L, &t.flagScan[cap]);
-    // B2: k-th misplaced element from the right records its position
     const int total = t.flagScan[cap];
+    // P2: split of every range; misplaced elements of the right part record their position; the range's owner creates
+    //     the two child ranges (:905-930) in the other parity's records
     for (int p = tid; p < L; p += stride) {
-      int s = t.segStart[p], e = t.recEnd[s];
-      if (!(e - s > kSerialRange && t.recNode[s] >= 0)) continue;
-      int Fs = t.flagScan[s] + d.scanBlockSums[s / kCoopThreads];
-      int Fe = e < L ? t.flagScan[e] + d.scanBlockSums[e / kCoopThreads] : total;
-      int Fp = t.flagScan[p] + d.scanBlockSums[p / kCoopThreads];
-      int m = Fe - Fs, left = Fp - Fs;
-      if (p == s) t.recSplit[s] = (m > 0 && m < e - s) ? s + m : s + (e - s) / 2;
-      if (p >= s + m && t.flagArr[p]) t.pairR[s + (m - left - 1)] = p;
-    }
-    grid.sync();
-    // B3: k-th misplaced element from the left swaps with it
-    for (int p = tid; p < L; p += stride) {
-      int s = t.segStart[p], e = t.recEnd[s];
-      if (!(e - s > kSerialRange && t.recNode[s] >= 0)) continue;
-      int Fs = t.flagScan[s] + d.scanBlockSums[s / kCoopThreads];
-      int Fe = e < L ? t.flagScan[e] + d.scanBlockSums[e / kCoopThreads] : total;
-      int Fp = t.flagScan[p] + d.scanBlockSums[p / kCoopThreads];
-      int m = Fe - Fs, left = Fp - Fs;
-      if (p < s + m && !t.flagArr[p]) {
-        int q = t.pairR[s + ((p - s) - left)];
-        int ti = t.leafIdx[p]; t.leafIdx[p] = t.leafIdx[q]; t.leafIdx[q] = ti;
-        float2 tc = t.leafCtr[p]; t.leafCtr[p] = t.leafCtr[q]; t.leafCtr[q] = tc;
-      }
-    }
-    grid.sync();
-    // B4: the owner of each active range creates the two child ranges  :905-930
-    for (int p = tid; p < L; p += stride) {
-      int s = t.segStart[p];
-      if (p != s) continue;
-      int e = t.recEnd[s], node = t.recNode[s];
-      if (!(e - s > kSerialRange && node >= 0)) continue;
-      int split = t.recSplit[s];
-      int2 ch;
+      const int sg = t.segStart[p];
+      if (sg < 0) continue;
+      const int e = recEnd[sg], node = recNode[sg];
+      const int Fs = t.flagScan[sg] + d.scanBlockSums[sg / kCoopThreads];
+      const int Fe = e < L ? t.flagScan[e] + d.scanBlockSums[e / kCoopThreads] : total;
+      const int Fp = t.flagScan[p] + d.scanBlockSums[p / kCoopThreads];
+      const int m = Fe - Fs, left = Fp - Fs;
+      if (p >= sg + m && t.flagArr[p]) t.pairR[sg + (m - left - 1)] = p;
+      if (p != sg) continue;
+      const int split = (m > 0 && m < e - sg) ? sg + m : sg + (e - sg) / 2;
+      t.recSplit[sg] = split; t.recM[sg] = m;
       for (int side = 0; side < 2; side++) {
-        int cs = side == 0 ? s : split, ce = side == 0 ? split : e;
-        int childNode;
-        if (ce - cs == 1) {
-          childNode = t.leafIdx[cs];
-          t.parent[childNode] = node;
-          t.recEnd[cs] = ce; t.recNode[cs] = -1;
-        } else {
-          childNode = rbAllocNode(t);
-          t.parent[childNode] = node;
-          t.recEnd[cs] = ce; t.recNode[cs] = childNode; t.recBox[cs] = make_float4(FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX);
-          if (ce - cs > kSerialRange) atomicAdd(&t.rb[nextSlot], 1);
-          else t.serialList[atomicAdd(&t.rb[5], 1)] = cs;
-        }
-        if (side == 0) ch.x = childNode; else ch.y = childNode;
+        const int cs = side == 0 ? sg : split, ce = side == 0 ? split : e;
+        if (ce - cs == 1) continue;                  // a single element: linked in P3, once the swaps have settled who it is
+        const int childNode = rbAllocNode(t);
+        t.parent[childNode] = node; ((int*)&t.child[node])[side] = childNode;
+        recEndP[nxt][cs] = ce; recNodeP[nxt][cs] = childNode; recBoxP[nxt][cs] = make_float4(FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX);
+        if (ce - cs > kSerialRange) atomicAdd(&t.rb[nextSlot], 1);
+        else { int k = atomicAdd(&t.rb[5], 1); t.serialList[k] = cs; t.serEnd[k] = ce; t.serNode[k] = childNode; }
       }
-      t.child[node] = ch;
-      __threadfence();
-      if (split - s == 1) rbWalkUp(t, ch.x);
-      if (e - split == 1) rbWalkUp(t, ch.y);
+    }
+    grid.sync();
+    // P3: k-th misplaced element from the left swaps with the k-th from the right; every element then moves to its child
+    //     range: single elements are linked (and completed upward), long ranges collect their center bounds for the next level
+    for (int p = tid; p < L; p += stride) {
+      const int sg = t.segStart[p];
+      if (sg < 0) continue;
+      const int e = recEnd[sg], node = recNode[sg], split = t.recSplit[sg], m = t.recM[sg];
+      const int left = (t.flagScan[p] + d.scanBlockSums[p / kCoopThreads]) - (t.flagScan[sg] + d.scanBlockSums[sg / kCoopThreads]);
+      const bool f = t.flagArr[p] != 0;
+      if (p >= sg + m && f) continue;               // misplaced on the right: its partner on the left handles both positions
+      int pos[2] = {p, -1}; int idx[2] = {t.leafIdx[p], -1}; float2 ctr[2] = {t.leafCtr[p], make_float2(0.0f, 0.0f)};
+      if (p < sg + m && !f) {
+        const int q = t.pairR[sg + ((p - sg) - left)];
+        pos[1] = q; idx[1] = idx[0]; ctr[1] = ctr[0];
+        idx[0] = t.leafIdx[q]; ctr[0] = t.leafCtr[q];
+        t.leafIdx[p] = idx[0]; t.leafCtr[p] = ctr[0]; t.leafIdx[q] = idx[1]; t.leafCtr[q] = ctr[1];
+      }
+      for (int k = 0; k < 2; k++) {
+        if (pos[k] < 0) continue;
+        const int side = pos[k] < split ? 0 : 1;
+        const int cs = side == 0 ? sg : split, ce = side == 0 ? split : e;
+        if (ce - cs == 1) {
+          t.parent[idx[k]] = node; ((int*)&t.child[node])[side] = idx[k];
+          t.segStart[pos[k]] = -1;
+          __threadfence();
+          rbWalkUp(t, idx[k]);
+        } else if (ce - cs > kSerialRange) {
+          t.segStart[pos[k]] = cs;
+          float* b = (float*)&recBoxP[nxt][cs];
+          rbAtomicMinF(b + 0, ctr[k].x); rbAtomicMinF(b + 1, ctr[k].y); rbAtomicMaxF(b + 2, ctr[k].x); rbAtomicMaxF(b + 3, ctr[k].y);
+        } else t.segStart[pos[k]] = -1;
+      }
     }
     grid.sync();
     level++;
@@ -309,9 +315,8 @@ __device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeT
   // small ranges: sequential BuildTree, one thread per range, then completion upward
   const int nSerial = t.rb[5];
   for (int k = tid >> 5; k < nSerial; k += stride >> 5) {       // one warp per range
-    int s = t.serialList[k];
-    int node = t.recNode[s];
-    rbBuildWarp(t, s, t.recEnd[s], node);
+    int node = t.serNode[k];
+    rbBuildWarp(t, t.serialList[k], t.serEnd[k], node);
     if ((threadIdx.x & 31) == 0) rbWalkUp(t, node);
   }
   if (tid == 0) t.meta[0] = t.rb[6];

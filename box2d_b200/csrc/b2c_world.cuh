@@ -35,6 +35,7 @@ struct TreeDev {
   // parallel rebuild scratch (b2c_rebuild.cuh), all sized `capacity`
   int* segStart; int* recEnd; int* recNode; int* recSplit; float4* recBox; int* flagScan; int* flagArr; int* pairR; int* freeIds;
   int* subCount; int* visit; int* serialList;
+  int* recEnd2; int* recNode2; float4* recBox2; int* recM; int* serEnd; int* serNode;   // second parity of the range records, flag count per range
   int* rb;             // [0] L [1] freed internal nodes [2] node cursor [3],[4] active ranges (level parity) [5] serial ranges [6] new root
   int capacity;
   int stackCapacity;
