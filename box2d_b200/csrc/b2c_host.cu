@@ -423,7 +423,7 @@ int World::upload() {
     d.bigScratch = std::max(1 << 21, sumCap);
     d.bigQueryVisits = kBigQueryVisits;
     d.islandMaxBodies = kIslandMaxBodies;
-    d.debugChecksums = getenv("B2CUDA_DEBUG_CHECKSUMS") ? 1 : 0;
+    d.debugChecksums = getenv("B2CUDA_DEBUG_CHECKSUMS") ? atoi(getenv("B2CUDA_DEBUG_CHECKSUMS")) : 0;
     if (const char* e = getenv("B2CUDA_ISLAND_MAX_BODIES")) { int v = atoi(e); if (v >= 0 && v <= kIslandMaxBodies) d.islandMaxBodies = v; }
     if (const char* e = getenv("B2CUDA_BIG_QUERY_VISITS")) { int v = atoi(e); if (v > 0) d.bigQueryVisits = v; }
     DA(d.moveBig, int, d.moveCapacity); DA(d.moveHitBuf, int2, (size_t)d.moveCapacity * 4); DA(d.bigList, int, kMaxBigQueries); DA(d.bigSegStart, int, kMaxBigQueries + 1); DA(d.bigOff, int, kMaxBigQueries + 1);

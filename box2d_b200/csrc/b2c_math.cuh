@@ -27,7 +27,8 @@ constexpr float kMaxRotation = 0.25f * kPi;
 constexpr int kGraphColorCount = 24;
 constexpr int kIslandMaxBodies = 192;   // island solver: body rows staged in shared memory (b2c_islands.cuh)
 constexpr int kMaxBigQueries = 1024;    // wide broadphase queries answered by a leaf sweep per step (more fall back to a one-thread traversal)
-constexpr int kBigQueryVisits = 256;    // node visits after which a one-thread tree query is reclassified as wide
+constexpr int kBigQueryVisits = 256;
+constexpr int kWideQueryCells = 256;    // a query box covering this many average leaf cells of the dynamic tree is wide without traversing   // node visits after which a one-thread tree query is reclassified as wide
 constexpr int kDynamicColorCount = 20;
 constexpr int kOverflowIndex = kGraphColorCount - 1;
 constexpr int kMaxPolygonVertices = 8;

@@ -167,6 +167,7 @@ __device__ __forceinline__ bool acceptPair(const WorldDev& d, int queryKey, int 
 
 // DynamicTree.Query (src/DynamicTree.cs:531-557): explicit stack, child1 pushed first so child2 is visited first.
 // BUDGET: give up (return -1) after kBigQueryVisits node visits — the query is then answered by the leaf sweep below.
+__device__ __forceinline__ void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 constexpr int kHitBuf = 4;     // accepted hits kept from the count pass; queries with more re-traverse in the fill pass
 struct HitSink {               // where accepted hits of one query go
   int2* out; int outLast;      // FILL: movePairs and the query's last slot (hits are written in reverse)
@@ -197,6 +198,8 @@ template <bool FILL, bool BUDGET> __device__ inline int queryTree(const WorldDev
     } else {
       if (sp + 2 > kQueryStack) { atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); continue; }
       stack[sp++] = c.x; stack[sp++] = c.y;
+      // pointer chasing: ask for child1's node now (it is popped after child2's whole subtree), so that pop finds it in L1
+      prefetchL1(&t.aabb[c.x]); prefetchL1(&t.child[c.x]);
     }
   }
   return hits;
@@ -236,7 +239,17 @@ template <bool FILL> __device__ void p_find_pairs(const WorldDev& d, int tid, in
         Box fat = toBox(d.trees[type].aabb[id]);
         int queryShape = d.trees[type].user[id];
         int big = -1;
-        count = queryTrees<false, true>(d, fat, queryKey, type, queryShape, sink);
+        // A box that covers many average leaf cells of the dynamic tree is wide for certain (the tumbler's walls): do not
+        // spend the visit budget on finding that out. The budget stays as the general detector.
+        bool wide = false;
+        { const TreeDev& dt = d.trees[kDynamicBody]; int root = dt.meta[0], leaves = dt.meta[3];
+          if (root != -1 && leaves > 4 * kWideQueryCells) {
+            float4 rb = dt.aabb[root];
+            float ox = fminf(fat.hi.x, rb.z) - fmaxf(fat.lo.x, rb.x), oy = fminf(fat.hi.y, rb.w) - fmaxf(fat.lo.y, rb.y);
+            float cell = (rb.z - rb.x) * (rb.w - rb.y) / (float)leaves;
+            wide = ox > 0.0f && oy > 0.0f && ox * oy > (float)kWideQueryCells * cell;
+          } }
+        count = wide ? -1 : queryTrees<false, true>(d, fat, queryKey, type, queryShape, sink);
         if (count < 0) {
           int slot = atomicAdd(&d.sc->bigQueryCount, 1);
           if (slot < kMaxBigQueries) { d.bigList[slot] = i; big = slot; count = 0; }
@@ -1253,21 +1266,27 @@ namespace b2c {
 // Fused cooperative phase kernels: one launch per reference phase, grid.sync() between dependent sub-phases, and a
 // uniform early-out when the phase has nothing to do (no moved proxies / no contact state change / no enlarged proxy).
 // ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long globalTimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ void phase_broadphase(cg::grid_group& grid, const WorldDev& d) {      // UpdateBroadPhasePairs + RebuildTrees
   const int tid = gtid(), stride = gsize();
   Scalars& s = *d.sc;
   if (s.moveCount > 0) {
+    if (d.debugChecksums == 2 && tid == 0) d.sc->dbg[6] = globalTimer();
     for (int i = tid; i < d.pairTableSize; i += stride) d.pairTable[i] = kEmptyKey;
     grid.sync();
     p_pair_insert(d, tid, stride);
     grid.sync();
+    if (d.debugChecksums == 2 && tid == 0) d.sc->dbg[7] = globalTimer();
     p_find_pairs<false>(d, tid, stride);
     grid.sync();
+    if (d.debugChecksums == 2 && tid == 0) { d.sc->dbg[8] = globalTimer(); d.sc->dbg[11] = d.sc->bigQueryCount; }
     phase_big_queries(grid, d);
+    if (d.debugChecksums == 2 && tid == 0) d.sc->dbg[9] = globalTimer();
     gridScan<int>(grid, d.moveHitCount, d.scanBlockSums, s.moveCount, &s.newPairCount);
     p_find_pairs<true>(d, tid, stride);
     p_big_fill(d, tid, stride);
     grid.sync();
+    if (d.debugChecksums == 2 && tid == 0) d.sc->dbg[10] = globalTimer();
     p_create_contacts(d, tid, stride);
     p_clear_moved(d, tid, stride);
     grid.sync();
@@ -1307,13 +1326,13 @@ __device__ void dbgAdd(const WorldDev& d, int slot, unsigned long long sum) {
   if ((threadIdx.x & 31) == 0 && sum) atomicAdd(&d.sc->dbg[slot], sum);
 }
 __device__ void dbgBodies(const WorldDev& d, int slot) {
-  if (!d.debugChecksums) return;
+  if (d.debugChecksums != 1) return;
   unsigned long long sum = 0;
   for (int i = gtid(); i < d.awakeCount; i += gsize()) sum += hf4(hf4(mix64(i + 1), d.st0[i]), d.st1[i]);
   dbgAdd(d, slot, sum);
 }
 __device__ void dbgContacts(const WorldDev& d, int slot) {
-  if (!d.debugChecksums) return;
+  if (d.debugChecksums != 1) return;
   unsigned long long sum = 0;
   int n = d.sc->contactNext;
   for (int i = gtid(); i < n; i += gsize()) {
@@ -1329,7 +1348,7 @@ __device__ void dbgContacts(const WorldDev& d, int slot) {
   dbgAdd(d, slot, sum);
 }
 __device__ void dbgLanes(const WorldDev& d, int slot, bool all) {
-  if (!d.debugChecksums) return;
+  if (d.debugChecksums != 1) return;
   unsigned long long sum = 0;
   int n = d.sc->smallConStart;
   for (int t = gtid(); t < n; t += gsize()) {
@@ -1347,7 +1366,7 @@ __device__ void dbgLanes(const WorldDev& d, int slot, bool all) {
 // debug: number of (color, dynamic body) pairs claimed by more than one touching constraint (must be 0), and the same
 // test on the solver's own arrangement (slot -> contact -> bodies)
 __device__ void dbgColorConflicts(cg::grid_group& grid, const WorldDev& d, int slot) {
-  if (!d.debugChecksums) return;
+  if (d.debugChecksums != 1) return;
   const int awake = d.awakeCount, n = d.sc->contactNext;
   grid.sync();
   for (int i = gtid(); i < awake * kGraphColorCount; i += gsize()) d.rootColorCount[i] = 0;
@@ -1388,7 +1407,6 @@ __device__ void dbgColorConflicts(cg::grid_group& grid, const WorldDev& d, int s
   grid.sync();
 }
 
-__device__ __forceinline__ unsigned long long globalTimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ void stamp(const WorldDev& d, int k) { if (gtid() == 0) d.sc->phaseStamp[k] = globalTimer(); }
 
 // One launch for UpdateBroadPhasePairs -> Collide -> (islands) -> PrepareContacts -> grid-path solver. Phases that have
@@ -1417,10 +1435,10 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   if (gridWork) { phase_prepare(d, sp, !cachedLanes); if (!cachedLanes) grid.sync(); }
   stamp(d, 3);
   dbgLanes(d, 3, true); dbgBodies(d, 4); dbgColorConflicts(grid, d, 10);
-  if (d.debugChecksums) grid.sync();
+  if (d.debugChecksums == 1) grid.sync();
   if (gridWork) { if (cachedLanes) phase_solver_grid<true>(grid, d, sp); else phase_solver_grid<false>(grid, d, sp); }
   stamp(d, 4);
-  if (d.debugChecksums) { grid.sync(); dbgBodies(d, 5); dbgLanes(d, 6, false); dbgContacts(d, 7); }
+  if (d.debugChecksums == 1) { grid.sync(); dbgBodies(d, 5); dbgLanes(d, 6, false); dbgContacts(d, 7); }
   if (gtid() == 0) { for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k]; s.phaseAcc[4] += s.phaseStamp[5] - s.phaseStamp[1]; }
 }
 
@@ -1428,7 +1446,7 @@ __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, Ste
   cg::grid_group grid = cg::this_grid();
   const int tid = gtid(), stride = gsize();
   Scalars& s = *d.sc;
-  if (d.debugChecksums) { dbgBodies(d, 8); dbgContacts(d, 9); grid.sync(); }
+  if (d.debugChecksums == 1) { dbgBodies(d, 8); dbgContacts(d, 9); grid.sync(); }
   p_finalize(d, sp, tid, stride);
   if (s.anyHitShapes) p_hit_events(d, sp, tid, stride);
   grid.sync();
