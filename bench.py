@@ -217,7 +217,7 @@ def b200_arm(args, rank, world_size, local_rank):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
             "e2e": {"value": total_units / (e2e_ms_max * 1e-3), "unit": "body-substeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(d2h),
                     "note": "Step(dt,substeps) has no per-step host input; scene uploaded once at the first step; each step reads back all body transforms/velocities and contact events to host"},
-            "gpu_launches": (KERNELS_PER_STEP + (1 if args.workload == "batched_pyramids" else 0)) * K,   # + k_solver_islands_warp when thousands of islands "clocks": sampler.result(),
+            "gpu_launches": (KERNELS_PER_STEP + (1 if args.workload == "batched_pyramids" else 0)) * K, "clocks": sampler.result(),
             "batch_stats": {"bodies": int(stats[0]), "sum_v2": float(stats[1]), "max_speed": float(stats[2]), "min_y": float(stats[3])}}
     if world_size == 1 and not args.no_cpu:
         cpu_warm = min(W, 60)
