@@ -211,7 +211,7 @@ def b200_arm(args, rank, world_size, local_rank):
             "value_l2_resident": total_units / (warm_ms_max * 1e-3), "ms_per_step_l2_resident": warm_ms_max / K,
             "phase_ms": dict(zip(("pairs", "collide", "color_sort_prepare", "solver_kernel", "finalize_refit", "tree_rebuild_in_collide"), [x / K for x in phases])),
             "roofline": {"bound": "hbm", "kernel": "k_solver_islands (+ grid-path solver inside k_step_front)", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": 9349632 if args.workload == "many_pyramids" else None,   # dram read+write per launch, profiles/r01c_summary.txt
+                         "traffic": 9350912 if args.workload == "many_pyramids" else None,   # dram read+write per launch, profiles/r01d_summary.txt
                         
                          "algorithmic_bytes_per_launch": algo_bytes, "avg_launch_ms": avg_solver_ms,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
