@@ -168,7 +168,7 @@ def b200_arm(args, rank, world_size, local_rank):
     # ---- timed region 3: end to end through the C-ABI with host buffers: step + bulk body read-back + contact events ----
     for _ in range(max(3, min(W, 8))):         # untimed warm-up of the read-back path itself (first call packs all bodies, loads the kernel)
         w.Step(DT, SUBSTEPS)
-        w.GetBodyEvents(copy=False)
+        w.GetBodyMoveEvents(copy=False)
         w.GetContactEvents()
     w.Synchronize()
     barrier()
@@ -176,7 +176,7 @@ def b200_arm(args, rank, world_size, local_rank):
     d2h = 0
     for _ in range(K):
         w.Step(DT, SUBSTEPS)
-        b = w.GetBodyEvents(copy=False)        # records packed by FinalizeBodies, one D2H into pinned memory behind the step, zero-copy view
+        b = w.GetBodyMoveEvents(copy=False)    # WorldAPI.GetBodyEvents: 24 B per awake body, filled by FinalizeBodies, one D2H into pinned memory behind the step
         ev = w.GetContactEvents()
         d2h = b.nbytes + sum(e.nbytes for e in ev)
     torch.cuda.synchronize()
@@ -189,7 +189,8 @@ def b200_arm(args, rank, world_size, local_rank):
         raise SystemExit(f"bench.py: device error flags 0x{c2.errorFlags:x}")
     from box2d_b200 import batch
     (step_ms_max, warm_ms_max, e2e_ms_max), total_units = batch.reduce_timing([step_ms, warm_ms, e2e_s * 1000.0], bodies * SUBSTEPS * K, dist, "cuda")
-    stats = batch.reduce_stats(batch.batch_stats(b[b["flags"] != 0]), dist, "cuda")   # NCCL is used for batch statistics only
+    bodies_read = w.GetBodyEvents(copy=False)
+    stats = batch.reduce_stats(batch.batch_stats(bodies_read[bodies_read["flags"] != 0]), dist, "cuda")   # NCCL is used for batch statistics only
     if rank != 0:
         w.Destroy()
         return
@@ -216,7 +217,7 @@ def b200_arm(args, rank, world_size, local_rank):
                          "algorithmic_bytes_per_launch": algo_bytes, "avg_launch_ms": avg_solver_ms,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
             "e2e": {"value": total_units / (e2e_ms_max * 1e-3), "unit": "body-substeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(d2h),
-                    "note": "Step(dt,substeps) has no per-step host input; scene uploaded once at the first step; each step reads back all body transforms/velocities and contact events to host"},
+                    "note": "Step(dt,substeps) has no per-step host input; scene uploaded once at the first step; each step reads back the body move events (transform + id of every awake body, the reference's GetBodyEvents payload) and the contact begin/end/hit events to host"},
             "gpu_launches": (KERNELS_PER_STEP + (1 if args.workload == "batched_pyramids" else 0)) * K, "clocks": sampler.result(),
             "batch_stats": {"bodies": int(stats[0]), "sum_v2": float(stats[1]), "max_speed": float(stats[2]), "min_y": float(stats[3])}}
     if world_size == 1 and not args.no_cpu:

@@ -250,6 +250,15 @@ class World:
         arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value * C.sizeof(BodyRead),)).view(np.dtype(BodyRead))
         return arr.copy() if copy else arr
 
+    def GetBodyMoveEvents(self, copy=True):
+        """WorldAPI.GetBodyEvents as the reference fills it: one (transform, bodyId, fellAsleep) per awake body, awake-set order."""
+        p, n = C.POINTER(capi.BodyMoveEvent)(), C.c_int32()
+        self._check(self.fns["world_get_body_move_events"](self.handle, C.byref(p), C.byref(n)))
+        if n.value == 0:
+            return np.zeros(0, dtype=np.dtype(capi.BodyMoveEvent))
+        arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value * C.sizeof(capi.BodyMoveEvent),)).view(np.dtype(capi.BodyMoveEvent))
+        return arr.copy() if copy else arr
+
     def ReadBodies(self):
         return self._read("world_read_bodies", BodyRead, self.GetCounters().bodyCount + 16)
 

@@ -103,6 +103,10 @@ class Counters(C.Structure):
                [("colorCounts", C.c_int32 * 24)]
 
 
+class BodyMoveEvent(C.Structure):
+    _fields_ = [("transform", Transform), ("bodyId", C.c_int32), ("fellAsleep", C.c_uint32)]
+
+
 class Profile(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("step", "pairs", "collide", "solve", "prepareStages", "solveConstraints",
                                          "prepareConstraints", "integrateVelocities", "warmStart", "solveImpulses",
@@ -135,6 +139,7 @@ PROTOS = {
                                  C.POINTER(C.POINTER(ContactHitEvent)), C.POINTER(C.c_int32)],
     "world_get_joint_events": [_W, C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32)],
     "world_get_body_events": [_W, C.POINTER(C.POINTER(BodyRead)), C.POINTER(C.c_int32)],
+    "world_get_body_move_events": [_W, C.POINTER(C.POINTER(BodyMoveEvent)), C.POINTER(C.c_int32)],
     "world_read_bodies": [_W, C.POINTER(BodyRead), C.c_int32, C.POINTER(C.c_int32)],
     "world_read_contacts": [_W, C.POINTER(ContactRead), C.c_int32, C.POINTER(C.c_int32)],
     "world_read_joints": [_W, C.POINTER(JointRead), C.c_int32, C.POINTER(C.c_int32)],

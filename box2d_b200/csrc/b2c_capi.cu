@@ -86,6 +86,7 @@ int32_t b2cuda_world_get_contact_events(B2CWorld* h, const B2CContactTouchEvent*
 }
 int32_t b2cuda_world_get_joint_events(B2CWorld* h, const int32_t** ids, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->getJointEvents(ids, n)); }
 int32_t b2cuda_world_read_bodies(B2CWorld* h, B2CBodyRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readBodies(dst, cap, n)); }
+int32_t b2cuda_world_get_body_move_events(B2CWorld* h, const B2CBodyMoveEvent** e, int32_t* n) { CHECK_HANDLE(h); if (!e || !n) return B2C_E_INVALID; return done(h, h->w->getBodyMoveEvents(e, n)); }
 int32_t b2cuda_world_get_body_events(B2CWorld* h, const B2CBodyRead** r, int32_t* n) { CHECK_HANDLE(h); if (!r || !n) return B2C_E_INVALID; return done(h, h->w->getBodyEvents(r, n)); }
 int32_t b2cuda_world_read_contacts(B2CWorld* h, B2CContactRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readContacts(dst, cap, n)); }
 int32_t b2cuda_world_read_joints(B2CWorld* h, B2CJointRead* dst, int32_t cap, int32_t* n) { CHECK_HANDLE(h); return done(h, h->w->readJoints(dst, cap, n)); }

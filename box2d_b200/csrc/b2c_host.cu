@@ -106,6 +106,8 @@ void World::freeDevice() {
   if (hHit_) cudaFreeHost(hHit_);
   if (hJointEvents_) cudaFreeHost(hJointEvents_);
   if (hBodyRead_) cudaFreeHost(hBodyRead_);
+  if (hMoveEvents_) cudaFreeHost(hMoveEvents_);
+  hMoveEvents_ = nullptr;
   hBodyRead_ = nullptr;
   hostScalars_ = nullptr; hBegin_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
   for (auto& e : ev_) if (e) { cudaEventDestroy(e); e = nullptr; }
@@ -461,6 +463,9 @@ int World::upload() {
   CK(cudaHostGetDevicePointer((void**)&d.hitEvents, hHit_, 0));
   d.bodyOut = nullptr;
   DA(dBodyRead_, B2CBodyRead, nBody);
+  DA(dMoveEvents_, B2CBodyMoveEvent, nAwake);
+  CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)std::max(nAwake, 1), cudaHostAllocDefault));
+  d.moveOut = nullptr;
   CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(nBody, 1), cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(nJoint, 1), cudaHostAllocDefault));
   CK(cudaStreamSynchronize(stream_));

@@ -86,6 +86,7 @@ class World {
   int readJoints(B2CJointRead* dst, int capacity, int* count);
   int readShapes(B2CShapeRead* dst, int capacity, int* count);
   int getCounters(B2CCounters* out);
+  int getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count);
   int getProfile(B2CProfile* out);
   int debugChecksums(unsigned long long* out16);
   int timerStart();
@@ -139,7 +140,9 @@ class World {
   B2CProfile profile_{};
   bool profileValid_ = false;
   int coopBlocks_ = 0;
-  B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false; bool streamBodies_ = false; int islandMode_ = 0;   // 0 auto, 1 CTA per island, 2 warp per island   // streamBodies_: every step packs + copies the body records (set by the first GetBodyEvents)
+  B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false; bool streamBodies_ = false;
+  B2CBodyMoveEvent* dMoveEvents_ = nullptr; B2CBodyMoveEvent* hMoveEvents_ = nullptr; bool movesFetched_ = false, streamMoves_ = false, lastStepDtZero_ = false;
+  int islandMode_ = 0;   // 0 auto, 1 CTA per island, 2 warp per island   // streamBodies_: every step packs + copies the body records (set by the first GetBodyEvents)
   friend struct StepLauncher;
 };
 

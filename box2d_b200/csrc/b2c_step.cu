@@ -1176,7 +1176,8 @@ __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int
       }
     }
     d.simFlags[i] = simFlags;
-    if (d.bodyOut) {                               // bodyMoveEvents (src/Solver.cs:432-438): one packed record per body
+    if (d.moveOut) { B2CBodyMoveEvent ev; ev.transform.p = {xf.p.x, xf.p.y}; ev.transform.q = {q.c, q.s}; ev.bodyId = bodyId; ev.fellAsleep = 0; d.moveOut[i] = ev; }   // src/Solver.cs:432-438
+    if (d.bodyOut) {                               // the same per body id, with velocities (bulk BodyAPI getters)
       B2CBodyRead r;
       r.transform.p = {xf.p.x, xf.p.y}; r.transform.q = {q.c, q.s}; r.center = {center.x, center.y};
       r.linearVelocity = {s.x, s.y}; r.angularVelocity = s.z; r.flags = simFlags;
@@ -1485,7 +1486,8 @@ int World::step(float timeStep, int subStepCount) {
   if (!onDevice_) { int rc = upload(); if (rc) return rc; }
   CK(cudaSetDevice(device_));
   WorldDev& d = d_;
-  eventsFetched_ = false; bodiesFetched_ = false;
+  eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false;
+  lastStepDtZero_ = timeStep == 0.0f;              // api/World.cs:38,44-51: the move events are cleared and the step returns early
   if (timeStep == 0.0f) {                          // api/World.cs:44-51
     lastEndIndex_ = endIndex_;
     endIndex_ = 1 - endIndex_;
@@ -1533,12 +1535,40 @@ int World::step(float timeStep, int subStepCount) {
   cudaEventRecord(pe[3], stream_);
   profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
   CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
+  if (streamMoves_) {
+    CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)d.awakeCount, cudaMemcpyDeviceToHost, stream_));
+    movesFetched_ = true;
+  }
   if (streamBodies_) {                             // the caller reads body records every step: the copy rides behind the step
     CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)d.bodyCapacity, cudaMemcpyDeviceToHost, stream_));
     bodiesFetched_ = true;
   }
   CK(cudaGetLastError());
   stepCount_++;
+  return B2C_OK;
+}
+
+__global__ void __launch_bounds__(kThreads) k_pack_moves(WorldDev d, B2CBodyMoveEvent* out) {
+  for (int i = gtid(); i < d.awakeCount; i += gsize()) {
+    int bodyId = d.simBodyId[i];
+    float4 xf = d.bodyXf[bodyId];
+    B2CBodyMoveEvent ev; ev.transform.p = {xf.x, xf.y}; ev.transform.q = {xf.z, xf.w}; ev.bodyId = bodyId; ev.fellAsleep = 0;
+    out[i] = ev;
+  }
+}
+int World::getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count) {
+  *events = nullptr; *count = 0;
+  if (!onDevice_) return fail(B2C_E_INVALID, "get_body_move_events before the first step");
+  CK(cudaSetDevice(device_));
+  if (!movesFetched_) {
+    int n = d_.awakeCount;
+    k_pack_moves<<<gridFor(n, kThreads, 148 * 8), kThreads, 0, stream_>>>(d_, dMoveEvents_);
+    CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
+    movesFetched_ = true;
+    streamMoves_ = true; d_.moveOut = dMoveEvents_;   // from now on FinalizeBodies fills the events and step() copies them
+  }
+  int rc = synchronize(); if (rc) return rc;
+  *events = hMoveEvents_; *count = lastStepDtZero_ ? 0 : d_.awakeCount;
   return B2C_OK;
 }
 

@@ -200,6 +200,7 @@ struct WorldDev {
   // --- events ---
   B2CContactTouchEvent* beginEvents; B2CContactTouchEvent* endEvents[2]; B2CContactHitEvent* hitEvents;
   int eventCapacity;
+  B2CBodyMoveEvent* moveOut;   // when set, FinalizeBodies writes bodyMoveEvents[awake sim index]
   B2CBodyRead* bodyOut;   // when set, FinalizeBodies also writes the packed per-body record (bodyMoveEvents equivalent)
   // --- finalize / refit scratch ---
   int* bodyEnlargedCount;   // per awake sim: enlarged shapes, then exclusive offsets

@@ -86,6 +86,9 @@ typedef struct B2CRevoluteJointDef {
 typedef struct B2CBodyRead {      /* BodyAPI.GetTransform/GetLinearVelocity/GetAngularVelocity... api/Body.cs:282-357 */
   B2CTransform transform; B2CVec2 center; B2CVec2 linearVelocity; float angularVelocity; uint32_t flags;
 } B2CBodyRead;
+typedef struct B2CBodyMoveEvent {       /* BodyMoveEvent include/Types.cs:761-767 without the managed userData (the shim maps bodyId -> userData) */
+  B2CTransform transform; int32_t bodyId; uint32_t fellAsleep;
+} B2CBodyMoveEvent;
 typedef struct B2CManifoldPointRead {   /* include/Collision.cs:916-945 */
   B2CVec2 point, anchorA, anchorB;
   float separation, normalImpulse, tangentImpulse, totalNormalImpulse, normalVelocity;
@@ -161,6 +164,10 @@ int32_t b2cuda_world_read_bodies(B2CWorld* world, B2CBodyRead* dst, int32_t capa
 /* WorldAPI.GetBodyEvents — api/World.cs:283-290 (bodyMoveEvents, src/Solver.cs:432-438): one record per body id, packed on the
  * device and copied once into library-owned pinned host memory; the pointer is valid until the next step ("transient"). */
 int32_t b2cuda_world_get_body_events(B2CWorld* world, const B2CBodyRead** records, int32_t* count);
+/* WorldAPI.GetBodyEvents exactly as the reference fills it (src/Solver.cs:432-438): one B2CBodyMoveEvent per AWAKE body in
+ * awake-set order (24 B each), written by FinalizeBodies; after the first call every step copies the array to pinned host
+ * memory behind the step, so the call only synchronises. Pointer valid until the next step. */
+int32_t b2cuda_world_get_body_move_events(B2CWorld* world, const B2CBodyMoveEvent** events, int32_t* count);
 /* ContactAPI.GetData for every live contact in ascending contactId */
 int32_t b2cuda_world_read_contacts(B2CWorld* world, B2CContactRead* dst, int32_t capacity, int32_t* count);
 int32_t b2cuda_world_read_joints(B2CWorld* world, B2CJointRead* dst, int32_t capacity, int32_t* count);

@@ -107,6 +107,17 @@ int32_t b2o_world_get_body_events(World* w, const B2CBodyRead** records, int32_t
   *records = tBodies.data();
   return 0;
 }
+static thread_local std::vector<B2CBodyMoveEvent> tMoves;
+int32_t b2o_world_get_body_move_events(World* w, const B2CBodyMoveEvent** events, int32_t* count) {   // src/Solver.cs:432-438
+  const auto& sims = w->awakeSet.bodySims;
+  tMoves.resize(sims.size());
+  for (size_t i = 0; i < sims.size(); i++) {
+    B2CBodyMoveEvent e; e.transform.p = CV(sims[i].transform.p); e.transform.q = {sims[i].transform.q.c, sims[i].transform.q.s}; e.bodyId = sims[i].bodyId; e.fellAsleep = 0;
+    tMoves[i] = e;
+  }
+  *events = tMoves.data(); *count = w->lastStepDtZero ? 0 : (int)sims.size();
+  return 0;
+}
 static void FillPoint(B2CManifoldPointRead& o, const ManifoldPoint& p) {
   o.point = CV(p.point); o.anchorA = CV(p.anchorA); o.anchorB = CV(p.anchorB); o.separation = p.separation; o.normalImpulse = p.normalImpulse;
   o.tangentImpulse = p.tangentImpulse; o.totalNormalImpulse = p.totalNormalImpulse; o.normalVelocity = p.normalVelocity; o.id = p.id; o.persisted = p.persisted;

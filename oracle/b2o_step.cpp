@@ -182,6 +182,7 @@ void World::Solve(StepContext& stepContext) {      // :739-1322
 }
 
 void World::Step(float timeStep, int subStepCount) {      // api/World.cs:31-113
+  lastStepDtZero = timeStep == 0.0f;                        // :38 bodyMoveEvents.Clear(); :44-51 early return
   contactBeginEvents.clear(); contactHitEvents.clear(); jointEvents.clear();
   if (timeStep == 0) { endEventArrayIndex = 1 - endEventArrayIndex; contactEndEvents[endEventArrayIndex].clear(); return; }
   double t0 = NowMs();

@@ -200,6 +200,7 @@ class World {
   IdPool bodyIdPool, shapeIdPool, jointIdPool, contactIdPool;
   std::vector<Body> bodies; std::vector<Shape> shapes; std::vector<Joint> joints; std::vector<Contact> contacts;
   SolverSet staticSet, awakeSet;
+  bool lastStepDtZero = false;
   std::vector<ContactTouchEvent> contactBeginEvents, contactEndEvents[2]; int endEventArrayIndex = 0;
   std::vector<ContactHitEvent> contactHitEvents;
   std::vector<int> jointEvents;

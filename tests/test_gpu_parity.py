@@ -110,3 +110,28 @@ def test_warp_per_island_variant_bit_exact(scene, steps, monkeypatch):
              "tumbler": lambda w: scenes.tumbler(w, n=600, half=6.0)}[scene]
     res = parity.run_pair(build, steps=steps, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+def test_body_move_events_match_reference_layout():
+    """WorldAPI.GetBodyEvents: one event per awake body in awake-set order, equal to the oracle's, streamed after the first call."""
+    from box2d_b200 import api
+    from oracle_backend import OracleBackend
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    orc = api.World(OracleBackend(), scenes.world_def())
+    try:
+        scenes.mixed_drop(cuda)
+        scenes.mixed_drop(orc)
+        for step in range(12):
+            cuda.Step(1.0 / 60.0, 4)
+            orc.Step(1.0 / 60.0, 4)
+            a, b = cuda.GetBodyMoveEvents(), orc.GetBodyMoveEvents()
+            assert len(a) == len(b) == cuda.GetCounters().awakeBodyCount
+            assert a.tobytes() == b.tobytes(), f"step {step}"
+            bodies = cuda.ReadBodies()
+            assert a["transform"].tobytes() == bodies["transform"][a["bodyId"]].tobytes()
+        cuda.Step(0.0, 4)
+        orc.Step(0.0, 4)
+        assert len(cuda.GetBodyMoveEvents()) == 0 and len(orc.GetBodyMoveEvents()) == 0
+    finally:
+        cuda.Destroy()
+        orc.Destroy()
