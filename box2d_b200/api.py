@@ -150,6 +150,50 @@ class World:
     def ApplyLinearImpulseToCenter(self, body_id, i, wake=True):
         self._check(self.fns["body_apply_linear_impulse_to_center"](self.handle, body_id, Vec2(*i), int(wake)))
 
+    def ApplyForce(self, body_id, f, point, wake=True):
+        self._check(self.fns["body_apply_force"](self.handle, body_id, Vec2(*f), Vec2(*point), int(wake)))
+
+    def ClearForces(self, body_id):
+        self._check(self.fns["body_clear_forces"](self.handle, body_id))
+
+    def ApplyLinearImpulse(self, body_id, i, point, wake=True):
+        self._check(self.fns["body_apply_linear_impulse"](self.handle, body_id, Vec2(*i), Vec2(*point), int(wake)))
+
+    def ApplyAngularImpulse(self, body_id, i, wake=True):
+        self._check(self.fns["body_apply_angular_impulse"](self.handle, body_id, float(i), int(wake)))
+
+    def SetLinearDamping(self, body_id, v):
+        self._check(self.fns["body_set_linear_damping"](self.handle, body_id, float(v)))
+
+    def SetAngularDamping(self, body_id, v):
+        self._check(self.fns["body_set_angular_damping"](self.handle, body_id, float(v)))
+
+    def SetGravityScale(self, body_id, v):
+        self._check(self.fns["body_set_gravity_scale"](self.handle, body_id, float(v)))
+
+    def _body(self, body_id):
+        out = BodyRead()
+        self._check(self.fns["body_get"](self.handle, body_id, C.byref(out)))
+        return out
+
+    def GetTransform(self, body_id):
+        t = self._body(body_id).transform
+        return (t.p.x, t.p.y), (t.q.c, t.q.s)
+
+    def GetPosition(self, body_id):
+        return self.GetTransform(body_id)[0]
+
+    def GetLinearVelocity(self, body_id):
+        v = self._body(body_id).linearVelocity
+        return (v.x, v.y)
+
+    def GetAngularVelocity(self, body_id):
+        return self._body(body_id).angularVelocity
+
+    def GetWorldCenterOfMass(self, body_id):
+        c = self._body(body_id).center
+        return (c.x, c.y)
+
     # --- ShapeAPI ---
     def CreateShape(self, body_id, shape_def, geometry):
         out = C.c_int32(-1)
@@ -179,6 +223,15 @@ class World:
 
     def SetContactTuning(self, hertz, damping, push):
         self._check(self.fns["world_set_contact_tuning"](self.handle, hertz, damping, push))
+
+    def SetRestitutionThreshold(self, value):
+        self._check(self.fns["world_set_restitution_threshold"](self.handle, float(value)))
+
+    def SetHitEventThreshold(self, value):
+        self._check(self.fns["world_set_hit_event_threshold"](self.handle, float(value)))
+
+    def SetMaximumLinearSpeed(self, value):
+        self._check(self.fns["world_set_maximum_linear_speed"](self.handle, float(value)))
 
     def Step(self, time_step, sub_step_count):
         self._check(self.fns["world_step"](self.handle, float(time_step), int(sub_step_count)))

@@ -126,6 +126,17 @@ PROTOS = {
     "body_apply_force_to_center": [_W, C.c_int32, Vec2, C.c_int32],
     "body_apply_torque": [_W, C.c_int32, C.c_float, C.c_int32],
     "body_apply_linear_impulse_to_center": [_W, C.c_int32, Vec2, C.c_int32],
+    "body_apply_force": [_W, C.c_int32, Vec2, Vec2, C.c_int32],
+    "body_clear_forces": [_W, C.c_int32],
+    "body_apply_linear_impulse": [_W, C.c_int32, Vec2, Vec2, C.c_int32],
+    "body_apply_angular_impulse": [_W, C.c_int32, C.c_float, C.c_int32],
+    "body_set_linear_damping": [_W, C.c_int32, C.c_float],
+    "body_set_angular_damping": [_W, C.c_int32, C.c_float],
+    "body_set_gravity_scale": [_W, C.c_int32, C.c_float],
+    "body_get": [_W, C.c_int32, C.POINTER(BodyRead)],
+    "world_set_restitution_threshold": [_W, C.c_float],
+    "world_set_hit_event_threshold": [_W, C.c_float],
+    "world_set_maximum_linear_speed": [_W, C.c_float],
     "world_set_gravity": [_W, Vec2],
     "world_enable_warm_starting": [_W, C.c_int32],
     "world_enable_speculative": [_W, C.c_int32],

@@ -70,6 +70,17 @@ int32_t b2cuda_body_set_angular_velocity(B2CWorld* h, int32_t id, float w) { CHE
 int32_t b2cuda_body_apply_force_to_center(B2CWorld* h, int32_t id, B2CVec2 f, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyForceToCenter(id, mk(f.x, f.y))); }
 int32_t b2cuda_body_apply_torque(B2CWorld* h, int32_t id, float t, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyTorque(id, t)); }
 int32_t b2cuda_body_apply_linear_impulse_to_center(B2CWorld* h, int32_t id, B2CVec2 i, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyLinearImpulseToCenter(id, mk(i.x, i.y))); }
+int32_t b2cuda_body_apply_force(B2CWorld* h, int32_t id, B2CVec2 f, B2CVec2 p, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyForce(id, mk(f.x, f.y), mk(p.x, p.y))); }
+int32_t b2cuda_body_clear_forces(B2CWorld* h, int32_t id) { CHECK_HANDLE(h); return done(h, h->w->clearForces(id)); }
+int32_t b2cuda_body_apply_linear_impulse(B2CWorld* h, int32_t id, B2CVec2 i, B2CVec2 p, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyLinearImpulse(id, mk(i.x, i.y), mk(p.x, p.y))); }
+int32_t b2cuda_body_apply_angular_impulse(B2CWorld* h, int32_t id, float i, int32_t) { CHECK_HANDLE(h); return done(h, h->w->applyAngularImpulse(id, i)); }
+int32_t b2cuda_body_set_linear_damping(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->setLinearDamping(id, v)); }
+int32_t b2cuda_body_set_angular_damping(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->setAngularDamping(id, v)); }
+int32_t b2cuda_body_set_gravity_scale(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->setGravityScale(id, v)); }
+int32_t b2cuda_body_get(B2CWorld* h, int32_t id, B2CBodyRead* out) { CHECK_HANDLE(h); if (!out) return B2C_E_INVALID; return done(h, h->w->readBody(id, out)); }
+int32_t b2cuda_world_set_restitution_threshold(B2CWorld* h, float v) { CHECK_HANDLE(h); h->w->restitutionThreshold = netClamp(v, 0.0f, FLT_MAX); return B2C_OK; }
+int32_t b2cuda_world_set_hit_event_threshold(B2CWorld* h, float v) { CHECK_HANDLE(h); h->w->hitEventThreshold = netClamp(v, 0.0f, FLT_MAX); return B2C_OK; }
+int32_t b2cuda_world_set_maximum_linear_speed(B2CWorld* h, float v) { CHECK_HANDLE(h); if (!(v > 0.0f)) return B2C_E_INVALID; h->w->maxLinearSpeed = v; return B2C_OK; }
 int32_t b2cuda_world_set_gravity(B2CWorld* h, B2CVec2 g) { CHECK_HANDLE(h); h->w->gravity = mk(g.x, g.y); return B2C_OK; }
 int32_t b2cuda_world_enable_warm_starting(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableWarmStarting = f != 0; return B2C_OK; }
 int32_t b2cuda_world_enable_speculative(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableSpeculative = f != 0; return B2C_OK; }

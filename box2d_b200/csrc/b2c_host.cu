@@ -3,6 +3,7 @@
 // (UpdateBodyMassData), src/joints/RevoluteJoint.cs:32-56 + src/Joint.cs:181-296 (CreateJoint),
 // src/ConstraintGraph.cs:91-128 (AssignJointColor). None of this is on the step path.
 #include "b2c_host.cuh"
+#include "b2c_treeops.cuh"
 #include <cstring>
 #include <cstdio>
 #include <algorithm>
@@ -287,9 +288,47 @@ int World::createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId) {
   return B2C_OK;
 }
 
+// BodyAPI.SetTransform after the upload: the same teleport as one device thread, ordered on the world's stream. The fat
+// box test needs the device's current fatAABB (enlarged by earlier steps), the proxy moves through the shared tree ops,
+// and BufferMove appends behind the moves the last step's FinalizeBodies buffered (src/BroadPhase.cs:56-59, :90-96).
+__global__ void k_set_transform(WorldDev d, int bodyId, V2 p, Rot q) {
+  Scalars& s = *d.sc;
+  Xf xf = mkXf(p, q);
+  float4 mass = d.bodyMass[bodyId];
+  V2 center = xfPoint(xf, mk(mass.z, mass.w));
+  float4 pose = make_float4(center.x, center.y, q.c, q.s);
+  d.bodyXf[bodyId] = make_float4(p.x, p.y, q.c, q.s);
+  d.bodyCenter[bodyId] = make_float2(center.x, center.y);
+  int sim = d.bodySim[bodyId];
+  if (sim >= 0) { d.simPose[sim] = pose; d.simPose0[sim] = pose; }
+  for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+    Box aabb = boxGrow(geomAABB(d.shapes[sid].geom, xf), kSpeculativeDistance);
+    d.shapeAABB[sid] = make_float4(aabb.lo.x, aabb.lo.y, aabb.hi.x, aabb.hi.y);
+    float4 f4 = d.shapeFat[sid]; Box cur; cur.lo = mk(f4.x, f4.y); cur.hi = mk(f4.z, f4.w);
+    if (boxContains(cur, aabb)) continue;
+    Box fat = boxGrow(aabb, kAABBMargin);
+    d.shapeFat[sid] = make_float4(fat.lo.x, fat.lo.y, fat.hi.x, fat.hi.y);
+    int key = d.shapes[sid].proxyKey;
+    if (key == -1) continue;
+    const TreeDev& t = d.trees[key & 3];
+    TreeView v{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta};
+    if (!tvMoveProxy(v, key >> 2, fat)) s.errorFlags |= (int)ERR_TREE;
+    if ((key & 3) == kStaticBody) s.staticRanksValid = 0;
+    if (!t.moved[key >> 2]) {
+      t.moved[key >> 2] = 1;
+      if (s.moveCount < d.moveCapacity) d.moveArray[s.moveCount++] = key; else s.errorFlags |= (int)ERR_PAIR_CAPACITY;
+    }
+  }
+}
+
 int World::setTransform(int bodyId, V2 p, Rot q) {          // api/Body.cs:293-325
-  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "body_set_transform after the first step is not supported in this build");
   if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (onDevice_) {
+    CK(cudaSetDevice(device_));
+    k_set_transform<<<1, 1, 0, stream_>>>(d_, bodyId, p, q);
+    CK(cudaGetLastError());
+    return B2C_OK;
+  }
   HBody& b = bodies_[bodyId];
   b.xf.p = p; b.xf.q = q;
   b.center = xfPoint(b.xf, b.localCenter);
@@ -509,51 +548,72 @@ int World::setAngularVelocity(int bodyId, float w) {
   CK(cudaStreamSynchronize(stream_));
   return B2C_OK;
 }
-int World::applyForceToCenter(int bodyId, V2 f) {            // api/Body.cs:457-467 (accumulates)
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
-  HBody& b = bodies_[bodyId];
-  if (b.type != kDynamicBody) return B2C_OK;
-  if (!onDevice_) { b.force = b.force + f; return B2C_OK; }
-  CK(cudaSetDevice(device_));
-  float cur[2];
-  CK(cudaMemcpyAsync(cur, &d_.simForce[b.simIndex], sizeof(cur), cudaMemcpyDeviceToHost, stream_));
-  CK(cudaStreamSynchronize(stream_));
-  cur[0] = cur[0] + f.x; cur[1] = cur[1] + f.y;
-  CK(cudaMemcpyAsync(&d_.simForce[b.simIndex], cur, sizeof(cur), cudaMemcpyHostToDevice, stream_));
-  CK(cudaStreamSynchronize(stream_));
-  return B2C_OK;
-}
-int World::applyTorque(int bodyId, float t) {                 // api/Body.cs:469-479 (assigns — port quirk)
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
-  HBody& b = bodies_[bodyId];
-  if (b.type != kDynamicBody) return B2C_OK;
-  if (!onDevice_) { b.torque = t; return B2C_OK; }
-  CK(cudaSetDevice(device_));
-  CK(cudaMemcpyAsync(&d_.simForce[b.simIndex].z, &t, sizeof(float), cudaMemcpyHostToDevice, stream_));
-  CK(cudaStreamSynchronize(stream_));
-  return B2C_OK;
-}
-int World::applyLinearImpulseToCenter(int bodyId, V2 imp) {   // api/Body.cs:531-545
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
-  HBody& b = bodies_[bodyId];
-  if (b.type != kDynamicBody) return B2C_OK;
-  V2 v = b.v;
-  if (onDevice_) {
-    CK(cudaSetDevice(device_));
-    float cur[2];
-    CK(cudaMemcpyAsync(cur, &d_.st0[b.simIndex], sizeof(cur), cudaMemcpyDeviceToHost, stream_));
-    CK(cudaStreamSynchronize(stream_));
-    v = mk(cur[0], cur[1]);
+// Force / impulse / per-body tuning mutators run as a one-thread kernel ordered on the world's stream: no read-back, no
+// synchronisation, and the arithmetic is the reference's expression by expression (fp32, no contraction).
+enum BodyOp { OP_FORCE_CENTER, OP_FORCE_POINT, OP_TORQUE, OP_CLEAR_FORCES, OP_IMPULSE_CENTER, OP_IMPULSE_POINT, OP_ANGULAR_IMPULSE,
+              OP_LINEAR_DAMPING, OP_ANGULAR_DAMPING, OP_GRAVITY_SCALE };
+__global__ void k_body_op(WorldDev d, int op, int sim, V2 a, V2 point, float maxLinearSpeed) {
+  float4 f = d.simForce[sim], m = d.simMass[sim], s0 = d.st0[sim];
+  V2 center = mk(d.simPose[sim].x, d.simPose[sim].y);
+  switch (op) {
+    case OP_FORCE_CENTER: f.x = f.x + a.x; f.y = f.y + a.y; d.simForce[sim] = f; break;                                  // api/Body.cs:457-467
+    case OP_FORCE_POINT: f.x = f.x + a.x; f.y = f.y + a.y; f.z += cross(point - center, a); d.simForce[sim] = f; break;  // :439-451
+    case OP_TORQUE: f.z = a.x; d.simForce[sim] = f; break;                                                               // :469-479 (assigns — port quirk)
+    case OP_CLEAR_FORCES: f.x = 0.0f; f.y = 0.0f; f.z = 0.0f; d.simForce[sim] = f; break;                                // :486-491
+    case OP_IMPULSE_CENTER: case OP_IMPULSE_POINT: {                                                                     // :504-520, :531-545
+      V2 v = mulAdd(mk(s0.x, s0.y), m.x, a);
+      if (op == OP_IMPULSE_POINT) s0.z += m.y * cross(point - center, a);
+      float v2 = lengthSq(v);                                                                                            // src/Body.cs:131-135
+      if (v2 > maxLinearSpeed * maxLinearSpeed) v = (maxLinearSpeed / sqrtf(v2)) * v;
+      s0.x = v.x; s0.y = v.y; d.st0[sim] = s0;
+    } break;
+    case OP_ANGULAR_IMPULSE: s0.z += m.y * a.x; d.st0[sim] = s0; break;                                                  // :554-568
+    case OP_LINEAR_DAMPING: m.z = a.x; d.simMass[sim] = m; break;                                                        // :624-629
+    case OP_ANGULAR_DAMPING: m.w = a.x; d.simMass[sim] = m; break;                                                       // :635-640
+    case OP_GRAVITY_SCALE: f.w = a.x; d.simForce[sim] = f; break;                                                        // :647-653
   }
-  v = mulAdd(v, b.invMass, imp);
-  float v2 = lengthSq(v);
-  if (v2 > maxLinearSpeed * maxLinearSpeed) v = (maxLinearSpeed / sqrtf(v2)) * v;
-  if (!onDevice_) { b.v = v; return B2C_OK; }
-  float xy[2] = {v.x, v.y};
-  CK(cudaMemcpyAsync(&d_.st0[b.simIndex], xy, sizeof(xy), cudaMemcpyHostToDevice, stream_));
-  CK(cudaStreamSynchronize(stream_));
+}
+int World::bodyOp(int bodyId, int op, V2 a, V2 point) {
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  const bool tuning = op == OP_LINEAR_DAMPING || op == OP_ANGULAR_DAMPING || op == OP_GRAVITY_SCALE;
+  if (!tuning && op != OP_CLEAR_FORCES && b.type != kDynamicBody) return B2C_OK;
+  if (!onDevice_) {                                 // before the first step the host mirror is the world
+    switch (op) {
+      case OP_FORCE_CENTER: b.force = b.force + a; break;
+      case OP_FORCE_POINT: b.force = b.force + a; b.torque += cross(point - b.center, a); break;
+      case OP_TORQUE: b.torque = a.x; break;
+      case OP_CLEAR_FORCES: b.force = mk(0, 0); b.torque = 0; break;
+      case OP_IMPULSE_CENTER: case OP_IMPULSE_POINT: {
+        V2 v = mulAdd(b.v, b.invMass, a);
+        if (op == OP_IMPULSE_POINT) b.w += b.invInertia * cross(point - b.center, a);
+        float v2 = lengthSq(v);
+        if (v2 > maxLinearSpeed * maxLinearSpeed) v = (maxLinearSpeed / sqrtf(v2)) * v;
+        b.v = v;
+      } break;
+      case OP_ANGULAR_IMPULSE: b.w += b.invInertia * a.x; break;
+      case OP_LINEAR_DAMPING: b.linearDamping = a.x; break;
+      case OP_ANGULAR_DAMPING: b.angularDamping = a.x; break;
+      case OP_GRAVITY_SCALE: b.gravityScale = a.x; break;
+    }
+    return B2C_OK;
+  }
+  if (b.simIndex < 0) return B2C_OK;               // static bodies have no solver rows
+  CK(cudaSetDevice(device_));
+  k_body_op<<<1, 1, 0, stream_>>>(d_, op, b.simIndex, a, point, maxLinearSpeed);
+  CK(cudaGetLastError());
   return B2C_OK;
 }
+int World::applyForceToCenter(int bodyId, V2 f) { return bodyOp(bodyId, OP_FORCE_CENTER, f, mk(0, 0)); }
+int World::applyForce(int bodyId, V2 f, V2 p) { return bodyOp(bodyId, OP_FORCE_POINT, f, p); }
+int World::applyTorque(int bodyId, float t) { return bodyOp(bodyId, OP_TORQUE, mk(t, 0), mk(0, 0)); }
+int World::clearForces(int bodyId) { return bodyOp(bodyId, OP_CLEAR_FORCES, mk(0, 0), mk(0, 0)); }
+int World::applyLinearImpulseToCenter(int bodyId, V2 i) { return bodyOp(bodyId, OP_IMPULSE_CENTER, i, mk(0, 0)); }
+int World::applyLinearImpulse(int bodyId, V2 i, V2 p) { return bodyOp(bodyId, OP_IMPULSE_POINT, i, p); }
+int World::applyAngularImpulse(int bodyId, float i) { return bodyOp(bodyId, OP_ANGULAR_IMPULSE, mk(i, 0), mk(0, 0)); }
+int World::setLinearDamping(int bodyId, float v) { return bodyOp(bodyId, OP_LINEAR_DAMPING, mk(v, 0), mk(0, 0)); }
+int World::setAngularDamping(int bodyId, float v) { return bodyOp(bodyId, OP_ANGULAR_DAMPING, mk(v, 0), mk(0, 0)); }
+int World::setGravityScale(int bodyId, float v) { return bodyOp(bodyId, OP_GRAVITY_SCALE, mk(v, 0), mk(0, 0)); }
 
 // ---- read-back ----
 template <class T> static int fetch(std::vector<T>& out, const T* dev, size_t n, cudaStream_t s) {
@@ -588,6 +648,30 @@ int World::readBodies(B2CBodyRead* dst, int capacity, int* count) {
     }
     dst[i] = r;
   }
+  return B2C_OK;
+}
+
+// BodyAPI.GetTransform / GetLinearVelocity / GetAngularVelocity / GetWorldCenterOfMass for one body (api/Body.cs:218-259, :589)
+int World::readBody(int bodyId, B2CBodyRead* out) {
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id == -1) return fail(B2C_E_INVALID, "bad body id");
+  const HBody& b = bodies_[bodyId]; B2CBodyRead r; memset(&r, 0, sizeof(r));
+  if (!onDevice_) {
+    r.transform.p = {b.xf.p.x, b.xf.p.y}; r.transform.q = {b.xf.q.c, b.xf.q.s}; r.center = {b.center.x, b.center.y};
+    r.linearVelocity = {b.v.x, b.v.y}; r.angularVelocity = b.w; r.flags = b.flags;
+    *out = r; return B2C_OK;
+  }
+  int rc = synchronize(); if (rc) return rc;
+  float4 xf; float2 ctr; float4 s = make_float4(0, 0, 0, 0); uint32_t sf = b.flags;
+  CK(cudaMemcpyAsync(&xf, &d_.bodyXf[bodyId], sizeof(xf), cudaMemcpyDeviceToHost, stream_));
+  CK(cudaMemcpyAsync(&ctr, &d_.bodyCenter[bodyId], sizeof(ctr), cudaMemcpyDeviceToHost, stream_));
+  if (b.simIndex >= 0) {
+    CK(cudaMemcpyAsync(&s, &d_.st0[b.simIndex], sizeof(s), cudaMemcpyDeviceToHost, stream_));
+    CK(cudaMemcpyAsync(&sf, &d_.simFlags[b.simIndex], sizeof(sf), cudaMemcpyDeviceToHost, stream_));
+  }
+  CK(cudaStreamSynchronize(stream_));
+  r.transform.p = {xf.x, xf.y}; r.transform.q = {xf.z, xf.w}; r.center = {ctr.x, ctr.y};
+  r.linearVelocity = {s.x, s.y}; r.angularVelocity = s.z; r.flags = sf;
+  *out = r;
   return B2C_OK;
 }
 

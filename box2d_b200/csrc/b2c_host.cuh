@@ -26,20 +26,7 @@ struct HostTree {
   int capacity() const { return (int)aabb.size(); }
   int createProxy(Box box, uint64_t categoryBits, int userData);
   void moveProxy(int id, Box box);
- private:
-  int allocNode();
-  void freeNode(int id);
-  int findBestSibling(Box boxD);
-  void rotate(int iA);
-  void applyRot(int iA, int iInner, int iMove, int iUp, int iStay, bool aChild1, bool innerChild1, Box box);
-  void insertLeaf(int leaf, bool shouldRotate);
-  void removeLeaf(int leaf);
-  Box box(int i) const { float4 a = aabb[i]; Box b; b.lo = mk(a.x, a.y); b.hi = mk(a.z, a.w); return b; }
-  void setBox(int i, Box b) { aabb[i] = make_float4(b.lo.x, b.lo.y, b.hi.x, b.hi.y); }
-  int height(int i) const { return (int)(hf[i] & 0xffffu); }
-  uint32_t flags(int i) const { return hf[i] >> 16; }
-  void setHeight(int i, int h) { hf[i] = (hf[i] & 0xffff0000u) | (uint32_t)h; }
-  void orFlags(int i, uint32_t f) { hf[i] |= f << 16; }
+  void ensureFreeNode();
 };
 
 struct HBody {                  // src/Body.cs:35-93 Body + BodySim + BodyState at creation time
@@ -77,6 +64,15 @@ class World {
   int applyForceToCenter(int bodyId, V2 f);
   int applyTorque(int bodyId, float t);
   int applyLinearImpulseToCenter(int bodyId, V2 i);
+  int applyForce(int bodyId, V2 f, V2 point);
+  int clearForces(int bodyId);
+  int applyLinearImpulse(int bodyId, V2 i, V2 point);
+  int applyAngularImpulse(int bodyId, float i);
+  int setLinearDamping(int bodyId, float v);
+  int setAngularDamping(int bodyId, float v);
+  int setGravityScale(int bodyId, float v);
+  int bodyOp(int bodyId, int op, V2 a, V2 point);
+  int readBody(int bodyId, B2CBodyRead* out);
   // --- step + readback (device) ---
   int step(float dt, int subSteps);
   int synchronize();

@@ -141,6 +141,22 @@ int32_t b2cuda_body_set_angular_velocity(B2CWorld* world, int32_t bodyId, float 
 int32_t b2cuda_body_apply_force_to_center(B2CWorld* world, int32_t bodyId, B2CVec2 force, int32_t wake);
 int32_t b2cuda_body_apply_torque(B2CWorld* world, int32_t bodyId, float torque, int32_t wake);
 int32_t b2cuda_body_apply_linear_impulse_to_center(B2CWorld* world, int32_t bodyId, B2CVec2 impulse, int32_t wake);
+/* BodyAPI.ApplyForce :439 / ClearForces :486 / ApplyLinearImpulse :504 / ApplyAngularImpulse :554 / SetLinearDamping :624 /
+ * SetAngularDamping :635 / SetGravityScale :647 — api/Body.cs. Stream-ordered device patches: no host synchronisation. */
+int32_t b2cuda_body_apply_force(B2CWorld* world, int32_t bodyId, B2CVec2 force, B2CVec2 point, int32_t wake);
+int32_t b2cuda_body_clear_forces(B2CWorld* world, int32_t bodyId);
+int32_t b2cuda_body_apply_linear_impulse(B2CWorld* world, int32_t bodyId, B2CVec2 impulse, B2CVec2 point, int32_t wake);
+int32_t b2cuda_body_apply_angular_impulse(B2CWorld* world, int32_t bodyId, float impulse, int32_t wake);
+int32_t b2cuda_body_set_linear_damping(B2CWorld* world, int32_t bodyId, float linearDamping);
+int32_t b2cuda_body_set_angular_damping(B2CWorld* world, int32_t bodyId, float angularDamping);
+int32_t b2cuda_body_set_gravity_scale(B2CWorld* world, int32_t bodyId, float gravityScale);
+/* BodyAPI.GetTransform :218 / GetLinearVelocity :250 / GetAngularVelocity :256 / GetWorldCenterOfMass :589 for one body
+ * (synchronises with the world's stream; use b2cuda_world_read_bodies or the move events for bulk reads). */
+int32_t b2cuda_body_get(B2CWorld* world, int32_t bodyId, B2CBodyRead* out);
+/* WorldAPI.SetRestitutionThreshold :666 / SetHitEventThreshold :678 / SetMaximumLinearSpeed :789 — api/World.cs */
+int32_t b2cuda_world_set_restitution_threshold(B2CWorld* world, float value);
+int32_t b2cuda_world_set_hit_event_threshold(B2CWorld* world, float value);
+int32_t b2cuda_world_set_maximum_linear_speed(B2CWorld* world, float maximumLinearSpeed);
 /* WorldAPI.SetGravity :698 / EnableWarmStarting :801 / EnableSpeculative :941 / EnableContinuous :654 / SetContactTuning :780 */
 int32_t b2cuda_world_set_gravity(B2CWorld* world, B2CVec2 gravity);
 int32_t b2cuda_world_enable_warm_starting(B2CWorld* world, int32_t flag);

@@ -61,6 +61,17 @@ int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAng
 int32_t b2o_body_apply_force_to_center(World* w, int32_t id, B2CVec2 f, int32_t) { w->ApplyForceToCenter(id, V(f)); return 0; }
 int32_t b2o_body_apply_torque(World* w, int32_t id, float t, int32_t) { w->ApplyTorque(id, t); return 0; }
 int32_t b2o_body_apply_linear_impulse_to_center(World* w, int32_t id, B2CVec2 i, int32_t) { w->ApplyLinearImpulseToCenter(id, V(i)); return 0; }
+int32_t b2o_body_apply_force(World* w, int32_t id, B2CVec2 f, B2CVec2 p, int32_t) { w->ApplyForce(id, V(f), V(p)); return 0; }
+int32_t b2o_body_clear_forces(World* w, int32_t id) { w->ClearForces(id); return 0; }
+int32_t b2o_body_apply_linear_impulse(World* w, int32_t id, B2CVec2 i, B2CVec2 p, int32_t) { w->ApplyLinearImpulse(id, V(i), V(p)); return 0; }
+int32_t b2o_body_apply_angular_impulse(World* w, int32_t id, float i, int32_t) { w->ApplyAngularImpulse(id, i); return 0; }
+int32_t b2o_body_set_linear_damping(World* w, int32_t id, float v) { w->SetLinearDamping(id, v); return 0; }
+int32_t b2o_body_set_angular_damping(World* w, int32_t id, float v) { w->SetAngularDamping(id, v); return 0; }
+int32_t b2o_body_set_gravity_scale(World* w, int32_t id, float v) { w->SetGravityScale(id, v); return 0; }
+// api/World.cs:666-670, :678-682, :789-794
+int32_t b2o_world_set_restitution_threshold(World* w, float v) { w->restitutionThreshold = v < 0 ? 0 : v; return 0; }
+int32_t b2o_world_set_hit_event_threshold(World* w, float v) { w->hitEventThreshold = v < 0 ? 0 : v; return 0; }
+int32_t b2o_world_set_maximum_linear_speed(World* w, float v) { w->maxLinearSpeed = v; return 0; }
 int32_t b2o_world_set_gravity(World* w, B2CVec2 g) { w->gravity = V(g); return 0; }
 int32_t b2o_world_enable_warm_starting(World* w, int32_t f) { w->enableWarmStarting = f != 0; return 0; }
 int32_t b2o_world_enable_speculative(World* w, int32_t f) { w->enableSpeculative = f != 0; return 0; }
@@ -97,6 +108,15 @@ int32_t b2o_world_read_bodies(World* w, B2CBodyRead* dst, int32_t capacity, int3
     }
     dst[i] = r;
   }
+  return 0;
+}
+int32_t b2o_body_get(World* w, int32_t id, B2CBodyRead* out) {      // api/Body.cs:218-259, :589
+  if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id == -1) return 1;
+  B2CBodyRead r; memset(&r, 0, sizeof(r));
+  const Body& b = w->bodies[id]; const BodySim& s = w->GetBodySim(b);
+  r.transform.p = CV(s.transform.p); r.transform.q = {s.transform.q.c, s.transform.q.s}; r.center = CV(s.center); r.flags = s.flags;
+  if (const BodyState* st = w->GetBodyState(b)) { r.linearVelocity = CV(st->linearVelocity); r.angularVelocity = st->angularVelocity; }
+  *out = r;
   return 0;
 }
 static thread_local std::vector<B2CBodyRead> tBodies;

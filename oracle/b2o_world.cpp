@@ -288,4 +288,36 @@ void World::ApplyLinearImpulseToCenter(int bodyId, Vec2 impulse) {   // api/Body
   }
 }
 
+void World::ApplyForce(int bodyId, Vec2 force, Vec2 point) {   // api/Body.cs:439-451
+  Body& body = bodies[bodyId]; if (body.type != kDynamicBody) return;
+  if (body.setIndex == kAwakeSet) {
+    BodySim& sim = GetBodySim(body);
+    sim.force = sim.force + force;
+    sim.torque += Cross(point - sim.center, force);
+  }
+}
+void World::ClearForces(int bodyId) {                          // api/Body.cs:486-491
+  BodySim& sim = GetBodySim(bodies[bodyId]); sim.force = {0, 0}; sim.torque = 0;
+}
+void World::ApplyLinearImpulse(int bodyId, Vec2 impulse, Vec2 point) {   // api/Body.cs:504-520
+  Body& body = bodies[bodyId]; if (body.type != kDynamicBody) return;
+  if (body.setIndex == kAwakeSet) {
+    BodyState& st = awakeSet.bodyStates[body.localIndex]; const BodySim& sim = awakeSet.bodySims[body.localIndex];
+    st.linearVelocity = MulAdd(st.linearVelocity, sim.invMass, impulse);
+    st.angularVelocity += sim.invInertia * Cross(point - sim.center, impulse);
+    float v2 = LengthSquared(st.linearVelocity);
+    if (v2 > maxLinearSpeed * maxLinearSpeed) st.linearVelocity = st.linearVelocity * (maxLinearSpeed / sqrtf(v2));
+  }
+}
+void World::ApplyAngularImpulse(int bodyId, float impulse) {   // api/Body.cs:554-568
+  Body& body = bodies[bodyId]; if (body.type != kDynamicBody) return;
+  if (body.setIndex == kAwakeSet) {
+    BodyState& st = awakeSet.bodyStates[body.localIndex]; const BodySim& sim = awakeSet.bodySims[body.localIndex];
+    st.angularVelocity += sim.invInertia * impulse;
+  }
+}
+void World::SetLinearDamping(int bodyId, float v) { GetBodySim(bodies[bodyId]).linearDamping = v; }     // api/Body.cs:624-629
+void World::SetAngularDamping(int bodyId, float v) { GetBodySim(bodies[bodyId]).angularDamping = v; }   // api/Body.cs:635-640
+void World::SetGravityScale(int bodyId, float v) { GetBodySim(bodies[bodyId]).gravityScale = v; }       // api/Body.cs:647-653
+
 }  // namespace b2o

@@ -190,6 +190,13 @@ class World {
   void ApplyForceToCenter(int bodyId, Vec2 force);
   void ApplyTorque(int bodyId, float torque);
   void ApplyLinearImpulseToCenter(int bodyId, Vec2 impulse);
+  void ApplyForce(int bodyId, Vec2 force, Vec2 point);
+  void ClearForces(int bodyId);
+  void ApplyLinearImpulse(int bodyId, Vec2 impulse, Vec2 point);
+  void ApplyAngularImpulse(int bodyId, float impulse);
+  void SetLinearDamping(int bodyId, float v);
+  void SetAngularDamping(int bodyId, float v);
+  void SetGravityScale(int bodyId, float v);
   void Step(float timeStep, int subStepCount);
 
   // --- state ---

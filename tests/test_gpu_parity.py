@@ -1,7 +1,7 @@
 """-m gpu: the CUDA step vs the oracle through the C-ABI, bit-exact unless a tolerance is stated."""
 import pytest
 import parity
-from box2d_b200 import scenes
+from box2d_b200 import api, scenes
 
 pytestmark = pytest.mark.gpu
 
@@ -135,3 +135,96 @@ def test_body_move_events_match_reference_layout():
     finally:
         cuda.Destroy()
         orc.Destroy()
+
+
+def _poke(world, step):
+    """Every body mutator of the boundary, interleaved with steps (api/Body.cs:293-653, api/World.cs:666-794)."""
+    if step == 0:                                   # before the first step: the host mirror takes the patch
+        world.SetGravityScale(3, 0.5)
+        world.SetLinearDamping(4, 0.8)
+        world.SetAngularDamping(4, 1.5)
+        world.ApplyLinearImpulse(5, (0.7, 1.9), (0.2, 3.1))
+        world.ApplyForce(6, (30.0, 12.0), (1.0, 2.0))
+        world.ApplyAngularImpulse(7, 0.35)
+    if step == 2:
+        world.ApplyForce(9, (-40.0, 25.0), (0.3, 4.4))
+        world.ApplyForceToCenter(9, (3.0, 1.0))
+        world.ApplyTorque(10, 7.5)
+        world.ApplyForce(11, (50.0, 50.0), (0.0, 0.0))
+        world.ClearForces(11)
+    if step == 3:
+        world.ApplyLinearImpulse(12, (2.5, 0.25), (-1.2, 2.6))
+        world.ApplyLinearImpulseToCenter(13, (-1.0, 3.0))
+        world.ApplyAngularImpulse(14, -0.6)
+        world.SetGravityScale(15, -0.25)
+        world.SetLinearDamping(16, 2.0)
+        world.SetAngularDamping(16, 0.4)
+        world.SetLinearVelocity(17, (1.5, 6.0))
+        world.SetAngularVelocity(18, -3.0)
+    if step == 5:
+        world.SetRestitutionThreshold(0.25)
+        world.SetHitEventThreshold(0.1)
+        world.SetMaximumLinearSpeed(5.0)
+        world.ApplyLinearImpulse(20, (40.0, 90.0), (0.0, 5.0))     # clipped by the new speed limit
+    if step == 7:
+        world.SetTransform(21, (6.0, 9.0), (0.8, 0.6))
+        world.SetMaximumLinearSpeed(4.0 * 100.0)
+
+
+def test_body_and_world_mutators_between_steps_bit_exact():
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 8), steps=24, mutate=_poke)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_single_body_getters_match_bulk_read():
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        scenes.add_pyramid(cuda, 5)
+        for phase in range(2):                      # host mirror, then device rows
+            bulk = cuda.ReadBodies()
+            for i in (0, 1, 7, 15):
+                (p, q), v, w, c = cuda.GetTransform(i), cuda.GetLinearVelocity(i), cuda.GetAngularVelocity(i), cuda.GetWorldCenterOfMass(i)
+                r = bulk[i]
+                assert p == (r["transform"]["p"]["x"], r["transform"]["p"]["y"]) and q == (r["transform"]["q"]["c"], r["transform"]["q"]["s"])
+                assert v == (r["linearVelocity"]["x"], r["linearVelocity"]["y"]) and w == r["angularVelocity"]
+                assert c == (r["center"]["x"], r["center"]["y"])
+            for _ in range(5):
+                cuda.Step(1.0 / 60.0, 4)
+        with pytest.raises(Exception):
+            cuda.GetTransform(10_000)
+    finally:
+        cuda.Destroy()
+
+
+def _teleport(world, step):
+    """BodyAPI.SetTransform after the upload (api/Body.cs:293-325): device-side MoveProxy + BufferMove."""
+    if step == 3:
+        world.SetTransform(55, (7.5, 0.6), (1.0, 0.0))            # the top box, dropped beside the pile
+    if step == 5:
+        world.SetTransform(0, (0.25, -0.05), (1.0, 0.0))          # the static ground: static tree move, pairs re-found
+    if step == 8:
+        world.SetTransform(54, (0.1, 3.2), (0.6, 0.8))            # into the middle of the pile
+        world.SetTransform(54, (0.2, 3.3), (0.6, 0.8))            # twice: buffered once
+        world.SetTransform(12, (-30.0, 40.0), (0.0, 1.0))         # far away: every contact of the box ends
+    if step == 9:
+        world.SetTransform(12, (-30.0, 40.01), (0.0, 1.0))        # inside the fat box: no proxy move
+    if step == 12:
+        for b in range(20, 30):
+            world.SetTransform(b, (float(b) - 25.0, 14.0 + 0.01 * b), (1.0, 0.0))
+
+
+def test_set_transform_after_upload_bit_exact():
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 10), steps=30, mutate=_teleport)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_set_transform_kinematic_and_jointed_bodies():
+    def poke(world, step):
+        if step in (4, 9):
+            world.SetTransform(0, (0.0, 0.5 if step == 4 else -0.5), (0.98006657, 0.19866933))   # the kinematic tumbler frame
+            world.SetTransform(40, (0.0, 10.0), (1.0, 0.0))
+    res = parity.run_pair(lambda w: scenes.tumbler(w, 400), steps=16, mutate=poke)
+    assert res["max_rel_err"] == 0.0
+    res = parity.run_pair(lambda w: scenes.joint_grid(w, 8), steps=12,
+                          mutate=lambda w, s: w.SetTransform(10, (3.0, -2.0), (0.8, -0.6)) if s == 5 else None)
+    assert res["max_rel_err"] == 0.0
