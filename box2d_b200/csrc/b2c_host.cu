@@ -559,8 +559,8 @@ __global__ void k_body_op(WorldDev d, int op, int sim, V2 a, V2 point, float max
     case OP_FORCE_CENTER: f.x = f.x + a.x; f.y = f.y + a.y; d.simForce[sim] = f; break;                                  // api/Body.cs:457-467
     case OP_FORCE_POINT: f.x = f.x + a.x; f.y = f.y + a.y; f.z += cross(point - center, a); d.simForce[sim] = f; break;  // :439-451
     case OP_TORQUE: f.z = a.x; d.simForce[sim] = f; break;                                                               // :469-479 (assigns — port quirk)
-    case OP_CLEAR_FORCES: f.x = 0.0f; f.y = 0.0f; f.z = 0.0f; d.simForce[sim] = f; break;                                // :486-491
-    case OP_IMPULSE_CENTER: case OP_IMPULSE_POINT: {                                                                     // :504-520, :531-545
+    case OP_CLEAR_FORCES: f.x = 0.0f; f.y = 0.0f; f.z = 0.0f; d.simForce[sim] = f; break;                                // :490-495
+    case OP_IMPULSE_CENTER: case OP_IMPULSE_POINT: {                                                                     // :507-523, :531-545
       V2 v = mulAdd(mk(s0.x, s0.y), m.x, a);
       if (op == OP_IMPULSE_POINT) s0.z += m.y * cross(point - center, a);
       float v2 = lengthSq(v);                                                                                            // src/Body.cs:131-135
@@ -651,7 +651,7 @@ int World::readBodies(B2CBodyRead* dst, int capacity, int* count) {
   return B2C_OK;
 }
 
-// BodyAPI.GetTransform / GetLinearVelocity / GetAngularVelocity / GetWorldCenterOfMass for one body (api/Body.cs:218-259, :589)
+// BodyAPI.GetTransform / GetLinearVelocity / GetAngularVelocity / GetWorldCenterOfMass for one body (api/Body.cs:288, :345-357, :580)
 int World::readBody(int bodyId, B2CBodyRead* out) {
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id == -1) return fail(B2C_E_INVALID, "bad body id");
   const HBody& b = bodies_[bodyId]; B2CBodyRead r; memset(&r, 0, sizeof(r));

@@ -141,7 +141,7 @@ int32_t b2cuda_body_set_angular_velocity(B2CWorld* world, int32_t bodyId, float 
 int32_t b2cuda_body_apply_force_to_center(B2CWorld* world, int32_t bodyId, B2CVec2 force, int32_t wake);
 int32_t b2cuda_body_apply_torque(B2CWorld* world, int32_t bodyId, float torque, int32_t wake);
 int32_t b2cuda_body_apply_linear_impulse_to_center(B2CWorld* world, int32_t bodyId, B2CVec2 impulse, int32_t wake);
-/* BodyAPI.ApplyForce :439 / ClearForces :486 / ApplyLinearImpulse :504 / ApplyAngularImpulse :554 / SetLinearDamping :624 /
+/* BodyAPI.ApplyForce :439 / ClearForces :490 / ApplyLinearImpulse :507 / ApplyAngularImpulse :554 / SetLinearDamping :624 /
  * SetAngularDamping :635 / SetGravityScale :647 — api/Body.cs. Stream-ordered device patches: no host synchronisation. */
 int32_t b2cuda_body_apply_force(B2CWorld* world, int32_t bodyId, B2CVec2 force, B2CVec2 point, int32_t wake);
 int32_t b2cuda_body_clear_forces(B2CWorld* world, int32_t bodyId);
@@ -150,7 +150,7 @@ int32_t b2cuda_body_apply_angular_impulse(B2CWorld* world, int32_t bodyId, float
 int32_t b2cuda_body_set_linear_damping(B2CWorld* world, int32_t bodyId, float linearDamping);
 int32_t b2cuda_body_set_angular_damping(B2CWorld* world, int32_t bodyId, float angularDamping);
 int32_t b2cuda_body_set_gravity_scale(B2CWorld* world, int32_t bodyId, float gravityScale);
-/* BodyAPI.GetTransform :218 / GetLinearVelocity :250 / GetAngularVelocity :256 / GetWorldCenterOfMass :589 for one body
+/* BodyAPI.GetTransform :288 / GetLinearVelocity :345 / GetAngularVelocity :352 / GetWorldCenterOfMass :580 for one body
  * (synchronises with the world's stream; use b2cuda_world_read_bodies or the move events for bulk reads). */
 int32_t b2cuda_body_get(B2CWorld* world, int32_t bodyId, B2CBodyRead* out);
 /* WorldAPI.SetRestitutionThreshold :666 / SetHitEventThreshold :678 / SetMaximumLinearSpeed :789 — api/World.cs */

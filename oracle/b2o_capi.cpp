@@ -110,7 +110,7 @@ int32_t b2o_world_read_bodies(World* w, B2CBodyRead* dst, int32_t capacity, int3
   }
   return 0;
 }
-int32_t b2o_body_get(World* w, int32_t id, B2CBodyRead* out) {      // api/Body.cs:218-259, :589
+int32_t b2o_body_get(World* w, int32_t id, B2CBodyRead* out) {      // api/Body.cs:288, :345-357, :580
   if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id == -1) return 1;
   B2CBodyRead r; memset(&r, 0, sizeof(r));
   const Body& b = w->bodies[id]; const BodySim& s = w->GetBodySim(b);

@@ -296,10 +296,10 @@ void World::ApplyForce(int bodyId, Vec2 force, Vec2 point) {   // api/Body.cs:43
     sim.torque += Cross(point - sim.center, force);
   }
 }
-void World::ClearForces(int bodyId) {                          // api/Body.cs:486-491
+void World::ClearForces(int bodyId) {                          // api/Body.cs:490-495
   BodySim& sim = GetBodySim(bodies[bodyId]); sim.force = {0, 0}; sim.torque = 0;
 }
-void World::ApplyLinearImpulse(int bodyId, Vec2 impulse, Vec2 point) {   // api/Body.cs:504-520
+void World::ApplyLinearImpulse(int bodyId, Vec2 impulse, Vec2 point) {   // api/Body.cs:507-523
   Body& body = bodies[bodyId]; if (body.type != kDynamicBody) return;
   if (body.setIndex == kAwakeSet) {
     BodyState& st = awakeSet.bodyStates[body.localIndex]; const BodySim& sim = awakeSet.bodySims[body.localIndex];
