@@ -11,7 +11,7 @@ product library; the oracle is bound only by tests/ (never from this package).
 import ctypes as C
 import numpy as np
 from . import capi
-from .capi import (Vec2, Rot, Transform, WorldDef, BodyDef, ShapeDef, Geometry, RevoluteJointDef, BodyRead, ContactRead,
+from .capi import (Vec2, Rot, Transform, WorldDef, BodyDef, ShapeDef, Geometry, RevoluteJointDef, JointDef, BodyRead, ContactRead,
                    ContactTouchEvent, ContactHitEvent, JointRead, ShapeRead, Counters, Profile)
 
 STATIC_BODY, KINEMATIC_BODY, DYNAMIC_BODY = 0, 1, 2
@@ -75,6 +75,27 @@ def default_revolute_joint_def():
     d.constraintHertz = 60.0
     d.constraintDampingRatio = 2.0
     d.drawScale = 1.0
+    return d
+
+
+def default_joint_def(joint_type):
+    """JointDef base include/Types.cs:431-456 + the per-type defaults :460-586 (Distance/Motor/Filter/Prismatic/Revolute/Weld/Wheel
+    JointDef), flattened as B2CJointDef. ``joint_type`` is the reference's JointType value (capi.JOINT_*)."""
+    d = JointDef()
+    d.type = joint_type
+    d.bodyIdA = -1
+    d.bodyIdB = -1
+    d.localFrameA = Transform(Vec2(0, 0), Rot(1, 0))
+    d.localFrameB = Transform(Vec2(0, 0), Rot(1, 0))
+    d.forceThreshold = FLT_MAX
+    d.torqueThreshold = FLT_MAX
+    d.constraintHertz = 60.0
+    d.constraintDampingRatio = 2.0
+    d.drawScale = 1.0
+    d.length = 1.0
+    d.maxLength = 100000.0
+    d.lowerSpringForce = -FLT_MAX
+    d.upperSpringForce = FLT_MAX
     return d
 
 
@@ -207,6 +228,34 @@ class World:
         out = C.c_int32(-1)
         self._check(self.fns["create_revolute_joint"](self.handle, C.byref(joint_def), C.byref(out)))
         return out.value
+
+    def CreateJoint(self, joint_def):
+        """JointAPI.Create{Distance,Motor,Filter,Prismatic,Revolute,Weld,Wheel}Joint api/Joint.cs:182,324,408,412,555,672,720"""
+        out = C.c_int32(-1)
+        self._check(self.fns["create_joint"](self.handle, C.byref(joint_def), C.byref(out)))
+        return out.value
+
+    def _typed(self, joint_def, joint_type):
+        assert joint_def.type == joint_type, "joint definition built for another joint type"
+        return self.CreateJoint(joint_def)
+
+    def CreateDistanceJoint(self, joint_def):
+        return self._typed(joint_def, capi.JOINT_DISTANCE)
+
+    def CreateMotorJoint(self, joint_def):
+        return self._typed(joint_def, capi.JOINT_MOTOR)
+
+    def CreateFilterJoint(self, joint_def):
+        return self._typed(joint_def, capi.JOINT_FILTER)
+
+    def CreatePrismaticJoint(self, joint_def):
+        return self._typed(joint_def, capi.JOINT_PRISMATIC)
+
+    def CreateWeldJoint(self, joint_def):
+        return self._typed(joint_def, capi.JOINT_WELD)
+
+    def CreateWheelJoint(self, joint_def):
+        return self._typed(joint_def, capi.JOINT_WHEEL)
 
     # --- WorldAPI ---
     def SetGravity(self, g):

@@ -61,6 +61,23 @@ class RevoluteJointDef(C.Structure):
                 ("enableMotor", C.c_int32), ("maxMotorTorque", C.c_float), ("motorSpeed", C.c_float)]
 
 
+JOINT_DISTANCE, JOINT_FILTER, JOINT_MOTOR, JOINT_PRISMATIC, JOINT_REVOLUTE, JOINT_WELD, JOINT_WHEEL = range(7)
+
+
+class JointDef(C.Structure):
+    _fields_ = [("type", C.c_int32), ("bodyIdA", C.c_int32), ("bodyIdB", C.c_int32), ("localFrameA", Transform),
+                ("localFrameB", Transform), ("forceThreshold", C.c_float), ("torqueThreshold", C.c_float),
+                ("constraintHertz", C.c_float), ("constraintDampingRatio", C.c_float), ("drawScale", C.c_float),
+                ("collideConnected", C.c_int32), ("userData", C.c_uint64), ("enableSpring", C.c_int32),
+                ("enableLimit", C.c_int32), ("enableMotor", C.c_int32), ("hertz", C.c_float), ("dampingRatio", C.c_float),
+                ("target", C.c_float), ("lower", C.c_float), ("upper", C.c_float), ("maxMotor", C.c_float),
+                ("motorSpeed", C.c_float), ("length", C.c_float), ("minLength", C.c_float), ("maxLength", C.c_float),
+                ("lowerSpringForce", C.c_float), ("upperSpringForce", C.c_float), ("angularHertz", C.c_float),
+                ("angularDampingRatio", C.c_float), ("linearVelocity", Vec2), ("angularVelocity", C.c_float),
+                ("maxVelocityForce", C.c_float), ("maxVelocityTorque", C.c_float), ("maxSpringForce", C.c_float),
+                ("maxSpringTorque", C.c_float)]
+
+
 class BodyRead(C.Structure):
     _fields_ = [("transform", Transform), ("center", Vec2), ("linearVelocity", Vec2), ("angularVelocity", C.c_float),
                 ("flags", C.c_uint32)]
@@ -89,7 +106,8 @@ class ContactHitEvent(C.Structure):
 
 class JointRead(C.Structure):
     _fields_ = [("jointId", C.c_int32), ("colorIndex", C.c_int32), ("linearImpulse", Vec2), ("springImpulse", C.c_float),
-                ("motorImpulse", C.c_float), ("lowerImpulse", C.c_float), ("upperImpulse", C.c_float)]
+                ("motorImpulse", C.c_float), ("lowerImpulse", C.c_float), ("upperImpulse", C.c_float),
+                ("type", C.c_int32), ("linearImpulse2", Vec2)]
 
 
 class ShapeRead(C.Structure):
@@ -120,6 +138,7 @@ PROTOS = {
     "create_body": [_W, C.POINTER(BodyDef), C.POINTER(C.c_int32)],
     "create_shape": [_W, C.c_int32, C.POINTER(ShapeDef), C.POINTER(Geometry), C.POINTER(C.c_int32)],
     "create_revolute_joint": [_W, C.POINTER(RevoluteJointDef), C.POINTER(C.c_int32)],
+    "create_joint": [_W, C.POINTER(JointDef), C.POINTER(C.c_int32)],
     "body_set_transform": [_W, C.c_int32, Vec2, Rot],
     "body_set_linear_velocity": [_W, C.c_int32, Vec2],
     "body_set_angular_velocity": [_W, C.c_int32, C.c_float],
@@ -164,6 +183,7 @@ PRODUCT_ONLY = {
     "default_body_def": ([C.POINTER(BodyDef)], C.c_int32),
     "default_shape_def": ([C.POINTER(ShapeDef)], C.c_int32),
     "default_revolute_joint_def": ([C.POINTER(RevoluteJointDef)], C.c_int32),
+    "default_joint_def": ([C.c_int32, C.POINTER(JointDef)], C.c_int32),
     "world_create": ([C.POINTER(WorldDef), C.c_int32, C.POINTER(_W)], C.c_int32),
     "world_get_profile": ([_W, C.POINTER(Profile)], C.c_int32),
     "world_timer_start": ([_W], C.c_int32),

@@ -41,6 +41,14 @@ int32_t b2cuda_default_revolute_joint_def(B2CRevoluteJointDef* d) {   // include
   d->forceThreshold = FLT_MAX; d->torqueThreshold = FLT_MAX; d->constraintHertz = 60.0f; d->constraintDampingRatio = 2.0f; d->drawScale = 1.0f;
   return B2C_OK;
 }
+int32_t b2cuda_default_joint_def(int32_t type, B2CJointDef* d) {   // include/Types.cs:431-456 (base) and :460-586 (per type)
+  if (!d || type < B2C_JOINT_DISTANCE || type > B2C_JOINT_WHEEL) return B2C_E_INVALID;
+  memset(d, 0, sizeof(*d));
+  d->type = type; d->bodyIdA = -1; d->bodyIdB = -1; d->localFrameA.q = {1.0f, 0.0f}; d->localFrameB.q = {1.0f, 0.0f};
+  d->forceThreshold = FLT_MAX; d->torqueThreshold = FLT_MAX; d->constraintHertz = 60.0f; d->constraintDampingRatio = 2.0f; d->drawScale = 1.0f;
+  d->length = 1.0f; d->maxLength = 100000.0f; d->lowerSpringForce = -FLT_MAX; d->upperSpringForce = FLT_MAX;   // DistanceJointDef :465-482
+  return B2C_OK;
+}
 
 int32_t b2cuda_world_create(const B2CWorldDef* def, int32_t device, B2CWorld** out) {
   if (!def || !out) { g_lastError = "null argument"; return B2C_E_INVALID; }
@@ -64,6 +72,7 @@ int32_t b2cuda_create_shape(B2CWorld* h, int32_t bodyId, const B2CShapeDef* def,
   CHECK_HANDLE(h); if (!def || !g || !shapeId) return B2C_E_INVALID; return done(h, h->w->createShape(bodyId, *def, *g, shapeId));
 }
 int32_t b2cuda_create_revolute_joint(B2CWorld* h, const B2CRevoluteJointDef* def, int32_t* jointId) { CHECK_HANDLE(h); if (!def || !jointId) return B2C_E_INVALID; return done(h, h->w->createRevoluteJoint(*def, jointId)); }
+int32_t b2cuda_create_joint(B2CWorld* h, const B2CJointDef* def, int32_t* jointId) { CHECK_HANDLE(h); if (!def || !jointId) return B2C_E_INVALID; return done(h, h->w->createJoint(*def, jointId)); }
 int32_t b2cuda_body_set_transform(B2CWorld* h, int32_t id, B2CVec2 p, B2CRot q) { CHECK_HANDLE(h); return done(h, h->w->setTransform(id, mk(p.x, p.y), mkRot(q.c, q.s))); }
 int32_t b2cuda_body_set_linear_velocity(B2CWorld* h, int32_t id, B2CVec2 v) { CHECK_HANDLE(h); return done(h, h->w->setLinearVelocity(id, mk(v.x, v.y))); }
 int32_t b2cuda_body_set_angular_velocity(B2CWorld* h, int32_t id, float w) { CHECK_HANDLE(h); return done(h, h->w->setAngularVelocity(id, w)); }

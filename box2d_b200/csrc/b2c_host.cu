@@ -252,8 +252,21 @@ int World::assignJointColor(int bodyIdA, int bodyIdB, int typeA, int typeB) {   
   return kOverflowIndex;
 }
 
-int World::createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId) {
-  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_revolute_joint after the first step is not supported in this build");
+int World::createRevoluteJoint(const B2CRevoluteJointDef& r, int* jointId) {     // api/Joint.cs:555 -> the generic path
+  B2CJointDef def; memset(&def, 0, sizeof(def));
+  def.type = B2C_JOINT_REVOLUTE; def.bodyIdA = r.bodyIdA; def.bodyIdB = r.bodyIdB; def.localFrameA = r.localFrameA; def.localFrameB = r.localFrameB;
+  def.forceThreshold = r.forceThreshold; def.torqueThreshold = r.torqueThreshold; def.constraintHertz = r.constraintHertz;
+  def.constraintDampingRatio = r.constraintDampingRatio; def.drawScale = r.drawScale; def.collideConnected = r.collideConnected; def.userData = r.userData;
+  def.enableSpring = r.enableSpring; def.enableLimit = r.enableLimit; def.enableMotor = r.enableMotor; def.hertz = r.hertz; def.dampingRatio = r.dampingRatio;
+  def.target = r.targetAngle; def.lower = r.lowerAngle; def.upper = r.upperAngle; def.maxMotor = r.maxMotorTorque; def.motorSpeed = r.motorSpeed;
+  return createJoint(def, jointId);
+}
+
+// World.CreateJoint src/Joint.cs:181-296 + the per-type Create (DistanceJoint.cs:35-63, FilterJoint.cs:7-17, MotorJoint.cs:33-52,
+// PrismaticJoint.cs:33-53, RevoluteJoint.cs:32-56, WeldJoint.cs:24-39, WheelJoint.cs:33-56)
+int World::createJoint(const B2CJointDef& def, int* jointId) {
+  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_joint after the first step is not supported in this build");
+  if (def.type < B2C_JOINT_DISTANCE || def.type > B2C_JOINT_WHEEL) return fail(B2C_E_INVALID, "bad joint type");
   int nb = (int)bodies_.size();
   if (def.bodyIdA < 0 || def.bodyIdA >= nb || def.bodyIdB < 0 || def.bodyIdB >= nb) return fail(B2C_E_INVALID, "bad body id");
   HBody& bodyA = bodies_[def.bodyIdA]; HBody& bodyB = bodies_[def.bodyIdB];
@@ -273,15 +286,44 @@ int World::createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId) {
   if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   JointDev& s = j.sim;
   memset(&s, 0, sizeof(s));
-  s.jointId = id; s.bodyIdA = bodyA.id; s.bodyIdB = bodyB.id; s.colorIndex = color;
+  s.jointId = id; s.bodyIdA = bodyA.id; s.bodyIdB = bodyB.id; s.colorIndex = color; s.type = def.type;
   auto T = [](B2CTransform t) { return mkXf(mk(t.p.x, t.p.y), mkRot(t.q.c, t.q.s)); };
   s.localFrameA = T(def.localFrameA); s.localFrameB = T(def.localFrameB);
   s.constraintHertz = def.constraintHertz; s.constraintDampingRatio = def.constraintDampingRatio;
   s.forceThreshold = def.forceThreshold; s.torqueThreshold = def.torqueThreshold;
-  s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.targetAngle = netClamp(def.targetAngle, -kPi, kPi);
-  s.maxMotorTorque = def.maxMotorTorque; s.motorSpeed = def.motorSpeed; s.lowerAngle = def.lowerAngle; s.upperAngle = def.upperAngle;
-  s.enableSpring = def.enableSpring != 0; s.enableMotor = def.enableMotor != 0; s.enableLimit = def.enableLimit != 0;
   s.constraintSoftness.biasRate = 0; s.constraintSoftness.massScale = 1; s.constraintSoftness.impulseScale = 0;
+  const bool spring = def.enableSpring != 0, limit = def.enableLimit != 0, motor = def.enableMotor != 0;
+  switch (def.type) {
+    case B2C_JOINT_REVOLUTE:
+      s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.targetAngle = netClamp(def.target, -kPi, kPi);
+      s.maxMotorTorque = def.maxMotor; s.motorSpeed = def.motorSpeed; s.lowerAngle = def.lower; s.upperAngle = def.upper;
+      s.enableSpring = spring; s.enableMotor = motor; s.enableLimit = limit;
+      break;
+    case B2C_JOINT_DISTANCE:
+      if (!(def.length > 0.0f) || !(def.lowerSpringForce <= def.upperSpringForce)) return fail(B2C_E_INVALID, "distance joint: length must be > 0 and lowerSpringForce <= upperSpringForce");
+      s.length = netMax(def.length, kLinearSlop); s.hertz = def.hertz; s.dampingRatio = def.dampingRatio;
+      s.minLength = netMax(def.minLength, kLinearSlop); s.maxLength = netMax(def.minLength, def.maxLength);
+      s.maxMotorTorque = def.maxMotor; s.motorSpeed = def.motorSpeed; s.lowerSpringForce = def.lowerSpringForce; s.upperSpringForce = def.upperSpringForce;
+      s.enableSpring = spring; s.enableMotor = motor; s.enableLimit = limit;
+      break;
+    case B2C_JOINT_FILTER: break;
+    case B2C_JOINT_MOTOR:
+      s.linearVelocity = mk(def.linearVelocity.x, def.linearVelocity.y); s.maxVelocityForce = def.maxVelocityForce; s.angularVelocity = def.angularVelocity;
+      s.maxVelocityTorque = def.maxVelocityTorque; s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.maxSpringForce = def.maxSpringForce;
+      s.angularHertz = def.angularHertz; s.angularDampingRatio = def.angularDampingRatio; s.maxSpringTorque = def.maxSpringTorque;
+      break;
+    case B2C_JOINT_PRISMATIC:
+      s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.targetAngle = def.target; s.lowerAngle = def.lower; s.upperAngle = def.upper;
+      s.maxMotorTorque = def.maxMotor; s.motorSpeed = def.motorSpeed; s.enableSpring = spring; s.enableMotor = motor; s.enableLimit = limit;
+      break;
+    case B2C_JOINT_WELD:
+      s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.angularHertz = def.angularHertz; s.angularDampingRatio = def.angularDampingRatio;
+      break;
+    case B2C_JOINT_WHEEL:
+      s.lowerAngle = def.lower; s.upperAngle = def.upper; s.maxMotorTorque = def.maxMotor; s.motorSpeed = def.motorSpeed;
+      s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.enableSpring = spring; s.enableMotor = motor; s.enableLimit = limit;
+      break;
+  }
   colorJoints_[color].push_back(id);
   // DestroyContactsBetweenBodies (src/Joint.cs:155-180): no contacts exist before the first step.
   *jointId = id;
@@ -719,7 +761,7 @@ int World::readJoints(B2CJointRead* dst, int capacity, int* count) {
   } else { jd.resize(n); for (int i = 0; i < n; i++) jd[i] = joints_[i].sim; }
   for (int i = 0; i < n && i < capacity; i++) {
     const JointDev& s = jd[i];
-    dst[i] = {s.jointId, s.colorIndex, {s.linearImpulse.x, s.linearImpulse.y}, s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse};
+    dst[i] = {s.jointId, s.colorIndex, {s.linearImpulse.x, s.linearImpulse.y}, s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse, s.type, {s.linearImpulse2.x, s.linearImpulse2.y}};
   }
   return B2C_OK;
 }

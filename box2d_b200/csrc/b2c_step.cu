@@ -843,10 +843,24 @@ __device__ __forceinline__ void storeImpulsesRegs(const WorldDev& d, int ci, flo
   d.mC0[ci].z = relVel1; d.mC1[ci].z = relVel2;
 }
 
-// ---- revolute joint (src/Joint.cs:125-130, src/joints/RevoluteJoint.cs:72-235) ----
+#include "b2c_joints.cuh"
+
+__device__ __noinline__ void prepareJointOther(const StepParams& sp, JointDev& j, float invMassA, float invMassB) {
+  switch (j.type) {
+    case kDistanceJoint: prepareDistance(sp, j, invMassA, invMassB); break;
+    case kMotorJoint: prepareMotor(sp, j); break;
+    case kPrismaticJoint: preparePrismatic(sp, j); break;
+    case kWeldJoint: prepareWeld(sp, j); break;
+    case kWheelJoint: prepareWheel(sp, j); break;
+    default: break;
+  }
+}
+// ---- JointSim.PrepareJoint src/Joint.cs:125-130 + IJoint.Prepare: the body/frame part is the same text in every joint type
+// (RevoluteJoint.cs:72-95, WeldJoint.cs:46-66, MotorJoint.cs:60-81, PrismaticJoint.cs:86-106, WheelJoint.cs:91-111, DistanceJoint.cs:91-113) ----
 __device__ void prepareJoint(const WorldDev& d, const StepParams& sp, JointDev& j) {
   float hertz = netMin(j.constraintHertz, 0.25f * sp.inv_h);
   j.constraintSoftness = makeSoft(hertz, j.constraintDampingRatio, sp.h);
+  if (j.type == kFilterJoint) return;
   float4 massA = d.bodyMass[j.bodyIdA], massB = d.bodyMass[j.bodyIdB];
   j.invMassA = massA.x; j.invIA = massA.y; j.invMassB = massB.x; j.invIB = massB.y;
   j.indexA = d.bodySim[j.bodyIdA]; j.indexB = d.bodySim[j.bodyIdB];
@@ -857,12 +871,14 @@ __device__ void prepareJoint(const WorldDev& d, const StepParams& sp, JointDev& 
   j.frameB.p = rotate(xfB.q, j.localFrameB.p - mk(massB.z, massB.w));
   float2 cA = d.bodyCenter[j.bodyIdA], cB = d.bodyCenter[j.bodyIdB];
   j.deltaCenter = mk(cB.x, cB.y) - mk(cA.x, cA.y);
+  if (j.type != kRevoluteJoint) { prepareJointOther(sp, j, massA.x, massB.x); return; }
+  // revolute: src/joints/RevoluteJoint.cs:96-104
   float k = j.invIA + j.invIB;
   j.axialMass = k > 0.0f ? 1.0f / k : 0.0f;
   j.springSoftness = makeSoft(j.hertz, j.dampingRatio, sp.h);
   if (!sp.enableWarmStarting) { j.linearImpulse = mk(0, 0); j.springImpulse = 0; j.motorImpulse = 0; j.lowerImpulse = 0; j.upperImpulse = 0; }
 }
-__device__ void warmStartJoint(const WorldDev& d, JointDev& j) {
+__device__ void warmStartRevolute(const WorldDev& d, JointDev& j) {
   BodyW bA = gatherBody(d, j.indexA), bB = gatherBody(d, j.indexB);
   V2 rA = rotate(bA.dq, j.frameA.p), rB = rotate(bB.dq, j.frameB.p);
   float axialImpulse = j.springImpulse + j.motorImpulse + j.lowerImpulse - j.upperImpulse;
@@ -876,7 +892,7 @@ __device__ void warmStartJoint(const WorldDev& d, JointDev& j) {
   }
   scatterBody(d, j.indexA, bA); scatterBody(d, j.indexB, bB);
 }
-__device__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {
+__device__ void solveRevolute(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {
   float mA = j.invMassA, mB = j.invMassB, iA = j.invIA, iB = j.invIB;
   BodyW bA = gatherBody(d, j.indexA), bB = gatherBody(d, j.indexB);
   V2 vA = bA.v, vB = bB.v; float wA = bA.w, wB = bB.w;
@@ -953,8 +969,36 @@ __device__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j,
   }
   bA.v = vA; bA.w = wA; bB.v = vB; bB.w = wB;
   scatterBody(d, j.indexA, bA); scatterBody(d, j.indexB, bB);
+}
+// Joint types other than revolute are kept out of line (their own frames and registers): the cooperative front kernel is compiled for
+// 512 threads x 128 registers and the configs' hot joint is the revolute, which stays inline.
+__device__ __noinline__ void warmStartJointOther(const WorldDev& d, JointDev& j) {
+  switch (j.type) {
+    case kDistanceJoint: warmStartDistance(d, j); break;
+    case kMotorJoint: warmStartLinearAngular(d, j, j.linearImpulse + j.linearImpulse2, j.motorImpulse + j.springImpulse); break;
+    case kPrismaticJoint: warmStartPrismatic(d, j); break;
+    case kWeldJoint: warmStartLinearAngular(d, j, j.linearImpulse, j.springImpulse); break;
+    case kWheelJoint: warmStartWheel(d, j); break;
+    default: break;                                                    // filter: IJoint default, empty
+  }
+}
+__device__ __noinline__ void solveJointOther(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {
+  switch (j.type) {
+    case kDistanceJoint: solveDistance(d, sp, j, useBias); break;
+    case kMotorJoint: solveMotor(d, sp, j); break;
+    case kPrismaticJoint: solvePrismatic(d, sp, j, useBias); break;
+    case kWeldJoint: solveWeld(d, sp, j, useBias); break;
+    case kWheelJoint: solveWheel(d, sp, j, useBias); break;
+    default: break;
+  }
+}
+__device__ __forceinline__ void warmStartJoint(const WorldDev& d, JointDev& j) {      // JointSim.WarmStart src/Joint.cs:131
+  if (j.type == kRevoluteJoint) warmStartRevolute(d, j); else warmStartJointOther(d, j);
+}
+__device__ __forceinline__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {    // JointSim.Solve src/Joint.cs:132 + SolveJointsTask src/Solver.cs:180-198
+  if (j.type == kRevoluteJoint) solveRevolute(d, sp, j, useBias); else solveJointOther(d, sp, j, useBias);
   if (useBias && (j.forceThreshold < FLT_MAX || j.torqueThreshold < FLT_MAX) && !d.jointEventFlag[j.jointId]) {   // src/Solver.cs:186-196
-    float force = length(j.linearImpulse) * sp.inv_h, torque = fabsf(j.motorImpulse + j.lowerImpulse - j.upperImpulse) * sp.inv_h;
+    float force, torque; jointReaction(j, sp.inv_h, &force, &torque);
     if (force >= j.forceThreshold || torque >= j.torqueThreshold) d.jointEventFlag[j.jointId] = 1;
   }
 }

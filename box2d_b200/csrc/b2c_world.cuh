@@ -64,7 +64,22 @@ struct JointDev {      // src/Joint.cs:74-133 + src/joints/RevoluteJoint.cs:6-31
   Softness constraintSoftness, springSoftness;
   // accumulated impulses
   V2 linearImpulse; float springImpulse, motorImpulse, lowerImpulse, upperImpulse;
+  // ---- joint types other than revolute (src/joints/*.cs). The slots above are shared where the reference's field plays the same role:
+  //   distance  impulse -> springImpulse, maxMotorForce -> maxMotorTorque, distanceSoftness -> springSoftness, anchorA/B -> frameA/B.p
+  //   weld      linearHertz/linearDampingRatio -> hertz/dampingRatio, angularImpulse -> springImpulse, linearSpring -> springSoftness
+  //   motor     linearVelocityImpulse -> linearImpulse, angularVelocityImpulse -> motorImpulse, linearSpringImpulse -> linearImpulse2,
+  //             angularSpringImpulse -> springImpulse, angularMass -> axialMass, linearSpring -> springSoftness
+  //   prismatic impulse -> linearImpulse, targetTranslation -> targetAngle, maxMotorForce -> maxMotorTorque, lower/upperTranslation -> lower/upperAngle
+  //   wheel     perpImpulse -> linearImpulse.x, lower/upperTranslation -> lower/upperAngle
+  int type;            // JointType include/Types.cs:423-426
+  float length, minLength, maxLength, lowerSpringForce, upperSpringForce;                              // distance
+  float angularHertz, angularDampingRatio;                                                             // weld, motor
+  float maxSpringForce, maxSpringTorque, maxVelocityForce, maxVelocityTorque, angularVelocity;         // motor
+  V2 linearVelocity, linearImpulse2;
+  Softness angularSoftness; float4 linearMass;   // Mat22 as (cx.x, cx.y, cy.x, cy.y)
+  float perpMass, motorMass;
 };
+enum { kDistanceJoint = 0, kFilterJoint = 1, kMotorJoint = 2, kPrismaticJoint = 3, kRevoluteJoint = 4, kWeldJoint = 5, kWheelJoint = 6 };
 
 // scalar overflow constraint (src/ContactSolver.cs:9-37)
 struct OvPoint { V2 anchorA, anchorB; float baseSeparation, relativeVelocity, normalImpulse, tangentImpulse, totalNormalImpulse, normalMass, tangentMass; };

@@ -210,6 +210,140 @@ def overflow_plank(world, n=26):
     return ground, plank, bodies
 
 
+def joint_zoo(world, copies=1, pitch=40.0, angles=True):
+    """Every joint type of the reference (include/Types.cs:423-426) with its options switched on, over a ground segment so that
+    contacts share the colouring with the joints: rigid and springy distance joints (limit + motor), rigid and soft welds, a
+    prismatic slider (spring, limit, motor), motor joints (velocity and spring drives), a filter joint (overlapping bodies that must not collide) and a revolute pendulum with force/torque thresholds."""
+    J = api.capi
+    sd = _shape_def()
+    out = []
+    for c in range(copies):
+        ox = c * pitch
+        ground = world.CreateBody(api.default_body_def())
+        world.CreateSegmentShape(ground, sd, geo.Segment((ox - 18.0, 0.0), (ox + 18.0, 0.0)))
+
+        def dyn(x, y, angle=0.0, w=0.0, v=(0.0, 0.0)):
+            bd = api.default_body_def()
+            bd.type = api.DYNAMIC_BODY
+            bd.position = api.Vec2(ox + x, y)
+            bd.rotation = api.Rot(float(np.float32(np.cos(angle))), float(np.float32(np.sin(angle))))
+            bd.angularVelocity = w
+            bd.linearVelocity = api.Vec2(*v)
+            return world.CreateBody(bd)
+
+        def jdef(t, a, b, pa, pb, qa=0.0, qb=0.0):
+            d = api.default_joint_def(t)
+            d.bodyIdA, d.bodyIdB = a, b
+            d.localFrameA = api.Transform(api.Vec2(*pa), api.Rot(float(np.float32(np.cos(qa))), float(np.float32(np.sin(qa)))))
+            d.localFrameB = api.Transform(api.Vec2(*pb), api.Rot(float(np.float32(np.cos(qb))), float(np.float32(np.sin(qb)))))
+            return d
+
+        ids = {}
+        # distance: rigid rope from the ground anchor, then a springy link with limits and a motor between two dynamic bodies
+        b0 = dyn(-15.0, 6.0, w=0.5)
+        world.CreatePolygonShape(b0, sd, geo.MakeBox(0.4, 0.3))
+        d = jdef(J.JOINT_DISTANCE, ground, b0, (ox - 14.0, 9.0), (0.2, 0.1))
+        d.length = 3.0
+        d.forceThreshold = 20.0
+        ids["distance_rigid"] = world.CreateJoint(d)
+        b1 = dyn(-15.0, 4.0)
+        world.CreateCircleShape(b1, sd, geo.Circle((0.0, 0.0), 0.35))
+        d = jdef(J.JOINT_DISTANCE, b0, b1, (0.0, -0.3), (0.0, 0.1))
+        d.length = 1.5
+        d.enableSpring, d.hertz, d.dampingRatio = 1, 2.0, 0.3
+        d.lowerSpringForce, d.upperSpringForce = -50.0, 80.0
+        d.enableLimit, d.minLength, d.maxLength = 1, 1.0, 2.2
+        d.enableMotor, d.maxMotor, d.motorSpeed = 1, 3.0, 0.5
+        ids["distance_spring"] = world.CreateJoint(d)
+        # weld: rigid cantilever off the ground body, then a soft weld at its tip
+        prev, px = ground, -10.0
+        for k in range(3 if angles else 0):
+            b = dyn(px + 1.0 * k + 0.5, 5.0)
+            world.CreatePolygonShape(b, sd, geo.MakeBox(0.5, 0.125))
+            if prev == ground:
+                d = jdef(J.JOINT_WELD, prev, b, (ox + px, 5.0), (-0.5, 0.0))
+            else:
+                d = jdef(J.JOINT_WELD, prev, b, (0.5, 0.0), (-0.5, 0.0))
+            if k == 2:
+                d.hertz, d.dampingRatio, d.angularHertz, d.angularDampingRatio = 5.0, 0.7, 3.0, 0.5
+                d.torqueThreshold = 0.5
+            ids[f"weld{k}"] = world.CreateJoint(d)
+            prev = b
+        # prismatic: slider on a tilted axis with spring, limits and a motor
+        if angles:
+            b = dyn(-4.0, 3.0, angle=0.2)
+            world.CreatePolygonShape(b, sd, geo.MakeBox(0.5, 0.25))
+            d = jdef(J.JOINT_PRISMATIC, ground, b, (ox - 4.0, 3.0), (0.0, 0.0), qa=0.35, qb=0.15)
+            d.enableSpring, d.hertz, d.dampingRatio, d.target = 1, 1.5, 0.4, 0.5
+            d.enableLimit, d.lower, d.upper = 1, -1.0, 2.0
+            d.enableMotor, d.maxMotor, d.motorSpeed = 1, 8.0, -1.0
+            ids["prismatic"] = world.CreateJoint(d)
+            b2 = dyn(-1.0, 2.0)
+            world.CreateCircleShape(b2, sd, geo.Circle((0.0, 0.0), 0.3))
+            d = jdef(J.JOINT_PRISMATIC, b, b2, (0.5, 0.0), (0.0, 0.0), qa=1.2)
+            ids["prismatic_plain"] = world.CreateJoint(d)
+        # motor: velocity drive against the ground, spring drive between two dynamic bodies
+        m0 = dyn(10.0, 4.0)
+        world.CreatePolygonShape(m0, sd, geo.MakeBox(0.4, 0.4))
+        d = jdef(J.JOINT_MOTOR, ground, m0, (ox + 10.0, 4.0), (0.0, 0.0))
+        d.linearVelocity, d.maxVelocityForce = api.Vec2(0.5, 0.25), 200.0
+        d.angularVelocity, d.maxVelocityTorque = 1.0, 20.0
+        ids["motor_velocity"] = world.CreateJoint(d)
+        m1 = dyn(12.0, 4.5, angle=0.3)
+        world.CreateCapsuleShape(m1, sd, geo.Capsule((-0.3, 0.0), (0.3, 0.0), 0.15))
+        d = jdef(J.JOINT_MOTOR, m0, m1, (0.4, 0.0), (-0.45, 0.0))
+        d.hertz, d.dampingRatio, d.maxSpringForce = 3.0, 0.5, 60.0
+        if angles:
+            d.angularHertz, d.angularDampingRatio, d.maxSpringTorque = 2.0, 0.8, 5.0
+        d.maxVelocityForce, d.maxVelocityTorque = 1.0, 0.5
+        ids["motor_spring"] = world.CreateJoint(d)
+        # filter: two overlapping boxes that fall together without colliding
+        f0, f1 = dyn(15.0, 2.0), dyn(15.2, 2.1)
+        world.CreatePolygonShape(f0, sd, geo.MakeBox(0.4, 0.4))
+        world.CreatePolygonShape(f1, sd, geo.MakeBox(0.4, 0.4))
+        ids["filter"] = world.CreateJoint(jdef(J.JOINT_FILTER, f0, f1, (0.0, 0.0), (0.0, 0.0)))
+        # revolute pendulum with thresholds (joint events)
+        p0 = dyn(-17.0, 3.0)
+        world.CreatePolygonShape(p0, sd, geo.MakeBox(0.2, 1.0))
+        d = jdef(J.JOINT_REVOLUTE, ground, p0, (ox - 17.0, 4.0), (0.0, 1.0))
+        d.forceThreshold = 5.0
+        ids["revolute"] = world.CreateJoint(d)
+        out.append(ids)
+    return out
+
+
+def wheel_rig(world, copies=1, pitch=12.0):
+    """Wheel joints (spring, limit, motor). The port's WheelJoint.Solve measures the point-to-line velocity along axisA instead of
+    perpA (src/joints/WheelJoint.cs:266), so a free chassis on two sprung wheels gains energy within a few steps; the rig hangs the
+    wheels from the static ground body on vertical axes instead, where the same code stays bounded, and adds one free two-body pair."""
+    J = api.capi
+    sd = _shape_def()
+    out = []
+    for c in range(copies):
+        ox = c * pitch
+        ground = world.CreateBody(api.default_body_def())
+        world.CreateSegmentShape(ground, sd, geo.Segment((ox - 6.0, -20.0), (ox + 6.0, -20.0)))      # out of reach: the rig swings wide
+        ids = []
+        for k, wx in enumerate((-3.0, 0.0, 3.0)):
+            bd = api.default_body_def()
+            bd.type = api.DYNAMIC_BODY
+            bd.position = api.Vec2(ox + wx, 2.0)
+            bd.angularVelocity = 0.5 * k
+            wheel = world.CreateBody(bd)
+            world.CreateCircleShape(wheel, sd, geo.Circle((0.0, 0.0), 0.4))
+            d = api.default_joint_def(J.JOINT_WHEEL)
+            d.bodyIdA, d.bodyIdB = ground, wheel
+            q = 0.5 * np.pi + 0.1 * k
+            d.localFrameA = api.Transform(api.Vec2(ox + wx, 2.0), api.Rot(float(np.float32(np.cos(q))), float(np.float32(np.sin(q)))))
+            d.enableSpring, d.hertz, d.dampingRatio = 1, 3.0, 0.7
+            d.enableLimit, d.lower, d.upper = int(k != 1), -0.15, 0.25
+            d.enableMotor, d.maxMotor, d.motorSpeed = int(k != 2), 4.0, 2.0
+            d.torqueThreshold = 1.0
+            ids.append(world.CreateJoint(d))
+        out.append(ids)
+    return out
+
+
 def batched_pyramids(world, n_worlds=8192, first=0, rows=10, pitch=15.0, cols=128):
     """BASELINE.json configs[4]: `n_worlds` independent 10-row pyramids (world index first..first+n), each on its own ground,
     x positions jittered per world by splitmix64(seed=world index) so worlds are not bit-copies."""
@@ -224,5 +358,7 @@ SCENES = {
     "joint_grid": joint_grid,
     "mixed_drop": mixed_drop,
     "overflow_plank": overflow_plank,
+    "joint_zoo": joint_zoo,
+    "wheel_rig": wheel_rig,
     "batched_pyramids": batched_pyramids,
 }

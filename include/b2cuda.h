@@ -82,6 +82,33 @@ typedef struct B2CRevoluteJointDef {
   int32_t enableMotor; float maxMotorTorque, motorSpeed;
 } B2CRevoluteJointDef;
 
+/* Generic joint definition: JointDef base (include/Types.cs:431-456) + the per-type definitions flattened — DistanceJointDef :460-492,
+ * MotorJointDef :496-523, FilterJointDef :524-529, PrismaticJointDef :530-545, RevoluteJointDef :546-561, WeldJointDef :562-570,
+ * WheelJointDef :571-586. `type` is the reference's JointType (include/Types.cs:423-426). Fields a type does not have are ignored.
+ *   hertz/dampingRatio   distance, prismatic, revolute, wheel spring; weld/motor LINEAR hertz/dampingRatio
+ *   target               revolute targetAngle / prismatic targetTranslation
+ *   lower/upper          revolute angles / prismatic, wheel translations
+ *   maxMotor             revolute, wheel maxMotorTorque / distance, prismatic maxMotorForce */
+#define B2C_JOINT_DISTANCE 0
+#define B2C_JOINT_FILTER 1
+#define B2C_JOINT_MOTOR 2
+#define B2C_JOINT_PRISMATIC 3
+#define B2C_JOINT_REVOLUTE 4
+#define B2C_JOINT_WELD 5
+#define B2C_JOINT_WHEEL 6
+typedef struct B2CJointDef {
+  int32_t type, bodyIdA, bodyIdB;
+  B2CTransform localFrameA, localFrameB;
+  float forceThreshold, torqueThreshold, constraintHertz, constraintDampingRatio, drawScale;
+  int32_t collideConnected;
+  uint64_t userData;
+  int32_t enableSpring, enableLimit, enableMotor;
+  float hertz, dampingRatio, target, lower, upper, maxMotor, motorSpeed;
+  float length, minLength, maxLength, lowerSpringForce, upperSpringForce;              /* distance */
+  float angularHertz, angularDampingRatio;                                             /* weld, motor */
+  B2CVec2 linearVelocity; float angularVelocity, maxVelocityForce, maxVelocityTorque, maxSpringForce, maxSpringTorque;   /* motor */
+} B2CJointDef;
+
 /* Read-back records */
 typedef struct B2CBodyRead {      /* BodyAPI.GetTransform/GetLinearVelocity/GetAngularVelocity... api/Body.cs:282-357 */
   B2CTransform transform; B2CVec2 center; B2CVec2 linearVelocity; float angularVelocity; uint32_t flags;
@@ -103,7 +130,11 @@ typedef struct B2CContactRead {         /* ContactAPI.GetData api/Contact.cs + g
 } B2CContactRead;
 typedef struct B2CContactTouchEvent { int32_t shapeIdA, shapeIdB, contactId; uint32_t contactGeneration; } B2CContactTouchEvent; /* include/Types.cs:697-730 */
 typedef struct B2CContactHitEvent { int32_t shapeIdA, shapeIdB; B2CVec2 point, normal; float approachSpeed; } B2CContactHitEvent;
-typedef struct B2CJointRead { int32_t jointId, colorIndex; B2CVec2 linearImpulse; float springImpulse, motorImpulse, lowerImpulse, upperImpulse; } B2CJointRead;
+/* Accumulated joint impulses. Slots by type (reference field -> slot): revolute as named; distance impulse -> springImpulse; weld
+ * angularImpulse -> springImpulse; prismatic impulse -> linearImpulse; wheel perpImpulse -> linearImpulse.x; motor linearVelocityImpulse ->
+ * linearImpulse, angularVelocityImpulse -> motorImpulse, linearSpringImpulse -> linearImpulse2, angularSpringImpulse -> springImpulse. */
+typedef struct B2CJointRead { int32_t jointId, colorIndex; B2CVec2 linearImpulse; float springImpulse, motorImpulse, lowerImpulse, upperImpulse;
+                              int32_t type; B2CVec2 linearImpulse2; } B2CJointRead;
 typedef struct B2CShapeRead { B2CVec2 aabbLo, aabbHi, fatLo, fatHi; int32_t proxyKey, enlarged; } B2CShapeRead;
 typedef struct B2CCounters {            /* WorldAPI.GetCounters api/World.cs:817-834 */
   int32_t bodyCount, awakeBodyCount, shapeCount, contactCount, touchingContactCount, jointCount, contactIdCapacity,
@@ -133,6 +164,10 @@ int32_t b2cuda_create_body(B2CWorld* world, const B2CBodyDef* def, int32_t* body
 int32_t b2cuda_create_shape(B2CWorld* world, int32_t bodyId, const B2CShapeDef* def, const B2CGeometry* geometry, int32_t* shapeId);
 /* JointAPI.CreateRevoluteJoint — api/Joint.cs:555, src/joints/RevoluteJoint.cs:32-56 */
 int32_t b2cuda_create_revolute_joint(B2CWorld* world, const B2CRevoluteJointDef* def, int32_t* jointId);
+/* JointAPI.CreateDistanceJoint :182 / CreateMotorJoint :324 / CreateFilterJoint :408 / CreatePrismaticJoint :412 / CreateRevoluteJoint :555 /
+ * CreateWeldJoint :672 / CreateWheelJoint :720 — api/Joint.cs; World.CreateJoint src/Joint.cs:181-296 */
+int32_t b2cuda_default_joint_def(int32_t type, B2CJointDef* def);
+int32_t b2cuda_create_joint(B2CWorld* world, const B2CJointDef* def, int32_t* jointId);
 /* BodyAPI.SetTransform :293 / SetLinearVelocity :359 / SetAngularVelocity :369 / ApplyForceToCenter :457 /
  * ApplyTorque :469 / ApplyLinearImpulseToCenter :531 — api/Body.cs */
 int32_t b2cuda_body_set_transform(B2CWorld* world, int32_t bodyId, B2CVec2 position, B2CRot rotation);

@@ -55,6 +55,20 @@ int32_t b2o_create_revolute_joint(World* w, const B2CRevoluteJointDef* d, int32_
   *jointId = w->CreateRevoluteJoint(def);
   return 0;
 }
+int32_t b2o_create_joint(World* w, const B2CJointDef* d, int32_t* jointId) {
+  JointDef def; def.type = d->type; def.bodyIdA = d->bodyIdA; def.bodyIdB = d->bodyIdB; def.localFrameA = T(d->localFrameA); def.localFrameB = T(d->localFrameB);
+  def.forceThreshold = d->forceThreshold; def.torqueThreshold = d->torqueThreshold; def.constraintHertz = d->constraintHertz;
+  def.constraintDampingRatio = d->constraintDampingRatio; def.collideConnected = d->collideConnected; def.userData = d->userData;
+  def.enableSpring = d->enableSpring; def.enableLimit = d->enableLimit; def.enableMotor = d->enableMotor;
+  def.hertz = d->hertz; def.dampingRatio = d->dampingRatio; def.target = d->target; def.lower = d->lower; def.upper = d->upper;
+  def.maxMotor = d->maxMotor; def.motorSpeed = d->motorSpeed;
+  def.length = d->length; def.minLength = d->minLength; def.maxLength = d->maxLength; def.lowerSpringForce = d->lowerSpringForce; def.upperSpringForce = d->upperSpringForce;
+  def.angularHertz = d->angularHertz; def.angularDampingRatio = d->angularDampingRatio;
+  def.linearVelocity = V(d->linearVelocity); def.angularVelocity = d->angularVelocity; def.maxVelocityForce = d->maxVelocityForce;
+  def.maxVelocityTorque = d->maxVelocityTorque; def.maxSpringForce = d->maxSpringForce; def.maxSpringTorque = d->maxSpringTorque;
+  *jointId = w->CreateJoint(def);
+  return 0;
+}
 int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
 int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }
 int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAngularVelocity(id, x); return 0; }
@@ -169,7 +183,7 @@ int32_t b2o_world_read_joints(World* w, B2CJointRead* dst, int32_t capacity, int
     if (j.jointId == -1 || j.colorIndex == -1) continue;
     if (n < capacity) {
       const JointSim& s = w->GetJointSim(j);
-      dst[n] = {j.jointId, j.colorIndex, CV(s.linearImpulse), s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse};
+      dst[n] = {j.jointId, j.colorIndex, CV(s.linearImpulse), s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse, s.type, CV(s.linearImpulse2)};
     }
     n++;
   }

@@ -213,10 +213,14 @@ static void RestitutionGroup(std::vector<BodyState>& states, ConstraintLane* lan
   for (int j = 0; j < 8; j++) Scatter(states, lanes[j].indexB, bB[j]);
 }
 
-// ---- revolute joint: src/joints/RevoluteJoint.cs:72-235, src/Joint.cs:125-130 ----
+#include "b2o_joints.inc"
+
+// ---- JointSim.PrepareJoint src/Joint.cs:125-130, then IJoint.Prepare. The body/frame part is the same text in every joint type
+// (RevoluteJoint.cs:72-95, WeldJoint.cs:46-66, MotorJoint.cs:60-81, PrismaticJoint.cs:86-106, WheelJoint.cs:91-111, DistanceJoint.cs:91-113) ----
 static void PrepareJoint(World& world, StepContext& context, JointSim& joint) {
   float hertz = netMin(joint.constraintHertz, 0.25f * context.inv_h);
   joint.constraintSoftness = Softness(hertz, joint.constraintDampingRatio, context.h);
+  if (joint.type == kFilterJoint) return;
   const Body& bodyA = world.bodies[joint.bodyIdA]; const Body& bodyB = world.bodies[joint.bodyIdB];
   const BodySim& bodySimA = world.GetBodySim(bodyA); const BodySim& bodySimB = world.GetBodySim(bodyB);
   float mA = bodySimA.invMass, iA = bodySimA.invInertia, mB = bodySimB.invMass, iB = bodySimB.invInertia;
@@ -228,12 +232,21 @@ static void PrepareJoint(World& world, StepContext& context, JointSim& joint) {
   joint.frameB.q = MulRot(bodySimB.transform.q, joint.localFrameB.q);
   joint.frameB.p = RotateVector(bodySimB.transform.q, joint.localFrameB.p - bodySimB.localCenter);
   joint.deltaCenter = bodySimB.center - bodySimA.center;
+  switch (joint.type) {
+    case kDistanceJoint: PrepareDistance(world, context, joint, bodySimA, bodySimB); return;
+    case kMotorJoint: PrepareMotor(world, context, joint); return;
+    case kPrismaticJoint: PreparePrismatic(world, context, joint); return;
+    case kWeldJoint: PrepareWeld(world, context, joint); return;
+    case kWheelJoint: PrepareWheel(world, context, joint); return;
+    default: break;
+  }
+  // revolute: src/joints/RevoluteJoint.cs:96-104
   float k = iA + iB;
   joint.axialMass = k > 0 ? 1 / k : 0;
   joint.springSoftness = Softness(joint.hertz, joint.dampingRatio, context.h);
   if (!context.enableWarmStarting) { joint.linearImpulse = {0, 0}; joint.springImpulse = 0; joint.motorImpulse = 0; joint.lowerImpulse = 0; joint.upperImpulse = 0; }
 }
-static void WarmStartJoint(World& world, JointSim& j) {
+static void WarmStartRevolute(World& world, JointSim& j) {
   float mA = j.invMassA, mB = j.invMassB, iA = j.invIA, iB = j.invIB;
   BodyState dummy;
   BodyState* stateA = j.indexA != -1 ? &world.awakeSet.bodyStates[j.indexA] : &dummy;
@@ -249,7 +262,7 @@ static void WarmStartJoint(World& world, JointSim& j) {
     stateB->angularVelocity += iB * (Cross(rB, j.linearImpulse) + axialImpulse);
   }
 }
-static void SolveJoint(World& world, StepContext& context, JointSim& j, bool useBias) {
+static void SolveRevolute(World& world, StepContext& context, JointSim& j, bool useBias) {
   float mA = j.invMassA, mB = j.invMassB, iA = j.invIA, iB = j.invIB;
   BodyState dummy;
   BodyState* stateA = j.indexA != -1 ? &world.awakeSet.bodyStates[j.indexA] : &dummy;
@@ -329,6 +342,29 @@ static void SolveJoint(World& world, StepContext& context, JointSim& j, bool use
   }
   if (stateA->flags & kDynamicFlag) { stateA->linearVelocity = vA; stateA->angularVelocity = wA; }
   if (stateB->flags & kDynamicFlag) { stateB->linearVelocity = vB; stateB->angularVelocity = wB; }
+}
+
+static void WarmStartJoint(World& world, JointSim& j) {        // JointSim.WarmStart src/Joint.cs:131
+  switch (j.type) {
+    case kDistanceJoint: WarmStartDistance(world, j); break;
+    case kMotorJoint: WarmStartMotor(world, j); break;
+    case kPrismaticJoint: WarmStartPrismatic(world, j); break;
+    case kRevoluteJoint: WarmStartRevolute(world, j); break;
+    case kWeldJoint: WarmStartWeld(world, j); break;
+    case kWheelJoint: WarmStartWheel(world, j); break;
+    default: break;                                              // filter: IJoint default, empty
+  }
+}
+static void SolveJoint(World& world, StepContext& context, JointSim& j, bool useBias) {   // JointSim.Solve src/Joint.cs:132
+  switch (j.type) {
+    case kDistanceJoint: SolveDistance(world, context, j, useBias); break;
+    case kMotorJoint: SolveMotor(world, context, j, useBias); break;
+    case kPrismaticJoint: SolvePrismatic(world, context, j, useBias); break;
+    case kRevoluteJoint: SolveRevolute(world, context, j, useBias); break;
+    case kWeldJoint: SolveWeld(world, context, j, useBias); break;
+    case kWheelJoint: SolveWheel(world, context, j, useBias); break;
+    default: break;
+  }
 }
 
 // ---- integrate: src/Solver.cs:121-160,199-212 ----

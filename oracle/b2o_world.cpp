@@ -187,7 +187,18 @@ int World::AssignJointColor(int bodyIdA, int bodyIdB, int typeA, int typeB) {   
   return kOverflowIndex;
 }
 
-int World::CreateRevoluteJoint(const RevoluteJointDef& def) {    // src/joints/RevoluteJoint.cs:32-56, src/Joint.cs:181-296
+int World::CreateRevoluteJoint(const RevoluteJointDef& r) {      // api/Joint.cs:555 -> the generic path below
+  JointDef def; def.type = kRevoluteJoint; def.bodyIdA = r.bodyIdA; def.bodyIdB = r.bodyIdB; def.localFrameA = r.localFrameA; def.localFrameB = r.localFrameB;
+  def.forceThreshold = r.forceThreshold; def.torqueThreshold = r.torqueThreshold; def.constraintHertz = r.constraintHertz;
+  def.constraintDampingRatio = r.constraintDampingRatio; def.collideConnected = r.collideConnected; def.userData = r.userData;
+  def.target = r.targetAngle; def.enableSpring = r.enableSpring; def.hertz = r.hertz; def.dampingRatio = r.dampingRatio; def.enableLimit = r.enableLimit;
+  def.lower = r.lowerAngle; def.upper = r.upperAngle; def.enableMotor = r.enableMotor; def.maxMotor = r.maxMotorTorque; def.motorSpeed = r.motorSpeed;
+  return CreateJoint(def);
+}
+
+// World.CreateJoint src/Joint.cs:181-296 followed by the per-type Create: DistanceJoint.cs:35-63, FilterJoint.cs:7-17, MotorJoint.cs:33-52,
+// PrismaticJoint.cs:33-53, RevoluteJoint.cs:32-56, WeldJoint.cs:24-39, WheelJoint.cs:33-56
+int World::CreateJoint(const JointDef& def) {
   Body& bodyA = bodies[def.bodyIdA]; Body& bodyB = bodies[def.bodyIdB];
   int bodyIdA = bodyA.id, bodyIdB = bodyB.id;
   int jointId = jointIdPool.AllocId();
@@ -196,7 +207,7 @@ int World::CreateRevoluteJoint(const RevoluteJointDef& def) {    // src/joints/R
   uint16_t gen = joint.generation;
   joint = Joint();
   joint.generation = (uint16_t)(gen + 1);
-  joint.jointId = jointId; joint.userData = def.userData; joint.type = 4; joint.collideConnected = def.collideConnected;
+  joint.jointId = jointId; joint.userData = def.userData; joint.type = def.type; joint.collideConnected = def.collideConnected;
   joint.edge0.bodyId = bodyIdA; joint.edge0.prevKey = -1; joint.edge0.nextKey = bodyA.headJointKey;
   int keyA = jointId << 1;
   if (bodyA.headJointKey != -1) {
@@ -215,13 +226,43 @@ int World::CreateRevoluteJoint(const RevoluteJointDef& def) {    // src/joints/R
   joint.setIndex = kAwakeSet;
   int colorIndex = AssignJointColor(bodyIdA, bodyIdB, bodyA.type, bodyB.type);   // src/ConstraintGraph.cs:242-251
   JointSim sim; sim.jointId = jointId; sim.bodyIdA = bodyIdA; sim.bodyIdB = bodyIdB;
-  sim.localFrameA = def.localFrameA; sim.localFrameB = def.localFrameB; sim.type = 4;
+  sim.localFrameA = def.localFrameA; sim.localFrameB = def.localFrameB; sim.type = def.type;
   sim.constraintHertz = def.constraintHertz; sim.constraintDampingRatio = def.constraintDampingRatio;
   sim.constraintSoftness.biasRate = 0; sim.constraintSoftness.massScale = 1; sim.constraintSoftness.impulseScale = 0;
   sim.forceThreshold = def.forceThreshold; sim.torqueThreshold = def.torqueThreshold;
-  sim.targetAngle = netClamp(def.targetAngle, -kPi, kPi); sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio;
-  sim.lowerAngle = def.lowerAngle; sim.upperAngle = def.upperAngle; sim.maxMotorTorque = def.maxMotorTorque; sim.motorSpeed = def.motorSpeed;
-  sim.enableSpring = def.enableSpring; sim.enableLimit = def.enableLimit; sim.enableMotor = def.enableMotor;
+  switch (def.type) {
+    case kRevoluteJoint:
+      sim.targetAngle = netClamp(def.target, -kPi, kPi); sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio;
+      sim.lowerAngle = def.lower; sim.upperAngle = def.upper; sim.maxMotorTorque = def.maxMotor; sim.motorSpeed = def.motorSpeed;
+      sim.enableSpring = def.enableSpring; sim.enableLimit = def.enableLimit; sim.enableMotor = def.enableMotor;
+      break;
+    case kDistanceJoint:
+      sim.length = netMax(def.length, kLinearSlop); sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio;
+      sim.minLength = netMax(def.minLength, kLinearSlop); sim.maxLength = netMax(def.minLength, def.maxLength);
+      sim.maxMotorTorque = def.maxMotor; sim.motorSpeed = def.motorSpeed; sim.enableSpring = def.enableSpring;
+      sim.lowerSpringForce = def.lowerSpringForce; sim.upperSpringForce = def.upperSpringForce;
+      sim.enableLimit = def.enableLimit; sim.enableMotor = def.enableMotor;
+      break;
+    case kFilterJoint: break;
+    case kMotorJoint:
+      sim.linearVelocity = def.linearVelocity; sim.maxVelocityForce = def.maxVelocityForce; sim.angularVelocity = def.angularVelocity;
+      sim.maxVelocityTorque = def.maxVelocityTorque; sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio; sim.maxSpringForce = def.maxSpringForce;
+      sim.angularHertz = def.angularHertz; sim.angularDampingRatio = def.angularDampingRatio; sim.maxSpringTorque = def.maxSpringTorque;
+      break;
+    case kPrismaticJoint:
+      sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio; sim.targetAngle = def.target; sim.lowerAngle = def.lower; sim.upperAngle = def.upper;
+      sim.maxMotorTorque = def.maxMotor; sim.motorSpeed = def.motorSpeed;
+      sim.enableSpring = def.enableSpring; sim.enableLimit = def.enableLimit; sim.enableMotor = def.enableMotor;
+      break;
+    case kWeldJoint:
+      sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio; sim.angularHertz = def.angularHertz; sim.angularDampingRatio = def.angularDampingRatio;
+      break;
+    case kWheelJoint:
+      sim.lowerAngle = def.lower; sim.upperAngle = def.upper; sim.maxMotorTorque = def.maxMotor; sim.motorSpeed = def.motorSpeed;
+      sim.hertz = def.hertz; sim.dampingRatio = def.dampingRatio;
+      sim.enableSpring = def.enableSpring; sim.enableLimit = def.enableLimit; sim.enableMotor = def.enableMotor;
+      break;
+  }
   colors[colorIndex].jointSims.push_back(sim);
   joint.colorIndex = colorIndex; joint.localIndex = (int)colors[colorIndex].jointSims.size() - 1;
   if (!def.collideConnected) DestroyContactsBetweenBodies(bodyA, bodyB);

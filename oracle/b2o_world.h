@@ -109,7 +109,20 @@ struct JointSim {               // src/Joint.cs:74-133 + src/joints/RevoluteJoin
   float hertz = 0, dampingRatio = 0, targetAngle = 0, maxMotorTorque = 0, motorSpeed = 0, lowerAngle = 0, upperAngle = 0;
   int indexA = -1, indexB = -1; Transform frameA, frameB; Vec2 deltaCenter{0, 0}; float axialMass = 0; Softness springSoftness;
   bool enableSpring = false, enableMotor = false, enableLimit = false;
+  // Other joint types (src/joints/*.cs) reuse the slots above where the reference's field has the same role:
+  //   distance  impulse -> springImpulse, maxMotorForce -> maxMotorTorque, distanceSoftness -> springSoftness, anchorA/B -> frameA/B.p
+  //   weld      linearHertz/linearDampingRatio -> hertz/dampingRatio, angularImpulse -> springImpulse, linearSpring -> springSoftness
+  //   motor     linearVelocityImpulse -> linearImpulse, angularVelocityImpulse -> motorImpulse, linearSpringImpulse -> linearImpulse2,
+  //             angularSpringImpulse -> springImpulse, angularMass -> axialMass, linearSpring -> springSoftness
+  //   prismatic impulse -> linearImpulse, targetTranslation -> targetAngle, maxMotorForce -> maxMotorTorque, lower/upperTranslation -> lower/upperAngle
+  //   wheel     perpImpulse -> linearImpulse.x, lower/upperTranslation -> lower/upperAngle
+  float length = 0, minLength = 0, maxLength = 0, lowerSpringForce = 0, upperSpringForce = 0;                       // distance
+  float angularHertz = 0, angularDampingRatio = 0;                                                                   // weld, motor
+  float maxSpringForce = 0, maxSpringTorque = 0, maxVelocityForce = 0, maxVelocityTorque = 0, angularVelocity = 0;   // motor
+  Vec2 linearVelocity{0, 0}, linearImpulse2{0, 0};
+  Softness angularSoftness; Mat22 linearMass{{0, 0}, {0, 0}}; float perpMass = 0, motorMass = 0;
 };
+enum { kDistanceJoint = 0, kFilterJoint = 1, kMotorJoint = 2, kPrismaticJoint = 3, kRevoluteJoint = 4, kWeldJoint = 5, kWheelJoint = 6 };  // include/Types.cs:423-426
 
 // AVX lane of ContactConstraintSIMD (src/ContactSolver.cs:378-406)
 struct ConstraintLane {
@@ -159,6 +172,16 @@ struct ShapeDef {               // include/Types.cs:307-344
   bool enableCustomFiltering = false, isSensor = false, enableSensorEvents = false, enableContactEvents = false,
     enableHitEvents = false, enablePreSolveEvents = false, invokeContactCreation = true, updateBodyMass = true;
 };
+struct JointDef {               // include/Types.cs:431-456 (base) + the per-type defs :460-640, flattened
+  int type = kRevoluteJoint;
+  int bodyIdA = -1, bodyIdB = -1; Transform localFrameA, localFrameB; float forceThreshold = FLT_MAX, torqueThreshold = FLT_MAX,
+    constraintHertz = 60, constraintDampingRatio = 2; bool collideConnected = false; uint64_t userData = 0;
+  bool enableSpring = false, enableLimit = false, enableMotor = false;
+  float hertz = 0, dampingRatio = 0, target = 0, lower = 0, upper = 0, maxMotor = 0, motorSpeed = 0;
+  float length = 1, minLength = 0, maxLength = kHuge, lowerSpringForce = -FLT_MAX, upperSpringForce = FLT_MAX;
+  float angularHertz = 0, angularDampingRatio = 0;
+  Vec2 linearVelocity{0, 0}; float angularVelocity = 0, maxVelocityForce = 0, maxVelocityTorque = 0, maxSpringForce = 0, maxSpringTorque = 0;
+};
 struct RevoluteJointDef {       // include/Types.cs:431-456,569-597
   int bodyIdA = -1, bodyIdB = -1; Transform localFrameA, localFrameB; float forceThreshold = FLT_MAX, torqueThreshold = FLT_MAX,
     constraintHertz = 60, constraintDampingRatio = 2; bool collideConnected = false; uint64_t userData = 0;
@@ -184,6 +207,7 @@ class World {
   int CreateBody(const BodyDef& def);
   int CreateShape(int bodyId, const ShapeDef& def, const Geom& geom);
   int CreateRevoluteJoint(const RevoluteJointDef& def);
+  int CreateJoint(const JointDef& def);
   void SetTransform(int bodyId, Vec2 position, Rot rotation);
   void SetLinearVelocity(int bodyId, Vec2 v);
   void SetAngularVelocity(int bodyId, float w);

@@ -15,6 +15,9 @@ CASES = {
     "mixed_drop": (lambda w: scenes.mixed_drop(w), 30, {}),
     "joint_grid8": (lambda w: scenes.joint_grid(w, 8), 20, {}),
     "tumbler300": (lambda w: scenes.tumbler(w, n=300, half=4.0), 20, {}),
+    "joint_zoo": (lambda w: scenes.joint_zoo(w, copies=2), 40, {}),                       # every joint type (weld/prismatic use Atan2)
+    "joint_zoo_exact": (lambda w: scenes.joint_zoo(w, copies=2, angles=False), 40, {}),   # the Atan2-free subset
+    "wheel_rig": (lambda w: scenes.wheel_rig(w, copies=2), 30, {}),
 }
 
 
@@ -32,6 +35,12 @@ def record(world, build, steps):
         out[f"s{s}_begin"] = np.stack([ev[0]["shapeIdA"], ev[0]["shapeIdB"], ev[0]["contactId"]], axis=1) if len(ev[0]) else np.zeros((0, 3), np.int32)
         out[f"s{s}_end"] = np.stack([ev[1]["shapeIdA"], ev[1]["shapeIdB"], ev[1]["contactId"]], axis=1) if len(ev[1]) else np.zeros((0, 3), np.int32)
         if s == 0 or s == steps - 1:
+            j = world.ReadJoints()
+            if len(j):
+                out[f"s{s}_joint_ids"] = np.stack([j["jointId"], j["colorIndex"], j["type"]], axis=1)
+                out[f"s{s}_joint_impulses"] = np.stack([j["linearImpulse"]["x"], j["linearImpulse"]["y"], j["springImpulse"], j["motorImpulse"], j["lowerImpulse"],
+                                                        j["upperImpulse"], j["linearImpulse2"]["x"], j["linearImpulse2"]["y"]], axis=1).astype(np.float32)
+                out[f"s{s}_joint_events"] = np.asarray(world.GetJointEvents(), dtype=np.int32)
             b = world.ReadBodies()
             out[f"s{s}_bodies"] = np.stack([b["transform"]["p"]["x"], b["transform"]["p"]["y"], b["transform"]["q"]["c"], b["transform"]["q"]["s"],
                                             b["linearVelocity"]["x"], b["linearVelocity"]["y"], b["angularVelocity"]], axis=1).astype(np.float32)

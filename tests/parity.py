@@ -47,7 +47,7 @@ def compare_struct(name, a, b, exact_fields=None, skip=(), report=None):
 def snapshot(w):
     ev = w.GetContactEvents()
     return dict(bodies=w.ReadBodies(), contacts=w.ReadContacts(), shapes=w.ReadShapes(), joints=w.ReadJoints(),
-                begin=ev[0], end=ev[1], hit=ev[2], counters=w.GetCounters())
+                begin=ev[0], end=ev[1], hit=ev[2], counters=w.GetCounters(), joint_events=np.asarray(w.GetJointEvents(), dtype=np.int32))
 
 
 def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0, verbose=False, mutate=None):
@@ -71,6 +71,7 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
             # exact: pair set / ids / colors / manifold ids / events
             for key in ("begin", "end"):
                 compare_struct(f"step{step}.{key}", a[key], b[key], report=rep)
+            assert a["joint_events"].tolist() == b["joint_events"].tolist(), f"step{step} joint events {a['joint_events']} vs {b['joint_events']}"
             ca, cb = a["counters"], b["counters"]
             max_overflow = max(max_overflow, ca.colorCounts[23])
             for f in ("contactCount", "touchingContactCount", "contactIdCapacity", "activeColorCount", "moveCount", "newPairCount"):

@@ -27,7 +27,7 @@ def test_exports_every_declared_symbol(lib):
 
 def test_pod_sizes_match_header(tmp_path):
     names = ["B2CWorldDef", "B2CBodyDef", "B2CShapeDef", "B2CGeometry", "B2CRevoluteJointDef", "B2CBodyRead", "B2CManifoldPointRead",
-             "B2CContactRead", "B2CContactTouchEvent", "B2CContactHitEvent", "B2CJointRead", "B2CShapeRead", "B2CCounters", "B2CProfile"]
+             "B2CContactRead", "B2CContactTouchEvent", "B2CContactHitEvent", "B2CJointRead", "B2CJointDef", "B2CShapeRead", "B2CCounters", "B2CProfile"]
     src = '#include <stdio.h>\n#include "b2cuda.h"\nint main(){' + "".join(f'printf("{n} %zu\\n", sizeof({n}));' for n in names) + "return 0;}"
     c = tmp_path / "s.c"
     c.write_text(src)
@@ -35,7 +35,7 @@ def test_pod_sizes_match_header(tmp_path):
     subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(c), "-o", str(exe)])
     sizes = dict(line.split() for line in subprocess.check_output([str(exe)]).decode().splitlines())
     mirror = {"B2CWorldDef": capi.WorldDef, "B2CBodyDef": capi.BodyDef, "B2CShapeDef": capi.ShapeDef, "B2CGeometry": capi.Geometry,
-              "B2CRevoluteJointDef": capi.RevoluteJointDef, "B2CBodyRead": capi.BodyRead, "B2CManifoldPointRead": capi.ManifoldPointRead,
+              "B2CRevoluteJointDef": capi.RevoluteJointDef, "B2CJointDef": capi.JointDef, "B2CBodyRead": capi.BodyRead, "B2CManifoldPointRead": capi.ManifoldPointRead,
               "B2CContactRead": capi.ContactRead, "B2CContactTouchEvent": capi.ContactTouchEvent, "B2CContactHitEvent": capi.ContactHitEvent,
               "B2CJointRead": capi.JointRead, "B2CShapeRead": capi.ShapeRead, "B2CCounters": capi.Counters, "B2CProfile": capi.Profile}
     for n, ty in mirror.items():
@@ -54,6 +54,11 @@ def test_defaults_match_reference_defs(lib):
     assert abs(sd.friction - 0.6) < 1e-7 and sd.density == 1.0 and sd.categoryBits == 2**64 - 1 and sd.invokeContactCreation == 1
     assert bd.gravityScale == 1.0 and bd.isAwake == 1 and bd.isEnabled == 1 and (bd.rotation.c, bd.rotation.s) == (1.0, 0.0)
     assert jd.constraintHertz == 60.0 and jd.constraintDampingRatio == 2.0 and jd.bodyIdA == -1
+    for t in range(7):          # the generic joint definition: C defaults == the Python mirror's, field by field
+        gd, ref = capi.JointDef(), api.default_joint_def(t)
+        assert be.fns["default_joint_def"](t, C.byref(gd)) == 0
+        assert bytes(gd) == bytes(ref), t
+    assert be.fns["default_joint_def"](7, C.byref(capi.JointDef())) == -1
 
 
 def test_no_gpu_means_loud_failure_not_fallback(lib):
