@@ -257,6 +257,26 @@ class World:
     def CreateWheelJoint(self, joint_def):
         return self._typed(joint_def, capi.JOINT_WHEEL)
 
+    # Joint setters (api/Joint.cs). The C# shim maps each named setter onto one of these three calls, e.g.
+    # RevoluteJoint_SetMotorSpeed(j, v) -> JointSetParam(j, JP_MOTOR_SPEED, v); WheelJoint_EnableMotor(j, f) -> JointEnable(j, JOINT_MOTOR_SWITCH, f);
+    # PrismaticJoint_SetLimits / DistanceJoint_SetLengthRange -> JointSetLimits(j, lower, upper).
+    def JointSetParam(self, joint_id, param, value):
+        self._check(self.fns["joint_set_param"](self.handle, joint_id, param, value))
+
+    def JointEnable(self, joint_id, feature, flag):
+        self._check(self.fns["joint_enable"](self.handle, joint_id, feature, int(bool(flag))))
+
+    def JointSetLimits(self, joint_id, lower, upper):
+        self._check(self.fns["joint_set_limits"](self.handle, joint_id, lower, upper))
+
+    def SetConstraintTuning(self, joint_id, hertz, damping_ratio):
+        self.JointSetParam(joint_id, capi.JP_CONSTRAINT_HERTZ, hertz)
+        self.JointSetParam(joint_id, capi.JP_CONSTRAINT_DAMPING_RATIO, damping_ratio)
+
+    def MotorJoint_SetLinearVelocity(self, joint_id, v):
+        self.JointSetParam(joint_id, capi.JP_LINEAR_VELOCITY_X, v[0])
+        self.JointSetParam(joint_id, capi.JP_LINEAR_VELOCITY_Y, v[1])
+
     # --- WorldAPI ---
     def SetGravity(self, g):
         self._check(self.fns["world_set_gravity"](self.handle, Vec2(*g)))

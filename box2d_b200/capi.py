@@ -61,6 +61,12 @@ class RevoluteJointDef(C.Structure):
                 ("enableMotor", C.c_int32), ("maxMotorTorque", C.c_float), ("motorSpeed", C.c_float)]
 
 
+# B2C_JP_* / B2C_JOINT_{SPRING,LIMIT,MOTOR} of include/b2cuda.h
+(JP_CONSTRAINT_HERTZ, JP_CONSTRAINT_DAMPING_RATIO, JP_FORCE_THRESHOLD, JP_TORQUE_THRESHOLD, JP_SPRING_HERTZ, JP_SPRING_DAMPING_RATIO, JP_TARGET,
+ JP_MOTOR_SPEED, JP_MAX_MOTOR, JP_LENGTH, JP_LOWER_SPRING_FORCE, JP_UPPER_SPRING_FORCE, JP_ANGULAR_HERTZ, JP_ANGULAR_DAMPING_RATIO,
+ JP_LINEAR_VELOCITY_X, JP_LINEAR_VELOCITY_Y, JP_ANGULAR_VELOCITY, JP_MAX_VELOCITY_FORCE, JP_MAX_VELOCITY_TORQUE, JP_MAX_SPRING_FORCE,
+ JP_MAX_SPRING_TORQUE) = range(21)
+JOINT_SPRING, JOINT_LIMIT, JOINT_MOTOR_SWITCH = range(3)
 JOINT_DISTANCE, JOINT_FILTER, JOINT_MOTOR, JOINT_PRISMATIC, JOINT_REVOLUTE, JOINT_WELD, JOINT_WHEEL = range(7)
 
 
@@ -139,6 +145,9 @@ PROTOS = {
     "create_shape": [_W, C.c_int32, C.POINTER(ShapeDef), C.POINTER(Geometry), C.POINTER(C.c_int32)],
     "create_revolute_joint": [_W, C.POINTER(RevoluteJointDef), C.POINTER(C.c_int32)],
     "create_joint": [_W, C.POINTER(JointDef), C.POINTER(C.c_int32)],
+    "joint_set_param": [_W, C.c_int32, C.c_int32, C.c_float],
+    "joint_enable": [_W, C.c_int32, C.c_int32, C.c_int32],
+    "joint_set_limits": [_W, C.c_int32, C.c_float, C.c_float],
     "body_set_transform": [_W, C.c_int32, Vec2, Rot],
     "body_set_linear_velocity": [_W, C.c_int32, Vec2],
     "body_set_angular_velocity": [_W, C.c_int32, C.c_float],

@@ -3,6 +3,7 @@
 // (UpdateBodyMassData), src/joints/RevoluteJoint.cs:32-56 + src/Joint.cs:181-296 (CreateJoint),
 // src/ConstraintGraph.cs:91-128 (AssignJointColor). None of this is on the step path.
 #include "b2c_host.cuh"
+#include "b2c_jointops.cuh"
 #include "b2c_treeops.cuh"
 #include <cstring>
 #include <cstdio>
@@ -327,6 +328,21 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   colorJoints_[color].push_back(id);
   // DestroyContactsBetweenBodies (src/Joint.cs:155-180): no contacts exist before the first step.
   *jointId = id;
+  return B2C_OK;
+}
+
+// Joint setters (api/Joint.cs): the host mirror is patched before the upload, the device record after it (stream-ordered, one thread).
+__global__ void k_joint_patch(WorldDev d, int jointId, int patch, int which, float a, float b) { jointPatch(d.joints[jointId], patch, which, a, b); }
+int World::jointOp(int jointId, int patch, int which, float a, float b) {
+  if (jointId < 0 || jointId >= (int)joints_.size() || joints_[jointId].id != jointId) return fail(B2C_E_INVALID, "bad joint id");
+  JointDev& s = joints_[jointId].sim;
+  if (patch == JPATCH_PARAM && !jointParamValid(s.type, which)) return fail(B2C_E_INVALID, "joint parameter does not exist for this joint type");
+  if (patch == JPATCH_ENABLE && !jointHasSpringLimitMotor(s.type, which)) return fail(B2C_E_INVALID, "joint type has no spring/limit/motor switch");
+  if (patch == JPATCH_LIMITS && !jointHasSpringLimitMotor(s.type, B2C_JOINT_LIMIT)) return fail(B2C_E_INVALID, "joint type has no limits");
+  if (!onDevice_) { jointPatch(s, patch, which, a, b); return B2C_OK; }
+  CK(cudaSetDevice(device_));
+  k_joint_patch<<<1, 1, 0, stream_>>>(d_, jointId, patch, which, a, b);
+  CK(cudaGetLastError());
   return B2C_OK;
 }
 

@@ -59,6 +59,7 @@ class World {
   int createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId);
   int createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId);
   int createJoint(const B2CJointDef& def, int* jointId);
+  int jointOp(int jointId, int patch, int which, float a, float b);
   int setTransform(int bodyId, V2 p, Rot q);
   int setLinearVelocity(int bodyId, V2 v);
   int setAngularVelocity(int bodyId, float w);

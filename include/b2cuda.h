@@ -168,6 +168,45 @@ int32_t b2cuda_create_revolute_joint(B2CWorld* world, const B2CRevoluteJointDef*
  * CreateWeldJoint :672 / CreateWheelJoint :720 — api/Joint.cs; World.CreateJoint src/Joint.cs:181-296 */
 int32_t b2cuda_default_joint_def(int32_t type, B2CJointDef* def);
 int32_t b2cuda_create_joint(B2CWorld* world, const B2CJointDef* def, int32_t* jointId);
+/* Joint mutators — api/Joint.cs. One generic entry per shape of setter; `param` selects the field (B2C_JP_*). Wrong joint type for a
+ * field returns B2C_E_INVALID (the reference asserts the type, api/Joint.cs:169-179). After the first step each call is a one-thread
+ * patch of the device joint record, ordered on the world's stream (no read-back, no synchronisation).
+ *   set_param   plain stores: JointAPI.SetConstraintTuning :130, SetForceThreshold :148, SetTorqueThreshold :159, <Type>Joint_SetSpringHertz /
+ *               SetSpringDampingRatio / SetMotorSpeed / SetMaxMotorForce|Torque / SetTargetAngle|Translation, DistanceJoint_SetLength :187
+ *               (clamped to [linearSlop, huge], clears lower/upper impulse), DistanceJoint_SetSpringForceRange :204, MotorJoint_Set* :327-360
+ *               (Max(0, x) where the reference clamps), WeldJoint_Set* :675-700
+ *   enable      <Type>Joint_EnableSpring / EnableLimit / EnableMotor: on a change the matching accumulated impulses are cleared
+ *               (WheelJoint_EnableLimit :755 stores false whenever the flag changes - kept as written)
+ *   set_limits  RevoluteJoint_SetLimits :626, PrismaticJoint_SetLimits :471, WheelJoint_SetLimits :769 (min/max, impulses cleared when
+ *               changed), DistanceJoint_SetLengthRange :236 (clamped, all three impulses cleared) */
+#define B2C_JP_CONSTRAINT_HERTZ 0
+#define B2C_JP_CONSTRAINT_DAMPING_RATIO 1
+#define B2C_JP_FORCE_THRESHOLD 2
+#define B2C_JP_TORQUE_THRESHOLD 3
+#define B2C_JP_SPRING_HERTZ 4            /* weld/motor: linear hertz */
+#define B2C_JP_SPRING_DAMPING_RATIO 5    /* weld/motor: linear damping ratio */
+#define B2C_JP_TARGET 6                  /* revolute target angle / prismatic target translation */
+#define B2C_JP_MOTOR_SPEED 7
+#define B2C_JP_MAX_MOTOR 8               /* max motor torque (revolute, wheel) / force (distance, prismatic) */
+#define B2C_JP_LENGTH 9
+#define B2C_JP_LOWER_SPRING_FORCE 10
+#define B2C_JP_UPPER_SPRING_FORCE 11
+#define B2C_JP_ANGULAR_HERTZ 12
+#define B2C_JP_ANGULAR_DAMPING_RATIO 13
+#define B2C_JP_LINEAR_VELOCITY_X 14
+#define B2C_JP_LINEAR_VELOCITY_Y 15
+#define B2C_JP_ANGULAR_VELOCITY 16
+#define B2C_JP_MAX_VELOCITY_FORCE 17
+#define B2C_JP_MAX_VELOCITY_TORQUE 18
+#define B2C_JP_MAX_SPRING_FORCE 19
+#define B2C_JP_MAX_SPRING_TORQUE 20
+#define B2C_JP_COUNT 21
+#define B2C_JOINT_SPRING 0
+#define B2C_JOINT_LIMIT 1
+#define B2C_JOINT_MOTOR 2
+int32_t b2cuda_joint_set_param(B2CWorld* world, int32_t jointId, int32_t param, float value);
+int32_t b2cuda_joint_enable(B2CWorld* world, int32_t jointId, int32_t feature, int32_t flag);
+int32_t b2cuda_joint_set_limits(B2CWorld* world, int32_t jointId, float lower, float upper);
 /* BodyAPI.SetTransform :293 / SetLinearVelocity :359 / SetAngularVelocity :369 / ApplyForceToCenter :457 /
  * ApplyTorque :469 / ApplyLinearImpulseToCenter :531 — api/Body.cs */
 int32_t b2cuda_body_set_transform(B2CWorld* world, int32_t bodyId, B2CVec2 position, B2CRot rotation);

@@ -269,6 +269,68 @@ int World::CreateJoint(const JointDef& def) {
   return jointId;
 }
 
+// ---- joint setters, api/Joint.cs. `param` numbering = B2C_JP_* of include/b2cuda.h (the test harness drives both sides with it). ----
+bool World::JointSetParam(int jointId, int param, float v) {
+  JointSim& j = GetJointSim(joints[jointId]);
+  const int t = j.type;
+  const bool slm = t == kRevoluteJoint || t == kPrismaticJoint || t == kWheelJoint || t == kDistanceJoint;
+  switch (param) {
+    case 0: j.constraintHertz = v; return true;                 // JointAPI.SetConstraintTuning :130-138
+    case 1: j.constraintDampingRatio = v; return true;
+    case 2: j.forceThreshold = v; return true;                  // SetForceThreshold :148
+    case 3: j.torqueThreshold = v; return true;                 // SetTorqueThreshold :159
+    case 4: if (!(slm || t == kWeldJoint || t == kMotorJoint)) return false; j.hertz = v; return true;          // *_SetSpringHertz / *_SetLinearHertz
+    case 5: if (!(slm || t == kWeldJoint || t == kMotorJoint)) return false; j.dampingRatio = v; return true;
+    case 6: if (t != kRevoluteJoint && t != kPrismaticJoint) return false; j.targetAngle = v; return true;      // :444, :585
+    case 7: if (!slm) return false; j.motorSpeed = v; return true;
+    case 8: if (!slm) return false; j.maxMotorTorque = v; return true;
+    case 9: if (t != kDistanceJoint) return false; j.length = netClamp(v, kLinearSlop, kHuge); j.lowerImpulse = 0; j.upperImpulse = 0; return true;   // :187-194
+    case 10: if (t != kDistanceJoint) return false; j.lowerSpringForce = v; return true;                         // :204-210
+    case 11: if (t != kDistanceJoint) return false; j.upperSpringForce = v; return true;
+    case 12: if (t != kWeldJoint && t != kMotorJoint) return false; j.angularHertz = v; return true;
+    case 13: if (t != kWeldJoint && t != kMotorJoint) return false; j.angularDampingRatio = v; return true;
+    case 14: if (t != kMotorJoint) return false; j.linearVelocity.x = v; return true;                            // MotorJoint_SetLinearVelocity :327
+    case 15: if (t != kMotorJoint) return false; j.linearVelocity.y = v; return true;
+    case 16: if (t != kMotorJoint) return false; j.angularVelocity = v; return true;
+    case 17: if (t != kMotorJoint) return false; j.maxVelocityForce = netMax(0, v); return true;                 // :333
+    case 18: if (t != kMotorJoint) return false; j.maxVelocityTorque = v; return true;                           // :336
+    case 19: if (t != kMotorJoint) return false; j.maxSpringForce = netMax(0, v); return true;
+    case 20: if (t != kMotorJoint) return false; j.maxSpringTorque = netMax(0, v); return true;
+  }
+  return false;
+}
+bool World::JointEnable(int jointId, int feature, bool flag) {
+  JointSim& j = GetJointSim(joints[jointId]);
+  const int t = j.type;
+  if (t != kRevoluteJoint && t != kPrismaticJoint && t != kWheelJoint && t != kDistanceJoint) return false;
+  if (feature == 0) {           // *_EnableSpring: DistanceJoint :197 stores; Prismatic :432, Revolute :573, Wheel :735 clear springImpulse on a change
+    if (t == kDistanceJoint) j.enableSpring = flag;
+    else if (flag != j.enableSpring) { j.enableSpring = flag; j.springImpulse = 0; }
+  } else if (feature == 1) {    // *_EnableLimit: DistanceJoint :229 stores; Prismatic :452, Revolute :613; Wheel :755 writes false when changed
+    if (t == kDistanceJoint) j.enableLimit = flag;
+    else if (flag != j.enableLimit) { j.lowerImpulse = 0; j.upperImpulse = 0; j.enableLimit = t == kWheelJoint ? false : flag; }
+  } else if (feature == 2) {    // *_EnableMotor :277, :484, :639, :782
+    if (flag != j.enableMotor) { j.enableMotor = flag; j.motorImpulse = 0; }
+  } else return false;
+  return true;
+}
+bool World::JointSetLimits(int jointId, float lower, float upper) {
+  JointSim& j = GetJointSim(joints[jointId]);
+  const int t = j.type;
+  if (t == kDistanceJoint) {    // DistanceJoint_SetLengthRange :236-247
+    float minLength = netClamp(lower, kLinearSlop, kHuge), maxLength = netClamp(upper, kLinearSlop, kHuge);
+    j.minLength = netMin(minLength, maxLength); j.maxLength = netMax(minLength, maxLength);
+    j.springImpulse = 0; j.lowerImpulse = 0; j.upperImpulse = 0;
+    return true;
+  }
+  if (t != kRevoluteJoint && t != kPrismaticJoint && t != kWheelJoint) return false;
+  if (lower != j.lowerAngle || upper != j.upperAngle) {          // :471-481, :626-637, :769-780
+    j.lowerAngle = netMin(lower, upper); j.upperAngle = netMax(lower, upper);
+    j.lowerImpulse = 0; j.upperImpulse = 0;
+  }
+  return true;
+}
+
 void World::DestroyContactsBetweenBodies(Body& bodyA, Body& bodyB) {    // src/Joint.cs:155-180
   int contactKey, otherBodyId;
   if (bodyA.contactCount < bodyB.contactCount) { contactKey = bodyA.headContactKey; otherBodyId = bodyB.id; }

@@ -208,6 +208,9 @@ class World {
   int CreateShape(int bodyId, const ShapeDef& def, const Geom& geom);
   int CreateRevoluteJoint(const RevoluteJointDef& def);
   int CreateJoint(const JointDef& def);
+  bool JointSetParam(int jointId, int param, float value);      // api/Joint.cs setters, see b2o_world.cpp
+  bool JointEnable(int jointId, int feature, bool flag);
+  bool JointSetLimits(int jointId, float lower, float upper);
   void SetTransform(int bodyId, Vec2 position, Rot rotation);
   void SetLinearVelocity(int bodyId, Vec2 v);
   void SetAngularVelocity(int bodyId, float w);

@@ -283,3 +283,66 @@ def test_joint_warm_starting_off_and_substep_variants():
     assert res["max_rel_err"] == 0.0
     res = parity.run_pair(lambda w: scenes.wheel_rig(w), steps=20, substeps=8, dt=1.0 / 120.0, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+def test_joint_setters_between_steps_bit_exact():
+    """api/Joint.cs setters applied between steps on both sides (device: one-thread patches on the world's stream): parameters,
+    spring/limit/motor switches with their impulse resets, limits, thresholds, constraint tuning."""
+    from box2d_b200 import capi as J
+    holder = {}
+
+    def build(w):
+        holder["zoo"] = scenes.joint_zoo(w, copies=2, angles=False)
+        holder["rig"] = scenes.wheel_rig(w, copies=1, pitch=-30.0)
+
+    def mutate(w, step):
+        zoo, rig = holder["zoo"], holder["rig"][0]
+        if step == 3:
+            for ids in zoo:
+                w.JointSetParam(ids["distance_spring"], J.JP_MOTOR_SPEED, -0.75)
+                w.JointSetParam(ids["distance_spring"], J.JP_SPRING_HERTZ, 3.5)
+                w.JointSetParam(ids["distance_rigid"], J.JP_LENGTH, 2.5)
+                w.MotorJoint_SetLinearVelocity(ids["motor_velocity"], (-0.25, 0.5))
+                w.JointSetParam(ids["motor_velocity"], J.JP_ANGULAR_VELOCITY, -2.0)
+                w.JointSetParam(ids["motor_spring"], J.JP_MAX_SPRING_FORCE, -1.0)      # Max(0, x)
+                w.JointSetParam(ids["revolute"], J.JP_FORCE_THRESHOLD, 1.0e9)
+            w.JointSetParam(rig[0], J.JP_MOTOR_SPEED, -4.0)
+            w.JointSetLimits(rig[0], 0.3, -0.1)                                        # swapped on purpose: min/max
+        if step == 6:
+            for ids in zoo:
+                w.JointEnable(ids["distance_spring"], J.JOINT_MOTOR_SWITCH, False)
+                w.JointEnable(ids["distance_spring"], J.JOINT_LIMIT, False)
+                w.JointSetLimits(ids["distance_spring"], 0.5, 3.0)
+                w.JointEnable(ids["revolute"], J.JOINT_MOTOR_SWITCH, True)
+                w.JointSetParam(ids["revolute"], J.JP_MAX_MOTOR, 30.0)
+                w.JointSetParam(ids["revolute"], J.JP_MOTOR_SPEED, 1.5)
+                w.SetConstraintTuning(ids["revolute"], 30.0, 1.0)
+            w.JointEnable(rig[1], J.JOINT_LIMIT, True)      # was off -> the port stores false and clears the impulses
+            w.JointEnable(rig[2], J.JOINT_SPRING, False)
+        if step == 12:
+            for ids in zoo:
+                w.JointEnable(ids["distance_spring"], J.JOINT_MOTOR_SWITCH, True)
+                w.JointSetLimits(ids["revolute"], -0.2, 0.3)          # limit stays off: the revolute limit evaluates Atan2 (tolerance-only)
+            w.JointEnable(rig[0], J.JOINT_MOTOR_SWITCH, False)
+
+    res = parity.run_pair(build, steps=40, verbose=True, mutate=mutate)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_joint_setter_rejects_fields_of_other_types():
+    from box2d_b200 import capi as J
+    w = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        ids = scenes.joint_zoo(w, copies=1, angles=False)[0]
+        for jid, param in ((ids["filter"], J.JP_MOTOR_SPEED), (ids["revolute"], J.JP_LENGTH), (ids["distance_rigid"], J.JP_TARGET),
+                           (ids["motor_velocity"], J.JP_MAX_MOTOR)):
+            with pytest.raises(api.B2Error):
+                w.JointSetParam(jid, param, 1.0)
+        with pytest.raises(api.B2Error):
+            w.JointEnable(ids["filter"], J.JOINT_SPRING, True)
+        with pytest.raises(api.B2Error):
+            w.JointSetLimits(ids["motor_velocity"], 0.0, 1.0)
+        with pytest.raises(api.B2Error):
+            w.JointSetParam(999, J.JP_MOTOR_SPEED, 1.0)
+    finally:
+        w.Destroy()
