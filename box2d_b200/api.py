@@ -156,6 +156,19 @@ class World:
     def SetTransform(self, body_id, position, rotation=(1.0, 0.0)):
         self._check(self.fns["body_set_transform"](self.handle, body_id, Vec2(*position), Rot(*rotation)))
 
+    def SetTargetTransform(self, body_id, position, rotation, time_step):
+        t = Transform(Vec2(*position), Rot(*rotation))
+        self._check(self.fns["body_set_target_transform"](self.handle, body_id, t, time_step))
+
+    def SetMassData(self, body_id, mass, rotational_inertia, center=(0.0, 0.0)):
+        self._check(self.fns["body_set_mass_data"](self.handle, body_id, mass, rotational_inertia, Vec2(*center)))
+
+    def SetMotionLocks(self, body_id, linear_x, linear_y, angular_z):
+        self._check(self.fns["body_set_motion_locks"](self.handle, body_id, int(linear_x), int(linear_y), int(angular_z)))
+
+    def SetSurfaceMaterial(self, shape_id, friction, restitution=0.0, rolling_resistance=0.0, tangent_speed=0.0):
+        self._check(self.fns["shape_set_surface_material"](self.handle, shape_id, friction, restitution, rolling_resistance, tangent_speed))
+
     def SetLinearVelocity(self, body_id, v):
         self._check(self.fns["body_set_linear_velocity"](self.handle, body_id, Vec2(*v)))
 

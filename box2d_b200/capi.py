@@ -150,6 +150,10 @@ PROTOS = {
     "joint_set_limits": [_W, C.c_int32, C.c_float, C.c_float],
     "body_set_transform": [_W, C.c_int32, Vec2, Rot],
     "body_set_linear_velocity": [_W, C.c_int32, Vec2],
+    "body_set_target_transform": [_W, C.c_int32, Transform, C.c_float],
+    "body_set_mass_data": [_W, C.c_int32, C.c_float, C.c_float, Vec2],
+    "body_set_motion_locks": [_W, C.c_int32, C.c_int32, C.c_int32, C.c_int32],
+    "shape_set_surface_material": [_W, C.c_int32, C.c_float, C.c_float, C.c_float, C.c_float],
     "body_set_angular_velocity": [_W, C.c_int32, C.c_float],
     "body_apply_force_to_center": [_W, C.c_int32, Vec2, C.c_int32],
     "body_apply_torque": [_W, C.c_int32, C.c_float, C.c_int32],

@@ -89,6 +89,10 @@ int32_t b2cuda_body_apply_angular_impulse(B2CWorld* h, int32_t id, float i, int3
 int32_t b2cuda_body_set_linear_damping(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->setLinearDamping(id, v)); }
 int32_t b2cuda_body_set_angular_damping(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->setAngularDamping(id, v)); }
 int32_t b2cuda_body_set_gravity_scale(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->setGravityScale(id, v)); }
+int32_t b2cuda_body_set_target_transform(B2CWorld* h, int32_t id, B2CTransform t, float dt) { CHECK_HANDLE(h); return done(h, h->w->setTargetTransform(id, mkXf(mk(t.p.x, t.p.y), mkRot(t.q.c, t.q.s)), dt)); }
+int32_t b2cuda_body_set_mass_data(B2CWorld* h, int32_t id, float mass, float inertia, B2CVec2 c) { CHECK_HANDLE(h); return done(h, h->w->setMassData(id, mass, inertia, mk(c.x, c.y))); }
+int32_t b2cuda_body_set_motion_locks(B2CWorld* h, int32_t id, int32_t lx, int32_t ly, int32_t az) { CHECK_HANDLE(h); return done(h, h->w->setMotionLocks(id, lx != 0, ly != 0, az != 0)); }
+int32_t b2cuda_shape_set_surface_material(B2CWorld* h, int32_t id, float f, float r, float rr, float ts) { CHECK_HANDLE(h); return done(h, h->w->setSurfaceMaterial(id, f, r, rr, ts)); }
 int32_t b2cuda_body_get(B2CWorld* h, int32_t id, B2CBodyRead* out) { CHECK_HANDLE(h); if (!out) return B2C_E_INVALID; return done(h, h->w->readBody(id, out)); }
 int32_t b2cuda_world_set_restitution_threshold(B2CWorld* h, float v) { CHECK_HANDLE(h); h->w->restitutionThreshold = netClamp(v, 0.0f, FLT_MAX); return B2C_OK; }
 int32_t b2cuda_world_set_hit_event_threshold(B2CWorld* h, float v) { CHECK_HANDLE(h); h->w->hitEventThreshold = netClamp(v, 0.0f, FLT_MAX); return B2C_OK; }

@@ -455,6 +455,7 @@ int World::upload() {
     bodySim[i] = b.simIndex; bodyType[i] = b.type; bodyHeadShape[i] = b.headShapeId; bodyHeadJoint[i] = b.headJointKey; bodyJointCount[i] = b.jointCount;
     bodySleep[i] = b.sleepThreshold; bodyFlags[i] = b.flags;
   }
+  for (int id : lockQuirk_) bodyFlags[id] |= kLockLinearX | kLockLinearY | kLockAngularZ;
   colorMask_.resize(nBody, 0);
   DA(d.bodyXf, float4, nBody); DA(d.bodyMass, float4, nBody); DA(d.bodyCenter, float2, nBody); DA(d.bodySim, int, nBody); DA(d.bodyType, int, nBody);
   DA(d.bodyHeadShape, int, nBody); DA(d.bodyHeadJoint, int, nBody); DA(d.bodyJointCount, int, nBody); DA(d.bodyColorMask, uint32_t, nBody);
@@ -672,6 +673,112 @@ int World::applyAngularImpulse(int bodyId, float i) { return bodyOp(bodyId, OP_A
 int World::setLinearDamping(int bodyId, float v) { return bodyOp(bodyId, OP_LINEAR_DAMPING, mk(v, 0), mk(0, 0)); }
 int World::setAngularDamping(int bodyId, float v) { return bodyOp(bodyId, OP_ANGULAR_DAMPING, mk(v, 0), mk(0, 0)); }
 int World::setGravityScale(int bodyId, float v) { return bodyOp(bodyId, OP_GRAVITY_SCALE, mk(v, 0), mk(0, 0)); }
+
+// BodyAPI.SetTargetTransform api/Body.cs:378-400, SetMassData :585-598, SetMotionLocks :796-818; ShapeAPI.SetSurfaceMaterial api/Shape.cs:110-146.
+__global__ void k_body_target_transform(WorldDev d, int bodyId, Xf target, float timeStep) {
+  int sim = d.bodySim[bodyId];
+  if (sim < 0) return;
+  float4 pose = d.simPose[sim], loc = d.simLocal[sim], s0 = d.st0[sim];
+  V2 center1 = mk(pose.x, pose.y), center2 = xfPoint(target, mk(loc.x, loc.y));
+  float invTimeStep = 1.0f / timeStep;
+  V2 linearVelocity = invTimeStep * (center2 - center1);
+  Rot q1 = mkRot(pose.z, pose.w), q2 = target.q;
+  float deltaAngle = atan2f(q1.c * q2.s - q1.s * q2.c, q1.c * q2.c + q1.s * q2.s);     // Rotation.RelativeAngle include/MathFunctions.cs:162
+  s0.x = linearVelocity.x; s0.y = linearVelocity.y; s0.z = invTimeStep * deltaAngle;
+  d.st0[sim] = s0;
+}
+__global__ void k_body_mass_data(WorldDev d, int bodyId, float mass, float inertia, V2 localCenter) {
+  float4 xf4 = d.bodyXf[bodyId];
+  V2 center = xfPoint(mkXf(mk(xf4.x, xf4.y), mkRot(xf4.z, xf4.w)), localCenter);
+  float invMass = mass > 0.0f ? 1.0f / mass : 0.0f, invInertia = inertia > 0.0f ? 1.0f / inertia : 0.0f;
+  d.bodyMass[bodyId] = make_float4(invMass, invInertia, localCenter.x, localCenter.y);
+  d.bodyCenter[bodyId] = make_float2(center.x, center.y);
+  int sim = d.bodySim[bodyId];
+  if (sim < 0) return;
+  float4 m = d.simMass[sim]; m.x = invMass; m.y = invInertia; d.simMass[sim] = m;
+  float4 loc = d.simLocal[sim]; loc.x = localCenter.x; loc.y = localCenter.y; d.simLocal[sim] = loc;
+  float4 pose = d.simPose[sim]; pose.x = center.x; pose.y = center.y; d.simPose[sim] = pose;
+  float4 pose0 = d.simPose0[sim]; pose0.x = center.x; pose0.y = center.y; d.simPose0[sim] = pose0;
+}
+__global__ void k_body_motion_locks(WorldDev d, int bodyId, uint32_t newFlags) {
+  const uint32_t allLocks = kLockLinearX | kLockLinearY | kLockAngularZ;
+  uint32_t bf = d.bodyFlags[bodyId];
+  if ((bf & allLocks) == newFlags) return;
+  d.bodyFlags[bodyId] = bf | allLocks;                     // `body.flags |= allLocks` as written (api/Body.cs:807)
+  int sim = d.bodySim[bodyId];
+  if (sim < 0) return;
+  uint32_t sf = (d.simFlags[sim] & ~allLocks) | newFlags;
+  d.simFlags[sim] = sf;
+  float4 s0 = d.st0[sim];
+  s0.w = __uint_as_float(sf);
+  if (newFlags & kLockLinearX) s0.x = 0.0f;
+  if (newFlags & kLockLinearY) s0.y = 0.0f;
+  if (newFlags & kLockAngularZ) s0.z = 0.0f;
+  d.st0[sim] = s0;
+}
+__global__ void k_shape_material(WorldDev d, int shapeId, float4 material) { d.shapes[shapeId].material = material; }
+
+int World::setTargetTransform(int bodyId, Xf target, float timeStep) {
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  if (b.type == kStaticBody || timeStep <= 0.0f) return B2C_OK;
+  if (!onDevice_) {
+    V2 center2 = xfPoint(target, b.localCenter);
+    float invTimeStep = 1.0f / timeStep;
+    b.v = invTimeStep * (center2 - b.center);
+    Rot q1 = b.xf.q, q2 = target.q;
+    b.w = invTimeStep * atan2f(q1.c * q2.s - q1.s * q2.c, q1.c * q2.c + q1.s * q2.s);
+    return B2C_OK;
+  }
+  CK(cudaSetDevice(device_));
+  k_body_target_transform<<<1, 1, 0, stream_>>>(d_, bodyId, target, timeStep);
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
+int World::setMassData(int bodyId, float mass, float inertia, V2 center) {
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  b.mass = mass; b.inertia = inertia;
+  if (!onDevice_) {
+    b.localCenter = center; b.center = xfPoint(b.xf, center); b.center0 = b.center;
+    b.invMass = mass > 0.0f ? 1.0f / mass : 0.0f; b.invInertia = inertia > 0.0f ? 1.0f / inertia : 0.0f;
+    return B2C_OK;
+  }
+  CK(cudaSetDevice(device_));
+  k_body_mass_data<<<1, 1, 0, stream_>>>(d_, bodyId, mass, inertia, center);
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
+int World::setMotionLocks(int bodyId, bool lx, bool ly, bool az) {
+  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  const uint32_t allLocks = kLockLinearX | kLockLinearY | kLockAngularZ;
+  uint32_t newFlags = (lx ? kLockLinearX : 0u) | (ly ? kLockLinearY : 0u) | (az ? kLockAngularZ : 0u);
+  if (!onDevice_) {
+    // before the upload HBody::flags stands for both Body.flags and BodySim.flags: the sim's locks are what the solver reads
+    if ((b.flags & allLocks) == newFlags) return B2C_OK;
+    b.flags = (b.flags & ~allLocks) | newFlags;
+    if (lx) b.v.x = 0.0f;
+    if (ly) b.v.y = 0.0f;
+    if (az) b.w = 0.0f;
+    lockQuirk_.push_back(bodyId);
+    return B2C_OK;
+  }
+  CK(cudaSetDevice(device_));
+  k_body_motion_locks<<<1, 1, 0, stream_>>>(d_, bodyId, newFlags);
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
+int World::setSurfaceMaterial(int shapeId, float friction, float restitution, float rolling, float tangentSpeed) {
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  HShape& sh = shapes_[shapeId];
+  sh.friction = friction; sh.restitution = restitution; sh.rollingResistance = rolling; sh.tangentSpeed = tangentSpeed;
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_shape_material<<<1, 1, 0, stream_>>>(d_, shapeId, make_float4(friction, restitution, rolling, tangentSpeed));
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
 
 // ---- read-back ----
 template <class T> static int fetch(std::vector<T>& out, const T* dev, size_t n, cudaStream_t s) {

@@ -62,6 +62,10 @@ class World {
   int jointOp(int jointId, int patch, int which, float a, float b);
   int setTransform(int bodyId, V2 p, Rot q);
   int setLinearVelocity(int bodyId, V2 v);
+  int setTargetTransform(int bodyId, Xf target, float timeStep);
+  int setMassData(int bodyId, float mass, float inertia, V2 center);
+  int setMotionLocks(int bodyId, bool lx, bool ly, bool az);
+  int setSurfaceMaterial(int shapeId, float friction, float restitution, float rolling, float tangentSpeed);
   int setAngularVelocity(int bodyId, float w);
   int applyForceToCenter(int bodyId, V2 f);
   int applyTorque(int bodyId, float t);
@@ -120,6 +124,7 @@ class World {
   std::vector<int> moveArray_; std::vector<std::vector<uint8_t>> moved_;
   std::vector<uint32_t> colorMask_;    // per bodyId
   std::vector<std::vector<int>> colorJoints_;
+  std::vector<int> lockQuirk_;   // bodies whose Body.flags got all three lock bits from SetMotionLocks before the upload (api/Body.cs:807)
   // device state
   WorldDev d_{};
   std::vector<void*> allocs_;

@@ -224,6 +224,13 @@ int32_t b2cuda_body_apply_angular_impulse(B2CWorld* world, int32_t bodyId, float
 int32_t b2cuda_body_set_linear_damping(B2CWorld* world, int32_t bodyId, float linearDamping);
 int32_t b2cuda_body_set_angular_damping(B2CWorld* world, int32_t bodyId, float angularDamping);
 int32_t b2cuda_body_set_gravity_scale(B2CWorld* world, int32_t bodyId, float gravityScale);
+/* BodyAPI.SetTargetTransform :378 (velocities that reach `target` in `timeStep`; the angle uses Atan2) / SetMassData :585 /
+ * SetMotionLocks :796 — api/Body.cs; ShapeAPI.SetFriction :110 / SetRestitution :122 / SetSurfaceMaterial :144 — api/Shape.cs (the mixed
+ * contact friction/restitution is recomputed by every UpdateContact, src/Contact.cs:330-340, so the change shows on the next step). */
+int32_t b2cuda_body_set_target_transform(B2CWorld* world, int32_t bodyId, B2CTransform target, float timeStep);
+int32_t b2cuda_body_set_mass_data(B2CWorld* world, int32_t bodyId, float mass, float rotationalInertia, B2CVec2 center);
+int32_t b2cuda_body_set_motion_locks(B2CWorld* world, int32_t bodyId, int32_t linearX, int32_t linearY, int32_t angularZ);
+int32_t b2cuda_shape_set_surface_material(B2CWorld* world, int32_t shapeId, float friction, float restitution, float rollingResistance, float tangentSpeed);
 /* BodyAPI.GetTransform :288 / GetLinearVelocity :345 / GetAngularVelocity :352 / GetWorldCenterOfMass :580 for one body
  * (synchronises with the world's stream; use b2cuda_world_read_bodies or the move events for bulk reads). */
 int32_t b2cuda_body_get(B2CWorld* world, int32_t bodyId, B2CBodyRead* out);

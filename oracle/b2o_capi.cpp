@@ -72,6 +72,10 @@ int32_t b2o_create_joint(World* w, const B2CJointDef* d, int32_t* jointId) {
 int32_t b2o_joint_set_param(World* w, int32_t id, int32_t param, float v) { return w->JointSetParam(id, param, v) ? 0 : -1; }
 int32_t b2o_joint_enable(World* w, int32_t id, int32_t feature, int32_t flag) { return w->JointEnable(id, feature, flag != 0) ? 0 : -1; }
 int32_t b2o_joint_set_limits(World* w, int32_t id, float lo, float hi) { return w->JointSetLimits(id, lo, hi) ? 0 : -1; }
+int32_t b2o_body_set_target_transform(World* w, int32_t id, B2CTransform t, float dt) { w->SetTargetTransform(id, T(t), dt); return 0; }
+int32_t b2o_body_set_mass_data(World* w, int32_t id, float mass, float inertia, B2CVec2 c) { w->SetMassData(id, mass, inertia, V(c)); return 0; }
+int32_t b2o_body_set_motion_locks(World* w, int32_t id, int32_t lx, int32_t ly, int32_t az) { w->SetMotionLocks(id, lx != 0, ly != 0, az != 0); return 0; }
+int32_t b2o_shape_set_surface_material(World* w, int32_t id, float f, float r, float rr, float ts) { w->SetSurfaceMaterial(id, f, r, rr, ts); return 0; }
 int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
 int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }
 int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAngularVelocity(id, x); return 0; }

@@ -365,6 +365,49 @@ void World::SetTransform(int bodyId, Vec2 position, Rot rotation) {      // api/
     shapeId = shape.nextShapeId;
   }
 }
+void World::SetTargetTransform(int bodyId, const Transform& target, float timeStep) {    // api/Body.cs:378-400 (awake set only: sleep is not restated)
+  Body& body = bodies[bodyId];
+  if (body.type == kStaticBody || timeStep <= 0) return;
+  BodySim& sim = GetBodySim(body);
+  Vec2 center1 = sim.center, center2 = TransformPoint(target, sim.localCenter);
+  float invTimeStep = 1 / timeStep;
+  Vec2 linearVelocity = invTimeStep * (center2 - center1);
+  Rot q1 = sim.transform.q, q2 = target.q;
+  float deltaAngle = atan2f(q1.c * q2.s - q1.s * q2.c, q1.c * q2.c + q1.s * q2.s);    // Rotation.RelativeAngle include/MathFunctions.cs:162
+  float angularVelocity = invTimeStep * deltaAngle;
+  if (BodyState* state = GetBodyState(body)) { state->linearVelocity = linearVelocity; state->angularVelocity = angularVelocity; }
+}
+void World::SetMassData(int bodyId, float mass, float rotationalInertia, Vec2 localCenter) {   // api/Body.cs:585-598
+  Body& body = bodies[bodyId];
+  BodySim& bodySim = GetBodySim(body);
+  body.mass = mass; body.inertia = rotationalInertia;
+  bodySim.localCenter = localCenter;
+  Vec2 center = TransformPoint(bodySim.transform, localCenter);
+  bodySim.center = center; bodySim.center0 = center;
+  bodySim.invMass = body.mass > 0 ? 1 / body.mass : 0;
+  bodySim.invInertia = body.inertia > 0 ? 1 / body.inertia : 0;
+}
+void World::SetMotionLocks(int bodyId, bool linearX, bool linearY, bool angularZ) {            // api/Body.cs:796-818
+  uint32_t newFlags = (linearX ? kLockLinearX : 0u) | (linearY ? kLockLinearY : 0u) | (angularZ ? kLockAngularZ : 0u);
+  Body& body = bodies[bodyId];
+  const uint32_t allLocks = kLockLinearX | kLockLinearY | kLockAngularZ;
+  if ((body.flags & allLocks) != newFlags) {
+    body.flags &= ~allLocks;
+    body.flags |= allLocks;                                 // as written (:807): Body.flags ends with every lock bit set
+    BodySim& bodySim = GetBodySim(body);
+    bodySim.flags &= ~allLocks;
+    bodySim.flags |= newFlags;
+    if (BodyState* state = GetBodyState(body)) {
+      state->flags = bodySim.flags;
+      state->linearVelocity = {linearX ? 0 : state->linearVelocity.x, linearY ? 0 : state->linearVelocity.y};
+      state->angularVelocity = angularZ ? 0 : state->angularVelocity;
+    }
+  }
+}
+void World::SetSurfaceMaterial(int shapeId, float friction, float restitution, float rollingResistance, float tangentSpeed) {   // api/Shape.cs:110-146
+  SurfaceMaterial& m = shapes[shapeId].material;
+  m.friction = friction; m.restitution = restitution; m.rollingResistance = rollingResistance; m.tangentSpeed = tangentSpeed;
+}
 void World::SetLinearVelocity(int bodyId, Vec2 v) {       // api/Body.cs:359-367
   Body& body = bodies[bodyId]; if (body.type == kStaticBody) return;
   if (BodyState* s = GetBodyState(body)) s->linearVelocity = v;

@@ -208,6 +208,10 @@ class World {
   int CreateShape(int bodyId, const ShapeDef& def, const Geom& geom);
   int CreateRevoluteJoint(const RevoluteJointDef& def);
   int CreateJoint(const JointDef& def);
+  void SetTargetTransform(int bodyId, const Transform& target, float timeStep);
+  void SetMassData(int bodyId, float mass, float rotationalInertia, Vec2 center);
+  void SetMotionLocks(int bodyId, bool linearX, bool linearY, bool angularZ);
+  void SetSurfaceMaterial(int shapeId, float friction, float restitution, float rollingResistance, float tangentSpeed);
   bool JointSetParam(int jointId, int param, float value);      // api/Joint.cs setters, see b2o_world.cpp
   bool JointEnable(int jointId, int feature, bool flag);
   bool JointSetLimits(int jointId, float lower, float upper);

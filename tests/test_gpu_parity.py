@@ -346,3 +346,45 @@ def test_joint_setter_rejects_fields_of_other_types():
             w.JointSetParam(999, J.JP_MOTOR_SPEED, 1.0)
     finally:
         w.Destroy()
+
+
+def test_mass_locks_material_mutators_between_steps_bit_exact():
+    """BodyAPI.SetMassData / SetMotionLocks and ShapeAPI.SetSurfaceMaterial before the first step and between steps."""
+    def build(w):
+        scenes.add_pyramid(w, 8)
+        w.SetMotionLocks(5, False, False, True)           # before the upload: host mirror
+        w.SetMassData(6, 3.0, 0.75, (0.1, -0.05))
+        w.SetSurfaceMaterial(7, 0.1, 0.0, 0.0, 0.5)
+
+    def mutate(w, step):
+        if step == 2:
+            w.SetMotionLocks(9, True, False, False)
+            w.SetMotionLocks(10, False, True, True)
+            w.SetMassData(11, 0.5, 0.02, (0.0, 0.2))
+            w.SetSurfaceMaterial(0, 0.05, 0.0, 0.0, 0.0)   # the ground becomes slippery
+            w.SetSurfaceMaterial(12, 0.9, 0.0, 0.1, -0.3)  # rolling resistance + tangent speed
+        if step == 6:
+            w.SetMotionLocks(9, False, False, False)
+            w.SetMotionLocks(5, False, False, True)        # same locks again: no change
+            w.SetMassData(13, 0.0, 0.0, (0.0, 0.0))        # massless: infinite-mass body in the solver
+            w.ApplyLinearImpulseToCenter(14, (3.0, 1.0))
+    res = parity.run_pair(build, steps=30, verbose=True, mutate=mutate)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_set_target_transform_within_tolerance():
+    """BodyAPI.SetTargetTransform: the angular part goes through Atan2 (CRT-dependent), the linear part is exact."""
+    def build(w):
+        scenes.add_pyramid(w, 4)
+        kd = api.default_body_def()
+        kd.type = api.KINEMATIC_BODY
+        kd.position = api.Vec2(-6.0, 2.0)
+        k = w.CreateBody(kd)
+        w.CreatePolygonShape(k, scenes._shape_def(), __import__("box2d_b200").geometry.MakeBox(0.5, 0.25))
+
+    def mutate(w, step):
+        k = w.GetCounters().bodyCount - 1
+        if step % 3 == 0:
+            w.SetTargetTransform(k, (-6.0 + 0.25 * step, 2.0), (0.9800666, 0.19866933), 1.0 / 60.0)
+    res = parity.run_pair(build, steps=20, tol=1e-5, verbose=True, mutate=mutate)
+    assert res["max_rel_err"] <= 1e-5
