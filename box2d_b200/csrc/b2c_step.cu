@@ -1059,7 +1059,12 @@ __device__ void phase_prepare(const WorldDev& d, const StepParams& sp, bool cont
 // reference's per-stage spin barrier; empty colors cost nothing.
 // CACHED: the grid-path constraints fit one per thread, so each thread builds its lane in registers (PrepareContacts fused in,
 // as in the island kernel) and keeps it there for the whole step: a stage then loads only the two body rows after the barrier.
-template <bool CACHED> __device__ void phase_solver_grid(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {
+// The stage barrier: the whole cooperative grid (cg grid.sync, ~1.2 us over 148 CTAs) or one thread-block cluster (barrier.cluster,
+// ~0.2 us over <= 16 CTAs of one GPC). With a one-cluster grid gtid()/gsize() are the cluster's thread rank and size.
+struct GridScope { cg::grid_group& g; __device__ __forceinline__ void sync() const { g.sync(); } };
+struct ClusterScope { __device__ __forceinline__ void sync() const { cg::this_cluster().sync(); } };
+
+template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scope& grid, const WorldDev& d, const StepParams& sp) {
   const Scalars& s = *d.sc;
   __shared__ int sBegin[kGraphColorCount], sEnd[kGraphColorCount], sJBegin[kGraphColorCount], sJEnd[kGraphColorCount], sActiveCount;
   if (threadIdx.x == 0) {
@@ -1476,15 +1481,32 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   phase_islands(grid, d);
   if (dirty) grid.sync();
   const bool gridWork = s.smallConStart > 0 || d.jointColorStart[kGraphColorCount] > 0 || s.bigBodyCount > 0;
-  const bool cachedLanes = s.smallConStart <= gsize();   // one grid-path constraint per thread: lanes stay in registers
+  // Scenes whose grid-path work is one cluster's worth are solved by k_solver_cluster (launched next when sp.clusterThreads > 0):
+  // every colour stage is one barrier + one L2 round trip, so the cheaper barrier wins although 16 SMs do the work of 148.
+  const int gridJoints = d.jointColorStart[kGraphColorCount];
+  // Measured (B200): the cluster wins where stages are many and thin (joints, an active overflow colour) or the lanes fit its registers;
+  // a contact-only scene between 8 192 and 75 776 constraints keeps its lanes in the grid's registers, which beats the cheaper barrier.
+  const bool clusterFits = s.smallConStart + gridJoints <= 12 * sp.clusterThreads && s.bigBodyCount <= 8 * sp.clusterThreads;
+  const bool clusterWins = gridJoints > 0 || s.ovCount > 0 || s.smallConStart <= sp.clusterThreads || s.smallConStart > gsize();
+  const bool clusterPath = gridWork && sp.clusterThreads > 0 && clusterFits && clusterWins;
+  if (gtid() == 0) s.clusterSolve = clusterPath ? 1 : 0;
+  const bool cachedLanes = s.smallConStart <= (clusterPath ? sp.clusterThreads : gsize());   // one grid-path constraint per thread: lanes stay in registers
   if (gridWork) { phase_prepare(d, sp, !cachedLanes); if (!cachedLanes) grid.sync(); }
   stamp(d, 3);
   dbgLanes(d, 3, true); dbgBodies(d, 4); dbgColorConflicts(grid, d, 10);
   if (d.debugChecksums == 1) grid.sync();
-  if (gridWork) { if (cachedLanes) phase_solver_grid<true>(grid, d, sp); else phase_solver_grid<false>(grid, d, sp); }
+  if (gridWork && !clusterPath) { GridScope gs{grid}; if (cachedLanes) phase_solver_grid<true>(gs, d, sp); else phase_solver_grid<false>(gs, d, sp); }
   stamp(d, 4);
   if (d.debugChecksums == 1) { grid.sync(); dbgBodies(d, 5); dbgLanes(d, 6, false); dbgContacts(d, 7); }
   if (gtid() == 0) { for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k]; s.phaseAcc[4] += s.phaseStamp[5] - s.phaseStamp[1]; }
+}
+
+// The grid-path solver on one thread-block cluster (see clusterPath in k_step_front). All CTAs of the cluster take the same path.
+__global__ void __launch_bounds__(kCoopThreads) k_solver_cluster(WorldDev d, StepParams sp) {
+  const Scalars& s = *d.sc;
+  if (!s.clusterSolve) return;
+  ClusterScope cs;
+  if (s.smallConStart <= gsize()) phase_solver_grid<true>(cs, d, sp); else phase_solver_grid<false>(cs, d, sp);
 }
 
 __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, StepParams sp, int newEndIndex) {   // FinalizeBodies + refit
@@ -1561,12 +1583,36 @@ int World::step(float timeStep, int subStepCount) {
     CK(cudaFuncSetAttribute(k_solver_islands_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kWarpIslandsPerCta * sizeof(WarpIslandSlice))));
     if (const char* e = getenv("B2CUDA_ISLAND_MODE")) islandMode_ = !strcmp(e, "cta") ? 1 : !strcmp(e, "warp") ? 2 : 0;   // tests force a variant
     if (coopBlocks_ < 3) return fail(B2C_E_CUDA, "device too small");
+    // thread-block cluster for the grid-path solver: 16 CTAs (non-portable size) when the device can co-schedule them, else 8
+    clusterCtas_ = 0;
+    const char* ce = getenv("B2CUDA_CLUSTER");
+    if (!ce || strcmp(ce, "0")) {
+      for (int size : {16, 8}) {
+        if (size > 8 && cudaFuncSetAttribute(k_solver_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); continue; }
+        cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(size); cfg.blockDim = dim3(kCoopThreads); cfg.stream = stream_;
+        cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = size; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+        cfg.attrs = &at; cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, k_solver_cluster, &cfg) == cudaSuccess && n >= 1) { clusterCtas_ = size; break; }
+        cudaGetLastError();
+      }
+    }
   }
   const dim3 cgrid(coopBlocks_), cblock(kCoopThreads);
   cudaEvent_t* pe = ev_ + (profHead_ % kProfRing) * kProfEvents;
   cudaEventRecord(pe[0], stream_);
+  // the cluster kernel is launched only when the last step that reached the host had grid-path work (large or jointed islands);
+  // the front kernel takes the cluster path only when told the kernel follows, so a stale view costs speed, never correctness
+  const bool clusterLaunch = clusterCtas_ > 0 && !d.debugChecksums && (hostScalars_->smallConStart > 0 || hostScalars_->bigBodyCount > 0 || d.jointColorStart[kGraphColorCount] > 0);
+  sp.clusterThreads = clusterLaunch ? clusterCtas_ * kCoopThreads : 0;
   { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
   cudaEventRecord(pe[1], stream_);
+  if (clusterLaunch) {
+    cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(clusterCtas_); cfg.blockDim = dim3(kCoopThreads); cfg.stream = stream_;
+    cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = clusterCtas_; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+    cfg.attrs = &at; cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, k_solver_cluster, d, sp));
+  }
   // few islands: one CTA each (shortest stage chain); thousands (batched worlds): one warp each (b2c_islands_warp.cuh).
   // The count comes from the last step whose scalars reached the host; either variant is correct for any count.
   int warpMode = islandMode_ == 2 || (islandMode_ == 0 && hostScalars_->islandCount >= 8 * coopBlocks_);

@@ -98,6 +98,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int awakeCount, anyRestitution, anyContactFlag, anyHitShapes;
   unsigned long long phaseStamp[8], phaseAcc[8];   // %globaltimer stamps inside k_step_front and their per-phase sums (ns)
   int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
+  int clusterSolve;    // this step's grid-path constraints are solved by k_solver_cluster (one thread-block cluster) instead of the front kernel
   int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
   int bigQueryCount, bigHitTotal, bigGroupTotal, staticRanksValid;   // wide broadphase queries (b2c_bigquery.cuh)
   int rebuildLevels[3], ovCount;        // ovCount: contacts in the overflow colour
@@ -112,6 +113,7 @@ struct StepParams {    // src/Solver.cs:57-112 StepContext (scalars only)
   V2 gravity;
   int enableWarmStarting, enableContactSoftening, enableContinuous, enableSpeculative, enableSleep;
   int endIndex;        // which contactEndEvents buffer this step appends to
+  int clusterThreads;  // > 0: k_solver_cluster follows the front kernel with this many threads (one cluster); 0: grid path only
 };
 
 struct WorldDev {

@@ -388,3 +388,14 @@ def test_set_target_transform_within_tolerance():
             w.SetTargetTransform(k, (-6.0 + 0.25 * step, 2.0), (0.9800666, 0.19866933), 1.0 / 60.0)
     res = parity.run_pair(build, steps=20, tol=1e-5, verbose=True, mutate=mutate)
     assert res["max_rel_err"] <= 1e-5
+
+
+@pytest.mark.parametrize("scene,steps", [("pyramid", 20), ("joints", 30), ("tumbler", 30), ("zoo", 40)])
+def test_grid_barrier_solver_variant_bit_exact(scene, steps, monkeypatch):
+    """Large / jointed islands are solved by one thread-block cluster by default (k_solver_cluster); B2CUDA_CLUSTER=0 keeps them in
+    the cooperative front kernel with grid-wide barriers. Both must give the reference's floats."""
+    monkeypatch.setenv("B2CUDA_CLUSTER", "0")
+    build = {"pyramid": lambda w: scenes.large_pyramid(w, 40), "joints": lambda w: scenes.joint_grid(w, 12),
+             "tumbler": lambda w: scenes.tumbler(w, n=600, half=6.0), "zoo": lambda w: scenes.joint_zoo(w, copies=2, angles=False)}[scene]
+    res = parity.run_pair(build, steps=steps, verbose=True)
+    assert res["max_rel_err"] == 0.0
