@@ -342,6 +342,10 @@ class World:
         self._check(self.fns["world_debug_checksums"](self.handle, out))
         return list(out)
 
+    def EnableGraphLaunch(self, flag=True):
+        """(no reference counterpart) one CUDA-graph launch per step; see include/b2cuda.h"""
+        self._check(self.fns["world_enable_graph_launch"](self.handle, int(bool(flag))))
+
     def TimerStart(self):
         self._check(self.fns["world_timer_start"](self.handle))
 

@@ -199,6 +199,7 @@ PRODUCT_ONLY = {
     "default_joint_def": ([C.c_int32, C.POINTER(JointDef)], C.c_int32),
     "world_create": ([C.POINTER(WorldDef), C.c_int32, C.POINTER(_W)], C.c_int32),
     "world_get_profile": ([_W, C.POINTER(Profile)], C.c_int32),
+    "world_enable_graph_launch": ([_W, C.c_int32], C.c_int32),
     "world_timer_start": ([_W], C.c_int32),
     "world_timer_stop": ([_W, C.POINTER(C.c_float)], C.c_int32),
     "world_debug_checksums": ([_W, C.POINTER(C.c_uint64)], C.c_int32),

@@ -122,6 +122,7 @@ int32_t b2cuda_world_get_counters(B2CWorld* h, B2CCounters* out) { CHECK_HANDLE(
 int32_t b2cuda_world_debug_checksums(B2CWorld* h, uint64_t* out16) { CHECK_HANDLE(h); return done(h, h->w->debugChecksums((unsigned long long*)out16)); }
 int32_t b2cuda_world_get_profile(B2CWorld* h, B2CProfile* out) { CHECK_HANDLE(h); return done(h, h->w->getProfile(out)); }
 
+int32_t b2cuda_world_enable_graph_launch(B2CWorld* h, int32_t flag) { CHECK_HANDLE(h); h->w->enableGraphLaunch(flag != 0); return B2C_OK; }
 int32_t b2cuda_world_timer_start(B2CWorld* h) { CHECK_HANDLE(h); return done(h, h->w->timerStart()); }
 int32_t b2cuda_world_timer_stop(B2CWorld* h, float* ms) { CHECK_HANDLE(h); if (!ms) return B2C_E_INVALID; return done(h, h->w->timerStop(ms)); }
 

@@ -113,6 +113,8 @@ void World::freeDevice() {
   hBodyRead_ = nullptr;
   hostScalars_ = nullptr; hBegin_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
   for (auto& e : ev_) if (e) { cudaEventDestroy(e); e = nullptr; }
+  for (auto& g : graphs_) { if (g.exec) cudaGraphExecDestroy(g.exec); for (auto& e : g.ev) if (e) cudaEventDestroy(e); }
+  graphs_.clear();
   for (auto& e : timer_) if (e) { cudaEventDestroy(e); e = nullptr; }
   if (stream_) { cudaStreamDestroy(stream_); stream_ = nullptr; }
 }
@@ -963,9 +965,14 @@ int World::getProfile(B2CProfile* out) {       // averages over the steps since 
   memset(out, 0, sizeof(*out));
   if (!onDevice_ || profCount_ == 0) return B2C_OK;
   int rc = synchronize(); if (rc) return rc;
+  for (auto& g : graphs_) harvestGraph(g);
   int n = profCount_ < kProfRing ? profCount_ : kProfRing;
   double acc[4] = {0, 0, 0, 0};
-  for (int k = 0; k < n; k++) {
+  if (graphMode_ == 1) {                 // steps were graph launches: event times were harvested per launch
+    n = profN_ > 0 ? profN_ : 1;
+    for (int j = 0; j < 4; j++) { acc[j] = profAcc_[j]; profAcc_[j] = 0; }
+    profN_ = 0;
+  } else for (int k = 0; k < n; k++) {
     int slot = (profHead_ - 1 - k + 2 * kProfRing) % kProfRing;
     cudaEvent_t* e = ev_ + slot * kProfEvents;
     float ms;

@@ -60,6 +60,7 @@ class World {
   int createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId);
   int createJoint(const B2CJointDef& def, int* jointId);
   int jointOp(int jointId, int patch, int which, float a, float b);
+  void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }
   int setTransform(int bodyId, V2 p, Rot q);
   int setLinearVelocity(int bodyId, V2 v);
   int setTargetTransform(int bodyId, Xf target, float timeStep);
@@ -139,6 +140,14 @@ class World {
   cudaEvent_t ev_[kProfRing * kProfEvents] = {};
   cudaEvent_t timer_[2] = {};
   int profHead_ = 0, profCount_ = 0;
+  // One CUDA graph per distinct step configuration (parameters, end-event buffer parity, solver variant, streamed read-backs): a step is
+  // then ONE launch, so the kernels run back to back whatever the host's launch latency is (matters with 8 ranks on one host).
+  struct StepGraph { std::vector<unsigned char> key; cudaGraphExec_t exec = nullptr; cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr}; bool pending = false; };
+  std::vector<StepGraph> graphs_;
+  int graphMode_ = -1;          // -1 undecided (B2CUDA_GRAPH decides at the first step), 0 direct launches (default, or capture failed), 1 graphs
+  double profAcc_[4] = {0, 0, 0, 0}; int profN_ = 0;   // event times harvested from graph launches (ms)
+  int enqueueStep(const StepParams& sp, bool warpMode, bool clusterLaunch, int newEndIndex, cudaEvent_t* pe, bool external);
+  void harvestGraph(StepGraph& g);
   unsigned long long lastPhaseAcc_[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   B2CProfile profile_{};
   bool profileValid_ = false;

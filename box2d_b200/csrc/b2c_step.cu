@@ -1547,6 +1547,40 @@ static int gridFor(int n, int threads, int maxBlocks) {
   return b > maxBlocks ? maxBlocks : b;
 }
 
+// The launches of one step on the world's stream; captured into a CUDA graph (external = event-record nodes) or issued directly.
+int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch, int newEndIndex, cudaEvent_t* pe, bool external) {
+  WorldDev& d = d_;
+  StepParams sp = spIn;
+  const dim3 cgrid(coopBlocks_), cblock(kCoopThreads);
+  auto rec = [&](cudaEvent_t e) { return external ? cudaEventRecordWithFlags(e, stream_, cudaEventRecordExternal) : cudaEventRecord(e, stream_); };
+  CK(rec(pe[0]));
+  { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
+  CK(rec(pe[1]));
+  if (clusterLaunch) {
+    cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(clusterCtas_); cfg.blockDim = dim3(kCoopThreads); cfg.stream = stream_;
+    cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = clusterCtas_; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+    cfg.attrs = &at; cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, k_solver_cluster, d, sp));
+  }
+  if (warpMode) k_solver_islands_warp<<<coopBlocks_, 32 * kWarpIslandsPerCta, kWarpIslandsPerCta * sizeof(WarpIslandSlice), stream_>>>(d, sp);
+  k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp, (int)warpMode);
+  CK(rec(pe[2]));
+  { void* args[] = {(void*)&d, (void*)&sp, (void*)&newEndIndex}; CK(cudaLaunchCooperativeKernel((void*)k_finalize_phase, cgrid, cblock, args, 0, stream_)); }
+  CK(rec(pe[3]));
+  CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
+  if (streamMoves_) CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)d.awakeCount, cudaMemcpyDeviceToHost, stream_));
+  if (streamBodies_) CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)d.bodyCapacity, cudaMemcpyDeviceToHost, stream_));   // the caller reads body records every step: the copy rides behind the step
+  return B2C_OK;
+}
+void World::harvestGraph(StepGraph& g) {          // event times of the graph's previous launch, if it has finished
+  if (!g.pending || cudaEventQuery(g.ev[3]) != cudaSuccess) { cudaGetLastError(); return; }
+  float ms;
+  for (int j = 0; j < 3; j++) if (cudaEventElapsedTime(&ms, g.ev[j], g.ev[j + 1]) == cudaSuccess) profAcc_[j] += ms;
+  if (cudaEventElapsedTime(&ms, g.ev[0], g.ev[3]) == cudaSuccess) profAcc_[3] += ms;
+  profN_++; g.pending = false;
+  cudaGetLastError();
+}
+
 int World::step(float timeStep, int subStepCount) {
   if (enableSleep) return fail(B2C_E_UNSUPPORTED, "enableSleep=true (islands/sleep, src/Island.cs) is not supported in this build; create the world with enableSleep=0");
   if (!onDevice_) { int rc = upload(); if (rc) return rc; }
@@ -1598,41 +1632,67 @@ int World::step(float timeStep, int subStepCount) {
       }
     }
   }
-  const dim3 cgrid(coopBlocks_), cblock(kCoopThreads);
-  cudaEvent_t* pe = ev_ + (profHead_ % kProfRing) * kProfEvents;
-  cudaEventRecord(pe[0], stream_);
+  // few islands: one CTA each (shortest stage chain); many (batched worlds): one warp each (b2c_islands_warp.cuh) - measured
+  // break-even ~5 islands per SM (scripts/gpu_islandmode.sh). The count comes from the last step whose scalars reached the host;
+  // either variant is correct for any count.
+  const bool warpMode = islandMode_ == 2 || (islandMode_ == 0 && hostScalars_->islandCount >= 5 * coopBlocks_);
   // the cluster kernel is launched only when the last step that reached the host had grid-path work (large or jointed islands);
   // the front kernel takes the cluster path only when told the kernel follows, so a stale view costs speed, never correctness
   const bool clusterLaunch = clusterCtas_ > 0 && !d.debugChecksums && (hostScalars_->smallConStart > 0 || hostScalars_->bigBodyCount > 0 || d.jointColorStart[kGraphColorCount] > 0);
   sp.clusterThreads = clusterLaunch ? clusterCtas_ * kCoopThreads : 0;
-  { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
-  cudaEventRecord(pe[1], stream_);
-  if (clusterLaunch) {
-    cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(clusterCtas_); cfg.blockDim = dim3(kCoopThreads); cfg.stream = stream_;
-    cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = clusterCtas_; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
-    cfg.attrs = &at; cfg.numAttrs = 1;
-    CK(cudaLaunchKernelEx(&cfg, k_solver_cluster, d, sp));
-  }
-  // few islands: one CTA each (shortest stage chain); thousands (batched worlds): one warp each (b2c_islands_warp.cuh).
-  // The count comes from the last step whose scalars reached the host; either variant is correct for any count.
-  int warpMode = islandMode_ == 2 || (islandMode_ == 0 && hostScalars_->islandCount >= 8 * coopBlocks_);
-  if (warpMode) k_solver_islands_warp<<<coopBlocks_, 32 * kWarpIslandsPerCta, kWarpIslandsPerCta * sizeof(WarpIslandSlice), stream_>>>(d, sp);
-  k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp, warpMode);
-  cudaEventRecord(pe[2], stream_);
   lastEndIndex_ = endIndex_;
   endIndex_ = 1 - endIndex_;
-  { void* args[] = {(void*)&d, (void*)&sp, (void*)&endIndex_}; CK(cudaLaunchCooperativeKernel((void*)k_finalize_phase, cgrid, cblock, args, 0, stream_)); }
-  cudaEventRecord(pe[3], stream_);
-  profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
-  CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
-  if (streamMoves_) {
-    CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)d.awakeCount, cudaMemcpyDeviceToHost, stream_));
-    movesFetched_ = true;
+  // Graph launches trade ~7 us of start latency for immunity to host launch jitter: off by default (a caller that synchronises every step is
+  // latency-bound), on through b2cuda_world_enable_graph_launch / B2CUDA_GRAPH=1 (several ranks on one host, or steps enqueued back to back).
+  if (graphMode_ < 0) { const char* e = getenv("B2CUDA_GRAPH"); graphMode_ = e && !strcmp(e, "1") && !d.debugChecksums ? 1 : 0; }
+  bool launched = false;
+  if (graphMode_ == 1) {
+    // key = everything baked into the graph's nodes
+    std::vector<unsigned char> key(sizeof(WorldDev) + sizeof(StepParams) + 5 * sizeof(int));
+    { unsigned char* k = key.data(); memcpy(k, &d, sizeof(WorldDev)); k += sizeof(WorldDev); memcpy(k, &sp, sizeof(StepParams)); k += sizeof(StepParams);
+      int f[5] = {endIndex_, warpMode, clusterLaunch, streamMoves_, streamBodies_}; memcpy(k, f, sizeof(f)); }
+    StepGraph* g = nullptr;
+    for (auto& c : graphs_) if (c.key == key) { g = &c; break; }
+    if (!g) {
+      if (graphs_.size() >= 8) {                    // parameters keep changing: drop the oldest
+        StepGraph& o = graphs_.front(); harvestGraph(o);
+        if (o.exec) cudaGraphExecDestroy(o.exec);
+        for (auto& e : o.ev) if (e) cudaEventDestroy(e);
+        graphs_.erase(graphs_.begin());
+      }
+      StepGraph ng; ng.key = key;
+      bool ok = true;
+      for (auto& e : ng.ev) ok = ok && cudaEventCreate(&e) == cudaSuccess;
+      cudaGraph_t graph = nullptr;
+      ok = ok && cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+      if (ok) {
+        int rc = enqueueStep(sp, warpMode, clusterLaunch, endIndex_, ng.ev, true);
+        ok = cudaStreamEndCapture(stream_, &graph) == cudaSuccess && rc == B2C_OK && graph != nullptr;
+      }
+      ok = ok && cudaGraphInstantiate(&ng.exec, graph, 0) == cudaSuccess;
+      if (graph) cudaGraphDestroy(graph);
+      if (ok) { graphs_.push_back(std::move(ng)); g = &graphs_.back(); }
+      else {                                          // this driver cannot capture the sequence: direct launches from now on
+        cudaGetLastError();
+        for (auto& e : ng.ev) if (e) cudaEventDestroy(e);
+        if (ng.exec) cudaGraphExecDestroy(ng.exec);
+        graphMode_ = 0;
+      }
+    }
+    if (g) {
+      harvestGraph(*g);
+      CK(cudaGraphLaunch(g->exec, stream_));
+      g->pending = true; profCount_++;
+      launched = true;
+    }
   }
-  if (streamBodies_) {                             // the caller reads body records every step: the copy rides behind the step
-    CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)d.bodyCapacity, cudaMemcpyDeviceToHost, stream_));
-    bodiesFetched_ = true;
+  if (!launched) {
+    cudaEvent_t* pe = ev_ + (profHead_ % kProfRing) * kProfEvents;
+    int rc = enqueueStep(sp, warpMode, clusterLaunch, endIndex_, pe, false); if (rc) return rc;
+    profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
   }
+  if (streamMoves_) movesFetched_ = true;
+  if (streamBodies_) bodiesFetched_ = true;
   CK(cudaGetLastError());
   stepCount_++;
   return B2C_OK;

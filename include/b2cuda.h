@@ -274,6 +274,10 @@ int32_t b2cuda_world_get_counters(B2CWorld* world, B2CCounters* out);
    order-independent checksums of the device state between the phases of the last step (scripts/gpu_determinism.py). */
 int32_t b2cuda_world_debug_checksums(B2CWorld* world, uint64_t* out16);
 int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);   /* averages over the steps since the previous call (<= 64) */
+/* (new, no reference counterpart) one CUDA-graph launch per step instead of one launch per kernel. The kernels then run back to back whatever
+ * the host's launch latency is - use it when several processes drive GPUs from one host (bench.py does for world_size > 1) or when
+ * steps are enqueued without reading results in between. Costs ~7 us of start latency per step, hence off by default (B2CUDA_GRAPH=1 also enables). */
+int32_t b2cuda_world_enable_graph_launch(B2CWorld* world, int32_t flag);
 /* (new, no reference counterpart) device-time stopwatch on the world's own stream: CUDA events around whatever was
  * enqueued between the two calls; stop synchronises. Used by bench.py so timing does not depend on torch's stream. */
 int32_t b2cuda_world_timer_start(B2CWorld* world);

@@ -399,3 +399,46 @@ def test_grid_barrier_solver_variant_bit_exact(scene, steps, monkeypatch):
              "tumbler": lambda w: scenes.tumbler(w, n=600, half=6.0), "zoo": lambda w: scenes.joint_zoo(w, copies=2, angles=False)}[scene]
     res = parity.run_pair(build, steps=steps, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+@pytest.mark.parametrize("scene", ["mixed", "zoo"])
+def test_graph_launch_path_bit_exact(scene, monkeypatch):
+    """B2CUDA_GRAPH=1 / b2cuda_world_enable_graph_launch: a step is ONE CUDA-graph launch instead of one launch per kernel. Same results."""
+    monkeypatch.setenv("B2CUDA_GRAPH", "1")
+    build = {"mixed": lambda w: scenes.mixed_drop(w), "zoo": lambda w: scenes.joint_zoo(w, copies=1, angles=False)}[scene]
+    res = parity.run_pair(build, steps=25, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_graph_rekeys_when_step_parameters_change(monkeypatch):
+    """Setters that change what is baked into the graph (gravity, tuning, warm starting, dt, substeps) re-key it."""
+    monkeypatch.setenv("B2CUDA_GRAPH", "1")
+
+    def mutate(w, step):
+        if step == 4:
+            w.SetGravity((1.0, -9.0))
+        if step == 8:
+            w.SetContactTuning(20.0, 5.0, 2.0)
+        if step == 12:
+            w.EnableWarmStarting(False)
+        if step == 16:
+            w.EnableWarmStarting(True)
+            w.SetGravity((0.0, -10.0))
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 8), steps=24, verbose=True, mutate=mutate)
+    assert res["max_rel_err"] == 0.0
+    # varying dt / substeps every step: more than 8 distinct configurations, the oldest graphs are dropped
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    from oracle_backend import OracleBackend
+    orc = api.World(OracleBackend(), scenes.world_def())
+    try:
+        for w in (cuda, orc):
+            scenes.add_pyramid(w, 6)
+        for k in range(24):
+            dt, sub = 1.0 / (50 + (k % 11)), 2 + (k % 3)
+            cuda.Step(dt, sub)
+            orc.Step(dt, sub)
+        a, b = cuda.ReadBodies(), orc.ReadBodies()
+        assert a.tobytes() == b.tobytes()
+    finally:
+        cuda.Destroy()
+        orc.Destroy()
