@@ -564,7 +564,11 @@ int World::upload() {
   d.bodyOut = nullptr;
   DA(dBodyRead_, B2CBodyRead, nBody);
   DA(dMoveEvents_, B2CBodyMoveEvent, nAwake);
-  CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)std::max(nAwake, 1), cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)std::max(nAwake, 1), cudaHostAllocMapped));
+  // B2CUDA_ZEROCOPY_MOVES=1: FinalizeBodies writes the move events straight into this mapped buffer instead of a device array + copy behind
+  // the step. Measured slower end to end (many_pyramids 560 vs 582 M body-substeps/s, batched 1663 vs 1779): off by default.
+  { const char* e = getenv("B2CUDA_ZEROCOPY_MOVES"); hMoveEventsDev_ = nullptr;
+    if (e && !strcmp(e, "1") && cudaHostGetDevicePointer((void**)&hMoveEventsDev_, hMoveEvents_, 0) != cudaSuccess) { hMoveEventsDev_ = nullptr; cudaGetLastError(); } }
   d.moveOut = nullptr;
   CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(nBody, 1), cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(nJoint, 1), cudaHostAllocDefault));

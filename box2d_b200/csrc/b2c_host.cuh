@@ -154,7 +154,8 @@ class World {
   int coopBlocks_ = 0;
   int clusterCtas_ = 0;   // CTAs of the solver cluster (16, 8 or 0 = off)
   B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false; bool streamBodies_ = false;
-  B2CBodyMoveEvent* dMoveEvents_ = nullptr; B2CBodyMoveEvent* hMoveEvents_ = nullptr; bool movesFetched_ = false, streamMoves_ = false, lastStepDtZero_ = false;
+  B2CBodyMoveEvent* dMoveEvents_ = nullptr; B2CBodyMoveEvent* hMoveEvents_ = nullptr; B2CBodyMoveEvent* hMoveEventsDev_ = nullptr;   // device alias of the mapped host buffer
+  bool movesFetched_ = false, streamMoves_ = false, lastStepDtZero_ = false;
   int islandMode_ = 0;   // 0 auto, 1 CTA per island, 2 warp per island   // streamBodies_: every step packs + copies the body records (set by the first GetBodyEvents)
   friend struct StepLauncher;
 };

@@ -1568,7 +1568,7 @@ int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch
   { void* args[] = {(void*)&d, (void*)&sp, (void*)&newEndIndex}; CK(cudaLaunchCooperativeKernel((void*)k_finalize_phase, cgrid, cblock, args, 0, stream_)); }
   CK(rec(pe[3]));
   CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
-  if (streamMoves_) CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)d.awakeCount, cudaMemcpyDeviceToHost, stream_));
+  if (streamMoves_ && !hMoveEventsDev_) CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)d.awakeCount, cudaMemcpyDeviceToHost, stream_));
   if (streamBodies_) CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)d.bodyCapacity, cudaMemcpyDeviceToHost, stream_));   // the caller reads body records every step: the copy rides behind the step
   return B2C_OK;
 }
@@ -1715,7 +1715,7 @@ int World::getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count) {
     k_pack_moves<<<gridFor(n, kThreads, 148 * 8), kThreads, 0, stream_>>>(d_, dMoveEvents_);
     CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
     movesFetched_ = true;
-    streamMoves_ = true; d_.moveOut = dMoveEvents_;   // from now on FinalizeBodies fills the events and step() copies them
+    streamMoves_ = true; d_.moveOut = hMoveEventsDev_ ? hMoveEventsDev_ : dMoveEvents_;   // from now on FinalizeBodies fills the events (mapped host memory, else device array + copy in step())
   }
   int rc = synchronize(); if (rc) return rc;
   *events = hMoveEvents_; *count = lastStepDtZero_ ? 0 : d_.awakeCount;
