@@ -242,6 +242,14 @@ class World:
         self._check(self.fns["create_revolute_joint"](self.handle, C.byref(joint_def), C.byref(out)))
         return out.value
 
+    def DestroyJoint(self, joint_id, wake_attached=True):
+        """JointAPI.DestroyJoint api/Joint.cs:9-17"""
+        self._check(self.fns["destroy_joint"](self.handle, joint_id, int(bool(wake_attached))))
+
+    def DestroyBody(self, body_id):
+        """BodyAPI.DestroyBody api/Body.cs:106-160"""
+        self._check(self.fns["destroy_body"](self.handle, body_id))
+
     def CreateJoint(self, joint_def):
         """JointAPI.Create{Distance,Motor,Filter,Prismatic,Revolute,Weld,Wheel}Joint api/Joint.cs:182,324,408,412,555,672,720"""
         out = C.c_int32(-1)

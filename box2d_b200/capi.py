@@ -145,6 +145,8 @@ PROTOS = {
     "create_shape": [_W, C.c_int32, C.POINTER(ShapeDef), C.POINTER(Geometry), C.POINTER(C.c_int32)],
     "create_revolute_joint": [_W, C.POINTER(RevoluteJointDef), C.POINTER(C.c_int32)],
     "create_joint": [_W, C.POINTER(JointDef), C.POINTER(C.c_int32)],
+    "destroy_joint": [_W, C.c_int32, C.c_int32],
+    "destroy_body": [_W, C.c_int32],
     "joint_set_param": [_W, C.c_int32, C.c_int32, C.c_float],
     "joint_enable": [_W, C.c_int32, C.c_int32, C.c_int32],
     "joint_set_limits": [_W, C.c_int32, C.c_float, C.c_float],

@@ -282,9 +282,12 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   j.generation = (uint16_t)(gen + 1);
   j.id = id; j.collideConnected = def.collideConnected != 0;
   j.bodyIdA = bodyA.id; j.prevKeyA = -1; j.nextKeyA = bodyA.headJointKey;      // src/Joint.cs:208-236
-  bodyA.headJointKey = id << 1; bodyA.jointCount++;
+  const int keyA = id << 1, keyB = (id << 1) | 1;
+  if (bodyA.headJointKey != -1) { HJoint& h = joints_[bodyA.headJointKey >> 1]; if (bodyA.headJointKey & 1) h.prevKeyB = keyA; else h.prevKeyA = keyA; }
+  bodyA.headJointKey = keyA; bodyA.jointCount++;
   j.bodyIdB = bodyB.id; j.prevKeyB = -1; j.nextKeyB = bodyB.headJointKey;
-  bodyB.headJointKey = (id << 1) | 1; bodyB.jointCount++;
+  if (bodyB.headJointKey != -1) { HJoint& h = joints_[bodyB.headJointKey >> 1]; if (bodyA.headJointKey & 1) h.prevKeyB = keyB; else h.prevKeyA = keyB; }   // tests bodyA's key, as written (:229)
+  bodyB.headJointKey = keyB; bodyB.jointCount++;
   int color = assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type);
   if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   JointDev& s = j.sim;
@@ -330,6 +333,160 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   colorJoints_[color].push_back(id);
   // DestroyContactsBetweenBodies (src/Joint.cs:155-180): no contacts exist before the first step.
   *jointId = id;
+  return B2C_OK;
+}
+
+// ---- JointAPI.DestroyJoint api/Joint.cs:9-17 / BodyAPI.DestroyBody api/Body.cs:106-160 -------------------------------------------------
+// The host mirror owns what only creation and destruction change (id pools, body shape/joint lists, joint colour arrays, the awake-set
+// order); the device owns what the step changes (contacts, colour bitsets, trees, move array, body rows). A destroy call edits the host
+// part as the reference writes it, then patches the device part with a small kernel on the world's stream.
+__global__ void k_joint_removed(WorldDev d, int bodyIdA, int bodyIdB, int color) {      // RemoveJointFromGraph src/ConstraintGraph.cs:256-264
+  if (color != kOverflowIndex) { d.bodyColorMask[bodyIdA] &= ~(1u << color); d.bodyColorMask[bodyIdB] &= ~(1u << color); }
+  d.sc->graphDirty = 1;                           // islands follow the joints
+}
+__device__ void destroyContactSerial(const WorldDev& d, int id, int endIndex) {          // World.DestroyContact src/Contact.cs:228-312
+  Scalars& s = *d.sc;
+  uint32_t flags = d.cFlags[id];
+  int2 sh = d.cShape[id], b = d.cBody[id];
+  bool touching = (flags & CF_TOUCHING) != 0;
+  if (touching && (flags & CF_ENABLE_CONTACT_EVENTS)) {
+    int k = s.endCount[endIndex];
+    if (k < d.eventCapacity) { B2CContactTouchEvent ev = {sh.x, sh.y, id, d.cGen[id]}; d.endEvents[endIndex][k] = ev; s.endCount[endIndex] = k + 1; }
+  }
+  int color = d.cColor[id];
+  if (color != -1) {                              // RemoveContactFromGraph src/ConstraintGraph.cs:221-241
+    if (color != kOverflowIndex) { d.bodyColorMask[b.x] &= ~(1u << color); d.bodyColorMask[b.y] &= ~(1u << color); }
+    else {
+      int li = d.cOvIndex[id], last = s.ovCount - 1;
+      if (li >= 0 && li <= last) {
+        if (li != last) { int moved = d.ovList[last]; d.ovList[li] = moved; d.cOvIndex[moved] = li; }
+        d.cOvIndex[id] = -1; s.ovCount = last;
+      }
+    }
+    d.cColor[id] = -1;
+  }
+  d.cFlags[id] = 0;
+  d.contactFree[s.contactFreeCount++] = id;       // IDPool.FreeId src/IDPool.cs
+  s.liveContactCount--;
+  s.graphDirty = 1;
+}
+// One CTA: every thread looks for the body's contacts, thread 0 then walks them in the order of the body's contact list (newest first),
+// removes the shapes' proxies and takes the body out of the awake set by swap-remove (api/Body.cs:142-153).
+__global__ void k_destroy_body(WorldDev d, int bodyId, int endIndex) {
+  __shared__ int sCount;
+  Scalars& s = *d.sc;
+  if (threadIdx.x == 0) sCount = 0;
+  __syncthreads();
+  const int n = s.contactNext;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (!(d.cFlags[i] & CF_ALIVE)) continue;
+    int2 b = d.cBody[i];
+    if (b.x == bodyId || b.y == bodyId) { int k = atomicAdd(&sCount, 1); d.opList[k] = i; }
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const int count = sCount;
+  for (int i = 1; i < count; i++) {               // insertion sort, descending creation stamp (a body has tens of contacts)
+    int id = d.opList[i]; uint32_t st = d.cStamp[id]; int j = i - 1;
+    while (j >= 0 && d.cStamp[d.opList[j]] < st) { d.opList[j + 1] = d.opList[j]; j--; }
+    d.opList[j + 1] = id;
+  }
+  for (int i = 0; i < count; i++) destroyContactSerial(d, d.opList[i], endIndex);     // DestroyBodyContacts src/Body.cs:232-244
+  for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+    int key = d.shapes[sid].proxyKey;
+    if (key == -1) continue;
+    const TreeDev& t = d.trees[key & 3];
+    const int proxyId = key >> 2;
+    if (t.moved[proxyId]) {                       // BroadPhase.UnBufferMove src/BroadPhase.cs:60-71
+      t.moved[proxyId] = 0;
+      for (int i = 0; i < s.moveCount; i++) if (d.moveArray[i] == key) { d.moveArray[i] = d.moveArray[s.moveCount - 1]; s.moveCount--; break; }
+    }
+    TreeView v{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta};
+    tvRemoveLeaf(v, proxyId); tvFreeNode(v, proxyId); t.meta[3]--;       // DynamicTree.DestroyProxy src/DynamicTree.cs:460-468
+    if ((key & 3) == kStaticBody) s.staticRanksValid = 0;
+    d.shapes[sid].proxyKey = -1;
+    d.shapeAABB[sid] = make_float4(0, 0, 0, 0); d.shapeFat[sid] = make_float4(0, 0, 0, 0);
+  }
+  d.bodyHeadShape[bodyId] = -1;
+  int sim = d.bodySim[bodyId];
+  if (sim >= 0) {                                 // bodySims / bodyStates RemoveSwap; the host lowers awakeCount (a kernel parameter) after this launch
+    int last = d.awakeCount - 1;
+    if (sim != last) {
+      d.st0[sim] = d.st0[last]; d.st1[sim] = d.st1[last]; d.simMass[sim] = d.simMass[last]; d.simForce[sim] = d.simForce[last];
+      d.simPose[sim] = d.simPose[last]; d.simLocal[sim] = d.simLocal[last]; d.simPose0[sim] = d.simPose0[last]; d.simFlags[sim] = d.simFlags[last];
+      int movedBody = d.simBodyId[last]; d.simBodyId[sim] = movedBody; d.bodySim[movedBody] = sim;
+    }
+    d.bodySim[bodyId] = -1;
+  }
+  d.bodyType[bodyId] = kStaticBody; d.bodyColorMask[bodyId] = 0; d.bodyHeadJoint[bodyId] = -1; d.bodyJointCount[bodyId] = 0;
+  d.bodyXf[bodyId] = make_float4(0, 0, 0, 0); d.bodyCenter[bodyId] = make_float2(0, 0); d.bodyFlags[bodyId] = 0;
+  s.graphDirty = 1;
+}
+
+int World::destroyJoint(int jointId) {           // DestroyJointInternal src/Joint.cs:297-375 (wakeBodies: no sleeping sets in this build)
+  if (jointId < 0 || jointId >= (int)joints_.size() || joints_[jointId].id != jointId) return fail(B2C_E_INVALID, "bad joint id");
+  HJoint& j = joints_[jointId];
+  HBody& bodyA = bodies_[j.bodyIdA]; HBody& bodyB = bodies_[j.bodyIdB];
+  auto setNext = [&](int key, int v) { HJoint& o = joints_[key >> 1]; if (key & 1) o.nextKeyB = v; else o.nextKeyA = v; };
+  auto setPrev = [&](int key, int v) { HJoint& o = joints_[key >> 1]; if (key & 1) o.prevKeyB = v; else o.prevKeyA = v; };
+  if (j.prevKeyA != -1) setNext(j.prevKeyA, j.nextKeyA);
+  if (j.nextKeyA != -1) setPrev(j.nextKeyA, j.prevKeyA);
+  if (bodyA.headJointKey == (jointId << 1)) bodyA.headJointKey = j.nextKeyA;
+  bodyA.jointCount--;
+  if (j.prevKeyB != -1) setNext(j.prevKeyB, j.nextKeyB);
+  if (j.nextKeyB != -1) setPrev(j.nextKeyB, j.prevKeyB);
+  if (bodyB.headJointKey == ((jointId << 1) | 1)) bodyB.headJointKey = j.nextKeyB;
+  bodyB.jointCount--;
+  const int color = j.sim.colorIndex;
+  std::vector<int>& arr = colorJoints_[color];      // RemoveJointFromGraph: RemoveSwap in the colour's array
+  for (size_t k = 0; k < arr.size(); k++) if (arr[k] == jointId) { arr[k] = arr.back(); arr.pop_back(); break; }
+  if (!onDevice_ && color != kOverflowIndex) { colorMask_[j.bodyIdA] &= ~(1u << color); colorMask_[j.bodyIdB] &= ~(1u << color); }
+  const int idA = j.bodyIdA, idB = j.bodyIdB;
+  j.id = -1;
+  jointIds_.release(jointId);
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_joint_removed<<<1, 1, 0, stream_>>>(d_, idA, idB, color);
+  CK(cudaGetLastError());
+  return uploadJointLists();
+}
+int World::uploadJointLists() {                  // joint edges, per-body list heads and the colour-grouped joint order after a destroy
+  const int nJoint = (int)joints_.size(), nBody = (int)bodies_.size();
+  std::vector<int4> je(nJoint); std::vector<int> jsorted, head(nBody), cnt(nBody);
+  for (int i = 0; i < nJoint; i++) { const HJoint& j = joints_[i]; je[i] = make_int4(j.bodyIdA, j.nextKeyA, j.bodyIdB, j.nextKeyB); }
+  for (int i = 0; i < nBody; i++) { head[i] = bodies_[i].id == i ? bodies_[i].headJointKey : -1; cnt[i] = bodies_[i].id == i ? bodies_[i].jointCount : 0; }
+  d_.jointColorStart[0] = 0;
+  for (int c = 0; c < kGraphColorCount; c++) { for (int id : colorJoints_[c]) jsorted.push_back(id); d_.jointColorStart[c + 1] = (int)jsorted.size(); }
+  CK(cudaStreamSynchronize(stream_));            // pageable sources: the copies below must not outlive these vectors
+  if (nJoint) CK(cudaMemcpy(d_.jointEdges, je.data(), sizeof(int4) * nJoint, cudaMemcpyHostToDevice));
+  if (!jsorted.empty()) CK(cudaMemcpy(d_.jointSorted, jsorted.data(), sizeof(int) * jsorted.size(), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_.bodyHeadJoint, head.data(), sizeof(int) * nBody, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_.bodyJointCount, cnt.data(), sizeof(int) * nBody, cudaMemcpyHostToDevice));
+  return B2C_OK;
+}
+int World::destroyBody(int bodyId) {             // BodyAPI.DestroyBody api/Body.cs:106-160
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "destroy_body before the first step is not supported in this build (the world is still being assembled on the host)");
+  HBody& b = bodies_[bodyId];
+  int edgeKey = b.headJointKey;
+  while (edgeKey != -1) {
+    int jointId = edgeKey >> 1, edge = edgeKey & 1;
+    edgeKey = edge == 1 ? joints_[jointId].nextKeyB : joints_[jointId].nextKeyA;
+    int rc = destroyJoint(jointId); if (rc) return rc;
+  }
+  CK(cudaSetDevice(device_));
+  k_destroy_body<<<1, 256, 0, stream_>>>(d_, bodyId, endIndex_);      // contacts (list order), proxies, awake-set swap-remove
+  CK(cudaGetLastError());
+  for (int sid = b.headShapeId; sid != -1;) { HShape& sh = shapes_[sid]; int next = sh.nextShapeId; sh.proxyKey = -1; sh.id = -1; shapeIds_.release(sid); sid = next; }
+  if (b.simIndex >= 0) {
+    int last = (int)awakeOrder_.size() - 1;
+    if (b.simIndex != last) { int moved = awakeOrder_[last]; awakeOrder_[b.simIndex] = moved; bodies_[moved].simIndex = b.simIndex; }
+    awakeOrder_.pop_back();
+    d_.awakeCount = (int)awakeOrder_.size();
+  }
+  bodyIds_.release(bodyId);
+  b.id = -1; b.simIndex = -1; b.headShapeId = -1; b.headJointKey = -1; b.jointCount = 0;
+  eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false;
   return B2C_OK;
 }
 
@@ -531,7 +688,7 @@ int World::upload() {
     DA(d.moveBig, int, d.moveCapacity); DA(d.moveHitBuf, int2, (size_t)d.moveCapacity * 4); DA(d.bigList, int, kMaxBigQueries); DA(d.bigSegStart, int, kMaxBigQueries + 1); DA(d.bigOff, int, kMaxBigQueries + 1);
     DA(d.bigScan, int, d.bigScratch); DA(d.bigFlag, uint8_t, d.bigScratch); DA(d.bigHits, int2, d.pairCapacity); }
   UP(d.moveArray, moveArray_);
-  DA(d.cShape, int2, contactCap); DA(d.cBody, int2, contactCap); DA(d.cFlags, uint32_t, contactCap); DA(d.cColor, int, contactCap); DA(d.cGen, uint32_t, contactCap);
+  DA(d.cShape, int2, contactCap); DA(d.cBody, int2, contactCap); DA(d.cFlags, uint32_t, contactCap); DA(d.cColor, int, contactCap); DA(d.cGen, uint32_t, contactCap); DA(d.cStamp, uint32_t, contactCap);
   DA(d.cMat, float4, contactCap); DA(d.cMass, float4, contactCap); DA(d.cSim, int2, contactCap);
   DA(d.mN, float4, contactCap); DA(d.mA0, float4, contactCap); DA(d.mA1, float4, contactCap); DA(d.mB0, float4, contactCap); DA(d.mB1, float4, contactCap);
   DA(d.mC0, float4, contactCap); DA(d.mC1, float4, contactCap); DA(d.contactFree, int, contactCap);
@@ -888,10 +1045,14 @@ int World::readJoints(B2CJointRead* dst, int capacity, int* count) {
     if (fetch(jd, d_.joints, n, stream_)) return fail(B2C_E_CUDA, "read_joints copy failed");
     CK(cudaStreamSynchronize(stream_));
   } else { jd.resize(n); for (int i = 0; i < n; i++) jd[i] = joints_[i].sim; }
-  for (int i = 0; i < n && i < capacity; i++) {
+  int m = 0;
+  for (int i = 0; i < n; i++) {
+    if (joints_[i].id == -1) continue;             // destroyed: the slot waits in the id pool
     const JointDev& s = jd[i];
-    dst[i] = {s.jointId, s.colorIndex, {s.linearImpulse.x, s.linearImpulse.y}, s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse, s.type, {s.linearImpulse2.x, s.linearImpulse2.y}};
+    if (m < capacity) dst[m] = {s.jointId, s.colorIndex, {s.linearImpulse.x, s.linearImpulse.y}, s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse, s.type, {s.linearImpulse2.x, s.linearImpulse2.y}};
+    m++;
   }
+  *count = m;
   return B2C_OK;
 }
 
@@ -901,6 +1062,7 @@ int World::readShapes(B2CShapeRead* dst, int capacity, int* count) {
   if (!onDevice_) {
     for (int i = 0; i < n && i < capacity; i++) {
       const HShape& s = shapes_[i];
+      if (s.id == -1) { dst[i] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, -1, 0}; continue; }
       dst[i] = {{s.aabb.lo.x, s.aabb.lo.y}, {s.aabb.hi.x, s.aabb.hi.y}, {s.fat.lo.x, s.fat.lo.y}, {s.fat.hi.x, s.fat.hi.y}, s.proxyKey, 0};
     }
     return B2C_OK;
@@ -909,8 +1071,10 @@ int World::readShapes(B2CShapeRead* dst, int capacity, int* count) {
   std::vector<float4> a, f; std::vector<ShapeDev> sh;
   if (fetch(a, d_.shapeAABB, n, stream_) | fetch(f, d_.shapeFat, n, stream_) | fetch(sh, d_.shapes, n, stream_)) return fail(B2C_E_CUDA, "read_shapes copy failed");
   CK(cudaStreamSynchronize(stream_));
-  for (int i = 0; i < n && i < capacity; i++)
+  for (int i = 0; i < n && i < capacity; i++) {
+    if (shapes_[i].id == -1) { dst[i] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, -1, 0}; continue; }      // destroyed with its body
     dst[i] = {{a[i].x, a[i].y}, {a[i].z, a[i].w}, {f[i].x, f[i].y}, {f[i].z, f[i].w}, sh[i].proxyKey, (sh[i].flags & SF_ENLARGED) ? 1 : 0};
+  }
   return B2C_OK;
 }
 

@@ -59,6 +59,9 @@ class World {
   int createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId);
   int createRevoluteJoint(const B2CRevoluteJointDef& def, int* jointId);
   int createJoint(const B2CJointDef& def, int* jointId);
+  int destroyJoint(int jointId);
+  int destroyBody(int bodyId);
+  int uploadJointLists();
   int jointOp(int jointId, int patch, int which, float a, float b);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }
   int setTransform(int bodyId, V2 p, Rot q);

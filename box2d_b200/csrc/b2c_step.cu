@@ -282,6 +282,7 @@ __device__ void p_create_contacts(const WorldDev& d, int tid, int stride) {
     d.cFlags[id] = flags;
     d.cColor[id] = -1;
     d.cGen[id] = d.cGen[id] + 1;
+    d.cStamp[id] = d.sc->contactStamp + (unsigned)r;
     d.cConstraint[id] = -1;
     float4 ma = sa.material, mb = sb.material;
     d.cMat[id] = make_float4(sqrtf(ma.x * mb.x), netMax(ma.y, mb.y), 0.0f, 0.0f);   // src/World.cs:139-140
@@ -305,7 +306,7 @@ __device__ void p_pairs_finish(const WorldDev& d) {
   s.contactFreeCount -= fromFree;
   s.contactNext += n - fromFree;
   if (s.contactNext > d.contactCapacity) { s.contactNext = d.contactCapacity; s.errorFlags |= (int)ERR_CONTACT_CAPACITY; }
-  s.liveContactCount += n;
+  s.liveContactCount += n; s.contactStamp += (unsigned)n;
   s.moveCount = 0; s.bigQueryCount = 0;
   s.beginCount = 0; s.hitCount = 0; s.jointEventCount = 0; s.anyRestitution = 0;
 }
@@ -456,6 +457,7 @@ __device__ void p_collide(const WorldDev& d, const StepParams& sp, int tid, int 
 __device__ void p_contact_events(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.sc->contactNext;
   int freeCount = d.sc->contactFreeCount;
+  const int endBase = d.sc->endCount[sp.endIndex];     // events appended by DestroyContact between steps come first (src/Contact.cs:236-252)
   for (int i = tid; i < n; i += stride) {
     uint32_t flags = d.cFlags[i];
     if (!(flags & CF_STATE_MASK)) continue;
@@ -463,7 +465,7 @@ __device__ void p_contact_events(const WorldDev& d, const StepParams& sp, int ti
     int2 sh = d.cShape[i];
     B2CContactTouchEvent ev = {sh.x, sh.y, i, d.cGen[i]};
     if (flags & CF_DISJOINT) {
-      if ((flags & CF_TOUCHING) && (flags & CF_ENABLE_CONTACT_EVENTS)) d.endEvents[sp.endIndex][rank.y] = ev;
+      if ((flags & CF_TOUCHING) && (flags & CF_ENABLE_CONTACT_EVENTS) && endBase + rank.y < d.eventCapacity) d.endEvents[sp.endIndex][endBase + rank.y] = ev;
       d.contactFree[freeCount + rank.z] = i;
       if (flags & CF_TOUCHING) d.opList[rank.w] = i;
       d.cFlags[i] = 0;                             // slot is dead; cBody/cColor stay readable for the graph op
@@ -472,7 +474,7 @@ __device__ void p_contact_events(const WorldDev& d, const StepParams& sp, int ti
       d.opList[rank.w] = i;
       d.cFlags[i] = (flags & ~CF_STATE_MASK) | CF_TOUCHING;
     } else {
-      if (flags & CF_ENABLE_CONTACT_EVENTS) d.endEvents[sp.endIndex][rank.y] = ev;
+      if ((flags & CF_ENABLE_CONTACT_EVENTS) && endBase + rank.y < d.eventCapacity) d.endEvents[sp.endIndex][endBase + rank.y] = ev;
       d.opList[rank.w] = i;
       d.cFlags[i] = flags & ~(CF_STATE_MASK | CF_TOUCHING);
     }
@@ -482,7 +484,7 @@ __device__ void p_events_finish(const WorldDev& d, const StepParams& sp, int4* t
   Scalars& s = *d.sc;
   int4 t = *totals;
   if (s.contactNext == 0) t = make_int4(0, 0, 0, 0);
-  s.beginCount = t.x; s.endCount[sp.endIndex] = t.y;
+  s.beginCount = t.x; s.endCount[sp.endIndex] += t.y;
   s.contactFreeCount += t.z; s.liveContactCount -= t.z;
   s.opCount = t.w;
   if (t.w > 0) s.graphDirty = 1;
@@ -1350,7 +1352,7 @@ __device__ void phase_collide(cg::grid_group& grid, const WorldDev& d, const Ste
   p_collide(d, sp, tid, stride);
   grid.sync();
   if (s.anyContactFlag == 0) {                    // no begin / end / destroy anywhere: the serial pass is empty
-    if (tid == 0) { s.beginCount = 0; s.endCount[sp.endIndex] = 0; s.opCount = 0; }
+    if (tid == 0) { s.beginCount = 0; s.opCount = 0; }      // endCount keeps the events DestroyContact appended since the last step
     return;
   }
   gridScan<int4>(grid, d.flagScan, d.scanBlockSums4, s.contactNext, d.flagScan + d.contactCapacity);

@@ -98,6 +98,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int awakeCount, anyRestitution, anyContactFlag, anyHitShapes;
   unsigned long long phaseStamp[8], phaseAcc[8];   // %globaltimer stamps inside k_step_front and their per-phase sums (ns)
   int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
+  unsigned int contactStamp;   // contacts created so far (see cStamp)
   int clusterSolve;    // this step's grid-path constraints are solved by k_solver_cluster (one thread-block cluster) instead of the front kernel
   int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
   int bigQueryCount, bigHitTotal, bigGroupTotal, staticRanksValid;   // wide broadphase queries (b2c_bigquery.cuh)
@@ -177,6 +178,7 @@ struct WorldDev {
   int pairTableSize;   // power of two
   // --- contacts, slot == contactId (src/Contact.cs Contact + ContactSim) ---
   int2* cShape; int2* cBody; uint32_t* cFlags; int* cColor; uint32_t* cGen;
+  uint32_t* cStamp;    // creation sequence number: a body's contact list (src/Contact.cs:196-216, pushed at the head) is its contacts by descending stamp
   float4* cMat; float4* cMass; int2* cSim;
   float4* mN;          // normal.x normal.y rollingImpulse pointCount(bits)
   float4* mA0; float4* mA1;   // anchorA.xy anchorB.xy

@@ -168,6 +168,12 @@ int32_t b2cuda_create_revolute_joint(B2CWorld* world, const B2CRevoluteJointDef*
  * CreateWeldJoint :672 / CreateWheelJoint :720 — api/Joint.cs; World.CreateJoint src/Joint.cs:181-296 */
 int32_t b2cuda_default_joint_def(int32_t type, B2CJointDef* def);
 int32_t b2cuda_create_joint(B2CWorld* world, const B2CJointDef* def, int32_t* jointId);
+/* JointAPI.DestroyJoint api/Joint.cs:9-17 (DestroyJointInternal src/Joint.cs:297-375) and BodyAPI.DestroyBody api/Body.cs:106-160: the body's joints,
+ * then its contacts in contact-list order (end-touch events go to the buffer the NEXT step reports, ids return to the LIFO pool), its shapes'
+ * proxies (UnBufferMove + tree RemoveLeaf), then the body leaves the awake set by swap-remove. Allowed between steps once the world has been
+ * stepped (destroy_joint also before). Creating bodies, shapes or joints after the first step stays unsupported (B2C_E_UNSUPPORTED). */
+int32_t b2cuda_destroy_joint(B2CWorld* world, int32_t jointId, int32_t wakeAttached);
+int32_t b2cuda_destroy_body(B2CWorld* world, int32_t bodyId);
 /* Joint mutators — api/Joint.cs. One generic entry per shape of setter; `param` selects the field (B2C_JP_*). Wrong joint type for a
  * field returns B2C_E_INVALID (the reference asserts the type, api/Joint.cs:169-179). After the first step each call is a one-thread
  * patch of the device joint record, ordered on the world's stream (no read-back, no synchronisation).

@@ -76,6 +76,8 @@ int32_t b2o_body_set_target_transform(World* w, int32_t id, B2CTransform t, floa
 int32_t b2o_body_set_mass_data(World* w, int32_t id, float mass, float inertia, B2CVec2 c) { w->SetMassData(id, mass, inertia, V(c)); return 0; }
 int32_t b2o_body_set_motion_locks(World* w, int32_t id, int32_t lx, int32_t ly, int32_t az) { w->SetMotionLocks(id, lx != 0, ly != 0, az != 0); return 0; }
 int32_t b2o_shape_set_surface_material(World* w, int32_t id, float f, float r, float rr, float ts) { w->SetSurfaceMaterial(id, f, r, rr, ts); return 0; }
+int32_t b2o_destroy_joint(World* w, int32_t id, int32_t) { if (id < 0 || id >= (int)w->joints.size() || w->joints[id].jointId != id) return -1; w->DestroyJoint(id); return 0; }
+int32_t b2o_destroy_body(World* w, int32_t id) { if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id != id) return -1; w->DestroyBody(id); return 0; }
 int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
 int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }
 int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAngularVelocity(id, x); return 0; }
@@ -201,6 +203,7 @@ int32_t b2o_world_read_shapes(World* w, B2CShapeRead* dst, int32_t capacity, int
   int n = (int)w->shapes.size(); *count = n;
   for (int i = 0; i < n && i < capacity; i++) {
     const Shape& s = w->shapes[i];
+    if (s.id == -1) { dst[i] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, -1, 0}; continue; }      // destroyed with its body
     dst[i] = {CV(s.aabb.lo), CV(s.aabb.hi), CV(s.fatAABB.lo), CV(s.fatAABB.hi), s.proxyKey, s.enlargedAABB ? 1 : 0};
   }
   return 0;

@@ -331,6 +331,84 @@ bool World::JointSetLimits(int jointId, float lower, float upper) {
   return true;
 }
 
+template <class T> static int RemoveSwap(std::vector<T>& a, int index) {   // include/Box2D.cs:9-19
+  int movedIndex = -1;
+  if (index != (int)a.size() - 1) { movedIndex = (int)a.size() - 1; a[index] = a[movedIndex]; }
+  a.pop_back();
+  return movedIndex;
+}
+
+// DestroyJointInternal src/Joint.cs:297-375 (wakeBodies: no sleeping sets here; islands are not restated)
+void World::DestroyJoint(int jointId) {
+  Joint& joint = joints[jointId];
+  JointEdge edgeA = joint.edge0, edgeB = joint.edge1;
+  Body& bodyA = bodies[edgeA.bodyId]; Body& bodyB = bodies[edgeB.bodyId];
+  if (edgeA.prevKey != -1) { Joint& prev = joints[edgeA.prevKey >> 1]; if (edgeA.prevKey & 1) prev.edge1.nextKey = edgeA.nextKey; else prev.edge0.nextKey = edgeA.nextKey; }
+  if (edgeA.nextKey != -1) { Joint& next = joints[edgeA.nextKey >> 1]; if (edgeA.nextKey & 1) next.edge1.prevKey = edgeA.prevKey; else next.edge0.prevKey = edgeA.prevKey; }
+  int edgeKeyA = jointId << 1;
+  if (bodyA.headJointKey == edgeKeyA) bodyA.headJointKey = edgeA.nextKey;
+  bodyA.jointCount--;
+  if (edgeB.prevKey != -1) { Joint& prev = joints[edgeB.prevKey >> 1]; if (edgeB.prevKey & 1) prev.edge1.nextKey = edgeB.nextKey; else prev.edge0.nextKey = edgeB.nextKey; }
+  if (edgeB.nextKey != -1) { Joint& next = joints[edgeB.nextKey >> 1]; if (edgeB.nextKey & 1) next.edge1.prevKey = edgeB.prevKey; else next.edge0.prevKey = edgeB.prevKey; }
+  int edgeKeyB = (jointId << 1) | 1;
+  if (bodyB.headJointKey == edgeKeyB) bodyB.headJointKey = edgeB.nextKey;
+  bodyB.jointCount--;
+  if (joint.setIndex == kAwakeSet && joint.colorIndex != -1) {     // RemoveJointFromGraph src/ConstraintGraph.cs:256-276
+    GraphColor& color = colors[joint.colorIndex];
+    if (joint.colorIndex != kOverflowIndex) { color.bodySet.ClearBit(edgeA.bodyId); color.bodySet.ClearBit(edgeB.bodyId); }
+    int movedIndex = RemoveSwap(color.jointSims, joint.localIndex);
+    if (movedIndex != -1) joints[color.jointSims[joint.localIndex].jointId].localIndex = joint.localIndex;
+  }
+  joint.setIndex = -1; joint.localIndex = -1; joint.colorIndex = -1; joint.jointId = -1;
+  jointIdPool.FreeId(jointId);
+}
+
+void World::UnBufferMove(int proxyKey) {        // src/BroadPhase.cs:60-71
+  if (moveSet.erase(proxyKey)) {
+    for (size_t i = 0; i < moveArray.size(); i++) if (moveArray[i] == proxyKey) { moveArray[i] = moveArray.back(); moveArray.pop_back(); break; }
+  }
+}
+
+void World::DestroyBody(int bodyId) {           // api/Body.cs:106-160 (awake or static set; no sensors, chains, islands)
+  Body& body = bodies[bodyId];
+  int edgeKey = body.headJointKey;
+  while (edgeKey != -1) {
+    int jointId = edgeKey >> 1, edgeIndex = edgeKey & 1;
+    Joint& joint = joints[jointId];
+    edgeKey = edgeIndex == 1 ? joint.edge1.nextKey : joint.edge0.nextKey;
+    DestroyJoint(jointId);
+  }
+  edgeKey = body.headContactKey;                // DestroyBodyContacts src/Body.cs:232-244
+  while (edgeKey != -1) {
+    int contactId = edgeKey >> 1, edgeIndex = edgeKey & 1;
+    Contact& contact = contacts[contactId];
+    edgeKey = edgeIndex == 1 ? contact.edge1.nextKey : contact.edge0.nextKey;
+    DestroyContact(contact);
+  }
+  int shapeId = body.headShapeId;
+  while (shapeId != -1) {
+    Shape& shape = shapes[shapeId];
+    if (shape.proxyKey != -1) {                 // Shape.DestroyProxy src/Shape.cs:128-131 -> BroadPhase.DestroyProxy src/BroadPhase.cs:80-86
+      UnBufferMove(shape.proxyKey);
+      trees[ProxyType(shape.proxyKey)].DestroyProxy(ProxyId(shape.proxyKey));
+      shape.proxyKey = -1;
+    }
+    shapeIdPool.FreeId(shapeId);
+    shape.id = -1;
+    shapeId = shape.nextShapeId;
+  }
+  if (body.setIndex == kAwakeSet) {
+    int movedIndex = RemoveSwap(awakeSet.bodySims, body.localIndex);
+    if (movedIndex != -1) bodies[awakeSet.bodySims[body.localIndex].bodyId].localIndex = body.localIndex;
+    RemoveSwap(awakeSet.bodyStates, body.localIndex);
+  } else {
+    int movedIndex = RemoveSwap(staticSet.bodySims, body.localIndex);
+    if (movedIndex != -1) bodies[staticSet.bodySims[body.localIndex].bodyId].localIndex = body.localIndex;
+  }
+  bodyIdPool.FreeId(body.id);
+  body.setIndex = -1; body.localIndex = -1; body.id = -1;
+}
+
 void World::DestroyContactsBetweenBodies(Body& bodyA, Body& bodyB) {    // src/Joint.cs:155-180
   int contactKey, otherBodyId;
   if (bodyA.contactCount < bodyB.contactCount) { contactKey = bodyA.headContactKey; otherBodyId = bodyB.id; }

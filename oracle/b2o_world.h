@@ -208,6 +208,9 @@ class World {
   int CreateShape(int bodyId, const ShapeDef& def, const Geom& geom);
   int CreateRevoluteJoint(const RevoluteJointDef& def);
   int CreateJoint(const JointDef& def);
+  void DestroyJoint(int jointId);          // JointAPI.DestroyJoint api/Joint.cs:9-17 -> DestroyJointInternal src/Joint.cs:297-375
+  void DestroyBody(int bodyId);            // BodyAPI.DestroyBody api/Body.cs:106-160
+  void UnBufferMove(int proxyKey);         // src/BroadPhase.cs:60-71
   void SetTargetTransform(int bodyId, const Transform& target, float timeStep);
   void SetMassData(int bodyId, float mass, float rotationalInertia, Vec2 center);
   void SetMotionLocks(int bodyId, bool linearX, bool linearY, bool angularZ);

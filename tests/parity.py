@@ -74,7 +74,7 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
             assert a["joint_events"].tolist() == b["joint_events"].tolist(), f"step{step} joint events {a['joint_events']} vs {b['joint_events']}"
             ca, cb = a["counters"], b["counters"]
             max_overflow = max(max_overflow, ca.colorCounts[23])
-            for f in ("contactCount", "touchingContactCount", "contactIdCapacity", "activeColorCount", "moveCount", "newPairCount"):
+            for f in ("bodyCount", "awakeBodyCount", "shapeCount", "jointCount", "contactCount", "touchingContactCount", "contactIdCapacity", "activeColorCount", "moveCount", "newPairCount"):
                 assert getattr(ca, f) == getattr(cb, f), f"step{step} counters.{f}: {getattr(ca, f)} vs {getattr(cb, f)}"
             assert list(ca.colorCounts) == list(cb.colorCounts), f"step{step} colorCounts {list(ca.colorCounts)} vs {list(cb.colorCounts)}"
             e = compare_struct(f"step{step}.contacts", a["contacts"], b["contacts"], report=rep)

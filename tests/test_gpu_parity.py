@@ -442,3 +442,94 @@ def test_graph_rekeys_when_step_parameters_change(monkeypatch):
     finally:
         cuda.Destroy()
         orc.Destroy()
+
+
+def test_destroy_bodies_between_steps_bit_exact():
+    """BodyAPI.DestroyBody (api/Body.cs:106-160) between steps: the body's contacts leave in contact-list order (end events reported by the
+    next step, ids back to the LIFO pool, colour bits cleared), its proxies leave the trees, the awake set closes the gap by swap-remove.
+    Bodies from the bottom row, the middle and the top of a pyramid, then the static ground itself."""
+    def mutate(w, step):
+        if step == 6:
+            w.DestroyBody(5)
+        elif step == 10:
+            w.DestroyBody(30)
+            w.DestroyBody(31)
+        elif step == 15:
+            w.DestroyBody(55)
+            w.DestroyBody(1)
+        elif step == 22:
+            w.DestroyBody(0)
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 10), steps=36, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    assert res["bodies"] == 56 - 6
+
+
+def test_destroy_bodies_in_overflow_colour_and_pile_bit_exact():
+    def mutate(w, step):
+        if step == 5:
+            w.DestroyBody(3)           # a box under the plank: one of its contacts sits in the overflow colour
+        elif step == 9:
+            w.DestroyBody(27)          # the plank
+    res = parity.run_pair(lambda w: scenes.overflow_plank(w, 26), steps=20, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+    def cull(w, step):
+        if step in (8, 16, 24):
+            for b in range(10 + step, 400, 37):
+                w.DestroyBody(b)
+    res = parity.run_pair(lambda w: scenes.tumbler(w, 400), steps=32, mutate=cull, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_destroy_joints_and_jointed_bodies_bit_exact():
+    """JointAPI.DestroyJoint (DestroyJointInternal src/Joint.cs:297-375) before and after the first step, and DestroyBody on bodies that
+    carry joints (api/Body.cs:117-129 walks the joint list first)."""
+    holder = {}
+
+    def build(w):
+        holder["zoo"] = scenes.joint_zoo(w, copies=3, angles=False)
+        w.DestroyJoint(holder["zoo"][2]["distance_rigid"])          # host-side path: the world is still being assembled
+
+    def mutate(w, step):
+        zoo = holder["zoo"]
+        if step == 4:
+            w.DestroyJoint(zoo[0]["filter"])                        # the two overlapping boxes start to collide
+            w.DestroyJoint(zoo[1]["revolute"])
+        elif step == 9:
+            w.DestroyJoint(zoo[0]["distance_spring"])
+            w.DestroyJoint(zoo[1]["motor_velocity"])
+        elif step == 14:
+            j = w.ReadJoints()
+            assert zoo[0]["filter"] not in j["jointId"].tolist()
+            w.DestroyBody(3)                                        # carries joints in the Atan2-free zoo
+            w.DestroyBody(1)
+        elif step == 20:
+            w.DestroyBody(0)                                        # the first copy's ground: every joint anchored to it goes too
+    res = parity.run_pair(build, steps=40, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+    res = parity.run_pair(lambda w: scenes.joint_grid(w, 8), steps=24, verbose=True,
+                          mutate=lambda w, s: (w.DestroyBody(27), w.DestroyJoint(5), w.DestroyJoint(40)) if s == 6 else None)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_destroy_rejects_stale_ids_and_reports_counts():
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        scenes.add_pyramid(cuda, 4)
+        with pytest.raises(Exception):
+            cuda.DestroyBody(3)                                     # before the first step: unsupported, said loudly
+        cuda.Step(1.0 / 60.0, 4)
+        cuda.DestroyBody(3)
+        with pytest.raises(Exception):
+            cuda.DestroyBody(3)
+        with pytest.raises(Exception):
+            cuda.DestroyJoint(0)
+        with pytest.raises(Exception):
+            cuda.GetTransform(3)
+        cuda.Step(1.0 / 60.0, 4)
+        c = cuda.GetCounters()
+        assert c.bodyCount == 10 and c.awakeBodyCount == 9 and c.shapeCount == 10
+        assert len(cuda.GetBodyMoveEvents()) == 9
+    finally:
+        cuda.Destroy()
