@@ -250,6 +250,18 @@ class World:
         """BodyAPI.DestroyBody api/Body.cs:106-160"""
         self._check(self.fns["destroy_body"](self.handle, body_id))
 
+    def DestroyShape(self, shape_id, update_body_mass=True):
+        """ShapeAPI.DestroyShape api/Shape.cs:48-56"""
+        self._check(self.fns["destroy_shape"](self.handle, shape_id, int(bool(update_body_mass))))
+
+    def SetDensity(self, shape_id, density, update_body_mass=True):
+        """ShapeAPI.SetDensity api/Shape.cs:95-103"""
+        self._check(self.fns["shape_set_density"](self.handle, shape_id, density, int(bool(update_body_mass))))
+
+    def ApplyMassFromShapes(self, body_id):
+        """BodyAPI.ApplyMassFromShapes api/Body.cs:617-621"""
+        self._check(self.fns["body_apply_mass_from_shapes"](self.handle, body_id))
+
     def CreateJoint(self, joint_def):
         """JointAPI.Create{Distance,Motor,Filter,Prismatic,Revolute,Weld,Wheel}Joint api/Joint.cs:182,324,408,412,555,672,720"""
         out = C.c_int32(-1)

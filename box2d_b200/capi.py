@@ -147,6 +147,9 @@ PROTOS = {
     "create_joint": [_W, C.POINTER(JointDef), C.POINTER(C.c_int32)],
     "destroy_joint": [_W, C.c_int32, C.c_int32],
     "destroy_body": [_W, C.c_int32],
+    "destroy_shape": [_W, C.c_int32, C.c_int32],
+    "shape_set_density": [_W, C.c_int32, C.c_float, C.c_int32],
+    "body_apply_mass_from_shapes": [_W, C.c_int32],
     "joint_set_param": [_W, C.c_int32, C.c_int32, C.c_float],
     "joint_enable": [_W, C.c_int32, C.c_int32, C.c_int32],
     "joint_set_limits": [_W, C.c_int32, C.c_float, C.c_float],

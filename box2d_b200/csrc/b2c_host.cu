@@ -195,7 +195,7 @@ void World::updateBodyMassData(HBody& body) {     // src/Body.cs:255-353
   body.mass = 0; body.inertia = 0; body.invMass = 0; body.invInertia = 0; body.localCenter = mk(0, 0);
   body.minExtent = kHuge; body.maxExtent = 0;
   if (body.type != kDynamicBody) {
-    body.center = body.xf.p; body.center0 = body.center;
+    if (!onDevice_) { body.center = body.xf.p; body.center0 = body.center; }
     if (body.type == kKinematicBody) {
       for (int sid = body.headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) {
         float mn, mx; geomExtent(shapes_[sid].geom, mk(0, 0), &mn, &mx);
@@ -227,11 +227,13 @@ void World::updateBodyMassData(HBody& body) {     // src/Body.cs:255-353
     body.inertia += inertia;
   }
   if (body.inertia > 0.0f) body.invInertia = 1.0f / body.inertia; else { body.inertia = 0; body.invInertia = 0; }
-  V2 oldCenter = body.center;
   body.localCenter = localCenter;
-  body.center = xfPoint(body.xf, localCenter);
-  body.center0 = body.center;
-  body.v = body.v + crossSV(body.w, body.center - oldCenter);
+  if (!onDevice_) {                               // after the upload pose and velocity live on the device: k_body_mass_update
+    V2 oldCenter = body.center;
+    body.center = xfPoint(body.xf, localCenter);
+    body.center0 = body.center;
+    body.v = body.v + crossSV(body.w, body.center - oldCenter);
+  }
   for (int sid = body.headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) {
     float mn, mx; geomExtent(shapes_[sid].geom, localCenter, &mn, &mx);
     body.minExtent = netMin(body.minExtent, mn); body.maxExtent = netMax(body.maxExtent, mx);
@@ -372,41 +374,59 @@ __device__ void destroyContactSerial(const WorldDev& d, int id, int endIndex) { 
 }
 // One CTA: every thread looks for the body's contacts, thread 0 then walks them in the order of the body's contact list (newest first),
 // removes the shapes' proxies and takes the body out of the awake set by swap-remove (api/Body.cs:142-153).
-__global__ void k_destroy_body(WorldDev d, int bodyId, int endIndex) {
-  __shared__ int sCount;
+// Collects the live contacts of a body (shapeId < 0) or of one of its shapes and destroys them in the order of the body's contact list.
+__device__ void destroyContactsOf(const WorldDev& d, int bodyId, int shapeId, int endIndex, int* sCount) {
   Scalars& s = *d.sc;
-  if (threadIdx.x == 0) sCount = 0;
+  if (threadIdx.x == 0) *sCount = 0;
   __syncthreads();
   const int n = s.contactNext;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     if (!(d.cFlags[i] & CF_ALIVE)) continue;
-    int2 b = d.cBody[i];
-    if (b.x == bodyId || b.y == bodyId) { int k = atomicAdd(&sCount, 1); d.opList[k] = i; }
+    bool hit;
+    if (shapeId < 0) { int2 b = d.cBody[i]; hit = b.x == bodyId || b.y == bodyId; }
+    else { int2 sh = d.cShape[i]; hit = sh.x == shapeId || sh.y == shapeId; }
+    if (hit) { int k = atomicAdd(sCount, 1); d.opList[k] = i; }
   }
   __syncthreads();
   if (threadIdx.x != 0) return;
-  const int count = sCount;
+  const int count = *sCount;
   for (int i = 1; i < count; i++) {               // insertion sort, descending creation stamp (a body has tens of contacts)
     int id = d.opList[i]; uint32_t st = d.cStamp[id]; int j = i - 1;
     while (j >= 0 && d.cStamp[d.opList[j]] < st) { d.opList[j + 1] = d.opList[j]; j--; }
     d.opList[j + 1] = id;
   }
-  for (int i = 0; i < count; i++) destroyContactSerial(d, d.opList[i], endIndex);     // DestroyBodyContacts src/Body.cs:232-244
-  for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
-    int key = d.shapes[sid].proxyKey;
-    if (key == -1) continue;
-    const TreeDev& t = d.trees[key & 3];
-    const int proxyId = key >> 2;
-    if (t.moved[proxyId]) {                       // BroadPhase.UnBufferMove src/BroadPhase.cs:60-71
-      t.moved[proxyId] = 0;
-      for (int i = 0; i < s.moveCount; i++) if (d.moveArray[i] == key) { d.moveArray[i] = d.moveArray[s.moveCount - 1]; s.moveCount--; break; }
-    }
-    TreeView v{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta};
-    tvRemoveLeaf(v, proxyId); tvFreeNode(v, proxyId); t.meta[3]--;       // DynamicTree.DestroyProxy src/DynamicTree.cs:460-468
-    if ((key & 3) == kStaticBody) s.staticRanksValid = 0;
-    d.shapes[sid].proxyKey = -1;
-    d.shapeAABB[sid] = make_float4(0, 0, 0, 0); d.shapeFat[sid] = make_float4(0, 0, 0, 0);
+  for (int i = 0; i < count; i++) destroyContactSerial(d, d.opList[i], endIndex);     // DestroyBodyContacts src/Body.cs:232-244, src/Shape.cs:235-244
+}
+__device__ void destroyProxySerial(const WorldDev& d, int sid) {      // Shape.DestroyProxy src/Shape.cs:128-131 -> BroadPhase.DestroyProxy src/BroadPhase.cs:80-86
+  Scalars& s = *d.sc;
+  int key = d.shapes[sid].proxyKey;
+  if (key == -1) return;
+  const TreeDev& t = d.trees[key & 3];
+  const int proxyId = key >> 2;
+  if (t.moved[proxyId]) {                         // BroadPhase.UnBufferMove src/BroadPhase.cs:60-71
+    t.moved[proxyId] = 0;
+    for (int i = 0; i < s.moveCount; i++) if (d.moveArray[i] == key) { d.moveArray[i] = d.moveArray[s.moveCount - 1]; s.moveCount--; break; }
   }
+  TreeView v{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta};
+  tvRemoveLeaf(v, proxyId); tvFreeNode(v, proxyId); t.meta[3]--;         // DynamicTree.DestroyProxy src/DynamicTree.cs:460-468
+  if ((key & 3) == kStaticBody) s.staticRanksValid = 0;
+  d.shapes[sid].proxyKey = -1;
+  d.shapeAABB[sid] = make_float4(0, 0, 0, 0); d.shapeFat[sid] = make_float4(0, 0, 0, 0);
+}
+__global__ void k_destroy_shape(WorldDev d, int shapeId, int bodyId, int prevShapeId, int nextShapeId, int endIndex) {   // DestroyShapeInternal src/Shape.cs:219-272
+  __shared__ int sCount;
+  destroyContactsOf(d, bodyId, shapeId, endIndex, &sCount);
+  if (threadIdx.x != 0) return;
+  destroyProxySerial(d, shapeId);
+  if (prevShapeId != -1) d.shapes[prevShapeId].nextShapeId = nextShapeId;
+  else d.bodyHeadShape[bodyId] = nextShapeId;
+}
+__global__ void k_destroy_body(WorldDev d, int bodyId, int endIndex) {
+  __shared__ int sCount;
+  Scalars& s = *d.sc;
+  destroyContactsOf(d, bodyId, -1, endIndex, &sCount);
+  if (threadIdx.x != 0) return;
+  for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) destroyProxySerial(d, sid);
   d.bodyHeadShape[bodyId] = -1;
   int sim = d.bodySim[bodyId];
   if (sim >= 0) {                                 // bodySims / bodyStates RemoveSwap; the host lowers awakeCount (a kernel parameter) after this launch
@@ -488,6 +508,44 @@ int World::destroyBody(int bodyId) {             // BodyAPI.DestroyBody api/Body
   b.id = -1; b.simIndex = -1; b.headShapeId = -1; b.headJointKey = -1; b.jointCount = 0;
   eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false;
   return B2C_OK;
+}
+
+__global__ void k_body_mass_update(WorldDev d, int bodyId, int type, float invMass, float invInertia, V2 localCenter, float minExtent, float maxExtent);
+int World::applyMassFromShapes(int bodyId) {     // BodyAPI.ApplyMassFromShapes api/Body.cs:617-621 -> UpdateBodyMassData src/Body.cs:255-353
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  HBody& b = bodies_[bodyId];
+  updateBodyMassData(b);
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_body_mass_update<<<1, 1, 0, stream_>>>(d_, bodyId, b.type, b.invMass, b.invInertia, b.localCenter, b.minExtent, b.maxExtent);
+  CK(cudaGetLastError());
+  bodiesFetched_ = false; movesFetched_ = false;
+  return B2C_OK;
+}
+int World::setShapeDensity(int shapeId, float density, bool updateBodyMass) {   // ShapeAPI.SetDensity api/Shape.cs:95-103
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  HShape& s = shapes_[shapeId];
+  if (density == s.density) return B2C_OK;
+  s.density = density;
+  return updateBodyMass ? applyMassFromShapes(s.bodyId) : B2C_OK;
+}
+int World::destroyShape(int shapeId, bool updateBodyMass) {      // ShapeAPI.DestroyShape api/Shape.cs:48-56, DestroyShapeInternal src/Shape.cs:219-272
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "destroy_shape before the first step is not supported in this build (the world is still being assembled on the host)");
+  HShape& s = shapes_[shapeId];
+  HBody& body = bodies_[s.bodyId];
+  const int prev = s.prevShapeId, next = s.nextShapeId, bodyId = s.bodyId;
+  if (prev != -1) shapes_[prev].nextShapeId = next;
+  if (next != -1) shapes_[next].prevShapeId = prev;
+  if (shapeId == body.headShapeId) body.headShapeId = next;
+  body.shapeCount--;
+  CK(cudaSetDevice(device_));
+  k_destroy_shape<<<1, 256, 0, stream_>>>(d_, shapeId, bodyId, prev, next, endIndex_);
+  CK(cudaGetLastError());
+  s.proxyKey = -1; s.id = -1;
+  shapeIds_.release(shapeId);
+  eventsFetched_ = false;
+  return updateBodyMass ? applyMassFromShapes(bodyId) : B2C_OK;
 }
 
 // Joint setters (api/Joint.cs): the host mirror is patched before the upload, the device record after it (stream-ordered, one thread).
@@ -863,6 +921,35 @@ __global__ void k_body_mass_data(WorldDev d, int bodyId, float mass, float inert
   float4 pose = d.simPose[sim]; pose.x = center.x; pose.y = center.y; d.simPose[sim] = pose;
   float4 pose0 = d.simPose0[sim]; pose0.x = center.x; pose0.y = center.y; d.simPose0[sim] = pose0;
 }
+// World.UpdateBodyMassData src/Body.cs:255-353 after the upload: the host sums the shapes (geometry and densities never change on the
+// device), this patch does the part that depends on the body's current pose and velocity.
+__global__ void k_body_mass_update(WorldDev d, int bodyId, int type, float invMass, float invInertia, V2 localCenter, float minExtent, float maxExtent) {
+  float4 xf4 = d.bodyXf[bodyId];
+  int sim = d.bodySim[bodyId];
+  if (type != kDynamicBody) {                      // :262-279
+    d.bodyMass[bodyId] = make_float4(0, 0, 0, 0);
+    d.bodyCenter[bodyId] = make_float2(xf4.x, xf4.y);
+    if (sim < 0) return;
+    float4 m = d.simMass[sim]; m.x = 0; m.y = 0; d.simMass[sim] = m;
+    d.simLocal[sim] = make_float4(0, 0, minExtent, maxExtent);
+    float4 pose = d.simPose[sim]; pose.x = xf4.x; pose.y = xf4.y; d.simPose[sim] = pose;
+    float4 pose0 = d.simPose0[sim]; pose0.x = xf4.x; pose0.y = xf4.y; d.simPose0[sim] = pose0;
+    return;
+  }
+  V2 center = xfPoint(mkXf(mk(xf4.x, xf4.y), mkRot(xf4.z, xf4.w)), localCenter);
+  d.bodyMass[bodyId] = make_float4(invMass, invInertia, localCenter.x, localCenter.y);
+  d.bodyCenter[bodyId] = make_float2(center.x, center.y);
+  if (sim < 0) return;
+  float4 m = d.simMass[sim]; m.x = invMass; m.y = invInertia; d.simMass[sim] = m;
+  d.simLocal[sim] = make_float4(localCenter.x, localCenter.y, minExtent, maxExtent);
+  float4 pose = d.simPose[sim];
+  V2 oldCenter = mk(pose.x, pose.y);
+  pose.x = center.x; pose.y = center.y; d.simPose[sim] = pose;
+  float4 pose0 = d.simPose0[sim]; pose0.x = center.x; pose0.y = center.y; d.simPose0[sim] = pose0;
+  float4 st = d.st0[sim];
+  V2 dv = crossSV(st.z, center - oldCenter);      // :338-339
+  st.x = st.x + dv.x; st.y = st.y + dv.y; d.st0[sim] = st;
+}
 __global__ void k_body_motion_locks(WorldDev d, int bodyId, uint32_t newFlags) {
   const uint32_t allLocks = kLockLinearX | kLockLinearY | kLockAngularZ;
   uint32_t bf = d.bodyFlags[bodyId];
@@ -1124,7 +1211,7 @@ int World::getJointEvents(const int** ids, int* count) {
   if (fetch(flags, d_.jointEventFlag, joints_.size(), stream_)) return fail(B2C_E_CUDA, "joint event copy failed");
   CK(cudaStreamSynchronize(stream_));
   int n = 0;
-  for (size_t i = 0; i < flags.size(); i++) if (flags[i]) hJointEvents_[n++] = (int)i;
+  for (size_t i = 0; i < flags.size(); i++) if (flags[i] && joints_[i].id != -1) hJointEvents_[n++] = (int)i;   // a destroyed joint keeps its last flag: prepare only clears live joints
   *count = n;
   return B2C_OK;
 }

@@ -61,6 +61,9 @@ class World {
   int createJoint(const B2CJointDef& def, int* jointId);
   int destroyJoint(int jointId);
   int destroyBody(int bodyId);
+  int destroyShape(int shapeId, bool updateBodyMass);
+  int setShapeDensity(int shapeId, float density, bool updateBodyMass);
+  int applyMassFromShapes(int bodyId);
   int uploadJointLists();
   int jointOp(int jointId, int patch, int which, float a, float b);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }

@@ -174,6 +174,14 @@ int32_t b2cuda_create_joint(B2CWorld* world, const B2CJointDef* def, int32_t* jo
  * stepped (destroy_joint also before). Creating bodies, shapes or joints after the first step stays unsupported (B2C_E_UNSUPPORTED). */
 int32_t b2cuda_destroy_joint(B2CWorld* world, int32_t jointId, int32_t wakeAttached);
 int32_t b2cuda_destroy_body(B2CWorld* world, int32_t bodyId);
+/* ShapeAPI.DestroyShape api/Shape.cs:48-56 (DestroyShapeInternal src/Shape.cs:219-272: the shape leaves its body's list, its proxy leaves the tree,
+ * the body's contacts that involve it are destroyed in contact-list order), ShapeAPI.SetDensity api/Shape.cs:95-103 and
+ * BodyAPI.ApplyMassFromShapes api/Body.cs:617-621. updateBodyMass runs World.UpdateBodyMassData src/Body.cs:255-353: mass, inertia, local centre
+ * and extents are summed over the remaining shapes, the centre of mass moves and the linear velocity takes w x (newCentre - oldCentre).
+ * destroy_shape needs a stepped world (like destroy_body); the other two also work while the world is being assembled. */
+int32_t b2cuda_destroy_shape(B2CWorld* world, int32_t shapeId, int32_t updateBodyMass);
+int32_t b2cuda_shape_set_density(B2CWorld* world, int32_t shapeId, float density, int32_t updateBodyMass);
+int32_t b2cuda_body_apply_mass_from_shapes(B2CWorld* world, int32_t bodyId);
 /* Joint mutators — api/Joint.cs. One generic entry per shape of setter; `param` selects the field (B2C_JP_*). Wrong joint type for a
  * field returns B2C_E_INVALID (the reference asserts the type, api/Joint.cs:169-179). After the first step each call is a one-thread
  * patch of the device joint record, ordered on the world's stream (no read-back, no synchronisation).

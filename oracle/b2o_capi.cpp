@@ -78,6 +78,9 @@ int32_t b2o_body_set_motion_locks(World* w, int32_t id, int32_t lx, int32_t ly, 
 int32_t b2o_shape_set_surface_material(World* w, int32_t id, float f, float r, float rr, float ts) { w->SetSurfaceMaterial(id, f, r, rr, ts); return 0; }
 int32_t b2o_destroy_joint(World* w, int32_t id, int32_t) { if (id < 0 || id >= (int)w->joints.size() || w->joints[id].jointId != id) return -1; w->DestroyJoint(id); return 0; }
 int32_t b2o_destroy_body(World* w, int32_t id) { if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id != id) return -1; w->DestroyBody(id); return 0; }
+int32_t b2o_destroy_shape(World* w, int32_t id, int32_t upd) { if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1; w->DestroyShape(id, upd != 0); return 0; }
+int32_t b2o_shape_set_density(World* w, int32_t id, float density, int32_t upd) { if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1; w->SetDensity(id, density, upd != 0); return 0; }
+int32_t b2o_body_apply_mass_from_shapes(World* w, int32_t id) { if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id != id) return -1; w->ApplyMassFromShapes(id); return 0; }
 int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
 int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }
 int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAngularVelocity(id, x); return 0; }

@@ -409,6 +409,37 @@ void World::DestroyBody(int bodyId) {           // api/Body.cs:106-160 (awake or
   body.setIndex = -1; body.localIndex = -1; body.id = -1;
 }
 
+void World::DestroyShape(int shapeId, bool updateBodyMass) {      // api/Shape.cs:48-56, DestroyShapeInternal src/Shape.cs:219-272 (no sensors)
+  Shape& shape = shapes[shapeId];
+  Body& body = bodies[shape.bodyId];
+  if (shape.prevShapeId != -1) shapes[shape.prevShapeId].nextShapeId = shape.nextShapeId;
+  if (shape.nextShapeId != -1) shapes[shape.nextShapeId].prevShapeId = shape.prevShapeId;
+  if (shapeId == body.headShapeId) body.headShapeId = shape.nextShapeId;
+  body.shapeCount--;
+  if (shape.proxyKey != -1) {                    // Shape.DestroyProxy src/Shape.cs:128-131
+    UnBufferMove(shape.proxyKey);
+    trees[ProxyType(shape.proxyKey)].DestroyProxy(ProxyId(shape.proxyKey));
+    shape.proxyKey = -1;
+  }
+  int contactKey = body.headContactKey;
+  while (contactKey != -1) {
+    int contactId = contactKey >> 1, edgeIndex = contactKey & 1;
+    Contact& contact = contacts[contactId];
+    contactKey = edgeIndex == 1 ? contact.edge1.nextKey : contact.edge0.nextKey;
+    if (contact.shapeIdA == shapeId || contact.shapeIdB == shapeId) DestroyContact(contact);
+  }
+  shapeIdPool.FreeId(shapeId);
+  shape.id = -1;
+  if (updateBodyMass) UpdateBodyMassData(body);
+}
+void World::SetDensity(int shapeId, float density, bool updateBodyMass) {      // api/Shape.cs:95-103
+  Shape& shape = shapes[shapeId];
+  if (density == shape.density) return;
+  shape.density = density;
+  if (updateBodyMass) UpdateBodyMassData(bodies[shape.bodyId]);
+}
+void World::ApplyMassFromShapes(int bodyId) { UpdateBodyMassData(bodies[bodyId]); }   // api/Body.cs:617-621
+
 void World::DestroyContactsBetweenBodies(Body& bodyA, Body& bodyB) {    // src/Joint.cs:155-180
   int contactKey, otherBodyId;
   if (bodyA.contactCount < bodyB.contactCount) { contactKey = bodyA.headContactKey; otherBodyId = bodyB.id; }

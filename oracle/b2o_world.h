@@ -210,6 +210,9 @@ class World {
   int CreateJoint(const JointDef& def);
   void DestroyJoint(int jointId);          // JointAPI.DestroyJoint api/Joint.cs:9-17 -> DestroyJointInternal src/Joint.cs:297-375
   void DestroyBody(int bodyId);            // BodyAPI.DestroyBody api/Body.cs:106-160
+  void DestroyShape(int shapeId, bool updateBodyMass);             // ShapeAPI.DestroyShape api/Shape.cs:48-56 -> DestroyShapeInternal src/Shape.cs:219-272
+  void SetDensity(int shapeId, float density, bool updateBodyMass);  // ShapeAPI.SetDensity api/Shape.cs:95-103
+  void ApplyMassFromShapes(int bodyId);                              // BodyAPI.ApplyMassFromShapes api/Body.cs:617-621
   void UnBufferMove(int proxyKey);         // src/BroadPhase.cs:60-71
   void SetTargetTransform(int bodyId, const Transform& target, float timeStep);
   void SetMassData(int bodyId, float mass, float rotationalInertia, Vec2 center);

@@ -533,3 +533,32 @@ def test_destroy_rejects_stale_ids_and_reports_counts():
         assert len(cuda.GetBodyMoveEvents()) == 9
     finally:
         cuda.Destroy()
+
+
+def test_destroy_shapes_and_mass_updates_bit_exact():
+    """ShapeAPI.DestroyShape (api/Shape.cs:48-56), ShapeAPI.SetDensity (:95-103) and BodyAPI.ApplyMassFromShapes (api/Body.cs:617-621) between
+    steps on the mixed scene: second and first shapes of compound bodies (with and without the mass update), a static terrain piece, a
+    kinematic paddle's capsule, a body left without any shape."""
+    def mutate(w, step):
+        if step == 5:
+            w.DestroyShape(7, True)            # body 2: the extra circle
+            w.DestroyShape(14, True)           # body 9: its main shape, the small circle stays
+            w.DestroyShape(22, False)          # body 16: mass data left as it was
+        elif step == 9:
+            w.DestroyShape(3, True)            # the static rounded box
+            w.DestroyShape(5, True)            # the paddle's capsule
+        elif step == 12:
+            w.SetDensity(8, 3.0, True)
+            w.SetDensity(16, 0.25, True)
+            w.SetDensity(9, 5.0, False)
+        elif step == 14:
+            w.ApplyMassFromShapes(4)           # picks up shape 9's new density
+            w.ApplyMassFromShapes(0)
+            w.ApplyMassFromShapes(1)
+        elif step == 16:
+            w.DestroyShape(8, True)            # body 3 has no shape left: zero mass, it hangs where it is
+        elif step == 20:
+            w.DestroyBody(2)
+            w.DestroyBody(3)
+    res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=40, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
