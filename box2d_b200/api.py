@@ -262,6 +262,22 @@ class World:
         """BodyAPI.ApplyMassFromShapes api/Body.cs:617-621"""
         self._check(self.fns["body_apply_mass_from_shapes"](self.handle, body_id))
 
+    def Shape_EnableContactEvents(self, shape_id, flag):
+        """ShapeAPI.EnableContactEvents api/Shape.cs:182-186"""
+        self._check(self.fns["shape_enable_events"](self.handle, shape_id, capi.SHAPE_CONTACT_EVENTS, int(bool(flag))))
+
+    def Shape_EnableHitEvents(self, shape_id, flag):
+        """ShapeAPI.EnableHitEvents api/Shape.cs:205-209"""
+        self._check(self.fns["shape_enable_events"](self.handle, shape_id, capi.SHAPE_HIT_EVENTS, int(bool(flag))))
+
+    def Body_EnableContactEvents(self, body_id, flag):
+        """BodyAPI.EnableContactEvents api/Body.cs:848-858"""
+        self._check(self.fns["body_enable_events"](self.handle, body_id, capi.SHAPE_CONTACT_EVENTS, int(bool(flag))))
+
+    def Body_EnableHitEvents(self, body_id, flag):
+        """BodyAPI.EnableHitEvents api/Body.cs:862-872"""
+        self._check(self.fns["body_enable_events"](self.handle, body_id, capi.SHAPE_HIT_EVENTS, int(bool(flag))))
+
     def CreateJoint(self, joint_def):
         """JointAPI.Create{Distance,Motor,Filter,Prismatic,Revolute,Weld,Wheel}Joint api/Joint.cs:182,324,408,412,555,672,720"""
         out = C.c_int32(-1)

@@ -66,6 +66,7 @@ class RevoluteJointDef(C.Structure):
  JP_MOTOR_SPEED, JP_MAX_MOTOR, JP_LENGTH, JP_LOWER_SPRING_FORCE, JP_UPPER_SPRING_FORCE, JP_ANGULAR_HERTZ, JP_ANGULAR_DAMPING_RATIO,
  JP_LINEAR_VELOCITY_X, JP_LINEAR_VELOCITY_Y, JP_ANGULAR_VELOCITY, JP_MAX_VELOCITY_FORCE, JP_MAX_VELOCITY_TORQUE, JP_MAX_SPRING_FORCE,
  JP_MAX_SPRING_TORQUE) = range(21)
+SHAPE_CONTACT_EVENTS, SHAPE_HIT_EVENTS = 0, 1
 JOINT_SPRING, JOINT_LIMIT, JOINT_MOTOR_SWITCH = range(3)
 JOINT_DISTANCE, JOINT_FILTER, JOINT_MOTOR, JOINT_PRISMATIC, JOINT_REVOLUTE, JOINT_WELD, JOINT_WHEEL = range(7)
 
@@ -150,6 +151,8 @@ PROTOS = {
     "destroy_shape": [_W, C.c_int32, C.c_int32],
     "shape_set_density": [_W, C.c_int32, C.c_float, C.c_int32],
     "body_apply_mass_from_shapes": [_W, C.c_int32],
+    "shape_enable_events": [_W, C.c_int32, C.c_int32, C.c_int32],
+    "body_enable_events": [_W, C.c_int32, C.c_int32, C.c_int32],
     "joint_set_param": [_W, C.c_int32, C.c_int32, C.c_float],
     "joint_enable": [_W, C.c_int32, C.c_int32, C.c_int32],
     "joint_set_limits": [_W, C.c_int32, C.c_float, C.c_float],

@@ -273,7 +273,7 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_joint after the first step is not supported in this build");
   if (def.type < B2C_JOINT_DISTANCE || def.type > B2C_JOINT_WHEEL) return fail(B2C_E_INVALID, "bad joint type");
   int nb = (int)bodies_.size();
-  if (def.bodyIdA < 0 || def.bodyIdA >= nb || def.bodyIdB < 0 || def.bodyIdB >= nb) return fail(B2C_E_INVALID, "bad body id");
+  if (def.bodyIdA < 0 || def.bodyIdA >= nb || def.bodyIdB < 0 || def.bodyIdB >= nb || bodies_[def.bodyIdA].id != def.bodyIdA || bodies_[def.bodyIdB].id != def.bodyIdB) return fail(B2C_E_INVALID, "bad body id");
   HBody& bodyA = bodies_[def.bodyIdA]; HBody& bodyB = bodies_[def.bodyIdB];
   if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) return fail(B2C_E_UNSUPPORTED, "joint between two non-dynamic bodies (static set) is not supported");
   int id = jointIds_.alloc();
@@ -597,7 +597,7 @@ __global__ void k_set_transform(WorldDev d, int bodyId, V2 p, Rot q) {
 }
 
 int World::setTransform(int bodyId, V2 p, Rot q) {          // api/Body.cs:293-325
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   if (onDevice_) {
     CK(cudaSetDevice(device_));
     k_set_transform<<<1, 1, 0, stream_>>>(d_, bodyId, p, q);
@@ -808,7 +808,7 @@ int World::synchronize() {
 
 // ---- mutators that patch device rows directly (api/Body.cs:359-545) ----
 int World::setLinearVelocity(int bodyId, V2 v) {
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   HBody& b = bodies_[bodyId];
   if (b.type == kStaticBody) return B2C_OK;
   if (!onDevice_) { b.v = v; return B2C_OK; }
@@ -819,7 +819,7 @@ int World::setLinearVelocity(int bodyId, V2 v) {
   return B2C_OK;
 }
 int World::setAngularVelocity(int bodyId, float w) {
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   HBody& b = bodies_[bodyId];
   if (b.type == kStaticBody) return B2C_OK;
   if (!onDevice_) { b.w = w; return B2C_OK; }
@@ -854,7 +854,7 @@ __global__ void k_body_op(WorldDev d, int op, int sim, V2 a, V2 point, float max
   }
 }
 int World::bodyOp(int bodyId, int op, V2 a, V2 point) {
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   HBody& b = bodies_[bodyId];
   const bool tuning = op == OP_LINEAR_DAMPING || op == OP_ANGULAR_DAMPING || op == OP_GRAVITY_SCALE;
   if (!tuning && op != OP_CLEAR_FORCES && b.type != kDynamicBody) return B2C_OK;
@@ -969,7 +969,7 @@ __global__ void k_body_motion_locks(WorldDev d, int bodyId, uint32_t newFlags) {
 __global__ void k_shape_material(WorldDev d, int shapeId, float4 material) { d.shapes[shapeId].material = material; }
 
 int World::setTargetTransform(int bodyId, Xf target, float timeStep) {
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   HBody& b = bodies_[bodyId];
   if (b.type == kStaticBody || timeStep <= 0.0f) return B2C_OK;
   if (!onDevice_) {
@@ -986,7 +986,7 @@ int World::setTargetTransform(int bodyId, Xf target, float timeStep) {
   return B2C_OK;
 }
 int World::setMassData(int bodyId, float mass, float inertia, V2 center) {
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   HBody& b = bodies_[bodyId];
   b.mass = mass; b.inertia = inertia;
   if (!onDevice_) {
@@ -1000,7 +1000,7 @@ int World::setMassData(int bodyId, float mass, float inertia, V2 center) {
   return B2C_OK;
 }
 int World::setMotionLocks(int bodyId, bool lx, bool ly, bool az) {
-  if (bodyId < 0 || bodyId >= (int)bodies_.size()) return fail(B2C_E_INVALID, "bad body id");
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   HBody& b = bodies_[bodyId];
   const uint32_t allLocks = kLockLinearX | kLockLinearY | kLockAngularZ;
   uint32_t newFlags = (lx ? kLockLinearX : 0u) | (ly ? kLockLinearY : 0u) | (az ? kLockAngularZ : 0u);
@@ -1027,6 +1027,27 @@ int World::setSurfaceMaterial(int shapeId, float friction, float restitution, fl
   CK(cudaSetDevice(device_));
   k_shape_material<<<1, 1, 0, stream_>>>(d_, shapeId, make_float4(friction, restitution, rolling, tangentSpeed));
   CK(cudaGetLastError());
+  return B2C_OK;
+}
+
+// ShapeAPI.EnableContactEvents api/Shape.cs:182-186 / EnableHitEvents :205-209: the flag is read when a contact is created
+// (src/Contact.cs:188) or starts touching (:386), contacts that exist keep what they have.
+__global__ void k_shape_flag(WorldDev d, int shapeId, uint32_t bit, int on) { uint32_t f = d.shapes[shapeId].flags; d.shapes[shapeId].flags = on ? (f | bit) : (f & ~bit); }
+int World::shapeEnableEvents(int shapeId, int which, bool flag) {
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  if (which != B2C_SHAPE_CONTACT_EVENTS && which != B2C_SHAPE_HIT_EVENTS) return fail(B2C_E_INVALID, "bad event selector");
+  const uint32_t bit = which == B2C_SHAPE_CONTACT_EVENTS ? SF_CONTACT_EVENTS : SF_HIT_EVENTS;
+  HShape& sh = shapes_[shapeId];
+  sh.flags = flag ? (sh.flags | bit) : (sh.flags & ~bit);
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_shape_flag<<<1, 1, 0, stream_>>>(d_, shapeId, bit, flag ? 1 : 0);
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
+int World::bodyEnableEvents(int bodyId, int which, bool flag) {     // BodyAPI.EnableContactEvents api/Body.cs:848-858 / EnableHitEvents :862-872
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  for (int sid = bodies_[bodyId].headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) { int rc = shapeEnableEvents(sid, which, flag); if (rc) return rc; }
   return B2C_OK;
 }
 

@@ -64,6 +64,8 @@ class World {
   int destroyShape(int shapeId, bool updateBodyMass);
   int setShapeDensity(int shapeId, float density, bool updateBodyMass);
   int applyMassFromShapes(int bodyId);
+  int shapeEnableEvents(int shapeId, int which, bool flag);
+  int bodyEnableEvents(int bodyId, int which, bool flag);
   int uploadJointLists();
   int jointOp(int jointId, int patch, int which, float a, float b);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }

@@ -182,6 +182,13 @@ int32_t b2cuda_destroy_body(B2CWorld* world, int32_t bodyId);
 int32_t b2cuda_destroy_shape(B2CWorld* world, int32_t shapeId, int32_t updateBodyMass);
 int32_t b2cuda_shape_set_density(B2CWorld* world, int32_t shapeId, float density, int32_t updateBodyMass);
 int32_t b2cuda_body_apply_mass_from_shapes(B2CWorld* world, int32_t bodyId);
+/* ShapeAPI.EnableContactEvents api/Shape.cs:182-186 / EnableHitEvents :205-209 and the per-body loops BodyAPI.EnableContactEvents
+ * api/Body.cs:848-858 / EnableHitEvents :862-872. The flag is sampled when a contact is created (contact events) or starts touching
+ * (hit events); existing contacts keep theirs, as in the reference. */
+#define B2C_SHAPE_CONTACT_EVENTS 0
+#define B2C_SHAPE_HIT_EVENTS 1
+int32_t b2cuda_shape_enable_events(B2CWorld* world, int32_t shapeId, int32_t which, int32_t flag);
+int32_t b2cuda_body_enable_events(B2CWorld* world, int32_t bodyId, int32_t which, int32_t flag);
 /* Joint mutators — api/Joint.cs. One generic entry per shape of setter; `param` selects the field (B2C_JP_*). Wrong joint type for a
  * field returns B2C_E_INVALID (the reference asserts the type, api/Joint.cs:169-179). After the first step each call is a one-thread
  * patch of the device joint record, ordered on the world's stream (no read-back, no synchronisation).

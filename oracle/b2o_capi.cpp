@@ -81,6 +81,16 @@ int32_t b2o_destroy_body(World* w, int32_t id) { if (id < 0 || id >= (int)w->bod
 int32_t b2o_destroy_shape(World* w, int32_t id, int32_t upd) { if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1; w->DestroyShape(id, upd != 0); return 0; }
 int32_t b2o_shape_set_density(World* w, int32_t id, float density, int32_t upd) { if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1; w->SetDensity(id, density, upd != 0); return 0; }
 int32_t b2o_body_apply_mass_from_shapes(World* w, int32_t id) { if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id != id) return -1; w->ApplyMassFromShapes(id); return 0; }
+int32_t b2o_shape_enable_events(World* w, int32_t id, int32_t which, int32_t flag) {      // api/Shape.cs:182-186, :205-209
+  if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id || which < 0 || which > 1) return -1;
+  if (which == 0) w->shapes[id].enableContactEvents = flag != 0; else w->shapes[id].enableHitEvents = flag != 0;
+  return 0;
+}
+int32_t b2o_body_enable_events(World* w, int32_t id, int32_t which, int32_t flag) {       // api/Body.cs:848-872
+  if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id != id || which < 0 || which > 1) return -1;
+  for (int sid = w->bodies[id].headShapeId; sid != -1; sid = w->shapes[sid].nextShapeId) b2o_shape_enable_events(w, sid, which, flag);
+  return 0;
+}
 int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
 int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }
 int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAngularVelocity(id, x); return 0; }

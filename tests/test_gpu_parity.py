@@ -527,6 +527,11 @@ def test_destroy_rejects_stale_ids_and_reports_counts():
             cuda.DestroyJoint(0)
         with pytest.raises(Exception):
             cuda.GetTransform(3)
+        for call in (lambda: cuda.SetTransform(3, (0.0, 9.0), (1.0, 0.0)), lambda: cuda.SetLinearVelocity(3, (1.0, 0.0)),
+                     lambda: cuda.SetMassData(3, 1.0, 1.0, (0.0, 0.0)), lambda: cuda.ApplyMassFromShapes(3), lambda: cuda.DestroyShape(3, True),
+                     lambda: cuda.SetSurfaceMaterial(3, 0.5, 0.0, 0.0, 0.0), lambda: cuda.Shape_EnableHitEvents(3, True)):
+            with pytest.raises(Exception):
+                call()                                              # body 3 and its shape 3 are gone: every mutator says so
         cuda.Step(1.0 / 60.0, 4)
         c = cuda.GetCounters()
         assert c.bodyCount == 10 and c.awakeBodyCount == 9 and c.shapeCount == 10
@@ -561,4 +566,26 @@ def test_destroy_shapes_and_mass_updates_bit_exact():
             w.DestroyBody(2)
             w.DestroyBody(3)
     res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=40, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_event_enable_flags_between_steps_bit_exact():
+    """ShapeAPI/BodyAPI.EnableContactEvents and EnableHitEvents (api/Shape.cs:182-209, api/Body.cs:848-872) toggled between steps: contacts
+    created afterwards sample the new flag, contacts that exist keep theirs, so begin/end event lists must still agree exactly."""
+    wd = scenes.world_def()
+    wd.hitEventThreshold = 0.5
+
+    def mutate(w, step):
+        if step == 2:
+            for sid in range(6, 30, 2):
+                w.Shape_EnableContactEvents(sid, False)
+            w.Body_EnableContactEvents(0, False)          # the ground: its four shapes
+        elif step == 8:
+            for sid in range(6, 30, 4):
+                w.Shape_EnableContactEvents(sid, True)
+                w.Shape_EnableHitEvents(sid, True)
+            w.Body_EnableHitEvents(1, True)
+        elif step == 20:
+            w.Body_EnableContactEvents(0, True)
+    res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=50, world_def=wd, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
