@@ -126,8 +126,68 @@ void World::bufferMove(int key) {                 // src/BroadPhase.cs:56-59
   if (!m[id]) { m[id] = 1; moveArray_.push_back(key); }
 }
 
+// ---- creation after the upload (BodyAPI.CreateBody api/Body.cs:16-105, ShapeAPI.CreateShape api/Shape.cs:8-24) -----------------------------
+// The host allocates the id from its LIFO pool and fills its mirror as before; one thread then writes the body's rows (appended to the
+// awake rows for a moving body) or creates the shape's proxy with the tree code the host used before the upload — free-list order included:
+// the step's tree rebuild hands the doomed internal nodes straight to the new internal nodes and never touches the free list, so the
+// node a new leaf receives is the one the reference's tree would give it.
+struct BodyRows {
+  float4 st0, st1, simMass, simForce, simPose, simLocal, simPose0, bodyXf, bodyMass; float2 bodyCenter;
+  uint32_t flags; int type, sim; float sleepThreshold;
+};
+__global__ void k_create_body(WorldDev d, int id, BodyRows r) {
+  d.bodyXf[id] = r.bodyXf; d.bodyMass[id] = r.bodyMass; d.bodyCenter[id] = r.bodyCenter; d.bodySim[id] = r.sim; d.bodyType[id] = r.type;
+  d.bodyHeadShape[id] = -1; d.bodyHeadJoint[id] = -1; d.bodyJointCount[id] = 0; d.bodyColorMask[id] = 0; d.bodyMinOp[id] = 0x7f7f7f7f;
+  d.bodySleepThreshold[id] = r.sleepThreshold; d.bodyFlags[id] = r.flags;
+  if (r.sim < 0) return;
+  const int i = r.sim;
+  d.st0[i] = r.st0; d.st1[i] = r.st1; d.simMass[i] = r.simMass; d.simForce[i] = r.simForce; d.simPose[i] = r.simPose; d.simLocal[i] = r.simLocal;
+  d.simPose0[i] = r.simPose0; d.simFlags[i] = r.flags; d.simBodyId[i] = id;
+  d.sc->graphDirty = 1;
+}
+// growFrom/growTo: AllocateNode's growth branch (src/DynamicTree.cs:56-66) decided by the host, which knows node count and capacity
+__device__ void treeGrowSerial(const TreeDev& t, int from, int to) {
+  if (from >= to) return;
+  for (int i = from; i < to - 1; i++) t.parent[i] = i + 1;
+  t.parent[to - 1] = -1;
+  t.meta[2] = from;
+}
+__global__ void k_create_shape(WorldDev d, int shapeId, ShapeDev row, int type, int forceMove, int grow0From, int grow0To, int grow1From, int grow1To) {
+  Scalars& s = *d.sc;
+  const int bodyId = row.bodyId;
+  float4 xf4 = d.bodyXf[bodyId];
+  Xf xf = mkXf(mk(xf4.x, xf4.y), mkRot(xf4.z, xf4.w));
+  Box aabb = boxGrow(geomAABB(row.geom, xf), kSpeculativeDistance);                       // Shape.UpdateShapeAABBs src/Shape.cs:64-75
+  Box fat = boxGrow(aabb, type == kStaticBody ? kSpeculativeDistance : kAABBMargin);
+  const TreeDev& t = d.trees[type];
+  TreeView v{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta};
+  treeGrowSerial(t, grow0From, grow0To);
+  int id = tvAllocNode(v);                                                                 // DynamicTree.CreateProxy src/DynamicTree.cs:443-458
+  if (id < 0) { atomicOr(&s.errorFlags, (int)ERR_TREE); return; }
+  tvSetBox(v, id, fat); t.user[id] = shapeId; t.cat[id] = row.categoryBits; t.hf[id] = tvPackHF(0, NODE_ALLOCATED | NODE_LEAF); t.moved[id] = 0;
+  treeGrowSerial(t, grow1From, grow1To);
+  tvInsertLeaf(v, id, true); t.meta[3]++;
+  const int key = (id << 2) | type;
+  if (type != kStaticBody || forceMove) {                                                 // BroadPhase.CreateProxy src/BroadPhase.cs:71-79 -> BufferMove :56-59
+    if (s.moveCount < d.moveCapacity) { t.moved[id] = 1; d.moveArray[s.moveCount++] = key; } else atomicOr(&s.errorFlags, (int)ERR_PAIR_CAPACITY);
+  }
+  if (type == kStaticBody) s.staticRanksValid = 0;
+  row.proxyKey = key; row.nextShapeId = d.bodyHeadShape[bodyId];
+  d.shapes[shapeId] = row; d.bodyHeadShape[bodyId] = shapeId;
+  d.shapeAABB[shapeId] = make_float4(aabb.lo.x, aabb.lo.y, aabb.hi.x, aabb.hi.y);
+  d.shapeFat[shapeId] = make_float4(fat.lo.x, fat.lo.y, fat.hi.x, fat.hi.y);
+}
+void World::treeProxyRemoved(int type) {          // DestroyProxy: the leaf and, unless it was the root, its parent go back to the free list
+  if (!onDevice_) return;
+  treeNodeCount_[type] -= treeProxyCount_[type] > 1 ? 2 : 1;
+  treeProxyCount_[type]--;
+}
+
 int World::createBody(const B2CBodyDef& def, int* bodyId) {
-  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_body after the first step is not supported in this build");
+  if (onDevice_) {
+    if (bodyIds_.freeArray.empty() && (int)bodies_.size() >= capBody_) return fail(B2C_E_CAPACITY, "body rows are full: create the world with a larger B2CWorldDef.bodyCapacity");
+    if (def.type != kStaticBody && (int)awakeOrder_.size() >= capAwake_) return fail(B2C_E_CAPACITY, "awake-body rows are full: create the world with a larger B2CWorldDef.bodyCapacity");
+  }
   if (!def.isEnabled || def.isBullet || !(def.isAwake || !def.enableSleep))
     return fail(B2C_E_UNSUPPORTED, "disabled / bullet / initially-asleep bodies are not supported");
   int id = bodyIds_.alloc();
@@ -147,6 +207,20 @@ int World::createBody(const B2CBodyDef& def, int* bodyId) {
   if ((int)colorMask_.size() <= id) colorMask_.resize(id + 1, 0);
   colorMask_[id] = 0;
   *bodyId = id;
+  if (!onDevice_) return B2C_OK;
+  BodyRows r;
+  const uint32_t fl = b.flags;
+  r.st0 = make_float4(b.v.x, b.v.y, b.w, __builtin_bit_cast(float, fl)); r.st1 = make_float4(0, 0, 1, 0);
+  r.simMass = make_float4(b.invMass, b.invInertia, b.linearDamping, b.angularDamping); r.simForce = make_float4(b.force.x, b.force.y, b.torque, b.gravityScale);
+  r.simPose = make_float4(b.center.x, b.center.y, b.xf.q.c, b.xf.q.s); r.simLocal = make_float4(b.localCenter.x, b.localCenter.y, b.minExtent, b.maxExtent);
+  r.simPose0 = make_float4(b.center0.x, b.center0.y, b.rot0.c, b.rot0.s);
+  r.bodyXf = make_float4(b.xf.p.x, b.xf.p.y, b.xf.q.c, b.xf.q.s); r.bodyMass = make_float4(b.invMass, b.invInertia, b.localCenter.x, b.localCenter.y);
+  r.bodyCenter = make_float2(b.center.x, b.center.y); r.flags = fl; r.type = b.type; r.sim = b.simIndex; r.sleepThreshold = b.sleepThreshold;
+  CK(cudaSetDevice(device_));
+  k_create_body<<<1, 1, 0, stream_>>>(d_, id, r);
+  CK(cudaGetLastError());
+  d_.awakeCount = (int)awakeOrder_.size(); d_.bodyCapacity = (int)bodies_.size();
+  bodiesFetched_ = false; movesFetched_ = false;
   return B2C_OK;
 }
 
@@ -157,8 +231,17 @@ void World::updateShapeAABBs(HShape& s, Xf xf, int proxyType) {   // src/Shape.c
 }
 
 int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId) {
-  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_shape after the first step is not supported in this build");
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  int grow[4] = {0, 0, 0, 0}, grownCap = 0;
+  if (onDevice_) {                               // every check first: a refused call leaves both sides untouched
+    if (shapeIds_.freeArray.empty() && (int)shapes_.size() >= capShape_) return fail(B2C_E_CAPACITY, "shape rows are full: create the world with a larger B2CWorldDef.shapeCapacity");
+    const int t = bodies_[bodyId].type;
+    int cap = d_.trees[t].capacity, nodes = treeNodeCount_[t];
+    if (nodes == cap) { grow[0] = cap; cap += cap >> 1; grow[1] = cap; }                  // HostTree::createProxy: ensureFreeNode before each allocation
+    if (nodes + 1 == cap) { grow[2] = cap; cap += cap >> 1; grow[3] = cap; }
+    if (cap > treeAllocCap_[t]) return fail(B2C_E_CAPACITY, "broad-phase tree is full: create the world with a larger B2CWorldDef.shapeCapacity");
+    grownCap = cap;
+  }
   if (def.isSensor) return fail(B2C_E_UNSUPPORTED, "sensor shapes are not supported (src/Sensor.cs is out of scope)");
   if (def.enableCustomFiltering || def.enablePreSolveEvents) return fail(B2C_E_UNSUPPORTED, "managed callbacks (custom filter / preSolve) cannot run on the device");
   if (g.type < 0 || g.type > kPolygon) return fail(B2C_E_UNSUPPORTED, "chain segments are not supported");
@@ -178,6 +261,22 @@ int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g,
   s.density = def.density; s.categoryBits = def.categoryBits; s.maskBits = def.maskBits; s.groupIndex = def.groupIndex; s.userData = def.userData;
   s.flags = (def.enableContactEvents ? SF_CONTACT_EVENTS : 0) | (def.enableHitEvents ? SF_HIT_EVENTS : 0);
   int proxyType = body.type;
+  if (onDevice_) {
+    ShapeDev row; memset(&row, 0, sizeof(row));
+    row.geom = s.geom; row.material = make_float4(s.friction, s.restitution, s.rollingResistance, s.tangentSpeed);
+    row.categoryBits = s.categoryBits; row.maskBits = s.maskBits; row.groupIndex = s.groupIndex; row.bodyId = bodyId; row.flags = s.flags; row.sensorIndex = -1;
+    CK(cudaSetDevice(device_));
+    k_create_shape<<<1, 1, 0, stream_>>>(d_, id, row, proxyType, def.invokeContactCreation ? 1 : 0, grow[0], grow[1], grow[2], grow[3]);
+    CK(cudaGetLastError());
+    d_.trees[proxyType].capacity = grownCap;
+    treeNodeCount_[proxyType] += treeProxyCount_[proxyType] > 0 ? 2 : 1; treeProxyCount_[proxyType]++;
+    s.proxyKey = 0;                               // "has a proxy"; the key itself lives on the device (b2cuda_world_read_shapes)
+    d_.shapeCapacity = (int)shapes_.size();
+    if (body.headShapeId != -1) shapes_[body.headShapeId].prevShapeId = id;
+    s.prevShapeId = -1; s.nextShapeId = body.headShapeId; body.headShapeId = id; body.shapeCount++;
+    *shapeId = id;
+    return def.updateBodyMass ? applyMassFromShapes(bodyId) : B2C_OK;
+  }
   updateShapeAABBs(s, body.xf, proxyType);
   {                                               // src/BroadPhase.cs:71-79
     int proxyId = trees_[proxyType].createProxy(s.fat, s.categoryBits, id);
@@ -497,7 +596,7 @@ int World::destroyBody(int bodyId) {             // BodyAPI.DestroyBody api/Body
   CK(cudaSetDevice(device_));
   k_destroy_body<<<1, 256, 0, stream_>>>(d_, bodyId, endIndex_);      // contacts (list order), proxies, awake-set swap-remove
   CK(cudaGetLastError());
-  for (int sid = b.headShapeId; sid != -1;) { HShape& sh = shapes_[sid]; int next = sh.nextShapeId; sh.proxyKey = -1; sh.id = -1; shapeIds_.release(sid); sid = next; }
+  for (int sid = b.headShapeId; sid != -1;) { HShape& sh = shapes_[sid]; int next = sh.nextShapeId; if (sh.proxyKey != -1) treeProxyRemoved(b.type); sh.proxyKey = -1; sh.id = -1; shapeIds_.release(sid); sid = next; }
   if (b.simIndex >= 0) {
     int last = (int)awakeOrder_.size() - 1;
     if (b.simIndex != last) { int moved = awakeOrder_[last]; awakeOrder_[b.simIndex] = moved; bodies_[moved].simIndex = b.simIndex; }
@@ -542,6 +641,7 @@ int World::destroyShape(int shapeId, bool updateBodyMass) {      // ShapeAPI.Des
   CK(cudaSetDevice(device_));
   k_destroy_shape<<<1, 256, 0, stream_>>>(d_, shapeId, bodyId, prev, next, endIndex_);
   CK(cudaGetLastError());
+  if (s.proxyKey != -1) treeProxyRemoved(body.type);
   s.proxyKey = -1; s.id = -1;
   shapeIds_.release(shapeId);
   eventsFetched_ = false;
@@ -642,6 +742,11 @@ int World::upload() {
   WorldDev& d = d_;
   const int nBody = (int)bodies_.size(), nAwake = (int)awakeOrder_.size(), nShape = (int)shapes_.size(), nJoint = (int)joints_.size();
   d.awakeCount = nAwake; d.bodyCapacity = nBody; d.shapeCapacity = nShape; d.jointCapacity = nJoint;
+  // Headroom for bodies and shapes created after this upload (b2cuda_create_body / _create_shape between steps): a quarter more, at least
+  // 256, or what the world definition asks for. Past it the create call fails with B2C_E_CAPACITY; nothing here grows behind a running step.
+  capBody_ = std::max(nBody + std::max(256, nBody / 4), capHintBody); capShape_ = std::max(nShape + std::max(256, nShape / 4), capHintShape);
+  capAwake_ = nAwake + (capBody_ - nBody);
+  const int capBody = capBody_, capAwake = capAwake_, capShape = capShape_;
   // ---- bodies ----
   std::vector<float4> st0(nAwake), st1(nAwake), simMass(nAwake), simForce(nAwake), simPose(nAwake), simLocal(nAwake), simPose0(nAwake);
   std::vector<uint32_t> simFlags(nAwake); std::vector<int> simBodyId(nAwake);
@@ -657,8 +762,8 @@ int World::upload() {
     simPose0[i] = make_float4(b.center0.x, b.center0.y, b.rot0.c, b.rot0.s);
     simFlags[i] = fl; simBodyId[i] = b.id;
   }
-  DA(d.st0, float4, nAwake); DA(d.st1, float4, nAwake); DA(d.simMass, float4, nAwake); DA(d.simForce, float4, nAwake);
-  DA(d.simPose, float4, nAwake); DA(d.simLocal, float4, nAwake); DA(d.simPose0, float4, nAwake); DA(d.simFlags, uint32_t, nAwake); DA(d.simBodyId, int, nAwake);
+  DA(d.st0, float4, capAwake); DA(d.st1, float4, capAwake); DA(d.simMass, float4, capAwake); DA(d.simForce, float4, capAwake);
+  DA(d.simPose, float4, capAwake); DA(d.simLocal, float4, capAwake); DA(d.simPose0, float4, capAwake); DA(d.simFlags, uint32_t, capAwake); DA(d.simBodyId, int, capAwake);
   UP(d.st0, st0); UP(d.st1, st1); UP(d.simMass, simMass); UP(d.simForce, simForce); UP(d.simPose, simPose); UP(d.simLocal, simLocal);
   UP(d.simPose0, simPose0); UP(d.simFlags, simFlags); UP(d.simBodyId, simBodyId);
   std::vector<float4> bodyXf(nBody), bodyMass(nBody); std::vector<float2> bodyCenter(nBody);
@@ -674,13 +779,13 @@ int World::upload() {
   }
   for (int id : lockQuirk_) bodyFlags[id] |= kLockLinearX | kLockLinearY | kLockAngularZ;
   colorMask_.resize(nBody, 0);
-  DA(d.bodyXf, float4, nBody); DA(d.bodyMass, float4, nBody); DA(d.bodyCenter, float2, nBody); DA(d.bodySim, int, nBody); DA(d.bodyType, int, nBody);
-  DA(d.bodyHeadShape, int, nBody); DA(d.bodyHeadJoint, int, nBody); DA(d.bodyJointCount, int, nBody); DA(d.bodyColorMask, uint32_t, nBody);
-  DA(d.bodyMinOp, int, nBody); DA(d.bodySleepThreshold, float, nBody); DA(d.bodyFlags, uint32_t, nBody);
+  DA(d.bodyXf, float4, capBody); DA(d.bodyMass, float4, capBody); DA(d.bodyCenter, float2, capBody); DA(d.bodySim, int, capBody); DA(d.bodyType, int, capBody);
+  DA(d.bodyHeadShape, int, capBody); DA(d.bodyHeadJoint, int, capBody); DA(d.bodyJointCount, int, capBody); DA(d.bodyColorMask, uint32_t, capBody);
+  DA(d.bodyMinOp, int, capBody); DA(d.bodySleepThreshold, float, capBody); DA(d.bodyFlags, uint32_t, capBody);
   UP(d.bodyXf, bodyXf); UP(d.bodyMass, bodyMass); UP(d.bodyCenter, bodyCenter); UP(d.bodySim, bodySim); UP(d.bodyType, bodyType);
   UP(d.bodyHeadShape, bodyHeadShape); UP(d.bodyHeadJoint, bodyHeadJoint); UP(d.bodyJointCount, bodyJointCount); UP(d.bodyColorMask, colorMask_);
   UP(d.bodySleepThreshold, bodySleep); UP(d.bodyFlags, bodyFlags);
-  CK(cudaMemsetAsync(d.bodyMinOp, 0x7f, sizeof(int) * (size_t)std::max(nBody, 1), stream_));
+  CK(cudaMemsetAsync(d.bodyMinOp, 0x7f, sizeof(int) * (size_t)std::max(capBody, 1), stream_));
   // ---- shapes ----
   std::vector<ShapeDev> sh(nShape); std::vector<float4> shAABB(nShape), shFat(nShape);
   for (int i = 0; i < nShape; i++) {
@@ -692,7 +797,7 @@ int World::upload() {
     shAABB[i] = make_float4(s.aabb.lo.x, s.aabb.lo.y, s.aabb.hi.x, s.aabb.hi.y);
     shFat[i] = make_float4(s.fat.lo.x, s.fat.lo.y, s.fat.hi.x, s.fat.hi.y);
   }
-  DA(d.shapes, ShapeDev, nShape); DA(d.shapeAABB, float4, nShape); DA(d.shapeFat, float4, nShape);
+  DA(d.shapes, ShapeDev, capShape); DA(d.shapeAABB, float4, capShape); DA(d.shapeFat, float4, capShape);
   UP(d.shapes, sh); UP(d.shapeAABB, shAABB); UP(d.shapeFat, shFat);
   // ---- joints ----
   std::vector<JointDev> jd(nJoint); std::vector<int4> je(nJoint); std::vector<int> jc(nJoint), jsorted;
@@ -711,8 +816,11 @@ int World::upload() {
   int totalProxies = 0;
   for (int t = 0; t < 3; t++) {
     HostTree& h = trees_[t]; TreeDev& td = d.trees[t];
-    int cap = h.capacity();
-    td.capacity = cap; td.stackCapacity = 16384;
+    const int logicalCap = h.capacity();
+    int cap = logicalCap;                          // allocation: the reference's growth steps (x1.5) until the reserved shapes fit
+    while (cap - h.nodeCount < 2 * (capShape - nShape) + 2) cap += cap >> 1;
+    treeAllocCap_[t] = cap; treeNodeCount_[t] = h.nodeCount; treeProxyCount_[t] = h.proxyCount;
+    td.capacity = logicalCap; td.stackCapacity = 16384;
     DA(td.aabb, float4, cap); DA(td.child, int2, cap); DA(td.parent, int, cap); DA(td.hf, uint32_t, cap); DA(td.cat, uint64_t, cap);
     DA(td.user, int, cap); DA(td.moved, uint8_t, cap); DA(td.meta, int, 4); DA(td.leafIdx, int, cap); DA(td.leafCtr, float2, cap); DA(td.stack, int, td.stackCapacity);
     DA(td.segStart, int, cap); DA(td.recEnd, int, cap + 1); DA(td.recNode, int, cap + 1); DA(td.recSplit, int, cap + 1); DA(td.recBox, float4, cap + 1);
@@ -728,7 +836,7 @@ int World::upload() {
     CK(cudaStreamSynchronize(stream_));
     totalProxies += h.proxyCount;
   }
-  d.moveCapacity = std::max(totalProxies, 16);
+  d.moveCapacity = std::max(totalProxies + (capShape - nShape), 16);
   int contactCap = capHintContact > 0 ? capHintContact : std::max(4096, 12 * nShape);
   d.contactCapacity = contactCap; d.pairCapacity = contactCap; d.eventCapacity = contactCap;
   d.constraintCapacity = contactCap + 32 * kGraphColorCount;
@@ -736,7 +844,7 @@ int World::upload() {
   d.pairTableSize = tableSize;
   DA(d.moveArray, int, d.moveCapacity); DA(d.moveHitCount, int, d.moveCapacity + 1); DA(d.movePairs, int2, d.pairCapacity);
   DA(d.pairTable, unsigned long long, tableSize);
-  { int sumCap = 0; for (int t = 0; t < 3; t++) sumCap += d.trees[t].capacity;
+  { int sumCap = 0; for (int t = 0; t < 3; t++) sumCap += treeAllocCap_[t];
     d.bigScratch = std::max(1 << 21, sumCap);
     d.bigQueryVisits = kBigQueryVisits;
     d.islandMaxBodies = kIslandMaxBodies;
@@ -758,13 +866,13 @@ int World::upload() {
   DA(d.sA, float4, cc); DA(d.sB, float4, cc); DA(d.sC, float4, cc); DA(d.sD, float4, cc); DA(d.sE, float4, cc); DA(d.sF, float4, cc);
   DA(d.sG, float4, cc); DA(d.sH, float4, cc); DA(d.sI, float4, cc); DA(d.sJ, float4, cc); DA(d.sContact, int, cc); DA(d.cConstraint, int, contactCap);
   DA(d.blockHist, int, (size_t)(contactCap / 256 + 2) * kGraphColorCount);
-  DA(d.ufParent, int, nAwake); DA(d.rootBodyCount, int, nAwake); DA(d.rootConCount, int, nAwake); DA(d.rootColorCount, int, (size_t)nAwake * kGraphColorCount);
-  DA(d.rootInfo, int, nAwake); DA(d.rootScan, int4, nAwake + 1); DA(d.islandBodyStart, int, nAwake + 1); DA(d.islandConStart, int, nAwake + 1);
-  DA(d.islandColorOff, int, (size_t)(nAwake + 1) * (kGraphColorCount + 1)); DA(d.islandBodies, int, nAwake); DA(d.bodyLocal, int, nAwake);
-  DA(d.freeBodies, int, nAwake); DA(d.bigBodies, int, nAwake); DA(d.kinematicUsed, uint8_t, nAwake); DA(d.sLocal, int2, cc);
-  DA(d.bodyEnlargedCount, int, nAwake + 1);
+  DA(d.ufParent, int, capAwake); DA(d.rootBodyCount, int, capAwake); DA(d.rootConCount, int, capAwake); DA(d.rootColorCount, int, (size_t)capAwake * kGraphColorCount);
+  DA(d.rootInfo, int, capAwake); DA(d.rootScan, int4, capAwake + 1); DA(d.islandBodyStart, int, capAwake + 1); DA(d.islandConStart, int, capAwake + 1);
+  DA(d.islandColorOff, int, (size_t)(capAwake + 1) * (kGraphColorCount + 1)); DA(d.islandBodies, int, capAwake); DA(d.bodyLocal, int, capAwake);
+  DA(d.freeBodies, int, capAwake); DA(d.bigBodies, int, capAwake); DA(d.kinematicUsed, uint8_t, capAwake); DA(d.sLocal, int2, cc);
+  DA(d.bodyEnlargedCount, int, capAwake + 1);
   DA(d.sc, Scalars, 1);
-  int scanBlocks = std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, nAwake)) / 256 + 2;
+  int scanBlocks = std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, capAwake)) / 256 + 2;
   DA(d.scanBlockSums, int, scanBlocks); DA(d.scanBlockSums4, int4, scanBlocks);
   Scalars init; memset(&init, 0, sizeof(init));
   init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;
@@ -777,15 +885,15 @@ int World::upload() {
   for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.endEvents[k], hEnd_[k], 0));
   CK(cudaHostGetDevicePointer((void**)&d.hitEvents, hHit_, 0));
   d.bodyOut = nullptr;
-  DA(dBodyRead_, B2CBodyRead, nBody);
-  DA(dMoveEvents_, B2CBodyMoveEvent, nAwake);
-  CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)std::max(nAwake, 1), cudaHostAllocMapped));
+  DA(dBodyRead_, B2CBodyRead, capBody);
+  DA(dMoveEvents_, B2CBodyMoveEvent, capAwake);
+  CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)std::max(capAwake, 1), cudaHostAllocMapped));
   // B2CUDA_ZEROCOPY_MOVES=1: FinalizeBodies writes the move events straight into this mapped buffer instead of a device array + copy behind
   // the step. Measured slower end to end (many_pyramids 560 vs 582 M body-substeps/s, batched 1663 vs 1779): off by default.
   { const char* e = getenv("B2CUDA_ZEROCOPY_MOVES"); hMoveEventsDev_ = nullptr;
     if (e && !strcmp(e, "1") && cudaHostGetDevicePointer((void**)&hMoveEventsDev_, hMoveEvents_, 0) != cudaSuccess) { hMoveEventsDev_ = nullptr; cudaGetLastError(); } }
   d.moveOut = nullptr;
-  CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(nBody, 1), cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(capBody, 1), cudaHostAllocDefault));
   CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(nJoint, 1), cudaHostAllocDefault));
   CK(cudaStreamSynchronize(stream_));
   onDevice_ = true;

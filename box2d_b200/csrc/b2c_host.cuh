@@ -67,6 +67,7 @@ class World {
   int shapeEnableEvents(int shapeId, int which, bool flag);
   int bodyEnableEvents(int bodyId, int which, bool flag);
   int uploadJointLists();
+  void treeProxyRemoved(int type);
   int jointOp(int jointId, int patch, int which, float a, float b);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }
   int setTransform(int bodyId, V2 p, Rot q);
@@ -111,6 +112,8 @@ class World {
   std::string error;
   int unsupported = 0;
   int capHintBody, capHintShape, capHintContact, capHintJoint;
+  int capBody_ = 0, capAwake_ = 0, capShape_ = 0;                       // device rows allocated at upload (bodies / awake sims / shapes)
+  int treeAllocCap_[3] = {0, 0, 0}, treeNodeCount_[3] = {0, 0, 0}, treeProxyCount_[3] = {0, 0, 0};   // allocated nodes per tree; the logical capacity (TreeDev::capacity) grows x1.5 as the reference's does
 
  private:
   void updateBodyMassData(HBody& body);

@@ -35,7 +35,7 @@ typedef struct B2CWorldDef {
   B2CVec2 gravity;
   float restitutionThreshold, hitEventThreshold, contactHertz, contactDampingRatio, contactSpeed, maximumLinearSpeed;
   int32_t enableSleep, enableContinuous, enableContactSoftening;
-  int32_t bodyCapacity, shapeCapacity, contactCapacity, jointCapacity;   /* hints, 0 = default; buffers grow between steps */
+  int32_t bodyCapacity, shapeCapacity, contactCapacity, jointCapacity;   /* 0 = default. body/shape: rows reserved for creation after the first step; contact: contact slots */
 } B2CWorldDef;
 
 /* BodyDef POD — include/Types.cs:170-223 */
@@ -171,7 +171,9 @@ int32_t b2cuda_create_joint(B2CWorld* world, const B2CJointDef* def, int32_t* jo
 /* JointAPI.DestroyJoint api/Joint.cs:9-17 (DestroyJointInternal src/Joint.cs:297-375) and BodyAPI.DestroyBody api/Body.cs:106-160: the body's joints,
  * then its contacts in contact-list order (end-touch events go to the buffer the NEXT step reports, ids return to the LIFO pool), its shapes'
  * proxies (UnBufferMove + tree RemoveLeaf), then the body leaves the awake set by swap-remove. Allowed between steps once the world has been
- * stepped (destroy_joint also before). Creating bodies, shapes or joints after the first step stays unsupported (B2C_E_UNSUPPORTED). */
+ * stepped (destroy_joint also before). b2cuda_create_body / b2cuda_create_shape also work between steps after the first one: rows for them
+ * are reserved at the first step (a quarter more than the world holds then, at least 256, or B2CWorldDef.bodyCapacity / shapeCapacity);
+ * past the reservation the call fails with B2C_E_CAPACITY and changes nothing. */
 int32_t b2cuda_destroy_joint(B2CWorld* world, int32_t jointId, int32_t wakeAttached);
 int32_t b2cuda_destroy_body(B2CWorld* world, int32_t bodyId);
 /* ShapeAPI.DestroyShape api/Shape.cs:48-56 (DestroyShapeInternal src/Shape.cs:219-272: the shape leaves its body's list, its proxy leaves the tree,

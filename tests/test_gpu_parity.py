@@ -1,7 +1,7 @@
 """-m gpu: the CUDA step vs the oracle through the C-ABI, bit-exact unless a tolerance is stated."""
 import pytest
 import parity
-from box2d_b200 import api, scenes
+from box2d_b200 import api, scenes, geometry as geo
 
 pytestmark = pytest.mark.gpu
 
@@ -589,3 +589,85 @@ def test_event_enable_flags_between_steps_bit_exact():
             w.Body_EnableContactEvents(0, True)
     res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=50, world_def=wd, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+def _spawn(w, x, y, kind, v=(0.0, 0.0), body_type=None):
+    bd = api.default_body_def()
+    bd.type = api.DYNAMIC_BODY if body_type is None else body_type
+    bd.position = api.Vec2(x, y)
+    bd.linearVelocity = api.Vec2(*v)
+    bd.angularVelocity = 0.5 if kind != "static" else 0.0
+    b = w.CreateBody(bd)
+    sd = scenes._shape_def()
+    if kind == "box":
+        w.CreatePolygonShape(b, sd, geo.MakeBox(0.5, 0.5))
+    elif kind == "circle":
+        w.CreateCircleShape(b, sd, geo.Circle((0.0, 0.0), 0.4))
+    elif kind == "compound":
+        w.CreatePolygonShape(b, sd, geo.MakeBox(0.4, 0.2))
+        w.CreateCircleShape(b, sd, geo.Circle((0.5, 0.0), 0.25))
+        w.CreateCapsuleShape(b, sd, geo.Capsule((-0.6, -0.2), (-0.6, 0.2), 0.1))
+    elif kind == "static":
+        w.CreateSegmentShape(b, sd, geo.Segment((-3.0, 0.0), (3.0, 0.5)))
+    elif kind == "paddle":
+        w.CreatePolygonShape(b, sd, geo.MakeBox(2.0, 0.1))
+    return b
+
+
+def test_create_bodies_and_shapes_between_steps_bit_exact():
+    """BodyAPI.CreateBody (api/Body.cs:16-105) and ShapeAPI.CreateShape (api/Shape.cs:8-24) after the first step: new rows are appended to
+    the awake set, proxies enter the device trees through the reference's CreateProxy / InsertLeaf (free-list order included, so proxy keys
+    agree), the move buffer and the mass update run as at creation time. Ids freed by DestroyBody come back LIFO."""
+    made = {}
+
+    def mutate(w, step):
+        if step == 5:
+            made[id(w)] = [_spawn(w, -2.0, 14.0, "box", (0.0, -3.0)), _spawn(w, 1.3, 15.0, "circle"), _spawn(w, 0.2, 17.0, "compound", (0.5, -1.0))]
+        elif step == 9:
+            _spawn(w, 14.0, 3.0, "static")
+            _spawn(w, 13.0, 8.0, "box")
+            _spawn(w, -12.0, 6.0, "paddle", body_type=api.KINEMATIC_BODY)
+        elif step == 14:
+            w.DestroyBody(made[id(w)][0])
+            w.DestroyBody(7)
+            a = _spawn(w, -1.0, 16.0, "circle", (0.0, -6.0))         # takes body id 7 and its shape id back
+            b = _spawn(w, 3.0, 16.0, "compound")
+            assert a == 7 and b == made[id(w)][0]
+        elif step == 20:
+            for k in range(12):
+                _spawn(w, -6.0 + k, 12.0 + 0.3 * k, ("box", "circle", "compound")[k % 3])
+        elif step == 26:
+            sd = scenes._shape_def()
+            w.CreateCircleShape(3, sd, geo.Circle((0.0, 0.6), 0.3))    # a second shape on a body of the pyramid, mass updated
+            sd.updateBodyMass = 0
+            w.CreateCircleShape(4, sd, geo.Circle((0.0, 0.6), 0.3))    # and one that leaves the mass alone
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 8), steps=60, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    assert res["bodies"] == 37 + 3 + 3 + 12
+
+
+def test_create_many_bodies_grows_the_device_trees():
+    """Spawning more proxies than the tree's node pool holds: the pool grows by the reference's x1.5 steps inside the rows allocated at
+    upload (B2CWorldDef.bodyCapacity / shapeCapacity); past the allocation the call fails loudly and changes nothing."""
+    wd = scenes.world_def()
+    wd.bodyCapacity, wd.shapeCapacity = 2000, 2000
+
+    def mutate(w, step):
+        if step in (3, 6, 9):
+            for k in range(150):
+                _spawn(w, -30.0 + 0.41 * k, 6.0 + (k % 5) * 1.1 + step, ("box", "circle")[k % 2])
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 5), steps=24, world_def=wd, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        scenes.add_pyramid(cuda, 3)
+        cuda.Step(1.0 / 60.0, 4)
+        with pytest.raises(Exception, match="bodyCapacity"):
+            for k in range(400):
+                _spawn(cuda, float(k), 30.0, "circle")
+        n = cuda.GetCounters().bodyCount
+        cuda.Step(1.0 / 60.0, 4)
+        assert cuda.GetCounters().bodyCount == n and len(cuda.GetBodyMoveEvents()) == n - 1
+    finally:
+        cuda.Destroy()
