@@ -103,6 +103,7 @@ void World::freeDevice() {
   for (void* p : allocs_) cudaFree(p);
   allocs_.clear();
   if (hostScalars_) cudaFreeHost(hostScalars_);
+  if (hJointColor_) { cudaFreeHost(hJointColor_); hJointColor_ = nullptr; hJointColorDev_ = nullptr; }
   if (hBegin_) cudaFreeHost(hBegin_);
   for (auto& e : hEnd_) { if (e) cudaFreeHost(e); e = nullptr; }
   if (hHit_) cudaFreeHost(hHit_);
@@ -356,6 +357,52 @@ int World::assignJointColor(int bodyIdA, int bodyIdB, int typeA, int typeB) {   
   return kOverflowIndex;
 }
 
+// AssignJointColor (src/ConstraintGraph.cs:91-128) against the colour bitsets the steps maintain on the device; the colour comes back
+// through a mapped int so that the host can file the joint under it.
+__global__ void k_joint_color(WorldDev d, int bodyIdA, int bodyIdB, int typeA, int typeB, int* out) {
+  uint32_t mA = d.bodyColorMask[bodyIdA], mB = d.bodyColorMask[bodyIdB];
+  int color = kOverflowIndex;
+  if (typeA != kStaticBody && typeB != kStaticBody) {
+    for (int i = 0; i < kDynamicColorCount; i++) {
+      if (((mA >> i) & 1u) || ((mB >> i) & 1u)) continue;
+      if (typeA == kDynamicBody) mA |= 1u << i;
+      if (typeB == kDynamicBody) mB |= 1u << i;
+      color = i; break;
+    }
+  } else if (typeA == kDynamicBody) {
+    for (int i = kGraphColorCount - 2; i >= 1; i--) { if ((mA >> i) & 1u) continue; mA |= 1u << i; color = i; break; }
+  } else if (typeB == kDynamicBody) {
+    for (int i = kGraphColorCount - 2; i >= 1; i--) { if ((mB >> i) & 1u) continue; mB |= 1u << i; color = i; break; }
+  }
+  d.bodyColorMask[bodyIdA] = mA; d.bodyColorMask[bodyIdB] = mB;
+  *out = color;
+}
+__device__ void destroyContactSerial(const WorldDev& d, int id, int endIndex);
+// The joint's row, its collide flag and, unless the bodies may collide, DestroyContactsBetweenBodies (src/Joint.cs:155-180): both contact
+// lists hold the shared contacts in the same relative order (newest first), so the walk over the shorter list is a descending-stamp walk.
+__global__ void k_joint_created(WorldDev d, int jointId, JointDev row, int collide, int endIndex) {
+  __shared__ int sCount;
+  Scalars& s = *d.sc;
+  if (threadIdx.x == 0) { sCount = 0; d.joints[jointId] = row; d.jointCollide[jointId] = collide; d.jointEventFlag[jointId] = 0; s.graphDirty = 1; }
+  __syncthreads();
+  if (collide) return;
+  const int n = s.contactNext, a = row.bodyIdA, b = row.bodyIdB;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (!(d.cFlags[i] & CF_ALIVE)) continue;
+    int2 cb = d.cBody[i];
+    if ((cb.x == a && cb.y == b) || (cb.x == b && cb.y == a)) { int k = atomicAdd(&sCount, 1); d.opList[k] = i; }
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const int count = sCount;
+  for (int i = 1; i < count; i++) {
+    int id = d.opList[i]; uint32_t st = d.cStamp[id]; int j = i - 1;
+    while (j >= 0 && d.cStamp[d.opList[j]] < st) { d.opList[j + 1] = d.opList[j]; j--; }
+    d.opList[j + 1] = id;
+  }
+  for (int i = 0; i < count; i++) destroyContactSerial(d, d.opList[i], endIndex);
+}
+
 int World::createRevoluteJoint(const B2CRevoluteJointDef& r, int* jointId) {     // api/Joint.cs:555 -> the generic path
   B2CJointDef def; memset(&def, 0, sizeof(def));
   def.type = B2C_JOINT_REVOLUTE; def.bodyIdA = r.bodyIdA; def.bodyIdB = r.bodyIdB; def.localFrameA = r.localFrameA; def.localFrameB = r.localFrameB;
@@ -369,12 +416,23 @@ int World::createRevoluteJoint(const B2CRevoluteJointDef& r, int* jointId) {    
 // World.CreateJoint src/Joint.cs:181-296 + the per-type Create (DistanceJoint.cs:35-63, FilterJoint.cs:7-17, MotorJoint.cs:33-52,
 // PrismaticJoint.cs:33-53, RevoluteJoint.cs:32-56, WeldJoint.cs:24-39, WheelJoint.cs:33-56)
 int World::createJoint(const B2CJointDef& def, int* jointId) {
-  if (onDevice_) return fail(B2C_E_UNSUPPORTED, "create_joint after the first step is not supported in this build");
   if (def.type < B2C_JOINT_DISTANCE || def.type > B2C_JOINT_WHEEL) return fail(B2C_E_INVALID, "bad joint type");
   int nb = (int)bodies_.size();
   if (def.bodyIdA < 0 || def.bodyIdA >= nb || def.bodyIdB < 0 || def.bodyIdB >= nb || bodies_[def.bodyIdA].id != def.bodyIdA || bodies_[def.bodyIdB].id != def.bodyIdB) return fail(B2C_E_INVALID, "bad body id");
   HBody& bodyA = bodies_[def.bodyIdA]; HBody& bodyB = bodies_[def.bodyIdB];
   if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) return fail(B2C_E_UNSUPPORTED, "joint between two non-dynamic bodies (static set) is not supported");
+  if (def.type == B2C_JOINT_DISTANCE && (!(def.length > 0.0f) || !(def.lowerSpringForce <= def.upperSpringForce)))
+    return fail(B2C_E_INVALID, "distance joint: length must be > 0 and lowerSpringForce <= upperSpringForce");
+  int deviceColor = -1;
+  if (onDevice_) {                               // the colour first: a refused call must leave both sides as they were
+    if (jointIds_.freeArray.empty() && (int)joints_.size() >= capJoint_) return fail(B2C_E_CAPACITY, "joint rows are full: create the world with a larger B2CWorldDef.jointCapacity");
+    CK(cudaSetDevice(device_));
+    k_joint_color<<<1, 1, 0, stream_>>>(d_, bodyA.id, bodyB.id, bodyA.type, bodyB.type, hJointColorDev_);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(stream_));
+    deviceColor = *hJointColor_;
+    if (deviceColor == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
+  }
   int id = jointIds_.alloc();
   if (id == (int)joints_.size()) joints_.emplace_back();
   HJoint& j = joints_[id];
@@ -389,7 +447,7 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   j.bodyIdB = bodyB.id; j.prevKeyB = -1; j.nextKeyB = bodyB.headJointKey;
   if (bodyB.headJointKey != -1) { HJoint& h = joints_[bodyB.headJointKey >> 1]; if (bodyA.headJointKey & 1) h.prevKeyB = keyB; else h.prevKeyA = keyB; }   // tests bodyA's key, as written (:229)
   bodyB.headJointKey = keyB; bodyB.jointCount++;
-  int color = assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type);
+  int color = onDevice_ ? deviceColor : assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type);
   if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   JointDev& s = j.sim;
   memset(&s, 0, sizeof(s));
@@ -432,9 +490,13 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
       break;
   }
   colorJoints_[color].push_back(id);
-  // DestroyContactsBetweenBodies (src/Joint.cs:155-180): no contacts exist before the first step.
   *jointId = id;
-  return B2C_OK;
+  if (!onDevice_) return B2C_OK;                  // DestroyContactsBetweenBodies (src/Joint.cs:155-180): no contacts exist before the first step
+  k_joint_created<<<1, 256, 0, stream_>>>(d_, id, s, j.collideConnected ? 1 : 0, endIndex_);
+  CK(cudaGetLastError());
+  d_.jointCapacity = (int)joints_.size();
+  eventsFetched_ = false;
+  return uploadJointLists();
 }
 
 // ---- JointAPI.DestroyJoint api/Joint.cs:9-17 / BodyAPI.DestroyBody api/Body.cs:106-160 -------------------------------------------------
@@ -746,7 +808,8 @@ int World::upload() {
   // 256, or what the world definition asks for. Past it the create call fails with B2C_E_CAPACITY; nothing here grows behind a running step.
   capBody_ = std::max(nBody + std::max(256, nBody / 4), capHintBody); capShape_ = std::max(nShape + std::max(256, nShape / 4), capHintShape);
   capAwake_ = nAwake + (capBody_ - nBody);
-  const int capBody = capBody_, capAwake = capAwake_, capShape = capShape_;
+  capJoint_ = std::max(nJoint + std::max(256, nJoint / 4), capHintJoint);
+  const int capBody = capBody_, capAwake = capAwake_, capShape = capShape_, capJoint = capJoint_;
   // ---- bodies ----
   std::vector<float4> st0(nAwake), st1(nAwake), simMass(nAwake), simForce(nAwake), simPose(nAwake), simLocal(nAwake), simPose0(nAwake);
   std::vector<uint32_t> simFlags(nAwake); std::vector<int> simBodyId(nAwake);
@@ -810,7 +873,7 @@ int World::upload() {
     for (int id : colorJoints_[c]) jsorted.push_back(id);
     d.jointColorStart[c + 1] = (int)jsorted.size();
   }
-  DA(d.joints, JointDev, nJoint); DA(d.jointEdges, int4, nJoint); DA(d.jointCollide, int, nJoint); DA(d.jointSorted, int, nJoint); DA(d.jointEventFlag, uint8_t, nJoint);
+  DA(d.joints, JointDev, capJoint); DA(d.jointEdges, int4, capJoint); DA(d.jointCollide, int, capJoint); DA(d.jointSorted, int, capJoint); DA(d.jointEventFlag, uint8_t, capJoint);
   UP(d.joints, jd); UP(d.jointEdges, je); UP(d.jointCollide, jc); UP(d.jointSorted, jsorted);
   // ---- trees ----
   int totalProxies = 0;
@@ -894,7 +957,9 @@ int World::upload() {
     if (e && !strcmp(e, "1") && cudaHostGetDevicePointer((void**)&hMoveEventsDev_, hMoveEvents_, 0) != cudaSuccess) { hMoveEventsDev_ = nullptr; cudaGetLastError(); } }
   d.moveOut = nullptr;
   CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(capBody, 1), cudaHostAllocDefault));
-  CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(nJoint, 1), cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(capJoint, 1), cudaHostAllocDefault));
+  CK(cudaHostAlloc((void**)&hJointColor_, sizeof(int), cudaHostAllocMapped));
+  CK(cudaHostGetDevicePointer((void**)&hJointColorDev_, hJointColor_, 0));
   CK(cudaStreamSynchronize(stream_));
   onDevice_ = true;
   return B2C_OK;

@@ -112,6 +112,7 @@ class World {
   std::string error;
   int unsupported = 0;
   int capHintBody, capHintShape, capHintContact, capHintJoint;
+  int capJoint_ = 0; int* hJointColor_ = nullptr; int* hJointColorDev_ = nullptr;   // joint rows; mapped int the colour kernel answers through
   int capBody_ = 0, capAwake_ = 0, capShape_ = 0;                       // device rows allocated at upload (bodies / awake sims / shapes)
   int treeAllocCap_[3] = {0, 0, 0}, treeNodeCount_[3] = {0, 0, 0}, treeProxyCount_[3] = {0, 0, 0};   // allocated nodes per tree; the logical capacity (TreeDev::capacity) grows x1.5 as the reference's does
 

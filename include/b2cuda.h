@@ -171,8 +171,10 @@ int32_t b2cuda_create_joint(B2CWorld* world, const B2CJointDef* def, int32_t* jo
 /* JointAPI.DestroyJoint api/Joint.cs:9-17 (DestroyJointInternal src/Joint.cs:297-375) and BodyAPI.DestroyBody api/Body.cs:106-160: the body's joints,
  * then its contacts in contact-list order (end-touch events go to the buffer the NEXT step reports, ids return to the LIFO pool), its shapes'
  * proxies (UnBufferMove + tree RemoveLeaf), then the body leaves the awake set by swap-remove. Allowed between steps once the world has been
- * stepped (destroy_joint also before). b2cuda_create_body / b2cuda_create_shape also work between steps after the first one: rows for them
- * are reserved at the first step (a quarter more than the world holds then, at least 256, or B2CWorldDef.bodyCapacity / shapeCapacity);
+ * stepped (destroy_joint also before). b2cuda_create_body / b2cuda_create_shape / b2cuda_create_joint also work between steps after the first
+ * one (the joint's colour is assigned against the device's colour bitsets, contacts between its bodies are destroyed unless collideConnected): rows
+ * are reserved at the first step (a quarter more than the world holds then, at least 256, or B2CWorldDef.bodyCapacity / shapeCapacity /
+ * jointCapacity);
  * past the reservation the call fails with B2C_E_CAPACITY and changes nothing. */
 int32_t b2cuda_destroy_joint(B2CWorld* world, int32_t jointId, int32_t wakeAttached);
 int32_t b2cuda_destroy_body(B2CWorld* world, int32_t bodyId);

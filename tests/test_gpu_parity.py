@@ -671,3 +671,59 @@ def test_create_many_bodies_grows_the_device_trees():
         assert cuda.GetCounters().bodyCount == n and len(cuda.GetBodyMoveEvents()) == n - 1
     finally:
         cuda.Destroy()
+
+
+def _jdef(t, a, b, pa, pb):
+    d = api.default_joint_def(t)
+    d.bodyIdA, d.bodyIdB = a, b
+    d.localFrameA = api.Transform(api.Vec2(*pa), api.Rot(1.0, 0.0))
+    d.localFrameB = api.Transform(api.Vec2(*pb), api.Rot(1.0, 0.0))
+    return d
+
+
+def test_create_joints_between_steps_bit_exact():
+    """World.CreateJoint (src/Joint.cs:181-296) after the first step: the colour is assigned against the device's colour bitsets (contacts
+    have taken bits since the upload), the contacts between the two bodies are destroyed when collideConnected is off (:155-180, end events
+    in the next step), joint ids freed by DestroyJoint come back LIFO. Atan2-free joint types, so everything is bit-exact."""
+    from box2d_b200 import capi as J
+    made = {}
+
+    def mutate(w, step):
+        if step == 6:
+            # bodies 1 and 2 are neighbours in the bottom row, 1 and 9 touch across rows: their contacts go away with the joints
+            d = _jdef(J.JOINT_REVOLUTE, 1, 2, (0.5, 0.0), (-0.5, 0.0))
+            d.forceThreshold = 1.0
+            j0 = w.CreateJoint(d)
+            j1 = w.CreateJoint(_jdef(J.JOINT_FILTER, 1, 9, (0.0, 0.0), (0.0, 0.0)))
+            d = _jdef(J.JOINT_DISTANCE, 0, 36, (0.0, 14.0), (0.0, 0.0))
+            d.length, d.enableSpring, d.hertz, d.dampingRatio = 6.0, 1, 2.0, 0.3
+            d.minLength, d.maxLength, d.enableLimit = 4.0, 8.0, 1
+            j2 = w.CreateJoint(d)
+            made[id(w)] = [j0, j1, j2]
+        elif step == 11:
+            d = _jdef(J.JOINT_MOTOR, 0, 30, (0.0, 0.0), (0.0, 0.0))
+            d.linearVelocity, d.maxVelocityForce, d.angularVelocity, d.maxVelocityTorque = api.Vec2(0.5, 0.2), 40.0, 1.0, 5.0
+            d.collideConnected = 1
+            w.CreateJoint(d)
+            b = _spawn(w, 6.0, 9.0, "box")
+            d = _jdef(J.JOINT_DISTANCE, b, 35, (0.0, 0.0), (0.0, 0.0))
+            d.length = 4.0
+            made[id(w)].append(w.CreateJoint(d))
+        elif step == 18:
+            w.DestroyJoint(made[id(w)][1])
+            w.DestroyJoint(made[id(w)][0])
+            d = _jdef(J.JOINT_WHEEL, 20, 21, (0.5, 0.0), (-0.5, 0.0))
+            d.enableSpring, d.hertz, d.dampingRatio = 1, 3.0, 0.5
+            j = w.CreateJoint(d)
+            assert j == made[id(w)][0]                      # freed last, handed out first
+        elif step == 25:
+            w.DestroyBody(36)                               # takes its distance joint with it
+            w.CreateJoint(_jdef(J.JOINT_REVOLUTE, 0, 33, (1.0, 9.0), (0.0, 0.0)))
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 8), steps=50, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+    # a world uploaded without any joint gets its first ones afterwards
+    res = parity.run_pair(lambda w: scenes.mixed_drop(w, 40), steps=30, verbose=True,
+                          mutate=lambda w, s: (w.CreateJoint(_jdef(J.JOINT_REVOLUTE, 1, 5, (1.0, 0.0), (0.0, 0.0))),
+                                               w.CreateJoint(_jdef(J.JOINT_FILTER, 6, 7, (0.0, 0.0), (0.0, 0.0)))) if s == 8 else None)
+    assert res["max_rel_err"] == 0.0
