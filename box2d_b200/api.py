@@ -278,6 +278,14 @@ class World:
         """BodyAPI.EnableHitEvents api/Body.cs:862-872"""
         self._check(self.fns["body_enable_events"](self.handle, body_id, capi.SHAPE_HIT_EVENTS, int(bool(flag))))
 
+    def SetFilter(self, shape_id, category_bits, mask_bits, group_index=0):
+        """ShapeAPI.SetFilter api/Shape.cs:157-166"""
+        self._check(self.fns["shape_set_filter"](self.handle, shape_id, category_bits, mask_bits, group_index))
+
+    def SetShapeGeometry(self, shape_id, geometry):
+        """ShapeAPI.SetCircle / SetCapsule / SetSegment / SetPolygon api/Shape.cs:289-326"""
+        self._check(self.fns["shape_set_geometry"](self.handle, shape_id, C.byref(geometry)))
+
     def CreateJoint(self, joint_def):
         """JointAPI.Create{Distance,Motor,Filter,Prismatic,Revolute,Weld,Wheel}Joint api/Joint.cs:182,324,408,412,555,672,720"""
         out = C.c_int32(-1)

@@ -178,6 +178,78 @@ __global__ void k_create_shape(WorldDev d, int shapeId, ShapeDev row, int type, 
   d.shapeAABB[shapeId] = make_float4(aabb.lo.x, aabb.lo.y, aabb.hi.x, aabb.hi.y);
   d.shapeFat[shapeId] = make_float4(fat.lo.x, fat.lo.y, fat.hi.x, fat.hi.y);
 }
+// World.ResetProxy src/Shape.cs:273-301 behind ShapeAPI.SetFilter (api/Shape.cs:157-166) and SetCircle/SetCapsule/SetSegment/SetPolygon
+// (:289-326): the shape's contacts go (contact-list order), the AABBs are recomputed from the body's current transform, and the proxy is
+// either re-created (the leaf and its parent come straight back from the LIFO free list, the move is buffered) or moved.
+__device__ void destroyContactsOf(const WorldDev& d, int bodyId, int shapeId, int endIndex, int* sCount);
+__global__ void k_reset_proxy(WorldDev d, int shapeId, int setGeom, Geom geom, int setFilter, uint64_t categoryBits, uint64_t maskBits, int groupIndex, int destroyProxy, int endIndex) {
+  __shared__ int sCount;
+  Scalars& s = *d.sc;
+  const int bodyId = d.shapes[shapeId].bodyId;
+  destroyContactsOf(d, bodyId, shapeId, endIndex, &sCount);
+  if (threadIdx.x != 0) return;
+  ShapeDev& sh = d.shapes[shapeId];
+  if (setGeom) sh.geom = geom;
+  if (setFilter) { sh.categoryBits = categoryBits; sh.maskBits = maskBits; sh.groupIndex = groupIndex; }
+  float4 xf4 = d.bodyXf[bodyId];
+  Xf xf = mkXf(mk(xf4.x, xf4.y), mkRot(xf4.z, xf4.w));
+  const int key = sh.proxyKey;
+  const int type = key != -1 ? (key & 3) : d.bodyType[bodyId];
+  Box aabb = boxGrow(geomAABB(sh.geom, xf), kSpeculativeDistance);
+  Box fat = boxGrow(aabb, type == kStaticBody ? kSpeculativeDistance : kAABBMargin);
+  d.shapeAABB[shapeId] = make_float4(aabb.lo.x, aabb.lo.y, aabb.hi.x, aabb.hi.y);
+  d.shapeFat[shapeId] = make_float4(fat.lo.x, fat.lo.y, fat.hi.x, fat.hi.y);
+  sh.flags &= ~SF_ENLARGED;
+  if (key == -1) return;
+  const TreeDev& t = d.trees[type];
+  TreeView v{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta};
+  int proxyId = key >> 2;
+  if (destroyProxy) {
+    if (t.moved[proxyId]) {                       // UnBufferMove
+      t.moved[proxyId] = 0;
+      for (int i = 0; i < s.moveCount; i++) if (d.moveArray[i] == key) { d.moveArray[i] = d.moveArray[s.moveCount - 1]; s.moveCount--; break; }
+    }
+    tvRemoveLeaf(v, proxyId); tvFreeNode(v, proxyId); t.meta[3]--;
+    proxyId = tvAllocNode(v);
+    tvSetBox(v, proxyId, fat); t.user[proxyId] = shapeId; t.cat[proxyId] = sh.categoryBits; t.hf[proxyId] = tvPackHF(0, NODE_ALLOCATED | NODE_LEAF); t.moved[proxyId] = 0;
+    tvInsertLeaf(v, proxyId, true); t.meta[3]++;
+    sh.proxyKey = (proxyId << 2) | type;
+  } else tvMoveProxy(v, proxyId, fat);
+  if (!t.moved[proxyId]) {                        // BufferMove (forced for the new proxy, src/BroadPhase.cs:76-77; always after MoveProxy :94)
+    if (s.moveCount < d.moveCapacity) { t.moved[proxyId] = 1; d.moveArray[s.moveCount++] = sh.proxyKey; } else atomicOr(&s.errorFlags, (int)ERR_PAIR_CAPACITY);
+  }
+  if (type == kStaticBody) s.staticRanksValid = 0;
+}
+int World::resetProxy(int shapeId, const Geom* geom, bool setFilter, bool destroyProxy) {
+  HShape& sh = shapes_[shapeId];
+  Geom g; memset(&g, 0, sizeof(g));
+  if (geom) g = *geom;
+  CK(cudaSetDevice(device_));
+  k_reset_proxy<<<1, 256, 0, stream_>>>(d_, shapeId, geom ? 1 : 0, g, setFilter ? 1 : 0, sh.categoryBits, sh.maskBits, sh.groupIndex, destroyProxy ? 1 : 0, endIndex_);
+  CK(cudaGetLastError());
+  eventsFetched_ = false;
+  return B2C_OK;
+}
+int World::setShapeFilter(int shapeId, uint64_t categoryBits, uint64_t maskBits, int groupIndex) {   // ShapeAPI.SetFilter api/Shape.cs:157-166
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  HShape& sh = shapes_[shapeId];
+  if (maskBits == sh.maskBits && categoryBits == sh.categoryBits && groupIndex == sh.groupIndex) return B2C_OK;
+  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "shape_set_filter before the first step: pass the filter in the shape definition");
+  const bool destroyProxy = categoryBits != sh.categoryBits;
+  sh.categoryBits = categoryBits; sh.maskBits = maskBits; sh.groupIndex = groupIndex;
+  return resetProxy(shapeId, nullptr, true, destroyProxy);
+}
+int World::setShapeGeometry(int shapeId, const B2CGeometry& g) {  // ShapeAPI.SetCircle / SetCapsule / SetSegment / SetPolygon api/Shape.cs:289-326
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  if (g.type < 0 || g.type > kPolygon) return fail(B2C_E_UNSUPPORTED, "chain segments are not supported");
+  if (g.type == kPolygon && (g.count < 1 || g.count > kMaxPolygonVertices)) return fail(B2C_E_UNSUPPORTED, "polygon vertex count must be 1..8");
+  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "shape_set_geometry before the first step: create the shape with the geometry it should have");
+  HShape& sh = shapes_[shapeId];
+  memset(&sh.geom, 0, sizeof(Geom));
+  sh.geom.type = g.type; sh.geom.count = g.count; sh.geom.radius = g.radius; sh.geom.centroid = mk(g.centroid.x, g.centroid.y);
+  for (int i = 0; i < kMaxPolygonVertices; i++) { sh.geom.v[i] = mk(g.v[i].x, g.v[i].y); sh.geom.n[i] = mk(g.n[i].x, g.n[i].y); }
+  return resetProxy(shapeId, &sh.geom, false, true);
+}
 void World::treeProxyRemoved(int type) {          // DestroyProxy: the leaf and, unless it was the root, its parent go back to the free list
   if (!onDevice_) return;
   treeNodeCount_[type] -= treeProxyCount_[type] > 1 ? 2 : 1;

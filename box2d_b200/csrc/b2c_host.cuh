@@ -68,6 +68,9 @@ class World {
   int bodyEnableEvents(int bodyId, int which, bool flag);
   int uploadJointLists();
   void treeProxyRemoved(int type);
+  int resetProxy(int shapeId, const Geom* geom, bool setFilter, bool destroyProxy);
+  int setShapeFilter(int shapeId, uint64_t categoryBits, uint64_t maskBits, int groupIndex);
+  int setShapeGeometry(int shapeId, const B2CGeometry& g);
   int jointOp(int jointId, int patch, int which, float a, float b);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }
   int setTransform(int bodyId, V2 p, Rot q);

@@ -193,6 +193,12 @@ int32_t b2cuda_body_apply_mass_from_shapes(B2CWorld* world, int32_t bodyId);
 #define B2C_SHAPE_HIT_EVENTS 1
 int32_t b2cuda_shape_enable_events(B2CWorld* world, int32_t shapeId, int32_t which, int32_t flag);
 int32_t b2cuda_body_enable_events(B2CWorld* world, int32_t bodyId, int32_t which, int32_t flag);
+/* ShapeAPI.SetFilter api/Shape.cs:157-166 and ShapeAPI.SetCircle / SetCapsule / SetSegment / SetPolygon :289-326, both through World.ResetProxy
+ * src/Shape.cs:273-301: the shape's contacts are destroyed (end events in the next step), its AABBs are recomputed from the body's current
+ * transform and the proxy is re-created (new category bits or new geometry) or moved; contacts come back in the next step. The geometry
+ * setters leave the mass alone, as in the reference (call b2cuda_body_apply_mass_from_shapes). Between steps of a stepped world only. */
+int32_t b2cuda_shape_set_filter(B2CWorld* world, int32_t shapeId, uint64_t categoryBits, uint64_t maskBits, int32_t groupIndex);
+int32_t b2cuda_shape_set_geometry(B2CWorld* world, int32_t shapeId, const B2CGeometry* geometry);
 /* Joint mutators — api/Joint.cs. One generic entry per shape of setter; `param` selects the field (B2C_JP_*). Wrong joint type for a
  * field returns B2C_E_INVALID (the reference asserts the type, api/Joint.cs:169-179). After the first step each call is a one-thread
  * patch of the device joint record, ordered on the world's stream (no read-back, no synchronisation).

@@ -91,6 +91,17 @@ int32_t b2o_body_enable_events(World* w, int32_t id, int32_t which, int32_t flag
   for (int sid = w->bodies[id].headShapeId; sid != -1; sid = w->shapes[sid].nextShapeId) b2o_shape_enable_events(w, sid, which, flag);
   return 0;
 }
+int32_t b2o_shape_set_filter(World* w, int32_t id, uint64_t categoryBits, uint64_t maskBits, int32_t groupIndex) {
+  if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1;
+  Filter f; f.categoryBits = categoryBits; f.maskBits = maskBits; f.groupIndex = groupIndex;
+  w->SetFilter(id, f); return 0;
+}
+int32_t b2o_shape_set_geometry(World* w, int32_t id, const B2CGeometry* g) {
+  if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1;
+  Geom geom; geom.type = g->type; geom.count = g->count; geom.radius = g->radius; geom.centroid = V(g->centroid);
+  for (int i = 0; i < kMaxPolygonVertices; i++) { geom.v[i] = V(g->v[i]); geom.n[i] = V(g->n[i]); }
+  w->SetGeometry(id, geom); return 0;
+}
 int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
 int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }
 int32_t b2o_body_set_angular_velocity(World* w, int32_t id, float x) { w->SetAngularVelocity(id, x); return 0; }

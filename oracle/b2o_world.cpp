@@ -432,6 +432,41 @@ void World::DestroyShape(int shapeId, bool updateBodyMass) {      // api/Shape.c
   shape.id = -1;
   if (updateBodyMass) UpdateBodyMassData(body);
 }
+void World::ResetProxy(Shape& shape, bool destroyProxy) {         // src/Shape.cs:273-301
+  Body& body = bodies[shape.bodyId];
+  int shapeId = shape.id;
+  int contactKey = body.headContactKey;
+  while (contactKey != -1) {
+    int contactId = contactKey >> 1, edgeIndex = contactKey & 1;
+    Contact& contact = contacts[contactId];
+    contactKey = edgeIndex == 1 ? contact.edge1.nextKey : contact.edge0.nextKey;
+    if (contact.shapeIdA == shapeId || contact.shapeIdB == shapeId) DestroyContact(contact);
+  }
+  Transform transform = GetBodySim(body).transform;
+  if (shape.proxyKey != -1) {
+    int proxyType = ProxyType(shape.proxyKey);
+    UpdateShapeAABBs(shape, transform, proxyType);
+    if (destroyProxy) {
+      UnBufferMove(shape.proxyKey);                // BroadPhase.DestroyProxy src/BroadPhase.cs:80-86
+      trees[proxyType].DestroyProxy(ProxyId(shape.proxyKey));
+      shape.proxyKey = BroadPhaseCreateProxy(proxyType, shape.fatAABB, shape.filter.categoryBits, shapeId, true);
+    } else {
+      trees[proxyType].MoveProxy(ProxyId(shape.proxyKey), shape.fatAABB); BufferMove(shape.proxyKey);   // src/BroadPhase.cs:89-95
+    }
+  } else UpdateShapeAABBs(shape, transform, body.type);
+}
+void World::SetFilter(int shapeId, Filter filter) {               // api/Shape.cs:157-166
+  Shape& shape = shapes[shapeId];
+  if (filter.maskBits == shape.filter.maskBits && filter.categoryBits == shape.filter.categoryBits && filter.groupIndex == shape.filter.groupIndex) return;
+  bool destroyProxy = filter.categoryBits != shape.filter.categoryBits;
+  shape.filter = filter;
+  ResetProxy(shape, destroyProxy);
+}
+void World::SetGeometry(int shapeId, const Geom& geom) {          // api/Shape.cs:289-326
+  Shape& shape = shapes[shapeId];
+  shape.geom = geom;
+  ResetProxy(shape, true);
+}
 void World::SetDensity(int shapeId, float density, bool updateBodyMass) {      // api/Shape.cs:95-103
   Shape& shape = shapes[shapeId];
   if (density == shape.density) return;

@@ -212,6 +212,9 @@ class World {
   void DestroyBody(int bodyId);            // BodyAPI.DestroyBody api/Body.cs:106-160
   void DestroyShape(int shapeId, bool updateBodyMass);             // ShapeAPI.DestroyShape api/Shape.cs:48-56 -> DestroyShapeInternal src/Shape.cs:219-272
   void SetDensity(int shapeId, float density, bool updateBodyMass);  // ShapeAPI.SetDensity api/Shape.cs:95-103
+  void ResetProxy(Shape& shape, bool destroyProxy);                  // src/Shape.cs:273-301
+  void SetFilter(int shapeId, Filter filter);                        // ShapeAPI.SetFilter api/Shape.cs:157-166
+  void SetGeometry(int shapeId, const Geom& geom);                   // ShapeAPI.SetCircle/SetCapsule/SetSegment/SetPolygon api/Shape.cs:289-326
   void ApplyMassFromShapes(int bodyId);                              // BodyAPI.ApplyMassFromShapes api/Body.cs:617-621
   void UnBufferMove(int proxyKey);         // src/BroadPhase.cs:60-71
   void SetTargetTransform(int bodyId, const Transform& target, float timeStep);

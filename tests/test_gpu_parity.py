@@ -727,3 +727,30 @@ def test_create_joints_between_steps_bit_exact():
                           mutate=lambda w, s: (w.CreateJoint(_jdef(J.JOINT_REVOLUTE, 1, 5, (1.0, 0.0), (0.0, 0.0))),
                                                w.CreateJoint(_jdef(J.JOINT_FILTER, 6, 7, (0.0, 0.0), (0.0, 0.0)))) if s == 8 else None)
     assert res["max_rel_err"] == 0.0
+
+
+def test_set_filter_and_geometry_between_steps_bit_exact():
+    """ShapeAPI.SetFilter (api/Shape.cs:157-166) and SetCircle/SetCapsule/SetSegment/SetPolygon (:289-326) through World.ResetProxy
+    (src/Shape.cs:273-301): mask-only changes move the proxy, category or geometry changes re-create it (same node back from the LIFO free
+    list), the shape's contacts are destroyed first and return in the next step if the filter still lets them."""
+    def mutate(w, step):
+        if step == 6:
+            w.SetFilter(10, 1, 0)                      # mask 0: falls through everything from now on
+            w.SetFilter(12, 2, 0xFFFFFFFFFFFFFFFF)     # new category: proxy re-created, still collides
+            w.SetFilter(16, 1, 0xFFFFFFFFFFFFFFFF, -3)
+            w.SetFilter(17, 1, 0xFFFFFFFFFFFFFFFF, -3)  # same negative group: these two stop colliding with each other
+            w.SetFilter(18, 1, 0xFFFFFFFFFFFFFFFF, 0)   # unchanged: early return
+        elif step == 11:
+            w.SetShapeGeometry(9, geo.Circle((0.0, 0.0), 0.3))
+            w.SetShapeGeometry(11, geo.MakeBox(0.3, 0.1))
+            w.SetShapeGeometry(13, geo.Capsule((-0.25, 0.0), (0.25, 0.0), 0.1))
+            w.ApplyMassFromShapes(5)                   # shape 11's body takes the new mass, the other two keep the old one
+        elif step == 15:
+            w.SetShapeGeometry(3, geo.Segment((-2.0, 0.5), (2.0, 0.9)))      # the static rounded box becomes a ramp
+            w.SetShapeGeometry(5, geo.Capsule((0.0, -1.0), (0.0, 1.0), 0.15))  # the kinematic paddle's capsule grows
+            w.SetFilter(0, 1, 0xFFFFFFFFFFFFFFFE)      # the ground segment ignores category 1: only shape 12's body stays on it
+        elif step == 24:
+            w.SetFilter(0, 1, 0xFFFFFFFFFFFFFFFF)
+            w.SetFilter(10, 1, 0xFFFFFFFFFFFFFFFF)
+    res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=44, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
