@@ -278,6 +278,10 @@ class World:
         """BodyAPI.EnableHitEvents api/Body.cs:862-872"""
         self._check(self.fns["body_enable_events"](self.handle, body_id, capi.SHAPE_HIT_EVENTS, int(bool(flag))))
 
+    def SetType(self, body_id, body_type):
+        """BodyAPI.SetType api/Body.cs:185-268"""
+        self._check(self.fns["body_set_type"](self.handle, body_id, body_type))
+
     def SetFilter(self, shape_id, category_bits, mask_bits, group_index=0):
         """ShapeAPI.SetFilter api/Shape.cs:157-166"""
         self._check(self.fns["shape_set_filter"](self.handle, shape_id, category_bits, mask_bits, group_index))

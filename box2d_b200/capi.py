@@ -153,6 +153,7 @@ PROTOS = {
     "body_apply_mass_from_shapes": [_W, C.c_int32],
     "shape_enable_events": [_W, C.c_int32, C.c_int32, C.c_int32],
     "body_enable_events": [_W, C.c_int32, C.c_int32, C.c_int32],
+    "body_set_type": [_W, C.c_int32, C.c_int32],
     "shape_set_filter": [_W, C.c_int32, C.c_uint64, C.c_uint64, C.c_int32],
     "shape_set_geometry": [_W, C.c_int32, C.POINTER(Geometry)],
     "joint_set_param": [_W, C.c_int32, C.c_int32, C.c_float],

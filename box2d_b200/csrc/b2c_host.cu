@@ -153,6 +153,61 @@ __device__ void treeGrowSerial(const TreeDev& t, int from, int to) {
   t.parent[to - 1] = -1;
   t.meta[2] = from;
 }
+__device__ void destroyProxySerial(const WorldDev& d, int sid);
+// BodyAPI.SetType api/Body.cs:185-268 for a body without joints. k_body_retype: DestroyBodyContacts, Body.type / Body.flags, TransferBody
+// (src/SolverSet.cs:354-376: awake rows appended with an identity state, or closed by swap-remove). k_shape_retype, once per shape in list
+// order: DestroyProxy in the old tree, UpdateAABBs with the new type's margin, CreateProxy (forced move) in the new tree.
+__global__ void k_shape_retype(WorldDev d, int shapeId, int type, int grow0From, int grow0To, int grow1From, int grow1To) {
+  Scalars& s = *d.sc;
+  destroyProxySerial(d, shapeId);
+  ShapeDev& sh = d.shapes[shapeId];
+  float4 xf4 = d.bodyXf[sh.bodyId];
+  Xf xf = mkXf(mk(xf4.x, xf4.y), mkRot(xf4.z, xf4.w));
+  Box aabb = boxGrow(geomAABB(sh.geom, xf), kSpeculativeDistance);
+  Box fat = boxGrow(aabb, type == kStaticBody ? kSpeculativeDistance : kAABBMargin);
+  const TreeDev& t = d.trees[type];
+  TreeView v{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta};
+  treeGrowSerial(t, grow0From, grow0To);
+  int id = tvAllocNode(v);
+  if (id < 0) { atomicOr(&s.errorFlags, (int)ERR_TREE); return; }
+  tvSetBox(v, id, fat); t.user[id] = shapeId; t.cat[id] = sh.categoryBits; t.hf[id] = tvPackHF(0, NODE_ALLOCATED | NODE_LEAF); t.moved[id] = 0;
+  treeGrowSerial(t, grow1From, grow1To);
+  tvInsertLeaf(v, id, true); t.meta[3]++;
+  const int key = (id << 2) | type;
+  if (s.moveCount < d.moveCapacity) { t.moved[id] = 1; d.moveArray[s.moveCount++] = key; } else atomicOr(&s.errorFlags, (int)ERR_PAIR_CAPACITY);
+  if (type == kStaticBody) s.staticRanksValid = 0;
+  sh.proxyKey = key; sh.flags &= ~SF_ENLARGED;
+  d.shapeAABB[shapeId] = make_float4(aabb.lo.x, aabb.lo.y, aabb.hi.x, aabb.hi.y);
+  d.shapeFat[shapeId] = make_float4(fat.lo.x, fat.lo.y, fat.hi.x, fat.hi.y);
+}
+__device__ void destroyContactsOf(const WorldDev& d, int bodyId, int shapeId, int endIndex, int* sCount);
+__global__ void k_body_retype(WorldDev d, int bodyId, int type, int transfer, int newSim, uint32_t bodyFlags, uint32_t simFlags, float linearDamping, float angularDamping, float gravityScale, int endIndex) {
+  __shared__ int sCount;
+  destroyContactsOf(d, bodyId, -1, endIndex, &sCount);
+  if (threadIdx.x != 0) return;
+  d.bodyType[bodyId] = type; d.bodyFlags[bodyId] = bodyFlags;
+  const int sim = d.bodySim[bodyId];
+  if (transfer == 1 && sim >= 0) {                 // awake -> static: bodySims / bodyStates RemoveSwap; the host lowers awakeCount after this launch
+    int last = d.awakeCount - 1;
+    if (sim != last) {
+      d.st0[sim] = d.st0[last]; d.st1[sim] = d.st1[last]; d.simMass[sim] = d.simMass[last]; d.simForce[sim] = d.simForce[last];
+      d.simPose[sim] = d.simPose[last]; d.simLocal[sim] = d.simLocal[last]; d.simPose0[sim] = d.simPose0[last]; d.simFlags[sim] = d.simFlags[last];
+      int movedBody = d.simBodyId[last]; d.simBodyId[sim] = movedBody; d.bodySim[movedBody] = sim;
+    }
+    d.bodySim[bodyId] = -1;
+  } else if (transfer == 2) {                      // static -> awake: the sim is copied, the state starts as identity with Body.flags
+    float4 xf4 = d.bodyXf[bodyId], m = d.bodyMass[bodyId]; float2 c = d.bodyCenter[bodyId];
+    const int i = newSim;
+    d.st0[i] = make_float4(0, 0, 0, __uint_as_float(bodyFlags)); d.st1[i] = make_float4(0, 0, 1, 0);
+    d.simMass[i] = make_float4(m.x, m.y, linearDamping, angularDamping); d.simForce[i] = make_float4(0, 0, 0, gravityScale);
+    d.simPose[i] = make_float4(c.x, c.y, xf4.z, xf4.w); d.simPose0[i] = d.simPose[i];
+    d.simLocal[i] = make_float4(m.z, m.w, kHuge, 0);
+    d.simFlags[i] = simFlags; d.simBodyId[i] = bodyId; d.bodySim[bodyId] = i;
+  } else if (sim >= 0) {                           // dynamic <-> kinematic: `state->flags = body.flags` (:264-265)
+    float4 s0 = d.st0[sim]; s0.w = __uint_as_float(bodyFlags); d.st0[sim] = s0;
+  }
+  d.sc->graphDirty = 1;
+}
 __global__ void k_create_shape(WorldDev d, int shapeId, ShapeDev row, int type, int forceMove, int grow0From, int grow0To, int grow1From, int grow1To) {
   Scalars& s = *d.sc;
   const int bodyId = row.bodyId;
@@ -250,6 +305,58 @@ int World::setShapeGeometry(int shapeId, const B2CGeometry& g) {  // ShapeAPI.Se
   for (int i = 0; i < kMaxPolygonVertices; i++) { sh.geom.v[i] = mk(g.v[i].x, g.v[i].y); sh.geom.n[i] = mk(g.n[i].x, g.n[i].y); }
   return resetProxy(shapeId, &sh.geom, false, true);
 }
+__global__ void k_body_mass_update(WorldDev d, int bodyId, int type, float invMass, float invInertia, V2 localCenter, float minExtent, float maxExtent);
+int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:185-268
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  if (type < kStaticBody || type > kDynamicBody) return fail(B2C_E_INVALID, "bad body type");
+  HBody& b = bodies_[bodyId];
+  const int oldType = b.type;
+  if (oldType == type) return B2C_OK;
+  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "body_set_type before the first step: create the body with the type it should have");
+  if (b.headJointKey != -1) return fail(B2C_E_UNSUPPORTED, "body_set_type on a body that carries joints (joints would pass through the static set) is not supported");
+  const int transfer = type == kStaticBody ? 1 : (oldType == kStaticBody ? 2 : 0);
+  if (transfer == 2 && (int)awakeOrder_.size() >= capAwake_) return fail(B2C_E_CAPACITY, "awake-body rows are full: create the world with a larger B2CWorldDef.bodyCapacity");
+  // growth of the target tree, shape by shape, before anything changes (HostTree::createProxy: ensureFreeNode before each allocation)
+  std::vector<int> sids; std::vector<int> grows;
+  { int cap = d_.trees[type].capacity, nodes = treeNodeCount_[type], proxies = treeProxyCount_[type];
+    for (int sid = b.headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) {
+      int g[4] = {0, 0, 0, 0};
+      if (nodes == cap) { g[0] = cap; cap += cap >> 1; g[1] = cap; }
+      if (nodes + 1 == cap) { g[2] = cap; cap += cap >> 1; g[3] = cap; }
+      nodes += proxies > 0 ? 2 : 1; proxies++;
+      sids.push_back(sid); grows.insert(grows.end(), g, g + 4);
+    }
+    if (cap > treeAllocCap_[type]) return fail(B2C_E_CAPACITY, "broad-phase tree is full: create the world with a larger B2CWorldDef.shapeCapacity");
+  }
+  b.type = type;
+  if (type == kDynamicBody) b.bodyFlags |= kDynamicFlag; else b.bodyFlags &= ~(uint32_t)kDynamicFlag;
+  const uint32_t simFlags = b.flags & ~(uint32_t)(kIsFast | kIsSpeedCapped | kHadTimeOfImpact);
+  const int newSim = transfer == 2 ? (int)awakeOrder_.size() : -1;
+  CK(cudaSetDevice(device_));
+  k_body_retype<<<1, 256, 0, stream_>>>(d_, bodyId, type, transfer, newSim, b.bodyFlags, simFlags, b.linearDamping, b.angularDamping, b.gravityScale, endIndex_);
+  CK(cudaGetLastError());
+  if (transfer == 1) {
+    int last = (int)awakeOrder_.size() - 1;
+    if (b.simIndex != last) { int moved = awakeOrder_[last]; awakeOrder_[b.simIndex] = moved; bodies_[moved].simIndex = b.simIndex; }
+    awakeOrder_.pop_back(); b.simIndex = -1;
+  } else if (transfer == 2) { b.simIndex = newSim; awakeOrder_.push_back(bodyId); }
+  d_.awakeCount = (int)awakeOrder_.size();
+  for (size_t k = 0; k < sids.size(); k++) {
+    const int* g = &grows[4 * k];
+    k_shape_retype<<<1, 1, 0, stream_>>>(d_, sids[k], type, g[0], g[1], g[2], g[3]);
+    CK(cudaGetLastError());
+    if (g[1] > d_.trees[type].capacity) d_.trees[type].capacity = g[1];
+    if (g[3] > d_.trees[type].capacity) d_.trees[type].capacity = g[3];
+    if (shapes_[sids[k]].proxyKey != -1) treeProxyRemoved(oldType);
+    treeNodeCount_[type] += treeProxyCount_[type] > 0 ? 2 : 1; treeProxyCount_[type]++;
+    shapes_[sids[k]].proxyKey = 0;
+  }
+  updateBodyMassData(b);                           // UpdateBodyMassData src/Body.cs:255-353 with the new type
+  k_body_mass_update<<<1, 1, 0, stream_>>>(d_, bodyId, b.type, b.invMass, b.invInertia, b.localCenter, b.minExtent, b.maxExtent);
+  CK(cudaGetLastError());
+  eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false;
+  return B2C_OK;
+}
 void World::treeProxyRemoved(int type) {          // DestroyProxy: the leaf and, unless it was the root, its parent go back to the free list
   if (!onDevice_) return;
   treeNodeCount_[type] -= treeProxyCount_[type] > 1 ? 2 : 1;
@@ -276,6 +383,7 @@ int World::createBody(const B2CBodyDef& def, int* bodyId) {
   b.center = b.xf.p; b.center0 = b.xf.p; b.rot0 = b.xf.q; b.localCenter = mk(0, 0); b.force = mk(0, 0);
   b.linearDamping = def.linearDamping; b.angularDamping = def.angularDamping; b.gravityScale = def.gravityScale;
   b.v = mk(def.linearVelocity.x, def.linearVelocity.y); b.w = def.angularVelocity;
+  b.bodyFlags = b.flags;
   if (def.type != kStaticBody) { b.simIndex = (int)awakeOrder_.size(); awakeOrder_.push_back(id); }
   if ((int)colorMask_.size() <= id) colorMask_.resize(id + 1, 0);
   colorMask_[id] = 0;
@@ -1123,6 +1231,7 @@ int World::bodyOp(int bodyId, int op, V2 a, V2 point) {
     }
     return B2C_OK;
   }
+  if (op == OP_LINEAR_DAMPING) b.linearDamping = a.x; else if (op == OP_ANGULAR_DAMPING) b.angularDamping = a.x; else if (op == OP_GRAVITY_SCALE) b.gravityScale = a.x;
   if (b.simIndex < 0) return B2C_OK;               // static bodies have no solver rows
   CK(cudaSetDevice(device_));
   k_body_op<<<1, 1, 0, stream_>>>(d_, op, b.simIndex, a, point, maxLinearSpeed);
@@ -1252,13 +1361,14 @@ int World::setMotionLocks(int bodyId, bool lx, bool ly, bool az) {
   if (!onDevice_) {
     // before the upload HBody::flags stands for both Body.flags and BodySim.flags: the sim's locks are what the solver reads
     if ((b.flags & allLocks) == newFlags) return B2C_OK;
-    b.flags = (b.flags & ~allLocks) | newFlags;
+    b.flags = (b.flags & ~allLocks) | newFlags; b.bodyFlags |= allLocks;
     if (lx) b.v.x = 0.0f;
     if (ly) b.v.y = 0.0f;
     if (az) b.w = 0.0f;
     lockQuirk_.push_back(bodyId);
     return B2C_OK;
   }
+  if ((b.bodyFlags & allLocks) != newFlags) { b.bodyFlags |= allLocks; b.flags = (b.flags & ~allLocks) | newFlags; }   // the kernel's branch, mirrored for SetType
   CK(cudaSetDevice(device_));
   k_body_motion_locks<<<1, 1, 0, stream_>>>(d_, bodyId, newFlags);
   CK(cudaGetLastError());

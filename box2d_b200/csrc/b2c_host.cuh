@@ -33,7 +33,8 @@ struct HBody {                  // src/Body.cs:35-93 Body + BodySim + BodyState 
   int id = -1, type = kStaticBody, simIndex = -1;
   int headShapeId = -1, shapeCount = 0, headJointKey = -1, jointCount = 0;
   float mass = 0, inertia = 0, sleepThreshold = 0.05f;
-  uint32_t flags = 0; uint16_t generation = 0; uint64_t userData = 0; bool enableSleep = true;
+  uint32_t flags = 0, bodyFlags = 0;      // BodySim.flags (persistent bits) / Body.flags: they part ways in SetMotionLocks (api/Body.cs:807) and SetType (:217-218)
+  uint16_t generation = 0; uint64_t userData = 0; bool enableSleep = true;
   Xf xf; V2 center, center0, localCenter, force; Rot rot0;
   float torque = 0, invMass = 0, invInertia = 0, minExtent = kHuge, maxExtent = 0, linearDamping = 0, angularDamping = 0, gravityScale = 1;
   V2 v; float w = 0;
@@ -71,6 +72,7 @@ class World {
   int resetProxy(int shapeId, const Geom* geom, bool setFilter, bool destroyProxy);
   int setShapeFilter(int shapeId, uint64_t categoryBits, uint64_t maskBits, int groupIndex);
   int setShapeGeometry(int shapeId, const B2CGeometry& g);
+  int setBodyType(int bodyId, int type);
   int jointOp(int jointId, int patch, int which, float a, float b);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }
   int setTransform(int bodyId, V2 p, Rot q);

@@ -467,6 +467,52 @@ void World::SetGeometry(int shapeId, const Geom& geom) {          // api/Shape.c
   shape.geom = geom;
   ResetProxy(shape, true);
 }
+int World::SetType(int bodyId, int type) {        // api/Body.cs:185-268; joints would move through the static set (SolverSet.TransferJoint), not restated
+  Body& body = bodies[bodyId];
+  int originalType = body.type;
+  if (originalType == type) return 0;
+  if (body.headJointKey != -1) return -1;
+  int edgeKey = body.headContactKey;              // DestroyBodyContacts src/Body.cs:232-244
+  while (edgeKey != -1) {
+    int contactId = edgeKey >> 1, edgeIndex = edgeKey & 1;
+    Contact& contact = contacts[contactId];
+    edgeKey = edgeIndex == 1 ? contact.edge1.nextKey : contact.edge0.nextKey;
+    DestroyContact(contact);
+  }
+  body.type = type;
+  if (type == kDynamicBody) body.flags |= kDynamicFlag; else body.flags &= ~(uint32_t)kDynamicFlag;
+  SolverSet& sourceSet = body.setIndex == kStaticSet ? staticSet : awakeSet;
+  const int targetSetIndex = type == kStaticBody ? kStaticSet : kAwakeSet;
+  SolverSet& targetSet = type == kStaticBody ? staticSet : awakeSet;
+  if (&targetSet != &sourceSet) {                 // SolverSet.TransferBody src/SolverSet.cs:354-376
+    int sourceIndex = body.localIndex;
+    BodySim targetSim = sourceSet.bodySims[sourceIndex];
+    targetSim.flags &= ~(uint32_t)(kIsFast | kIsSpeedCapped | kHadTimeOfImpact);
+    int targetIndex = (int)targetSet.bodySims.size();
+    targetSet.bodySims.push_back(targetSim);
+    int movedIndex = RemoveSwap(sourceSet.bodySims, sourceIndex);
+    if (movedIndex != -1) bodies[sourceSet.bodySims[sourceIndex].bodyId].localIndex = sourceIndex;
+    if (body.setIndex == kAwakeSet) RemoveSwap(sourceSet.bodyStates, sourceIndex);
+    else { BodyState st; st.flags = body.flags; targetSet.bodyStates.push_back(st); }
+    body.setIndex = targetSetIndex; body.localIndex = targetIndex;
+  }
+  Transform transform = GetBodySim(body).transform;
+  int shapeId = body.headShapeId;
+  while (shapeId != -1) {
+    Shape& shape = shapes[shapeId];
+    shapeId = shape.nextShapeId;
+    if (shape.proxyKey != -1) {                   // Shape.DestroyProxy src/Shape.cs:128-131
+      UnBufferMove(shape.proxyKey);
+      trees[ProxyType(shape.proxyKey)].DestroyProxy(ProxyId(shape.proxyKey));
+      shape.proxyKey = -1;
+    }
+    UpdateShapeAABBs(shape, transform, type);     // Shape.CreateProxy src/Shape.cs:121-127
+    shape.proxyKey = BroadPhaseCreateProxy(type, shape.fatAABB, shape.filter.categoryBits, shape.id, true);
+  }
+  UpdateBodyMassData(body);
+  if (BodyState* state = GetBodyState(body)) state->flags = body.flags;
+  return 0;
+}
 void World::SetDensity(int shapeId, float density, bool updateBodyMass) {      // api/Shape.cs:95-103
   Shape& shape = shapes[shapeId];
   if (density == shape.density) return;

@@ -754,3 +754,49 @@ def test_set_filter_and_geometry_between_steps_bit_exact():
             w.SetFilter(10, 1, 0xFFFFFFFFFFFFFFFF)
     res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=44, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+def test_set_body_type_between_steps_bit_exact():
+    """BodyAPI.SetType (api/Body.cs:185-268) on bodies without joints: a box frozen to static and released again (it restarts at rest with
+    an identity state, SolverSet.TransferBody), dynamic <-> kinematic in place (velocity kept, mass data recomputed), a spawned static
+    platform turned kinematic, a compound body. Contacts of the body go first (end events), proxies change trees in shape-list order."""
+    def mutate(w, step):
+        if step == 6:
+            w.SetType(5, api.STATIC_BODY)
+            w.SetType(5, api.STATIC_BODY)               # same type: early return
+        elif step == 10:
+            w.SetType(20, api.KINEMATIC_BODY)
+            w.SetLinearVelocity(20, (0.4, 0.0))
+        elif step == 14:
+            w.SetType(5, api.DYNAMIC_BODY)
+            made = _spawn(w, 12.0, 4.0, "static")
+            w.SetMotionLocks(30, False, False, True)
+        elif step == 18:
+            w.SetType(20, api.DYNAMIC_BODY)
+            w.SetType(30, api.STATIC_BODY)
+            w.SetType(37, api.KINEMATIC_BODY)           # the platform spawned at step 14
+            w.SetAngularVelocity(37, 0.3)
+        elif step == 24:
+            w.SetType(30, api.DYNAMIC_BODY)             # comes back with its lock bits (Body.flags carries all three, api/Body.cs:807)
+            w.SetType(36, api.STATIC_BODY)              # the top of the pyramid
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 8), steps=44, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+    def mutate2(w, step):
+        if step == 7:
+            w.SetType(2, api.STATIC_BODY)               # two shapes
+            w.SetType(1, api.DYNAMIC_BODY)              # the kinematic paddle (box + capsule) becomes a free body
+        elif step == 15:
+            w.SetType(2, api.DYNAMIC_BODY)
+            w.SetType(0, api.KINEMATIC_BODY)            # the ground itself: four proxies move from the static to the kinematic tree
+    res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=30, mutate=mutate2, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        scenes.joint_grid(cuda, 4)
+        cuda.Step(1.0 / 60.0, 4)
+        with pytest.raises(Exception, match="joints"):
+            cuda.SetType(3, api.STATIC_BODY)
+    finally:
+        cuda.Destroy()
