@@ -101,7 +101,7 @@ World::~World() { freeDevice(); }
 void World::freeDevice() {
   if (device_ >= 0) cudaSetDevice(device_);
   for (void* p : allocs_) cudaFree(p);
-  allocs_.clear();
+  allocs_.clear(); allocRecs_.clear();
   if (hostScalars_) cudaFreeHost(hostScalars_);
   if (hJointColor_) { cudaFreeHost(hJointColor_); hJointColor_ = nullptr; hJointColorDev_ = nullptr; }
   if (hBegin_) cudaFreeHost(hBegin_);
@@ -315,7 +315,7 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
   if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "body_set_type before the first step: create the body with the type it should have");
   if (b.headJointKey != -1) return fail(B2C_E_UNSUPPORTED, "body_set_type on a body that carries joints (joints would pass through the static set) is not supported");
   const int transfer = type == kStaticBody ? 1 : (oldType == kStaticBody ? 2 : 0);
-  if (transfer == 2 && (int)awakeOrder_.size() >= capAwake_) return fail(B2C_E_CAPACITY, "awake-body rows are full: create the world with a larger B2CWorldDef.bodyCapacity");
+  if (transfer == 2) { int rc = growBodies(0, (int)awakeOrder_.size() + 1); if (rc) return rc; }
   // growth of the target tree, shape by shape, before anything changes (HostTree::createProxy: ensureFreeNode before each allocation)
   std::vector<int> sids; std::vector<int> grows;
   { int cap = d_.trees[type].capacity, nodes = treeNodeCount_[type], proxies = treeProxyCount_[type];
@@ -326,7 +326,7 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
       nodes += proxies > 0 ? 2 : 1; proxies++;
       sids.push_back(sid); grows.insert(grows.end(), g, g + 4);
     }
-    if (cap > treeAllocCap_[type]) return fail(B2C_E_CAPACITY, "broad-phase tree is full: create the world with a larger B2CWorldDef.shapeCapacity");
+    int rc = growTree(type, cap); if (rc) return rc;
   }
   b.type = type;
   if (type == kDynamicBody) b.bodyFlags |= kDynamicFlag; else b.bodyFlags &= ~(uint32_t)kDynamicFlag;
@@ -365,8 +365,8 @@ void World::treeProxyRemoved(int type) {          // DestroyProxy: the leaf and,
 
 int World::createBody(const B2CBodyDef& def, int* bodyId) {
   if (onDevice_) {
-    if (bodyIds_.freeArray.empty() && (int)bodies_.size() >= capBody_) return fail(B2C_E_CAPACITY, "body rows are full: create the world with a larger B2CWorldDef.bodyCapacity");
-    if (def.type != kStaticBody && (int)awakeOrder_.size() >= capAwake_) return fail(B2C_E_CAPACITY, "awake-body rows are full: create the world with a larger B2CWorldDef.bodyCapacity");
+    int rc = growBodies(bodyIds_.freeArray.empty() ? (int)bodies_.size() + 1 : 0, def.type != kStaticBody ? (int)awakeOrder_.size() + 1 : 0);
+    if (rc) return rc;
   }
   if (!def.isEnabled || def.isBullet || !(def.isAwake || !def.enableSleep))
     return fail(B2C_E_UNSUPPORTED, "disabled / bullet / initially-asleep bodies are not supported");
@@ -415,12 +415,12 @@ int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g,
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   int grow[4] = {0, 0, 0, 0}, grownCap = 0;
   if (onDevice_) {                               // every check first: a refused call leaves both sides untouched
-    if (shapeIds_.freeArray.empty() && (int)shapes_.size() >= capShape_) return fail(B2C_E_CAPACITY, "shape rows are full: create the world with a larger B2CWorldDef.shapeCapacity");
+    if (shapeIds_.freeArray.empty()) { int rc = growShapes((int)shapes_.size() + 1); if (rc) return rc; }
     const int t = bodies_[bodyId].type;
     int cap = d_.trees[t].capacity, nodes = treeNodeCount_[t];
     if (nodes == cap) { grow[0] = cap; cap += cap >> 1; grow[1] = cap; }                  // HostTree::createProxy: ensureFreeNode before each allocation
     if (nodes + 1 == cap) { grow[2] = cap; cap += cap >> 1; grow[3] = cap; }
-    if (cap > treeAllocCap_[t]) return fail(B2C_E_CAPACITY, "broad-phase tree is full: create the world with a larger B2CWorldDef.shapeCapacity");
+    { int rc = growTree(t, cap); if (rc) return rc; }
     grownCap = cap;
   }
   if (def.isSensor) return fail(B2C_E_UNSUPPORTED, "sensor shapes are not supported (src/Sensor.cs is out of scope)");
@@ -605,7 +605,7 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
     return fail(B2C_E_INVALID, "distance joint: length must be > 0 and lowerSpringForce <= upperSpringForce");
   int deviceColor = -1;
   if (onDevice_) {                               // the colour first: a refused call must leave both sides as they were
-    if (jointIds_.freeArray.empty() && (int)joints_.size() >= capJoint_) return fail(B2C_E_CAPACITY, "joint rows are full: create the world with a larger B2CWorldDef.jointCapacity");
+    if (jointIds_.freeArray.empty()) { int rc = growJoints((int)joints_.size() + 1); if (rc) return rc; }
     CK(cudaSetDevice(device_));
     k_joint_color<<<1, 1, 0, stream_>>>(d_, bodyA.id, bodyB.id, bodyA.type, bodyB.type, hJointColorDev_);
     CK(cudaGetLastError());
@@ -972,7 +972,111 @@ template <class T> T* World::dalloc(size_t n) {
 }
 
 #define UP(dst, vec) do { if (!(vec).empty()) CK(cudaMemcpyAsync((dst), (vec).data(), (vec).size() * sizeof((vec)[0]), cudaMemcpyHostToDevice, stream_)); } while (0)
-#define DA(ptr, T, n) do { (ptr) = dalloc<T>(n); if (!(ptr)) return fail(B2C_E_CUDA, "cudaMalloc failed for " #ptr); } while (0)
+#define DA(ptr, T, n) do { (ptr) = dalloc<T>(n); if (!(ptr)) return fail(B2C_E_CUDA, "cudaMalloc failed for " #ptr); allocRecs_.push_back({(void**)&(ptr), sizeof(T), std::max<size_t>((size_t)(n), 1)}); } while (0)
+
+// ---- growth between steps ---------------------------------------------------------------------------------------------------------
+// The reference's lists grow on demand (List<T>, the tree's x1.5 node pool). Here a creation call that finds its class of rows full
+// re-allocates that class at x1.5 on the world's stream — new array, zero fill, device-to-device copy of the old rows, member pointer
+// swapped — before it touches anything else. Kernels take WorldDev by value, so the next launch simply sees the new pointers (a cached
+// CUDA graph is keyed by WorldDev and is re-captured). Contact-sized arrays do not grow: their capacity error stays loud.
+int World::regrow(void** slot, size_t newCount, int fillByte) {
+  for (AllocRec& r : allocRecs_) {
+    if (r.slot != slot) continue;
+    if (newCount <= r.count) return B2C_OK;
+    void* p = nullptr;
+    if (cudaMalloc(&p, newCount * r.elem) != cudaSuccess) { cudaGetLastError(); return fail(B2C_E_CUDA, "cudaMalloc failed while growing a device array"); }
+    CK(cudaMemsetAsync(p, fillByte, newCount * r.elem, stream_));
+    void* old = *slot;
+    CK(cudaMemcpyAsync(p, old, r.count * r.elem, cudaMemcpyDeviceToDevice, stream_));
+    CK(cudaStreamSynchronize(stream_));
+    cudaFree(old);
+    for (void*& a : allocs_) if (a == old) a = p;
+    *slot = p; r.count = newCount;
+    for (auto& g : graphs_) { if (g.exec) cudaGraphExecDestroy(g.exec); for (auto& e : g.ev) if (e) cudaEventDestroy(e); }
+    graphs_.clear();                               // captured launches hold the old pointers
+    return B2C_OK;
+  }
+  return fail(B2C_E_INVALID, "regrow: unknown device array");
+}
+#define RG(ptr, n) do { int rc_ = regrow((void**)&(ptr), (size_t)(n)); if (rc_) return rc_; } while (0)
+#define RGF(ptr, n, fill) do { int rc_ = regrow((void**)&(ptr), (size_t)(n), fill); if (rc_) return rc_; } while (0)
+int World::growScanScratch() {
+  int scanBlocks = std::max(std::max(d_.contactCapacity, d_.bigScratch), std::max(d_.moveCapacity, capAwake_)) / 256 + 2;
+  RG(d_.scanBlockSums, scanBlocks); RG(d_.scanBlockSums4, scanBlocks);
+  return B2C_OK;
+}
+int World::growBodies(int minBodies, int minAwake) {
+  WorldDev& d = d_;
+  CK(cudaSetDevice(device_));
+  if (minBodies > capBody_) {
+    const int c = std::max(minBodies, capBody_ + capBody_ / 2);
+    RG(d.bodyXf, c); RG(d.bodyMass, c); RG(d.bodyCenter, c); RG(d.bodySim, c); RG(d.bodyType, c); RG(d.bodyHeadShape, c); RG(d.bodyHeadJoint, c);
+    RG(d.bodyJointCount, c); RG(d.bodyColorMask, c); RGF(d.bodyMinOp, c, 0x7f); RG(d.bodySleepThreshold, c); RG(d.bodyFlags, c); RG(dBodyRead_, c);
+    if (hBodyRead_) cudaFreeHost(hBodyRead_);
+    hBodyRead_ = nullptr;
+    CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)c, cudaHostAllocDefault));
+    if (d.bodyOut) d.bodyOut = dBodyRead_;
+    bodiesFetched_ = false;
+    capBody_ = c;
+  }
+  if (minAwake > capAwake_) {
+    const int c = std::max(minAwake, capAwake_ + capAwake_ / 2);
+    RG(d.st0, c); RG(d.st1, c); RG(d.simMass, c); RG(d.simForce, c); RG(d.simPose, c); RG(d.simLocal, c); RG(d.simPose0, c); RG(d.simFlags, c); RG(d.simBodyId, c);
+    RG(d.ufParent, c); RG(d.rootBodyCount, c); RG(d.rootConCount, c); RG(d.rootColorCount, (size_t)c * kGraphColorCount);
+    RG(d.rootInfo, c); RG(d.rootScan, c + 1); RG(d.islandBodyStart, c + 1); RG(d.islandConStart, c + 1);
+    RG(d.islandColorOff, (size_t)(c + 1) * (kGraphColorCount + 1)); RG(d.islandBodies, c); RG(d.bodyLocal, c);
+    RG(d.freeBodies, c); RG(d.bigBodies, c); RG(d.kinematicUsed, c); RG(d.bodyEnlargedCount, c + 1); RG(dMoveEvents_, c);
+    if (hMoveEvents_) cudaFreeHost(hMoveEvents_);
+    hMoveEvents_ = nullptr;
+    CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)c, cudaHostAllocMapped));
+    if (hMoveEventsDev_ && cudaHostGetDevicePointer((void**)&hMoveEventsDev_, hMoveEvents_, 0) != cudaSuccess) { hMoveEventsDev_ = nullptr; cudaGetLastError(); }
+    if (d.moveOut) d.moveOut = hMoveEventsDev_ ? hMoveEventsDev_ : dMoveEvents_;
+    movesFetched_ = false;
+    capAwake_ = c;
+    int rc = growScanScratch(); if (rc) return rc;
+  }
+  return B2C_OK;
+}
+int World::growShapes(int minShapes) {
+  if (minShapes <= capShape_) return B2C_OK;
+  WorldDev& d = d_;
+  CK(cudaSetDevice(device_));
+  const int c = std::max(minShapes, capShape_ + capShape_ / 2), extra = c - capShape_;
+  RG(d.shapes, c); RG(d.shapeAABB, c); RG(d.shapeFat, c);
+  const int m = d.moveCapacity + extra;              // every new shape may sit in the move buffer
+  RG(d.moveArray, m); RG(d.moveHitCount, m + 1); RG(d.moveBig, m); RG(d.moveHitBuf, (size_t)m * 4);
+  d.moveCapacity = m;
+  capShape_ = c;
+  return growScanScratch();
+}
+int World::growJoints(int minJoints) {
+  if (minJoints <= capJoint_) return B2C_OK;
+  WorldDev& d = d_;
+  CK(cudaSetDevice(device_));
+  const int c = std::max(minJoints, capJoint_ + capJoint_ / 2);
+  RG(d.joints, c); RG(d.jointEdges, c); RG(d.jointCollide, c); RG(d.jointSorted, c); RG(d.jointEventFlag, c);
+  if (hJointEvents_) cudaFreeHost(hJointEvents_);
+  hJointEvents_ = nullptr;
+  CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)c, cudaHostAllocDefault));
+  capJoint_ = c;
+  return B2C_OK;
+}
+int World::growTree(int type, int minNodes) {      // the allocation behind the tree's logical capacity (which follows the reference's x1.5 steps)
+  if (minNodes <= treeAllocCap_[type]) return B2C_OK;
+  TreeDev& td = d_.trees[type];
+  CK(cudaSetDevice(device_));
+  int cap = treeAllocCap_[type];
+  while (cap < minNodes) cap += cap >> 1;
+  RG(td.aabb, cap); RG(td.child, cap); RG(td.parent, cap); RG(td.hf, cap); RG(td.cat, cap); RG(td.user, cap); RG(td.moved, cap); RG(td.leafIdx, cap); RG(td.leafCtr, cap);
+  RG(td.segStart, cap); RG(td.recEnd, cap + 1); RG(td.recNode, cap + 1); RG(td.recSplit, cap + 1); RG(td.recBox, cap + 1);
+  RG(td.flagScan, cap + 1); RG(td.flagArr, cap + 1); RG(td.pairR, cap + 1); RG(td.freeIds, cap + 1); RG(td.subCount, cap);
+  RG(td.visit, cap); RG(td.serialList, cap + 1);
+  RG(td.recEnd2, cap + 1); RG(td.recNode2, cap + 1); RG(td.recBox2, cap + 1); RG(td.recM, cap + 1); RG(td.serEnd, cap + 1); RG(td.serNode, cap + 1);
+  treeAllocCap_[type] = cap;
+  int sumCap = 0; for (int t = 0; t < 3; t++) sumCap += treeAllocCap_[t];
+  if (sumCap > d_.bigScratch) { RG(d_.bigScan, sumCap); RG(d_.bigFlag, sumCap); d_.bigScratch = sumCap; }
+  return growScanScratch();
+}
 
 int World::upload() {
   CK(cudaSetDevice(device_));

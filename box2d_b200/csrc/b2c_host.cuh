@@ -146,6 +146,14 @@ class World {
   // device state
   WorldDev d_{};
   std::vector<void*> allocs_;
+  struct AllocRec { void** slot; size_t elem, count; };
+  std::vector<AllocRec> allocRecs_;     // every device array with the member that points at it: lets a class of arrays grow between steps
+  int regrow(void** slot, size_t newCount, int fillByte = 0);
+  int growBodies(int minBodies, int minAwake);
+  int growShapes(int minShapes);
+  int growJoints(int minJoints);
+  int growTree(int type, int minNodes);
+  int growScanScratch();
   Scalars* hostScalars_ = nullptr;     // pinned
   int endIndex_ = 0;
   int stepCount_ = 0;

@@ -174,8 +174,9 @@ int32_t b2cuda_create_joint(B2CWorld* world, const B2CJointDef* def, int32_t* jo
  * stepped (destroy_joint also before). b2cuda_create_body / b2cuda_create_shape / b2cuda_create_joint also work between steps after the first
  * one (the joint's colour is assigned against the device's colour bitsets, contacts between its bodies are destroyed unless collideConnected): rows
  * are reserved at the first step (a quarter more than the world holds then, at least 256, or B2CWorldDef.bodyCapacity / shapeCapacity /
- * jointCapacity);
- * past the reservation the call fails with B2C_E_CAPACITY and changes nothing. */
+ * jointCapacity) and, when a class of rows is full, re-allocated at x1.5 on the world's stream before the call touches anything — as the
+ * reference's lists grow. Pointers handed out by the event getters are then stale, as after a step. Contact-sized buffers do not grow
+ * (B2CWorldDef.contactCapacity, default 12 per shape present at the first step): their overflow is reported as B2C_E_CAPACITY. */
 int32_t b2cuda_destroy_joint(B2CWorld* world, int32_t jointId, int32_t wakeAttached);
 int32_t b2cuda_destroy_body(B2CWorld* world, int32_t bodyId);
 /* ShapeAPI.DestroyShape api/Shape.cs:48-56 (DestroyShapeInternal src/Shape.cs:219-272: the shape leaves its body's list, its proxy leaves the tree,

@@ -646,31 +646,51 @@ def test_create_bodies_and_shapes_between_steps_bit_exact():
     assert res["bodies"] == 37 + 3 + 3 + 12
 
 
-def test_create_many_bodies_grows_the_device_trees():
-    """Spawning more proxies than the tree's node pool holds: the pool grows by the reference's x1.5 steps inside the rows allocated at
-    upload (B2CWorldDef.bodyCapacity / shapeCapacity); past the allocation the call fails loudly and changes nothing."""
-    wd = scenes.world_def()
-    wd.bodyCapacity, wd.shapeCapacity = 2000, 2000
-
+def test_create_many_bodies_grows_the_device_arrays():
+    """Spawning far more than the rows reserved at upload (default: a quarter more, at least 256): body, awake, shape, move-buffer and
+    tree arrays are re-allocated at x1.5 between steps, the tree's node pool follows the reference's own x1.5 steps inside them, and the
+    step stays bit-exact. Also with rows reserved up front through the world definition, and with move/body events streaming."""
     def mutate(w, step):
-        if step in (3, 6, 9):
+        if step in (3, 6, 9, 12):
             for k in range(150):
                 _spawn(w, -30.0 + 0.41 * k, 6.0 + (k % 5) * 1.1 + step, ("box", "circle")[k % 2])
-    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 5), steps=24, world_def=wd, mutate=mutate, verbose=True)
+        if step == 5:
+            w.GetBodyMoveEvents()                        # from here on the step streams the events: the buffers must follow the growth
+            w.GetBodyEvents()
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 5), steps=26, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0 and res["bodies"] == 16 + 600
+
+    wd = scenes.world_def()
+    wd.bodyCapacity, wd.shapeCapacity = 2000, 2000
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 5), steps=16, world_def=wd, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
 
     cuda = api.World(api.CudaBackend(), scenes.world_def())
     try:
         scenes.add_pyramid(cuda, 3)
         cuda.Step(1.0 / 60.0, 4)
-        with pytest.raises(Exception, match="bodyCapacity"):
-            for k in range(400):
-                _spawn(cuda, float(k), 30.0, "circle")
-        n = cuda.GetCounters().bodyCount
+        for k in range(700):
+            _spawn(cuda, float(k), 30.0, "circle")
         cuda.Step(1.0 / 60.0, 4)
-        assert cuda.GetCounters().bodyCount == n and len(cuda.GetBodyMoveEvents()) == n - 1
+        n = cuda.GetCounters().bodyCount
+        assert n == 7 + 700 and len(cuda.GetBodyMoveEvents()) == n - 1 and len(cuda.GetBodyEvents()) == n
+        moves = cuda.GetBodyMoveEvents()
+        assert sorted(moves["bodyId"].tolist()) == list(range(1, n))
     finally:
         cuda.Destroy()
+
+
+def test_create_many_joints_grows_the_joint_rows():
+    from box2d_b200 import capi as J
+
+    def mutate(w, step):
+        if step == 4:
+            for k in range(300):                         # chains the boxes of the pile pairwise, far past the 256 reserved joint rows
+                d = _jdef(J.JOINT_DISTANCE, 2 + k, 3 + k, (0.0, 0.0), (0.0, 0.0))
+                d.length, d.enableSpring, d.hertz, d.dampingRatio, d.collideConnected = 0.6, 1, 4.0, 0.5, 1
+                w.CreateJoint(d)
+    res = parity.run_pair(lambda w: scenes.tumbler(w, 400), steps=14, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
 
 
 def _jdef(t, a, b, pa, pb):
