@@ -289,7 +289,7 @@ int World::setShapeFilter(int shapeId, uint64_t categoryBits, uint64_t maskBits,
   if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
   HShape& sh = shapes_[shapeId];
   if (maskBits == sh.maskBits && categoryBits == sh.categoryBits && groupIndex == sh.groupIndex) return B2C_OK;
-  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "shape_set_filter before the first step: pass the filter in the shape definition");
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }   // the first call that needs the device state uploads the world (as the first step would)
   const bool destroyProxy = categoryBits != sh.categoryBits;
   sh.categoryBits = categoryBits; sh.maskBits = maskBits; sh.groupIndex = groupIndex;
   return resetProxy(shapeId, nullptr, true, destroyProxy);
@@ -298,7 +298,7 @@ int World::setShapeGeometry(int shapeId, const B2CGeometry& g) {  // ShapeAPI.Se
   if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
   if (g.type < 0 || g.type > kPolygon) return fail(B2C_E_UNSUPPORTED, "chain segments are not supported");
   if (g.type == kPolygon && (g.count < 1 || g.count > kMaxPolygonVertices)) return fail(B2C_E_UNSUPPORTED, "polygon vertex count must be 1..8");
-  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "shape_set_geometry before the first step: create the shape with the geometry it should have");
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }   // the first call that needs the device state uploads the world (as the first step would)
   HShape& sh = shapes_[shapeId];
   memset(&sh.geom, 0, sizeof(Geom));
   sh.geom.type = g.type; sh.geom.count = g.count; sh.geom.radius = g.radius; sh.geom.centroid = mk(g.centroid.x, g.centroid.y);
@@ -312,7 +312,7 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
   HBody& b = bodies_[bodyId];
   const int oldType = b.type;
   if (oldType == type) return B2C_OK;
-  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "body_set_type before the first step: create the body with the type it should have");
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }   // the first call that needs the device state uploads the world (as the first step would)
   if (b.headJointKey != -1) return fail(B2C_E_UNSUPPORTED, "body_set_type on a body that carries joints (joints would pass through the static set) is not supported");
   const int transfer = type == kStaticBody ? 1 : (oldType == kStaticBody ? 2 : 0);
   if (transfer == 2) { int rc = growBodies(0, (int)awakeOrder_.size() + 1); if (rc) return rc; }
@@ -827,7 +827,7 @@ int World::uploadJointLists() {                  // joint edges, per-body list h
 }
 int World::destroyBody(int bodyId) {             // BodyAPI.DestroyBody api/Body.cs:106-160
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
-  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "destroy_body before the first step is not supported in this build (the world is still being assembled on the host)");
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }   // the first call that needs the device state uploads the world (as the first step would)
   HBody& b = bodies_[bodyId];
   int edgeKey = b.headJointKey;
   while (edgeKey != -1) {
@@ -872,7 +872,7 @@ int World::setShapeDensity(int shapeId, float density, bool updateBodyMass) {   
 }
 int World::destroyShape(int shapeId, bool updateBodyMass) {      // ShapeAPI.DestroyShape api/Shape.cs:48-56, DestroyShapeInternal src/Shape.cs:219-272
   if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
-  if (!onDevice_) return fail(B2C_E_UNSUPPORTED, "destroy_shape before the first step is not supported in this build (the world is still being assembled on the host)");
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }   // the first call that needs the device state uploads the world (as the first step would)
   HShape& s = shapes_[shapeId];
   HBody& body = bodies_[s.bodyId];
   const int prev = s.prevShapeId, next = s.nextShapeId, bodyId = s.bodyId;

@@ -517,8 +517,6 @@ def test_destroy_rejects_stale_ids_and_reports_counts():
     cuda = api.World(api.CudaBackend(), scenes.world_def())
     try:
         scenes.add_pyramid(cuda, 4)
-        with pytest.raises(Exception):
-            cuda.DestroyBody(3)                                     # before the first step: unsupported, said loudly
         cuda.Step(1.0 / 60.0, 4)
         cuda.DestroyBody(3)
         with pytest.raises(Exception):
@@ -820,3 +818,20 @@ def test_set_body_type_between_steps_bit_exact():
             cuda.SetType(3, api.STATIC_BODY)
     finally:
         cuda.Destroy()
+
+
+def test_mutators_before_the_first_step_bit_exact():
+    """Destroying, re-typing and re-shaping before the world was ever stepped: the first such call uploads the world (as the first step
+    would) and runs the device path; creation afterwards goes through the after-upload kernels. Same result as the reference."""
+    def build(w):
+        scenes.add_pyramid(w, 7)
+        w.DestroyBody(4)
+        w.DestroyShape(9, True)
+        w.SetType(12, api.STATIC_BODY)
+        w.SetFilter(15, 2, 0xFFFFFFFFFFFFFFFF)
+        w.SetShapeGeometry(16, geo.Circle((0.0, 0.0), 0.5))
+        w.ApplyMassFromShapes(16)
+        assert _spawn(w, 0.0, 12.0, "compound") == 4
+        _spawn(w, 2.0, 13.0, "box")
+    res = parity.run_pair(build, steps=30, verbose=True)
+    assert res["max_rel_err"] == 0.0
