@@ -139,7 +139,7 @@ struct BodyRows {
 __global__ void k_create_body(WorldDev d, int id, BodyRows r) {
   d.bodyXf[id] = r.bodyXf; d.bodyMass[id] = r.bodyMass; d.bodyCenter[id] = r.bodyCenter; d.bodySim[id] = r.sim; d.bodyType[id] = r.type;
   d.bodyHeadShape[id] = -1; d.bodyHeadJoint[id] = -1; d.bodyJointCount[id] = 0; d.bodyColorMask[id] = 0; d.bodyMinOp[id] = 0x7f7f7f7f;
-  d.bodySleepThreshold[id] = r.sleepThreshold; d.bodyFlags[id] = r.flags;
+  d.bodySleepThreshold[id] = r.sleepThreshold; d.bodyFlags[id] = r.flags; d.bodySimFlags[id] = r.flags;
   if (r.sim < 0) return;
   const int i = r.sim;
   d.st0[i] = r.st0; d.st1[i] = r.st1; d.simMass[i] = r.simMass; d.simForce[i] = r.simForce; d.simPose[i] = r.simPose; d.simLocal[i] = r.simLocal;
@@ -188,6 +188,7 @@ __global__ void k_body_retype(WorldDev d, int bodyId, int type, int transfer, in
   d.bodyType[bodyId] = type; d.bodyFlags[bodyId] = bodyFlags;
   const int sim = d.bodySim[bodyId];
   if (transfer == 1 && sim >= 0) {                 // awake -> static: bodySims / bodyStates RemoveSwap; the host lowers awakeCount after this launch
+    d.bodySimFlags[bodyId] = d.simFlags[sim] & ~(uint32_t)(kIsFast | kIsSpeedCapped | kHadTimeOfImpact);
     int last = d.awakeCount - 1;
     if (sim != last) {
       d.st0[sim] = d.st0[last]; d.st1[sim] = d.st1[last]; d.simMass[sim] = d.simMass[last]; d.simForce[sim] = d.simForce[last];
@@ -202,7 +203,7 @@ __global__ void k_body_retype(WorldDev d, int bodyId, int type, int transfer, in
     d.simMass[i] = make_float4(m.x, m.y, linearDamping, angularDamping); d.simForce[i] = make_float4(0, 0, 0, gravityScale);
     d.simPose[i] = make_float4(c.x, c.y, xf4.z, xf4.w); d.simPose0[i] = d.simPose[i];
     d.simLocal[i] = make_float4(m.z, m.w, kHuge, 0);
-    d.simFlags[i] = simFlags; d.simBodyId[i] = bodyId; d.bodySim[bodyId] = i;
+    d.simFlags[i] = d.bodySimFlags[bodyId] & ~(uint32_t)(kIsFast | kIsSpeedCapped | kHadTimeOfImpact); d.simBodyId[i] = bodyId; d.bodySim[bodyId] = i;
   } else if (sim >= 0) {                           // dynamic <-> kinematic: `state->flags = body.flags` (:264-265)
     float4 s0 = d.st0[sim]; s0.w = __uint_as_float(bodyFlags); d.st0[sim] = s0;
   }
@@ -1011,7 +1012,7 @@ int World::growBodies(int minBodies, int minAwake) {
   if (minBodies > capBody_) {
     const int c = std::max(minBodies, capBody_ + capBody_ / 2);
     RG(d.bodyXf, c); RG(d.bodyMass, c); RG(d.bodyCenter, c); RG(d.bodySim, c); RG(d.bodyType, c); RG(d.bodyHeadShape, c); RG(d.bodyHeadJoint, c);
-    RG(d.bodyJointCount, c); RG(d.bodyColorMask, c); RGF(d.bodyMinOp, c, 0x7f); RG(d.bodySleepThreshold, c); RG(d.bodyFlags, c); RG(dBodyRead_, c);
+    RG(d.bodyJointCount, c); RG(d.bodyColorMask, c); RGF(d.bodyMinOp, c, 0x7f); RG(d.bodySleepThreshold, c); RG(d.bodyFlags, c); RG(d.bodySimFlags, c); RG(dBodyRead_, c);
     if (hBodyRead_) cudaFreeHost(hBodyRead_);
     hBodyRead_ = nullptr;
     CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)c, cudaHostAllocDefault));
@@ -1128,9 +1129,10 @@ int World::upload() {
   colorMask_.resize(nBody, 0);
   DA(d.bodyXf, float4, capBody); DA(d.bodyMass, float4, capBody); DA(d.bodyCenter, float2, capBody); DA(d.bodySim, int, capBody); DA(d.bodyType, int, capBody);
   DA(d.bodyHeadShape, int, capBody); DA(d.bodyHeadJoint, int, capBody); DA(d.bodyJointCount, int, capBody); DA(d.bodyColorMask, uint32_t, capBody);
-  DA(d.bodyMinOp, int, capBody); DA(d.bodySleepThreshold, float, capBody); DA(d.bodyFlags, uint32_t, capBody);
+  DA(d.bodyMinOp, int, capBody); DA(d.bodySleepThreshold, float, capBody); DA(d.bodyFlags, uint32_t, capBody); DA(d.bodySimFlags, uint32_t, capBody);
   UP(d.bodyXf, bodyXf); UP(d.bodyMass, bodyMass); UP(d.bodyCenter, bodyCenter); UP(d.bodySim, bodySim); UP(d.bodyType, bodyType);
   UP(d.bodyHeadShape, bodyHeadShape); UP(d.bodyHeadJoint, bodyHeadJoint); UP(d.bodyJointCount, bodyJointCount); UP(d.bodyColorMask, colorMask_);
+  { std::vector<uint32_t> sf(nBody); for (int i = 0; i < nBody; i++) sf[i] = bodies_[i].flags; UP(d.bodySimFlags, sf); CK(cudaStreamSynchronize(stream_)); }
   UP(d.bodySleepThreshold, bodySleep); UP(d.bodyFlags, bodyFlags);
   CK(cudaMemsetAsync(d.bodyMinOp, 0x7f, sizeof(int) * (size_t)std::max(capBody, 1), stream_));
   // ---- shapes ----
@@ -1414,7 +1416,7 @@ __global__ void k_body_motion_locks(WorldDev d, int bodyId, uint32_t newFlags) {
   if ((bf & allLocks) == newFlags) return;
   d.bodyFlags[bodyId] = bf | allLocks;                     // `body.flags |= allLocks` as written (api/Body.cs:807)
   int sim = d.bodySim[bodyId];
-  if (sim < 0) return;
+  if (sim < 0) { d.bodySimFlags[bodyId] = (d.bodySimFlags[bodyId] & ~allLocks) | newFlags; return; }      // the static sim's flags (:809-810)
   uint32_t sf = (d.simFlags[sim] & ~allLocks) | newFlags;
   d.simFlags[sim] = sf;
   float4 s0 = d.st0[sim];
@@ -1530,15 +1532,15 @@ int World::readBodies(B2CBodyRead* dst, int capacity, int* count) {
     return B2C_OK;
   }
   int rc = synchronize(); if (rc) return rc;
-  std::vector<float4> xf, st0; std::vector<float2> ctr; std::vector<uint32_t> sf;
-  if (fetch(xf, d_.bodyXf, n, stream_) | fetch(ctr, d_.bodyCenter, n, stream_) | fetch(st0, d_.st0, d_.awakeCount, stream_) | fetch(sf, d_.simFlags, d_.awakeCount, stream_))
+  std::vector<float4> xf, st0; std::vector<float2> ctr; std::vector<uint32_t> sf, bsf;
+  if (fetch(bsf, d_.bodySimFlags, n, stream_) | fetch(xf, d_.bodyXf, n, stream_) | fetch(ctr, d_.bodyCenter, n, stream_) | fetch(st0, d_.st0, d_.awakeCount, stream_) | fetch(sf, d_.simFlags, d_.awakeCount, stream_))
     return fail(B2C_E_CUDA, "read_bodies copy failed");
   CK(cudaStreamSynchronize(stream_));
   for (int i = 0; i < n && i < capacity; i++) {
     const HBody& b = bodies_[i]; B2CBodyRead r; memset(&r, 0, sizeof(r));
     if (b.id != -1) {
       r.transform.p = {xf[i].x, xf[i].y}; r.transform.q = {xf[i].z, xf[i].w}; r.center = {ctr[i].x, ctr[i].y};
-      r.flags = b.flags;
+      r.flags = bsf[i];
       if (b.simIndex >= 0) { float4 s = st0[b.simIndex]; r.linearVelocity = {s.x, s.y}; r.angularVelocity = s.z; r.flags = sf[b.simIndex]; }
     }
     dst[i] = r;
@@ -1557,6 +1559,7 @@ int World::readBody(int bodyId, B2CBodyRead* out) {
   }
   int rc = synchronize(); if (rc) return rc;
   float4 xf; float2 ctr; float4 s = make_float4(0, 0, 0, 0); uint32_t sf = b.flags;
+  CK(cudaMemcpyAsync(&sf, &d_.bodySimFlags[bodyId], sizeof(sf), cudaMemcpyDeviceToHost, stream_));
   CK(cudaMemcpyAsync(&xf, &d_.bodyXf[bodyId], sizeof(xf), cudaMemcpyDeviceToHost, stream_));
   CK(cudaMemcpyAsync(&ctr, &d_.bodyCenter[bodyId], sizeof(ctr), cudaMemcpyDeviceToHost, stream_));
   if (b.simIndex >= 0) {

@@ -1535,7 +1535,7 @@ __global__ void __launch_bounds__(kThreads) k_pack_bodies(WorldDev d, B2CBodyRea
     r.transform.p = {xf.x, xf.y}; r.transform.q = {xf.z, xf.w}; r.center = {c.x, c.y};
     int sim = d.bodySim[i];
     if (sim >= 0) { float4 s = d.st0[sim]; r.linearVelocity = {s.x, s.y}; r.angularVelocity = s.z; r.flags = d.simFlags[sim]; }
-    else { r.linearVelocity = {0.0f, 0.0f}; r.angularVelocity = 0.0f; r.flags = d.bodyFlags[i]; }
+    else { r.linearVelocity = {0.0f, 0.0f}; r.angularVelocity = 0.0f; r.flags = d.bodySimFlags[i]; }
     out[i] = r;
   }
 }
