@@ -307,6 +307,9 @@ int World::setShapeGeometry(int shapeId, const B2CGeometry& g) {  // ShapeAPI.Se
   return resetProxy(shapeId, &sh.geom, false, true);
 }
 __global__ void k_body_mass_update(WorldDev d, int bodyId, int type, float invMass, float invInertia, V2 localCenter, float minExtent, float maxExtent);
+__global__ void k_joint_color(WorldDev d, int bodyIdA, int bodyIdB, int typeA, int typeB, int* out);
+__global__ void k_joint_set_color(WorldDev d, int jointId, int color);
+__global__ void k_joint_removed(WorldDev d, int bodyIdA, int bodyIdB, int color);
 int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:185-268
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   if (type < kStaticBody || type > kDynamicBody) return fail(B2C_E_INVALID, "bad body type");
@@ -314,7 +317,8 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
   const int oldType = b.type;
   if (oldType == type) return B2C_OK;
   if (!onDevice_) { int rc = upload(); if (rc) return rc; }   // the first call that needs the device state uploads the world (as the first step would)
-  if (b.headJointKey != -1) return fail(B2C_E_UNSUPPORTED, "body_set_type on a body that carries joints (joints would pass through the static set) is not supported");
+  std::vector<int> jids;                           // the body's joints in list order
+  for (int key = b.headJointKey; key != -1;) { const HJoint& j = joints_[key >> 1]; jids.push_back(key >> 1); key = (key & 1) ? j.nextKeyB : j.nextKeyA; }
   const int transfer = type == kStaticBody ? 1 : (oldType == kStaticBody ? 2 : 0);
   if (transfer == 2) { int rc = growBodies(0, (int)awakeOrder_.size() + 1); if (rc) return rc; }
   // growth of the target tree, shape by shape, before anything changes (HostTree::createProxy: ensureFreeNode before each allocation)
@@ -329,6 +333,17 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
     }
     int rc = growTree(type, cap); if (rc) return rc;
   }
+  CK(cudaSetDevice(device_));
+  for (int jid : jids) {                            // :202-216 TransferJoint(staticSet <- graph): colour bits and the colour array give the joint up
+    HJoint& j = joints_[jid];
+    if (!j.inGraph) continue;
+    const int color = j.sim.colorIndex;
+    std::vector<int>& arr = colorJoints_[color];
+    for (size_t k = 0; k < arr.size(); k++) if (arr[k] == jid) { arr[k] = arr.back(); arr.pop_back(); break; }
+    k_joint_removed<<<1, 1, 0, stream_>>>(d_, j.bodyIdA, j.bodyIdB, color);
+    CK(cudaGetLastError());
+    j.inGraph = false; j.sim.colorIndex = -1;
+  }
   b.type = type;
   if (type == kDynamicBody) b.bodyFlags |= kDynamicFlag; else b.bodyFlags &= ~(uint32_t)kDynamicFlag;
   const uint32_t simFlags = b.flags & ~(uint32_t)(kIsFast | kIsSpeedCapped | kHadTimeOfImpact);
@@ -342,6 +357,22 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
     awakeOrder_.pop_back(); b.simIndex = -1;
   } else if (transfer == 2) { b.simIndex = newSim; awakeOrder_.push_back(bodyId); }
   d_.awakeCount = (int)awakeOrder_.size();
+  int parkedOverflow = 0;
+  for (int jid : jids) {                            // :226-241 back into the graph when either body is dynamic now (fresh colour, appended)
+    HJoint& j = joints_[jid];
+    const HBody& bodyA = bodies_[j.bodyIdA]; const HBody& bodyB = bodies_[j.bodyIdB];
+    if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) continue;
+    k_joint_color<<<1, 1, 0, stream_>>>(d_, bodyA.id, bodyB.id, bodyA.type, bodyB.type, hJointColorDev_);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(stream_));
+    const int color = *hJointColor_;
+    if (color == kOverflowIndex) { parkedOverflow++; continue; }
+    colorJoints_[color].push_back(jid);
+    j.inGraph = true; j.sim.colorIndex = color;
+    k_joint_set_color<<<1, 1, 0, stream_>>>(d_, jid, color);
+    CK(cudaGetLastError());
+  }
+  if (!jids.empty()) { int rc = uploadJointLists(); if (rc) return rc; }
   for (size_t k = 0; k < sids.size(); k++) {
     const int* g = &grows[4 * k];
     k_shape_retype<<<1, 1, 0, stream_>>>(d_, sids[k], type, g[0], g[1], g[2], g[3]);
@@ -356,6 +387,7 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
   k_body_mass_update<<<1, 1, 0, stream_>>>(d_, bodyId, b.type, b.invMass, b.invInertia, b.localCenter, b.minExtent, b.maxExtent);
   CK(cudaGetLastError());
   eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false;
+  if (parkedOverflow) return fail(B2C_E_UNSUPPORTED, "body_set_type: a joint of this body would land in the overflow colour (more than 20 joints on a body); it stays parked and is not simulated");
   return B2C_OK;
 }
 void World::treeProxyRemoved(int type) {          // DestroyProxy: the leaf and, unless it was the root, its parent go back to the free list
@@ -558,6 +590,7 @@ __global__ void k_joint_color(WorldDev d, int bodyIdA, int bodyIdB, int typeA, i
   d.bodyColorMask[bodyIdA] = mA; d.bodyColorMask[bodyIdB] = mB;
   *out = color;
 }
+__global__ void k_joint_set_color(WorldDev d, int jointId, int color) { d.joints[jointId].colorIndex = color; d.jointEventFlag[jointId] = 0; d.sc->graphDirty = 1; }
 __device__ void destroyContactSerial(const WorldDev& d, int id, int endIndex);
 // The joint's row, its collide flag and, unless the bodies may collide, DestroyContactsBetweenBodies (src/Joint.cs:155-180): both contact
 // lists hold the shared contacts in the same relative order (newest first), so the walk over the shorter list is a descending-stamp walk.
@@ -800,16 +833,18 @@ int World::destroyJoint(int jointId) {           // DestroyJointInternal src/Joi
   if (bodyB.headJointKey == ((jointId << 1) | 1)) bodyB.headJointKey = j.nextKeyB;
   bodyB.jointCount--;
   const int color = j.sim.colorIndex;
-  std::vector<int>& arr = colorJoints_[color];      // RemoveJointFromGraph: RemoveSwap in the colour's array
-  for (size_t k = 0; k < arr.size(); k++) if (arr[k] == jointId) { arr[k] = arr.back(); arr.pop_back(); break; }
-  if (!onDevice_ && color != kOverflowIndex) { colorMask_[j.bodyIdA] &= ~(1u << color); colorMask_[j.bodyIdB] &= ~(1u << color); }
+  const bool inGraph = j.inGraph;
+  if (inGraph) {
+    std::vector<int>& arr = colorJoints_[color];      // RemoveJointFromGraph: RemoveSwap in the colour's array
+    for (size_t k = 0; k < arr.size(); k++) if (arr[k] == jointId) { arr[k] = arr.back(); arr.pop_back(); break; }
+    if (!onDevice_ && color != kOverflowIndex) { colorMask_[j.bodyIdA] &= ~(1u << color); colorMask_[j.bodyIdB] &= ~(1u << color); }
+  }
   const int idA = j.bodyIdA, idB = j.bodyIdB;
   j.id = -1;
   jointIds_.release(jointId);
   if (!onDevice_) return B2C_OK;
   CK(cudaSetDevice(device_));
-  k_joint_removed<<<1, 1, 0, stream_>>>(d_, idA, idB, color);
-  CK(cudaGetLastError());
+  if (inGraph) { k_joint_removed<<<1, 1, 0, stream_>>>(d_, idA, idB, color); CK(cudaGetLastError()); }
   return uploadJointLists();
 }
 int World::uploadJointLists() {                  // joint edges, per-body list heads and the colour-grouped joint order after a destroy
@@ -1617,7 +1652,7 @@ int World::readJoints(B2CJointRead* dst, int capacity, int* count) {
   } else { jd.resize(n); for (int i = 0; i < n; i++) jd[i] = joints_[i].sim; }
   int m = 0;
   for (int i = 0; i < n; i++) {
-    if (joints_[i].id == -1) continue;             // destroyed: the slot waits in the id pool
+    if (joints_[i].id == -1 || !joints_[i].inGraph) continue;   // destroyed (the slot waits in the id pool) or parked in the static set
     const JointDev& s = jd[i];
     if (m < capacity) dst[m] = {s.jointId, s.colorIndex, {s.linearImpulse.x, s.linearImpulse.y}, s.springImpulse, s.motorImpulse, s.lowerImpulse, s.upperImpulse, s.type, {s.linearImpulse2.x, s.linearImpulse2.y}};
     m++;
@@ -1694,7 +1729,7 @@ int World::getJointEvents(const int** ids, int* count) {
   if (fetch(flags, d_.jointEventFlag, joints_.size(), stream_)) return fail(B2C_E_CUDA, "joint event copy failed");
   CK(cudaStreamSynchronize(stream_));
   int n = 0;
-  for (size_t i = 0; i < flags.size(); i++) if (flags[i] && joints_[i].id != -1) hJointEvents_[n++] = (int)i;   // a destroyed joint keeps its last flag: prepare only clears live joints
+  for (size_t i = 0; i < flags.size(); i++) if (flags[i] && joints_[i].id != -1 && joints_[i].inGraph) hJointEvents_[n++] = (int)i;   // a destroyed joint keeps its last flag: prepare only clears live joints
   *count = n;
   return B2C_OK;
 }

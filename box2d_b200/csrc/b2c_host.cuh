@@ -47,6 +47,7 @@ struct HShape {
 };
 struct HJoint {
   int id = -1; uint16_t generation = 0; bool collideConnected = false;
+  bool inGraph = true;            // false: parked in the static set by SetType (both bodies non-dynamic, SolverSet.TransferJoint) — not simulated, not reported
   int bodyIdA = -1, nextKeyA = -1, prevKeyA = -1, bodyIdB = -1, nextKeyB = -1, prevKeyB = -1;
   JointDev sim;
 };

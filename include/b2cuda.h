@@ -202,8 +202,9 @@ int32_t b2cuda_shape_set_filter(B2CWorld* world, int32_t shapeId, uint64_t categ
 int32_t b2cuda_shape_set_geometry(B2CWorld* world, int32_t shapeId, const B2CGeometry* geometry);
 /* BodyAPI.SetType api/Body.cs:185-268 (type: 0 static, 1 kinematic, 2 dynamic) between steps of a stepped world: the body's contacts are
  * destroyed, it moves between the static and the awake set (a body that becomes movable starts at rest, SolverSet.TransferBody
- * src/SolverSet.cs:354-376), its proxies move to the tree of the new type and the mass data is recomputed. A body that carries joints is
- * refused with B2C_E_UNSUPPORTED (its joints would pass through the static set). */
+ * src/SolverSet.cs:354-376), its proxies move to the tree of the new type and the mass data is recomputed. Its joints pass through the
+ * static set (SolverSet.TransferJoint :377-420): each comes back with a fresh colour when one of its bodies is dynamic afterwards; a joint
+ * between two non-dynamic bodies stays parked — not simulated, absent from b2cuda_world_read_joints — until one of them is dynamic again. */
 int32_t b2cuda_body_set_type(B2CWorld* world, int32_t bodyId, int32_t type);
 /* Joint mutators — api/Joint.cs. One generic entry per shape of setter; `param` selects the field (B2C_JP_*). Wrong joint type for a
  * field returns B2C_E_INVALID (the reference asserts the type, api/Joint.cs:169-179). After the first step each call is a one-thread

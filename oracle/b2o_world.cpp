@@ -359,6 +359,10 @@ void World::DestroyJoint(int jointId) {
     int movedIndex = RemoveSwap(color.jointSims, joint.localIndex);
     if (movedIndex != -1) joints[color.jointSims[joint.localIndex].jointId].localIndex = joint.localIndex;
   }
+  else if (joint.setIndex == kStaticSet) {       // src/Joint.cs:356-366 the sim leaves its solver set
+    int movedIndex = RemoveSwap(staticSet.jointSims, joint.localIndex);
+    if (movedIndex != -1) joints[staticSet.jointSims[joint.localIndex].jointId].localIndex = joint.localIndex;
+  }
   joint.setIndex = -1; joint.localIndex = -1; joint.colorIndex = -1; joint.jointId = -1;
   jointIdPool.FreeId(jointId);
 }
@@ -467,17 +471,42 @@ void World::SetGeometry(int shapeId, const Geom& geom) {          // api/Shape.c
   shape.geom = geom;
   ResetProxy(shape, true);
 }
-int World::SetType(int bodyId, int type) {        // api/Body.cs:185-268; joints would move through the static set (SolverSet.TransferJoint), not restated
+void World::TransferJoint(bool toAwake, Joint& joint) {      // src/SolverSet.cs:377-420
+  if (toAwake == (joint.setIndex == kAwakeSet)) return;
+  int localIndex = joint.localIndex, colorIndex = joint.colorIndex;
+  if (toAwake) {                                  // static set -> graph: AddJointToGraph / CreateJointInGraph src/ConstraintGraph.cs:242-255
+    JointSim sim = staticSet.jointSims[localIndex];
+    int bodyIdA = joint.edge0.bodyId, bodyIdB = joint.edge1.bodyId;
+    int c = AssignJointColor(bodyIdA, bodyIdB, bodies[bodyIdA].type, bodies[bodyIdB].type);
+    colors[c].jointSims.push_back(sim);
+    joint.colorIndex = c; joint.localIndex = (int)colors[c].jointSims.size() - 1; joint.setIndex = kAwakeSet;
+    int movedIndex = RemoveSwap(staticSet.jointSims, localIndex);
+    if (movedIndex != -1) joints[staticSet.jointSims[localIndex].jointId].localIndex = localIndex;
+  } else {                                        // graph -> static set, then RemoveJointFromGraph :256-276
+    JointSim sim = colors[colorIndex].jointSims[localIndex];
+    joint.setIndex = kStaticSet; joint.localIndex = (int)staticSet.jointSims.size(); joint.colorIndex = -1;
+    staticSet.jointSims.push_back(sim);
+    GraphColor& color = colors[colorIndex];
+    if (colorIndex != kOverflowIndex) { color.bodySet.ClearBit(joint.edge0.bodyId); color.bodySet.ClearBit(joint.edge1.bodyId); }
+    int movedIndex = RemoveSwap(color.jointSims, localIndex);
+    if (movedIndex != -1) joints[color.jointSims[localIndex].jointId].localIndex = localIndex;
+  }
+}
+int World::SetType(int bodyId, int type) {        // api/Body.cs:185-268
   Body& body = bodies[bodyId];
   int originalType = body.type;
   if (originalType == type) return 0;
-  if (body.headJointKey != -1) return -1;
   int edgeKey = body.headContactKey;              // DestroyBodyContacts src/Body.cs:232-244
   while (edgeKey != -1) {
     int contactId = edgeKey >> 1, edgeIndex = edgeKey & 1;
     Contact& contact = contacts[contactId];
     edgeKey = edgeIndex == 1 ? contact.edge1.nextKey : contact.edge0.nextKey;
     DestroyContact(contact);
+  }
+  for (int jointKey = body.headJointKey; jointKey != -1;) {      // :202-216 every joint of the body is parked in the static set
+    Joint& joint = joints[jointKey >> 1];
+    jointKey = (jointKey & 1) ? joint.edge1.nextKey : joint.edge0.nextKey;
+    TransferJoint(false, joint);
   }
   body.type = type;
   if (type == kDynamicBody) body.flags |= kDynamicFlag; else body.flags &= ~(uint32_t)kDynamicFlag;
@@ -495,6 +524,11 @@ int World::SetType(int bodyId, int type) {        // api/Body.cs:185-268; joints
     if (body.setIndex == kAwakeSet) RemoveSwap(sourceSet.bodyStates, sourceIndex);
     else { BodyState st; st.flags = body.flags; targetSet.bodyStates.push_back(st); }
     body.setIndex = targetSetIndex; body.localIndex = targetIndex;
+  }
+  for (int jointKey = body.headJointKey; jointKey != -1;) {      // :226-241 back into the graph when either body is dynamic now
+    Joint& joint = joints[jointKey >> 1];
+    jointKey = (jointKey & 1) ? joint.edge1.nextKey : joint.edge0.nextKey;
+    if (bodies[joint.edge0.bodyId].type == kDynamicBody || bodies[joint.edge1.bodyId].type == kDynamicBody) TransferJoint(true, joint);
   }
   Transform transform = GetBodySim(body).transform;
   int shapeId = body.headShapeId;

@@ -151,6 +151,7 @@ struct GraphColor {             // src/ConstraintGraph.cs:10-24
 };
 struct SolverSet {              // src/SolverSet.cs:13-30 (subset)
   std::vector<BodySim> bodySims; std::vector<BodyState> bodyStates; std::vector<ContactSim> contactSims;
+  std::vector<JointSim> jointSims;   // static set only: joints whose bodies are both non-dynamic (parked by SetType, SolverSet.TransferJoint)
 };
 
 struct ContactTouchEvent { int shapeIdA, shapeIdB, contactId; uint32_t contactGeneration; };
@@ -215,7 +216,7 @@ class World {
   void ResetProxy(Shape& shape, bool destroyProxy);                  // src/Shape.cs:273-301
   void SetFilter(int shapeId, Filter filter);                        // ShapeAPI.SetFilter api/Shape.cs:157-166
   void SetGeometry(int shapeId, const Geom& geom);                   // ShapeAPI.SetCircle/SetCapsule/SetSegment/SetPolygon api/Shape.cs:289-326
-  int SetType(int bodyId, int type);                                // BodyAPI.SetType api/Body.cs:185-268 (bodies without joints)
+  int SetType(int bodyId, int type);                                // BodyAPI.SetType api/Body.cs:185-268
   void ApplyMassFromShapes(int bodyId);                              // BodyAPI.ApplyMassFromShapes api/Body.cs:617-621
   void UnBufferMove(int proxyKey);         // src/BroadPhase.cs:60-71
   void SetTargetTransform(int bodyId, const Transform& target, float timeStep);
@@ -265,7 +266,8 @@ class World {
   BodySim& GetBodySim(const Body& b) { return b.setIndex == kAwakeSet ? awakeSet.bodySims[b.localIndex] : staticSet.bodySims[b.localIndex]; }
   BodyState* GetBodyState(const Body& b) { return b.setIndex == kAwakeSet ? &awakeSet.bodyStates[b.localIndex] : nullptr; }
   ContactSim& GetContactSim(const Contact& c) { return c.colorIndex != -1 ? colors[c.colorIndex].contactSims[c.localIndex] : awakeSet.contactSims[c.localIndex]; }
-  JointSim& GetJointSim(const Joint& j) { return colors[j.colorIndex].jointSims[j.localIndex]; }
+  JointSim& GetJointSim(const Joint& j) { return j.colorIndex == -1 ? staticSet.jointSims[j.localIndex] : colors[j.colorIndex].jointSims[j.localIndex]; }
+  void TransferJoint(bool toAwake, Joint& joint);   // src/SolverSet.cs:377-420 between the static set and the awake set (graph)
   void BufferMove(int key) { if (moveSet.insert(key).second) moveArray.push_back(key); }
   int BroadPhaseCreateProxy(int proxyType, const AABB& aabb, uint64_t categoryBits, int shapeIndex, bool forcePairCreation);
   void UpdateShapeAABBs(Shape& s, const Transform& xf, int proxyType);

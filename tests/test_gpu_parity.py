@@ -810,14 +810,48 @@ def test_set_body_type_between_steps_bit_exact():
     res = parity.run_pair(lambda w: scenes.mixed_drop(w, 60), steps=30, mutate=mutate2, verbose=True)
     assert res["max_rel_err"] == 0.0
 
-    cuda = api.World(api.CudaBackend(), scenes.world_def())
-    try:
-        scenes.joint_grid(cuda, 4)
-        cuda.Step(1.0 / 60.0, 4)
-        with pytest.raises(Exception, match="joints"):
-            cuda.SetType(3, api.STATIC_BODY)
-    finally:
-        cuda.Destroy()
+
+
+def test_set_body_type_with_joints_bit_exact():
+    """SetType on bodies that carry joints (api/Body.cs:202-241): every joint of the body is parked in the static set
+    (SolverSet.TransferJoint src/SolverSet.cs:377-420: colour bits and the colour array give it up) and comes back with a fresh colour,
+    appended, when one of its bodies is dynamic afterwards; a joint between two non-dynamic bodies stays parked (not simulated, not
+    reported) until one of them turns dynamic again. Accumulated impulses travel with the joint."""
+    def mutate(w, step):
+        if step == 5:
+            w.SetType(27, api.STATIC_BODY)              # an inner node of the revolute grid: four joints re-coloured against a static body
+        elif step == 9:
+            w.SetType(28, api.KINEMATIC_BODY)           # its neighbour: the joint 27-28 now links two non-dynamic bodies and is parked
+            w.SetAngularVelocity(28, 0.5)
+        elif step == 14:
+            w.SetType(27, api.DYNAMIC_BODY)             # the parked joint returns
+        elif step == 19:
+            w.SetType(28, api.DYNAMIC_BODY)
+            w.SetType(9, api.STATIC_BODY)
+        elif step == 23:
+            w.DestroyBody(9)                            # a static body with re-coloured joints
+            w.SetType(40, api.STATIC_BODY)
+            w.SetType(41, api.STATIC_BODY)              # parks the joint 40-41 ...
+        elif step == 26:
+            w.DestroyBody(41)                           # ... which is destroyed while parked
+    res = parity.run_pair(lambda w: scenes.joint_grid(w, 8), steps=40, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+    holder = {}
+
+    def build(w):
+        holder["zoo"] = scenes.joint_zoo(w, copies=2, angles=False)
+
+    def mutate2(w, step):
+        if step == 6:
+            w.SetType(1, api.KINEMATIC_BODY)
+            w.SetType(3, api.STATIC_BODY)
+        elif step == 14:
+            w.SetType(1, api.DYNAMIC_BODY)
+            w.SetType(3, api.DYNAMIC_BODY)
+            w.SetType(0, api.KINEMATIC_BODY)            # the first copy's ground with every joint anchored to it
+    res = parity.run_pair(build, steps=30, mutate=mutate2, verbose=True)
+    assert res["max_rel_err"] == 0.0
 
 
 def test_mutators_before_the_first_step_bit_exact():
@@ -870,10 +904,9 @@ def _churn(seed, steps, n0):
                     del m.joints[j]
                 w.DestroyBody(b)
             elif op == "retype" and live:
-                b = rnd.choice(live)
-                if not any(b in ac for ac in m.joints.values()):
-                    t = rnd.choice((api.STATIC_BODY, api.KINEMATIC_BODY, api.DYNAMIC_BODY))
-                    w.SetType(b, t); m.types[b] = t
+                b = rnd.choice(live)                      # jointed or not: its joints are parked / re-coloured
+                t = rnd.choice((api.STATIC_BODY, api.KINEMATIC_BODY, api.DYNAMIC_BODY))
+                w.SetType(b, t); m.types[b] = t
             elif op == "joint" and len(live) > 2:
                 a, c = rnd.sample(live, 2)
                 if m.types[a] == api.DYNAMIC_BODY or m.types[c] == api.DYNAMIC_BODY:
