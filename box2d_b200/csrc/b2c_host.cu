@@ -1501,7 +1501,7 @@ int World::setMotionLocks(int bodyId, bool lx, bool ly, bool az) {
   uint32_t newFlags = (lx ? kLockLinearX : 0u) | (ly ? kLockLinearY : 0u) | (az ? kLockAngularZ : 0u);
   if (!onDevice_) {
     // before the upload HBody::flags stands for both Body.flags and BodySim.flags: the sim's locks are what the solver reads
-    if ((b.flags & allLocks) == newFlags) return B2C_OK;
+    if ((b.bodyFlags & allLocks) == newFlags) return B2C_OK;     // tested on Body.flags, which holds all three bits after the first change (:805-807)
     b.flags = (b.flags & ~allLocks) | newFlags; b.bodyFlags |= allLocks;
     if (lx) b.v.x = 0.0f;
     if (ly) b.v.y = 0.0f;

@@ -956,3 +956,25 @@ def test_random_churn_of_creation_and_destruction_bit_exact(seed):
     build, mutate = _churn(seed, 120, 40)
     res = parity.run_pair(build, steps=120, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+def test_motion_locks_repeated_before_and_after_upload_bit_exact():
+    """SetMotionLocks tests Body.flags, which carries all three lock bits after the first change (api/Body.cs:805-807): a repeated call with
+    the same locks runs again and zeroes the locked velocity components once more — before the first step (host mirror) and after it."""
+    def build(w):
+        scenes.add_pyramid(w, 5)
+        w.SetMotionLocks(3, True, False, False)
+        w.SetLinearVelocity(3, (2.0, 1.0))
+        w.SetMotionLocks(3, True, False, False)        # runs again: vx back to 0
+        w.SetMotionLocks(4, True, True, True)
+        w.SetLinearVelocity(4, (1.0, 1.0))
+        w.SetMotionLocks(4, True, True, True)          # all three: Body.flags equals the request, early return, velocity stays
+
+    def mutate(w, step):
+        if step in (4, 9):
+            w.SetLinearVelocity(3, (1.5, 0.5))
+            w.SetMotionLocks(3, True, False, False)
+            w.SetLinearVelocity(6, (1.0, 2.0))
+            w.SetMotionLocks(6, False, True, False)
+    res = parity.run_pair(build, steps=16, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
