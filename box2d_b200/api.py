@@ -278,6 +278,10 @@ class World:
         """BodyAPI.EnableHitEvents api/Body.cs:862-872"""
         self._check(self.fns["body_enable_events"](self.handle, body_id, capi.SHAPE_HIT_EVENTS, int(bool(flag))))
 
+    def Explode(self, position, radius, falloff, impulse_per_length, mask_bits=0xFFFFFFFFFFFFFFFF):
+        """WorldAPI.Explode api/World.cs:758-776"""
+        self._check(self.fns["world_explode"](self.handle, Vec2(*position), radius, falloff, impulse_per_length, mask_bits))
+
     def SetType(self, body_id, body_type):
         """BodyAPI.SetType api/Body.cs:185-268"""
         self._check(self.fns["body_set_type"](self.handle, body_id, body_type))

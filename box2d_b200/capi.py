@@ -154,6 +154,7 @@ PROTOS = {
     "shape_enable_events": [_W, C.c_int32, C.c_int32, C.c_int32],
     "body_enable_events": [_W, C.c_int32, C.c_int32, C.c_int32],
     "body_set_type": [_W, C.c_int32, C.c_int32],
+    "world_explode": [_W, Vec2, C.c_float, C.c_float, C.c_float, C.c_uint64],
     "shape_set_filter": [_W, C.c_int32, C.c_uint64, C.c_uint64, C.c_int32],
     "shape_set_geometry": [_W, C.c_int32, C.POINTER(Geometry)],
     "joint_set_param": [_W, C.c_int32, C.c_int32, C.c_float],

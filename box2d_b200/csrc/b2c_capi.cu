@@ -83,6 +83,7 @@ int32_t b2cuda_body_enable_events(B2CWorld* h, int32_t id, int32_t which, int32_
 int32_t b2cuda_shape_set_filter(B2CWorld* h, int32_t id, uint64_t categoryBits, uint64_t maskBits, int32_t groupIndex) { CHECK_HANDLE(h); return done(h, h->w->setShapeFilter(id, categoryBits, maskBits, groupIndex)); }
 int32_t b2cuda_shape_set_geometry(B2CWorld* h, int32_t id, const B2CGeometry* g) { CHECK_HANDLE(h); if (!g) return B2C_E_INVALID; return done(h, h->w->setShapeGeometry(id, *g)); }
 int32_t b2cuda_body_set_type(B2CWorld* h, int32_t id, int32_t type) { CHECK_HANDLE(h); return done(h, h->w->setBodyType(id, type)); }
+int32_t b2cuda_world_explode(B2CWorld* h, B2CVec2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits) { CHECK_HANDLE(h); return done(h, h->w->explode(mk(position.x, position.y), radius, falloff, impulsePerLength, maskBits)); }
 int32_t b2cuda_joint_set_param(B2CWorld* h, int32_t id, int32_t param, float v) { CHECK_HANDLE(h); return done(h, h->w->jointOp(id, 0, param, v, 0.0f)); }
 int32_t b2cuda_joint_enable(B2CWorld* h, int32_t id, int32_t feature, int32_t flag) { CHECK_HANDLE(h); return done(h, h->w->jointOp(id, 1, feature, flag ? 1.0f : 0.0f, 0.0f)); }
 int32_t b2cuda_joint_set_limits(B2CWorld* h, int32_t id, float lo, float hi) { CHECK_HANDLE(h); return done(h, h->w->jointOp(id, 2, 0, lo, hi)); }

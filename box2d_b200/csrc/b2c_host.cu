@@ -5,6 +5,7 @@
 #include "b2c_host.cuh"
 #include "b2c_jointops.cuh"
 #include "b2c_treeops.cuh"
+#include "b2c_distance.cuh"
 #include <cstring>
 #include <cstdio>
 #include <algorithm>
@@ -1544,6 +1545,60 @@ int World::shapeEnableEvents(int shapeId, int which, bool flag) {
 int World::bodyEnableEvents(int bodyId, int which, bool flag) {     // BodyAPI.EnableContactEvents api/Body.cs:848-858 / EnableHitEvents :862-872
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   for (int sid = bodies_[bodyId].headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) { int rc = shapeEnableEvents(sid, which, flag); if (rc) return rc; }
+  return B2C_OK;
+}
+
+// WorldAPI.Explode api/World.cs:703-776: one thread walks the dynamic tree in the reference's Query order (child2 popped first) and applies
+// the impulses in that order (a body with several shapes accumulates them in callback order). The point proxy is built with radius 1 as
+// the port writes it (`Distance.MakeProxy([position], 1)`, :721 — upstream passes count 1, radius 0).
+__global__ void k_explode(WorldDev d, V2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits) {
+  const TreeDev& t = d.trees[kDynamicBody];
+  int root = t.meta[0];
+  if (t.meta[1] == 0 || root == -1) return;
+  const float reach = radius + falloff;
+  Box query; query.lo = mk(position.x - reach, position.y - reach); query.hi = mk(position.x + reach, position.y + reach);
+  DistProxy point; for (int i = 0; i < kMaxPolygonVertices; i++) point.pts[i] = mk(0, 0);
+  point.pts[0] = position; point.count = 1; point.radius = 1.0f;
+  const Xf identity = mkXf(mk(0, 0), mkRot(1, 0));
+  constexpr int kExplodeStack = 256;
+  int stack[kExplodeStack]; int sp = 0;
+  stack[sp++] = root;
+  while (sp > 0) {
+    int id = stack[--sp];
+    if (!boxOverlaps(tvBox(TreeView{t.aabb, t.child, t.parent, t.hf, t.cat, t.user, t.meta}, id), query) || (t.cat[id] & maskBits) == 0) continue;
+    if (!((t.hf[id] >> 16) & NODE_LEAF)) { if (sp + 2 <= kExplodeStack) { int2 c = t.child[id]; stack[sp++] = c.x; stack[sp++] = c.y; } else atomicOr(&d.sc->errorFlags, (int)ERR_STACK_OVERFLOW); continue; }
+    const ShapeDev& shape = d.shapes[t.user[id]];
+    const int bodyId = shape.bodyId;
+    float4 xf4 = d.bodyXf[bodyId];
+    Xf xf = mkXf(mk(xf4.x, xf4.y), mkRot(xf4.z, xf4.w));
+    DistOut out = shapeDistance(makeDistProxy(shape.geom), point, xf, identity, true);
+    if (out.distance > reach) continue;
+    const int sim = d.bodySim[bodyId];
+    if (sim < 0) continue;
+    V2 closest = out.pointA;
+    if (out.distance == 0.0f) closest = xfPoint(xf, geomCentroid(shape.geom));
+    V2 direction = closest - position;
+    direction = lengthSq(direction) > 100.0f * FLT_EPSILON * FLT_EPSILON ? normalize(direction) : mk(1, 0);
+    V2 localLine = invRotate(xf.q, leftPerp(direction));
+    float perimeter = geomProjectedPerimeter(shape.geom, localLine);
+    float scale = 1.0f;
+    if (out.distance > radius && falloff > 0.0f) scale = netClamp((radius + falloff - out.distance) / falloff, 0.0f, 1.0f);
+    float magnitude = impulsePerLength * perimeter * scale;
+    V2 impulse = magnitude * direction;
+    float4 s0 = d.st0[sim], m = d.simMass[sim], pose = d.simPose[sim];
+    V2 v = mulAdd(mk(s0.x, s0.y), m.x, impulse);
+    s0.x = v.x; s0.y = v.y;
+    s0.z += m.y * cross(closest - mk(pose.x, pose.y), impulse);
+    d.st0[sim] = s0;
+  }
+}
+int World::explode(V2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits) {
+  if (!(radius >= 0.0f) || !(falloff >= 0.0f)) return fail(B2C_E_INVALID, "explode: radius and falloff must be >= 0");
+  if (!onDevice_) { int rc = upload(); if (rc) return rc; }
+  CK(cudaSetDevice(device_));
+  k_explode<<<1, 1, 0, stream_>>>(d_, position, radius, falloff, impulsePerLength, maskBits);
+  CK(cudaGetLastError());
+  bodiesFetched_ = false;
   return B2C_OK;
 }
 

@@ -74,6 +74,7 @@ class World {
   int setShapeFilter(int shapeId, uint64_t categoryBits, uint64_t maskBits, int groupIndex);
   int setShapeGeometry(int shapeId, const B2CGeometry& g);
   int setBodyType(int bodyId, int type);
+  int explode(V2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits);
   int jointOp(int jointId, int patch, int which, float a, float b);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }
   int setTransform(int bodyId, V2 p, Rot q);

@@ -206,6 +206,10 @@ int32_t b2cuda_shape_set_geometry(B2CWorld* world, int32_t shapeId, const B2CGeo
  * static set (SolverSet.TransferJoint :377-420): each comes back with a fresh colour when one of its bodies is dynamic afterwards; a joint
  * between two non-dynamic bodies stays parked — not simulated, absent from b2cuda_world_read_joints — until one of them is dynamic again. */
 int32_t b2cuda_body_set_type(B2CWorld* world, int32_t bodyId, int32_t type);
+/* WorldAPI.Explode api/World.cs:703-776 (ExplosionDef include/Types.cs: maskBits, position, radius, falloff, impulsePerLength): every shape in
+ * the dynamic tree within radius + falloff of the position (GJK distance, Distance.ShapeDistance src/Distance.cs:219-318) pushes its body
+ * away with impulsePerLength x projected perimeter x falloff scale, in the tree's query order. */
+int32_t b2cuda_world_explode(B2CWorld* world, B2CVec2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits);
 /* Joint mutators — api/Joint.cs. One generic entry per shape of setter; `param` selects the field (B2C_JP_*). Wrong joint type for a
  * field returns B2C_E_INVALID (the reference asserts the type, api/Joint.cs:169-179). After the first step each call is a one-thread
  * patch of the device joint record, ordered on the world's stream (no read-back, no synchronisation).

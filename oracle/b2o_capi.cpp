@@ -102,6 +102,7 @@ int32_t b2o_shape_set_geometry(World* w, int32_t id, const B2CGeometry* g) {
   for (int i = 0; i < kMaxPolygonVertices; i++) { geom.v[i] = V(g->v[i]); geom.n[i] = V(g->n[i]); }
   w->SetGeometry(id, geom); return 0;
 }
+int32_t b2o_world_explode(World* w, B2CVec2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits) { w->Explode(V(position), radius, falloff, impulsePerLength, maskBits); return 0; }
 int32_t b2o_body_set_type(World* w, int32_t id, int32_t type) { if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id != id || type < 0 || type > 2) return -1; return w->SetType(id, type); }
 int32_t b2o_body_set_transform(World* w, int32_t id, B2CVec2 p, B2CRot q) { w->SetTransform(id, V(p), R(q)); return 0; }
 int32_t b2o_body_set_linear_velocity(World* w, int32_t id, B2CVec2 v) { w->SetLinearVelocity(id, V(v)); return 0; }

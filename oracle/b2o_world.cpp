@@ -690,4 +690,6 @@ void World::SetLinearDamping(int bodyId, float v) { GetBodySim(bodies[bodyId]).l
 void World::SetAngularDamping(int bodyId, float v) { GetBodySim(bodies[bodyId]).angularDamping = v; }   // api/Body.cs:635-640
 void World::SetGravityScale(int bodyId, float v) { GetBodySim(bodies[bodyId]).gravityScale = v; }       // api/Body.cs:647-653
 
+#include "b2o_distance.inc"
+
 }  // namespace b2o

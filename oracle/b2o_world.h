@@ -216,6 +216,7 @@ class World {
   void ResetProxy(Shape& shape, bool destroyProxy);                  // src/Shape.cs:273-301
   void SetFilter(int shapeId, Filter filter);                        // ShapeAPI.SetFilter api/Shape.cs:157-166
   void SetGeometry(int shapeId, const Geom& geom);                   // ShapeAPI.SetCircle/SetCapsule/SetSegment/SetPolygon api/Shape.cs:289-326
+  void Explode(Vec2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits);   // WorldAPI.Explode api/World.cs:703-776
   int SetType(int bodyId, int type);                                // BodyAPI.SetType api/Body.cs:185-268
   void ApplyMassFromShapes(int bodyId);                              // BodyAPI.ApplyMassFromShapes api/Body.cs:617-621
   void UnBufferMove(int proxyKey);         // src/BroadPhase.cs:60-71

@@ -978,3 +978,22 @@ def test_motion_locks_repeated_before_and_after_upload_bit_exact():
             w.SetMotionLocks(6, False, True, False)
     res = parity.run_pair(build, steps=16, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+def test_explode_bit_exact():
+    """WorldAPI.Explode (api/World.cs:703-776) between steps: GJK distance of every dynamic shape in reach to the centre (circles, capsules,
+    boxes, rounded boxes, compound bodies), impulses applied in the tree's query order. Masks and a zero-falloff blast included."""
+    def mutate(w, step):
+        if step == 6:
+            w.Explode((0.0, 1.5), 3.0, 2.0, 1.5)
+        elif step == 12:
+            w.Explode((-4.0, 0.5), 2.0, 0.0, 0.8)
+            w.Explode((3.0, 4.0), 1.0, 4.0, -0.6)              # an implosion
+        elif step == 18:
+            w.Explode((0.0, 0.0), 50.0, 0.0, 0.2, 0x2)         # nobody carries category 2
+            w.Explode((1.0, 0.3), 0.4, 0.3, 2.0)               # small: centre inside some shape (distance 0 -> centroid direction)
+    res = parity.run_pair(lambda w: scenes.mixed_drop(w, 120), steps=30, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    res = parity.run_pair(lambda w: scenes.add_pyramid(w, 12), steps=24, verbose=True,
+                          mutate=lambda w, s: w.Explode((0.0, 3.0), 4.0, 3.0, 2.0) if s in (8, 16) else None)
+    assert res["max_rel_err"] == 0.0
