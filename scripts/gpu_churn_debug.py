@@ -2,8 +2,9 @@ import sys
 sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/tests')
 import parity, test_gpu_parity as T
 from box2d_b200 import api, scenes
-for seed in range(1, 13):
-    build, mutate = T._churn(seed, 120, 40)
+import os
+for seed in range(int(os.environ.get("CHURN_FIRST", "1")), int(os.environ.get("CHURN_LAST", "12")) + 1):
+    STEPS = int(os.environ.get("CHURN_STEPS", "120")); build, mutate = T._churn(seed, STEPS, int(os.environ.get("CHURN_BODIES", "40")))
     calls = []
     class Spy:
         def __init__(self, w): self.w = w
@@ -20,7 +21,7 @@ for seed in range(1, 13):
         cur[0] = step
         mutate(Spy(w), step)
     try:
-        res = parity.run_pair(build, steps=120, mutate=mut, verbose=False)
+        res = parity.run_pair(build, steps=STEPS, mutate=mut, verbose=False)
         print("seed", seed, "ok", res["max_rel_err"])
     except AssertionError as e:
         print("seed", seed, "FAIL", str(e)[:400])

@@ -893,7 +893,7 @@ def _churn(seed, steps, n0):
         m = models[id(getattr(w, 'w', w))]
         rnd = random.Random(seed * 1000 + step)
         for _ in range(rnd.randint(0, 4)):
-            op = rnd.choice(("spawn", "spawn", "destroy", "retype", "joint", "unjoint", "filter", "teleport", "impulse", "geometry", "density", "shapekill", "locks", "addshape"))
+            op = rnd.choice(("spawn", "spawn", "destroy", "retype", "joint", "unjoint", "filter", "teleport", "impulse", "geometry", "density", "shapekill", "locks", "addshape", "explode"))
             live = m.bodies
             if op == "spawn":
                 b = _spawn(w, rnd.uniform(-8.0, 8.0), rnd.uniform(5.0, 12.0), rnd.choice(("box", "circle", "compound")), (rnd.uniform(-2, 2), rnd.uniform(-4, 0)))
@@ -939,6 +939,8 @@ def _churn(seed, steps, n0):
                 alive = [i for i, k in enumerate(w.ReadShapes()["proxyKey"].tolist()) if k != -1 and i > 5]
                 if alive:
                     w.DestroyShape(rnd.choice(alive), bool(rnd.randint(0, 1)))
+            elif op == "explode":
+                w.Explode((rnd.uniform(-8.0, 8.0), rnd.uniform(0.0, 6.0)), rnd.uniform(0.5, 3.0), rnd.choice((0.0, 1.0, 2.5)), rnd.uniform(-0.5, 1.0))
             elif op == "locks" and live:
                 w.SetMotionLocks(rnd.choice(live), bool(rnd.randint(0, 1)), False, bool(rnd.randint(0, 1)))
             elif op == "addshape" and live:
