@@ -140,7 +140,7 @@ struct BodyRows {
 __global__ void k_create_body(WorldDev d, int id, BodyRows r) {
   d.bodyXf[id] = r.bodyXf; d.bodyMass[id] = r.bodyMass; d.bodyCenter[id] = r.bodyCenter; d.bodySim[id] = r.sim; d.bodyType[id] = r.type;
   d.bodyHeadShape[id] = -1; d.bodyHeadJoint[id] = -1; d.bodyJointCount[id] = 0; d.bodyColorMask[id] = 0; d.bodyMinOp[id] = 0x7f7f7f7f;
-  d.bodySleepThreshold[id] = r.sleepThreshold; d.bodyFlags[id] = r.flags; d.bodySimFlags[id] = r.flags;
+  d.bodySleepThreshold[id] = r.sleepThreshold; d.bodyFlags[id] = r.flags; d.bodySimFlags[id] = r.flags; d.bodyForce[id] = make_float4(0, 0, 0, 0);
   if (r.sim < 0) return;
   const int i = r.sim;
   d.st0[i] = r.st0; d.st1[i] = r.st1; d.simMass[i] = r.simMass; d.simForce[i] = r.simForce; d.simPose[i] = r.simPose; d.simLocal[i] = r.simLocal;
@@ -190,6 +190,7 @@ __global__ void k_body_retype(WorldDev d, int bodyId, int type, int transfer, in
   const int sim = d.bodySim[bodyId];
   if (transfer == 1 && sim >= 0) {                 // awake -> static: bodySims / bodyStates RemoveSwap; the host lowers awakeCount after this launch
     d.bodySimFlags[bodyId] = d.simFlags[sim] & ~(uint32_t)(kIsFast | kIsSpeedCapped | kHadTimeOfImpact);
+    d.bodyForce[bodyId] = d.simForce[sim];
     int last = d.awakeCount - 1;
     if (sim != last) {
       d.st0[sim] = d.st0[last]; d.st1[sim] = d.st1[last]; d.simMass[sim] = d.simMass[last]; d.simForce[sim] = d.simForce[last];
@@ -201,7 +202,7 @@ __global__ void k_body_retype(WorldDev d, int bodyId, int type, int transfer, in
     float4 xf4 = d.bodyXf[bodyId], m = d.bodyMass[bodyId]; float2 c = d.bodyCenter[bodyId];
     const int i = newSim;
     d.st0[i] = make_float4(0, 0, 0, __uint_as_float(bodyFlags)); d.st1[i] = make_float4(0, 0, 1, 0);
-    d.simMass[i] = make_float4(m.x, m.y, linearDamping, angularDamping); d.simForce[i] = make_float4(0, 0, 0, gravityScale);
+    d.simMass[i] = make_float4(m.x, m.y, linearDamping, angularDamping); { float4 f = d.bodyForce[bodyId]; d.simForce[i] = make_float4(f.x, f.y, f.z, gravityScale); }
     d.simPose[i] = make_float4(c.x, c.y, xf4.z, xf4.w); d.simPose0[i] = d.simPose[i];
     d.simLocal[i] = make_float4(m.z, m.w, kHuge, 0);
     d.simFlags[i] = d.bodySimFlags[bodyId] & ~(uint32_t)(kIsFast | kIsSpeedCapped | kHadTimeOfImpact); d.simBodyId[i] = bodyId; d.bodySim[bodyId] = i;
@@ -1048,7 +1049,7 @@ int World::growBodies(int minBodies, int minAwake) {
   if (minBodies > capBody_) {
     const int c = std::max(minBodies, capBody_ + capBody_ / 2);
     RG(d.bodyXf, c); RG(d.bodyMass, c); RG(d.bodyCenter, c); RG(d.bodySim, c); RG(d.bodyType, c); RG(d.bodyHeadShape, c); RG(d.bodyHeadJoint, c);
-    RG(d.bodyJointCount, c); RG(d.bodyColorMask, c); RGF(d.bodyMinOp, c, 0x7f); RG(d.bodySleepThreshold, c); RG(d.bodyFlags, c); RG(d.bodySimFlags, c); RG(dBodyRead_, c);
+    RG(d.bodyJointCount, c); RG(d.bodyColorMask, c); RGF(d.bodyMinOp, c, 0x7f); RG(d.bodySleepThreshold, c); RG(d.bodyFlags, c); RG(d.bodySimFlags, c); RG(d.bodyForce, c); RG(dBodyRead_, c);
     if (hBodyRead_) cudaFreeHost(hBodyRead_);
     hBodyRead_ = nullptr;
     CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)c, cudaHostAllocDefault));
@@ -1165,7 +1166,7 @@ int World::upload() {
   colorMask_.resize(nBody, 0);
   DA(d.bodyXf, float4, capBody); DA(d.bodyMass, float4, capBody); DA(d.bodyCenter, float2, capBody); DA(d.bodySim, int, capBody); DA(d.bodyType, int, capBody);
   DA(d.bodyHeadShape, int, capBody); DA(d.bodyHeadJoint, int, capBody); DA(d.bodyJointCount, int, capBody); DA(d.bodyColorMask, uint32_t, capBody);
-  DA(d.bodyMinOp, int, capBody); DA(d.bodySleepThreshold, float, capBody); DA(d.bodyFlags, uint32_t, capBody); DA(d.bodySimFlags, uint32_t, capBody);
+  DA(d.bodyMinOp, int, capBody); DA(d.bodySleepThreshold, float, capBody); DA(d.bodyFlags, uint32_t, capBody); DA(d.bodySimFlags, uint32_t, capBody); DA(d.bodyForce, float4, capBody);
   UP(d.bodyXf, bodyXf); UP(d.bodyMass, bodyMass); UP(d.bodyCenter, bodyCenter); UP(d.bodySim, bodySim); UP(d.bodyType, bodyType);
   UP(d.bodyHeadShape, bodyHeadShape); UP(d.bodyHeadJoint, bodyHeadJoint); UP(d.bodyJointCount, bodyJointCount); UP(d.bodyColorMask, colorMask_);
   { std::vector<uint32_t> sf(nBody); for (int i = 0; i < nBody; i++) sf[i] = bodies_[i].flags; UP(d.bodySimFlags, sf); CK(cudaStreamSynchronize(stream_)); }
@@ -1374,7 +1375,10 @@ int World::bodyOp(int bodyId, int op, V2 a, V2 point) {
     return B2C_OK;
   }
   if (op == OP_LINEAR_DAMPING) b.linearDamping = a.x; else if (op == OP_ANGULAR_DAMPING) b.angularDamping = a.x; else if (op == OP_GRAVITY_SCALE) b.gravityScale = a.x;
-  if (b.simIndex < 0) return B2C_OK;               // static bodies have no solver rows
+  if (b.simIndex < 0) {                            // static bodies have no solver rows; ClearForces still reaches a parked sim's force (api/Body.cs:490-495)
+    if (op == OP_CLEAR_FORCES) { CK(cudaSetDevice(device_)); CK(cudaMemsetAsync(&d_.bodyForce[bodyId], 0, sizeof(float4), stream_)); }
+    return B2C_OK;
+  }
   CK(cudaSetDevice(device_));
   k_body_op<<<1, 1, 0, stream_>>>(d_, op, b.simIndex, a, point, maxLinearSpeed);
   CK(cudaGetLastError());

@@ -142,6 +142,7 @@ struct WorldDev {
   int* bodyMinOp;      // coloring scratch
   float* bodySleepThreshold;
   uint32_t* bodyFlags;
+  float4* bodyForce;         // force.x force.y torque of a sim parked in the static set by SetType (BodySim is copied whole, src/SolverSet.cs:360)
   uint32_t* bodySimFlags;   // BodySim.flags of a body that has no awake row (static set): kept so that SetType can bring them back (src/SolverSet.cs:360-361)
   int bodyCapacity;
   // --- shapes ---

@@ -780,6 +780,8 @@ def test_set_body_type_between_steps_bit_exact():
     platform turned kinematic, a compound body. Contacts of the body go first (end events), proxies change trees in shape-list order."""
     def mutate(w, step):
         if step == 6:
+            w.ApplyForceToCenter(5, (30.0, 50.0))       # stays in the parked sim and acts in the first step after the body is dynamic again
+            w.ApplyTorque(5, 4.0)
             w.SetType(5, api.STATIC_BODY)
             w.SetType(5, api.STATIC_BODY)               # same type: early return
         elif step == 10:
