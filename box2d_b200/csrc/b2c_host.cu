@@ -636,12 +636,12 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   int nb = (int)bodies_.size();
   if (def.bodyIdA < 0 || def.bodyIdA >= nb || def.bodyIdB < 0 || def.bodyIdB >= nb || bodies_[def.bodyIdA].id != def.bodyIdA || bodies_[def.bodyIdB].id != def.bodyIdB) return fail(B2C_E_INVALID, "bad body id");
   HBody& bodyA = bodies_[def.bodyIdA]; HBody& bodyB = bodies_[def.bodyIdB];
-  if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) return fail(B2C_E_UNSUPPORTED, "joint between two non-dynamic bodies (static set) is not supported");
+  const bool parked = bodyA.type != kDynamicBody && bodyB.type != kDynamicBody;   // src/Joint.cs:242-248: kept in the static set until SetType makes a body dynamic
   if (def.type == B2C_JOINT_DISTANCE && (!(def.length > 0.0f) || !(def.lowerSpringForce <= def.upperSpringForce)))
     return fail(B2C_E_INVALID, "distance joint: length must be > 0 and lowerSpringForce <= upperSpringForce");
   int deviceColor = -1;
-  if (onDevice_) {                               // the colour first: a refused call must leave both sides as they were
-    if (jointIds_.freeArray.empty()) { int rc = growJoints((int)joints_.size() + 1); if (rc) return rc; }
+  if (onDevice_ && jointIds_.freeArray.empty()) { int rc = growJoints((int)joints_.size() + 1); if (rc) return rc; }
+  if (onDevice_ && !parked) {                    // the colour first: a refused call must leave both sides as they were
     CK(cudaSetDevice(device_));
     k_joint_color<<<1, 1, 0, stream_>>>(d_, bodyA.id, bodyB.id, bodyA.type, bodyB.type, hJointColorDev_);
     CK(cudaGetLastError());
@@ -663,7 +663,8 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   j.bodyIdB = bodyB.id; j.prevKeyB = -1; j.nextKeyB = bodyB.headJointKey;
   if (bodyB.headJointKey != -1) { HJoint& h = joints_[bodyB.headJointKey >> 1]; if (bodyA.headJointKey & 1) h.prevKeyB = keyB; else h.prevKeyA = keyB; }   // tests bodyA's key, as written (:229)
   bodyB.headJointKey = keyB; bodyB.jointCount++;
-  int color = onDevice_ ? deviceColor : assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type);
+  int color = parked ? -1 : (onDevice_ ? deviceColor : assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type));
+  j.inGraph = !parked;
   if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   JointDev& s = j.sim;
   memset(&s, 0, sizeof(s));
@@ -705,9 +706,10 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
       s.hertz = def.hertz; s.dampingRatio = def.dampingRatio; s.enableSpring = spring; s.enableMotor = motor; s.enableLimit = limit;
       break;
   }
-  colorJoints_[color].push_back(id);
+  if (!parked) colorJoints_[color].push_back(id);
   *jointId = id;
   if (!onDevice_) return B2C_OK;                  // DestroyContactsBetweenBodies (src/Joint.cs:155-180): no contacts exist before the first step
+  CK(cudaSetDevice(device_));
   k_joint_created<<<1, 256, 0, stream_>>>(d_, id, s, j.collideConnected ? 1 : 0, endIndex_);
   CK(cudaGetLastError());
   d_.jointCapacity = (int)joints_.size();

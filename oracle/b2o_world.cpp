@@ -222,9 +222,9 @@ int World::CreateJoint(const JointDef& def) {
     if (bodyA.headJointKey & 1) jointB.edge1.prevKey = keyB; else jointB.edge0.prevKey = keyB;   // Q11: tests bodyA's key
   }
   bodyB.headJointKey = keyB; bodyB.jointCount++;
-  if (bodyA.type != kDynamicBody && bodyB.type != kDynamicBody) { counters.unsupported++; lastError = "oracle: joint between two non-dynamic bodies (static set) not restated"; return jointId; }
-  joint.setIndex = kAwakeSet;
-  int colorIndex = AssignJointColor(bodyIdA, bodyIdB, bodyA.type, bodyB.type);   // src/ConstraintGraph.cs:242-251
+  const bool parked = bodyA.type != kDynamicBody && bodyB.type != kDynamicBody;   // src/Joint.cs:242-248: the static set holds it, nothing simulates it
+  joint.setIndex = parked ? kStaticSet : kAwakeSet;
+  int colorIndex = parked ? -1 : AssignJointColor(bodyIdA, bodyIdB, bodyA.type, bodyB.type);   // src/ConstraintGraph.cs:242-251
   JointSim sim; sim.jointId = jointId; sim.bodyIdA = bodyIdA; sim.bodyIdB = bodyIdB;
   sim.localFrameA = def.localFrameA; sim.localFrameB = def.localFrameB; sim.type = def.type;
   sim.constraintHertz = def.constraintHertz; sim.constraintDampingRatio = def.constraintDampingRatio;
@@ -263,8 +263,8 @@ int World::CreateJoint(const JointDef& def) {
       sim.enableSpring = def.enableSpring; sim.enableLimit = def.enableLimit; sim.enableMotor = def.enableMotor;
       break;
   }
-  colors[colorIndex].jointSims.push_back(sim);
-  joint.colorIndex = colorIndex; joint.localIndex = (int)colors[colorIndex].jointSims.size() - 1;
+  if (parked) { staticSet.jointSims.push_back(sim); joint.colorIndex = -1; joint.localIndex = (int)staticSet.jointSims.size() - 1; }
+  else { colors[colorIndex].jointSims.push_back(sim); joint.colorIndex = colorIndex; joint.localIndex = (int)colors[colorIndex].jointSims.size() - 1; }
   if (!def.collideConnected) DestroyContactsBetweenBodies(bodyA, bodyB);
   return jointId;
 }

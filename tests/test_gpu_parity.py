@@ -591,7 +591,7 @@ def test_event_enable_flags_between_steps_bit_exact():
 
 def _spawn(w, x, y, kind, v=(0.0, 0.0), body_type=None):
     bd = api.default_body_def()
-    bd.type = api.DYNAMIC_BODY if body_type is None else body_type
+    bd.type = (api.STATIC_BODY if kind == "static" else api.DYNAMIC_BODY) if body_type is None else body_type
     bd.position = api.Vec2(x, y)
     bd.linearVelocity = api.Vec2(*v)
     bd.angularVelocity = 0.5 if kind != "static" else 0.0
@@ -1000,4 +1000,36 @@ def test_explode_bit_exact():
     assert res["max_rel_err"] == 0.0
     res = parity.run_pair(lambda w: scenes.add_pyramid(w, 12), steps=24, verbose=True,
                           mutate=lambda w, s: w.Explode((0.0, 3.0), 4.0, 3.0, 2.0) if s in (8, 16) else None)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_joints_between_non_dynamic_bodies_are_parked_until_one_turns_dynamic():
+    """World.CreateJoint puts a joint whose bodies are both non-dynamic into the static set (src/Joint.cs:242-248): it is not simulated and
+    not reported; SetType(dynamic) on one of its bodies brings it into the graph (api/Body.cs:226-241). Before and after the first step."""
+    from box2d_b200 import capi as J
+    made = {}
+
+    def build(w):
+        scenes.mixed_drop(w, 40)
+        made[id(w)] = [w.CreateJoint(_jdef(J.JOINT_REVOLUTE, 0, 1, (-5.0, 1.5), (0.0, 0.0)))]      # ground (static) - paddle (kinematic)
+        assert len(w.ReadJoints()) == 0 and w.GetCounters().jointCount == 1
+
+    def mutate(w, step):
+        if step == 5:
+            p = _spawn(w, 6.0, 3.0, "static")
+            k = _spawn(w, 6.0, 5.0, "paddle", body_type=api.KINEMATIC_BODY)
+            d = _jdef(J.JOINT_DISTANCE, p, k, (0.0, 0.0), (0.0, 0.0))
+            d.length = 2.0
+            made[id(w)] += [w.CreateJoint(d), p, k]
+            assert len(w.ReadJoints()) == 0
+        elif step == 10:
+            w.SetType(1, api.DYNAMIC_BODY)                   # the paddle now swings on its pin
+            assert w.ReadJoints()["jointId"].tolist() == [made[id(w)][0]]
+        elif step == 16:
+            w.SetType(made[id(w)][3], api.DYNAMIC_BODY)
+        elif step == 24:
+            w.DestroyJoint(made[id(w)][0])
+            w.SetType(made[id(w)][3], api.STATIC_BODY)       # parked again
+            w.DestroyJoint(made[id(w)][1])                   # destroyed while parked
+    res = parity.run_pair(build, steps=34, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
