@@ -911,7 +911,7 @@ def _churn(seed, steps, n0):
                 w.SetType(b, t); m.types[b] = t
             elif op == "joint" and len(live) > 2:
                 a, c = rnd.sample(live, 2)
-                if m.types[a] == api.DYNAMIC_BODY or m.types[c] == api.DYNAMIC_BODY:
+                if True:                                          # two non-dynamic bodies: the joint is created parked (src/Joint.cs:242-248)
                     d = _jdef(rnd.choice((J.JOINT_DISTANCE, J.JOINT_FILTER, J.JOINT_REVOLUTE)), a, c, (0.0, 0.0), (0.0, 0.0))
                     if d.type == J.JOINT_DISTANCE:               # the revolute spring evaluates Atan2 (tolerance-only): plain pins here
                         d.length, d.enableSpring, d.hertz, d.dampingRatio = 2.0, 1, 2.0, 0.7
