@@ -282,6 +282,10 @@ class World:
         """WorldAPI.Explode api/World.cs:758-776"""
         self._check(self.fns["world_explode"](self.handle, Vec2(*position), radius, falloff, impulse_per_length, mask_bits))
 
+    def EnableSleeping(self, flag):
+        """WorldAPI.EnableSleeping api/World.cs:631-645 (only False is supported)"""
+        self._check(self.fns["world_enable_sleeping"](self.handle, int(bool(flag))))
+
     def SetType(self, body_id, body_type):
         """BodyAPI.SetType api/Body.cs:185-268"""
         self._check(self.fns["body_set_type"](self.handle, body_id, body_type))

@@ -185,6 +185,7 @@ PROTOS = {
     "world_enable_warm_starting": [_W, C.c_int32],
     "world_enable_speculative": [_W, C.c_int32],
     "world_enable_continuous": [_W, C.c_int32],
+    "world_enable_sleeping": [_W, C.c_int32],
     "world_set_contact_tuning": [_W, C.c_float, C.c_float, C.c_float],
     "world_step": [_W, C.c_float, C.c_int32],
     "world_synchronize": [_W],

@@ -111,6 +111,11 @@ int32_t b2cuda_world_set_maximum_linear_speed(B2CWorld* h, float v) { CHECK_HAND
 int32_t b2cuda_world_set_gravity(B2CWorld* h, B2CVec2 g) { CHECK_HANDLE(h); h->w->gravity = mk(g.x, g.y); return B2C_OK; }
 int32_t b2cuda_world_enable_warm_starting(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableWarmStarting = f != 0; return B2C_OK; }
 int32_t b2cuda_world_enable_speculative(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableSpeculative = f != 0; return B2C_OK; }
+int32_t b2cuda_world_enable_sleeping(B2CWorld* h, int32_t f) {
+  CHECK_HANDLE(h);
+  if (f) { h->w->error = "enable_sleeping(1): islands/sleep (src/Island.cs) are not supported in this build; sleeping stays off"; return done(h, B2C_E_UNSUPPORTED); }
+  h->w->enableSleep = false; return B2C_OK;
+}
 int32_t b2cuda_world_enable_continuous(B2CWorld* h, int32_t f) { CHECK_HANDLE(h); h->w->enableContinuous = f != 0; return B2C_OK; }
 int32_t b2cuda_world_set_contact_tuning(B2CWorld* h, float hertz, float damping, float push) {   // api/World.cs:780-787
   CHECK_HANDLE(h);

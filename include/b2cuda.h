@@ -285,6 +285,9 @@ int32_t b2cuda_world_set_gravity(B2CWorld* world, B2CVec2 gravity);
 int32_t b2cuda_world_enable_warm_starting(B2CWorld* world, int32_t flag);
 int32_t b2cuda_world_enable_speculative(B2CWorld* world, int32_t flag);
 int32_t b2cuda_world_enable_continuous(B2CWorld* world, int32_t flag);
+/* WorldAPI.EnableSleeping api/World.cs:631-645: flag 0 is accepted (nothing sleeps in this build, so there is nothing to wake);
+ * flag 1 returns B2C_E_UNSUPPORTED and leaves sleeping off (islands/sleep, src/Island.cs, are not built). */
+int32_t b2cuda_world_enable_sleeping(B2CWorld* world, int32_t flag);
 int32_t b2cuda_world_set_contact_tuning(B2CWorld* world, float hertz, float dampingRatio, float pushSpeed);
 
 /* WorldAPI.Step — api/World.cs:31-113. Asynchronous on the world's stream; read-backs synchronise. */

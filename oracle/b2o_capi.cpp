@@ -124,6 +124,7 @@ int32_t b2o_world_set_maximum_linear_speed(World* w, float v) { w->maxLinearSpee
 int32_t b2o_world_set_gravity(World* w, B2CVec2 g) { w->gravity = V(g); return 0; }
 int32_t b2o_world_enable_warm_starting(World* w, int32_t f) { w->enableWarmStarting = f != 0; return 0; }
 int32_t b2o_world_enable_speculative(World* w, int32_t f) { w->enableSpeculative = f != 0; return 0; }
+int32_t b2o_world_enable_sleeping(World* w, int32_t f) { if (f) return -1; w->enableSleep = false; return 0; }   // api/World.cs:631-645 (sleep is not restated)
 int32_t b2o_world_enable_continuous(World* w, int32_t f) { w->enableContinuous = f != 0; return 0; }
 int32_t b2o_world_set_contact_tuning(World* w, float hertz, float damping, float pushSpeed) {   // api/World.cs:780-787
   w->contactHertz = netClamp(hertz, 0, FLT_MAX); w->contactDampingRatio = netClamp(damping, 0, FLT_MAX); w->contactSpeed = netClamp(pushSpeed, 0, FLT_MAX);

@@ -518,6 +518,9 @@ def test_destroy_rejects_stale_ids_and_reports_counts():
     try:
         scenes.add_pyramid(cuda, 4)
         cuda.Step(1.0 / 60.0, 4)
+        cuda.EnableSleeping(False)                                  # accepted: nothing sleeps in this build
+        with pytest.raises(Exception, match="sleep"):
+            cuda.EnableSleeping(True)                               # refused loudly, sleeping stays off
         cuda.DestroyBody(3)
         with pytest.raises(Exception):
             cuda.DestroyBody(3)
