@@ -98,7 +98,7 @@ class ManifoldPointRead(C.Structure):
 
 class ContactRead(C.Structure):
     _fields_ = [("contactId", C.c_int32), ("shapeIdA", C.c_int32), ("shapeIdB", C.c_int32), ("colorIndex", C.c_int32),
-                ("flags", C.c_uint32), ("pointCount", C.c_int32), ("normal", Vec2), ("rollingImpulse", C.c_float),
+                ("localIndex", C.c_int32), ("flags", C.c_uint32), ("pointCount", C.c_int32), ("normal", Vec2), ("rollingImpulse", C.c_float),
                 ("friction", C.c_float), ("restitution", C.c_float), ("rollingResistance", C.c_float),
                 ("tangentSpeed", C.c_float), ("points", ManifoldPointRead * 2)]
 

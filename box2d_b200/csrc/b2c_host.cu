@@ -649,6 +649,10 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
     deviceColor = *hJointColor_;
     if (deviceColor == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   }
+  // the colour before anything is filed: a refused joint must leave id pool, body joint lists and colour masks untouched (assignJointColor
+  // sets no bit when it answers with the overflow colour)
+  const int color = parked ? -1 : (onDevice_ ? deviceColor : assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type));
+  if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   int id = jointIds_.alloc();
   if (id == (int)joints_.size()) joints_.emplace_back();
   HJoint& j = joints_[id];
@@ -663,9 +667,7 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
   j.bodyIdB = bodyB.id; j.prevKeyB = -1; j.nextKeyB = bodyB.headJointKey;
   if (bodyB.headJointKey != -1) { HJoint& h = joints_[bodyB.headJointKey >> 1]; if (bodyA.headJointKey & 1) h.prevKeyB = keyB; else h.prevKeyA = keyB; }   // tests bodyA's key, as written (:229)
   bodyB.headJointKey = keyB; bodyB.jointCount++;
-  int color = parked ? -1 : (onDevice_ ? deviceColor : assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type));
   j.inGraph = !parked;
-  if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   JointDev& s = j.sim;
   memset(&s, 0, sizeof(s));
   s.jointId = id; s.bodyIdA = bodyA.id; s.bodyIdB = bodyB.id; s.colorIndex = color; s.type = def.type;
@@ -682,7 +684,6 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
       s.enableSpring = spring; s.enableMotor = motor; s.enableLimit = limit;
       break;
     case B2C_JOINT_DISTANCE:
-      if (!(def.length > 0.0f) || !(def.lowerSpringForce <= def.upperSpringForce)) return fail(B2C_E_INVALID, "distance joint: length must be > 0 and lowerSpringForce <= upperSpringForce");
       s.length = netMax(def.length, kLinearSlop); s.hertz = def.hertz; s.dampingRatio = def.dampingRatio;
       s.minLength = netMax(def.minLength, kLinearSlop); s.maxLength = netMax(def.minLength, def.maxLength);
       s.maxMotorTorque = def.maxMotor; s.motorSpeed = def.motorSpeed; s.lowerSpringForce = def.lowerSpringForce; s.upperSpringForce = def.upperSpringForce;
@@ -737,13 +738,7 @@ __device__ void destroyContactSerial(const WorldDev& d, int id, int endIndex) { 
   int color = d.cColor[id];
   if (color != -1) {                              // RemoveContactFromGraph src/ConstraintGraph.cs:221-241
     if (color != kOverflowIndex) { d.bodyColorMask[b.x] &= ~(1u << color); d.bodyColorMask[b.y] &= ~(1u << color); }
-    else {
-      int li = d.cOvIndex[id], last = s.ovCount - 1;
-      if (li >= 0 && li <= last) {
-        if (li != last) { int moved = d.ovList[last]; d.ovList[li] = moved; d.cOvIndex[moved] = li; }
-        d.cOvIndex[id] = -1; s.ovCount = last;
-      }
-    }
+    colRemoveSwap(d, color, id);
     d.cColor[id] = -1;
   }
   d.cFlags[id] = 0;
@@ -1246,10 +1241,10 @@ int World::upload() {
   DA(d.cMat, float4, contactCap); DA(d.cMass, float4, contactCap); DA(d.cSim, int2, contactCap);
   DA(d.mN, float4, contactCap); DA(d.mA0, float4, contactCap); DA(d.mA1, float4, contactCap); DA(d.mB0, float4, contactCap); DA(d.mB1, float4, contactCap);
   DA(d.mC0, float4, contactCap); DA(d.mC1, float4, contactCap); DA(d.contactFree, int, contactCap);
-  DA(d.flagScan, int4, contactCap + 1); DA(d.opList, int, contactCap); DA(d.opDone, uint8_t, contactCap); DA(d.opOv, uint8_t, contactCap);
+  DA(d.flagScan, int4, contactCap + 1); DA(d.opList, int, contactCap); DA(d.opDone, uint8_t, contactCap); DA(d.opCol, uint8_t, contactCap);
   d.ovCapacity = contactCap / 4 + 1024;
-  DA(d.ovList, int, d.ovCapacity); DA(d.cOvIndex, int, contactCap); DA(d.ovCons, OvConstraint, d.ovCapacity);
-  CK(cudaMemsetAsync(d.cOvIndex, 0xff, sizeof(int) * (size_t)contactCap, stream_));
+  DA(d.colList, int, (size_t)kGraphColorCount * contactCap); DA(d.cLocal, int, contactCap); DA(d.cRestGroup, uint8_t, contactCap); DA(d.ovCons, OvConstraint, d.ovCapacity);
+  CK(cudaMemsetAsync(d.cLocal, 0xff, sizeof(int) * (size_t)contactCap, stream_));
   int cc = d.constraintCapacity;
   DA(d.sA, float4, cc); DA(d.sB, float4, cc); DA(d.sC, float4, cc); DA(d.sD, float4, cc); DA(d.sE, float4, cc); DA(d.sF, float4, cc);
   DA(d.sG, float4, cc); DA(d.sH, float4, cc); DA(d.sI, float4, cc); DA(d.sJ, float4, cc); DA(d.sContact, int, cc); DA(d.cConstraint, int, contactCap);
@@ -1674,8 +1669,8 @@ int World::readContacts(B2CContactRead* dst, int capacity, int* count) {
   if (!onDevice_) return B2C_OK;
   int rc = synchronize(); if (rc) return rc;
   int n = hostScalars_->contactNext;
-  std::vector<int2> cShape; std::vector<uint32_t> cFlags; std::vector<int> cColor; std::vector<float4> cMat, mN, mA0, mA1, mB0, mB1, mC0, mC1;
-  if (fetch(cShape, d_.cShape, n, stream_) | fetch(cFlags, d_.cFlags, n, stream_) | fetch(cColor, d_.cColor, n, stream_) | fetch(cMat, d_.cMat, n, stream_) |
+  std::vector<int2> cShape; std::vector<uint32_t> cFlags; std::vector<int> cColor, cLocal; std::vector<float4> cMat, mN, mA0, mA1, mB0, mB1, mC0, mC1;
+  if (fetch(cShape, d_.cShape, n, stream_) | fetch(cFlags, d_.cFlags, n, stream_) | fetch(cColor, d_.cColor, n, stream_) | fetch(cLocal, d_.cLocal, n, stream_) | fetch(cMat, d_.cMat, n, stream_) |
       fetch(mN, d_.mN, n, stream_) | fetch(mA0, d_.mA0, n, stream_) | fetch(mA1, d_.mA1, n, stream_) | fetch(mB0, d_.mB0, n, stream_) |
       fetch(mB1, d_.mB1, n, stream_) | fetch(mC0, d_.mC0, n, stream_) | fetch(mC1, d_.mC1, n, stream_))
     return fail(B2C_E_CUDA, "read_contacts copy failed");
@@ -1685,7 +1680,7 @@ int World::readContacts(B2CContactRead* dst, int capacity, int* count) {
     if (!(cFlags[i] & CF_ALIVE)) continue;
     if (k < capacity) {
       B2CContactRead r; memset(&r, 0, sizeof(r));
-      r.contactId = i; r.shapeIdA = cShape[i].x; r.shapeIdB = cShape[i].y; r.colorIndex = cColor[i];
+      r.contactId = i; r.shapeIdA = cShape[i].x; r.shapeIdB = cShape[i].y; r.colorIndex = cColor[i]; r.localIndex = cColor[i] != -1 ? cLocal[i] : -1;
       r.flags = (cFlags[i] & CF_TOUCHING) ? 1u : 0u;
       r.pointCount = __builtin_bit_cast(int, mN[i].w); r.normal = {mN[i].x, mN[i].y}; r.rollingImpulse = mN[i].z;
       r.friction = cMat[i].x; r.restitution = cMat[i].y; r.rollingResistance = cMat[i].z; r.tangentSpeed = cMat[i].w;

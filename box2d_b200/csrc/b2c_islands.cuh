@@ -228,15 +228,17 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
   // PrepareContacts for this island: lanes are built straight into registers (CACHED) or into the planes (large islands).
   // Velocities read here are the pre-step ones: nothing has integrated yet.
   Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int2 loc = make_int2(-1, -1); int myContact = -1;
+  // anyRest: one of this island's constraints sits in an 8-lane group (of the reference's colour arrays) that ApplyRestitution does not skip
+  const bool worldRest = d.sc->anyRestitution != 0;
   bool anyRest = false;
   if (CACHED) {
     if (tid < K) {
       myContact = d.sContact[cBegin + tid];
       computeLane(d, sp, myContact, c, I, J); loc = d.sLocal[cBegin + tid];
-      anyRest = !(c.restitution == 0.0f);
+      anyRest = worldRest && d.cRestGroup[myContact];
     } else myActive = -1;
   } else {
-    for (int t = tid; t < K; t += T) { Lane l; float4 li, lj; computeLane(d, sp, d.sContact[cBegin + t], l, li, lj); writeLane(d, cBegin + t, l, li, lj); anyRest |= !(l.restitution == 0.0f); }
+    for (int t = tid; t < K; t += T) { int ci = d.sContact[cBegin + t]; Lane l; float4 li, lj; computeLane(d, sp, ci, l, li, lj); writeLane(d, cBegin + t, l, li, lj); anyRest |= worldRest && d.cRestGroup[ci]; }
   }
   const bool islandRestitution = __syncthreads_or(anyRest);
   for (int sub = 0; sub < sp.subStepCount; sub++) {
@@ -267,15 +269,12 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
     }
   }
   if (islandRestitution) {
-    if (CACHED && tid < K) writeLane(d, cBegin + tid, c, I, J);                     // ApplyRestitution per color, 8-lane groups in this island's order
+    if (CACHED && tid < K) writeLane(d, cBegin + tid, c, I, J);                     // ApplyRestitution per colour; cRestGroup = the lane's 8-lane group is not AllZeroW
     __syncthreads();
     for (int k = 0; k < kOverflowIndex; k++) {
       if (colorOff[k] == colorOff[k + 1]) continue;
       for (int t = colorOff[k] + tid; t < colorOff[k + 1]; t += T) {
-        int g0 = colorOff[k] + ((t - colorOff[k]) & ~7);
-        bool allZero = true;
-        for (int q = g0; q < g0 + 8 && q < colorOff[k + 1]; q++) if (!(d.sD[cBegin + q].w == 0.0f)) allZero = false;
-        if (allZero) continue;
+        if (!d.cRestGroup[d.sContact[cBegin + t]]) continue;
         Lane l; loadLane(d, cBegin + t, l, false); int2 lc = d.sLocal[cBegin + t]; float4 li = d.sI[cBegin + t], lj = d.sJ[cBegin + t];
         restitutionLane(bs, sp, l, lc.x, lc.y, li, lj); d.sI[cBegin + t] = li; d.sJ[cBegin + t] = lj;
       }

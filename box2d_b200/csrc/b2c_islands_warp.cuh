@@ -60,10 +60,12 @@ __global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_w
     const int K = sl.colorOff[kGraphColorCount];
     BodyRows bs{sl.s0, sl.s1};
     // PrepareContacts into the slice (velocities are the pre-step ones)
+    const bool worldRest = d.sc->anyRestitution != 0;
     bool anyRest = false;
     for (int t = lane; t < K; t += 32) {
       Lane c; float4 I, J;
-      computeLane(d, sp, d.sContact[cBegin + t], c, I, J);
+      const int ci = d.sContact[cBegin + t];
+      computeLane(d, sp, ci, c, I, J);
       int2 loc = d.sLocal[cBegin + t];
       sl.plane[0][t] = make_float4(__int_as_float(loc.x), __int_as_float(loc.y), c.mA, c.mB);
       sl.plane[1][t] = make_float4(c.iA, c.iB, c.n.x, c.n.y);
@@ -74,7 +76,7 @@ __global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_w
       sl.plane[6][t] = make_float4(c.normalMass1, c.tangentMass1, c.normalMass2, c.tangentMass2);
       sl.plane[7][t] = make_float4(c.baseSep1, c.baseSep2, c.relVel1, c.relVel2);
       sl.plane[8][t] = I; sl.plane[9][t] = J;
-      anyRest |= !(c.restitution == 0.0f);
+      anyRest |= worldRest && d.cRestGroup[ci];
     }
     const bool islandRestitution = __any_sync(full, anyRest);
     __syncwarp();
@@ -108,15 +110,12 @@ __global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_w
         __syncwarp();
       }
     }
-    if (islandRestitution) {                       // ApplyRestitution per colour, 8-lane groups in this island's order (as in runIsland)
+    if (islandRestitution) {                       // ApplyRestitution per colour; cRestGroup = the lane's 8-lane group is not AllZeroW (as in runIsland)
       for (int k = 0; k < kOverflowIndex; k++) {
         const int b = sl.colorOff[k], e = sl.colorOff[k + 1];
         if (b == e) continue;
         for (int t = b + lane; t < e; t += 32) {
-          int g0 = b + ((t - b) & ~7);
-          bool allZero = true;
-          for (int q = g0; q < g0 + 8 && q < e; q++) if (!(sl.plane[3][q].w == 0.0f)) allZero = false;
-          if (allZero) continue;
+          if (!d.cRestGroup[d.sContact[cBegin + t]]) continue;
           Lane c; sliceLoadLane(sl, t, c, false); float4 I = sl.plane[8][t], J = sl.plane[9][t];
           restitutionLane(bs, sp, c, c.indexA, c.indexB, I, J); sl.plane[8][t] = I; sl.plane[9][t] = J;
         }

@@ -11,31 +11,52 @@
 
 namespace b2c {
 
-// contactSims of the overflow colour, maintained in the reference's order. `ops` are this step's graph ops in ascending
-// contact id (the order World.Collide applies them, src/World.cs:382-450); opOv[k] = 1 add to overflow, 2 remove from it.
-__device__ void ovReplayOps(const WorldDev& d, int n) {
+// GraphColor.contactSims of EVERY colour in the reference's order. `ops` are this step's graph ops in ascending contact id (the order
+// World.Collide applies them, src/World.cs:382-450); opCol[k] = colour | 0x40 (AddContactToGraph appended it) or | 0x80
+// (RemoveContactFromGraph swap-removed it). Arrays of different colours are independent, so one warp replays one colour: the lanes
+// scan the op list 32 at a time, lane 0 applies the ops of its colour in order. The array order decides which constraints share an
+// 8-lane SIMD group in ApplyRestitutionTask (src/ContactSolver.cs:913-923), the order of the hit events (src/Solver.cs:1154-1160) and,
+// for the overflow colour, the order of the serial solve.
+__device__ void colReplayOps(const WorldDev& d, int n) {
   Scalars& s = *d.sc;
-  int count = s.ovCount;
-  for (int k = 0; k < n; k++) {
-    int what = d.opOv[k];
-    if (!what) continue;
-    int id = d.opList[k];
-    if (what == 1) {                               // color.contactSims.Add  (:184-185)
-      if (count >= d.ovCapacity) { atomicOr(&s.errorFlags, (int)ERR_CONTACT_CAPACITY); continue; }
-      d.ovList[count] = id; d.cOvIndex[id] = count; count++;
-    } else {                                       // RemoveSwap(localIndex)  (:230-240)
-      int li = d.cOvIndex[id], last = count - 1;
-      if (li < 0 || li > last) continue;
-      if (li != last) { int moved = d.ovList[last]; d.ovList[li] = moved; d.cOvIndex[moved] = li; }
-      d.cOvIndex[id] = -1; count--;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+  const unsigned full = 0xffffffffu;
+  for (int c = warp; c < kGraphColorCount; c += warps) {
+    int count = s.colLen[c];
+    int* arr = d.colList + (size_t)c * d.contactCapacity;
+    const int cap = c == kOverflowIndex ? (d.ovCapacity < d.contactCapacity ? d.ovCapacity : d.contactCapacity) : d.contactCapacity;
+    for (int base = 0; base < n; base += 32) {
+      const int k = base + lane;
+      const int oc = k < n ? (int)d.opCol[k] : 0;
+      const bool mine = (oc & 0xc0) != 0 && (oc & 0x3f) == c;
+      unsigned m = __ballot_sync(full, mine);
+      if (m == 0) continue;
+      const int id = mine ? d.opList[k] : -1;
+      while (m) {
+        const int b = __ffs((int)m) - 1; m &= m - 1;
+        const int oid = __shfl_sync(full, id, b), ooc = __shfl_sync(full, oc, b);
+        if (lane == 0) {
+          if (ooc & 0x40) {                          // color.contactSims.Add  (:184-185)
+            if (count >= cap) atomicOr(&s.errorFlags, (int)ERR_CONTACT_CAPACITY);
+            else { arr[count] = oid; d.cLocal[oid] = count; count++; }
+          } else {                                   // RemoveSwap(localIndex)  (:230-240)
+            const int li = d.cLocal[oid], last = count - 1;
+            if (li >= 0 && li <= last) {
+              if (li != last) { int moved = arr[last]; arr[li] = moved; d.cLocal[moved] = li; }
+              d.cLocal[oid] = -1; count--;
+            }
+          }
+        }
+      }
     }
+    if (lane == 0) s.colLen[c] = count;
+    __syncwarp();
   }
-  s.ovCount = count;
 }
 
 // PrepareOverflowContacts :40-115, one thread per overflow constraint
 __device__ void ovPrepare(const WorldDev& d, const StepParams& sp, int k) {
-  const int ci = d.ovList[k];
+  const int ci = d.colList[(size_t)kOverflowIndex * d.contactCapacity + k];
   OvConstraint& c = d.ovCons[k];
   const float warmStartScale = sp.enableWarmStarting ? 1.0f : 0.0f;
   int2 idx = d.cSim[ci];
@@ -68,7 +89,6 @@ __device__ void ovPrepare(const WorldDev& d, const StepParams& sp, int k) {
     V2 vrA = vA + crossSV(wA, rA), vrB = vB + crossSV(wB, rB);
     cp.relativeVelocity = dot(normal, vrB - vrA);
   }
-  if (!(c.restitution == 0.0f)) d.sc->anyRestitution = 1;
 }
 
 struct OvBody { V2 v; float w; V2 dp; Rot dq; bool dynamic; };
@@ -192,7 +212,7 @@ __device__ void ovRestitution(const WorldDev& d, const StepParams& sp, int n) {
 // StoreOverflowImpulses :323-350, one thread per constraint
 __device__ void ovStoreImpulses(const WorldDev& d, int k) {
   const OvConstraint& c = d.ovCons[k];
-  const int ci = d.ovList[k];
+  const int ci = d.colList[(size_t)kOverflowIndex * d.contactCapacity + k];
   float4 mn = d.mN[ci];
   const int pointCount = (int)fbits(mn.w);
   if (pointCount > 0) { float4 b = d.mB0[ci]; b.y = c.p0.normalImpulse; b.z = c.p0.tangentImpulse; b.w = c.p0.totalNormalImpulse; d.mB0[ci] = b; d.mC0[ci].z = c.p0.relativeVelocity; }

@@ -283,7 +283,7 @@ __device__ void p_create_contacts(const WorldDev& d, int tid, int stride) {
     d.cColor[id] = -1;
     d.cGen[id] = d.cGen[id] + 1;
     d.cStamp[id] = d.sc->contactStamp + (unsigned)r;
-    d.cConstraint[id] = -1;
+    d.cConstraint[id] = -1; d.cLocal[id] = -1;
     float4 ma = sa.material, mb = sb.material;
     d.cMat[id] = make_float4(sqrtf(ma.x * mb.x), netMax(ma.y, mb.y), 0.0f, 0.0f);   // src/World.cs:139-140
     d.cMass[id] = make_float4(0, 0, 0, 0);
@@ -421,6 +421,7 @@ __device__ void p_collide(const WorldDev& d, const StepParams& sp, int tid, int 
         d.cMat[i] = make_float4(friction, restitution, rolling, ma.w + mb.w);
         int pointCount = m.pointCount;
         bool touching = pointCount > 0;
+        if (touching && !(restitution == 0.0f)) d.sc->anyRestitution = 1;    // some 8-lane group is not AllZeroW (src/ContactSolver.cs:923): p_rest_groups finds which
         if (!sp.enableSpeculative && pointCount == 2) {            // Q7: tests point0 twice (src/Contact.cs:366,371)
           if (m.p0.separation > 1.5f * kLinearSlop) { m.p0 = m.p1; m.pointCount = 1; }
           pointCount = m.pointCount;
@@ -500,9 +501,7 @@ __device__ void p_color_ops(const WorldDev& d) {
   __shared__ int sRemaining;
   int n = d.sc->opCount;
   if (n == 0) return;
-  for (int k = threadIdx.x; k < n; k += blockDim.x) { d.opDone[k] = 0; d.opOv[k] = 0; }
-  __shared__ int sAnyOv;
-  if (threadIdx.x == 0) sAnyOv = 0;
+  for (int k = threadIdx.x; k < n; k += blockDim.x) { d.opDone[k] = 0; d.opCol[k] = 0; }
   __syncthreads();
   int rounds = 0;
   while (true) {
@@ -539,9 +538,9 @@ __device__ void p_color_ops(const WorldDev& d) {
         if (typeA == kDynamicBody) d.bodyColorMask[b.x] = mA;
         if (typeB == kDynamicBody) d.bodyColorMask[b.y] = mB;
         d.cColor[id] = c;
-        if (c == kOverflowIndex) { d.opOv[k] = 1; sAnyOv = 1; }
+        d.opCol[k] = (uint8_t)(0x40 | c);
       } else {                                     // remove
-        if (color == kOverflowIndex) { d.opOv[k] = 2; sAnyOv = 1; }
+        d.opCol[k] = (uint8_t)(0x80 | color);
         if (color != kOverflowIndex) {
           if (typeA == kDynamicBody) d.bodyColorMask[b.x] &= ~(1u << color);
           if (typeB == kDynamicBody) d.bodyColorMask[b.y] &= ~(1u << color);
@@ -562,7 +561,9 @@ __device__ void p_color_ops(const WorldDev& d) {
     if (sRemaining == 0) break;
     __syncthreads();
   }
-  if (threadIdx.x == 0) { d.sc->colorRounds = rounds; if (sAnyOv) ovReplayOps(d, n); }
+  if (threadIdx.x == 0) d.sc->colorRounds = rounds;
+  __syncthreads();
+  colReplayOps(d, n);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -691,7 +692,6 @@ __device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
   Lane c; float4 I, J;
   computeLane(d, sp, d.sContact[t], c, I, J);
   writeLane(d, t, c, I, J);
-  if (!(c.restitution == 0.0f)) d.sc->anyRestitution = 1;
 }
 
 // WarmStartContactsTask :686-744
@@ -791,8 +791,7 @@ template <bool USE_BIAS> __device__ __forceinline__ void solveContact(const Worl
   d.sI[t] = I; d.sJ[t] = J;
 }
 
-// ApplyRestitutionTask :913-989, with quirk Q1 (multiplies by the compare mask, not the blended mass). The reference skips an
-// 8-lane SIMD group when all its lanes have restitution 0; groups here are 8 consecutive constraints of the device's color order.
+// ApplyRestitutionTask :913-989, with quirk Q1 (multiplies by the compare mask, not the blended mass).
 __device__ __forceinline__ void restitutionPoint(BodyW& bA, BodyW& bB, const Lane& c, V2 rA, V2 rB, float relativeVelocity, float& normalImpulse,
                                                  float& totalP, float threshold, bool restitutionMask) {
   bool mask1 = (relativeVelocity + threshold) > 0.0f;
@@ -815,16 +814,29 @@ __device__ __forceinline__ void restitutionLane(const BodyRows& bs, const StepPa
   restitutionPoint(bA, bB, c, c.rA2, c.rB2, c.relVel2, I.z, J.y, sp.restitutionThreshold, restitutionMask);
   bs.store(ia, bA); bs.store(ib, bB);
 }
-__device__ __forceinline__ void restitutionContact(const WorldDev& d, const StepParams& sp, int t, int colorBegin, int colorEnd) {
-  int g0 = colorBegin + ((t - colorBegin) & ~7);
-  bool allZero = true;
-  for (int k = g0; k < g0 + 8 && k < colorEnd; k++) if (!(d.sD[k].w == 0.0f)) allZero = false;
-  if (allZero) return;
+__device__ __forceinline__ void restitutionContact(const WorldDev& d, const StepParams& sp, int t) {
+  const int ci = d.sContact[t];
+  if (ci < 0 || !d.cRestGroup[ci]) return;         // AllZeroW group (or padding lane)
   Lane c; loadLane(d, t, c, false);
   float4 I = d.sI[t], J = d.sJ[t];
   BodyRows bs{d.st0, d.st1};
   restitutionLane(bs, sp, c, c.indexA, c.indexB, I, J);
   d.sI[t] = I; d.sJ[t] = J;
+}
+// The reference skips an 8-lane SIMD group when all its lanes have restitution 0 (AllZeroW, :923); otherwise EVERY lane of the group runs
+// the code above, and under quirk Q1 a zero-restitution lane of such a group has its normal impulses wiped. A group is 8 consecutive
+// entries of the colour's contactSims array (colList): every touching contact with restitution != 0 flags the members of its group.
+__device__ void p_rest_groups(const WorldDev& d, int tid, int stride) {
+  const int n = d.sc->contactNext;
+  for (int i = tid; i < n; i += stride) {
+    if ((d.cFlags[i] & (CF_ALIVE | CF_TOUCHING)) != (CF_ALIVE | CF_TOUCHING)) continue;
+    if (d.cMat[i].y == 0.0f) continue;
+    const int c = d.cColor[i], li = d.cLocal[i];
+    if (c < 0 || c >= kOverflowIndex || li < 0) continue;      // the overflow colour is solved by scalar code without groups (:265-322)
+    const int* arr = d.colList + (size_t)c * d.contactCapacity;
+    const int g0 = li & ~7, len = d.sc->colLen[c];
+    for (int k = g0; k < g0 + 8 && k < len; k++) d.cRestGroup[arr[k]] = 1;
+  }
 }
 // StoreImpulsesTask :990-1025
 __device__ __forceinline__ void storeImpulses(const WorldDev& d, int t) {
@@ -1053,7 +1065,7 @@ __device__ void phase_prepare(const WorldDev& d, const StepParams& sp, bool cont
   for (int t = gtid(); t < total; t += gsize()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
   int nj = d.jointColorStart[kGraphColorCount];
   for (int k = gtid(); k < nj; k += gsize()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
-  int nov = s.ovCount;
+  int nov = s.colLen[kOverflowIndex];
   for (int k = gtid(); k < nov; k += gsize()) ovPrepare(d, sp, k);
 }
 
@@ -1082,14 +1094,13 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   const int tid = gtid(), stride = gsize();
   const int awake = s.bigBodyCount;               // bodies of grid-path islands (+ kinematic bodies some constraint reads)
   if (awake == 0 && activeCount == 0) return;     // everything lives in small islands / free bodies: no grid barrier at all
-  const int nov = s.ovCount;                      // overflow colour: one thread, array order, before the colours of each stage (:633-670)
+  const int nov = s.colLen[kOverflowIndex];                      // overflow colour: one thread, array order, before the colours of each stage (:633-670)
   Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int myA = -1, myContact = -1;
   const BodyRows bs{d.st0, d.st1};
   if (CACHED) {
     if (tid < s.smallConStart) myContact = d.sContact[tid];
     if (myContact >= 0) {
       computeLane(d, sp, myContact, c, I, J);      // reads pre-step velocities: the barrier below keeps IntegrateVelocities behind it
-      if (!(c.restitution == 0.0f)) d.sc->anyRestitution = 1;
       for (int a = 0; a < activeCount; a++) if (tid >= sBegin[a] && tid < sEnd[a]) myA = a;
     }
     grid.sync();
@@ -1121,12 +1132,12 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
       grid.sync();
     }
   }
-  // restitution: skipped entirely (like every AllZeroW group) when no constraint has restitution (flag set by k_prepare)
+  // restitution: skipped entirely (like every AllZeroW group) when no touching contact has restitution (flag set by p_collide)
   if (s.anyRestitution) {
     if (CACHED) { if (myContact >= 0) writeLane(d, tid, c, I, J); grid.sync(); }      // restitution works on 8-lane groups of the planes
     if (nov > 0) { if (tid == 0) ovRestitution(d, sp, nov); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
-      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) restitutionContact(d, sp, t, sBegin[a], sEnd[a]);
+      for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) restitutionContact(d, sp, t);
       grid.sync();
     }
   }
@@ -1283,21 +1294,35 @@ __device__ void p_refit(const WorldDev& d, int tid, int stride) {
   }
 }
 
-// contact hit events (src/Solver.cs:1151-1190); order within a step is not defined by this build (appended atomically)
-__device__ void p_hit_events(const WorldDev& d, const StepParams& sp, int tid, int stride) {
-  int n = d.sc->contactNext;
-  for (int i = tid; i < n; i += stride) {
-    uint32_t flags = d.cFlags[i];
-    if ((flags & (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) != (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) continue;
-    float4 mn = d.mN[i];
-    int pointCount = (int)fbits(mn.w);
-    float best = sp.hitEventThreshold; V2 point = mk(0, 0); bool hit = false;
-    if (pointCount > 0) { float4 b = d.mB0[i], c = d.mC0[i]; float a = -c.z; if (a > best && b.w > 0.0f) { best = a; point = mk(c.x, c.y); hit = true; } }
-    if (pointCount > 1) { float4 b = d.mB1[i], c = d.mC1[i]; float a = -c.z; if (a > best && b.w > 0.0f) { best = a; point = mk(c.x, c.y); hit = true; } }
-    if (hit) {
-      int k = atomicAdd(&d.sc->hitCount, 1);
-      if (k < d.eventCapacity) { int2 sh = d.cShape[i]; B2CContactHitEvent ev = {sh.x, sh.y, {point.x, point.y}, {mn.x, mn.y}, best}; d.hitEvents[k] = ev; }
-    }
+// contact hit events (src/Solver.cs:1151-1190) in the reference's order: colours 0..23, each colour's contactSims array front to back.
+// Position p of the concatenated colour arrays (colList) -> contact slot; FILL=false writes the hit flag of every position (then an
+// exclusive prefix sum ranks them), FILL=true writes the event of every flagged position at its rank.
+__device__ __forceinline__ bool hitEventOf(const WorldDev& d, const StepParams& sp, int i, B2CContactHitEvent* ev) {
+  uint32_t flags = d.cFlags[i];
+  if ((flags & (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) != (CF_ALIVE | CF_TOUCHING | CF_ENABLE_HIT)) return false;
+  float4 mn = d.mN[i];
+  int pointCount = (int)fbits(mn.w);
+  float best = sp.hitEventThreshold; V2 point = mk(0, 0); bool hit = false;
+  if (pointCount > 0) { float4 b = d.mB0[i], c = d.mC0[i]; float a = -c.z; if (a > best && b.w > 0.0f) { best = a; point = mk(c.x, c.y); hit = true; } }
+  if (pointCount > 1) { float4 b = d.mB1[i], c = d.mC1[i]; float a = -c.z; if (a > best && b.w > 0.0f) { best = a; point = mk(c.x, c.y); hit = true; } }
+  if (hit && ev) { int2 sh = d.cShape[i]; B2CContactHitEvent e = {sh.x, sh.y, {point.x, point.y}, {mn.x, mn.y}, best}; *ev = e; }
+  return hit;
+}
+template <bool FILL> __device__ void p_hit_events(const WorldDev& d, const StepParams& sp, int tid, int stride, int* flags, const int* sums) {
+  __shared__ int sStart[kGraphColorCount + 1];
+  if (threadIdx.x == 0) { int acc = 0; for (int c = 0; c < kGraphColorCount; c++) { sStart[c] = acc; acc += d.sc->colLen[c]; } sStart[kGraphColorCount] = acc; }
+  __syncthreads();
+  const int total = sStart[kGraphColorCount];
+  for (int p = tid; p < total; p += stride) {
+    int c = 0;
+    while (p >= sStart[c + 1]) c++;
+    const int i = d.colList[(size_t)c * d.contactCapacity + (p - sStart[c])];
+    if (!FILL) { flags[p] = hitEventOf(d, sp, i, nullptr) ? 1 : 0; continue; }
+    const int rank = flags[p] + sums[p / kCoopThreads];
+    const int next = (p + 1 < total) ? flags[p + 1] + sums[(p + 1) / kCoopThreads] : d.sc->hitCount;
+    if (next == rank || rank >= d.eventCapacity) continue;
+    B2CContactHitEvent ev;
+    if (hitEventOf(d, sp, i, &ev)) d.hitEvents[rank] = ev;
   }
 }
 __device__ void p_step_finish(const WorldDev& d, int newEndIndex) {
@@ -1477,6 +1502,12 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   stamp(d, 5);
   phase_collide(grid, d, sp);
   grid.sync();
+  if (s.anyRestitution) {                         // rare: which 8-lane groups of the colour arrays ApplyRestitution will not skip
+    for (int i = gtid(); i < s.contactNext; i += gsize()) d.cRestGroup[i] = 0;
+    grid.sync();
+    p_rest_groups(d, gtid(), gsize());
+    grid.sync();
+  }
   stamp(d, 2);
   dbgContacts(d, 2);
   const bool dirty = s.graphDirty != 0;
@@ -1489,7 +1520,7 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   // Measured (B200): the cluster wins where stages are many and thin (joints, an active overflow colour) or the lanes fit its registers;
   // a contact-only scene between 8 192 and 75 776 constraints keeps its lanes in the grid's registers, which beats the cheaper barrier.
   const bool clusterFits = s.smallConStart + gridJoints <= 12 * sp.clusterThreads && s.bigBodyCount <= 8 * sp.clusterThreads;
-  const bool clusterWins = gridJoints > 0 || s.ovCount > 0 || s.smallConStart <= sp.clusterThreads || s.smallConStart > gsize();
+  const bool clusterWins = gridJoints > 0 || s.colLen[kOverflowIndex] > 0 || s.smallConStart <= sp.clusterThreads || s.smallConStart > gsize();
   const bool clusterPath = gridWork && sp.clusterThreads > 0 && clusterFits && clusterWins;
   if (gtid() == 0) s.clusterSolve = clusterPath ? 1 : 0;
   const bool cachedLanes = s.smallConStart <= (clusterPath ? sp.clusterThreads : gsize());   // one grid-path constraint per thread: lanes stay in registers
@@ -1517,7 +1548,14 @@ __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, Ste
   Scalars& s = *d.sc;
   if (d.debugChecksums == 1) { dbgBodies(d, 8); dbgContacts(d, 9); grid.sync(); }
   p_finalize(d, sp, tid, stride);
-  if (s.anyHitShapes) p_hit_events(d, sp, tid, stride);
+  if (s.anyHitShapes) {                           // hit events, ordered by (colour, position in the colour's array)
+    int* hitFlags = (int*)d.flagScan; int* hitSums = (int*)d.scanBlockSums4;
+    int total = 0; for (int c = 0; c < kGraphColorCount; c++) total += s.colLen[c];
+    p_hit_events<false>(d, sp, tid, stride, hitFlags, hitSums);
+    grid.sync();
+    gridScan<int>(grid, hitFlags, hitSums, total, &s.hitCount);
+    p_hit_events<true>(d, sp, tid, stride, hitFlags, hitSums);
+  }
   grid.sync();
   if (s.enlargedShapeCount > 0) {
     gridScan<int>(grid, d.bodyEnlargedCount, d.scanBlockSums, d.awakeCount, &s.moveCount);
@@ -1565,7 +1603,7 @@ int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch
     CK(cudaLaunchKernelEx(&cfg, k_solver_cluster, d, sp));
   }
   if (warpMode) k_solver_islands_warp<<<coopBlocks_, 32 * kWarpIslandsPerCta, kWarpIslandsPerCta * sizeof(WarpIslandSlice), stream_>>>(d, sp);
-  k_solver_islands<<<148 * 8, kIslandThreads, 0, stream_>>>(d, sp, (int)warpMode);
+  k_solver_islands<<<coopBlocks_ * 8, kIslandThreads, 0, stream_>>>(d, sp, (int)warpMode);
   CK(rec(pe[2]));
   { void* args[] = {(void*)&d, (void*)&sp, (void*)&newEndIndex}; CK(cudaLaunchCooperativeKernel((void*)k_finalize_phase, cgrid, cblock, args, 0, stream_)); }
   CK(rec(pe[3]));
@@ -1714,7 +1752,7 @@ int World::getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count) {
   CK(cudaSetDevice(device_));
   if (!movesFetched_) {
     int n = d_.awakeCount;
-    k_pack_moves<<<gridFor(n, kThreads, 148 * 8), kThreads, 0, stream_>>>(d_, dMoveEvents_);
+    k_pack_moves<<<gridFor(n, kThreads, (coopBlocks_ > 0 ? coopBlocks_ : 148) * 8), kThreads, 0, stream_>>>(d_, dMoveEvents_);
     CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
     movesFetched_ = true;
     streamMoves_ = true; d_.moveOut = hMoveEventsDev_ ? hMoveEventsDev_ : dMoveEvents_;   // from now on FinalizeBodies fills the events (mapped host memory, else device array + copy in step())
@@ -1730,7 +1768,7 @@ int World::getBodyEvents(const B2CBodyRead** records, int* count) {
   CK(cudaSetDevice(device_));
   if (!bodiesFetched_) {
     int n = d_.bodyCapacity;
-    k_pack_bodies<<<gridFor(n, kThreads, 148 * 8), kThreads, 0, stream_>>>(d_, dBodyRead_);
+    k_pack_bodies<<<gridFor(n, kThreads, (coopBlocks_ > 0 ? coopBlocks_ : 148) * 8), kThreads, 0, stream_>>>(d_, dBodyRead_);
     CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
     bodiesFetched_ = true;
     streamBodies_ = true; d_.bodyOut = dBodyRead_;   // from now on FinalizeBodies keeps the records current and step() copies them

@@ -102,7 +102,8 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int clusterSolve;    // this step's grid-path constraints are solved by k_solver_cluster (one thread-block cluster) instead of the front kernel
   int colorTotal[kGraphColorCount], bigCursor[kGraphColorCount];
   int bigQueryCount, bigHitTotal, bigGroupTotal, staticRanksValid;   // wide broadphase queries (b2c_bigquery.cuh)
-  int rebuildLevels[3], ovCount;        // ovCount: contacts in the overflow colour
+  int rebuildLevels[3];
+  int colLen[kGraphColorCount];         // GraphColor.contactSims.Count per colour (src/ConstraintGraph.cs:10-24); [kOverflowIndex] = contacts in the overflow colour
   unsigned long long dbg[16];           // order-independent state checksums per phase (B2CUDA_DEBUG_CHECKSUMS=1; b2cuda_world_debug_checksums)
 };
 
@@ -117,6 +118,7 @@ struct StepParams {    // src/Solver.cs:57-112 StepContext (scalars only)
   int clusterThreads;  // > 0: k_solver_cluster follows the front kernel with this many threads (one cluster); 0: grid path only
 };
 
+struct WorldDev;
 struct WorldDev {
   // --- awake body set, index = awake sim index (src/Body.cs:119-173 BodyState + BodySim) ---
   float4* st0;         // v.x v.y w flags
@@ -192,9 +194,11 @@ struct WorldDev {
   int4* flagScan;      // per contact slot: (begin, end, destroy, op) flags -> exclusive ranks
   int* opList;         // contact ids with a graph op (add/remove), ascending
   uint8_t* opDone;
-  uint8_t* opOv;       // per op: 1 = added to the overflow colour, 2 = removed from it
-  int* ovList;         // contact ids of the overflow colour in the reference's array order
-  int* cOvIndex;       // per contact slot: position in ovList (Contact.localIndex for that colour) or -1
+  uint8_t* opCol;      // per op: colour | 0x40 (added to it) or | 0x80 (removed from it)
+  int* colList;        // [kGraphColorCount][contactCapacity] contact ids of every colour in the reference's array order (GraphColor.contactSims:
+                       // append on add, swap-with-last on remove) — decides the 8-lane restitution groups and the hit-event order
+  int* cLocal;         // per contact slot: Contact.localIndex inside its colour's array, or -1
+  uint8_t* cRestGroup; // per contact slot: its 8-lane group (localIndex >> 3 within the colour) holds a lane with restitution != 0
   OvConstraint* ovCons; int ovCapacity;
   // --- solver constraint planes, index = constraint (grouped by color) ---
   float4* sA; float4* sB; float4* sC; float4* sD; float4* sE; float4* sF; float4* sG; float4* sH; float4* sI; float4* sJ;
@@ -229,5 +233,25 @@ struct WorldDev {
   // generic scan scratch
   int* scanBlockSums; int4* scanBlockSums4;
 };
+
+
+#ifdef __CUDACC__
+// GraphColor.contactSims as the reference maintains it: Add (src/ConstraintGraph.cs:184-185) and RemoveSwap (:230-240, include/Box2D.cs:9-19)
+__device__ __forceinline__ bool colAppend(const WorldDev& d, int c, int id) {
+  Scalars& s = *d.sc;
+  int n = s.colLen[c];
+  if (n >= d.contactCapacity || (c == kOverflowIndex && n >= d.ovCapacity)) return false;
+  d.colList[(size_t)c * d.contactCapacity + n] = id; d.cLocal[id] = n; s.colLen[c] = n + 1;
+  return true;
+}
+__device__ __forceinline__ void colRemoveSwap(const WorldDev& d, int c, int id) {
+  Scalars& s = *d.sc;
+  int li = d.cLocal[id], last = s.colLen[c] - 1;
+  if (li < 0 || li > last) return;
+  int* arr = d.colList + (size_t)c * d.contactCapacity;
+  if (li != last) { int moved = arr[last]; arr[li] = moved; d.cLocal[moved] = li; }
+  d.cLocal[id] = -1; s.colLen[c] = last;
+}
+#endif
 
 }  // namespace b2c

@@ -344,6 +344,46 @@ def wheel_rig(world, copies=1, pitch=12.0):
     return out
 
 
+def bounce_mix(world, n=48, seed=11, hits=True):
+    """Restitution != 0 mixed with restitution 0 (ApplyRestitutionTask, src/ContactSolver.cs:913-989, quirk Q1) and hit events
+    (src/Solver.cs:1151-1190): many separate islands land on one static segment, so their ground contacts share colours and the
+    8-lane SIMD groups of a colour mix zero and non-zero restitution lanes of different islands; bodies that leave the ground again
+    swap-remove their contacts from the colour arrays, which reshuffles the groups and the hit-event order."""
+    bd = api.default_body_def()
+    ground = world.CreateBody(bd)
+    sd0 = _shape_def(enableHitEvents=int(hits))
+    half = 0.6 * n + 12.0
+    world.CreateSegmentShape(ground, sd0, geo.Segment((-half, 0.0), (half, 0.0)))
+    rest = (0.0, 0.6, 0.0, 0.0, 0.9, 0.3, 0.0)
+    shapes = (geo.Circle((0.0, 0.0), 0.25), geo.MakeBox(0.25, 0.2), geo.Capsule((-0.15, 0.0), (0.15, 0.0), 0.15))
+    state = seed
+    bodies = []
+    for k in range(n):
+        state, dx = _uniform(state, -0.05, 0.05)
+        x = (k - 0.5 * (n - 1)) * 1.1 + dx
+        y = 0.6 + (k % 5) * 0.45
+        b = _dynamic_body(world, x, y, linearVelocity=api.Vec2(0.0, -float(2 + (k % 3))))
+        sd = _shape_def(enableHitEvents=int(hits and k % 4 != 3))
+        sd.restitution = rest[k % len(rest)]
+        world.CreateShape(b, sd, shapes[k % 3])
+        bodies.append(b)
+        if k % 6 == 0:      # a second body dropped on top: body-body contacts in the dynamic colours, restitution from either side
+            t = _dynamic_body(world, x, y + 0.7, linearVelocity=api.Vec2(0.0, -3.0))
+            sdt = _shape_def(enableHitEvents=int(hits))
+            sdt.restitution = rest[(k + 1) % len(rest)]
+            world.CreatePolygonShape(t, sdt, geo.MakeBox(0.2, 0.2))
+            bodies.append(t)
+    # a small resting pyramid (restitution 0 everywhere) on the same ground: its ground contacts share colour 22 with the bouncers
+    box = geo.MakeBox(0.5, 0.5)
+    px = 0.5 * (n - 1) * 1.1 + 6.0
+    for i in range(3):
+        for j in range(3 - i):
+            b = _dynamic_body(world, px + (j - (3 - i - 1) * 0.5) * 1.0, 0.5 + i * 1.0)
+            world.CreatePolygonShape(b, sd0, box)
+            bodies.append(b)
+    return ground, bodies
+
+
 def batched_pyramids(world, n_worlds=8192, first=0, rows=10, pitch=15.0, cols=128):
     """BASELINE.json configs[4]: `n_worlds` independent 10-row pyramids (world index first..first+n), each on its own ground,
     x positions jittered per world by splitmix64(seed=world index) so worlds are not bit-copies."""
@@ -361,4 +401,5 @@ SCENES = {
     "joint_zoo": joint_zoo,
     "wheel_rig": wheel_rig,
     "batched_pyramids": batched_pyramids,
+    "bounce_mix": bounce_mix,
 }

@@ -121,8 +121,9 @@ typedef struct B2CManifoldPointRead {   /* include/Collision.cs:916-945 */
   float separation, normalImpulse, tangentImpulse, totalNormalImpulse, normalVelocity;
   uint32_t id, persisted;
 } B2CManifoldPointRead;
-typedef struct B2CContactRead {         /* ContactAPI.GetData api/Contact.cs + graph color (Counters) */
-  int32_t contactId, shapeIdA, shapeIdB, colorIndex;
+typedef struct B2CContactRead {         /* ContactAPI.GetData api/Contact.cs + graph colour and Contact.localIndex (src/Contact.cs:41-47: the position in
+                                           the colour's contactSims array for a touching contact, -1 otherwise) */
+  int32_t contactId, shapeIdA, shapeIdB, colorIndex, localIndex;
   uint32_t flags;                        /* bit0 touching */
   int32_t pointCount;
   B2CVec2 normal; float rollingImpulse, friction, restitution, rollingResistance, tangentSpeed;

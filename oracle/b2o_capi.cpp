@@ -200,7 +200,7 @@ int32_t b2o_world_read_contacts(World* w, B2CContactRead* dst, int32_t capacity,
     if (n < capacity) {
       const ContactSim& s = w->GetContactSim(c);
       B2CContactRead r; memset(&r, 0, sizeof(r));
-      r.contactId = c.contactId; r.shapeIdA = c.shapeIdA; r.shapeIdB = c.shapeIdB; r.colorIndex = c.colorIndex;
+      r.contactId = c.contactId; r.shapeIdA = c.shapeIdA; r.shapeIdB = c.shapeIdB; r.colorIndex = c.colorIndex; r.localIndex = c.colorIndex != -1 ? c.localIndex : -1;
       r.flags = (c.flags & kContactTouching) ? 1u : 0u; r.pointCount = s.manifold.pointCount; r.normal = CV(s.manifold.normal);
       r.rollingImpulse = s.manifold.rollingImpulse; r.friction = s.friction; r.restitution = s.restitution;
       r.rollingResistance = s.rollingResistance; r.tangentSpeed = s.tangentSpeed;

@@ -18,6 +18,7 @@ CASES = {
     "joint_zoo": (lambda w: scenes.joint_zoo(w, copies=2), 40, {}),                       # every joint type (weld/prismatic use Atan2)
     "joint_zoo_exact": (lambda w: scenes.joint_zoo(w, copies=2, angles=False), 40, {}),   # the Atan2-free subset
     "wheel_rig": (lambda w: scenes.wheel_rig(w, copies=2), 30, {}),
+    "bounce_mix": (lambda w: scenes.bounce_mix(w), 45, {}),                                # restitution != 0 (quirk Q1) and hit events
 }
 
 
@@ -34,6 +35,11 @@ def record(world, build, steps):
                                          c["points"]["id"][:, 0].astype(np.int32), c["points"]["id"][:, 1].astype(np.int32)], axis=1)
         out[f"s{s}_begin"] = np.stack([ev[0]["shapeIdA"], ev[0]["shapeIdB"], ev[0]["contactId"]], axis=1) if len(ev[0]) else np.zeros((0, 3), np.int32)
         out[f"s{s}_end"] = np.stack([ev[1]["shapeIdA"], ev[1]["shapeIdB"], ev[1]["contactId"]], axis=1) if len(ev[1]) else np.zeros((0, 3), np.int32)
+        out[f"s{s}_local"] = np.asarray(c["localIndex"], dtype=np.int32)          # position in the colour's contactSims array (restitution groups, hit order)
+        h = ev[2]
+        out[f"s{s}_hit_ids"] = np.stack([h["shapeIdA"], h["shapeIdB"]], axis=1) if len(h) else np.zeros((0, 2), np.int32)
+        out[f"s{s}_hit_data"] = (np.stack([h["point"]["x"], h["point"]["y"], h["normal"]["x"], h["normal"]["y"], h["approachSpeed"]], axis=1).astype(np.float32)
+                                 if len(h) else np.zeros((0, 5), np.float32))
         if s == 0 or s == steps - 1:
             j = world.ReadJoints()
             if len(j):

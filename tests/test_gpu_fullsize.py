@@ -13,14 +13,31 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("name,steps", [("many_pyramids", 10), ("large_pyramid", 10), ("joint_grid", 10), ("tumbler", 10)])
 def test_baseline_config_first_steps_bit_exact(name, steps):
-    res = parity.run_pair(lambda w: scenes.SCENES[name](w), steps=steps, tol=1e-5 if name == "joint_grid" else 0.0)
-    assert res["max_rel_err"] <= (1e-5 if name == "joint_grid" else 0.0)     # joint_grid: atan2f in the revolute spring/limit path
+    """BASELINE.json configs[0..3] at full size, every step compared, tolerance 0 (joint_grid uses plain revolutes: no Atan2)."""
+    res = parity.run_pair(lambda w: scenes.SCENES[name](w), steps=steps, tol=0.0)
+    assert res["max_rel_err"] == 0.0
     assert res["bodies"] >= 5000
 
 
-def test_batched_worlds_1024_bit_exact():
-    res = parity.run_pair(lambda w: scenes.batched_pyramids(w, n_worlds=1024), steps=6)
+def test_tumbler_full_size_200_steps_bit_exact():
+    """configs[2]: 20 000 mixed bodies in the rotating kinematic box until the pile churns (every manifold pair type, wide wall
+    queries, tree rebuilds, thousands of begin/end events): events and counters every step, bulk state every 20th."""
+    res = parity.run_pair(lambda w: scenes.tumbler(w), steps=200, tol=0.0, full_every=20)
     assert res["max_rel_err"] == 0.0
+    assert res["bodies"] >= 20000 and res["touching"] > 10000
+
+
+def test_joint_grid_full_size_60_steps_bit_exact():
+    """configs[3]: 100x100 revolute grid with contacts, once the sheet has dropped onto the ground."""
+    res = parity.run_pair(lambda w: scenes.joint_grid(w), steps=60, tol=0.0, full_every=10)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_batched_worlds_8192_bit_exact():
+    """configs[4] at full size: 8192 independent 10-row pyramids (450 560 bodies), 10 steps, bit-exact."""
+    res = parity.run_pair(lambda w: scenes.batched_pyramids(w, n_worlds=8192), steps=10, full_every=3)
+    assert res["max_rel_err"] == 0.0
+    assert res["bodies"] >= 8192 * 56
 
 
 def _kinetic_energy(bodies):
@@ -29,14 +46,14 @@ def _kinetic_energy(bodies):
 
 
 def test_resting_pyramid_600_steps_energy_and_configuration():
-    """600 steps of a 20-row pyramid on both backends: the CUDA state must stay the oracle's state (bit-exact), hence kinetic
-    energy and the resting configuration agree to far better than the 1 % the north star asks for."""
+    """configs[0]: 600 steps of the 100-row pyramid (5050 boxes) on both backends: the CUDA state must stay the oracle's state
+    (bit-exact), hence kinetic energy and the resting configuration agree to far better than the 1 % the north star asks for."""
     from oracle_backend import OracleBackend
     cuda = api.World(api.CudaBackend(), scenes.world_def())
     orc = api.World(OracleBackend(), scenes.world_def())
     try:
-        scenes.large_pyramid(cuda, 20)
-        scenes.large_pyramid(orc, 20)
+        scenes.large_pyramid(cuda, 100)
+        scenes.large_pyramid(orc, 100)
         for step in range(600):
             cuda.Step(1.0 / 60.0, 4)
             orc.Step(1.0 / 60.0, 4)

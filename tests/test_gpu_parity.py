@@ -32,7 +32,7 @@ def test_tumbler_small():
     assert res["max_rel_err"] == 0.0
 
 
-@pytest.mark.parametrize("name", ["pyramid10", "mixed_drop", "joint_grid8", "tumbler300", "joint_zoo_exact", "wheel_rig"])
+@pytest.mark.parametrize("name", ["pyramid10", "mixed_drop", "joint_grid8", "tumbler300", "joint_zoo_exact", "wheel_rig", "bounce_mix"])
 def test_cuda_matches_committed_golden(name):
     """The CUDA path against tests/golden/*.npz (bit-exact pair sets, ids, colors, feature ids, events, body states)."""
     from box2d_b200 import api
@@ -1036,3 +1036,49 @@ def test_joints_between_non_dynamic_bodies_are_parked_until_one_turns_dynamic():
             w.DestroyJoint(made[id(w)][1])                   # destroyed while parked
     res = parity.run_pair(build, steps=34, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
+
+
+def _bounce_mutate(w, step):
+    """Kicks some bouncers off the ground (their contacts stop touching: swap-remove in the colour arrays), destroys two bodies and
+    turns restitution on/off on live shapes, so the 8-lane restitution groups and the hit-event order keep changing."""
+    if step in (24, 40):
+        for b in range(3, 40, 5):
+            w.ApplyLinearImpulseToCenter(b, (0.3, 2.5 + 0.1 * (b % 3)))
+    elif step == 30:
+        w.DestroyBody(7)
+        w.DestroyBody(20)
+    elif step == 34:
+        for sid in range(2, 30, 3):
+            w.SetSurfaceMaterial(sid, 0.6, 0.4 if sid % 2 else 0.0)
+
+
+@pytest.mark.parametrize("mode", ["auto", "cta", "warp", "grid", "gridsync"])
+def test_restitution_mixed_groups_and_hit_events_bit_exact(mode, monkeypatch):
+    """ApplyRestitutionTask (src/ContactSolver.cs:913-989): the 8-lane groups are 8 consecutive entries of a colour's contactSims array
+    in the reference's own order (append / swap-remove), the AllZeroW skip and quirk Q1 are per group; hit events (src/Solver.cs:1151-1190)
+    come out in (colour, array position) order. Every solver variant must reproduce them bit for bit."""
+    if mode in ("cta", "warp"):
+        monkeypatch.setenv("B2CUDA_ISLAND_MODE", mode)
+    elif mode in ("grid", "gridsync"):
+        monkeypatch.setenv("B2CUDA_ISLAND_MAX_BODIES", "0")      # every island down the grid / cluster path
+        if mode == "gridsync":
+            monkeypatch.setenv("B2CUDA_CLUSTER", "0")
+    res = parity.run_pair(lambda w: scenes.bounce_mix(w), steps=70, mutate=_bounce_mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    assert res["hits"] > 20          # the scene does produce hit events, in the reference's order (compared every step by run_pair)
+
+
+def test_restitution_in_pyramids_and_overflow_bit_exact():
+    """Restitution on a few boxes of a pile that also owns overflow-colour contacts: the scalar overflow restitution (Q2, Q3) and the
+    SIMD-group restitution in one step."""
+    def build(w):
+        scenes.overflow_plank(w)
+        scenes.add_pyramid(w, 6, origin=(30.0, 0.0))
+
+    def mutate(w, step):
+        if step == 0:
+            for sid in range(1, 60, 4):
+                w.SetSurfaceMaterial(sid, 0.6, 0.5)
+    res = parity.run_pair(build, steps=40, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    assert res["max_overflow"] > 0
