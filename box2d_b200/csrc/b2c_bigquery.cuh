@@ -16,8 +16,8 @@ namespace b2c {
 
 // DFS (child1-first) rank of every leaf of the trees; t.leafIdx[rank] = leaf node. The static tree never changes after
 // the upload, so its ranks are computed once.
-__device__ void phase_leaf_ranks(cg::grid_group& grid, const WorldDev& d, bool needStatic) {
-  const int tid = gtid(), stride = gsize();
+template <class S> __device__ void phase_leaf_ranks(const S& grid, const WorldDev& d, bool needStatic) {
+  const int tid = grid.tid(), stride = grid.size();
   for (int tt = 0; tt < 3; tt++) {
     if (tt == kStaticBody && !needStatic) continue;
     const TreeDev& t = d.trees[tt];
@@ -93,8 +93,8 @@ __device__ __forceinline__ BigItem bigDecode(const WorldDev& d, int g0, int g1, 
 }
 
 // Runs between the count pass and the offsets scan. Uniform control flow: every thread of the grid calls it.
-__device__ void phase_big_queries(cg::grid_group& grid, const WorldDev& d) {
-  const int tid = gtid(), stride = gsize();
+template <class S> __device__ void phase_big_queries(const S& grid, const WorldDev& d) {
+  const int tid = grid.tid(), stride = grid.size();
   Scalars& s = *d.sc;
   const int nBig = s.bigQueryCount < kMaxBigQueries ? s.bigQueryCount : kMaxBigQueries;
   if (nBig == 0) return;

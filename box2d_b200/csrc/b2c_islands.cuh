@@ -37,11 +37,11 @@ __device__ __forceinline__ void ufUnion(int* parent, int a, int b) {
 __device__ __forceinline__ bool simIsDynamic(const WorldDev& d, int sim) { return sim >= 0 && (fbits(d.st0[sim].w) & kDynamicFlag) != 0; }
 
 // grid-wide exclusive scan of int4 rows inside a cooperative kernel (chunk = blockDim.x); consumers add sums[i / blockDim.x]
-__device__ void gridScan4(cg::grid_group& grid, int4* data, int4* sums, int n, int4* totalOut) {
+template <class S> __device__ void gridScan4(const S& grid, int4* data, int4* sums, int n, int4* totalOut) {
   __shared__ int4 warpSums[32];
   const int chunk = blockDim.x;
   int chunks = (n + chunk - 1) / chunk;
-  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+  for (int c = grid.block(); c < chunks; c += grid.blocks()) {
     int i = c * chunk + threadIdx.x;
     int4 v = i < n ? data[i] : make_int4(0, 0, 0, 0);
     int4 total;
@@ -50,7 +50,7 @@ __device__ void gridScan4(cg::grid_group& grid, int4* data, int4* sums, int n, i
     if (threadIdx.x == 0) sums[c] = total;
   }
   grid.sync();
-  if (blockIdx.x == 0) {
+  if (grid.block() == 0) {
     int4 carry = make_int4(0, 0, 0, 0);
     for (int base = 0; base < chunks; base += chunk) {
       int i = base + threadIdx.x;
@@ -68,10 +68,10 @@ __device__ void gridScan4(cg::grid_group& grid, int4* data, int4* sums, int n, i
 // Rebuilds the island partition and the constraint order [grid-path colors | island 0 | island 1 | ...] when the graph
 // changed this step; a no-op (one uniform branch) otherwise. Order inside one (group, color) bucket is arbitrary:
 // constraints of one color never share a writable body, so it does not influence any result.
-__device__ void phase_islands(cg::grid_group& grid, const WorldDev& d) {
+template <class S> __device__ void phase_islands(const S& grid, const WorldDev& d) {
   Scalars& s = *d.sc;
   if (!s.graphDirty) return;
-  const int tid = gtid(), stride = gsize();
+  const int tid = grid.tid(), stride = grid.size();
   const int awake = d.awakeCount, nContacts = s.contactNext, nJoints = d.jointColorStart[kGraphColorCount];
   __shared__ int hist[kGraphColorCount];
   // P0 init

@@ -147,9 +147,9 @@ __device__ __forceinline__ int rbClassify(const TreeDev& t, int n) {     // 0 = 
 
 
 // All threads of the cooperative grid call this; every branch around a grid.sync() is uniform.
-__device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeType) {
+template <class S> __device__ void phase_rebuild(const S& grid, const WorldDev& d, int treeType) {
   const TreeDev& t = d.trees[treeType];
-  const int tid = gtid(), stride = gsize();
+  const int tid = grid.tid(), stride = grid.size();
   const int root = t.meta[0];
   if (t.meta[3] == 0 || root == -1) return;
   { uint32_t hf = t.hf[root]; if (!((hf >> 16) & NODE_ENLARGED) || (hf & 0xffffu) == 0) { if (tid == 0) d.sc->rebuildLeafCount[treeType] = 0; return; } }
@@ -218,7 +218,7 @@ __device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeT
     // P1: "< pivot" flag of every element (:810-845), fused into the first pass of the prefix sum
     {
       const int chunk = blockDim.x, chunks = (L + chunk - 1) / chunk;
-      for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+      for (int c = grid.block(); c < chunks; c += grid.blocks()) {
         int i = c * chunk + threadIdx.x, f = 0;
         if (i < L) {
           int sg = t.segStart[i];
@@ -235,7 +235,7 @@ __device__ void phase_rebuild(cg::grid_group& grid, const WorldDev& d, int treeT
       }
       if (tid == 0) t.rb[nextSlot] = 0;
       grid.sync();
-      if (blockIdx.x == 0) {
+      if (grid.block() == 0) {
         int carry = 0;
         for (int base = 0; base < chunks; base += chunk) {
           int i = base + threadIdx.x, v = i < chunks ? d.scanBlockSums[i] : 0;

@@ -33,6 +33,32 @@ __device__ __forceinline__ unsigned hashKey(unsigned long long k) {
 }
 constexpr unsigned long long kEmptyKey = ~0ull;
 
+// Barrier scopes. The phases below are written once and run at three scales: the whole cooperative grid (one big world: grid.sync),
+// one thread-block cluster (the grid-path solver: barrier.cluster) and ONE CTA (a small world of a batch: __syncthreads, see k_batch_step).
+// tid()/size() enumerate the threads of the scope, block()/blocks() its CTAs (prefix-sum chunks are handed out per CTA).
+struct GridScope {
+  cg::grid_group& g;
+  __device__ __forceinline__ void sync() const { g.sync(); }
+  __device__ __forceinline__ int tid() const { return blockIdx.x * blockDim.x + threadIdx.x; }
+  __device__ __forceinline__ int size() const { return gridDim.x * blockDim.x; }
+  __device__ __forceinline__ int block() const { return blockIdx.x; }
+  __device__ __forceinline__ int blocks() const { return gridDim.x; }
+};
+struct ClusterScope {       // launched as a one-cluster grid: grid ranks are cluster ranks
+  __device__ __forceinline__ void sync() const { cg::this_cluster().sync(); }
+  __device__ __forceinline__ int tid() const { return blockIdx.x * blockDim.x + threadIdx.x; }
+  __device__ __forceinline__ int size() const { return gridDim.x * blockDim.x; }
+  __device__ __forceinline__ int block() const { return blockIdx.x; }
+  __device__ __forceinline__ int blocks() const { return gridDim.x; }
+};
+struct CtaScope {
+  __device__ __forceinline__ void sync() const { __syncthreads(); }
+  __device__ __forceinline__ int tid() const { return threadIdx.x; }
+  __device__ __forceinline__ int size() const { return blockDim.x; }
+  __device__ __forceinline__ int block() const { return 0; }
+  __device__ __forceinline__ int blocks() const { return 1; }
+};
+
 // ------------------------------------------------------------------------------------------------------------
 // block / grid exclusive scans used by the ordered compactions
 // ------------------------------------------------------------------------------------------------------------
@@ -65,11 +91,11 @@ template <class T> __device__ __forceinline__ T blockInclusive(T v, T* warpSums,
   return v;
 }
 // grid-wide exclusive scan inside a cooperative kernel (chunk = blockDim.x); consumers read data[i] + sums[i / blockDim.x]
-template <class T> __device__ void gridScan(cg::grid_group& grid, T* data, T* sums, int n, T* totalOut) {
+template <class T, class S> __device__ void gridScan(const S& grid, T* data, T* sums, int n, T* totalOut) {
   __shared__ T warpSums[32];
   const int chunk = blockDim.x;
   int chunks = (n + chunk - 1) / chunk;
-  for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+  for (int c = grid.block(); c < chunks; c += grid.blocks()) {
     int i = c * chunk + threadIdx.x;
     T v = i < n ? data[i] : zeroOf<T>();
     T total;
@@ -78,7 +104,7 @@ template <class T> __device__ void gridScan(cg::grid_group& grid, T* data, T* su
     if (threadIdx.x == 0) sums[c] = total;
   }
   grid.sync();
-  if (blockIdx.x == 0) {
+  if (grid.block() == 0) {
     T carry = zeroOf<T>();
     for (int base = 0; base < chunks; base += chunk) {
       int i = base + threadIdx.x;
@@ -276,7 +302,6 @@ __device__ void p_create_contacts(const WorldDev& d, int tid, int stride) {
     const ShapeDev& sa = d.shapes[a]; const ShapeDev& sb = d.shapes[b];
     uint32_t flags = CF_ALIVE;
     if ((sa.flags | sb.flags) & SF_CONTACT_EVENTS) flags |= CF_ENABLE_CONTACT_EVENTS;
-    if ((sa.flags | sb.flags) & SF_HIT_EVENTS) { flags |= CF_SHAPE_HIT; d.sc->anyHitShapes = 1; }
     d.cShape[id] = make_int2(a, b);
     d.cBody[id] = make_int2(sa.bodyId, sb.bodyId);
     d.cFlags[id] = flags;
@@ -308,7 +333,7 @@ __device__ void p_pairs_finish(const WorldDev& d) {
   if (s.contactNext > d.contactCapacity) { s.contactNext = d.contactCapacity; s.errorFlags |= (int)ERR_CONTACT_CAPACITY; }
   s.liveContactCount += n; s.contactStamp += (unsigned)n;
   s.moveCount = 0; s.bigQueryCount = 0;
-  s.beginCount = 0; s.hitCount = 0; s.jointEventCount = 0; s.anyRestitution = 0;
+  s.beginCount = 0; s.hitCount = 0; s.jointEventCount = 0; s.anyRestitution = 0; s.anyHitShapes = 0;
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -426,7 +451,8 @@ __device__ void p_collide(const WorldDev& d, const StepParams& sp, int tid, int 
           if (m.p0.separation > 1.5f * kLinearSlop) { m.p0 = m.p1; m.pointCount = 1; }
           pointCount = m.pointCount;
         }
-        if (touching && (flags & CF_SHAPE_HIT)) flags |= CF_ENABLE_HIT; else flags &= ~CF_ENABLE_HIT;
+        // sampled by every UpdateContact (src/Contact.cs:375-377), not when the contact is created
+        if (touching && ((sa.flags | sb.flags) & SF_HIT_EVENTS)) { flags |= CF_ENABLE_HIT; d.sc->anyHitShapes = 1; } else flags &= ~CF_ENABLE_HIT;
         if (pointCount > 0) m.rollingImpulse = old.rollingImpulse;
         for (int k = 0; k < pointCount; k++) {
           MPoint& mp2 = k == 1 ? m.p1 : m.p0;
@@ -1059,14 +1085,14 @@ __device__ __forceinline__ void integratePosition(const WorldDev& d, const StepP
   d.st1[i] = p;
 }
 
-__device__ void phase_prepare(const WorldDev& d, const StepParams& sp, bool contactLanes) {
+template <class S> __device__ void phase_prepare(const S& grid, const WorldDev& d, const StepParams& sp, bool contactLanes) {
   const Scalars& s = *d.sc;
   int total = contactLanes ? s.smallConStart : 0; // grid-path constraints only (and only when they do not fit one per thread): small islands prepare their own lanes in registers
-  for (int t = gtid(); t < total; t += gsize()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
+  for (int t = grid.tid(); t < total; t += grid.size()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
   int nj = d.jointColorStart[kGraphColorCount];
-  for (int k = gtid(); k < nj; k += gsize()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
+  for (int k = grid.tid(); k < nj; k += grid.size()) { int id = d.jointSorted[k]; d.jointEventFlag[id] = 0; prepareJoint(d, sp, d.joints[id]); }
   int nov = s.colLen[kOverflowIndex];
-  for (int k = gtid(); k < nov; k += gsize()) ovPrepare(d, sp, k);
+  for (int k = grid.tid(); k < nov; k += grid.size()) ovPrepare(d, sp, k);
 }
 
 // SolverTask substep loop (src/Solver.cs:599-727) as one persistent cooperative kernel: a grid-wide barrier replaces the
@@ -1075,8 +1101,6 @@ __device__ void phase_prepare(const WorldDev& d, const StepParams& sp, bool cont
 // as in the island kernel) and keeps it there for the whole step: a stage then loads only the two body rows after the barrier.
 // The stage barrier: the whole cooperative grid (cg grid.sync, ~1.2 us over 148 CTAs) or one thread-block cluster (barrier.cluster,
 // ~0.2 us over <= 16 CTAs of one GPC). With a one-cluster grid gtid()/gsize() are the cluster's thread rank and size.
-struct GridScope { cg::grid_group& g; __device__ __forceinline__ void sync() const { g.sync(); } };
-struct ClusterScope { __device__ __forceinline__ void sync() const { cg::this_cluster().sync(); } };
 
 template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scope& grid, const WorldDev& d, const StepParams& sp) {
   const Scalars& s = *d.sc;
@@ -1091,7 +1115,7 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   }
   __syncthreads();
   const int activeCount = sActiveCount;
-  const int tid = gtid(), stride = gsize();
+  const int tid = grid.tid(), stride = grid.size();
   const int awake = s.bigBodyCount;               // bodies of grid-path islands (+ kinematic bodies some constraint reads)
   if (awake == 0 && activeCount == 0) return;     // everything lives in small islands / free bodies: no grid barrier at all
   const int nov = s.colLen[kOverflowIndex];                      // overflow colour: one thread, array order, before the colours of each stage (:633-670)
@@ -1344,8 +1368,8 @@ namespace b2c {
 // uniform early-out when the phase has nothing to do (no moved proxies / no contact state change / no enlarged proxy).
 // ------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned long long globalTimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-__device__ void phase_broadphase(cg::grid_group& grid, const WorldDev& d) {      // UpdateBroadPhasePairs + RebuildTrees
-  const int tid = gtid(), stride = gsize();
+template <class S> __device__ void phase_broadphase(const S& grid, const WorldDev& d) {      // UpdateBroadPhasePairs + RebuildTrees
+  const int tid = grid.tid(), stride = grid.size();
   Scalars& s = *d.sc;
   if (s.moveCount > 0) {
     if (d.debugChecksums == 2 && tid == 0) d.sc->dbg[6] = globalTimer();
@@ -1371,8 +1395,8 @@ __device__ void phase_broadphase(cg::grid_group& grid, const WorldDev& d) {     
   if (tid == 0) p_pairs_finish(d);
 }
 
-__device__ void phase_collide(cg::grid_group& grid, const WorldDev& d, const StepParams& sp) {   // World.Collide
-  const int tid = gtid(), stride = gsize();
+template <class S> __device__ void phase_collide(const S& grid, const WorldDev& d, const StepParams& sp) {   // World.Collide
+  const int tid = grid.tid(), stride = grid.size();
   Scalars& s = *d.sc;
   p_collide(d, sp, tid, stride);
   grid.sync();
@@ -1385,7 +1409,7 @@ __device__ void phase_collide(cg::grid_group& grid, const WorldDev& d, const Ste
   grid.sync();
   if (tid == 0) { p_events_finish(d, sp, d.flagScan + d.contactCapacity); s.anyContactFlag = 0; }
   grid.sync();
-  if (blockIdx.x == 0) p_color_ops(d);
+  if (grid.block() == 0) p_color_ops(d);
 }
 
 
@@ -1442,14 +1466,14 @@ __device__ void dbgLanes(const WorldDev& d, int slot, bool all) {
 
 // debug: number of (color, dynamic body) pairs claimed by more than one touching constraint (must be 0), and the same
 // test on the solver's own arrangement (slot -> contact -> bodies)
-__device__ void dbgColorConflicts(cg::grid_group& grid, const WorldDev& d, int slot) {
+template <class S> __device__ void dbgColorConflicts(const S& grid, const WorldDev& d, int slot) {
   if (d.debugChecksums != 1) return;
   const int awake = d.awakeCount, n = d.sc->contactNext;
   grid.sync();
-  for (int i = gtid(); i < awake * kGraphColorCount; i += gsize()) d.rootColorCount[i] = 0;
+  for (int i = grid.tid(); i < awake * kGraphColorCount; i += grid.size()) d.rootColorCount[i] = 0;
   grid.sync();
   unsigned long long bad = 0;
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = grid.tid(); i < n; i += grid.size()) {
     if (!(d.cFlags[i] & CF_TOUCHING)) continue;
     int c = d.cColor[i];
     if (c == kOverflowIndex) continue;             // solved serially, shares bodies by design
@@ -1463,8 +1487,8 @@ __device__ void dbgColorConflicts(cg::grid_group& grid, const WorldDev& d, int s
   // partition: both dynamic bodies of a touching contact share a root; roots are fixed points; a small island's constraint
   // indexes its own bodies; a body with a constraint is never on the free list
   unsigned long long bad2 = 0;
-  for (int i = gtid(); i < awake; i += gsize()) { int r = d.ufParent[i]; if (r < 0 || r >= awake || d.ufParent[r] != r) bad2 += 1; }
-  for (int i = gtid(); i < n; i += gsize()) {
+  for (int i = grid.tid(); i < awake; i += grid.size()) { int r = d.ufParent[i]; if (r < 0 || r >= awake || d.ufParent[r] != r) bad2 += 1; }
+  for (int i = grid.tid(); i < n; i += grid.size()) {
     if (!(d.cFlags[i] & CF_TOUCHING)) continue;
     int2 sim = d.cSim[i];
     bool dynA = sim.x >= 0 && (fbits(d.st0[sim.x].w) & kDynamicFlag), dynB = sim.y >= 0 && (fbits(d.st0[sim.y].w) & kDynamicFlag);
@@ -1524,7 +1548,7 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   const bool clusterPath = gridWork && sp.clusterThreads > 0 && clusterFits && clusterWins;
   if (gtid() == 0) s.clusterSolve = clusterPath ? 1 : 0;
   const bool cachedLanes = s.smallConStart <= (clusterPath ? sp.clusterThreads : gsize());   // one grid-path constraint per thread: lanes stay in registers
-  if (gridWork) { phase_prepare(d, sp, !cachedLanes); if (!cachedLanes) grid.sync(); }
+  if (gridWork) { phase_prepare(grid, d, sp, !cachedLanes); if (!cachedLanes) grid.sync(); }
   stamp(d, 3);
   dbgLanes(d, 3, true); dbgBodies(d, 4); dbgColorConflicts(grid, d, 10);
   if (d.debugChecksums == 1) grid.sync();

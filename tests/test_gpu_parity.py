@@ -1044,10 +1044,10 @@ def _bounce_mutate(w, step):
     if step in (24, 40):
         for b in range(3, 40, 5):
             w.ApplyLinearImpulseToCenter(b, (0.3, 2.5 + 0.1 * (b % 3)))
-    elif step == 30:
+    elif step == 34:
         w.DestroyBody(7)
         w.DestroyBody(20)
-    elif step == 34:
+    elif step == 29:
         for sid in range(2, 30, 3):
             w.SetSurfaceMaterial(sid, 0.6, 0.4 if sid % 2 else 0.0)
 
