@@ -123,7 +123,7 @@ template <class S> __device__ void phase_big_queries(const S& grid, const WorldD
     gridScan<int>(grid, d.bigScan, d.scanBlockSums, len, &s.bigGroupTotal);
     for (int e = tid; e < len; e += stride) {
       if (!d.bigFlag[e]) continue;
-      int pos = hitBase + d.bigScan[e] + d.scanBlockSums[e / kCoopThreads];
+      int pos = hitBase + d.bigScan[e] + d.scanBlockSums[e / (int)blockDim.x];
       if (pos >= d.pairCapacity) { atomicOr(&s.errorFlags, (int)ERR_PAIR_CAPACITY); continue; }
       BigItem it = bigDecode(d, g0, g1, base + e);
       int hitShape = d.trees[it.treeType].user[it.leaf];
@@ -132,8 +132,8 @@ template <class S> __device__ void phase_big_queries(const S& grid, const WorldD
     }
     for (int b = g0 + tid; b < g1; b += stride) {
       int e0 = d.bigSegStart[b] - base, e1 = d.bigSegStart[b + 1] - base;
-      int p0 = d.bigScan[e0] + d.scanBlockSums[e0 / kCoopThreads];
-      int p1 = e1 < len ? d.bigScan[e1] + d.scanBlockSums[e1 / kCoopThreads] : s.bigGroupTotal;
+      int p0 = d.bigScan[e0] + d.scanBlockSums[e0 / (int)blockDim.x];
+      int p1 = e1 < len ? d.bigScan[e1] + d.scanBlockSums[e1 / (int)blockDim.x] : s.bigGroupTotal;
       d.bigOff[b] = hitBase + p0;
       d.moveHitCount[d.bigList[b]] = p1 - p0;
     }
@@ -153,7 +153,7 @@ __device__ void p_big_fill(const WorldDev& d, int tid, int stride) {
   for (int e = tid; e < total; e += stride) {
     int b = lastNotAbove(d.bigOff, 0, nBig, e);
     int i = d.bigList[b], h = e - d.bigOff[b];
-    int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) / kCoopThreads] : s.newPairCount;
+    int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) / (int)blockDim.x] : s.newPairCount;
     if (end > d.pairCapacity) { atomicOr(&s.errorFlags, (int)ERR_PAIR_CAPACITY); continue; }
     d.movePairs[end - 1 - h] = d.bigHits[e];
   }

@@ -254,9 +254,9 @@ template <class S> __device__ void phase_rebuild(const S& grid, const WorldDev& 
       const int sg = t.segStart[p];
       if (sg < 0) continue;
       const int e = recEnd[sg], node = recNode[sg];
-      const int Fs = t.flagScan[sg] + d.scanBlockSums[sg / kCoopThreads];
-      const int Fe = e < L ? t.flagScan[e] + d.scanBlockSums[e / kCoopThreads] : total;
-      const int Fp = t.flagScan[p] + d.scanBlockSums[p / kCoopThreads];
+      const int Fs = t.flagScan[sg] + d.scanBlockSums[sg / (int)blockDim.x];
+      const int Fe = e < L ? t.flagScan[e] + d.scanBlockSums[e / (int)blockDim.x] : total;
+      const int Fp = t.flagScan[p] + d.scanBlockSums[p / (int)blockDim.x];
       const int m = Fe - Fs, left = Fp - Fs;
       if (p >= sg + m && t.flagArr[p]) t.pairR[sg + (m - left - 1)] = p;
       if (p != sg) continue;
@@ -279,7 +279,7 @@ template <class S> __device__ void phase_rebuild(const S& grid, const WorldDev& 
       const int sg = t.segStart[p];
       if (sg < 0) continue;
       const int e = recEnd[sg], node = recNode[sg], split = t.recSplit[sg], m = t.recM[sg];
-      const int left = (t.flagScan[p] + d.scanBlockSums[p / kCoopThreads]) - (t.flagScan[sg] + d.scanBlockSums[sg / kCoopThreads]);
+      const int left = (t.flagScan[p] + d.scanBlockSums[p / (int)blockDim.x]) - (t.flagScan[sg] + d.scanBlockSums[sg / (int)blockDim.x]);
       const bool f = t.flagArr[p] != 0;
       if (p >= sg + m && f) continue;               // misplaced on the right: its partner on the left handles both positions
       int pos[2] = {p, -1}; int idx[2] = {t.leafIdx[p], -1}; float2 ctr[2] = {t.leafCtr[p], make_float2(0.0f, 0.0f)};

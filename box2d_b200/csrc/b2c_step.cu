@@ -253,8 +253,8 @@ template <bool FILL> __device__ void p_find_pairs(const WorldDev& d, int tid, in
       int type = queryKey & 3, id = queryKey >> 2;
       HitSink sink; sink.out = d.movePairs; sink.outLast = 0; sink.buf = d.moveHitBuf + (size_t)i * kHitBuf;
       if (FILL) {
-        int begin = d.moveHitCount[i] + d.scanBlockSums[i / kCoopThreads];
-        int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) / kCoopThreads] : d.sc->newPairCount;
+        int begin = d.moveHitCount[i] + d.scanBlockSums[i / (int)blockDim.x];
+        int end = (i + 1 < n) ? d.moveHitCount[i + 1] + d.scanBlockSums[(i + 1) / (int)blockDim.x] : d.sc->newPairCount;
         if (end == begin) continue;
         if (end > d.pairCapacity) { atomicOr(&d.sc->errorFlags, (int)ERR_PAIR_CAPACITY); continue; }
         sink.outLast = end - 1;
@@ -488,7 +488,7 @@ __device__ void p_contact_events(const WorldDev& d, const StepParams& sp, int ti
   for (int i = tid; i < n; i += stride) {
     uint32_t flags = d.cFlags[i];
     if (!(flags & CF_STATE_MASK)) continue;
-    int4 rank = addT(d.flagScan[i], d.scanBlockSums4[i / kCoopThreads]);
+    int4 rank = addT(d.flagScan[i], d.scanBlockSums4[i / (int)blockDim.x]);
     int2 sh = d.cShape[i];
     B2CContactTouchEvent ev = {sh.x, sh.y, i, d.cGen[i]};
     if (flags & CF_DISJOINT) {
@@ -1288,8 +1288,8 @@ __device__ __forceinline__ void atomicMaxF(float* addr, float v) {
 __device__ void p_refit(const WorldDev& d, int tid, int stride) {
   int n = d.awakeCount;
   for (int i = tid; i < n; i += stride) {
-    int offset = d.bodyEnlargedCount[i] + d.scanBlockSums[i / kCoopThreads];
-    int next = (i + 1 < n) ? d.bodyEnlargedCount[i + 1] + d.scanBlockSums[(i + 1) / kCoopThreads] : d.sc->moveCount;
+    int offset = d.bodyEnlargedCount[i] + d.scanBlockSums[i / (int)blockDim.x];
+    int next = (i + 1 < n) ? d.bodyEnlargedCount[i + 1] + d.scanBlockSums[(i + 1) / (int)blockDim.x] : d.sc->moveCount;
     if (next == offset) continue;
     int bodyId = d.simBodyId[i];
     for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
@@ -1342,8 +1342,8 @@ template <bool FILL> __device__ void p_hit_events(const WorldDev& d, const StepP
     while (p >= sStart[c + 1]) c++;
     const int i = d.colList[(size_t)c * d.contactCapacity + (p - sStart[c])];
     if (!FILL) { flags[p] = hitEventOf(d, sp, i, nullptr) ? 1 : 0; continue; }
-    const int rank = flags[p] + sums[p / kCoopThreads];
-    const int next = (p + 1 < total) ? flags[p + 1] + sums[(p + 1) / kCoopThreads] : d.sc->hitCount;
+    const int rank = flags[p] + sums[p / (int)blockDim.x];
+    const int next = (p + 1 < total) ? flags[p + 1] + sums[(p + 1) / (int)blockDim.x] : d.sc->hitCount;
     if (next == rank || rank >= d.eventCapacity) continue;
     B2CContactHitEvent ev;
     if (hitEventOf(d, sp, i, &ev)) d.hitEvents[rank] = ev;
@@ -1510,29 +1510,29 @@ template <class S> __device__ void dbgColorConflicts(const S& grid, const WorldD
 
 __device__ __forceinline__ void stamp(const WorldDev& d, int k) { if (gtid() == 0) d.sc->phaseStamp[k] = globalTimer(); }
 
-// One launch for UpdateBroadPhasePairs -> Collide -> (islands) -> PrepareContacts -> grid-path solver. Phases that have
-// nothing to do leave through a uniform branch; barriers after phases that wrote nothing are skipped.
-__global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepParams sp) {
-  cg::grid_group grid = cg::this_grid();
+// UpdateBroadPhasePairs -> Collide -> (islands) -> PrepareContacts -> grid-path solver. Phases that have nothing to do leave through a
+// uniform branch; barriers after phases that wrote nothing are skipped. One launch at grid scope (k_step_front), or the first part of a
+// batch world's step at CTA scope (k_batch_step).
+template <class S> __device__ void stepFront(const S& grid, const WorldDev& d, const StepParams& sp) {
   Scalars& s = *d.sc;
-  stamp(d, 0);
-  if (gtid() < 16) s.dbg[gtid()] = 0;
+  if (grid.tid() == 0) s.phaseStamp[0] = globalTimer();
+  if (grid.tid() < 16) s.dbg[grid.tid()] = 0;
   phase_broadphase(grid, d);
   grid.sync();
-  stamp(d, 1);
+  if (grid.tid() == 0) s.phaseStamp[1] = globalTimer();
   dbgContacts(d, 0); dbgBodies(d, 1);
   phase_rebuild(grid, d, kDynamicBody);           // BroadPhase.RebuildTrees (src/BroadPhase.cs:112-116), part of Collide in the reference
   phase_rebuild(grid, d, kKinematicBody);
-  stamp(d, 5);
+  if (grid.tid() == 0) s.phaseStamp[5] = globalTimer();
   phase_collide(grid, d, sp);
   grid.sync();
   if (s.anyRestitution) {                         // rare: which 8-lane groups of the colour arrays ApplyRestitution will not skip
-    for (int i = gtid(); i < s.contactNext; i += gsize()) d.cRestGroup[i] = 0;
+    for (int i = grid.tid(); i < s.contactNext; i += grid.size()) d.cRestGroup[i] = 0;
     grid.sync();
-    p_rest_groups(d, gtid(), gsize());
+    p_rest_groups(d, grid.tid(), grid.size());
     grid.sync();
   }
-  stamp(d, 2);
+  if (grid.tid() == 0) s.phaseStamp[2] = globalTimer();
   dbgContacts(d, 2);
   const bool dirty = s.graphDirty != 0;
   phase_islands(grid, d);
@@ -1544,31 +1544,35 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepPar
   // Measured (B200): the cluster wins where stages are many and thin (joints, an active overflow colour) or the lanes fit its registers;
   // a contact-only scene between 8 192 and 75 776 constraints keeps its lanes in the grid's registers, which beats the cheaper barrier.
   const bool clusterFits = s.smallConStart + gridJoints <= 12 * sp.clusterThreads && s.bigBodyCount <= 8 * sp.clusterThreads;
-  const bool clusterWins = gridJoints > 0 || s.colLen[kOverflowIndex] > 0 || s.smallConStart <= sp.clusterThreads || s.smallConStart > gsize();
+  const bool clusterWins = gridJoints > 0 || s.colLen[kOverflowIndex] > 0 || s.smallConStart <= sp.clusterThreads || s.smallConStart > grid.size();
   const bool clusterPath = gridWork && sp.clusterThreads > 0 && clusterFits && clusterWins;
-  if (gtid() == 0) s.clusterSolve = clusterPath ? 1 : 0;
-  const bool cachedLanes = s.smallConStart <= (clusterPath ? sp.clusterThreads : gsize());   // one grid-path constraint per thread: lanes stay in registers
+  if (grid.tid() == 0) s.clusterSolve = clusterPath ? 1 : 0;
+  const bool cachedLanes = s.smallConStart <= (clusterPath ? sp.clusterThreads : grid.size());   // one grid-path constraint per thread: lanes stay in registers
   if (gridWork) { phase_prepare(grid, d, sp, !cachedLanes); if (!cachedLanes) grid.sync(); }
-  stamp(d, 3);
+  if (grid.tid() == 0) s.phaseStamp[3] = globalTimer();
   dbgLanes(d, 3, true); dbgBodies(d, 4); dbgColorConflicts(grid, d, 10);
   if (d.debugChecksums == 1) grid.sync();
-  if (gridWork && !clusterPath) { GridScope gs{grid}; if (cachedLanes) phase_solver_grid<true>(gs, d, sp); else phase_solver_grid<false>(gs, d, sp); }
-  stamp(d, 4);
+  if (gridWork && !clusterPath) { if (cachedLanes) phase_solver_grid<true>(grid, d, sp); else phase_solver_grid<false>(grid, d, sp); }
+  if (grid.tid() == 0) s.phaseStamp[4] = globalTimer();
   if (d.debugChecksums == 1) { grid.sync(); dbgBodies(d, 5); dbgLanes(d, 6, false); dbgContacts(d, 7); }
-  if (gtid() == 0) { for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k]; s.phaseAcc[4] += s.phaseStamp[5] - s.phaseStamp[1]; }
+  if (grid.tid() == 0) { for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k]; s.phaseAcc[4] += s.phaseStamp[5] - s.phaseStamp[1]; }
+}
+__global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepParams sp) {
+  cg::grid_group g = cg::this_grid();
+  GridScope grid{g};
+  stepFront(grid, d, sp);
 }
 
-// The grid-path solver on one thread-block cluster (see clusterPath in k_step_front). All CTAs of the cluster take the same path.
+// The grid-path solver on one thread-block cluster (see clusterPath in stepFront). All CTAs of the cluster take the same path.
 __global__ void __launch_bounds__(kCoopThreads) k_solver_cluster(WorldDev d, StepParams sp) {
   const Scalars& s = *d.sc;
   if (!s.clusterSolve) return;
   ClusterScope cs;
-  if (s.smallConStart <= gsize()) phase_solver_grid<true>(cs, d, sp); else phase_solver_grid<false>(cs, d, sp);
+  if (s.smallConStart <= cs.size()) phase_solver_grid<true>(cs, d, sp); else phase_solver_grid<false>(cs, d, sp);
 }
 
-__global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, StepParams sp, int newEndIndex) {   // FinalizeBodies + refit
-  cg::grid_group grid = cg::this_grid();
-  const int tid = gtid(), stride = gsize();
+template <class S> __device__ void finalizePhase(const S& grid, const WorldDev& d, const StepParams& sp, int newEndIndex) {   // FinalizeBodies + refit
+  const int tid = grid.tid(), stride = grid.size();
   Scalars& s = *d.sc;
   if (d.debugChecksums == 1) { dbgBodies(d, 8); dbgContacts(d, 9); grid.sync(); }
   p_finalize(d, sp, tid, stride);
@@ -1587,6 +1591,43 @@ __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, Ste
     grid.sync();
   } else if (tid == 0) s.moveCount = 0;
   if (tid == 0) { s.enlargedShapeCount = 0; p_step_finish(d, newEndIndex); }
+}
+__global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, StepParams sp, int newEndIndex) {
+  cg::grid_group g = cg::this_grid();
+  GridScope grid{g};
+  finalizePhase(grid, d, sp, newEndIndex);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Batches of independent worlds (api/World.cs:9-10 "Each world is completely independent and may be simulated in parallel"):
+// ONE CTA steps ONE world end to end — the same phases as above at CTA scope (every barrier is a __syncthreads(), no grid-wide
+// synchronisation anywhere), then its islands with the CTA island solver, then FinalizeBodies/refit. World index = blockIdx.x; each
+// world has its own arrays, id pools, trees and colour graph, so world k of a batch is bit-identical to the same world stepped alone.
+// ------------------------------------------------------------------------------------------------------------
+constexpr int kBatchThreads = 256;
+__global__ void __launch_bounds__(kBatchThreads, 2) k_batch_step(const WorldDev* __restrict__ worlds, StepParams sp, int newEndIndex) {
+  __shared__ __align__(16) unsigned char sdRaw[sizeof(WorldDev)];
+  __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
+  __shared__ int colorOff[kGraphColorCount + 1 + 2 * kGraphColorCount];
+  {
+    const int* src = reinterpret_cast<const int*>(worlds + blockIdx.x);
+    int* dst = reinterpret_cast<int*>(sdRaw);
+    for (int i = threadIdx.x; i < (int)(sizeof(WorldDev) / sizeof(int)); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const WorldDev& d = *reinterpret_cast<const WorldDev*>(sdRaw);
+  CtaScope cta;
+  stepFront(cta, d, sp);                          // sp.clusterThreads == 0: large / jointed islands are solved here, at CTA scope
+  __syncthreads();
+  const int n = d.sc->islandCount;
+  for (int g = 0; g < n; g++) {
+    int K = d.islandColorOff[g * (kGraphColorCount + 1) + kGraphColorCount];
+    if (K <= (int)blockDim.x) runIsland<true>(d, sp, g, s0, s1, colorOff);
+    else runIsland<false>(d, sp, g, s0, s1, colorOff);
+  }
+  freeBodies(d, sp, threadIdx.x, blockDim.x);
+  __syncthreads();
+  finalizePhase(cta, d, sp, newEndIndex);
 }
 
 // bodyMoveEvents equivalent: one packed record per body id (src/Solver.cs:432-438)
