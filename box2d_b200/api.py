@@ -454,6 +454,14 @@ class World:
         arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value * C.sizeof(capi.BodyMoveEvent),)).view(np.dtype(capi.BodyMoveEvent))
         return arr.copy() if copy else arr
 
+    def CopyBodyMoveEventsNoAlloc(self, out):
+        """b2cuda_world_copy_body_move_events_noalloc: the move events into the caller's array `out` (numpy, dtype BodyMoveEvent) through
+        the library's fixed device scratch, with no allocation anywhere in the library. Returns the number of records written."""
+        n = C.c_int32()
+        rc = self.fns["world_copy_body_move_events_noalloc"](self.handle, out.ctypes.data_as(C.POINTER(capi.BodyMoveEvent)), len(out), C.byref(n))
+        self._check(rc)
+        return n.value
+
     def ReadBodies(self):
         return self._read("world_read_bodies", BodyRead, self.GetCounters().bodyCount + 16)
 

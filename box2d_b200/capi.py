@@ -216,7 +216,9 @@ PRODUCT_ONLY = {
     "world_timer_start": ([_W], C.c_int32),
     "world_timer_stop": ([_W, C.POINTER(C.c_float)], C.c_int32),
     "world_debug_checksums": ([_W, C.POINTER(C.c_uint64)], C.c_int32),
+    "world_copy_body_move_events_noalloc": ([_W, C.POINTER(BodyMoveEvent), C.c_int32, C.POINTER(C.c_int32)], C.c_int32),
 }
+NOALLOC_MAX_MOVE_EVENTS = 65536     # B2C_NOALLOC_MAX_MOVE_EVENTS
 
 
 def bind(lib, prefix):

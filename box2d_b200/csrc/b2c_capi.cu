@@ -7,6 +7,7 @@ using namespace b2c;
 
 struct B2CWorld { World* w; };
 static thread_local std::string g_lastError;
+void b2cSetLastError(const std::string& msg) { g_lastError = msg; }   // for entry points that live in other files (b2c_noalloc.cu)
 static int done(B2CWorld* h, int rc) { if (rc != B2C_OK && h && h->w) g_lastError = h->w->error; return rc; }
 #define CHECK_HANDLE(h) do { if (!(h) || !(h)->w) { g_lastError = "null world handle"; return B2C_E_INVALID; } } while (0)
 

@@ -113,6 +113,10 @@ class World {
   int getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B2CContactTouchEvent** end, int* ne, const B2CContactHitEvent** hit, int* nh);
   int getJointEvents(const int** ids, int* count);
 
+  // read-only view for b2c_noalloc.cu (b2cuda_world_copy_body_move_events_noalloc): nothing here changes the world
+  struct NoAllocView { int device; cudaStream_t stream; bool onDevice, lastStepDtZero; const WorldDev* dev; };
+  NoAllocView noAllocView() const { return NoAllocView{device_, stream_, onDevice_, lastStepDtZero_, &d_}; }
+
   // tunables (api/World.cs setters)
   V2 gravity; float restitutionThreshold, hitEventThreshold, contactHertz, contactDampingRatio, contactSpeed, maxLinearSpeed;
   bool enableSleep, enableContinuous, enableContactSoftening, enableWarmStarting = true, enableSpeculative = true;

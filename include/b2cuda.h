@@ -311,6 +311,16 @@ int32_t b2cuda_world_get_body_events(B2CWorld* world, const B2CBodyRead** record
  * awake-set order (24 B each), written by FinalizeBodies; after the first call every step copies the array to pinned host
  * memory behind the step, so the call only synchronises. Pointer valid until the next step. */
 int32_t b2cuda_world_get_body_move_events(B2CWorld* world, const B2CBodyMoveEvent** events, int32_t* count);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it). Same records as b2cuda_world_get_body_move_events — one
+ * B2CBodyMoveEvent per AWAKE body in awake-set order — but packed into a file-scope device array of B2C_NOALLOC_MAX_MOVE_EVENTS records
+ * (1.5 MiB, held by every GPU that loads the library until exit) and copied into `dst`, which the CALLER owns: host memory (pageable or
+ * pinned) or device memory of at least `capacity` records. Calls no cudaMalloc / cudaFree / cudaHostAlloc or any other allocating routine.
+ * More awake bodies than the maximum: B2C_E_CAPACITY; `capacity` too small: B2C_E_INVALID; *count = records written (0 after a dt = 0 step).
+ * Synchronises the world's stream before returning. Every call on a GPU shares the one scratch array, which keeps the last call's
+ * contents (nothing needs clearing: records [0, count) are overwritten before they are copied): calls that overlap on the GPU race. */
+#define B2C_NOALLOC_MAX_MOVE_EVENTS 65536
+int32_t b2cuda_world_copy_body_move_events_noalloc(B2CWorld* world, B2CBodyMoveEvent* dst, int32_t capacity, int32_t* count);
 /* ContactAPI.GetData for every live contact in ascending contactId */
 int32_t b2cuda_world_read_contacts(B2CWorld* world, B2CContactRead* dst, int32_t capacity, int32_t* count);
 int32_t b2cuda_world_read_joints(B2CWorld* world, B2CJointRead* dst, int32_t capacity, int32_t* count);
