@@ -132,7 +132,9 @@ def CudaBackend(device=0):
             raise B2Error(f"b2cuda_world_create failed rc={rc}: {extra['last_error']().decode()}")
         return h
 
-    return Backend(fns, create, lambda h: extra["last_error"]().decode(), "cuda")
+    be = Backend(fns, create, lambda h: extra["last_error"]().decode(), "cuda")
+    be.device = device
+    return be
 
 
 class World:
@@ -473,3 +475,56 @@ class World:
 
     def ReadShapes(self):
         return self._read("world_read_shapes", ShapeRead, self.GetCounters().shapeCount + 16)
+
+
+class Batch:
+    """b2cuda_batch_*: N independent worlds on one device, stepped in lockstep by one launch (api/World.cs:9-10).
+    `worlds[k]` is an ordinary World facade on the handle of world k (build it, read it back, mutate it between steps)."""
+
+    def __init__(self, backend, n_worlds, world_def=None):
+        self.backend, self.fns = backend, backend.fns
+        self.handle = C.c_void_p()
+        wd = world_def if world_def is not None else default_world_def()
+        rc = self.fns["batch_create"](C.byref(wd), getattr(backend, "device", 0), n_worlds, C.byref(self.handle))
+        if rc != 0:
+            raise B2Error(f"b2cuda_batch_create failed rc={rc}: {self.fns['last_error']().decode()}")
+        self.worlds = []
+        for k in range(n_worlds):
+            h = C.c_void_p()
+            self._check(self.fns["batch_world"](self.handle, k, C.byref(h)))
+            w = World.__new__(World)
+            w.backend, w.fns, w.handle = backend, backend.fns, h
+            w.Destroy = lambda: None            # owned by the batch
+            self.worlds.append(w)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise B2Error(f"cuda batch rc={rc}: {self.fns['last_error']().decode()}")
+
+    def Step(self, dt, substeps):
+        self._check(self.fns["batch_step"](self.handle, dt, substeps))
+
+    def Synchronize(self):
+        self._check(self.fns["batch_synchronize"](self.handle))
+
+    def ResetWorld(self, index):
+        self._check(self.fns["batch_reset_world"](self.handle, index))
+
+    def Stats(self, device_ptr=None):
+        """Statistics reduced over all worlds on the device; device_ptr (e.g. a torch float64[8] tensor's data_ptr()) also receives them."""
+        s = capi.BatchStats()
+        self._check(self.fns["batch_stats"](self.handle, C.byref(s), C.c_void_p(device_ptr) if device_ptr else None))
+        return s
+
+    def TimerStart(self):
+        self._check(self.fns["batch_timer_start"](self.handle))
+
+    def TimerStop(self):
+        ms = C.c_float()
+        self._check(self.fns["batch_timer_stop"](self.handle, C.byref(ms)))
+        return ms.value
+
+    def Destroy(self):
+        if self.handle is not None:
+            self.fns["batch_destroy"](self.handle)
+            self.handle = None

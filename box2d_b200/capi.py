@@ -218,6 +218,22 @@ PRODUCT_ONLY = {
     "world_debug_checksums": ([_W, C.POINTER(C.c_uint64)], C.c_int32),
     "world_copy_body_move_events_noalloc": ([_W, C.POINTER(BodyMoveEvent), C.c_int32, C.POINTER(C.c_int32)], C.c_int32),
 }
+class BatchStats(C.Structure):
+    _fields_ = [(n, C.c_double) for n in ("awakeBodies", "sumV2", "touchingContacts", "beginEvents", "endEvents", "maxSpeed", "minY", "errorFlags")]
+
+
+_B = C.c_void_p
+PRODUCT_ONLY.update({
+    "batch_create": ([C.POINTER(WorldDef), C.c_int32, C.c_int32, C.POINTER(_B)], C.c_int32),
+    "batch_destroy": ([_B], C.c_int32),
+    "batch_world": ([_B, C.c_int32, C.POINTER(_W)], C.c_int32),
+    "batch_step": ([_B, C.c_float, C.c_int32], C.c_int32),
+    "batch_synchronize": ([_B], C.c_int32),
+    "batch_reset_world": ([_B, C.c_int32], C.c_int32),
+    "batch_stats": ([_B, C.POINTER(BatchStats), C.c_void_p], C.c_int32),
+    "batch_timer_start": ([_B], C.c_int32),
+    "batch_timer_stop": ([_B, C.POINTER(C.c_float)], C.c_int32),
+})
 NOALLOC_MAX_MOVE_EVENTS = 65536     # B2C_NOALLOC_MAX_MOVE_EVENTS
 
 

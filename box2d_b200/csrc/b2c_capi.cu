@@ -8,7 +8,11 @@ using namespace b2c;
 struct B2CWorld { World* w; };
 static thread_local std::string g_lastError;
 void b2cSetLastError(const std::string& msg) { g_lastError = msg; }   // for entry points that live in other files (b2c_noalloc.cu)
-static int done(B2CWorld* h, int rc) { if (rc != B2C_OK && h && h->w) g_lastError = h->w->error; return rc; }
+static int done(B2CWorld* h, int rc) {
+  if (h && h->w) h->w->markDeviceDirty();        // batch member: the call may have changed counts / capacities the kernels take from WorldDev
+  if (rc != B2C_OK && h && h->w) g_lastError = h->w->error;
+  return rc;
+}
 #define CHECK_HANDLE(h) do { if (!(h) || !(h)->w) { g_lastError = "null world handle"; return B2C_E_INVALID; } } while (0)
 
 extern "C" {
@@ -66,7 +70,11 @@ int32_t b2cuda_world_create(const B2CWorldDef* def, int32_t device, B2CWorld** o
   *out = h;
   return B2C_OK;
 }
-int32_t b2cuda_world_destroy(B2CWorld* h) { if (!h) return B2C_E_INVALID; delete h->w; delete h; return B2C_OK; }
+int32_t b2cuda_world_destroy(B2CWorld* h) {
+  if (!h) return B2C_E_INVALID;
+  if (h->w && h->w->inBatch()) { g_lastError = "this world belongs to a batch: b2cuda_batch_destroy frees it"; return B2C_E_INVALID; }
+  delete h->w; delete h; return B2C_OK;
+}
 
 int32_t b2cuda_create_body(B2CWorld* h, const B2CBodyDef* def, int32_t* bodyId) { CHECK_HANDLE(h); if (!def || !bodyId) return B2C_E_INVALID; return done(h, h->w->createBody(*def, bodyId)); }
 int32_t b2cuda_create_shape(B2CWorld* h, int32_t bodyId, const B2CShapeDef* def, const B2CGeometry* g, int32_t* shapeId) {
@@ -143,4 +151,43 @@ int32_t b2cuda_world_enable_graph_launch(B2CWorld* h, int32_t flag) { CHECK_HAND
 int32_t b2cuda_world_timer_start(B2CWorld* h) { CHECK_HANDLE(h); return done(h, h->w->timerStart()); }
 int32_t b2cuda_world_timer_stop(B2CWorld* h, float* ms) { CHECK_HANDLE(h); if (!ms) return B2C_E_INVALID; return done(h, h->w->timerStop(ms)); }
 
+// ---- batches of independent worlds (b2c_batch.cu) ----
+}  // extern "C"
+#include <vector>
+struct B2CBatch { Batch* b; std::vector<B2CWorld> handles; };
+#define CHECK_BATCH(h) do { if (!(h) || !(h)->b) { g_lastError = "null batch handle"; return B2C_E_INVALID; } } while (0)
+static int doneB(B2CBatch* h, int rc) { if (rc != B2C_OK) g_lastError = h->b->error; return rc; }
+extern "C" {
+int32_t b2cuda_batch_create(const B2CWorldDef* def, int32_t device, int32_t worldCount, B2CBatch** out) {
+  if (!def || !out || worldCount < 0) { g_lastError = "null argument or negative world count"; return B2C_E_INVALID; }
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) { g_lastError = std::string("no usable CUDA device: ") + cudaGetErrorString(e) + " (libb2cuda has no CPU fallback)"; return B2C_E_NO_DEVICE; }
+  if (device < 0 || device >= count) { g_lastError = "device index out of range"; return B2C_E_NO_DEVICE; }
+  if (def->enableSleep) { g_lastError = "enableSleep=1 (islands/sleep, src/Island.cs) is not supported in this build; set enableSleep=0"; return B2C_E_UNSUPPORTED; }
+  B2CBatch* h = new (std::nothrow) B2CBatch();
+  if (!h) return B2C_E_INVALID;
+  h->b = new (std::nothrow) Batch(*def, device, worldCount);
+  if (!h->b) { delete h; return B2C_E_INVALID; }
+  int rc = h->b->init();
+  if (rc != B2C_OK) { g_lastError = h->b->error; delete h->b; delete h; return rc; }
+  h->handles.resize(worldCount);
+  for (int i = 0; i < worldCount; i++) h->handles[i].w = h->b->world(i);
+  *out = h;
+  return B2C_OK;
+}
+int32_t b2cuda_batch_destroy(B2CBatch* h) { if (!h) return B2C_E_INVALID; delete h->b; delete h; return B2C_OK; }
+int32_t b2cuda_batch_world(B2CBatch* h, int32_t index, B2CWorld** world) {
+  CHECK_BATCH(h); if (!world) return B2C_E_INVALID;
+  if (index < 0 || index >= (int)h->handles.size()) { g_lastError = "world index out of range"; *world = nullptr; return B2C_E_INVALID; }
+  *world = &h->handles[index];
+  return B2C_OK;
+}
+int32_t b2cuda_batch_step(B2CBatch* h, float dt, int32_t sub) { CHECK_BATCH(h); return doneB(h, h->b->step(dt, sub)); }
+int32_t b2cuda_batch_synchronize(B2CBatch* h) { CHECK_BATCH(h); return doneB(h, h->b->synchronize()); }
+int32_t b2cuda_batch_reset_world(B2CBatch* h, int32_t index) { CHECK_BATCH(h); return doneB(h, h->b->resetWorld(index)); }
+int32_t b2cuda_batch_stats(B2CBatch* h, B2CBatchStats* out, double* deviceDst) { CHECK_BATCH(h); return doneB(h, h->b->stats(out, deviceDst)); }
+int32_t b2cuda_batch_timer_start(B2CBatch* h) { CHECK_BATCH(h); return doneB(h, h->b->timerStart()); }
+int32_t b2cuda_batch_timer_stop(B2CBatch* h, float* ms) { CHECK_BATCH(h); if (!ms) return B2C_E_INVALID; return doneB(h, h->b->timerStop(ms)); }
 }  // extern "C"

@@ -87,7 +87,7 @@ static void geomExtent(const Geom& g, V2 localCenter, float* minExtent, float* m
   }
 }
 
-World::World(const B2CWorldDef& def, int device) : device_(device) {
+World::World(const B2CWorldDef& def, int device, Batch* batch, int batchIndex) : device_(device), batch_(batch), batchIndex_(batchIndex) {
   gravity = mk(def.gravity.x, def.gravity.y);
   restitutionThreshold = def.restitutionThreshold; hitEventThreshold = def.hitEventThreshold; contactHertz = def.contactHertz;
   contactDampingRatio = def.contactDampingRatio; contactSpeed = def.contactSpeed; maxLinearSpeed = def.maximumLinearSpeed;
@@ -101,11 +101,12 @@ World::~World() { freeDevice(); }
 
 void World::freeDevice() {
   if (device_ >= 0) cudaSetDevice(device_);
-  for (void* p : allocs_) cudaFree(p);
+  if (!batch_) for (void* p : allocs_) cudaFree(p);      // a batch member's arrays live in the batch's arena
   allocs_.clear(); allocRecs_.clear();
-  if (hostScalars_) cudaFreeHost(hostScalars_);
+  if (hostScalars_) { if (batch_) free(hostScalars_); else cudaFreeHost(hostScalars_); }
+  if (batch_) hJointColor_ = nullptr;                    // the batch's mapped int
   if (hJointColor_) { cudaFreeHost(hJointColor_); hJointColor_ = nullptr; hJointColorDev_ = nullptr; }
-  if (hBegin_) cudaFreeHost(hBegin_);
+  if (hBegin_) cudaFreeHost(hBegin_);                   // (null for a batch member: its events stay in device memory)
   for (auto& e : hEnd_) { if (e) cudaFreeHost(e); e = nullptr; }
   if (hHit_) cudaFreeHost(hHit_);
   if (hJointEvents_) cudaFreeHost(hJointEvents_);
@@ -118,7 +119,8 @@ void World::freeDevice() {
   for (auto& g : graphs_) { if (g.exec) cudaGraphExecDestroy(g.exec); for (auto& e : g.ev) if (e) cudaEventDestroy(e); }
   graphs_.clear();
   for (auto& e : timer_) if (e) { cudaEventDestroy(e); e = nullptr; }
-  if (stream_) { cudaStreamDestroy(stream_); stream_ = nullptr; }
+  if (stream_ && !batch_) cudaStreamDestroy(stream_);
+  stream_ = nullptr;
 }
 
 void World::bufferMove(int key) {                 // src/BroadPhase.cs:56-59
@@ -1000,6 +1002,13 @@ int World::setTransform(int bodyId, V2 p, Rot q) {          // api/Body.cs:293-3
 template <class T> T* World::dalloc(size_t n) {
   void* p = nullptr;
   if (n == 0) n = 1;
+  if (batch_) {                                    // bump allocation inside the batch's arena (freed with the batch)
+    p = batchArenaAlloc(batch_, n * sizeof(T));    // arena chunks are zero-filled when they are created
+    if (!p) return nullptr;
+    arenaBlocks_.push_back({p, n * sizeof(T)});
+    allocs_.push_back(p);
+    return (T*)p;
+  }
   if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
   cudaMemsetAsync(p, 0, n * sizeof(T), stream_);
   allocs_.push_back(p);
@@ -1019,6 +1028,7 @@ int World::regrow(void** slot, size_t newCount, int fillByte) {
     if (r.slot != slot) continue;
     if (newCount <= r.count) return B2C_OK;
     void* p = nullptr;
+    if (batch_) return fail(B2C_E_CAPACITY, "a world of a batch cannot grow its device arrays: reserve rows with B2CWorldDef.bodyCapacity / shapeCapacity / jointCapacity");
     if (cudaMalloc(&p, newCount * r.elem) != cudaSuccess) { cudaGetLastError(); return fail(B2C_E_CUDA, "cudaMalloc failed while growing a device array"); }
     CK(cudaMemsetAsync(p, fillByte, newCount * r.elem, stream_));
     void* old = *slot;
@@ -1115,19 +1125,24 @@ int World::growTree(int type, int minNodes) {      // the allocation behind the 
 
 int World::upload() {
   CK(cudaSetDevice(device_));
-  CK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
-  for (auto& e : ev_) CK(cudaEventCreate(&e));
-  for (auto& e : timer_) CK(cudaEventCreate(&e));
-  CK(cudaHostAlloc((void**)&hostScalars_, sizeof(Scalars), cudaHostAllocDefault));
+  const bool member = batch_ != nullptr;           // batch member: the batch's stream and arena, slim reserves, no per-world events or pinned buffers
+  if (member) { stream_ = batchStream(batch_); if (!hostScalars_) hostScalars_ = (Scalars*)malloc(sizeof(Scalars)); }
+  else {
+    CK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+    for (auto& e : ev_) CK(cudaEventCreate(&e));
+    for (auto& e : timer_) CK(cudaEventCreate(&e));
+    CK(cudaHostAlloc((void**)&hostScalars_, sizeof(Scalars), cudaHostAllocDefault));
+  }
   memset(hostScalars_, 0, sizeof(Scalars));
   WorldDev& d = d_;
   const int nBody = (int)bodies_.size(), nAwake = (int)awakeOrder_.size(), nShape = (int)shapes_.size(), nJoint = (int)joints_.size();
   d.awakeCount = nAwake; d.bodyCapacity = nBody; d.shapeCapacity = nShape; d.jointCapacity = nJoint;
   // Headroom for bodies and shapes created after this upload (b2cuda_create_body / _create_shape between steps): a quarter more, at least
   // 256, or what the world definition asks for. Past it the create call fails with B2C_E_CAPACITY; nothing here grows behind a running step.
-  capBody_ = std::max(nBody + std::max(256, nBody / 4), capHintBody); capShape_ = std::max(nShape + std::max(256, nShape / 4), capHintShape);
+  const int reserve = member ? 8 : 256;            // a batch world is built before its first step; larger reserves come from the world definition
+  capBody_ = std::max(nBody + std::max(reserve, nBody / 4), capHintBody); capShape_ = std::max(nShape + std::max(reserve, nShape / 4), capHintShape);
   capAwake_ = nAwake + (capBody_ - nBody);
-  capJoint_ = std::max(nJoint + std::max(256, nJoint / 4), capHintJoint);
+  capJoint_ = std::max(nJoint + std::max(reserve, nJoint / 4), capHintJoint);
   const int capBody = capBody_, capAwake = capAwake_, capShape = capShape_, capJoint = capJoint_;
   // ---- bodies ----
   std::vector<float4> st0(nAwake), st1(nAwake), simMass(nAwake), simForce(nAwake), simPose(nAwake), simLocal(nAwake), simPose0(nAwake);
@@ -1203,7 +1218,7 @@ int World::upload() {
     int cap = logicalCap;                          // allocation: the reference's growth steps (x1.5) until the reserved shapes fit
     while (cap - h.nodeCount < 2 * (capShape - nShape) + 2) cap += cap >> 1;
     treeAllocCap_[t] = cap; treeNodeCount_[t] = h.nodeCount; treeProxyCount_[t] = h.proxyCount;
-    td.capacity = logicalCap; td.stackCapacity = 16384;
+    td.capacity = logicalCap; td.stackCapacity = member ? 1024 : 16384;
     DA(td.aabb, float4, cap); DA(td.child, int2, cap); DA(td.parent, int, cap); DA(td.hf, uint32_t, cap); DA(td.cat, uint64_t, cap);
     DA(td.user, int, cap); DA(td.moved, uint8_t, cap); DA(td.meta, int, 4); DA(td.leafIdx, int, cap); DA(td.leafCtr, float2, cap); DA(td.stack, int, td.stackCapacity);
     DA(td.segStart, int, cap); DA(td.recEnd, int, cap + 1); DA(td.recNode, int, cap + 1); DA(td.recSplit, int, cap + 1); DA(td.recBox, float4, cap + 1);
@@ -1220,15 +1235,15 @@ int World::upload() {
     totalProxies += h.proxyCount;
   }
   d.moveCapacity = std::max(totalProxies + (capShape - nShape), 16);
-  int contactCap = capHintContact > 0 ? capHintContact : std::max(4096, 12 * nShape);
+  int contactCap = capHintContact > 0 ? capHintContact : std::max(member ? 256 : 4096, 12 * nShape);
   d.contactCapacity = contactCap; d.pairCapacity = contactCap; d.eventCapacity = contactCap;
   d.constraintCapacity = contactCap + 32 * kGraphColorCount;
-  int tableSize = 1; while (tableSize < 4 * contactCap) tableSize <<= 1;
+  int tableSize = 1; while (tableSize < (member ? 2 : 4) * contactCap) tableSize <<= 1;
   d.pairTableSize = tableSize;
   DA(d.moveArray, int, d.moveCapacity); DA(d.moveHitCount, int, d.moveCapacity + 1); DA(d.movePairs, int2, d.pairCapacity);
   DA(d.pairTable, unsigned long long, tableSize);
   { int sumCap = 0; for (int t = 0; t < 3; t++) sumCap += treeAllocCap_[t];
-    d.bigScratch = std::max(1 << 21, sumCap);
+    d.bigScratch = member ? sumCap : std::max(1 << 21, sumCap);
     d.bigQueryVisits = kBigQueryVisits;
     d.islandMaxBodies = kIslandMaxBodies;
     d.debugChecksums = getenv("B2CUDA_DEBUG_CHECKSUMS") ? atoi(getenv("B2CUDA_DEBUG_CHECKSUMS")) : 0;
@@ -1242,7 +1257,7 @@ int World::upload() {
   DA(d.mN, float4, contactCap); DA(d.mA0, float4, contactCap); DA(d.mA1, float4, contactCap); DA(d.mB0, float4, contactCap); DA(d.mB1, float4, contactCap);
   DA(d.mC0, float4, contactCap); DA(d.mC1, float4, contactCap); DA(d.contactFree, int, contactCap);
   DA(d.flagScan, int4, contactCap + 1); DA(d.opList, int, contactCap); DA(d.opDone, uint8_t, contactCap); DA(d.opCol, uint8_t, contactCap);
-  d.ovCapacity = contactCap / 4 + 1024;
+  d.ovCapacity = contactCap / 4 + (member ? 16 : 1024);
   DA(d.colList, int, (size_t)kGraphColorCount * contactCap); DA(d.cLocal, int, contactCap); DA(d.cRestGroup, uint8_t, contactCap); DA(d.ovCons, OvConstraint, d.ovCapacity);
   CK(cudaMemsetAsync(d.cLocal, 0xff, sizeof(int) * (size_t)contactCap, stream_));
   int cc = d.constraintCapacity;
@@ -1260,28 +1275,52 @@ int World::upload() {
   Scalars init; memset(&init, 0, sizeof(init));
   init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;
   CK(cudaMemcpyAsync(d.sc, &init, sizeof(init), cudaMemcpyHostToDevice, stream_));
-  // contact events are written by the kernels straight into mapped pinned host memory (few per step; no copy, no extra sync)
-  CK(cudaHostAlloc((void**)&hBegin_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocMapped));
-  for (auto& e : hEnd_) CK(cudaHostAlloc((void**)&e, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocMapped));
-  CK(cudaHostAlloc((void**)&hHit_, sizeof(B2CContactHitEvent) * d.eventCapacity, cudaHostAllocMapped));
-  CK(cudaHostGetDevicePointer((void**)&d.beginEvents, hBegin_, 0));
-  for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.endEvents[k], hEnd_[k], 0));
-  CK(cudaHostGetDevicePointer((void**)&d.hitEvents, hHit_, 0));
-  d.bodyOut = nullptr;
+  d.bodyOut = nullptr; d.moveOut = nullptr;
   DA(dBodyRead_, B2CBodyRead, capBody);
   DA(dMoveEvents_, B2CBodyMoveEvent, capAwake);
-  CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)std::max(capAwake, 1), cudaHostAllocMapped));
-  // B2CUDA_ZEROCOPY_MOVES=1: FinalizeBodies writes the move events straight into this mapped buffer instead of a device array + copy behind
-  // the step. Measured slower end to end (many_pyramids 560 vs 582 M body-substeps/s, batched 1663 vs 1779): off by default.
-  { const char* e = getenv("B2CUDA_ZEROCOPY_MOVES"); hMoveEventsDev_ = nullptr;
-    if (e && !strcmp(e, "1") && cudaHostGetDevicePointer((void**)&hMoveEventsDev_, hMoveEvents_, 0) != cudaSuccess) { hMoveEventsDev_ = nullptr; cudaGetLastError(); } }
-  d.moveOut = nullptr;
-  CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(capBody, 1), cudaHostAllocDefault));
-  CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(capJoint, 1), cudaHostAllocDefault));
-  CK(cudaHostAlloc((void**)&hJointColor_, sizeof(int), cudaHostAllocMapped));
-  CK(cudaHostGetDevicePointer((void**)&hJointColorDev_, hJointColor_, 0));
+  hMoveEventsDev_ = nullptr;
+  if (member) {                                    // events stay in device memory and are copied on demand; pinned read-back buffers come on first use
+    DA(d.beginEvents, B2CContactTouchEvent, d.eventCapacity); DA(d.endEvents[0], B2CContactTouchEvent, d.eventCapacity);
+    DA(d.endEvents[1], B2CContactTouchEvent, d.eventCapacity); DA(d.hitEvents, B2CContactHitEvent, d.eventCapacity);
+    hJointColor_ = batchMappedInt(batch_, &hJointColorDev_);
+  } else {
+    // contact events are written by the kernels straight into mapped pinned host memory (few per step; no copy, no extra sync)
+    CK(cudaHostAlloc((void**)&hBegin_, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocMapped));
+    for (auto& e : hEnd_) CK(cudaHostAlloc((void**)&e, sizeof(B2CContactTouchEvent) * d.eventCapacity, cudaHostAllocMapped));
+    CK(cudaHostAlloc((void**)&hHit_, sizeof(B2CContactHitEvent) * d.eventCapacity, cudaHostAllocMapped));
+    CK(cudaHostGetDevicePointer((void**)&d.beginEvents, hBegin_, 0));
+    for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.endEvents[k], hEnd_[k], 0));
+    CK(cudaHostGetDevicePointer((void**)&d.hitEvents, hHit_, 0));
+    { int rc = ensureHostBuffers(); if (rc) return rc; }
+    // B2CUDA_ZEROCOPY_MOVES=1: FinalizeBodies writes the move events straight into this mapped buffer instead of a device array + copy behind
+    // the step. Measured slower end to end (many_pyramids 560 vs 582 M body-substeps/s, batched 1663 vs 1779): off by default.
+    { const char* e = getenv("B2CUDA_ZEROCOPY_MOVES");
+      if (e && !strcmp(e, "1") && cudaHostGetDevicePointer((void**)&hMoveEventsDev_, hMoveEvents_, 0) != cudaSuccess) { hMoveEventsDev_ = nullptr; cudaGetLastError(); } }
+    CK(cudaHostAlloc((void**)&hJointColor_, sizeof(int), cudaHostAllocMapped));
+    CK(cudaHostGetDevicePointer((void**)&hJointColorDev_, hJointColor_, 0));
+  }
   CK(cudaStreamSynchronize(stream_));
   onDevice_ = true;
+  return B2C_OK;
+}
+
+void World::saveHostSnap(HostSnap& h) const {
+  h.bodyIds = bodyIds_; h.shapeIds = shapeIds_; h.jointIds = jointIds_; h.bodies = bodies_; h.shapes = shapes_; h.joints = joints_;
+  h.awakeOrder = awakeOrder_; h.colorJoints = colorJoints_; h.colorMask = colorMask_; h.d = d_;
+  for (int t = 0; t < 3; t++) { h.treeNodeCount[t] = treeNodeCount_[t]; h.treeProxyCount[t] = treeProxyCount_[t]; }
+  h.valid = true;
+}
+void World::restoreHostSnap(const HostSnap& h) {
+  bodyIds_ = h.bodyIds; shapeIds_ = h.shapeIds; jointIds_ = h.jointIds; bodies_ = h.bodies; shapes_ = h.shapes; joints_ = h.joints;
+  awakeOrder_ = h.awakeOrder; colorJoints_ = h.colorJoints; colorMask_ = h.colorMask; d_ = h.d;
+  for (int t = 0; t < 3; t++) { treeNodeCount_[t] = h.treeNodeCount[t]; treeProxyCount_[t] = h.treeProxyCount[t]; }
+  eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false; lastStepDtZero_ = false;
+}
+
+int World::ensureHostBuffers() {                   // pinned read-back buffers (bulk body records, move events, joint events)
+  if (!hMoveEvents_) CK(cudaHostAlloc((void**)&hMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)std::max(capAwake_, 1), cudaHostAllocMapped));
+  if (!hBodyRead_) CK(cudaHostAlloc((void**)&hBodyRead_, sizeof(B2CBodyRead) * (size_t)std::max(capBody_, 1), cudaHostAllocDefault));
+  if (!hJointEvents_) CK(cudaHostAlloc((void**)&hJointEvents_, sizeof(int) * (size_t)std::max(capJoint_, 1), cudaHostAllocDefault));
   return B2C_OK;
 }
 
@@ -1289,6 +1328,7 @@ int World::synchronize() {
   if (!onDevice_) return B2C_OK;
   CK(cudaSetDevice(device_));
   CK(cudaStreamSynchronize(stream_));
+  if (batch_ && scalarsStale_) { CK(cudaMemcpy(hostScalars_, d_.sc, sizeof(Scalars), cudaMemcpyDeviceToHost)); scalarsStale_ = false; }
   if (hostScalars_->errorFlags & ~(int)ERR_TOI_CANDIDATE) {   // TOI candidates are counted (counters.toiCandidates), the step uses the no-hit result
     char buf[160]; snprintf(buf, sizeof(buf), "device error flags 0x%x (capacity/stack/overflow-color/TOI; see b2c_world.cuh ERR_*)", hostScalars_->errorFlags);
     uint32_t f = (uint32_t)hostScalars_->errorFlags;
@@ -1771,8 +1811,15 @@ int World::getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B
     if (hBeginN_ > d_.eventCapacity) hBeginN_ = d_.eventCapacity;
     if (hEndN_ > d_.eventCapacity) hEndN_ = d_.eventCapacity;
     if (hHitN_ > d_.eventCapacity) hHitN_ = d_.eventCapacity;
+    if (batch_) {                                  // batch member: the event arrays are device memory
+      stageBegin_.resize(std::max(hBeginN_, 1)); stageEnd_.resize(std::max(hEndN_, 1)); stageHit_.resize(std::max(hHitN_, 1));
+      if (hBeginN_) CK(cudaMemcpy(stageBegin_.data(), d_.beginEvents, sizeof(B2CContactTouchEvent) * hBeginN_, cudaMemcpyDeviceToHost));
+      if (hEndN_) CK(cudaMemcpy(stageEnd_.data(), d_.endEvents[lastEndIndex_], sizeof(B2CContactTouchEvent) * hEndN_, cudaMemcpyDeviceToHost));
+      if (hHitN_) CK(cudaMemcpy(stageHit_.data(), d_.hitEvents, sizeof(B2CContactHitEvent) * hHitN_, cudaMemcpyDeviceToHost));
+    }
     eventsFetched_ = true;
   }
+  if (batch_) { *begin = stageBegin_.data(); *nb = hBeginN_; *end = stageEnd_.data(); *ne = hEndN_; *hit = stageHit_.data(); *nh = hHitN_; return B2C_OK; }
   *begin = hBegin_; *nb = hBeginN_; *end = hEnd_[lastEndIndex_]; *ne = hEndN_; *hit = hHit_; *nh = hHitN_;
   return B2C_OK;
 }
@@ -1781,6 +1828,8 @@ int World::getJointEvents(const int** ids, int* count) {
   *ids = hJointEvents_; *count = 0;
   if (!onDevice_ || joints_.empty()) return B2C_OK;
   int rc = synchronize(); if (rc) return rc;
+  rc = ensureHostBuffers(); if (rc) return rc;
+  *ids = hJointEvents_;
   std::vector<uint8_t> flags;
   if (fetch(flags, d_.jointEventFlag, joints_.size(), stream_)) return fail(B2C_E_CUDA, "joint event copy failed");
   CK(cudaStreamSynchronize(stream_));

@@ -52,10 +52,19 @@ struct HJoint {
   JointDev sim;
 };
 
+class Batch;
+cudaStream_t batchStream(Batch* b);                       // b2c_batch.cu
+void* batchArenaAlloc(Batch* b, size_t bytes);
+int* batchMappedInt(Batch* b, int** devPtr);
+void batchMarkDirty(Batch* b, int index);
 class World {
  public:
-  explicit World(const B2CWorldDef& def, int device);
+  explicit World(const B2CWorldDef& def, int device, Batch* batch = nullptr, int batchIndex = -1);
   ~World();
+  // --- membership in a batch of independent worlds (b2c_batch.cu): the batch owns the stream and the device memory arena, steps all its
+  //     worlds with one launch and keeps a device array of their WorldDev records ---
+  bool inBatch() const { return batch_ != nullptr; }
+  void markDeviceDirty() { if (batch_ && !devDirty_) { devDirty_ = true; batchMarkDirty(batch_, batchIndex_); } }   // d_ may differ from the batch's device copy of it
   // --- creation API (host) ---
   int createBody(const B2CBodyDef& def, int* bodyId);
   int createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId);
@@ -140,6 +149,20 @@ class World {
   int device_;
   cudaStream_t stream_ = nullptr;
   bool onDevice_ = false;
+  friend class Batch;
+  Batch* batch_ = nullptr; int batchIndex_ = -1;
+  bool devDirty_ = false;
+  bool scalarsStale_ = false;     // batch member: hostScalars_ has not been fetched since the last batch step
+  std::vector<std::pair<void*, size_t>> arenaBlocks_;   // batch member: its device arrays inside the batch's arena, in allocation order
+  struct HostSnap {               // everything creation / destruction calls change on the host, for Batch::resetWorld
+    IdPool bodyIds, shapeIds, jointIds; std::vector<HBody> bodies; std::vector<HShape> shapes; std::vector<HJoint> joints;
+    std::vector<int> awakeOrder; std::vector<std::vector<int>> colorJoints; std::vector<uint32_t> colorMask;
+    int treeNodeCount[3], treeProxyCount[3]; WorldDev d; bool valid = false;
+  };
+  void saveHostSnap(HostSnap& h) const;
+  void restoreHostSnap(const HostSnap& h);
+  int ensureHostBuffers();        // pinned read-back buffers; a batch member allocates them on first use
+  std::vector<B2CContactTouchEvent> stageBegin_, stageEnd_; std::vector<B2CContactHitEvent> stageHit_;   // batch member: events live in device memory and are copied on demand
   // host creation state
   IdPool bodyIds_, shapeIds_, jointIds_;
   std::vector<HBody> bodies_; std::vector<HShape> shapes_; std::vector<HJoint> joints_;
@@ -189,6 +212,49 @@ class World {
   bool movesFetched_ = false, streamMoves_ = false, lastStepDtZero_ = false;
   int islandMode_ = 0;   // 0 auto, 1 CTA per island, 2 warp per island   // streamBodies_: every step packs + copies the body records (set by the first GetBodyEvents)
   friend struct StepLauncher;
+};
+
+
+// One handle = N independent worlds on one device (api/World.cs:9-10), stepped in lockstep by ONE launch: a CTA per world runs the
+// whole step (k_batch_step in b2c_step.cu). The worlds are built through the ordinary creation API on the handles b2cuda_batch_world
+// hands out; every world keeps its own id pools, trees, contact ids and colour graph in its own slice of the batch's device arena, so
+// world k is bit-identical to the same world stepped alone. Step parameters (gravity, contact tuning, thresholds, switches) are the
+// batch's: they are taken from the world definition the batch was created with.
+class Batch {
+ public:
+  Batch(const B2CWorldDef& def, int device, int worldCount);
+  ~Batch();
+  int init();
+  int worldCount() const { return (int)worlds_.size(); }
+  World* world(int i) { return i >= 0 && i < (int)worlds_.size() ? worlds_[i] : nullptr; }
+  int step(float dt, int subSteps);
+  int synchronize();
+  int stats(B2CBatchStats* out, double* deviceDst);
+  int resetWorld(int index);
+  int timerStart();
+  int timerStop(float* ms);
+  std::string error;
+  // used by member worlds
+  cudaStream_t stream() { return stream_; }
+  void* arenaAlloc(size_t bytes);
+  int* mappedInt(int** devPtr) { *devPtr = mappedIntDev_; return mappedInt_; }
+  void markDirty(int index) { dirty_.push_back(index); }
+ private:
+  int fail(int code, const std::string& msg) { error = msg; return code; }
+  int ensureUploaded();
+  int device_; B2CWorldDef def_;
+  cudaStream_t stream_ = nullptr;
+  std::vector<World*> worlds_;
+  WorldDev* dWorlds_ = nullptr;
+  bool uploaded_ = false;
+  std::vector<int> dirty_;
+  std::vector<void*> chunks_; char* chunkPtr_ = nullptr; size_t chunkLeft_ = 0;   // device arena: chunks of >= 256 MB, zero-filled, bump allocation, freed with the batch
+  struct Snap { World::HostSnap host; char* dev = nullptr; size_t bytes = 0; };   // state at the first step, for resetWorld
+  std::vector<Snap> snaps_; std::vector<void*> snapChunks_;
+  int* mappedInt_ = nullptr; int* mappedIntDev_ = nullptr;
+  int endIndex_ = 0, stepCount_ = 0;
+  double* dStats_ = nullptr; double* hStats_ = nullptr;
+  cudaEvent_t timer_[2] = {nullptr, nullptr};
 };
 
 }  // namespace b2c

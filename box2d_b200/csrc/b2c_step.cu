@@ -1687,6 +1687,7 @@ void World::harvestGraph(StepGraph& g) {          // event times of the graph's 
 }
 
 int World::step(float timeStep, int subStepCount) {
+  if (batch_) return fail(B2C_E_INVALID, "this world belongs to a batch: step it with b2cuda_batch_step");
   if (enableSleep) return fail(B2C_E_UNSUPPORTED, "enableSleep=true (islands/sleep, src/Island.cs) is not supported in this build; create the world with enableSleep=0");
   if (!onDevice_) { int rc = upload(); if (rc) return rc; }
   CK(cudaSetDevice(device_));
@@ -1815,28 +1816,75 @@ int World::getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count) {
   *events = nullptr; *count = 0;
   if (!onDevice_) return fail(B2C_E_INVALID, "get_body_move_events before the first step");
   CK(cudaSetDevice(device_));
+  { int rc = ensureHostBuffers(); if (rc) return rc; }
   if (!movesFetched_) {
     int n = d_.awakeCount;
     k_pack_moves<<<gridFor(n, kThreads, (coopBlocks_ > 0 ? coopBlocks_ : 148) * 8), kThreads, 0, stream_>>>(d_, dMoveEvents_);
     CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
     movesFetched_ = true;
-    streamMoves_ = true; d_.moveOut = hMoveEventsDev_ ? hMoveEventsDev_ : dMoveEvents_;   // from now on FinalizeBodies fills the events (mapped host memory, else device array + copy in step())
+    if (!batch_) { streamMoves_ = true; d_.moveOut = hMoveEventsDev_ ? hMoveEventsDev_ : dMoveEvents_; }   // from now on FinalizeBodies fills the events (mapped host memory, else device array + copy in step())
   }
   int rc = synchronize(); if (rc) return rc;
   *events = hMoveEvents_; *count = lastStepDtZero_ ? 0 : d_.awakeCount;
   return B2C_OK;
 }
 
+// One launch steps every world of a batch (b2c_batch.cu drives it)
+cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, cudaStream_t stream) {
+  k_batch_step<<<worldCount, kBatchThreads, 0, stream>>>(worlds, sp, newEndIndex);
+  return cudaGetLastError();
+}
+__global__ void k_batch_zero_step(const WorldDev* worlds, int newEndIndex) { Scalars& s = *worlds[blockIdx.x].sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; }
+cudaError_t launchBatchZeroStep(const WorldDev* worlds, int worldCount, int newEndIndex, cudaStream_t stream) {
+  k_batch_zero_step<<<worldCount, 1, 0, stream>>>(worlds, newEndIndex);
+  return cudaGetLastError();
+}
+// Batch statistics reduced on the device: out[0..4] sums (awake bodies, |v|^2, touching contacts, begin events, end events of the last step),
+// out[5] max |v|, out[6] min y, out[7] OR of the worlds' error flags. One CTA per world, one atomic per CTA and statistic.
+__device__ __forceinline__ void atomicMaxD(double* a, double v) { unsigned long long* p = (unsigned long long*)a; unsigned long long old = *p; while (__longlong_as_double((long long)old) < v) { unsigned long long prev = atomicCAS(p, old, (unsigned long long)__double_as_longlong(v)); if (prev == old) break; old = prev; } }
+__device__ __forceinline__ void atomicMinD(double* a, double v) { unsigned long long* p = (unsigned long long*)a; unsigned long long old = *p; while (__longlong_as_double((long long)old) > v) { unsigned long long prev = atomicCAS(p, old, (unsigned long long)__double_as_longlong(v)); if (prev == old) break; old = prev; } }
+__global__ void k_batch_stats_init(double* out) { out[0] = out[1] = out[2] = out[3] = out[4] = 0.0; out[5] = 0.0; out[6] = 1e300; out[7] = 0.0; }
+__global__ void __launch_bounds__(128) k_batch_stats(const WorldDev* worlds, int lastEndIndex, double* out, unsigned int* errOr) {
+  const WorldDev& d = worlds[blockIdx.x];
+  __shared__ double sSum[4], sMax[4], sMin[4];
+  double sum = 0.0, mx = 0.0, mn = 1e300;
+  for (int i = threadIdx.x; i < d.awakeCount; i += blockDim.x) {
+    float4 s = d.st0[i];
+    double v2 = (double)s.x * s.x + (double)s.y * s.y;
+    sum += v2; if (v2 > mx) mx = v2;
+    double y = d.bodyXf[d.simBodyId[i]].y; if (y < mn) mn = y;
+  }
+  for (int o = 16; o > 0; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o); double a = __shfl_xor_sync(0xffffffffu, mx, o), b = __shfl_xor_sync(0xffffffffu, mn, o); if (a > mx) mx = a; if (b < mn) mn = b; }
+  if ((threadIdx.x & 31) == 0) { sSum[threadIdx.x >> 5] = sum; sMax[threadIdx.x >> 5] = mx; sMin[threadIdx.x >> 5] = mn; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); w++) { sum += sSum[w]; if (sMax[w] > mx) mx = sMax[w]; if (sMin[w] < mn) mn = sMin[w]; }
+    const Scalars& s = *d.sc;
+    atomicAdd(&out[0], (double)d.awakeCount); atomicAdd(&out[1], sum); atomicAdd(&out[2], (double)s.touchingCount);
+    atomicAdd(&out[3], (double)s.beginCount); atomicAdd(&out[4], (double)s.endCount[lastEndIndex]);
+    atomicMaxD(&out[5], sqrt(mx)); if (d.awakeCount > 0) atomicMinD(&out[6], mn);
+    if (s.errorFlags) atomicOr(errOr, (unsigned int)s.errorFlags);
+  }
+}
+__global__ void k_batch_stats_finish(double* out, unsigned int* errOr) { out[7] = (double)*errOr; *errOr = 0u; }
+cudaError_t launchBatchStats(const WorldDev* worlds, int worldCount, int lastEndIndex, double* out, unsigned int* errOr, cudaStream_t stream) {
+  k_batch_stats_init<<<1, 1, 0, stream>>>(out);
+  k_batch_stats<<<worldCount, 128, 0, stream>>>(worlds, lastEndIndex, out, errOr);
+  k_batch_stats_finish<<<1, 1, 0, stream>>>(out, errOr);
+  return cudaGetLastError();
+}
+
 int World::getBodyEvents(const B2CBodyRead** records, int* count) {
   *records = nullptr; *count = 0;
   if (!onDevice_) return fail(B2C_E_INVALID, "get_body_events before the first step");
   CK(cudaSetDevice(device_));
+  { int rc = ensureHostBuffers(); if (rc) return rc; }
   if (!bodiesFetched_) {
     int n = d_.bodyCapacity;
     k_pack_bodies<<<gridFor(n, kThreads, (coopBlocks_ > 0 ? coopBlocks_ : 148) * 8), kThreads, 0, stream_>>>(d_, dBodyRead_);
     CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)n, cudaMemcpyDeviceToHost, stream_));
     bodiesFetched_ = true;
-    streamBodies_ = true; d_.bodyOut = dBodyRead_;   // from now on FinalizeBodies keeps the records current and step() copies them
+    if (!batch_) { streamBodies_ = true; d_.bodyOut = dBodyRead_; }   // from now on FinalizeBodies keeps the records current and step() copies them
   }
   int rc = synchronize(); if (rc) return rc;
   *records = hBodyRead_; *count = d_.bodyCapacity;

@@ -330,6 +330,31 @@ int32_t b2cuda_world_get_counters(B2CWorld* world, B2CCounters* out);
    order-independent checksums of the device state between the phases of the last step (scripts/gpu_determinism.py). */
 int32_t b2cuda_world_debug_checksums(B2CWorld* world, uint64_t* out16);
 int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);   /* averages over the steps since the previous call (<= 64) */
+/* ---- Batches of independent worlds (new; the reference's counterpart is the remark "Each world is completely independent and may be
+ * simulated in parallel", api/World.cs:9-10, and a loop over WorldAPI.Step). One handle owns `worldCount` worlds on one device and steps
+ * them in lockstep with ONE kernel launch: a thread block per world runs the whole step (pairs, collide, colouring, solver, finalize)
+ * with block-local barriers, so world k of a batch is bit-identical to the same world stepped alone with b2cuda_world_step.
+ *   b2cuda_batch_world   the handle of world `index`: build it (and read it back, and mutate it between steps) with the ordinary
+ *                        b2cuda_create_* / b2cuda_world_read_* / event entry points. b2cuda_world_step and b2cuda_world_destroy are
+ *                        refused on such a handle. Device rows do not grow inside a batch: reserve rows for bodies created after the
+ *                        first step with B2CWorldDef.bodyCapacity / shapeCapacity / jointCapacity / contactCapacity.
+ *   b2cuda_batch_step    WorldAPI.Step for every world; asynchronous on the batch's stream. Step parameters (gravity, contact tuning,
+ *                        thresholds, continuous / warm-starting switches) are those of the B2CWorldDef given to b2cuda_batch_create.
+ *   b2cuda_batch_reset_world  puts one world back into the state it had at the first b2cuda_batch_step (bodies, contacts, ids, trees).
+ *   b2cuda_batch_stats   statistics reduced over all worlds ON THE DEVICE; `deviceDst` (may be NULL) receives the same 8 doubles in device
+ *                        memory on the batch's stream, ready for ncclAllReduce: [bodies, sum |v|^2, touching contacts, begin events,
+ *                        end events] are sums, [max |v|] a maximum, [min y] a minimum, [error flags] an OR kept as a double. */
+typedef struct B2CBatch B2CBatch;
+typedef struct B2CBatchStats { double awakeBodies, sumV2, touchingContacts, beginEvents, endEvents, maxSpeed, minY, errorFlags; } B2CBatchStats;
+int32_t b2cuda_batch_create(const B2CWorldDef* def, int32_t device, int32_t worldCount, B2CBatch** out);
+int32_t b2cuda_batch_destroy(B2CBatch* batch);
+int32_t b2cuda_batch_world(B2CBatch* batch, int32_t index, B2CWorld** world);
+int32_t b2cuda_batch_step(B2CBatch* batch, float timeStep, int32_t subStepCount);
+int32_t b2cuda_batch_synchronize(B2CBatch* batch);
+int32_t b2cuda_batch_reset_world(B2CBatch* batch, int32_t index);
+int32_t b2cuda_batch_stats(B2CBatch* batch, B2CBatchStats* out, double* deviceDst);
+int32_t b2cuda_batch_timer_start(B2CBatch* batch);
+int32_t b2cuda_batch_timer_stop(B2CBatch* batch, float* elapsedMs);
 /* (new, no reference counterpart) one CUDA-graph launch per step instead of one launch per kernel. The kernels then run back to back whatever
  * the host's launch latency is - use it when several processes drive GPUs from one host (bench.py does for world_size > 1) or when
  * steps are enqueued without reading results in between. Costs ~7 us of start latency per step, hence off by default (B2CUDA_GRAPH=1 also enables). */
