@@ -8,6 +8,7 @@ Names and argument meaning follow the C# facade (api/World.cs, api/Body.cs, api/
 ``World`` is backend-agnostic: it is handed a bound function table (see capi.bind). ``CudaBackend`` binds the
 product library; the oracle is bound only by tests/ (never from this package).
 """
+import os
 import ctypes as C
 import numpy as np
 from . import capi
@@ -120,7 +121,12 @@ def CudaBackend(device=0):
     fns = capi.bind(lib, "b2cuda_")
     extra = {}
     for name, (args, res) in capi.PRODUCT_ONLY.items():
-        f = getattr(lib, "b2cuda_" + name)
+        try:
+            f = getattr(lib, "b2cuda_" + name)
+        except AttributeError:
+            if os.environ.get("B2CUDA_LIB"):      # A/B run against an older build of the library: newer entry points are simply absent
+                continue
+            raise
         f.argtypes, f.restype = args, res
         extra[name] = f
     fns.update(extra)

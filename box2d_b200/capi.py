@@ -249,6 +249,8 @@ def bind(lib, prefix):
 
 
 def product_library_path():
+    if os.environ.get("B2CUDA_LIB"):              # A/B runs of two builds of the library (scripts/ab_phases.py); still the CUDA library, never a fallback
+        return os.environ["B2CUDA_LIB"]
     return os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libb2cuda.so")
 
 

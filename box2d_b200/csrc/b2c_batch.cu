@@ -9,7 +9,7 @@ namespace b2c {
 
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(B2C_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
-cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, cudaStream_t stream);
+cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, int* maxIslandConsDev, int maxIslandConsSeen, cudaStream_t stream);
 cudaError_t launchBatchZeroStep(const WorldDev* worlds, int worldCount, int newEndIndex, cudaStream_t stream);
 cudaError_t launchBatchStats(const WorldDev* worlds, int worldCount, int lastEndIndex, double* out, unsigned int* errOr, cudaStream_t stream);
 
@@ -30,6 +30,9 @@ int Batch::init() {
   for (auto& e : timer_) CK(cudaEventCreate(&e));
   CK(cudaHostAlloc((void**)&mappedInt_, sizeof(int), cudaHostAllocMapped));
   CK(cudaHostGetDevicePointer((void**)&mappedIntDev_, mappedInt_, 0));
+  CK(cudaHostAlloc((void**)&maxCons_, sizeof(int), cudaHostAllocMapped));
+  *maxCons_ = 0;
+  CK(cudaHostGetDevicePointer((void**)&maxConsDev_, maxCons_, 0));
   CK(cudaMalloc((void**)&dStats_, sizeof(double) * 10));
   CK(cudaMemsetAsync(dStats_, 0, sizeof(double) * 10, stream_));
   CK(cudaHostAlloc((void**)&hStats_, sizeof(double) * 8, cudaHostAllocDefault));
@@ -50,6 +53,7 @@ Batch::~Batch() {
   if (dStats_) cudaFree(dStats_);
   if (hStats_) cudaFreeHost(hStats_);
   if (mappedInt_) cudaFreeHost(mappedInt_);
+  if (maxCons_) cudaFreeHost(maxCons_);
   for (auto& e : timer_) if (e) cudaEventDestroy(e);
   if (stream_) cudaStreamDestroy(stream_);
 }
@@ -163,7 +167,7 @@ int Batch::step(float timeStep, int subStepCount) {
     sp.enableWarmStarting = w0.enableWarmStarting; sp.enableContactSoftening = w0.enableContactSoftening; sp.enableContinuous = w0.enableContinuous;
     sp.enableSpeculative = w0.enableSpeculative; sp.enableSleep = 0; sp.endIndex = lastEnd;
     sp.clusterThreads = 0;
-    CK(launchBatchStep(dWorlds_, n, sp, endIndex_, stream_));
+    CK(launchBatchStep(dWorlds_, n, sp, endIndex_, maxConsDev_, *(volatile int*)maxCons_, stream_));   // the maximum may lag the running step: either CTA width is correct
   }
   const bool zero = timeStep == 0.0f;
   for (World* w : worlds_) {                       // per-world host bookkeeping of World::step

@@ -1841,6 +1841,17 @@ int World::getJointEvents(const int** ids, int* count) {
 
 int World::getProfile(B2CProfile* out) {       // averages over the steps since the previous call (events: at most kProfRing steps)
   memset(out, 0, sizeof(*out));
+  if (batch_) {                                // batch member: %globaltimer sums of this world's CTA (k_batch_step), no CUDA events
+    if (!onDevice_) return B2C_OK;
+    int rc = synchronize(); if (rc) return rc;
+    double ph[8]; const int n = stepCount_ - lastProfStep_ > 0 ? stepCount_ - lastProfStep_ : 1;
+    for (int k = 0; k < 8; k++) { ph[k] = (double)(hostScalars_->phaseAcc[k] - lastPhaseAcc_[k]) * 1e-6 / n; lastPhaseAcc_[k] = hostScalars_->phaseAcc[k]; }
+    lastProfStep_ = stepCount_;
+    out->pairs = (float)ph[0]; out->collide = (float)ph[1]; out->treeRebuild = (float)ph[4]; out->prepareConstraints = (float)ph[2];
+    out->solveConstraints = (float)(ph[3] + ph[5]); out->transforms = (float)ph[6]; out->refit = out->transforms;
+    out->solve = out->prepareConstraints + out->solveConstraints + out->transforms; out->step = (float)(ph[0] + ph[1] + ph[2] + ph[3] + ph[5] + ph[6]);
+    return B2C_OK;
+  }
   if (!onDevice_ || profCount_ == 0) return B2C_OK;
   int rc = synchronize(); if (rc) return rc;
   for (auto& g : graphs_) harvestGraph(g);

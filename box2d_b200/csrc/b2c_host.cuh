@@ -193,7 +193,7 @@ class World {
   static constexpr int kProfRing = 64, kProfEvents = 6;
   cudaEvent_t ev_[kProfRing * kProfEvents] = {};
   cudaEvent_t timer_[2] = {};
-  int profHead_ = 0, profCount_ = 0;
+  int profHead_ = 0, profCount_ = 0, lastProfStep_ = 0;
   // One CUDA graph per distinct step configuration (parameters, end-event buffer parity, solver variant, streamed read-backs): a step is
   // then ONE launch, so the kernels run back to back whatever the host's launch latency is (matters with 8 ranks on one host).
   struct StepGraph { std::vector<unsigned char> key; cudaGraphExec_t exec = nullptr; cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr}; bool pending = false; };
@@ -252,6 +252,7 @@ class Batch {
   struct Snap { World::HostSnap host; char* dev = nullptr; size_t bytes = 0; };   // state at the first step, for resetWorld
   std::vector<Snap> snaps_; std::vector<void*> snapChunks_;
   int* mappedInt_ = nullptr; int* mappedIntDev_ = nullptr;
+  int* maxCons_ = nullptr; int* maxConsDev_ = nullptr;     // running maximum of an island's constraint count, kept by k_batch_step (mapped host int)
   int endIndex_ = 0, stepCount_ = 0;
   double* dStats_ = nullptr; double* hStats_ = nullptr;
   cudaEvent_t timer_[2] = {nullptr, nullptr};

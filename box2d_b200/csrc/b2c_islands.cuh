@@ -293,7 +293,7 @@ template <bool CACHED> __device__ void runIsland(const WorldDev& d, const StepPa
 namespace b2c {
 
 // skipWarpEligible: this step's small islands are solved by k_solver_islands_warp; only the ones that do not fit a slice stay here
-__global__ void __launch_bounds__(kIslandThreads, 3) k_solver_islands(WorldDev d, StepParams sp, int skipWarpEligible) {
+__global__ void __launch_bounds__(kIslandThreads, 3) k_solver_islands(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp, int skipWarpEligible) {
   __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
   __shared__ int colorOff[kGraphColorCount + 1 + 2 * kGraphColorCount];   // colour offsets, then (begin, end) of the active colours
   int n = d.sc->islandCount;

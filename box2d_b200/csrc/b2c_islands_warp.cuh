@@ -37,7 +37,7 @@ __device__ __forceinline__ void sliceLoadLane(const WarpIslandSlice& sl, int t, 
   c.baseSep1 = H.x; c.baseSep2 = H.y; c.relVel1 = H.z; c.relVel2 = H.w;
 }
 
-__global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_warp(WorldDev d, StepParams sp) {
+__global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_warp(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp) {
   extern __shared__ __align__(16) unsigned char smemRaw[];
   WarpIslandSlice& sl = reinterpret_cast<WarpIslandSlice*>(smemRaw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;

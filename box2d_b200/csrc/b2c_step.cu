@@ -1557,14 +1557,14 @@ template <class S> __device__ void stepFront(const S& grid, const WorldDev& d, c
   if (d.debugChecksums == 1) { grid.sync(); dbgBodies(d, 5); dbgLanes(d, 6, false); dbgContacts(d, 7); }
   if (grid.tid() == 0) { for (int k = 0; k < 4; k++) s.phaseAcc[k] += s.phaseStamp[k + 1] - s.phaseStamp[k]; s.phaseAcc[4] += s.phaseStamp[5] - s.phaseStamp[1]; }
 }
-__global__ void __launch_bounds__(kCoopThreads) k_step_front(WorldDev d, StepParams sp) {
+__global__ void __launch_bounds__(kCoopThreads) k_step_front(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp) {
   cg::grid_group g = cg::this_grid();
   GridScope grid{g};
   stepFront(grid, d, sp);
 }
 
 // The grid-path solver on one thread-block cluster (see clusterPath in stepFront). All CTAs of the cluster take the same path.
-__global__ void __launch_bounds__(kCoopThreads) k_solver_cluster(WorldDev d, StepParams sp) {
+__global__ void __launch_bounds__(kCoopThreads) k_solver_cluster(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp) {
   const Scalars& s = *d.sc;
   if (!s.clusterSolve) return;
   ClusterScope cs;
@@ -1592,7 +1592,7 @@ template <class S> __device__ void finalizePhase(const S& grid, const WorldDev& 
   } else if (tid == 0) s.moveCount = 0;
   if (tid == 0) { s.enlargedShapeCount = 0; p_step_finish(d, newEndIndex); }
 }
-__global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, StepParams sp, int newEndIndex) {
+__global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp, int newEndIndex) {
   cg::grid_group g = cg::this_grid();
   GridScope grid{g};
   finalizePhase(grid, d, sp, newEndIndex);
@@ -1604,8 +1604,8 @@ __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(WorldDev d, Ste
 // synchronisation anywhere), then its islands with the CTA island solver, then FinalizeBodies/refit. World index = blockIdx.x; each
 // world has its own arrays, id pools, trees and colour graph, so world k of a batch is bit-identical to the same world stepped alone.
 // ------------------------------------------------------------------------------------------------------------
-constexpr int kBatchThreads = 256;
-__global__ void __launch_bounds__(kBatchThreads, 2) k_batch_step(const WorldDev* __restrict__ worlds, StepParams sp, int newEndIndex) {
+template <int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_batch_step(const WorldDev* __restrict__ worlds, StepParams sp, int newEndIndex, int* __restrict__ maxIslandCons) {
   __shared__ __align__(16) unsigned char sdRaw[sizeof(WorldDev)];
   __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
   __shared__ int colorOff[kGraphColorCount + 1 + 2 * kGraphColorCount];
@@ -1622,12 +1622,16 @@ __global__ void __launch_bounds__(kBatchThreads, 2) k_batch_step(const WorldDev*
   const int n = d.sc->islandCount;
   for (int g = 0; g < n; g++) {
     int K = d.islandColorOff[g * (kGraphColorCount + 1) + kGraphColorCount];
+    if (threadIdx.x == 0 && K > *maxIslandCons) atomicMax(maxIslandCons, K);   // the host sizes the next launches' CTAs by it (lanes stay in registers while K <= blockDim)
     if (K <= (int)blockDim.x) runIsland<true>(d, sp, g, s0, s1, colorOff);
     else runIsland<false>(d, sp, g, s0, s1, colorOff);
   }
   freeBodies(d, sp, threadIdx.x, blockDim.x);
   __syncthreads();
+  unsigned long long t6 = 0;
+  if (threadIdx.x == 0) t6 = globalTimer();
   finalizePhase(cta, d, sp, newEndIndex);
+  if (threadIdx.x == 0) { Scalars& s = *d.sc; s.phaseAcc[5] += t6 - s.phaseStamp[4]; s.phaseAcc[6] += globalTimer() - t6; }
 }
 
 // bodyMoveEvents equivalent: one packed record per body id (src/Solver.cs:432-438)
@@ -1830,8 +1834,14 @@ int World::getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count) {
 }
 
 // One launch steps every world of a batch (b2c_batch.cu drives it)
-cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, cudaStream_t stream) {
-  k_batch_step<<<worldCount, kBatchThreads, 0, stream>>>(worlds, sp, newEndIndex);
+// CTA width: 160 threads at 96 registers (4 worlds per SM) while every island's constraints fit 160 register lanes, else 256 threads
+// (2 worlds per SM). Measured on 8192 10-row pyramids (145 constraints each): 0.97 ms against 1.49 ms per step; narrower CTAs at
+// 80 / 72 / 64 registers spill and lose (1.14 - 1.17 ms). `maxIslandCons` is a mapped host int the kernel keeps a running maximum in.
+cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, int* maxIslandConsDev, int maxIslandConsSeen, cudaStream_t stream) {
+  static int forced = getenv("B2CUDA_BATCH_THREADS") ? atoi(getenv("B2CUDA_BATCH_THREADS")) : 0;
+  const bool narrow = forced ? forced == 160 : (maxIslandConsSeen > 0 && maxIslandConsSeen <= 160);
+  if (narrow) k_batch_step<160, 4><<<worldCount, 160, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
+  else k_batch_step<256, 2><<<worldCount, 256, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
   return cudaGetLastError();
 }
 __global__ void k_batch_zero_step(const WorldDev* worlds, int newEndIndex) { Scalars& s = *worlds[blockIdx.x].sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; }

@@ -23,13 +23,18 @@ first_s = time.perf_counter() - t0
 for _ in range(a.warmup):
     b.Step(1 / 60, 4)
 b.Synchronize()
+b.worlds[0].GetProfile(); b.worlds[a.worlds // 2].GetProfile()
 b.TimerStart()
 for _ in range(a.steps):
     b.Step(1 / 60, 4)
 ms = b.TimerStop()
+prof = []
+for k in (0, a.worlds // 2):
+    p = b.worlds[k].GetProfile()
+    prof.append({f: round(getattr(p, f) * 1000, 2) for f in ("pairs", "collide", "treeRebuild", "prepareConstraints", "solveConstraints", "transforms", "step")})
 s = b.Stats()
 bodies = s.awakeBodies
 print(json.dumps({"worlds": a.worlds, "rows": a.rows, "ms_per_step": ms / a.steps, "world_steps_per_s": a.worlds * a.steps / (ms * 1e-3),
                   "body_substeps_per_s": bodies * 4 * a.steps / (ms * 1e-3), "build_s": build_s, "first_step_s": first_s,
-                  "touching": s.touchingContacts, "errorFlags": s.errorFlags}))
+                  "touching": s.touchingContacts, "cta_phase_us": prof, "errorFlags": s.errorFlags}))
 b.Destroy()

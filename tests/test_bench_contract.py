@@ -29,7 +29,7 @@ def test_reference_arm_line():
 
 @pytest.mark.gpu
 def test_b200_arm_line():
-    d = _run(["--steps", "8", "--warmup", "3", "--cpu-steps", "3"], 900)
+    d = _run(["--steps", "8", "--warmup", "3", "--cpu-steps", "3", "--worlds", "256"], 900)
     for k in COMMON + ("roofline", "cpu_baseline", "clocks"):
         assert k in d, k
     r = d["roofline"]
@@ -40,3 +40,7 @@ def test_b200_arm_line():
     assert d["e2e"]["d2h_bytes_per_step"] > 0 and d["gpu_launches"] >= 3 * d["steps"]
     assert set(("sm_mhz", "sm_max_mhz", "reasons")) <= set(d["clocks"])
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] == 1
+    b = d["batched"]                               # BASELINE.json configs[4] beside the headline
+    assert b["worlds"] == 256 and b["worlds_per_gpu"] == 256 and b["scaling"] == "strong" and b["world_steps_per_s"] > 0
+    assert b["stats"]["awake_bodies"] == 256 * 55
+    assert d["roofline"]["traffic"] is None or d["roofline"]["traffic"] > 0
