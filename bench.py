@@ -159,8 +159,10 @@ def batched_record(args, rank, world_size, local_rank, dist, barrier):
     b0, b1 = batch.shard_range(args.worlds, rank, world_size)
     n = b1 - b0
     bt = api.Batch(api.CudaBackend(device=local_rank), n, scenes.world_def())
+    rec = api.Snapshot()                                                   # one recorded 10-row pyramid, replayed into every world by ONE C-ABI call each
+    scenes.add_pyramid(rec, 10)
     for w in bt.worlds:
-        scenes.add_pyramid(w, 10)
+        rec.upload(w)
     K, W = args.steps, max(args.warmup, 3)
     for _ in range(W):
         bt.Step(DT, SUBSTEPS)

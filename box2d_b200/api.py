@@ -346,6 +346,37 @@ class World:
     def JointSetLimits(self, joint_id, lower, upper):
         self._check(self.fns["joint_set_limits"](self.handle, joint_id, lower, upper))
 
+    def SetLocalFrameA(self, joint_id, frame):          # JointAPI.SetLocalFrameA api/Joint.cs:44
+        self._check(self.fns["joint_set_local_frame"](self.handle, joint_id, 0, frame))
+
+    def SetLocalFrameB(self, joint_id, frame):          # JointAPI.SetLocalFrameB api/Joint.cs:50
+        self._check(self.fns["joint_set_local_frame"](self.handle, joint_id, 1, frame))
+
+    def SetCollideConnected(self, joint_id, should_collide):   # JointAPI.SetCollideConnected api/Joint.cs:56
+        self._check(self.fns["joint_set_collide_connected"](self.handle, joint_id, int(bool(should_collide))))
+
+    # BodyAPI sleep / enable / bullet surface (api/Body.cs:664-842)
+    def SetSleepThreshold(self, body_id, v):
+        self._check(self.fns["body_set_sleep_threshold"](self.handle, body_id, v))
+
+    def EnableSleep(self, body_id, flag):
+        self._check(self.fns["body_enable_sleep"](self.handle, body_id, int(bool(flag))))
+
+    def SetAwake(self, body_id, awake):
+        self._check(self.fns["body_set_awake"](self.handle, body_id, int(bool(awake))))
+
+    def WakeTouching(self, body_id):
+        self._check(self.fns["body_wake_touching"](self.handle, body_id))
+
+    def DisableBody(self, body_id):
+        self._check(self.fns["body_disable"](self.handle, body_id))
+
+    def EnableBody(self, body_id):
+        self._check(self.fns["body_enable"](self.handle, body_id))
+
+    def SetBullet(self, body_id, flag):
+        self._check(self.fns["body_set_bullet"](self.handle, body_id, int(bool(flag))))
+
     def SetConstraintTuning(self, joint_id, hertz, damping_ratio):
         self.JointSetParam(joint_id, capi.JP_CONSTRAINT_HERTZ, hertz)
         self.JointSetParam(joint_id, capi.JP_CONSTRAINT_DAMPING_RATIO, damping_ratio)
@@ -481,6 +512,60 @@ class World:
 
     def ReadShapes(self):
         return self._read("world_read_shapes", ShapeRead, self.GetCounters().shapeCount + 16)
+
+
+class Snapshot:
+    """Records CreateBody / CreateShape / CreateJoint calls (ids returned are ORDINALS inside the recording) and replays them into a world
+    with ONE b2cuda_world_upload_snapshot call; a recording can be uploaded into any number of worlds (batched worlds of one topology)."""
+
+    def __init__(self):
+        self.parts, self.n_ops, self.n_bodies, self.n_shapes, self.n_joints = [], 0, 0, 0, 0
+        self._blob = None
+
+    def _rec(self, kind, ref, *payload):
+        self.parts.append(bytes((C.c_int32 * 2)(kind, ref)) + b"".join(bytes(p) for p in payload))
+        self.n_ops += 1
+        self._blob = None
+
+    def CreateBody(self, body_def):
+        self._rec(0, 0, body_def)
+        self.n_bodies += 1
+        return self.n_bodies - 1
+
+    def CreateShape(self, body, shape_def, geometry):
+        self._rec(1, body, shape_def, geometry)
+        self.n_shapes += 1
+        return self.n_shapes - 1
+
+    CreatePolygonShape = CreateCircleShape = CreateCapsuleShape = CreateSegmentShape = CreateShape
+
+    def CreateJoint(self, joint_def):
+        self._rec(2, 0, joint_def)
+        self.n_joints += 1
+        return self.n_joints - 1
+
+    def CreateRevoluteJoint(self, r):
+        """api/Joint.cs:555: the revolute definition goes down the generic joint path (as b2cuda_create_revolute_joint does)"""
+        d = JointDef()
+        d.type = capi.JOINT_REVOLUTE
+        for f in ("bodyIdA", "bodyIdB", "localFrameA", "localFrameB", "forceThreshold", "torqueThreshold", "constraintHertz", "constraintDampingRatio",
+                  "drawScale", "collideConnected", "userData", "enableSpring", "enableLimit", "enableMotor", "hertz", "dampingRatio", "motorSpeed"):
+            setattr(d, f, getattr(r, f))
+        d.target, d.lower, d.upper, d.maxMotor = r.targetAngle, r.lowerAngle, r.upperAngle, r.maxMotorTorque
+        return self.CreateJoint(d)
+
+    def blob(self):
+        if self._blob is None:
+            hd = capi.SnapshotHeader(capi.SNAPSHOT_MAGIC, 1, self.n_ops, self.n_bodies, self.n_shapes, self.n_joints)
+            self._blob = bytes(hd) + b"".join(self.parts)
+        return self._blob
+
+    def upload(self, world):
+        """Returns (body ids, shape ids, joint ids) as the world assigned them, in recording order."""
+        data = self.blob()
+        b, s, j = (C.c_int32 * max(self.n_bodies, 1))(), (C.c_int32 * max(self.n_shapes, 1))(), (C.c_int32 * max(self.n_joints, 1))()
+        world._check(world.fns["world_upload_snapshot"](world.handle, data, len(data), b, s, j))
+        return list(b)[:self.n_bodies], list(s)[:self.n_shapes], list(j)[:self.n_joints]
 
 
 class Batch:

@@ -160,6 +160,8 @@ PROTOS = {
     "joint_set_param": [_W, C.c_int32, C.c_int32, C.c_float],
     "joint_enable": [_W, C.c_int32, C.c_int32, C.c_int32],
     "joint_set_limits": [_W, C.c_int32, C.c_float, C.c_float],
+    "joint_set_local_frame": [_W, C.c_int32, C.c_int32, Transform],
+    "joint_set_collide_connected": [_W, C.c_int32, C.c_int32],
     "body_set_transform": [_W, C.c_int32, Vec2, Rot],
     "body_set_linear_velocity": [_W, C.c_int32, Vec2],
     "body_set_target_transform": [_W, C.c_int32, Transform, C.c_float],
@@ -233,6 +235,21 @@ PRODUCT_ONLY.update({
     "batch_stats": ([_B, C.POINTER(BatchStats), C.c_void_p], C.c_int32),
     "batch_timer_start": ([_B], C.c_int32),
     "batch_timer_stop": ([_B, C.POINTER(C.c_float)], C.c_int32),
+})
+class SnapshotHeader(C.Structure):
+    _fields_ = [("magic", C.c_uint32), ("version", C.c_uint32), ("opCount", C.c_int32), ("bodyCount", C.c_int32), ("shapeCount", C.c_int32), ("jointCount", C.c_int32)]
+
+
+SNAPSHOT_MAGIC = 0x42324353
+PRODUCT_ONLY["world_upload_snapshot"] = ([_W, C.c_void_p, C.c_size_t, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)], C.c_int32)
+PRODUCT_ONLY.update({
+    "body_set_sleep_threshold": ([_W, C.c_int32, C.c_float], C.c_int32),
+    "body_enable_sleep": ([_W, C.c_int32, C.c_int32], C.c_int32),
+    "body_set_awake": ([_W, C.c_int32, C.c_int32], C.c_int32),
+    "body_wake_touching": ([_W, C.c_int32], C.c_int32),
+    "body_disable": ([_W, C.c_int32], C.c_int32),
+    "body_enable": ([_W, C.c_int32], C.c_int32),
+    "body_set_bullet": ([_W, C.c_int32, C.c_int32], C.c_int32),
 })
 NOALLOC_MAX_MOVE_EVENTS = 65536     # B2C_NOALLOC_MAX_MOVE_EVENTS
 

@@ -151,6 +151,52 @@ int32_t b2cuda_world_enable_graph_launch(B2CWorld* h, int32_t flag) { CHECK_HAND
 int32_t b2cuda_world_timer_start(B2CWorld* h) { CHECK_HANDLE(h); return done(h, h->w->timerStart()); }
 int32_t b2cuda_world_timer_stop(B2CWorld* h, float* ms) { CHECK_HANDLE(h); if (!ms) return B2C_E_INVALID; return done(h, h->w->timerStop(ms)); }
 
+int32_t b2cuda_joint_set_local_frame(B2CWorld* h, int32_t id, int32_t which, B2CTransform f) { CHECK_HANDLE(h); return done(h, h->w->jointSetLocalFrame(id, which, mkXf(mk(f.p.x, f.p.y), mkRot(f.q.c, f.q.s)))); }
+int32_t b2cuda_joint_set_collide_connected(B2CWorld* h, int32_t id, int32_t flag) { CHECK_HANDLE(h); return done(h, h->w->jointSetCollideConnected(id, flag != 0)); }
+int32_t b2cuda_body_set_sleep_threshold(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->bodySetSleepThreshold(id, v)); }
+int32_t b2cuda_body_enable_sleep(B2CWorld* h, int32_t id, int32_t flag) { CHECK_HANDLE(h); return done(h, h->w->bodyEnableSleep(id, flag != 0)); }
+int32_t b2cuda_body_set_awake(B2CWorld* h, int32_t id, int32_t awake) { CHECK_HANDLE(h); return done(h, h->w->bodySetAwake(id, awake != 0)); }
+int32_t b2cuda_body_wake_touching(B2CWorld* h, int32_t id) { CHECK_HANDLE(h); return done(h, h->w->bodyWakeTouching(id)); }
+int32_t b2cuda_body_disable(B2CWorld* h, int32_t id) { CHECK_HANDLE(h); return done(h, h->w->bodySetEnabled(id, false)); }
+int32_t b2cuda_body_enable(B2CWorld* h, int32_t id) { CHECK_HANDLE(h); return done(h, h->w->bodySetEnabled(id, true)); }
+int32_t b2cuda_body_set_bullet(B2CWorld* h, int32_t id, int32_t flag) { CHECK_HANDLE(h); return done(h, h->w->bodySetBullet(id, flag != 0)); }
+int32_t b2cuda_world_upload_snapshot(B2CWorld* h, const void* blob, size_t bytes, int32_t* bodyIds, int32_t* shapeIds, int32_t* jointIds) {
+  CHECK_HANDLE(h);
+  const unsigned char* p = (const unsigned char*)blob; const unsigned char* end = p + bytes;
+  B2CSnapshotHeader hd;
+  if (!blob || bytes < sizeof(hd)) { g_lastError = "snapshot blob is null or shorter than its header"; return B2C_E_INVALID; }
+  memcpy(&hd, p, sizeof(hd)); p += sizeof(hd);
+  if (hd.magic != B2C_SNAPSHOT_MAGIC || hd.version != 1u || hd.opCount < 0) { g_lastError = "snapshot blob: bad magic / version"; return B2C_E_INVALID; }
+  std::vector<int32_t> bodyOf; bodyOf.reserve(hd.bodyCount > 0 ? hd.bodyCount : 0);
+  int nb = 0, ns = 0, nj = 0;
+  for (int i = 0; i < hd.opCount; i++) {
+    int32_t rec[2];
+    if ((size_t)(end - p) < sizeof(rec)) { g_lastError = "snapshot blob truncated"; return B2C_E_INVALID; }
+    memcpy(rec, p, sizeof(rec)); p += sizeof(rec);
+    int rc = B2C_OK;
+    if (rec[0] == 0) {
+      B2CBodyDef def; if ((size_t)(end - p) < sizeof(def)) { g_lastError = "snapshot blob truncated"; return B2C_E_INVALID; }
+      memcpy(&def, p, sizeof(def)); p += sizeof(def);
+      int32_t id = -1; rc = h->w->createBody(def, &id);
+      if (rc == B2C_OK) { bodyOf.push_back(id); if (bodyIds) bodyIds[nb] = id; nb++; }
+    } else if (rec[0] == 1) {
+      B2CShapeDef def; B2CGeometry g; if ((size_t)(end - p) < sizeof(def) + sizeof(g)) { g_lastError = "snapshot blob truncated"; return B2C_E_INVALID; }
+      memcpy(&def, p, sizeof(def)); p += sizeof(def); memcpy(&g, p, sizeof(g)); p += sizeof(g);
+      if (rec[1] < 0 || rec[1] >= (int)bodyOf.size()) { g_lastError = "snapshot blob: shape refers to a body ordinal that has not been created"; return B2C_E_INVALID; }
+      int32_t id = -1; rc = h->w->createShape(bodyOf[rec[1]], def, g, &id);
+      if (rc == B2C_OK) { if (shapeIds) shapeIds[ns] = id; ns++; }
+    } else if (rec[0] == 2) {
+      B2CJointDef def; if ((size_t)(end - p) < sizeof(def)) { g_lastError = "snapshot blob truncated"; return B2C_E_INVALID; }
+      memcpy(&def, p, sizeof(def)); p += sizeof(def);
+      if (def.bodyIdA < 0 || def.bodyIdA >= (int)bodyOf.size() || def.bodyIdB < 0 || def.bodyIdB >= (int)bodyOf.size()) { g_lastError = "snapshot blob: joint refers to a body ordinal that has not been created"; return B2C_E_INVALID; }
+      def.bodyIdA = bodyOf[def.bodyIdA]; def.bodyIdB = bodyOf[def.bodyIdB];
+      int32_t id = -1; rc = h->w->createJoint(def, &id);
+      if (rc == B2C_OK) { if (jointIds) jointIds[nj] = id; nj++; }
+    } else { g_lastError = "snapshot blob: unknown record kind"; return B2C_E_INVALID; }
+    if (rc != B2C_OK) return done(h, rc);
+  }
+  return done(h, B2C_OK);
+}
 // ---- batches of independent worlds (b2c_batch.cu) ----
 }  // extern "C"
 #include <vector>

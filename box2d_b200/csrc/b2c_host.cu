@@ -942,6 +942,109 @@ int World::jointOp(int jointId, int patch, int which, float a, float b) {
   return B2C_OK;
 }
 
+// JointAPI.SetLocalFrameA/B api/Joint.cs:44,50: a plain store into the joint sim (no wake, no impulse reset)
+__global__ void k_joint_frame(WorldDev d, int jointId, int which, Xf f) { if (which) d.joints[jointId].localFrameB = f; else d.joints[jointId].localFrameA = f; }
+int World::jointSetLocalFrame(int jointId, int which, Xf frame) {
+  if (jointId < 0 || jointId >= (int)joints_.size() || joints_[jointId].id != jointId) return fail(B2C_E_INVALID, "bad joint id");
+  if (which != 0 && which != 1) return fail(B2C_E_INVALID, "frame selector must be 0 (A) or 1 (B)");
+  JointDev& s = joints_[jointId].sim;
+  if (which) s.localFrameB = frame; else s.localFrameA = frame;      // the host record is the upload source and the read-back of parked joints
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_joint_frame<<<1, 1, 0, stream_>>>(d_, jointId, which, frame);
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
+// JointAPI.SetCollideConnected api/Joint.cs:56-75: on -> BufferMove for the shapes of the body with fewer shapes (pairs are found by the
+// next UpdateBroadPhasePairs); off -> DestroyContactsBetweenBodies, in contact-list order as at joint creation.
+__global__ void k_joint_collide(WorldDev d, int jointId, int flag, int bodyIdA, int bodyIdB, int moveBody, int endIndex) {
+  __shared__ int sCount;
+  Scalars& s = *d.sc;
+  if (threadIdx.x == 0) { sCount = 0; d.jointCollide[jointId] = flag; }
+  __syncthreads();
+  if (flag) {
+    if (threadIdx.x != 0) return;
+    for (int sid = d.bodyHeadShape[moveBody]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+      int key = d.shapes[sid].proxyKey;
+      if (key == -1) continue;
+      const TreeDev& t = d.trees[key & 3];
+      if (t.moved[key >> 2]) continue;
+      if (s.moveCount < d.moveCapacity) { t.moved[key >> 2] = 1; d.moveArray[s.moveCount++] = key; } else s.errorFlags |= (int)ERR_PAIR_CAPACITY;
+    }
+    return;
+  }
+  const int n = s.contactNext;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (!(d.cFlags[i] & CF_ALIVE)) continue;
+    int2 cb = d.cBody[i];
+    if ((cb.x == bodyIdA && cb.y == bodyIdB) || (cb.x == bodyIdB && cb.y == bodyIdA)) { int k = atomicAdd(&sCount, 1); d.opList[k] = i; }
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const int count = sCount;
+  for (int i = 1; i < count; i++) {              // newest first = the order of either body's contact list
+    int id = d.opList[i]; uint32_t st = d.cStamp[id]; int j = i - 1;
+    while (j >= 0 && d.cStamp[d.opList[j]] < st) { d.opList[j + 1] = d.opList[j]; j--; }
+    d.opList[j + 1] = id;
+  }
+  for (int i = 0; i < count; i++) destroyContactSerial(d, d.opList[i], endIndex);
+}
+int World::jointSetCollideConnected(int jointId, bool shouldCollide) {
+  if (jointId < 0 || jointId >= (int)joints_.size() || joints_[jointId].id != jointId) return fail(B2C_E_INVALID, "bad joint id");
+  HJoint& j = joints_[jointId];
+  if (j.collideConnected == shouldCollide) return B2C_OK;
+  j.collideConnected = shouldCollide;
+  const HBody& a = bodies_[j.bodyIdA]; const HBody& b = bodies_[j.bodyIdB];
+  const int moveBody = a.shapeCount < b.shapeCount ? j.bodyIdA : j.bodyIdB;
+  if (!onDevice_) {                               // no contacts exist before the first step
+    if (shouldCollide) for (int sid = bodies_[moveBody].headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) if (shapes_[sid].proxyKey != -1) bufferMove(shapes_[sid].proxyKey);
+    return B2C_OK;
+  }
+  CK(cudaSetDevice(device_));
+  k_joint_collide<<<1, 256, 0, stream_>>>(d_, jointId, shouldCollide ? 1 : 0, j.bodyIdA, j.bodyIdB, moveBody, endIndex_);
+  CK(cudaGetLastError());
+  eventsFetched_ = false;
+  return B2C_OK;
+}
+
+// BodyAPI sleep surface (api/Body.cs:664-716) while islands / sleep are not built: every body outside the static set is awake and stays
+// awake, so the calls that only wake (SetAwake(true), WakeTouching, EnableSleep(false)) have nothing to do, the stores are kept for
+// read-back, and the one call that would put an island to sleep is refused.
+__global__ void k_body_sleep_threshold(WorldDev d, int bodyId, float v) { d.bodySleepThreshold[bodyId] = v; }
+int World::bodySetSleepThreshold(int bodyId, float v) {               // api/Body.cs:712
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  bodies_[bodyId].sleepThreshold = v;
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_body_sleep_threshold<<<1, 1, 0, stream_>>>(d_, bodyId, v);
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
+int World::bodyEnableSleep(int bodyId, bool flag) {                   // api/Body.cs:700-706 (WakeBody finds the body awake)
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  bodies_[bodyId].enableSleep = flag;
+  return B2C_OK;
+}
+int World::bodySetAwake(int bodyId, bool awake) {                     // api/Body.cs:668-679
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  if (awake || bodies_[bodyId].simIndex < 0) return B2C_OK;           // already awake / a static-set body: the reference does nothing
+  return fail(B2C_E_UNSUPPORTED, "SetAwake(false) puts the body's island to sleep (TrySleepIsland, src/SolverSet.cs:136): islands / sleep are not built");
+}
+int World::bodyWakeTouching(int bodyId) {                             // api/Body.cs:682-697: WakeBody on bodies that are all awake
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  return B2C_OK;
+}
+int World::bodySetEnabled(int bodyId, bool enabled) {                 // api/Body.cs:721-790
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  if (enabled) return B2C_OK;                                         // Enable on a body that is not in the disabled set returns at once (:757)
+  return fail(B2C_E_UNSUPPORTED, "Body.Disable moves the body, its contacts and joints to the disabled solver set (api/Body.cs:721-752): the disabled set is not built");
+}
+int World::bodySetBullet(int bodyId, bool flag) {                     // api/Body.cs:835-842
+  if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
+  if (!flag) return B2C_OK;                                           // no body carries the bit
+  return fail(B2C_E_UNSUPPORTED, "SetBullet(true): the bullet continuous stage (src/Solver.cs:728-738,1238-1272) is not built");
+}
+
 // BodyAPI.SetTransform after the upload: the same teleport as one device thread, ordered on the world's stream. The fat
 // box test needs the device's current fatAABB (enlarged by earlier steps), the proxy moves through the shared tree ops,
 // and BufferMove appends behind the moves the last step's FinalizeBodies buffered (src/BroadPhase.cs:56-59, :90-96).

@@ -85,6 +85,14 @@ class World {
   int setBodyType(int bodyId, int type);
   int explode(V2 position, float radius, float falloff, float impulsePerLength, uint64_t maskBits);
   int jointOp(int jointId, int patch, int which, float a, float b);
+  int jointSetLocalFrame(int jointId, int which, Xf frame);
+  int jointSetCollideConnected(int jointId, bool shouldCollide);
+  int bodySetSleepThreshold(int bodyId, float v);
+  int bodyEnableSleep(int bodyId, bool flag);
+  int bodySetAwake(int bodyId, bool awake);
+  int bodyWakeTouching(int bodyId);
+  int bodySetEnabled(int bodyId, bool enabled);
+  int bodySetBullet(int bodyId, bool flag);
   void enableGraphLaunch(bool flag) { graphMode_ = flag ? 1 : 0; }
   int setTransform(int bodyId, V2 p, Rot q);
   int setLinearVelocity(int bodyId, V2 v);

@@ -14,6 +14,7 @@
 #ifndef B2CUDA_H
 #define B2CUDA_H
 #include <stdint.h>
+#include <stddef.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -250,6 +251,20 @@ int32_t b2cuda_world_explode(B2CWorld* world, B2CVec2 position, float radius, fl
 int32_t b2cuda_joint_set_param(B2CWorld* world, int32_t jointId, int32_t param, float value);
 int32_t b2cuda_joint_enable(B2CWorld* world, int32_t jointId, int32_t feature, int32_t flag);
 int32_t b2cuda_joint_set_limits(B2CWorld* world, int32_t jointId, float lower, float upper);
+/* JointAPI.SetLocalFrameA / SetLocalFrameB api/Joint.cs:44,50 (which = 0 for A, 1 for B): a plain store into the joint sim, picked up by the next
+ * PrepareJoints. JointAPI.SetCollideConnected api/Joint.cs:56-75: switching it on buffers a move for the shapes of the body with fewer shapes
+ * (the next step's pair update creates the contacts), switching it off destroys the contacts between the two bodies in contact-list order. */
+int32_t b2cuda_joint_set_local_frame(B2CWorld* world, int32_t jointId, int32_t which, B2CTransform localFrame);
+int32_t b2cuda_joint_set_collide_connected(B2CWorld* world, int32_t jointId, int32_t shouldCollide);
+/* BodyAPI sleep / enable / bullet surface (api/Body.cs): SetSleepThreshold :712, EnableSleep :700, SetAwake :668, WakeTouching :682,
+ * Disable :721, Enable :754, SetBullet :835. See DESIGN.md for which of them act and which are refused with B2C_E_UNSUPPORTED. */
+int32_t b2cuda_body_set_sleep_threshold(B2CWorld* world, int32_t bodyId, float sleepThreshold);
+int32_t b2cuda_body_enable_sleep(B2CWorld* world, int32_t bodyId, int32_t enableSleep);
+int32_t b2cuda_body_set_awake(B2CWorld* world, int32_t bodyId, int32_t awake);
+int32_t b2cuda_body_wake_touching(B2CWorld* world, int32_t bodyId);
+int32_t b2cuda_body_disable(B2CWorld* world, int32_t bodyId);
+int32_t b2cuda_body_enable(B2CWorld* world, int32_t bodyId);
+int32_t b2cuda_body_set_bullet(B2CWorld* world, int32_t bodyId, int32_t flag);
 /* BodyAPI.SetTransform :293 / SetLinearVelocity :359 / SetAngularVelocity :369 / ApplyForceToCenter :457 /
  * ApplyTorque :469 / ApplyLinearImpulseToCenter :531 — api/Body.cs */
 int32_t b2cuda_body_set_transform(B2CWorld* world, int32_t bodyId, B2CVec2 position, B2CRot rotation);
@@ -330,6 +345,18 @@ int32_t b2cuda_world_get_counters(B2CWorld* world, B2CCounters* out);
    order-independent checksums of the device state between the phases of the last step (scripts/gpu_determinism.py). */
 int32_t b2cuda_world_debug_checksums(B2CWorld* world, uint64_t* out16);
 int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);   /* averages over the steps since the previous call (<= 64) */
+/* ---- Bulk scene upload (new; no reference counterpart: the reference builds scenes call by call). One call replays a recorded
+ * sequence of BodyAPI.CreateBody / ShapeAPI.CreateShape / JointAPI.Create*Joint calls in order, so the ids, lists and trees come out exactly as
+ * if the calls had been made one by one. Blob layout (all little-endian PODs of this header, tightly packed in this order):
+ *   B2CSnapshotHeader, then `opCount` records of { int32 kind; int32 ref; payload }:
+ *     kind 0  body   ref unused          payload B2CBodyDef
+ *     kind 1  shape  ref = body ordinal  payload B2CShapeDef, B2CGeometry        (ordinal = position among the blob's body records)
+ *     kind 2  joint  ref unused          payload B2CJointDef whose bodyIdA / bodyIdB are body ordinals
+ * bodyIds / shapeIds / jointIds (each may be NULL) receive the ids in record order. Fails on the first refused record (the world then holds
+ * what was created before it). */
+#define B2C_SNAPSHOT_MAGIC 0x42324353u   /* "B2CS" */
+typedef struct B2CSnapshotHeader { uint32_t magic, version; int32_t opCount, bodyCount, shapeCount, jointCount; } B2CSnapshotHeader;
+int32_t b2cuda_world_upload_snapshot(B2CWorld* world, const void* blob, size_t bytes, int32_t* bodyIds, int32_t* shapeIds, int32_t* jointIds);
 /* ---- Batches of independent worlds (new; the reference's counterpart is the remark "Each world is completely independent and may be
  * simulated in parallel", api/World.cs:9-10, and a loop over WorldAPI.Step). One handle owns `worldCount` worlds on one device and steps
  * them in lockstep with ONE kernel launch: a thread block per world runs the whole step (pairs, collide, colouring, solver, finalize)

@@ -555,6 +555,25 @@ void World::SetDensity(int shapeId, float density, bool updateBodyMass) {      /
 }
 void World::ApplyMassFromShapes(int bodyId) { UpdateBodyMassData(bodies[bodyId]); }   // api/Body.cs:617-621
 
+void World::JointSetLocalFrame(int jointId, int which, const Transform& frame) {   // api/Joint.cs:44,50: a plain store into the joint sim
+  JointSim& j = GetJointSim(joints[jointId]);
+  if (which == 0) j.localFrameA = frame; else j.localFrameB = frame;
+}
+void World::JointSetCollideConnected(int jointId, bool shouldCollide) {           // api/Joint.cs:56-75
+  Joint& joint = joints[jointId];
+  if (joint.collideConnected == shouldCollide) return;
+  joint.collideConnected = shouldCollide;
+  Body& bodyA = bodies[joint.edge0.bodyId]; Body& bodyB = bodies[joint.edge1.bodyId];
+  if (shouldCollide) {
+    int shapeId = bodyA.shapeCount < bodyB.shapeCount ? bodyA.headShapeId : bodyB.headShapeId;
+    while (shapeId != -1) {
+      Shape& shape = shapes[shapeId];
+      if (shape.proxyKey != -1) BufferMove(shape.proxyKey);
+      shapeId = shape.nextShapeId;
+    }
+  } else DestroyContactsBetweenBodies(bodyA, bodyB);
+}
+
 void World::DestroyContactsBetweenBodies(Body& bodyA, Body& bodyB) {    // src/Joint.cs:155-180
   int contactKey, otherBodyId;
   if (bodyA.contactCount < bodyB.contactCount) { contactKey = bodyA.headContactKey; otherBodyId = bodyB.id; }

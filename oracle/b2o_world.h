@@ -227,6 +227,8 @@ class World {
   bool JointSetParam(int jointId, int param, float value);      // api/Joint.cs setters, see b2o_world.cpp
   bool JointEnable(int jointId, int feature, bool flag);
   bool JointSetLimits(int jointId, float lower, float upper);
+  void JointSetLocalFrame(int jointId, int which, const Transform& frame);   // JointAPI.SetLocalFrameA/B api/Joint.cs:44,50
+  void JointSetCollideConnected(int jointId, bool shouldCollide);            // JointAPI.SetCollideConnected api/Joint.cs:56-75
   void SetTransform(int bodyId, Vec2 position, Rot rotation);
   void SetLinearVelocity(int bodyId, Vec2 v);
   void SetAngularVelocity(int bodyId, float w);

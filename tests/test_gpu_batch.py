@@ -184,3 +184,49 @@ def test_batch_full_size_8192_pyramids_sampled_worlds_bit_exact():
     finally:
         batch.Destroy()
         orc.Destroy()
+
+
+def test_snapshot_upload_equals_call_by_call_build():
+    """b2cuda_world_upload_snapshot replays a recorded creation sequence in one call: ids, lists, trees and every later step are those of
+    the call-by-call build (compared with the oracle built call by call); one recording fills several worlds of a batch."""
+    def scene(w):
+        scenes.add_pyramid(w, 7)
+        scenes.joint_grid(w, n=5)
+        scenes.mixed_drop(w, n=30, seed=9)
+
+    rec = api.Snapshot()
+    scene(rec)
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    orc = api.World(OracleBackend(), scenes.world_def())
+    try:
+        b, s, j = rec.upload(cuda)
+        scene(orc)
+        assert len(b) == rec.n_bodies and len(s) == rec.n_shapes and len(j) == rec.n_joints and sorted(b) == list(range(len(b)))
+        for step in range(15):
+            cuda.Step(1.0 / 60.0, 4)
+            orc.Step(1.0 / 60.0, 4)
+            _compare_world(0, step, cuda, orc)
+        # truncated and corrupted blobs are refused, not half-read
+        data = rec.blob()
+        for bad in (data[:40], b"\0" * 64, data[:len(data) - 7]):
+            rc = cuda.fns["world_upload_snapshot"](cuda.handle, bad, len(bad), None, None, None)
+            assert rc != 0
+    finally:
+        cuda.Destroy()
+        orc.Destroy()
+    pyr = api.Snapshot()
+    scenes.add_pyramid(pyr, 10)
+    batch = api.Batch(api.CudaBackend(), 64, scenes.world_def())
+    orc = api.World(OracleBackend(), scenes.world_def())
+    try:
+        for w in batch.worlds:
+            pyr.upload(w)
+        scenes.add_pyramid(orc, 10)
+        for step in range(8):
+            batch.Step(1.0 / 60.0, 4)
+            orc.Step(1.0 / 60.0, 4)
+        for k in (0, 31, 63):
+            _compare_world(k, 7, batch.worlds[k], orc)
+    finally:
+        batch.Destroy()
+        orc.Destroy()

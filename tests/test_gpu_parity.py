@@ -1082,3 +1082,90 @@ def test_restitution_in_pyramids_and_overflow_bit_exact():
     res = parity.run_pair(build, steps=40, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0
     assert res["max_overflow"] > 0
+
+
+def test_joint_local_frames_and_collide_connected_between_steps_bit_exact():
+    """JointAPI.SetLocalFrameA/B (api/Joint.cs:44,50) and SetCollideConnected (:56-75) between steps: chains of overlapping boxes hinged
+    to each other; switching collision on buffers moves (contacts and begin events appear the next step), switching it off destroys the
+    contacts between the two bodies in contact-list order; the frame setters move the hinge."""
+    from box2d_b200 import geometry as G
+    holder = {}
+
+    def build(w):
+        ground = w.CreateBody(api.default_body_def())
+        w.CreatePolygonShape(ground, scenes._shape_def(), G.MakeOffsetBox(40.0, 1.0, (0.0, -1.0)))
+        joints = []
+        for k in range(6):
+            prev = None
+            for i in range(5):
+                b = scenes._dynamic_body(w, -20.0 + 8.0 * k + 0.6 * i, 0.5 + 0.3 * i)
+                w.CreatePolygonShape(b, scenes._shape_def(), G.MakeBox(0.5, 0.25))
+                if i % 2 == 0:
+                    w.CreateCircleShape(b, scenes._shape_def(), G.Circle((0.0, 0.2), 0.3))     # some bodies carry two shapes: shapeCount decides whose shapes move
+                if prev is not None:
+                    jd = api.default_revolute_joint_def()
+                    jd.bodyIdA, jd.bodyIdB = prev, b
+                    jd.localFrameA = api.Transform(api.Vec2(0.3, 0.15), api.Rot(1.0, 0.0))
+                    jd.localFrameB = api.Transform(api.Vec2(-0.3, -0.15), api.Rot(1.0, 0.0))
+                    jd.collideConnected = int(k % 2 == 1)
+                    joints.append(w.CreateRevoluteJoint(jd))
+                prev = b
+        holder["joints"] = joints
+
+    def mutate(w, step):
+        js = holder["joints"]
+        if step == 4:
+            for j in js[0::3]:
+                w.SetCollideConnected(j, True)
+            for j in js[1::3]:
+                w.SetCollideConnected(j, False)
+        if step == 9:
+            for j in js[0::4]:
+                w.SetLocalFrameA(j, api.Transform(api.Vec2(0.25, 0.2), api.Rot(1.0, 0.0)))
+            for j in js[2::4]:
+                w.SetLocalFrameB(j, api.Transform(api.Vec2(-0.35, -0.1), api.Rot(1.0, 0.0)))
+        if step == 14:
+            for j in js:
+                w.SetCollideConnected(j, False)
+        if step == 20:
+            for j in js[::2]:
+                w.SetCollideConnected(j, True)
+                w.SetCollideConnected(j, True)              # a repeated call returns at once
+
+    res = parity.run_pair(build, steps=36, verbose=True, mutate=mutate)
+    assert res["max_rel_err"] == 0.0
+    # before the first step the call only edits the host mirror (moves are buffered, no contacts exist yet)
+    def build2(w):
+        build(w)
+        for j in holder["joints"][::2]:
+            w.SetCollideConnected(j, True)
+        w.SetLocalFrameA(holder["joints"][1], api.Transform(api.Vec2(0.2, 0.1), api.Rot(1.0, 0.0)))
+    res = parity.run_pair(build2, steps=12, verbose=True)
+    assert res["max_rel_err"] == 0.0
+
+
+def test_body_sleep_enable_bullet_surface_while_sleep_is_not_built():
+    """api/Body.cs:664-842: the calls that only wake or store succeed, the calls that need islands / the disabled set / the bullet
+    stage are refused loudly (B2C_E_UNSUPPORTED = -2), and none of them disturbs the simulation."""
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        scenes.add_pyramid(cuda, 4)
+        cuda.Step(1.0 / 60.0, 4)
+        before = cuda.ReadBodies().tobytes()
+        b = 3
+        cuda.SetSleepThreshold(b, 0.2)
+        cuda.EnableSleep(b, False)
+        cuda.SetAwake(b, True)
+        cuda.WakeTouching(b)
+        cuda.WakeTouching(0)                 # the static ground
+        cuda.SetAwake(0, False)              # a static body: nothing to do
+        cuda.EnableBody(b)
+        cuda.SetBullet(b, False)
+        for call in (lambda: cuda.SetAwake(b, False), lambda: cuda.DisableBody(b), lambda: cuda.SetBullet(b, True)):
+            with pytest.raises(api.B2Error, match="rc=-2"):
+                call()
+        with pytest.raises(api.B2Error):
+            cuda.SetSleepThreshold(9999, 0.1)
+        assert cuda.ReadBodies().tobytes() == before
+    finally:
+        cuda.Destroy()
