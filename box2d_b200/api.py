@@ -462,6 +462,26 @@ class World:
                 np.frombuffer(C.string_at(ptr, n * C.sizeof(ty)), dtype=np.dtype(ty)).copy()
         return grab(b, nb.value, ContactTouchEvent), grab(e, ne.value, ContactTouchEvent), grab(h, nh.value, ContactHitEvent)
 
+    def GetSensorEvents(self):
+        """WorldAPI.GetSensorEvents api/World.cs:289-299 -> (begin, end) numpy structured arrays of (sensor, visitor) shape references."""
+        b, e = C.POINTER(capi.SensorEvent)(), C.POINTER(capi.SensorEvent)()
+        nb, ne = C.c_int32(), C.c_int32()
+        self._check(self.fns["world_get_sensor_events"](self.handle, C.byref(b), C.byref(nb), C.byref(e), C.byref(ne)))
+
+        def grab(ptr, n):
+            if n == 0:
+                return np.zeros(0, dtype=np.dtype(capi.SensorEvent))
+            return np.frombuffer(C.string_at(ptr, n * C.sizeof(capi.SensorEvent)), dtype=np.dtype(capi.SensorEvent)).copy()
+        return grab(b, nb.value), grab(e, ne.value)
+
+    def EnableSensorEvents(self, shape_id, flag):       # ShapeAPI.EnableSensorEvents api/Shape.cs:170
+        self._check(self.fns["shape_enable_sensor_events"](self.handle, shape_id, int(bool(flag))))
+
+    def GetSensorOverlaps(self, shape_id, capacity=64):  # ShapeAPI.GetSensorData api/Shape.cs:409
+        out, n = (capi.ShapeRef * capacity)(), C.c_int32()
+        self._check(self.fns["shape_get_sensor_overlaps"](self.handle, shape_id, out, capacity, C.byref(n)))
+        return [(out[i].shapeId, out[i].generation) for i in range(n.value)]
+
     def GetJointEvents(self):
         p, n = C.POINTER(C.c_int32)(), C.c_int32()
         self._check(self.fns["world_get_joint_events"](self.handle, C.byref(p), C.byref(n)))

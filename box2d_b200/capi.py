@@ -52,6 +52,14 @@ class Geometry(C.Structure):
                 ("n", Vec2 * MAX_POLY), ("centroid", Vec2)]
 
 
+class ShapeRef(C.Structure):
+    _fields_ = [("shapeId", C.c_int32), ("generation", C.c_uint32)]
+
+
+class SensorEvent(C.Structure):
+    _fields_ = [("sensor", ShapeRef), ("visitor", ShapeRef)]
+
+
 class RevoluteJointDef(C.Structure):
     _fields_ = [("bodyIdA", C.c_int32), ("bodyIdB", C.c_int32), ("localFrameA", Transform), ("localFrameB", Transform),
                 ("forceThreshold", C.c_float), ("torqueThreshold", C.c_float), ("constraintHertz", C.c_float),
@@ -195,6 +203,9 @@ PROTOS = {
     "world_get_contact_events": [_W, C.POINTER(C.POINTER(ContactTouchEvent)), C.POINTER(C.c_int32),
                                  C.POINTER(C.POINTER(ContactTouchEvent)), C.POINTER(C.c_int32),
                                  C.POINTER(C.POINTER(ContactHitEvent)), C.POINTER(C.c_int32)],
+    "world_get_sensor_events": [_W, C.POINTER(C.POINTER(SensorEvent)), C.POINTER(C.c_int32), C.POINTER(C.POINTER(SensorEvent)), C.POINTER(C.c_int32)],
+    "shape_enable_sensor_events": [_W, C.c_int32, C.c_int32],
+    "shape_get_sensor_overlaps": [_W, C.c_int32, C.POINTER(ShapeRef), C.c_int32, C.POINTER(C.c_int32)],
     "world_get_joint_events": [_W, C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32)],
     "world_get_body_events": [_W, C.POINTER(C.POINTER(BodyRead)), C.POINTER(C.c_int32)],
     "world_get_body_move_events": [_W, C.POINTER(C.POINTER(BodyMoveEvent)), C.POINTER(C.c_int32)],

@@ -151,6 +151,15 @@ int32_t b2cuda_world_enable_graph_launch(B2CWorld* h, int32_t flag) { CHECK_HAND
 int32_t b2cuda_world_timer_start(B2CWorld* h) { CHECK_HANDLE(h); return done(h, h->w->timerStart()); }
 int32_t b2cuda_world_timer_stop(B2CWorld* h, float* ms) { CHECK_HANDLE(h); if (!ms) return B2C_E_INVALID; return done(h, h->w->timerStop(ms)); }
 
+int32_t b2cuda_world_get_sensor_events(B2CWorld* h, const B2CSensorEvent** begin, int32_t* nb, const B2CSensorEvent** end, int32_t* ne) {
+  CHECK_HANDLE(h); if (!begin || !nb || !end || !ne) return B2C_E_INVALID;
+  return done(h, h->w->getSensorEvents(begin, nb, end, ne));
+}
+int32_t b2cuda_shape_enable_sensor_events(B2CWorld* h, int32_t id, int32_t flag) { CHECK_HANDLE(h); return done(h, h->w->shapeEnableSensorEvents(id, flag != 0)); }
+int32_t b2cuda_shape_get_sensor_overlaps(B2CWorld* h, int32_t id, B2CShapeRef* out, int32_t capacity, int32_t* count) {
+  CHECK_HANDLE(h); if (!count || (capacity > 0 && !out)) return B2C_E_INVALID;
+  return done(h, h->w->shapeGetSensorOverlaps(id, out, capacity, count));
+}
 int32_t b2cuda_joint_set_local_frame(B2CWorld* h, int32_t id, int32_t which, B2CTransform f) { CHECK_HANDLE(h); return done(h, h->w->jointSetLocalFrame(id, which, mkXf(mk(f.p.x, f.p.y), mkRot(f.q.c, f.q.s)))); }
 int32_t b2cuda_joint_set_collide_connected(B2CWorld* h, int32_t id, int32_t flag) { CHECK_HANDLE(h); return done(h, h->w->jointSetCollideConnected(id, flag != 0)); }
 int32_t b2cuda_body_set_sleep_threshold(B2CWorld* h, int32_t id, float v) { CHECK_HANDLE(h); return done(h, h->w->bodySetSleepThreshold(id, v)); }

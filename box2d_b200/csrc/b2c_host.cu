@@ -107,6 +107,8 @@ void World::freeDevice() {
   if (batch_) hJointColor_ = nullptr;                    // the batch's mapped int
   if (hJointColor_) { cudaFreeHost(hJointColor_); hJointColor_ = nullptr; hJointColorDev_ = nullptr; }
   if (hBegin_) cudaFreeHost(hBegin_);                   // (null for a batch member: its events stay in device memory)
+  if (hSensorBegin_) { cudaFreeHost(hSensorBegin_); hSensorBegin_ = nullptr; }
+  for (auto& e : hSensorEnd_) { if (e) cudaFreeHost(e); e = nullptr; }
   for (auto& e : hEnd_) { if (e) cudaFreeHost(e); e = nullptr; }
   if (hHit_) cudaFreeHost(hHit_);
   if (hJointEvents_) cudaFreeHost(hJointEvents_);
@@ -448,6 +450,10 @@ void World::updateShapeAABBs(HShape& s, Xf xf, int proxyType) {   // src/Shape.c
   s.fat = boxGrow(aabb, proxyType == kStaticBody ? kSpeculativeDistance : kAABBMargin);
 }
 
+// a sensor created after the upload: its slot in World.sensors starts with two empty overlap lists (src/Shape.cs:212-213)
+__global__ void k_sensor_created(WorldDev d, int sensorIndex, int shapeId) {
+  d.sensorShape[sensorIndex] = shapeId; d.sensorOverlapCount[2 * sensorIndex] = 0; d.sensorOverlapCount[2 * sensorIndex + 1] = 0;
+}
 int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId) {
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   int grow[4] = {0, 0, 0, 0}, grownCap = 0;
@@ -460,7 +466,7 @@ int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g,
     { int rc = growTree(t, cap); if (rc) return rc; }
     grownCap = cap;
   }
-  if (def.isSensor) return fail(B2C_E_UNSUPPORTED, "sensor shapes are not supported (src/Sensor.cs is out of scope)");
+  if (def.isSensor && onDevice_) { int rc = growSensors((int)sensorShapes_.size() + 1); if (rc) return rc; }
   if (def.enableCustomFiltering || def.enablePreSolveEvents) return fail(B2C_E_UNSUPPORTED, "managed callbacks (custom filter / preSolve) cannot run on the device");
   if (g.type < 0 || g.type > kPolygon) return fail(B2C_E_UNSUPPORTED, "chain segments are not supported");
   if (g.type == kPolygon && (g.count < 1 || g.count > kMaxPolygonVertices)) return fail(B2C_E_UNSUPPORTED, "polygon vertex count must be 1..8");
@@ -477,15 +483,18 @@ int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g,
   for (int i = 0; i < kMaxPolygonVertices; i++) { s.geom.v[i] = mk(g.v[i].x, g.v[i].y); s.geom.n[i] = mk(g.n[i].x, g.n[i].y); }
   s.friction = def.friction; s.restitution = def.restitution; s.rollingResistance = def.rollingResistance; s.tangentSpeed = def.tangentSpeed;
   s.density = def.density; s.categoryBits = def.categoryBits; s.maskBits = def.maskBits; s.groupIndex = def.groupIndex; s.userData = def.userData;
-  s.flags = (def.enableContactEvents ? SF_CONTACT_EVENTS : 0) | (def.enableHitEvents ? SF_HIT_EVENTS : 0);
+  s.flags = (def.enableContactEvents ? SF_CONTACT_EVENTS : 0) | (def.enableHitEvents ? SF_HIT_EVENTS : 0) | (def.enableSensorEvents ? SF_SENSOR_EVENTS : 0);
+  if (def.isSensor) { s.sensorIndex = (int)sensorShapes_.size(); sensorShapes_.push_back(id); }      // src/Shape.cs:210-215
+  const bool forcePairCreation = def.invokeContactCreation || def.isSensor;                       // src/Shape.cs:199
   int proxyType = body.type;
   if (onDevice_) {
     ShapeDev row; memset(&row, 0, sizeof(row));
     row.geom = s.geom; row.material = make_float4(s.friction, s.restitution, s.rollingResistance, s.tangentSpeed);
-    row.categoryBits = s.categoryBits; row.maskBits = s.maskBits; row.groupIndex = s.groupIndex; row.bodyId = bodyId; row.flags = s.flags; row.sensorIndex = -1;
+    row.categoryBits = s.categoryBits; row.maskBits = s.maskBits; row.groupIndex = s.groupIndex; row.bodyId = bodyId; row.flags = s.flags; row.sensorIndex = s.sensorIndex; row.generation = s.generation;
     CK(cudaSetDevice(device_));
-    k_create_shape<<<1, 1, 0, stream_>>>(d_, id, row, proxyType, def.invokeContactCreation ? 1 : 0, grow[0], grow[1], grow[2], grow[3]);
+    k_create_shape<<<1, 1, 0, stream_>>>(d_, id, row, proxyType, forcePairCreation ? 1 : 0, grow[0], grow[1], grow[2], grow[3]);
     CK(cudaGetLastError());
+    if (def.isSensor) { k_sensor_created<<<1, 1, 0, stream_>>>(d_, s.sensorIndex, id); CK(cudaGetLastError()); d_.sensorCount = (int)sensorShapes_.size(); }
     d_.trees[proxyType].capacity = grownCap;
     treeNodeCount_[proxyType] += treeProxyCount_[proxyType] > 0 ? 2 : 1; treeProxyCount_[proxyType]++;
     s.proxyKey = 0;                               // "has a proxy"; the key itself lives on the device (b2cuda_world_read_shapes)
@@ -499,7 +508,7 @@ int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g,
   {                                               // src/BroadPhase.cs:71-79
     int proxyId = trees_[proxyType].createProxy(s.fat, s.categoryBits, id);
     s.proxyKey = proxyKeyOf(proxyId, proxyType);
-    if (proxyType != kStaticBody || def.invokeContactCreation) bufferMove(s.proxyKey);
+    if (proxyType != kStaticBody || forcePairCreation) bufferMove(s.proxyKey);
   }
   if (body.headShapeId != -1) shapes_[body.headShapeId].prevShapeId = id;
   s.prevShapeId = -1; s.nextShapeId = body.headShapeId; body.headShapeId = id; body.shapeCount++;
@@ -862,6 +871,44 @@ int World::uploadJointLists() {                  // joint edges, per-body list h
   CK(cudaMemcpy(d_.bodyJointCount, cnt.data(), sizeof(int) * nBody, cudaMemcpyHostToDevice));
   return B2C_OK;
 }
+// World.DestroySensor src/Sensor.cs:219-235 (the same lines sit inside DestroyShapeInternal, src/Shape.cs:245-268): an end event for every shape
+// in the sensor's current overlap list, appended to the end-event buffer of the running index, then RemoveSwap in World.sensors.
+__global__ void k_destroy_sensor(WorldDev d, int sensorIndex, int shapeId, int lastIndex, int endIndex) {
+  Scalars& s = *d.sc;
+  const int parity = s.sensorParity;
+  const int n = d.sensorOverlapCount[2 * sensorIndex + parity];
+  const int2* o2 = d.sensorOverlaps + ((size_t)sensorIndex * 2 + parity) * kSensorMaxOverlaps;
+  B2CShapeRef ref; ref.shapeId = shapeId; ref.generation = d.shapes[shapeId].generation;
+  int base = s.sensorEndCount[endIndex];
+  for (int i = 0; i < n; i++) {
+    if (base >= d.sensorEventCapacity) { s.errorFlags |= (int)ERR_SENSOR_CAPACITY; break; }
+    B2CSensorEvent e; e.sensor = ref; e.visitor.shapeId = o2[i].x; e.visitor.generation = (uint32_t)o2[i].y;
+    d.sensorEndEvents[endIndex][base++] = e;
+  }
+  s.sensorEndCount[endIndex] = base;
+  if (sensorIndex != lastIndex) {
+    for (int p = 0; p < 2; p++) {
+      const int m = d.sensorOverlapCount[2 * lastIndex + p];
+      d.sensorOverlapCount[2 * sensorIndex + p] = m;
+      const int2* src = d.sensorOverlaps + ((size_t)lastIndex * 2 + p) * kSensorMaxOverlaps; int2* dst = d.sensorOverlaps + ((size_t)sensorIndex * 2 + p) * kSensorMaxOverlaps;
+      for (int i = 0; i < m; i++) dst[i] = src[i];
+    }
+    const int moved = d.sensorShape[lastIndex];
+    d.sensorShape[sensorIndex] = moved; d.shapes[moved].sensorIndex = sensorIndex;
+  }
+  d.shapes[shapeId].sensorIndex = -1;
+}
+int World::destroySensor(int shapeId) {
+  HShape& sh = shapes_[shapeId];
+  const int index = sh.sensorIndex, last = (int)sensorShapes_.size() - 1;
+  k_destroy_sensor<<<1, 1, 0, stream_>>>(d_, index, shapeId, last, endIndex_);
+  CK(cudaGetLastError());
+  if (index != last) { int moved = sensorShapes_[last]; sensorShapes_[index] = moved; shapes_[moved].sensorIndex = index; }
+  sensorShapes_.pop_back(); sh.sensorIndex = -1;
+  d_.sensorCount = (int)sensorShapes_.size();
+  eventsFetched_ = false;
+  return B2C_OK;
+}
 int World::destroyBody(int bodyId) {             // BodyAPI.DestroyBody api/Body.cs:106-160
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
   if (!onDevice_) { int rc = upload(); if (rc) return rc; }   // the first call that needs the device state uploads the world (as the first step would)
@@ -873,6 +920,7 @@ int World::destroyBody(int bodyId) {             // BodyAPI.DestroyBody api/Body
     int rc = destroyJoint(jointId); if (rc) return rc;
   }
   CK(cudaSetDevice(device_));
+  for (int sid = b.headShapeId; sid != -1; sid = shapes_[sid].nextShapeId) if (shapes_[sid].sensorIndex != -1) { int rc = destroySensor(sid); if (rc) return rc; }   // api/Body.cs:127, shape-list order
   k_destroy_body<<<1, 256, 0, stream_>>>(d_, bodyId, endIndex_);      // contacts (list order), proxies, awake-set swap-remove
   CK(cudaGetLastError());
   for (int sid = b.headShapeId; sid != -1;) { HShape& sh = shapes_[sid]; int next = sh.nextShapeId; if (sh.proxyKey != -1) treeProxyRemoved(b.type); sh.proxyKey = -1; sh.id = -1; shapeIds_.release(sid); sid = next; }
@@ -920,6 +968,7 @@ int World::destroyShape(int shapeId, bool updateBodyMass) {      // ShapeAPI.Des
   CK(cudaSetDevice(device_));
   k_destroy_shape<<<1, 256, 0, stream_>>>(d_, shapeId, bodyId, prev, next, endIndex_);
   CK(cudaGetLastError());
+  if (s.sensorIndex != -1) { int rc = destroySensor(shapeId); if (rc) return rc; }      // src/Shape.cs:245-268
   if (s.proxyKey != -1) treeProxyRemoved(body.type);
   s.proxyKey = -1; s.id = -1;
   shapeIds_.release(shapeId);
@@ -1149,7 +1198,7 @@ int World::regrow(void** slot, size_t newCount, int fillByte) {
 #define RG(ptr, n) do { int rc_ = regrow((void**)&(ptr), (size_t)(n)); if (rc_) return rc_; } while (0)
 #define RGF(ptr, n, fill) do { int rc_ = regrow((void**)&(ptr), (size_t)(n), fill); if (rc_) return rc_; } while (0)
 int World::growScanScratch() {
-  int scanBlocks = std::max(std::max(d_.contactCapacity, d_.bigScratch), std::max(d_.moveCapacity, capAwake_)) / 256 + 2;
+  int scanBlocks = std::max(std::max(std::max(d_.contactCapacity, d_.bigScratch), std::max(d_.moveCapacity, capAwake_)), capSensor_) / 128 + 2;   // chunk = block size of the scope, 160 at the narrowest
   RG(d_.scanBlockSums, scanBlocks); RG(d_.scanBlockSums4, scanBlocks);
   return B2C_OK;
 }
@@ -1195,6 +1244,29 @@ int World::growShapes(int minShapes) {
   RG(d.moveArray, m); RG(d.moveHitCount, m + 1); RG(d.moveBig, m); RG(d.moveHitBuf, (size_t)m * 4);
   d.moveCapacity = m;
   capShape_ = c;
+  return growScanScratch();
+}
+int World::growSensors(int minSensors) {
+  if (minSensors <= capSensor_) return B2C_OK;
+  if (batch_) return fail(B2C_E_CAPACITY, "a world of a batch cannot grow its sensor arrays: create its sensor shapes before the first step");
+  WorldDev& d = d_;
+  CK(cudaSetDevice(device_));
+  const int c = std::max(minSensors, capSensor_ + capSensor_ / 2 + 16);
+  RG(d.sensorShape, c); RG(d.sensorOverlaps, (size_t)c * 2 * kSensorMaxOverlaps); RG(d.sensorOverlapCount, (size_t)c * 2); RG(d.sensorScan, c + 1);
+  // event buffers are mapped host memory: a larger copy replaces them once the stream has drained (the pending end events move over)
+  CK(cudaStreamSynchronize(stream_));
+  const int evCap = c * kSensorMaxOverlaps;
+  B2CSensorEvent* nb = nullptr; B2CSensorEvent* ne[2] = {nullptr, nullptr};
+  CK(cudaHostAlloc((void**)&nb, sizeof(B2CSensorEvent) * (size_t)evCap, cudaHostAllocMapped));
+  for (auto& e : ne) CK(cudaHostAlloc((void**)&e, sizeof(B2CSensorEvent) * (size_t)evCap, cudaHostAllocMapped));
+  if (hSensorBegin_) {
+    memcpy(nb, hSensorBegin_, sizeof(B2CSensorEvent) * (size_t)d.sensorEventCapacity); cudaFreeHost(hSensorBegin_);
+    for (int k = 0; k < 2; k++) { memcpy(ne[k], hSensorEnd_[k], sizeof(B2CSensorEvent) * (size_t)d.sensorEventCapacity); cudaFreeHost(hSensorEnd_[k]); }
+  }
+  hSensorBegin_ = nb; hSensorEnd_[0] = ne[0]; hSensorEnd_[1] = ne[1];
+  CK(cudaHostGetDevicePointer((void**)&d.sensorBeginEvents, hSensorBegin_, 0));
+  for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.sensorEndEvents[k], hSensorEnd_[k], 0));
+  d.sensorEventCapacity = evCap; d.sensorCapacity = c; capSensor_ = c;
   return growScanScratch();
 }
 int World::growJoints(int minJoints) {
@@ -1294,7 +1366,7 @@ int World::upload() {
     memset(&o, 0, sizeof(o));
     o.geom = s.geom; o.material = make_float4(s.friction, s.restitution, s.rollingResistance, s.tangentSpeed);
     o.categoryBits = s.categoryBits; o.maskBits = s.maskBits; o.groupIndex = s.groupIndex; o.bodyId = s.bodyId; o.nextShapeId = s.nextShapeId;
-    o.proxyKey = s.proxyKey; o.flags = s.flags; o.sensorIndex = -1;
+    o.proxyKey = s.proxyKey; o.flags = s.flags; o.sensorIndex = s.sensorIndex; o.generation = s.generation;
     shAABB[i] = make_float4(s.aabb.lo.x, s.aabb.lo.y, s.aabb.hi.x, s.aabb.hi.y);
     shFat[i] = make_float4(s.fat.lo.x, s.fat.lo.y, s.fat.hi.x, s.fat.hi.y);
   }
@@ -1372,8 +1444,23 @@ int World::upload() {
   DA(d.islandColorOff, int, (size_t)(capAwake + 1) * (kGraphColorCount + 1)); DA(d.islandBodies, int, capAwake); DA(d.bodyLocal, int, capAwake);
   DA(d.freeBodies, int, capAwake); DA(d.bigBodies, int, capAwake); DA(d.kinematicUsed, uint8_t, capAwake); DA(d.sLocal, int2, cc);
   DA(d.bodyEnlargedCount, int, capAwake + 1);
+  // ---- sensors (src/Sensor.cs): World.sensors order, both overlap lists per sensor (empty at the start), event buffers ----
+  { const int nSensor = (int)sensorShapes_.size();
+    capSensor_ = nSensor + (member ? 2 : std::max(16, nSensor / 4));
+    d.sensorCount = nSensor; d.sensorCapacity = capSensor_; d.sensorEventCapacity = capSensor_ * kSensorMaxOverlaps;
+    DA(d.sensorShape, int, capSensor_); DA(d.sensorOverlaps, int2, (size_t)capSensor_ * 2 * kSensorMaxOverlaps); DA(d.sensorOverlapCount, int, (size_t)capSensor_ * 2);
+    DA(d.sensorScan, int4, capSensor_ + 1);
+    UP(d.sensorShape, sensorShapes_);
+    if (member) {
+      DA(d.sensorBeginEvents, B2CSensorEvent, d.sensorEventCapacity); DA(d.sensorEndEvents[0], B2CSensorEvent, d.sensorEventCapacity); DA(d.sensorEndEvents[1], B2CSensorEvent, d.sensorEventCapacity);
+    } else {
+      CK(cudaHostAlloc((void**)&hSensorBegin_, sizeof(B2CSensorEvent) * (size_t)d.sensorEventCapacity, cudaHostAllocMapped));
+      for (auto& e : hSensorEnd_) CK(cudaHostAlloc((void**)&e, sizeof(B2CSensorEvent) * (size_t)d.sensorEventCapacity, cudaHostAllocMapped));
+      CK(cudaHostGetDevicePointer((void**)&d.sensorBeginEvents, hSensorBegin_, 0));
+      for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.sensorEndEvents[k], hSensorEnd_[k], 0));
+    } }
   DA(d.sc, Scalars, 1);
-  int scanBlocks = std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, capAwake)) / 256 + 2;
+  int scanBlocks = std::max(std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, capAwake)), capSensor_) / 128 + 2;   // chunk = block size of the scope, 160 at the narrowest
   DA(d.scanBlockSums, int, scanBlocks); DA(d.scanBlockSums4, int4, scanBlocks);
   Scalars init; memset(&init, 0, sizeof(init));
   init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;
@@ -1409,13 +1496,13 @@ int World::upload() {
 
 void World::saveHostSnap(HostSnap& h) const {
   h.bodyIds = bodyIds_; h.shapeIds = shapeIds_; h.jointIds = jointIds_; h.bodies = bodies_; h.shapes = shapes_; h.joints = joints_;
-  h.awakeOrder = awakeOrder_; h.colorJoints = colorJoints_; h.colorMask = colorMask_; h.d = d_;
+  h.awakeOrder = awakeOrder_; h.sensorShapes = sensorShapes_; h.colorJoints = colorJoints_; h.colorMask = colorMask_; h.d = d_;
   for (int t = 0; t < 3; t++) { h.treeNodeCount[t] = treeNodeCount_[t]; h.treeProxyCount[t] = treeProxyCount_[t]; }
   h.valid = true;
 }
 void World::restoreHostSnap(const HostSnap& h) {
   bodyIds_ = h.bodyIds; shapeIds_ = h.shapeIds; jointIds_ = h.jointIds; bodies_ = h.bodies; shapes_ = h.shapes; joints_ = h.joints;
-  awakeOrder_ = h.awakeOrder; colorJoints_ = h.colorJoints; colorMask_ = h.colorMask; d_ = h.d;
+  awakeOrder_ = h.awakeOrder; sensorShapes_ = h.sensorShapes; colorJoints_ = h.colorJoints; colorMask_ = h.colorMask; d_ = h.d;
   for (int t = 0; t < 3; t++) { treeNodeCount_[t] = h.treeNodeCount[t]; treeProxyCount_[t] = h.treeProxyCount[t]; }
   eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false; lastStepDtZero_ = false;
 }
@@ -1433,7 +1520,7 @@ int World::synchronize() {
   CK(cudaStreamSynchronize(stream_));
   if (batch_ && scalarsStale_) { CK(cudaMemcpy(hostScalars_, d_.sc, sizeof(Scalars), cudaMemcpyDeviceToHost)); scalarsStale_ = false; }
   if (hostScalars_->errorFlags & ~(int)ERR_TOI_CANDIDATE) {   // TOI candidates are counted (counters.toiCandidates), the step uses the no-hit result
-    char buf[160]; snprintf(buf, sizeof(buf), "device error flags 0x%x (capacity/stack/overflow-color/TOI; see b2c_world.cuh ERR_*)", hostScalars_->errorFlags);
+    char buf[160]; snprintf(buf, sizeof(buf), "device error flags 0x%x (capacity/stack/overflow-color/TOI/sensor overlaps; see b2c_world.cuh ERR_*)", hostScalars_->errorFlags);
     uint32_t f = (uint32_t)hostScalars_->errorFlags;
     if (f & (ERR_CONTACT_CAPACITY | ERR_PAIR_CAPACITY | ERR_HASH_FULL | ERR_STACK_OVERFLOW)) return fail(B2C_E_CAPACITY, buf);
     if (f & ERR_OVERFLOW_COLOR) return fail(B2C_E_UNSUPPORTED, buf);
@@ -1927,6 +2014,51 @@ int World::getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B
   return B2C_OK;
 }
 
+int World::getSensorEvents(const B2CSensorEvent** begin, int* nb, const B2CSensorEvent** end, int* ne) {   // WorldAPI.GetSensorEvents api/World.cs:289-299
+  *begin = nullptr; *end = nullptr; *nb = 0; *ne = 0;
+  if (!onDevice_) return B2C_OK;
+  int rc = synchronize(); if (rc) return rc;
+  int b = hostScalars_->sensorBeginCount, e = hostScalars_->sensorEndCount[lastEndIndex_];
+  if (lastStepDtZero_) b = 0;
+  b = std::min(b, d_.sensorEventCapacity); e = std::min(e, d_.sensorEventCapacity);
+  if (batch_) {                                    // batch member: the event arrays are device memory
+    stageSensorBegin_.resize(std::max(b, 1)); stageSensorEnd_.resize(std::max(e, 1));
+    if (b) CK(cudaMemcpy(stageSensorBegin_.data(), d_.sensorBeginEvents, sizeof(B2CSensorEvent) * b, cudaMemcpyDeviceToHost));
+    if (e) CK(cudaMemcpy(stageSensorEnd_.data(), d_.sensorEndEvents[lastEndIndex_], sizeof(B2CSensorEvent) * e, cudaMemcpyDeviceToHost));
+    *begin = stageSensorBegin_.data(); *end = stageSensorEnd_.data();
+  } else { *begin = hSensorBegin_; *end = hSensorEnd_[lastEndIndex_]; }
+  *nb = b; *ne = e;
+  return B2C_OK;
+}
+__global__ void k_shape_flag(WorldDev d, int shapeId, uint32_t bit, int on);
+int World::shapeEnableSensorEvents(int shapeId, bool flag) {          // ShapeAPI.EnableSensorEvents api/Shape.cs:170-174
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  HShape& s = shapes_[shapeId];
+  s.flags = flag ? (s.flags | SF_SENSOR_EVENTS) : (s.flags & ~(uint32_t)SF_SENSOR_EVENTS);
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_shape_flag<<<1, 1, 0, stream_>>>(d_, shapeId, SF_SENSOR_EVENTS, flag ? 1 : 0);
+  CK(cudaGetLastError());
+  return B2C_OK;
+}
+int World::shapeGetSensorOverlaps(int shapeId, B2CShapeRef* out, int capacity, int* count) {   // ShapeAPI.GetSensorData api/Shape.cs:409-419
+  *count = 0;
+  if (shapeId < 0 || shapeId >= (int)shapes_.size() || shapes_[shapeId].id != shapeId) return fail(B2C_E_INVALID, "bad shape id");
+  const int index = shapes_[shapeId].sensorIndex;
+  if (index == -1 || !onDevice_) return B2C_OK;
+  int rc = synchronize(); if (rc) return rc;
+  CK(cudaStreamSynchronize(stream_));
+  Scalars sc; CK(cudaMemcpy(&sc, d_.sc, sizeof(sc), cudaMemcpyDeviceToHost));      // a DestroySensor since the step may have moved lists: read the live parity
+  int n = 0; CK(cudaMemcpy(&n, d_.sensorOverlapCount + 2 * index + sc.sensorParity, sizeof(int), cudaMemcpyDeviceToHost));
+  n = std::min(n, capacity);
+  if (n > 0) {
+    std::vector<int2> tmp(n);
+    CK(cudaMemcpy(tmp.data(), d_.sensorOverlaps + ((size_t)index * 2 + sc.sensorParity) * kSensorMaxOverlaps, sizeof(int2) * n, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; i++) { out[i].shapeId = tmp[i].x; out[i].generation = (uint32_t)tmp[i].y; }
+  }
+  *count = n;
+  return B2C_OK;
+}
 int World::getJointEvents(const int** ids, int* count) {
   *ids = hJointEvents_; *count = 0;
   if (!onDevice_ || joints_.empty()) return B2C_OK;

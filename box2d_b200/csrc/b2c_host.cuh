@@ -44,6 +44,7 @@ struct HShape {
   Geom geom; float friction = 0.6f, restitution = 0, rollingResistance = 0, tangentSpeed = 0, density = 1;
   uint64_t categoryBits = ~0ull, maskBits = ~0ull; int groupIndex = 0; uint32_t flags = 0; uint16_t generation = 0;
   Box aabb, fat; uint64_t userData = 0;
+  int sensorIndex = -1;           // Shape.sensorIndex: position in World.sensors (sensorShapes_) or -1
 };
 struct HJoint {
   int id = -1; uint16_t generation = 0; bool collideConnected = false;
@@ -129,6 +130,9 @@ class World {
   int timerStop(float* ms);
   int getContactEvents(const B2CContactTouchEvent** begin, int* nb, const B2CContactTouchEvent** end, int* ne, const B2CContactHitEvent** hit, int* nh);
   int getJointEvents(const int** ids, int* count);
+  int getSensorEvents(const B2CSensorEvent** begin, int* nb, const B2CSensorEvent** end, int* ne);
+  int shapeEnableSensorEvents(int shapeId, bool flag);
+  int shapeGetSensorOverlaps(int shapeId, B2CShapeRef* out, int capacity, int* count);
 
   // read-only view for b2c_noalloc.cu (b2cuda_world_copy_body_move_events_noalloc): nothing here changes the world
   struct NoAllocView { int device; cudaStream_t stream; bool onDevice, lastStepDtZero; const WorldDev* dev; };
@@ -164,11 +168,17 @@ class World {
   std::vector<std::pair<void*, size_t>> arenaBlocks_;   // batch member: its device arrays inside the batch's arena, in allocation order
   struct HostSnap {               // everything creation / destruction calls change on the host, for Batch::resetWorld
     IdPool bodyIds, shapeIds, jointIds; std::vector<HBody> bodies; std::vector<HShape> shapes; std::vector<HJoint> joints;
-    std::vector<int> awakeOrder; std::vector<std::vector<int>> colorJoints; std::vector<uint32_t> colorMask;
+    std::vector<int> awakeOrder, sensorShapes; std::vector<std::vector<int>> colorJoints; std::vector<uint32_t> colorMask;
     int treeNodeCount[3], treeProxyCount[3]; WorldDev d; bool valid = false;
   };
   void saveHostSnap(HostSnap& h) const;
   void restoreHostSnap(const HostSnap& h);
+  int growSensors(int minSensors);
+  int destroySensor(int shapeId);   // World.DestroySensor src/Sensor.cs:219-235
+  std::vector<int> sensorShapes_;   // World.sensors: shape id per sensor index
+  int capSensor_ = 0;
+  B2CSensorEvent* hSensorBegin_ = nullptr; B2CSensorEvent* hSensorEnd_[2] = {nullptr, nullptr};   // mapped pinned (a batch member: device memory + staging)
+  std::vector<B2CSensorEvent> stageSensorBegin_, stageSensorEnd_;
   int ensureHostBuffers();        // pinned read-back buffers; a batch member allocates them on first use
   std::vector<B2CContactTouchEvent> stageBegin_, stageEnd_; std::vector<B2CContactHitEvent> stageHit_;   // batch member: events live in device memory and are copied on demand
   // host creation state

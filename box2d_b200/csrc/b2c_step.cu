@@ -333,7 +333,7 @@ __device__ void p_pairs_finish(const WorldDev& d) {
   if (s.contactNext > d.contactCapacity) { s.contactNext = d.contactCapacity; s.errorFlags |= (int)ERR_CONTACT_CAPACITY; }
   s.liveContactCount += n; s.contactStamp += (unsigned)n;
   s.moveCount = 0; s.bigQueryCount = 0;
-  s.beginCount = 0; s.hitCount = 0; s.jointEventCount = 0; s.anyRestitution = 0; s.anyHitShapes = 0;
+  s.beginCount = 0; s.hitCount = 0; s.jointEventCount = 0; s.anyRestitution = 0; s.anyHitShapes = 0; s.sensorBeginCount = 0;
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -1355,12 +1355,14 @@ __device__ void p_step_finish(const WorldDev& d, int newEndIndex) {
   s.stepCount++;
   if (s.moveCount > d.moveCapacity) { s.moveCount = d.moveCapacity; s.errorFlags |= (int)ERR_PAIR_CAPACITY; }
   s.endCount[newEndIndex] = 0;                     // api/World.cs:106-108: swap, then clear the buffer the next step appends to
+  s.sensorEndCount[newEndIndex] = 0;
 }
-__global__ void k_zero_step(WorldDev d, int newEndIndex) { Scalars& s = *d.sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; }
+__global__ void k_zero_step(WorldDev d, int newEndIndex) { Scalars& s = *d.sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; s.sensorBeginCount = 0; s.sensorEndCount[newEndIndex] = 0; }
 
 }  // namespace b2c
 #include "b2c_rebuild.cuh"
 #include "b2c_bigquery.cuh"
+#include "b2c_sensor.cuh"
 namespace b2c {
 
 // ------------------------------------------------------------------------------------------------------------
@@ -1590,6 +1592,7 @@ template <class S> __device__ void finalizePhase(const S& grid, const WorldDev& 
     p_refit(d, tid, stride);
     grid.sync();
   } else if (tid == 0) s.moveCount = 0;
+  phase_sensors(grid, d, sp.endIndex);              // World.OverlapSensors, api/World.cs:97-102 (before the end-event buffers trade places)
   if (tid == 0) { s.enlargedShapeCount = 0; p_step_finish(d, newEndIndex); }
 }
 __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp, int newEndIndex) {
@@ -1844,7 +1847,7 @@ cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepPa
   else k_batch_step<256, 2><<<worldCount, 256, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
   return cudaGetLastError();
 }
-__global__ void k_batch_zero_step(const WorldDev* worlds, int newEndIndex) { Scalars& s = *worlds[blockIdx.x].sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; }
+__global__ void k_batch_zero_step(const WorldDev* worlds, int newEndIndex) { Scalars& s = *worlds[blockIdx.x].sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; s.sensorBeginCount = 0; s.sensorEndCount[newEndIndex] = 0; }
 cudaError_t launchBatchZeroStep(const WorldDev* worlds, int worldCount, int newEndIndex, cudaStream_t stream) {
   k_batch_zero_step<<<worldCount, 1, 0, stream>>>(worlds, newEndIndex);
   return cudaGetLastError();

@@ -16,7 +16,7 @@ enum : uint32_t {
   CF_DISJOINT = 0x100u, CF_STARTED = 0x200u, CF_STOPPED = 0x400u, CF_STATE_MASK = 0x700u
 };
 enum : uint32_t { ERR_CONTACT_CAPACITY = 1u, ERR_STACK_OVERFLOW = 2u, ERR_OVERFLOW_COLOR = 4u, ERR_PAIR_CAPACITY = 8u,
-                  ERR_TOI_CANDIDATE = 16u, ERR_HASH_FULL = 32u, ERR_TREE = 64u };
+                  ERR_TOI_CANDIDATE = 16u, ERR_HASH_FULL = 32u, ERR_TREE = 64u, ERR_SENSOR_CAPACITY = 128u };
 enum : uint16_t { NODE_ALLOCATED = 1, NODE_ENLARGED = 2, NODE_LEAF = 4 };   // src/DynamicTree.cs TreeNodeFlags
 
 // ---- dynamic AABB tree replica (src/DynamicTree.cs:11-32 TreeNode, SoA) ----
@@ -41,15 +41,18 @@ struct TreeDev {
   int stackCapacity;
 };
 
+constexpr int kSensorMaxOverlaps = 64;   // shapes one sensor can overlap at a time (src/Sensor.cs overlaps2); more sets ERR_SENSOR_CAPACITY and the step fails loudly
+
 struct ShapeDev {      // src/Shape.cs:25-52 (hot subset) — one AoS row per shapeId, 16-byte aligned
   Geom geom;                         // 152 B
   float4 material;                   // friction, restitution, rollingResistance, tangentSpeed
   uint64_t categoryBits, maskBits;
   int groupIndex, bodyId, nextShapeId, proxyKey;
   uint32_t flags;                    // SF_*
-  int sensorIndex; int pad0, pad1;
+  int sensorIndex;                   // Shape.sensorIndex (position in World.sensors) or -1
+  uint32_t generation; int pad1;
 };
-enum : uint32_t { SF_CONTACT_EVENTS = 1u, SF_HIT_EVENTS = 2u, SF_PRESOLVE = 4u, SF_CUSTOM_FILTER = 8u, SF_ENLARGED = 16u };
+enum : uint32_t { SF_CONTACT_EVENTS = 1u, SF_HIT_EVENTS = 2u, SF_PRESOLVE = 4u, SF_CUSTOM_FILTER = 8u, SF_ENLARGED = 16u, SF_SENSOR_EVENTS = 32u };
 
 struct JointDev {      // src/Joint.cs:74-133 + src/joints/RevoluteJoint.cs:6-31
   int jointId, bodyIdA, bodyIdB, colorIndex;
@@ -104,6 +107,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int bigQueryCount, bigHitTotal, bigGroupTotal, staticRanksValid;   // wide broadphase queries (b2c_bigquery.cuh)
   int rebuildLevels[3];
   int colLen[kGraphColorCount];         // GraphColor.contactSims.Count per colour (src/ConstraintGraph.cs:10-24); [kOverflowIndex] = contacts in the overflow colour
+  int sensorParity, sensorBeginCount, sensorEndCount[2];   // src/Sensor.cs: which overlap buffer is overlaps2; sensor event counts (end events double-buffered like contact end events)
   unsigned long long dbg[16];           // order-independent state checksums per phase (B2CUDA_DEBUG_CHECKSUMS=1; b2cuda_world_debug_checksums)
 };
 
@@ -227,6 +231,13 @@ struct WorldDev {
   int eventCapacity;
   B2CBodyMoveEvent* moveOut;   // when set, FinalizeBodies writes bodyMoveEvents[awake sim index]
   B2CBodyRead* bodyOut;   // when set, FinalizeBodies also writes the packed per-body record (bodyMoveEvents equivalent)
+  // --- sensors (src/Sensor.cs:22-27): World.sensors order = sensor index; both overlap lists of every sensor, sorted by shape id ---
+  int* sensorShape;          // [sensorCapacity] Sensor.shapeId
+  int2* sensorOverlaps;      // [sensorCapacity][2][kSensorMaxOverlaps] (shapeId, generation); list Scalars.sensorParity is overlaps2, the other overlaps1
+  int* sensorOverlapCount;   // [sensorCapacity][2]
+  int4* sensorScan;          // [sensorCapacity + 1] per sensor (begin events, end events, 0, 0) -> exclusive offsets
+  B2CSensorEvent* sensorBeginEvents; B2CSensorEvent* sensorEndEvents[2];
+  int sensorCount, sensorCapacity, sensorEventCapacity;
   // --- finalize / refit scratch ---
   int* bodyEnlargedCount;   // per awake sim: enlarged shapes, then exclusive offsets
   Scalars* sc;

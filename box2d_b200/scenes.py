@@ -188,6 +188,46 @@ def mixed_drop(world, n=120, seed=7):
     return ground, paddle, bodies
 
 
+def sensor_field(world, n=60, seed=21):
+    """Sensors of every kind (src/Sensor.cs): static sensor boxes / circles / a capsule over a ground, a sensor riding a kinematic
+    sweeper, a sensor carried by a dynamic body, a sensor whose own events are off, and visitors (circles, capsules, boxes) of which
+    some have enableSensorEvents off and some are filtered out by category. Returns (sensor shape ids, visitor body ids)."""
+    sd = _shape_def()
+    ground = world.CreateBody(api.default_body_def())
+    world.CreatePolygonShape(ground, _shape_def(enableSensorEvents=1), geo.MakeOffsetBox(14.0, 0.5, (0.0, -0.5)))   # a static visitor
+    sensors = []
+    zone = world.CreateBody(api.default_body_def())
+    sen = _shape_def(isSensor=1, enableSensorEvents=1)
+    sensors.append(world.CreatePolygonShape(zone, sen, geo.MakeOffsetBox(3.0, 1.0, (-6.0, 2.5))))
+    sensors.append(world.CreateCircleShape(zone, sen, geo.Circle((0.0, 3.0), 1.5)))
+    sensors.append(world.CreateCapsuleShape(zone, sen, geo.Capsule((4.0, 1.0), (8.0, 2.0), 0.6)))
+    sensors.append(world.CreatePolygonShape(zone, _shape_def(isSensor=1, enableSensorEvents=0), geo.MakeOffsetBox(2.0, 2.0, (0.0, 2.0))))   # events off: never reports
+    sensors.append(world.CreatePolygonShape(zone, _shape_def(isSensor=1, enableSensorEvents=1, maskBits=2), geo.MakeOffsetBox(14.0, 3.0, (0.0, 3.0))))   # sees category 2 only
+    sensors.append(world.CreatePolygonShape(zone, sen, geo.MakeOffsetBox(1.0, 0.4, (-6.0, 2.0))))      # a sensor inside another sensor's box (the port does not skip sensors)
+    kd = api.default_body_def()
+    kd.type = api.KINEMATIC_BODY
+    kd.position = api.Vec2(-10.0, 1.2)
+    kd.linearVelocity = api.Vec2(4.0, 0.0)
+    sweeper = world.CreateBody(kd)
+    world.CreatePolygonShape(sweeper, sd, geo.MakeBox(0.3, 0.3))
+    sensors.append(world.CreateCircleShape(sweeper, sen, geo.Circle((0.0, 0.0), 1.2)))
+    carrier = _dynamic_body(world, 9.0, 6.0)
+    world.CreatePolygonShape(carrier, _shape_def(enableSensorEvents=1), geo.MakeBox(0.4, 0.4))
+    sensors.append(world.CreateCircleShape(carrier, sen, geo.Circle((0.0, 0.0), 1.0)))                 # rides a falling body; its own body's box is skipped
+    shapes = [geo.Circle((0.0, 0.0), 0.2), geo.Capsule((-0.2, 0.0), (0.2, 0.0), 0.12), geo.MakeBox(0.2, 0.15), geo.MakeRoundedBox(0.15, 0.15, 0.05)]
+    state = seed
+    bodies = []
+    cols = 15
+    for k in range(n):
+        i, j = k % cols, k // cols
+        state, dx = _uniform(state, -0.1, 0.1)
+        b = _dynamic_body(world, (i - 7.0) * 1.3 + dx, 4.5 + j * 0.8)
+        vd = _shape_def(enableSensorEvents=int(k % 5 != 0), categoryBits=(2 if k % 3 == 0 else 1))
+        world.CreateShape(b, vd, shapes[k % len(shapes)])
+        bodies.append(b)
+    return sensors, bodies, carrier, sweeper
+
+
 def overflow_plank(world, n=26):
     """A long dynamic plank resting on n small dynamic boxes: the plank needs more than the 20 dynamic colours, so some
     contacts land in the overflow colour (src/ConstraintGraph.cs:140) and are solved by the scalar overflow path."""
@@ -392,6 +432,7 @@ def batched_pyramids(world, n_worlds=8192, first=0, rows=10, pitch=15.0, cols=12
 
 
 SCENES = {
+    "sensor_field": sensor_field,
     "large_pyramid": large_pyramid,
     "many_pyramids": many_pyramids,
     "tumbler": tumbler,

@@ -345,6 +345,19 @@ int32_t b2cuda_world_get_counters(B2CWorld* world, B2CCounters* out);
    order-independent checksums of the device state between the phases of the last step (scripts/gpu_determinism.py). */
 int32_t b2cuda_world_debug_checksums(B2CWorld* world, uint64_t* out16);
 int32_t b2cuda_world_get_profile(B2CWorld* world, B2CProfile* out);   /* averages over the steps since the previous call (<= 64) */
+/* ---- Sensors (src/Sensor.cs). A shape created with B2CShapeDef.isSensor generates no contacts (src/BroadPhase.cs:168); after every step
+ * World.OverlapSensors (src/Sensor.cs:130-218, called from WorldAPI.Step api/World.cs:97-102) queries the three trees with the sensor's AABB,
+ * keeps the shapes with enableSensorEvents on another body that pass the filter and whose GJK distance (radii included) is below
+ * 10 * FLT_EPSILON, sorted by shape id, and reports the difference to the previous step's set as begin / end events (sensor by sensor in
+ * sensor-array order, visitors ascending). End events use the same double buffer as the contact end events (api/World.cs:283-299).
+ *   b2cuda_world_get_sensor_events   WorldAPI.GetSensorEvents api/World.cs:289-299; pointers valid until the next step.
+ *   b2cuda_shape_enable_sensor_events ShapeAPI.EnableSensorEvents api/Shape.cs:170-174 (a plain flag store).
+ *   b2cuda_shape_get_sensor_overlaps  ShapeAPI.GetSensorData api/Shape.cs:409-419: the current overlap set of one sensor shape. */
+typedef struct B2CShapeRef { int32_t shapeId; uint32_t generation; } B2CShapeRef;
+typedef struct B2CSensorEvent { B2CShapeRef sensor, visitor; } B2CSensorEvent;
+int32_t b2cuda_world_get_sensor_events(B2CWorld* world, const B2CSensorEvent** begin, int32_t* beginCount, const B2CSensorEvent** end, int32_t* endCount);
+int32_t b2cuda_shape_enable_sensor_events(B2CWorld* world, int32_t shapeId, int32_t flag);
+int32_t b2cuda_shape_get_sensor_overlaps(B2CWorld* world, int32_t shapeId, B2CShapeRef* out, int32_t capacity, int32_t* count);
 /* ---- Bulk scene upload (new; no reference counterpart: the reference builds scenes call by call). One call replays a recorded
  * sequence of BodyAPI.CreateBody / ShapeAPI.CreateShape / JointAPI.Create*Joint calls in order, so the ids, lists and trees come out exactly as
  * if the calls had been made one by one. Blob layout (all little-endian PODs of this header, tightly packed in this order):

@@ -147,6 +147,22 @@ int32_t b2o_world_get_contact_events(World* w, const B2CContactTouchEvent** begi
   *hit = tHit.data(); *hitCount = (int)tHit.size();
   return 0;
 }
+static thread_local std::vector<B2CSensorEvent> tSensorBegin, tSensorEnd;
+int32_t b2o_world_get_sensor_events(World* w, const B2CSensorEvent** begin, int32_t* beginCount, const B2CSensorEvent** end, int32_t* endCount) {
+  tSensorBegin.clear(); tSensorEnd.clear();
+  for (auto& e : w->sensorBeginEvents) tSensorBegin.push_back({{e.sensorShapeId, e.sensorGeneration}, {e.visitorShapeId, e.visitorGeneration}});
+  for (auto& e : w->sensorEndEvents[1 - w->endEventArrayIndex]) tSensorEnd.push_back({{e.sensorShapeId, e.sensorGeneration}, {e.visitorShapeId, e.visitorGeneration}});
+  *begin = tSensorBegin.data(); *beginCount = (int)tSensorBegin.size(); *end = tSensorEnd.data(); *endCount = (int)tSensorEnd.size();
+  return 0;
+}
+int32_t b2o_shape_enable_sensor_events(World* w, int32_t id, int32_t flag) { if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1; w->EnableSensorEvents(id, flag != 0); return 0; }
+int32_t b2o_shape_get_sensor_overlaps(World* w, int32_t id, B2CShapeRef* out, int32_t capacity, int32_t* count) {
+  if (id < 0 || id >= (int)w->shapes.size() || w->shapes[id].id != id) return -1;
+  std::vector<Visitor> v(capacity > 0 ? capacity : 0);
+  int n = w->GetSensorOverlaps(id, v.data(), capacity);
+  for (int i = 0; i < n; i++) out[i] = {v[i].shapeId, v[i].generation};
+  *count = n; return 0;
+}
 int32_t b2o_world_get_joint_events(World* w, const int32_t** ids, int32_t* count) { *ids = w->jointEvents.data(); *count = (int)w->jointEvents.size(); return 0; }
 int32_t b2o_world_read_bodies(World* w, B2CBodyRead* dst, int32_t capacity, int32_t* count) {
   int n = (int)w->bodies.size(); *count = n;

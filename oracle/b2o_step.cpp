@@ -183,8 +183,8 @@ void World::Solve(StepContext& stepContext) {      // :739-1322
 
 void World::Step(float timeStep, int subStepCount) {      // api/World.cs:31-113
   lastStepDtZero = timeStep == 0.0f;                        // :38 bodyMoveEvents.Clear(); :44-51 early return
-  contactBeginEvents.clear(); contactHitEvents.clear(); jointEvents.clear();
-  if (timeStep == 0) { endEventArrayIndex = 1 - endEventArrayIndex; contactEndEvents[endEventArrayIndex].clear(); return; }
+  sensorBeginEvents.clear(); contactBeginEvents.clear(); contactHitEvents.clear(); jointEvents.clear();
+  if (timeStep == 0) { endEventArrayIndex = 1 - endEventArrayIndex; sensorEndEvents[endEventArrayIndex].clear(); contactEndEvents[endEventArrayIndex].clear(); return; }
   double t0 = NowMs();
   UpdateBroadPhasePairs();
   double t1 = NowMs();
@@ -202,8 +202,9 @@ void World::Step(float timeStep, int subStepCount) {      // api/World.cs:31-113
   if (context.dt > 0) Solve(context);
   double t3 = NowMs();
   profileMs[0] += t3 - t0; profileMs[1] += t1 - t0; profileMs[2] += t2 - t1; profileMs[3] += t3 - t2;
+  OverlapSensors();                                         // :97-102
   endEventArrayIndex = 1 - endEventArrayIndex;
-  contactEndEvents[endEventArrayIndex].clear();
+  sensorEndEvents[endEventArrayIndex].clear(); contactEndEvents[endEventArrayIndex].clear();
 }
 
 }  // namespace b2o

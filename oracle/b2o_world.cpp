@@ -64,7 +64,7 @@ void World::UpdateShapeAABBs(Shape& s, const Transform& xf, int proxyType) {    
 }
 
 int World::CreateShape(int bodyId, const ShapeDef& def, const Geom& geom) {     // api/Shape.cs:8-24, src/Shape.cs:171-218
-  if (def.isSensor || geom.type == kChainSegment) { counters.unsupported++; lastError = "oracle: sensors/chain segments not restated"; }
+  if (geom.type == kChainSegment) { counters.unsupported++; lastError = "oracle: chain segments not restated"; }
   Body& body = bodies[bodyId];
   Transform transform = GetBodySim(body).transform;
   int shapeId = shapeIdPool.AllocId();
@@ -85,7 +85,8 @@ int World::CreateShape(int bodyId, const ShapeDef& def, const Geom& geom) {     
   }
   if (body.headShapeId != -1) shapes[body.headShapeId].prevShapeId = shapeId;
   shape.prevShapeId = -1; shape.nextShapeId = body.headShapeId; body.headShapeId = shapeId; body.shapeCount++;
-  shape.sensorIndex = -1;
+  if (def.isSensor) { shape.sensorIndex = (int)sensors.size(); sensors.emplace_back(); sensors.back().shapeId = shapeId; }   // src/Shape.cs:210-215
+  else shape.sensorIndex = -1;
   if (def.updateBodyMass) UpdateBodyMassData(body);
   return shapeId;
 }
@@ -392,6 +393,7 @@ void World::DestroyBody(int bodyId) {           // api/Body.cs:106-160 (awake or
   int shapeId = body.headShapeId;
   while (shapeId != -1) {
     Shape& shape = shapes[shapeId];
+    if (shape.sensorIndex != -1) DestroySensor(shape);      // api/Body.cs:127
     if (shape.proxyKey != -1) {                 // Shape.DestroyProxy src/Shape.cs:128-131 -> BroadPhase.DestroyProxy src/BroadPhase.cs:80-86
       UnBufferMove(shape.proxyKey);
       trees[ProxyType(shape.proxyKey)].DestroyProxy(ProxyId(shape.proxyKey));
@@ -432,6 +434,7 @@ void World::DestroyShape(int shapeId, bool updateBodyMass) {      // api/Shape.c
     contactKey = edgeIndex == 1 ? contact.edge1.nextKey : contact.edge0.nextKey;
     if (contact.shapeIdA == shapeId || contact.shapeIdB == shapeId) DestroyContact(contact);
   }
+  if (shape.sensorIndex != -1) DestroySensor(shape);       // src/Shape.cs:245-268 (the same lines as DestroySensor)
   shapeIdPool.FreeId(shapeId);
   shape.id = -1;
   if (updateBodyMass) UpdateBodyMassData(body);
@@ -710,5 +713,6 @@ void World::SetAngularDamping(int bodyId, float v) { GetBodySim(bodies[bodyId]).
 void World::SetGravityScale(int bodyId, float v) { GetBodySim(bodies[bodyId]).gravityScale = v; }       // api/Body.cs:647-653
 
 #include "b2o_distance.inc"
+#include "b2o_sensor.inc"
 
 }  // namespace b2o

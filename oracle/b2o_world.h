@@ -2,7 +2,7 @@
 // Data model of the reference world restricted to the rigid-body step path:
 // src/Body.cs, src/Shape.cs, src/Contact.cs, src/Joint.cs, src/joints/RevoluteJoint.cs,
 // src/ConstraintGraph.cs, src/SolverSet.cs (static + awake sets only), src/BroadPhase.cs.
-// Not restated (asserted unused): islands/sleep, sensors, chains, bullets/TOI, particles.
+// Sensors: src/Sensor.cs (b2o_sensor.cpp). Not restated (asserted unused): islands/sleep, chains, bullets/TOI, particles.
 #pragma once
 #include <vector>
 #include <unordered_set>
@@ -154,6 +154,9 @@ struct SolverSet {              // src/SolverSet.cs:13-30 (subset)
   std::vector<JointSim> jointSims;   // static set only: joints whose bodies are both non-dynamic (parked by SetType, SolverSet.TransferJoint)
 };
 
+struct Visitor { int shapeId; uint16_t generation; };                      // src/Sensor.cs:12-17
+struct Sensor { std::vector<Visitor> hits, overlaps1, overlaps2; int shapeId = -1; };   // src/Sensor.cs:22-27
+struct SensorEvent { int sensorShapeId; uint32_t sensorGeneration; int visitorShapeId; uint32_t visitorGeneration; };   // SensorBegin/EndTouchEvent as (ShapeID, ShapeID)
 struct ContactTouchEvent { int shapeIdA, shapeIdB, contactId; uint32_t contactGeneration; };
 struct ContactHitEvent { int shapeIdA, shapeIdB; Vec2 point, normal; float approachSpeed; };
 
@@ -256,6 +259,7 @@ class World {
   std::vector<ContactTouchEvent> contactBeginEvents, contactEndEvents[2]; int endEventArrayIndex = 0;
   std::vector<ContactHitEvent> contactHitEvents;
   std::vector<int> jointEvents;
+  std::vector<Sensor> sensors; std::vector<SensorEvent> sensorBeginEvents, sensorEndEvents[2];   // src/World.cs:102-106
   Vec2 gravity; float hitEventThreshold, restitutionThreshold, maxLinearSpeed, contactSpeed, contactHertz, contactDampingRatio;
   float inv_h = 0, inv_dt = 0;
   bool enableSleep, enableWarmStarting = true, enableContactSoftening, enableContinuous, enableSpeculative = true;
@@ -289,6 +293,10 @@ class World {
   void SolverStages(StepContext& ctx);
   void FinalizeBodies(StepContext& ctx, BitSet& enlargedSimBitSet);
   void SolveContinuous(int bodySimIndex);
+  void OverlapSensors();                   // src/Sensor.cs:130-218
+  void DestroySensor(Shape& sensorShape);  // src/Sensor.cs:219-235 (and the same lines inside DestroyShapeInternal src/Shape.cs:245-268)
+  void EnableSensorEvents(int shapeId, bool flag) { shapes[shapeId].enableSensorEvents = flag; }   // ShapeAPI.EnableSensorEvents api/Shape.cs:170-174
+  int GetSensorOverlaps(int shapeId, Visitor* out, int capacity) const;   // ShapeAPI.GetSensorData api/Shape.cs:409-419
 };
 
 }  // namespace b2o

@@ -47,6 +47,7 @@ def compare_struct(name, a, b, exact_fields=None, skip=(), report=None):
 def snapshot(w, full=True):
     ev = w.GetContactEvents()
     out = dict(begin=ev[0], end=ev[1], hit=ev[2], counters=w.GetCounters(), joint_events=np.asarray(w.GetJointEvents(), dtype=np.int32))
+    out["sensor_begin"], out["sensor_end"] = w.GetSensorEvents()
     if full:
         out.update(bodies=w.ReadBodies(), contacts=w.ReadContacts(), shapes=w.ReadShapes(), joints=w.ReadJoints())
     return out
@@ -65,6 +66,7 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
         notes = []
         max_overflow = 0
         hits_total = 0
+        sensor_total = 0
         for step in range(steps):
             if mutate is not None:
                 mutate(cuda, step)
@@ -75,11 +77,12 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
             a, b = snapshot(cuda, full), snapshot(orc, full)
             rep = []
             # exact: pair set / ids / colors / manifold ids / events
-            for key in ("begin", "end", "hit"):          # hit events: reference order = colour, then position in the colour's array
+            for key in ("begin", "end", "hit", "sensor_begin", "sensor_end"):   # hit events: reference order = colour, then position in the colour's array; sensor events: sensor order, visitors ascending
                 err = compare_struct(f"step{step}.{key}", a[key], b[key], report=rep)
                 assert err == 0.0, f"step{step} {key} events differ: " + "; ".join(rep[:4])
             assert a["joint_events"].tolist() == b["joint_events"].tolist(), f"step{step} joint events {a['joint_events']} vs {b['joint_events']}"
             hits_total += len(a["hit"])
+            sensor_total += len(a["sensor_begin"]) + len(a["sensor_end"])
             ca, cb = a["counters"], b["counters"]
             max_overflow = max(max_overflow, ca.colorCounts[23])
             for f in ("bodyCount", "awakeBodyCount", "shapeCount", "jointCount", "contactCount", "touchingContactCount", "contactIdCapacity", "activeColorCount", "moveCount", "newPairCount"):
@@ -100,7 +103,7 @@ def run_pair(build, steps=10, dt=1.0 / 60.0, substeps=4, world_def=None, tol=0.0
         c = cuda.GetCounters()
         co = orc.GetCounters()
         return dict(max_rel_err=worst, steps=steps, contacts=c.contactCount, touching=c.touchingContactCount, bodies=c.bodyCount,
-                    colors=c.activeColorCount, toi=c.toiCandidates, toi_oracle=co.toiCandidates, max_overflow=max_overflow, hits=hits_total)
+                    colors=c.activeColorCount, toi=c.toiCandidates, toi_oracle=co.toiCandidates, max_overflow=max_overflow, hits=hits_total, sensor_events=sensor_total)
     finally:
         cuda.Destroy()
         orc.Destroy()

@@ -23,6 +23,7 @@ def _builders():
     out.append(lambda w: scenes.wheel_rig(w, copies=1))
     out.append(lambda w: scenes.bounce_mix(w, n=24, seed=2))
     out.append(lambda w: scenes.joint_grid(w, n=6))
+    out.append(lambda w: scenes.sensor_field(w, n=30))          # sensors at CTA scope
     out.append(lambda w: None)                                  # an empty world inside a batch
     return out
 
@@ -30,7 +31,7 @@ def _builders():
 def _compare_world(k, step, cw, ow):
     a, b = parity.snapshot(cw), parity.snapshot(ow)
     rep = []
-    for key in ("begin", "end", "hit"):
+    for key in ("begin", "end", "hit", "sensor_begin", "sensor_end"):
         assert parity.compare_struct(f"w{k}.step{step}.{key}", a[key], b[key], report=rep) == 0.0, rep[:4]
     assert a["joint_events"].tolist() == b["joint_events"].tolist()
     ca, cb = a["counters"], b["counters"]

@@ -1169,3 +1169,64 @@ def test_body_sleep_enable_bullet_surface_while_sleep_is_not_built():
         assert cuda.ReadBodies().tobytes() == before
     finally:
         cuda.Destroy()
+
+
+def test_sensor_events_bit_exact():
+    """src/Sensor.cs: static, kinematic-borne and dynamic-borne sensors, visitors with events off / filtered out, a sensor with its own
+    events off; sensor begin / end events (sensor order, visitors ascending) and the overlap sets must equal the oracle's every step."""
+    holder = {}
+
+    def build(w):
+        holder[w.backend.name] = scenes.sensor_field(w)
+
+
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    from oracle_backend import OracleBackend
+    orc = api.World(OracleBackend(), scenes.world_def())
+    try:
+        build(cuda), build(orc)
+        total = 0
+        for step in range(90):
+            cuda.Step(1.0 / 60.0, 4), orc.Step(1.0 / 60.0, 4)
+            a, b = cuda.GetSensorEvents(), orc.GetSensorEvents()
+            for x, y, name in ((a[0], b[0], "begin"), (a[1], b[1], "end")):
+                assert x.tobytes() == y.tobytes(), f"step {step}: sensor {name} events differ: {x.tolist()[:6]} vs {y.tolist()[:6]}"
+            total += len(a[0]) + len(a[1])
+            if step % 10 == 9:
+                for sid in holder["cuda"][0]:
+                    assert cuda.GetSensorOverlaps(sid) == orc.GetSensorOverlaps(sid), f"step {step}: overlaps of sensor shape {sid}"
+                assert cuda.ReadBodies().tobytes() == orc.ReadBodies().tobytes()
+        assert total > 60, f"scene produced only {total} sensor events"
+    finally:
+        cuda.Destroy(), orc.Destroy()
+
+
+def test_sensor_mutations_between_steps_bit_exact():
+    """DestroyShape of a sensor with visitors (end events go to the running end buffer, World.sensors swap-remove), EnableSensorEvents on
+    sensors and visitors, a sensor created after the first step, DestroyBody of a body that carries a sensor, visitor destroyed inside a sensor."""
+    from box2d_b200 import geometry as G
+    holder = {}
+
+    def build(w):
+        holder[id(w)] = scenes.sensor_field(w)
+
+    def mutate(w, step):
+        sensors, bodies, carrier, sweeper = holder[id(w)]
+        if step == 30:
+            w.DestroyShape(sensors[1])                        # the circle zone, with visitors inside
+        if step == 36:
+            w.EnableSensorEvents(sensors[0], False)           # the sensor stops reporting: end events for everything inside
+            w.EnableSensorEvents(sensors[3], True)            # the silent one starts
+        if step == 42:
+            zone = w.CreateBody(api.default_body_def())
+            holder[(id(w), "late")] = w.CreatePolygonShape(zone, scenes._shape_def(isSensor=1, enableSensorEvents=1), G.MakeOffsetBox(6.0, 1.0, (0.0, 1.0)))
+        if step == 48:
+            w.DestroyBody(carrier)                            # takes its sensor with it
+            w.DestroyBody(bodies[7])
+            w.EnableSensorEvents(sensors[0], True)
+        if step == 55:
+            w.DestroyShape(holder[(id(w), "late")])
+            w.DestroyBody(sweeper)
+
+    res = parity.run_pair(build, steps=70, verbose=True, mutate=mutate)
+    assert res["max_rel_err"] == 0.0 and res["sensor_events"] > 40
