@@ -74,8 +74,13 @@ B2C_HD V2 solveSimplex3(Simplex& s) {                 // :167-215
   s.v1.a = d123_1 * inv; s.v2.a = d123_2 * inv; s.v3.a = d123_3 * inv; s.count = 3;
   return mk(0, 0);
 }
-// ShapeDistance :219-318 with a fresh cache (count = 0)
-B2C_HD DistOut shapeDistance(const DistProxy& proxyA, const DistProxy& proxyB, Xf xfA, Xf xfB, bool useRadii) {
+// SimplexCache include/Collision.cs:779-788. count == 0: a fresh start.
+struct SimplexCache { int count; int indexA[3], indexB[3]; };
+// ShapeDistance :219-318. A warm cache (count > 0) goes through MakeSimplexFromCache as the port writes it (:100-135, quirk Q19): the B-side
+// vertex of every cached simplex point is read from proxyA (`wB = proxyA.points[indexB]`), in proxy A's frame. Where indexB is past proxy
+// A's last point the C# indexer throws IndexOutOfRangeException: *throws is set and the call returns (the caller reports it; nothing here
+// invents a result for a step the reference cannot finish). The cache is written back at the normal exit only (:307), as in the source.
+B2C_HD DistOut shapeDistanceCached(const DistProxy& proxyA, const DistProxy& proxyB, Xf xfA, Xf xfB, bool useRadii, SimplexCache& cache, bool* throws) {
   DistOut out; out.pointA = mk(0, 0); out.pointB = mk(0, 0); out.normal = mk(0, 0); out.distance = 0.0f; out.iterations = 0;
   DistProxy localB; localB.count = proxyB.count; localB.radius = 0.0f;
   Xf rel = invMulXf(xfA, xfB);
@@ -84,6 +89,16 @@ B2C_HD DistOut shapeDistance(const DistProxy& proxyA, const DistProxy& proxyB, X
   s.v1.indexA = 0; s.v1.indexB = 0; s.v1.wA = proxyA.pts[0]; s.v1.wB = localB.pts[0]; s.v1.a = 1; s.v1.w = s.v1.wA - s.v1.wB;
   s.v2 = s.v1; s.v3 = s.v1; s.v2.a = 0; s.v3.a = 0;
   s.count = 1;
+  if (cache.count > 0) {
+    s.count = cache.count;
+    SVertex* vs[3] = {&s.v1, &s.v2, &s.v3};
+    for (int k = 0; k < cache.count; k++) {
+      SVertex& v = *vs[k];
+      v.indexA = cache.indexA[k]; v.indexB = cache.indexB[k]; v.a = -1.0f;
+      if (v.indexA >= proxyA.count || v.indexB >= proxyA.count) { *throws = true; return out; }
+      v.wA = proxyA.pts[v.indexA]; v.wB = proxyA.pts[v.indexB]; v.w = v.wA - v.wB;
+    }
+  }
   V2 nonUnitNormal = mk(0, 0);
   int saveA1 = 0, saveA2 = 0, saveA3 = 0, saveB1 = 0, saveB2 = 0, saveB3 = 0;
   int iteration = 0;
@@ -123,6 +138,10 @@ B2C_HD DistOut shapeDistance(const DistProxy& proxyA, const DistProxy& proxyB, X
   out.normal = normal; out.distance = dist(la, lb);
   out.pointA = xfPoint(xfA, la); out.pointB = xfPoint(xfB, lb);
   out.iterations = iteration;
+  cache.count = s.count;                           // MakeSimplexCache :136-143
+  if (s.count > 0) { cache.indexA[0] = s.v1.indexA; cache.indexB[0] = s.v1.indexB; }
+  if (s.count > 1) { cache.indexA[1] = s.v2.indexA; cache.indexB[1] = s.v2.indexB; }
+  if (s.count > 2) { cache.indexA[2] = s.v3.indexA; cache.indexB[2] = s.v3.indexB; }
   if (useRadii && out.distance > 0.1f * kLinearSlop) {
     float rA = proxyA.radius, rB = proxyB.radius;
     out.distance = netMax(0.0f, out.distance - rA - rB);
@@ -130,6 +149,11 @@ B2C_HD DistOut shapeDistance(const DistProxy& proxyA, const DistProxy& proxyB, X
     out.pointB = mulSub(out.pointB, rB, normal);
   }
   return out;
+}
+
+B2C_HD DistOut shapeDistance(const DistProxy& proxyA, const DistProxy& proxyB, Xf xfA, Xf xfB, bool useRadii) {   // fresh cache
+  SimplexCache cache; cache.count = 0; bool throws = false;
+  return shapeDistanceCached(proxyA, proxyB, xfA, xfB, useRadii, cache, &throws);
 }
 
 B2C_HD V2 geomCentroid(const Geom& g) {              // GetCentroid include/Collision.cs:78,201,(polygon centroid),(segment lerp)

@@ -452,7 +452,7 @@ void World::updateShapeAABBs(HShape& s, Xf xf, int proxyType) {   // src/Shape.c
 
 // a sensor created after the upload: its slot in World.sensors starts with two empty overlap lists (src/Shape.cs:212-213)
 __global__ void k_sensor_created(WorldDev d, int sensorIndex, int shapeId) {
-  d.sensorShape[sensorIndex] = shapeId; d.sensorOverlapCount[2 * sensorIndex] = 0; d.sensorOverlapCount[2 * sensorIndex + 1] = 0;
+  d.sensorShape[sensorIndex] = shapeId; d.sensorOverlapCount[2 * sensorIndex] = 0; d.sensorOverlapCount[2 * sensorIndex + 1] = 0; d.sensorHitCount[sensorIndex] = 0;
 }
 int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g, int* shapeId) {
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
@@ -893,6 +893,9 @@ __global__ void k_destroy_sensor(WorldDev d, int sensorIndex, int shapeId, int l
       const int2* src = d.sensorOverlaps + ((size_t)lastIndex * 2 + p) * kSensorMaxOverlaps; int2* dst = d.sensorOverlaps + ((size_t)sensorIndex * 2 + p) * kSensorMaxOverlaps;
       for (int i = 0; i < m; i++) dst[i] = src[i];
     }
+    const int hits = d.sensorHitCount[lastIndex];
+    d.sensorHitCount[sensorIndex] = hits;
+    for (int i = 0; i < hits; i++) d.sensorHits[(size_t)sensorIndex * kSensorMaxHits + i] = d.sensorHits[(size_t)lastIndex * kSensorMaxHits + i];
     const int moved = d.sensorShape[lastIndex];
     d.sensorShape[sensorIndex] = moved; d.shapes[moved].sensorIndex = sensorIndex;
   }
@@ -1252,7 +1255,7 @@ int World::growSensors(int minSensors) {
   WorldDev& d = d_;
   CK(cudaSetDevice(device_));
   const int c = std::max(minSensors, capSensor_ + capSensor_ / 2 + 16);
-  RG(d.sensorShape, c); RG(d.sensorOverlaps, (size_t)c * 2 * kSensorMaxOverlaps); RG(d.sensorOverlapCount, (size_t)c * 2); RG(d.sensorScan, c + 1);
+  RG(d.sensorShape, c); RG(d.sensorOverlaps, (size_t)c * 2 * kSensorMaxOverlaps); RG(d.sensorOverlapCount, (size_t)c * 2); RG(d.sensorScan, c + 1); RG(d.sensorHits, (size_t)c * kSensorMaxHits); RG(d.sensorHitCount, c);
   // event buffers are mapped host memory: a larger copy replaces them once the stream has drained (the pending end events move over)
   CK(cudaStreamSynchronize(stream_));
   const int evCap = c * kSensorMaxOverlaps;
@@ -1449,7 +1452,7 @@ int World::upload() {
     capSensor_ = nSensor + (member ? 2 : std::max(16, nSensor / 4));
     d.sensorCount = nSensor; d.sensorCapacity = capSensor_; d.sensorEventCapacity = capSensor_ * kSensorMaxOverlaps;
     DA(d.sensorShape, int, capSensor_); DA(d.sensorOverlaps, int2, (size_t)capSensor_ * 2 * kSensorMaxOverlaps); DA(d.sensorOverlapCount, int, (size_t)capSensor_ * 2);
-    DA(d.sensorScan, int4, capSensor_ + 1);
+    DA(d.sensorScan, int4, capSensor_ + 1); DA(d.sensorHits, int2, (size_t)capSensor_ * kSensorMaxHits); DA(d.sensorHitCount, int, capSensor_);
     UP(d.sensorShape, sensorShapes_);
     if (member) {
       DA(d.sensorBeginEvents, B2CSensorEvent, d.sensorEventCapacity); DA(d.sensorEndEvents[0], B2CSensorEvent, d.sensorEventCapacity); DA(d.sensorEndEvents[1], B2CSensorEvent, d.sensorEventCapacity);
@@ -1519,11 +1522,12 @@ int World::synchronize() {
   CK(cudaSetDevice(device_));
   CK(cudaStreamSynchronize(stream_));
   if (batch_ && scalarsStale_) { CK(cudaMemcpy(hostScalars_, d_.sc, sizeof(Scalars), cudaMemcpyDeviceToHost)); scalarsStale_ = false; }
-  if (hostScalars_->errorFlags & ~(int)ERR_TOI_CANDIDATE) {   // TOI candidates are counted (counters.toiCandidates), the step uses the no-hit result
+  if (hostScalars_->errorFlags) {
     char buf[160]; snprintf(buf, sizeof(buf), "device error flags 0x%x (capacity/stack/overflow-color/TOI/sensor overlaps; see b2c_world.cuh ERR_*)", hostScalars_->errorFlags);
     uint32_t f = (uint32_t)hostScalars_->errorFlags;
     if (f & (ERR_CONTACT_CAPACITY | ERR_PAIR_CAPACITY | ERR_HASH_FULL | ERR_STACK_OVERFLOW)) return fail(B2C_E_CAPACITY, buf);
     if (f & ERR_OVERFLOW_COLOR) return fail(B2C_E_UNSUPPORTED, buf);
+    if (f & ERR_REFERENCE_THROWS) return fail(B2C_E_UNSUPPORTED, std::string(buf) + ": the C# reference throws IndexOutOfRangeException in this step (Distance.MakeSimplexFromCache reads B's cached vertex from proxy A, src/Distance.cs:116-132, reached from TimeOfImpact)");
     return fail(B2C_E_CUDA, buf);
   }
   return B2C_OK;

@@ -93,6 +93,11 @@ B2C_HD Rot normalizeRot(Rot q) {
   float mag = sqrtf(q.s * q.s + q.c * q.c), inv = mag > 0.0f ? 1.0f / mag : 0.0f;
   return mkRot(q.c * inv, q.s * inv);
 }
+B2C_HD Rot nlerpRot(Rot q1, Rot q2, float t) {       // Rotation.NLerp include/MathFunctions.cs:139-144
+  Rot q = mkRot(q1.c + (q2.c - q1.c) * t, q1.s + (q2.s - q1.s) * t);
+  float mag = sqrtf(q.c * q.c + q.s * q.s), inv = mag > 0.0f ? 1.0f / mag : 0.0f;
+  return mkRot(q.c * inv, q.s * inv);
+}
 B2C_HD Rot integrateRot(Rot q, float deltaAngle) {
   Rot q2 = mkRot(q.c - deltaAngle * q.s, q.s + deltaAngle * q.c);
   float mag = sqrtf(q2.s * q2.s + q2.c * q2.c), inv = mag > 0.0f ? 1.0f / mag : 0.0f;

@@ -16,15 +16,26 @@ constexpr int kSensorStack = 128;
 __device__ __forceinline__ int2* sensorList(const WorldDev& d, int i, int parity) { return d.sensorOverlaps + ((size_t)i * 2 + parity) * kSensorMaxOverlaps; }
 
 // overlaps2 of one sensor into `out` (sorted by shape id); returns the count
-__device__ inline int sensorQuery(const WorldDev& d, int sensorShapeId, int2* out) {
+__device__ inline int sensorQuery(const WorldDev& d, int sensorIndex, int sensorShapeId, int2* out) {
   Scalars& s = *d.sc;
   const ShapeDev& ss = d.shapes[sensorShapeId];
-  if (!(ss.flags & SF_SENSOR_EVENTS)) return 0;          // :96-101 (the disabled set does not exist here)
+  int n = 0;
+  {                                                      // :90-93 overlaps2 starts with the continuous hits of this step
+    const int hits = min(d.sensorHitCount[sensorIndex], kSensorMaxHits);
+    const int2* h = d.sensorHits + (size_t)sensorIndex * kSensorMaxHits;
+    for (int i = 0; i < hits; i++) {
+      int k = 0; while (k < n && out[k].x < h[i].x) k++;
+      if (k < n && out[k].x == h[i].x) continue;         // the unique pass (:111-116) keeps the first of equal shape ids
+      for (int m = n; m > k; m--) out[m] = out[m - 1];
+      out[k] = h[i]; n++;
+    }
+    d.sensorHitCount[sensorIndex] = 0;
+  }
+  if (!(ss.flags & SF_SENSOR_EVENTS)) return n;          // :96-101 (the disabled set does not exist here): the hits stay, nothing is queried
   const float4 xa = d.bodyXf[ss.bodyId];
   const Xf xfA = mkXf(mk(xa.x, xa.y), mkRot(xa.z, xa.w));
   const Box bounds = toBox(d.shapeAABB[sensorShapeId]);
   const DistProxy proxyA = makeDistProxy(ss.geom);
-  int n = 0;
   for (int tt = 0; tt < 3; tt++) {
     const TreeDev& t = d.trees[tt];
     int root = t.meta[0];
@@ -50,9 +61,10 @@ __device__ inline int sensorQuery(const WorldDev& d, int sensorShapeId, int2* ou
       DistOut o = shapeDistance(proxyA, makeDistProxy(so.geom), xfA, mkXf(mk(xb.x, xb.y), mkRot(xb.z, xb.w)), true);
       if (o.distance >= 10.0f * 1.192092896e-07f) continue;
       if (n >= kSensorMaxOverlaps) { atomicOr(&s.errorFlags, (int)ERR_SENSOR_CAPACITY); continue; }
-      int k = n++;                                       // insertion by shape id (a shape sits in one tree: no duplicates)
-      while (k > 0 && out[k - 1].x > other) { out[k] = out[k - 1]; k--; }
-      out[k] = make_int2(other, (int)so.generation);
+      int k = 0; while (k < n && out[k].x < other) k++;  // insertion by shape id; a shape sits in one tree, but a continuous hit may have brought it already
+      if (k < n && out[k].x == other) continue;
+      for (int m = n; m > k; m--) out[m] = out[m - 1];
+      out[k] = make_int2(other, (int)so.generation); n++;
     }
   }
   return n;
@@ -88,7 +100,7 @@ template <class S> __device__ void phase_sensors(const S& grid, const WorldDev& 
   for (int i = tid; i < n; i += stride) {
     const int shapeId = d.sensorShape[i];
     int2* o2 = sensorList(d, i, parity); const int2* o1 = sensorList(d, i, 1 - parity);
-    const int count2 = sensorQuery(d, shapeId, o2), count1 = d.sensorOverlapCount[2 * i + 1 - parity];
+    const int count2 = sensorQuery(d, i, shapeId, o2), count1 = d.sensorOverlapCount[2 * i + 1 - parity];
     d.sensorOverlapCount[2 * i + parity] = count2;
     B2CShapeRef ref; ref.shapeId = shapeId; ref.generation = d.shapes[shapeId].generation;
     int2 c = sensorMerge<false>(o1, count1, o2, count2, ref, nullptr, nullptr);   // equal lists produce no events: the eventBits test (:118-127) is implied

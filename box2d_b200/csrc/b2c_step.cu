@@ -1173,31 +1173,85 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
 
 }  // namespace b2c
 #include "b2c_islands.cuh"
+#include "b2c_toi.cuh"
 namespace b2c {
 
 // ------------------------------------------------------------------------------------------------------------
 // Phase 3: FinalizeBodiesTask (src/Solver.cs:402-503) + refit (:1191-1237, src/DynamicTree.cs:482-505)
 // ------------------------------------------------------------------------------------------------------------
-__device__ inline int countToiCandidates(const WorldDev& d, Box query, int fastShape, int fastBody) {   // ContinuousQueryCallback :224-253 (static tree)
+// World.SolveContinuous (src/Solver.cs:315-401) for a non-bullet fast body: every shape of the body sweeps the static tree with the union
+// of its old and new boxes (DynamicTree.Query order: child2 first), ContinuousQueryCallback (:224-314) runs TimeOfImpact on every
+// candidate in that order with the running fraction as the sweep limit, and the smallest positive fraction wins. Returns that fraction
+// (1 = no hit). Sensor shapes in the static tree collect the visitors whose sweep reaches them before the hit (Sensor.hits).
+constexpr int kContinuousSensorHits = 8;
+__device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf xf2, const Sweep& sweep, uint32_t* simFlags) {
+  Scalars& sc = *d.sc;
+  float fraction = 1.0f;
+  int hitSensor[kContinuousSensorHits], hitVisitor[kContinuousSensorHits]; float hitFraction[kContinuousSensorHits]; int nSensorHits = 0;
   const TreeDev& t = d.trees[kStaticBody];
-  int root = t.meta[0];
-  if (t.meta[1] == 0 || root == -1) return 0;
-  int stack[kQueryStack]; int sp = 0, found = 0;
-  stack[sp++] = root;
-  while (sp > 0) {
-    int id = stack[--sp];
-    if (!boxOverlaps(toBox(t.aabb[id]), query) || t.cat[id] == 0) continue;
-    if ((t.hf[id] >> 16) & NODE_LEAF) {
-      int other = t.user[id];
-      if (other == fastShape) break;
-      const ShapeDev& so = d.shapes[other];
-      if (so.bodyId == fastBody) continue;
-      if (!shouldShapesCollide(d.shapes[fastShape], so)) continue;
-      if (!shouldBodiesCollide(d, fastBody, so.bodyId)) continue;
-      found++;
-    } else if (sp + 2 <= kQueryStack) { int2 c = t.child[id]; stack[sp++] = c.x; stack[sp++] = c.y; }
+  for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+    const ShapeDev& fastShape = d.shapes[sid];
+    Box box1 = toBox(d.shapeAABB[sid]);
+    Box box2 = geomAABB(fastShape.geom, xf2);
+    d.shapeAABB[sid] = fromBox(box2);                    // raw AABB, no speculative margin (:337-339)
+    if (fastShape.sensorIndex != -1) continue;
+    const Box query = boxUnion(box1, box2);
+    int root = t.meta[0];
+    if (t.meta[1] == 0 || root == -1) continue;
+    const DistProxy proxyB = makeDistProxy(fastShape.geom);
+    int stack[kQueryStack]; int sp = 0;
+    stack[sp++] = root;
+    while (sp > 0) {
+      int id = stack[--sp];
+      if (!boxOverlaps(toBox(t.aabb[id]), query) || t.cat[id] == 0) continue;      // DEFAULT_MASK_BITS: only category 0 fails the mask test
+      if (!((t.hf[id] >> 16) & NODE_LEAF)) {
+        if (sp + 2 <= kQueryStack) { int2 c = t.child[id]; stack[sp++] = c.x; stack[sp++] = c.y; } else atomicOr(&sc.errorFlags, (int)ERR_STACK_OVERFLOW);
+        continue;
+      }
+      const int other = t.user[id];
+      if (other == sid) break;                           // the callback returns false: this query ends (:230)
+      const ShapeDev& shape = d.shapes[other];
+      if (shape.bodyId == bodyId) continue;
+      const bool isSensor = shape.sensorIndex != -1;
+      if (isSensor && (!(shape.flags & SF_SENSOR_EVENTS) || !(fastShape.flags & SF_SENSOR_EVENTS))) continue;
+      if (!shouldShapesCollide(fastShape, shape)) continue;
+      if (d.bodySimFlags[shape.bodyId] & kIsBullet) continue;
+      if (!shouldBodiesCollide(d, bodyId, shape.bodyId)) continue;
+      // (custom filter and chain segments cannot exist: refused at creation)
+      const float4 oxf = d.bodyXf[shape.bodyId]; const float2 oc = d.bodyCenter[shape.bodyId]; const float4 om = d.bodyMass[shape.bodyId];
+      Sweep sweepA; sweepA.localCenter = mk(om.z, om.w); sweepA.c1 = mk(oc.x, oc.y); sweepA.c2 = sweepA.c1; sweepA.q1 = mkRot(oxf.z, oxf.w); sweepA.q2 = sweepA.q1;   // BodySim.MakeSweep of a body at rest in the static set
+      const DistProxy proxyA = makeDistProxy(shape.geom);
+      bool throws = false;
+      atomicAdd(&sc.toiCandidates, 1);
+      ToiOut output = timeOfImpact(proxyA, proxyB, sweepA, sweep, fraction, &throws);
+      if (throws) { atomicOr(&sc.errorFlags, (int)ERR_REFERENCE_THROWS); continue; }
+      if (isSensor) {
+        if (output.fraction <= fraction) {
+          if (nSensorHits < kContinuousSensorHits) { hitSensor[nSensorHits] = other; hitVisitor[nSensorHits] = sid; hitFraction[nSensorHits] = output.fraction; nSensorHits++; }
+          else atomicOr(&sc.errorFlags, (int)ERR_SENSOR_CAPACITY);
+        }
+        continue;
+      }
+      float hit = fraction; bool didHit = false;
+      if (0.0f < output.fraction && output.fraction < fraction) { hit = output.fraction; didHit = true; }
+      else if (0.0f == output.fraction) {                // :291-299 fall back to the shape's core: a point of a quarter of the minimum extent at the centroid
+        DistProxy core; for (int k = 0; k < kMaxPolygonVertices; k++) core.pts[k] = mk(0, 0);
+        core.pts[0] = geomCentroid(fastShape.geom); core.count = 1; core.radius = 0.25f * geomMinExtent(fastShape.geom);
+        output = timeOfImpact(proxyA, core, sweepA, sweep, fraction, &throws);
+        if (throws) { atomicOr(&sc.errorFlags, (int)ERR_REFERENCE_THROWS); continue; }
+        if (0.0f < output.fraction && output.fraction < fraction) { hit = output.fraction; didHit = true; }
+      }
+      if (didHit) { *simFlags |= kHadTimeOfImpact; fraction = hit; }
+    }
   }
-  return found;
+  for (int k = 0; k < nSensorHits; k++) {                // :398-400, then src/Solver.cs:1276-1289
+    if (!(hitFraction[k] < fraction)) continue;
+    const int sensorIndex = d.shapes[hitSensor[k]].sensorIndex;
+    int slot = atomicAdd(&d.sensorHitCount[sensorIndex], 1);
+    if (slot < kSensorMaxHits) d.sensorHits[(size_t)sensorIndex * kSensorMaxHits + slot] = make_int2(hitVisitor[k], (int)d.shapes[hitVisitor[k]].generation);
+    else atomicOr(&sc.errorFlags, (int)ERR_SENSOR_CAPACITY);
+  }
+  return fraction;
 }
 
 __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int stride) {
@@ -1231,23 +1285,38 @@ __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int
     else d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
     int enlarged = 0;
     if (isFast) {
-      // SolveContinuous :315-401 for a non-bullet body, no-hit result; a would-be TOI candidate is reported, never ignored
-      int candidates = 0;
-      for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
-        Box box1 = toBox(d.shapeAABB[sid]);
-        Box box2 = geomAABB(d.shapes[sid].geom, xf);
-        d.shapeAABB[sid] = fromBox(box2);               // raw AABB, no speculative margin (:337-339)
-        candidates += countToiCandidates(d, boxUnion(box1, box2), sid, bodyId);
-      }
-      if (candidates) { atomicAdd(&d.sc->toiCandidates, candidates); atomicOr(&d.sc->errorFlags, (int)ERR_TOI_CANDIDATE); }
-      d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
-      for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
-        Box aabb = toBox(d.shapeAABB[sid]);
-        if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
-          d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
-          d.shapes[sid].flags |= SF_ENLARGED;
-          simFlags |= kEnlargeBounds;
-          enlarged++;
+      // SolveContinuous :315-401 (non-bullet body: static tree only)
+      float4 pose0 = d.simPose0[i];
+      Sweep sweep; sweep.localCenter = localCenter; sweep.c1 = mk(pose0.x, pose0.y); sweep.c2 = center; sweep.q1 = mkRot(pose0.z, pose0.w); sweep.q2 = q;   // BodySim.MakeSweep src/Body.cs:172
+      const float fraction = solveContinuous(d, bodyId, xf, sweep, &simFlags);
+      if (fraction < 1.0f) {                             // :356-379 the body stops at the time of impact
+        q = nlerpRot(sweep.q1, sweep.q2, fraction);
+        center = lerp(sweep.c1, sweep.c2, fraction);
+        xf = mkXf(center - rotate(q, localCenter), q);
+        d.simPose[i] = make_float4(center.x, center.y, q.c, q.s);
+        d.bodyXf[bodyId] = make_float4(xf.p.x, xf.p.y, q.c, q.s);
+        d.bodyCenter[bodyId] = make_float2(center.x, center.y);
+        d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
+        for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+          Box aabb = boxGrow(geomAABB(d.shapes[sid].geom, xf), kSpeculativeDistance);
+          d.shapeAABB[sid] = fromBox(aabb);
+          if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
+            d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
+            d.shapes[sid].flags |= SF_ENLARGED;
+            simFlags |= kEnlargeBounds;
+            enlarged++;
+          }
+        }
+      } else {                                           // :380-397
+        d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
+        for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+          Box aabb = toBox(d.shapeAABB[sid]);
+          if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
+            d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
+            d.shapes[sid].flags |= SF_ENLARGED;
+            simFlags |= kEnlargeBounds;
+            enlarged++;
+          }
         }
       }
     } else {

@@ -16,7 +16,8 @@ enum : uint32_t {
   CF_DISJOINT = 0x100u, CF_STARTED = 0x200u, CF_STOPPED = 0x400u, CF_STATE_MASK = 0x700u
 };
 enum : uint32_t { ERR_CONTACT_CAPACITY = 1u, ERR_STACK_OVERFLOW = 2u, ERR_OVERFLOW_COLOR = 4u, ERR_PAIR_CAPACITY = 8u,
-                  ERR_TOI_CANDIDATE = 16u, ERR_HASH_FULL = 32u, ERR_TREE = 64u, ERR_SENSOR_CAPACITY = 128u };
+                  ERR_TOI_CANDIDATE = 16u, ERR_HASH_FULL = 32u, ERR_TREE = 64u, ERR_SENSOR_CAPACITY = 128u,
+                  ERR_REFERENCE_THROWS = 256u };   // the C# reference throws here (IndexOutOfRangeException in Distance.MakeSimplexFromCache, quirk Q19): the step is reported as failed
 enum : uint16_t { NODE_ALLOCATED = 1, NODE_ENLARGED = 2, NODE_LEAF = 4 };   // src/DynamicTree.cs TreeNodeFlags
 
 // ---- dynamic AABB tree replica (src/DynamicTree.cs:11-32 TreeNode, SoA) ----
@@ -41,6 +42,7 @@ struct TreeDev {
   int stackCapacity;
 };
 
+constexpr int kSensorMaxHits = 16;       // continuous-collision hits one sensor can collect in one step (Sensor.hits, src/Solver.cs:1276-1289)
 constexpr int kSensorMaxOverlaps = 64;   // shapes one sensor can overlap at a time (src/Sensor.cs overlaps2); more sets ERR_SENSOR_CAPACITY and the step fails loudly
 
 struct ShapeDev {      // src/Shape.cs:25-52 (hot subset) — one AoS row per shapeId, 16-byte aligned
@@ -235,6 +237,8 @@ struct WorldDev {
   int* sensorShape;          // [sensorCapacity] Sensor.shapeId
   int2* sensorOverlaps;      // [sensorCapacity][2][kSensorMaxOverlaps] (shapeId, generation); list Scalars.sensorParity is overlaps2, the other overlaps1
   int* sensorOverlapCount;   // [sensorCapacity][2]
+  int2* sensorHits;          // [sensorCapacity][kSensorMaxHits] Sensor.hits: visitors whose swept core crossed the sensor this step (TOI), any order
+  int* sensorHitCount;       // [sensorCapacity]
   int4* sensorScan;          // [sensorCapacity + 1] per sensor (begin events, end events, 0, 0) -> exclusive offsets
   B2CSensorEvent* sensorBeginEvents; B2CSensorEvent* sensorEndEvents[2];
   int sensorCount, sensorCapacity, sensorEventCapacity;

@@ -228,6 +228,43 @@ def sensor_field(world, n=60, seed=21):
     return sensors, bodies, carrier, sweeper
 
 
+def fast_rain(world, n=48, seed=5, walls="box"):
+    """Continuous collision (src/Solver.cs:315-401): small fast bodies fired at thin static walls and a thin floor, so that without a time of
+    impact they would tunnel; a static sensor strip in front of the floor collects continuous sensor hits. walls="box": every static shape
+    is a polygon (4 points: the port's cached-simplex read stays in range); walls="segment": segment walls, for which the C# code throws."""
+    sd = _shape_def(enableSensorEvents=1)
+    ground = world.CreateBody(api.default_body_def())
+    if walls == "box":
+        world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(20.0, 0.05, (0.0, -0.05)))
+        world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(0.05, 6.0, (12.0, 6.0)))
+        world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(0.05, 6.0, (-12.0, 6.0)))
+        world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(0.6, 0.6, (0.0, 1.0), geo.MakeRot(0.4)))
+        world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(1.5, 0.1, (5.5, 1.0), geo.MakeRot(0.25)))
+    elif walls == "round":        # a static circle (1 point) and capsule (2 points): a fast box or capsule indexes past them -> the C# code throws
+        world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(20.0, 0.05, (0.0, -0.05)))
+        world.CreateCircleShape(ground, sd, geo.Circle((0.0, 1.0), 0.6))
+        world.CreateCapsuleShape(ground, sd, geo.Capsule((4.0, 0.6), (7.0, 1.4), 0.15))
+    else:
+        world.CreateSegmentShape(ground, sd, geo.Segment((-20.0, 0.0), (20.0, 0.0)))
+    strip = world.CreatePolygonShape(ground, _shape_def(isSensor=1, enableSensorEvents=1), geo.MakeOffsetBox(20.0, 0.1, (0.0, 0.5)))
+    shapes = [geo.Circle((0.0, 0.0), 0.08), geo.Capsule((-0.1, 0.0), (0.1, 0.0), 0.05), geo.MakeBox(0.1, 0.06), geo.MakeRoundedBox(0.06, 0.06, 0.03),
+              geo.Circle((0.05, 0.0), 0.06)]
+    state = seed
+    bodies = []
+    for k in range(n):
+        state, x = _uniform(state, -10.0, 10.0)
+        state, y = _uniform(state, 3.0, 9.0)
+        state, vx = _uniform(state, -60.0, 60.0)
+        state, vy = _uniform(state, -150.0, -20.0)
+        state, w = _uniform(state, -20.0, 20.0)
+        b = _dynamic_body(world, x, y, linearVelocity=api.Vec2(vx, vy), angularVelocity=w)
+        world.CreateShape(b, sd, shapes[k % len(shapes)])
+        if k % 6 == 0:
+            world.CreateCircleShape(b, sd, geo.Circle((0.0, 0.1), 0.04))
+        bodies.append(b)
+    return ground, strip, bodies
+
+
 def overflow_plank(world, n=26):
     """A long dynamic plank resting on n small dynamic boxes: the plank needs more than the 20 dynamic colours, so some
     contacts land in the overflow colour (src/ConstraintGraph.cs:140) and are solved by the scalar overflow path."""
@@ -432,6 +469,7 @@ def batched_pyramids(world, n_worlds=8192, first=0, rows=10, pitch=15.0, cols=12
 
 
 SCENES = {
+    "fast_rain": fast_rain,
     "sensor_field": sensor_field,
     "large_pyramid": large_pyramid,
     "many_pyramids": many_pyramids,

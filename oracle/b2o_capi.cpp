@@ -132,7 +132,12 @@ int32_t b2o_world_set_contact_tuning(World* w, float hertz, float damping, float
   w->contactHertz = netClamp(hertz, 0, FLT_MAX); w->contactDampingRatio = netClamp(damping, 0, FLT_MAX); w->contactSpeed = netClamp(pushSpeed, 0, FLT_MAX);
   return 0;
 }
-int32_t b2o_world_step(World* w, float dt, int32_t sub) { w->Step(dt, sub); return 0; }
+int32_t b2o_world_step(World* w, float dt, int32_t sub) {
+  int before = w->counters.referenceThrows;
+  w->Step(dt, sub);
+  if (w->counters.referenceThrows != before) { w->lastError = "the C# reference throws IndexOutOfRangeException in this step (Distance.MakeSimplexFromCache, src/Distance.cs:116-132)"; return B2C_E_UNSUPPORTED; }
+  return 0;
+}
 int32_t b2o_world_synchronize(World*) { return 0; }
 
 static thread_local std::vector<B2CContactTouchEvent> tBegin, tEnd;

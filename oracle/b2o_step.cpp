@@ -14,44 +14,7 @@ static bool ShouldShapesCollideF(const Filter& a, const Filter& b) {
   return (a.maskBits & b.categoryBits) != 0 && (a.categoryBits & b.maskBits) != 0;
 }
 
-// Non-bullet fast body: queries the static tree only. TOI itself is not restated; a candidate that
-// would reach TimeOfImpact is counted in counters.toiCandidates and treated as "no hit".
-void World::SolveContinuous(int bodySimIndex) {
-  BodySim& fastBodySim = awakeSet.bodySims[bodySimIndex];
-  Transform xf2; xf2.q = fastBodySim.transform.q; xf2.p = fastBodySim.center - RotateVector(fastBodySim.transform.q, fastBodySim.localCenter);   // :321-322
-  Body& fastBody = bodies[fastBodySim.bodyId];
-  int shapeId = fastBody.headShapeId;
-  while (shapeId != -1) {
-    Shape& fastShape = shapes[shapeId];
-    shapeId = fastShape.nextShapeId;
-    AABB box1 = fastShape.aabb;
-    AABB box2 = ComputeAABB(fastShape.geom, xf2);
-    fastShape.aabb = box2;                                  // :337-339 raw AABB, no speculative margin
-    if (fastShape.sensorIndex != -1) continue;
-    trees[kStaticBody].Query(Union(box1, box2), ~0ull, [&](int, uint64_t userData) -> bool {    // ContinuousQueryCallback :224-253
-      int otherId = (int)userData;
-      if (otherId == fastShape.id) return false;
-      const Shape& shape = shapes[otherId];
-      if (shape.bodyId == fastShape.bodyId) return true;
-      if (!ShouldShapesCollideF(fastShape.filter, shape.filter)) return true;
-      if (!ShouldBodiesCollide(fastBody, bodies[shape.bodyId])) return true;
-      counters.toiCandidates++;
-      return true;
-    });
-  }
-  // fraction == 1 (:380-397)
-  fastBodySim.rotation0 = fastBodySim.transform.q; fastBodySim.center0 = fastBodySim.center;
-  shapeId = fastBody.headShapeId;
-  while (shapeId != -1) {
-    Shape& shape = shapes[shapeId];
-    if (!Contains(shape.fatAABB, shape.aabb)) {
-      shape.fatAABB = {{shape.aabb.lo.x - kAABBMargin, shape.aabb.lo.y - kAABBMargin}, {shape.aabb.hi.x + kAABBMargin, shape.aabb.hi.y + kAABBMargin}};
-      shape.enlargedAABB = true;
-      fastBodySim.flags |= kEnlargeBounds;
-    }
-    shapeId = shape.nextShapeId;
-  }
-}
+// World::SolveContinuous lives in b2o_continuous.inc (it needs the GJK code of b2o_distance.inc).
 
 void World::FinalizeBodies(StepContext& stepContext, BitSet& enlargedSimBitSet) {     // :402-503
   int n = (int)awakeSet.bodySims.size();

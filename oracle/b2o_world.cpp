@@ -714,5 +714,6 @@ void World::SetGravityScale(int bodyId, float v) { GetBodySim(bodies[bodyId]).gr
 
 #include "b2o_distance.inc"
 #include "b2o_sensor.inc"
+#include "b2o_continuous.inc"
 
 }  // namespace b2o

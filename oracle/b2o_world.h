@@ -202,7 +202,7 @@ struct StepContext {            // src/Solver.cs:57-112
   int activeColorCount = 0; int activeColorIndices[kGraphColorCount];
 };
 
-struct Counters { int toiCandidates = 0, unsupported = 0; };
+struct Counters { int toiCandidates = 0, unsupported = 0, referenceThrows = 0; };   // referenceThrows: the C# code raises an exception at that point of the step
 
 class World {
  public:

@@ -23,7 +23,7 @@ def _builders():
     out.append(lambda w: scenes.wheel_rig(w, copies=1))
     out.append(lambda w: scenes.bounce_mix(w, n=24, seed=2))
     out.append(lambda w: scenes.joint_grid(w, n=6))
-    out.append(lambda w: scenes.sensor_field(w, n=30))          # sensors at CTA scope
+    out.append(lambda w: scenes.fast_rain(w, n=30))             # continuous collision + sensors (a polygon strip) at CTA scope
     out.append(lambda w: None)                                  # an empty world inside a batch
     return out
 

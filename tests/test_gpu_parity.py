@@ -1,4 +1,5 @@
 """-m gpu: the CUDA step vs the oracle through the C-ABI, bit-exact unless a tolerance is stated."""
+import numpy as np
 import pytest
 import parity
 from box2d_b200 import api, scenes, geometry as geo
@@ -961,7 +962,8 @@ def test_random_churn_of_creation_and_destruction_bit_exact(seed):
     identically to both backends for 120 steps: ids handed out, events, colours and every body state must agree exactly. (This test found
     the sticky EnlargeBounds bit that a body carries into the static set.)"""
     build, mutate = _churn(seed, 120, 40)
-    res = parity.run_pair(build, steps=120, mutate=mutate, verbose=True)
+    # continuous collision off: explosions make bodies fast next to the terrain segments, where the C# TimeOfImpact throws (see test_continuous_collision_where_the_reference_throws)
+    res = parity.run_pair(build, steps=120, mutate=mutate, verbose=True, world_def=scenes.world_def(enable_continuous=False))
     assert res["max_rel_err"] == 0.0
 
 
@@ -1180,9 +1182,12 @@ def test_sensor_events_bit_exact():
         holder[w.backend.name] = scenes.sensor_field(w)
 
 
-    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    # continuous collision off: the falling boxes and capsules become fast next to the static circle / capsule sensors, where the C#
+    # TimeOfImpact indexes past proxy A and throws (test_continuous_collision_where_the_reference_throws); fast_rain covers continuous sensor hits
+    wd = scenes.world_def(enable_continuous=False)
+    cuda = api.World(api.CudaBackend(), wd)
     from oracle_backend import OracleBackend
-    orc = api.World(OracleBackend(), scenes.world_def())
+    orc = api.World(OracleBackend(), wd)
     try:
         build(cuda), build(orc)
         total = 0
@@ -1228,5 +1233,72 @@ def test_sensor_mutations_between_steps_bit_exact():
             w.DestroyShape(holder[(id(w), "late")])
             w.DestroyBody(sweeper)
 
-    res = parity.run_pair(build, steps=70, verbose=True, mutate=mutate)
+    res = parity.run_pair(build, steps=70, verbose=True, mutate=mutate, world_def=scenes.world_def(enable_continuous=False))   # see test_sensor_events_bit_exact
     assert res["max_rel_err"] == 0.0 and res["sensor_events"] > 40
+
+
+def test_continuous_collision_bit_exact():
+    """World.SolveContinuous + Distance.TimeOfImpact as the port behaves (src/Solver.cs:224-401, src/Distance.cs:529-646): fast bodies
+    against thin static polygons; bodies stopped at a time of impact (HadTimeOfImpact), bodies the port lets tunnel (its cached-simplex
+    read, quirk Q19, derails most sweeps after the first GJK call) and continuous sensor hits must all equal the oracle's."""
+    res = parity.run_pair(lambda w: scenes.fast_rain(w, n=64), steps=45, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    assert res["toi"] > 100 and res["toi"] == res["toi_oracle"], res
+    res = parity.run_pair(lambda w: scenes.fast_rain(w, n=40, seed=77), steps=30, substeps=2, dt=1.0 / 30.0)
+    assert res["max_rel_err"] == 0.0 and res["toi"] == res["toi_oracle"]
+
+
+@pytest.mark.parametrize("walls", ["round", "segment"])
+def test_continuous_collision_where_the_reference_throws(walls):
+    """A fast polygon or capsule swept against a static shape with fewer points makes the C# code index past proxy A
+    (Distance.MakeSimplexFromCache, src/Distance.cs:116-132): IndexOutOfRangeException out of WorldAPI.Step. Both sides must report it,
+    in the same step, instead of inventing a result."""
+    from oracle_backend import OracleBackend
+    failed = {}
+    for name, be in (("cuda", api.CudaBackend()), ("oracle", OracleBackend())):
+        w = api.World(be, scenes.world_def())
+        try:
+            scenes.fast_rain(w, walls=walls)
+            failed[name] = None
+            for step in range(60):
+                try:
+                    w.Step(1.0 / 60.0, 4)
+                    w.GetCounters()                    # the device reports at the next synchronising call
+                except api.B2Error as e:
+                    assert "throws" in str(e)
+                    failed[name] = step
+                    break
+        finally:
+            w.Destroy()
+    assert failed["cuda"] == failed["oracle"], failed
+    if walls == "round":
+        assert failed["cuda"] is not None
+
+
+def test_continuous_parallel_motion_is_not_stopped():
+    """Known answer: a fast circle flying parallel to a thin static box, 0.1 m above it (distance 0.1 > target 0.075 + tolerance: TimeOfImpact returns Separated), is a TOI candidate every step (the swept boxes
+    overlap the fat box) and is never stopped: x advances by v*dt per step exactly as free flight, on both backends."""
+    from box2d_b200 import geometry as G
+
+    def build(w):
+        ground = w.CreateBody(api.default_body_def())
+        w.CreatePolygonShape(ground, scenes._shape_def(), G.MakeOffsetBox(50.0, 0.05, (0.0, -0.05)))
+        b = scenes._dynamic_body(w, -20.0, 0.1, linearVelocity=api.Vec2(120.0, 0.0), gravityScale=0.0)
+        w.CreateCircleShape(b, scenes._shape_def(), G.Circle((0.0, 0.0), 0.08))
+
+    res = parity.run_pair(build, steps=12)
+    assert res["max_rel_err"] == 0.0 and res["toi"] >= 10
+    w = api.World(api.CudaBackend(), scenes.world_def())
+    try:
+        build(w)
+        h = np.float32(np.float32(1.0 / 60.0) / np.float32(4))
+        x = np.float32(-20.0)
+        for _ in range(12):
+            w.Step(1.0 / 60.0, 4)
+            dx = np.float32(0.0)
+            for _ in range(4):
+                dx = np.float32(dx + np.float32(h * np.float32(120.0)))
+            x = np.float32(x + dx)
+        assert np.float32(w.ReadBodies()[1]["transform"]["p"]["x"]) == x
+    finally:
+        w.Destroy()
