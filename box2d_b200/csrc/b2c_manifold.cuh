@@ -389,6 +389,139 @@ __device__ inline Manifold collidePolygons(const Geom& polygonA, Xf xfA, const G
   return m;
 }
 
+// ---- the same function with the vertex counts known at compile time (boxes: 4 x 4). Every loop unrolls, the vertex and normal arrays live
+// in registers (the few run-time indexed reads go through select chains) and the 32 independent dot products of the two FindMaxSeparation
+// passes overlap instead of running as one dependent chain out of local memory. Operation for operation the arithmetic of collidePolygons
+// above: each value is computed by the same expression, comparisons run in the same order, nothing is contracted (-fmad=false).
+template <int C> struct PolyT { float radius; V2 v[C], n[C]; };
+template <int C> __device__ __forceinline__ V2 pickT(const V2 (&arr)[C], int i) {
+  V2 r = arr[0];
+#pragma unroll
+  for (int k = 1; k < C; k++) if (i == k) r = arr[k];
+  return r;
+}
+template <int C1, int C2> __device__ __forceinline__ float findMaxSeparationT(int* edgeIndex, const PolyT<C1>& poly1, const PolyT<C2>& poly2) {
+  int bestIndex = 0;
+  float maxSeparation = -FLT_MAX;
+#pragma unroll
+  for (int i = 0; i < C1; i++) {
+    V2 n = poly1.n[i], v1 = poly1.v[i];
+    float si = FLT_MAX;
+#pragma unroll
+    for (int j = 0; j < C2; j++) { float sij = dot(n, poly2.v[j] - v1); if (sij < si) si = sij; }
+    if (si > maxSeparation) { maxSeparation = si; bestIndex = i; }
+  }
+  *edgeIndex = bestIndex;
+  return maxSeparation;
+}
+// ClipPolygons (src/Manifold.cs:329-388) on picked vertices: (normal, v11, v12) from the reference polygon, (v21, v22) from the incident one
+__device__ __forceinline__ Manifold clipPicked(V2 normal, V2 v11, V2 v12, V2 v21, V2 v22, float r1, float r2, int i11, int i12, int i21, int i22, bool flip) {
+  Manifold m = emptyManifold();
+  V2 tangent = crossSV(1.0f, normal);
+  float lower1 = 0.0f;
+  float upper1 = dot(v12 - v11, tangent);
+  float upper2 = dot(v21 - v11, tangent);
+  float lower2 = dot(v22 - v11, tangent);
+  if (upper2 < lower1 || upper1 < lower2) return m;
+  V2 vLower = (lower2 < lower1 && upper2 - lower2 > kEps) ? lerp(v22, v21, (lower1 - lower2) / (upper2 - lower2)) : v22;
+  V2 vUpper = (upper2 > upper1 && upper2 - lower2 > kEps) ? lerp(v22, v21, (upper1 - lower2) / (upper2 - lower2)) : v21;
+  float separationLower = dot(vLower - v11, normal);
+  float separationUpper = dot(vUpper - v11, normal);
+  vLower = mulAdd(vLower, 0.5f * (r1 - r2 - separationLower), normal);
+  vUpper = mulAdd(vUpper, 0.5f * (r1 - r2 - separationUpper), normal);
+  float radius = r1 + r2;
+  if (!flip) {
+    m.normal = normal;
+    m.p0.anchorA = vLower; m.p0.separation = separationLower - radius; m.p0.id = makeId(i11, i22);
+    m.p1.anchorA = vUpper; m.p1.separation = separationUpper - radius; m.p1.id = makeId(i12, i21);
+  } else {
+    m.normal = -normal;
+    m.p0.anchorA = vUpper; m.p0.separation = separationUpper - radius; m.p0.id = makeId(i21, i12);
+    m.p1.anchorA = vLower; m.p1.separation = separationLower - radius; m.p1.id = makeId(i22, i11);
+  }
+  m.pointCount = 2;
+  return m;
+}
+template <int CA, int CB> __device__ inline Manifold collidePolygonsT(const Geom& polygonA, Xf xfA, const Geom& polygonB, Xf xfB) {
+  V2 origin = polygonA.v[0];
+  Xf sfA = mkXf(xfA.p + rotate(xfA.q, origin), xfA.q);
+  Xf xf = invMulXf(sfA, xfB);
+  PolyT<CA> A; A.radius = polygonA.radius;
+  A.v[0] = mk(0, 0); A.n[0] = polygonA.n[0];
+#pragma unroll
+  for (int i = 1; i < CA; i++) { A.v[i] = polygonA.v[i] - origin; A.n[i] = polygonA.n[i]; }
+  PolyT<CB> B; B.radius = polygonB.radius;
+#pragma unroll
+  for (int i = 0; i < CB; i++) { B.v[i] = xfPoint(xf, polygonB.v[i]); B.n[i] = rotate(xf.q, polygonB.n[i]); }
+  int edgeA, edgeB;
+  float separationA = findMaxSeparationT(&edgeA, A, B);
+  float separationB = findMaxSeparationT(&edgeB, B, A);
+  float radius = A.radius + B.radius;
+  if (separationA > kSpeculativeDistance + radius || separationB > kSpeculativeDistance + radius) return emptyManifold();
+  bool flip;
+  if (separationA >= separationB) {
+    flip = false;
+    V2 dir = pickT(A.n, edgeA);
+    edgeB = 0; float minDot = FLT_MAX;
+#pragma unroll
+    for (int i = 0; i < CB; i++) { float dt = dot(dir, B.n[i]); if (dt < minDot) { minDot = dt; edgeB = i; } }
+  } else {
+    flip = true;
+    V2 dir = pickT(B.n, edgeB);
+    edgeA = 0; float minDot = FLT_MAX;
+#pragma unroll
+    for (int i = 0; i < CA; i++) { float dt = dot(dir, A.n[i]); if (dt < minDot) { minDot = dt; edgeA = i; } }
+  }
+  const int i11 = edgeA, i12 = edgeA + 1 < CA ? edgeA + 1 : 0;
+  const int i21 = edgeB, i22 = edgeB + 1 < CB ? edgeB + 1 : 0;
+  const V2 v11 = pickT(A.v, i11), v12 = pickT(A.v, i12), v21 = pickT(B.v, i21), v22 = pickT(B.v, i22);
+  // ClipPolygons swaps the roles when flip is set: the reference polygon is B, the incident one A
+  const V2 clipNormal = flip ? pickT(B.n, i21) : pickT(A.n, i11);
+  Manifold m = emptyManifold();
+  if (separationA > 0.1f * kLinearSlop || separationB > 0.1f * kLinearSlop) {
+    SegDist result = segmentDistance(v11, v12, v21, v22);
+    float distance = sqrtf(result.distanceSquared);
+    float separation = distance - radius;
+    if (distance - radius > kSpeculativeDistance) return m;
+    m = flip ? clipPicked(clipNormal, v21, v22, v11, v12, B.radius, A.radius, i21, i22, i11, i12, true)
+             : clipPicked(clipNormal, v11, v12, v21, v22, A.radius, B.radius, i11, i12, i21, i22, false);
+    float minSeparation = FLT_MAX;
+    if (m.pointCount > 0) minSeparation = netMin(minSeparation, m.p0.separation);
+    if (m.pointCount > 1) minSeparation = netMin(minSeparation, m.p1.separation);
+    if (separation + 0.1f * kLinearSlop < minSeparation) {
+      V2 va = mk(0, 0), vb = mk(0, 0); int ia = -1, ib = -1;
+      if (result.fraction1 == 0.0f && result.fraction2 == 0.0f) { va = v11; vb = v21; ia = i11; ib = i21; }
+      else if (result.fraction1 == 0.0f && result.fraction2 == 1.0f) { va = v11; vb = v22; ia = i11; ib = i22; }
+      else if (result.fraction1 == 1.0f && result.fraction2 == 0.0f) { va = v12; vb = v21; ia = i12; ib = i21; }
+      else if (result.fraction1 == 1.0f && result.fraction2 == 1.0f) { va = v12; vb = v22; ia = i12; ib = i22; }
+      if (ia >= 0) {
+        V2 normal = vb - va;
+        float invDistance = 1.0f / distance;
+        normal = invDistance * normal;
+        V2 c1 = mulAdd(va, A.radius, normal), c2 = mulAdd(vb, -B.radius, normal);
+        m.normal = normal;
+        m.p0.anchorA = lerp(c1, c2, 0.5f);
+        m.p0.separation = distance - radius;
+        m.p0.id = makeId(ia, ib);
+        m.pointCount = 1;
+      }
+    }
+  } else m = flip ? clipPicked(clipNormal, v21, v22, v11, v12, B.radius, A.radius, i21, i22, i11, i12, true)
+                  : clipPicked(clipNormal, v11, v12, v21, v22, A.radius, B.radius, i11, i12, i21, i22, false);
+  if (m.pointCount > 0) {
+    m.normal = rotate(xfA.q, m.normal);
+    m.p0.anchorA = rotate(xfA.q, m.p0.anchorA + origin);
+    m.p0.anchorB = m.p0.anchorA + (xfA.p - xfB.p);
+    m.p0.point = xfA.p + m.p0.anchorA;
+    if (m.pointCount > 1) {
+      m.p1.anchorA = rotate(xfA.q, m.p1.anchorA + origin);
+      m.p1.anchorB = m.p1.anchorA + (xfA.p - xfB.p);
+      m.p1.point = xfA.p + m.p1.anchorA;
+    }
+  }
+  return m;
+}
+
 // Geometry.MakeCapsule as a 2-gon (src/Manifold.cs:8-17)
 __device__ inline void makeCapsulePoly(Geom& g, V2 p1, V2 p2, float radius) {
   g.type = kPolygon; g.count = 2; g.radius = radius;
@@ -423,6 +556,7 @@ __device__ inline Manifold computeManifold(const Geom& a, Xf xfA, const Geom& b,
     default: {
       if (b.type == kCircle) return collidePolygonAndCircle(a, xfA, b.v[0], b.radius, xfB);
       if (b.type == kCapsule) { Geom cap; makeCapsulePoly(cap, b.v[0], b.v[1], b.radius); return collidePolygons(a, xfA, cap, xfB); }
+      if (a.count == 4 && b.count == 4) return collidePolygonsT<4, 4>(a, xfA, b, xfB);   // boxes: the unrolled path (same arithmetic)
       return collidePolygons(a, xfA, b, xfB);
     }
   }
