@@ -206,6 +206,7 @@ def batched_record(args, rank, world_size, local_rank, dist, barrier):
             "world_steps_per_s": args.worlds * K / (ms_max * 1e-3), "body_substeps_per_s": v[0] * SUBSTEPS * K / (ms_max * 1e-3),
             "e2e_world_steps_per_s": args.worlds * K / (e2e_max * 1e-3), "e2e_d2h_bytes_per_step": 64, "gpu_launches_per_step": 1,
             "l2": "per-GPU working set (every world's own trees, contacts and solver arrays) exceeds the 126 MB L2 many times over",
+            "dram_traffic_bytes_per_launch": (measured_traffic("batched_8192")[0] if (args.worlds == 8192 and world_size == 1) else None),
             "stats": {"awake_bodies": int(v[0]), "sum_v2": v[1], "touching_contacts": int(v[2]), "max_speed": v[5], "min_y": v[6]}}
 
 
