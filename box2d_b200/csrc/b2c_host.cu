@@ -1201,7 +1201,7 @@ int World::regrow(void** slot, size_t newCount, int fillByte) {
 #define RG(ptr, n) do { int rc_ = regrow((void**)&(ptr), (size_t)(n)); if (rc_) return rc_; } while (0)
 #define RGF(ptr, n, fill) do { int rc_ = regrow((void**)&(ptr), (size_t)(n), fill); if (rc_) return rc_; } while (0)
 int World::growScanScratch() {
-  int scanBlocks = std::max(std::max(std::max(d_.contactCapacity, d_.bigScratch), std::max(d_.moveCapacity, capAwake_)), capSensor_) / 128 + 2;   // chunk = block size of the scope, 160 at the narrowest
+  int scanBlocks = std::max(std::max(std::max(d_.contactCapacity, d_.bigScratch), std::max(d_.moveCapacity, capAwake_)), capSensor_) / 64 + 2;   // chunk = block size of the scope, 64 at the narrowest (a batch world's finalize CTA)
   RG(d_.scanBlockSums, scanBlocks); RG(d_.scanBlockSums4, scanBlocks);
   return B2C_OK;
 }
@@ -1463,7 +1463,7 @@ int World::upload() {
       for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.sensorEndEvents[k], hSensorEnd_[k], 0));
     } }
   DA(d.sc, Scalars, 1);
-  int scanBlocks = std::max(std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, capAwake)), capSensor_) / 128 + 2;   // chunk = block size of the scope, 160 at the narrowest
+  int scanBlocks = std::max(std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, capAwake)), capSensor_) / 64 + 2;   // chunk = block size of the scope, 64 at the narrowest (a batch world's finalize CTA)
   DA(d.scanBlockSums, int, scanBlocks); DA(d.scanBlockSums4, int4, scanBlocks);
   Scalars init; memset(&init, 0, sizeof(init));
   init.moveCount = (int)moveArray_.size(); init.awakeCount = nAwake; init.graphDirty = 1;

@@ -37,15 +37,10 @@ __device__ __forceinline__ void sliceLoadLane(const WarpIslandSlice& sl, int t, 
   c.baseSep1 = H.x; c.baseSep2 = H.y; c.relVel1 = H.z; c.relVel2 = H.w;
 }
 
-__global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_warp(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp) {
-  extern __shared__ __align__(16) unsigned char smemRaw[];
-  WarpIslandSlice& sl = reinterpret_cast<WarpIslandSlice*>(smemRaw)[threadIdx.x >> 5];
-  const int lane = threadIdx.x & 31;
-  const int warpsTotal = gridDim.x * kWarpIslandsPerCta, warpId = blockIdx.x * kWarpIslandsPerCta + (threadIdx.x >> 5);
-  const int n = d.sc->islandCount;
+// one island, one warp: the whole SolverTask stage sequence with __syncwarp() as the colour barrier
+__device__ __forceinline__ void runIslandWarp(const WorldDev& d, const StepParams& sp, int g, WarpIslandSlice& sl, int lane) {
   const unsigned full = 0xffffffffu;
-  for (int g = warpId; g < n; g += warpsTotal) {
-    if (!warpIslandEligible(d, g)) continue;
+  {
     const int bBegin = d.islandBodyStart[g], nb = d.islandBodyStart[g + 1] - bBegin;
     const int cBegin = d.islandConStart[g];
     if (lane <= kGraphColorCount) sl.colorOff[lane] = d.islandColorOff[g * (kGraphColorCount + 1) + lane];
@@ -125,6 +120,34 @@ __global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_w
     for (int r = 0; r < 2; r++) { int b = lane + 32 * r; if (b < nb) { d.st0[sim[r]] = sl.s0[b]; d.st1[sim[r]] = sl.s1[b]; if (sf[r] != sf0[r]) d.simFlags[sim[r]] = sf[r]; } }
     for (int t = lane; t < K; t += 32) { float4 H = sl.plane[7][t]; storeImpulsesRegs(d, d.sContact[cBegin + t], sl.plane[8][t], sl.plane[9][t], H.z, H.w); }
     __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_solver_islands_warp(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp) {
+  extern __shared__ __align__(16) unsigned char smemRaw[];
+  WarpIslandSlice& sl = reinterpret_cast<WarpIslandSlice*>(smemRaw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const int warpsTotal = gridDim.x * kWarpIslandsPerCta, warpId = blockIdx.x * kWarpIslandsPerCta + (threadIdx.x >> 5);
+  const int n = d.sc->islandCount;
+  for (int g = warpId; g < n; g += warpsTotal) {
+    if (!warpIslandEligible(d, g)) continue;
+    runIslandWarp(d, sp, g, sl, lane);
+  }
+}
+
+// Batches of independent worlds (k_batch_front / k_batch_finalize in b2c_step.cu): ONE WARP per world walks the world's islands that fit a
+// slice; eight worlds share an SM. The islands that do not fit were solved by the world's CTA in k_batch_front.
+__global__ void __launch_bounds__(32 * kWarpIslandsPerCta, 1) k_batch_solve_warp(const WorldDev* __restrict__ worlds, int worldCount, const __grid_constant__ StepParams sp) {
+  extern __shared__ __align__(16) unsigned char smemRaw[];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WarpIslandSlice& sl = reinterpret_cast<WarpIslandSlice*>(smemRaw)[w];
+  const int world = blockIdx.x * kWarpIslandsPerCta + w;
+  if (world >= worldCount) return;
+  const WorldDev& d = worlds[world];                 // read through L1 (the slices leave no shared memory for a copy of the record)
+  const int n = d.sc->islandCount;
+  for (int g = 0; g < n; g++) {
+    if (!warpIslandEligible(d, g)) continue;
+    runIslandWarp(d, sp, g, sl, lane);
   }
 }
 

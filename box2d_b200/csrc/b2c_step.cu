@@ -1676,10 +1676,14 @@ __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(const __grid_co
 // synchronisation anywhere), then its islands with the CTA island solver, then FinalizeBodies/refit. World index = blockIdx.x; each
 // world has its own arrays, id pools, trees and colour graph, so world k of a batch is bit-identical to the same world stepped alone.
 // ------------------------------------------------------------------------------------------------------------
-template <int THREADS, int MINB>
+// MODE 0: the whole step in one launch. MODE 1 / 2: the step split in three launches — front (this kernel, MODE 1: pairs, collide, colouring,
+// islands, the islands that do NOT fit a warp slice, free bodies), k_batch_solve_warp (one warp per world, eight worlds per SM, for the
+// islands that fit a slice) and finalize (this kernel, MODE 2). The split gives each part the residency it can use: the solver's stage
+// chain keeps one warp busy per world, so eight warp-worlds per SM beat four CTA-worlds whose other warps idle at the barrier.
+template <int THREADS, int MINB, int MODE>
 __global__ void __launch_bounds__(THREADS, MINB) k_batch_step(const WorldDev* __restrict__ worlds, StepParams sp, int newEndIndex, int* __restrict__ maxIslandCons) {
   __shared__ __align__(16) unsigned char sdRaw[sizeof(WorldDev)];
-  __shared__ float4 s0[kIslandMaxBodies], s1[kIslandMaxBodies];
+  __shared__ float4 s0[MODE == 2 ? 1 : kIslandMaxBodies], s1[MODE == 2 ? 1 : kIslandMaxBodies];
   __shared__ int colorOff[kGraphColorCount + 1 + 2 * kGraphColorCount];
   {
     const int* src = reinterpret_cast<const int*>(worlds + blockIdx.x);
@@ -1689,21 +1693,26 @@ __global__ void __launch_bounds__(THREADS, MINB) k_batch_step(const WorldDev* __
   __syncthreads();
   const WorldDev& d = *reinterpret_cast<const WorldDev*>(sdRaw);
   CtaScope cta;
-  stepFront(cta, d, sp);                          // sp.clusterThreads == 0: large / jointed islands are solved here, at CTA scope
-  __syncthreads();
-  const int n = d.sc->islandCount;
-  for (int g = 0; g < n; g++) {
-    int K = d.islandColorOff[g * (kGraphColorCount + 1) + kGraphColorCount];
-    if (threadIdx.x == 0 && K > *maxIslandCons) atomicMax(maxIslandCons, K);   // the host sizes the next launches' CTAs by it (lanes stay in registers while K <= blockDim)
-    if (K <= (int)blockDim.x) runIsland<true>(d, sp, g, s0, s1, colorOff);
-    else runIsland<false>(d, sp, g, s0, s1, colorOff);
+  if (MODE != 2) {
+    stepFront(cta, d, sp);                        // sp.clusterThreads == 0: large / jointed islands are solved here, at CTA scope
+    __syncthreads();
+    const int n = d.sc->islandCount;
+    for (int g = 0; g < n; g++) {
+      int K = d.islandColorOff[g * (kGraphColorCount + 1) + kGraphColorCount];
+      if (threadIdx.x == 0 && K > *maxIslandCons) atomicMax(maxIslandCons, K);   // the host sizes the next launches' CTAs by it (lanes stay in registers while K <= blockDim)
+      if (MODE == 1 && warpIslandEligible(d, g)) continue;                      // k_batch_solve_warp takes it
+      if (K <= (int)blockDim.x) runIsland<true>(d, sp, g, s0, s1, colorOff);
+      else runIsland<false>(d, sp, g, s0, s1, colorOff);
+    }
+    freeBodies(d, sp, threadIdx.x, blockDim.x);
+    __syncthreads();
   }
-  freeBodies(d, sp, threadIdx.x, blockDim.x);
-  __syncthreads();
-  unsigned long long t6 = 0;
-  if (threadIdx.x == 0) t6 = globalTimer();
-  finalizePhase(cta, d, sp, newEndIndex);
-  if (threadIdx.x == 0) { Scalars& s = *d.sc; s.phaseAcc[5] += t6 - s.phaseStamp[4]; s.phaseAcc[6] += globalTimer() - t6; }
+  if (MODE != 1) {
+    unsigned long long t6 = 0;
+    if (threadIdx.x == 0) t6 = globalTimer();
+    finalizePhase(cta, d, sp, newEndIndex);
+    if (threadIdx.x == 0) { Scalars& s = *d.sc; s.phaseAcc[5] += t6 - s.phaseStamp[4]; s.phaseAcc[6] += globalTimer() - t6; }
+  }
 }
 
 // bodyMoveEvents equivalent: one packed record per body id (src/Solver.cs:432-438)
@@ -1905,15 +1914,29 @@ int World::getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count) {
   return B2C_OK;
 }
 
-// One launch steps every world of a batch (b2c_batch.cu drives it)
+// One step of every world of a batch (b2c_batch.cu drives it)
 // CTA width: 160 threads at 96 registers (4 worlds per SM) while every island's constraints fit 160 register lanes, else 256 threads
 // (2 worlds per SM). Measured on 8192 10-row pyramids (145 constraints each): 0.97 ms against 1.49 ms per step; narrower CTAs at
 // 80 / 72 / 64 registers spill and lose (1.14 - 1.17 ms). `maxIslandCons` is a mapped host int the kernel keeps a running maximum in.
+// Three launches while every island fits a warp slice-sized CTA (see MODE above): measured on 8192 10-row pyramids against the one-launch
+// step (B2CUDA_BATCH_SPLIT=0 keeps one launch, =1 forces the split).
 cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, int* maxIslandConsDev, int maxIslandConsSeen, cudaStream_t stream) {
   static int forced = getenv("B2CUDA_BATCH_THREADS") ? atoi(getenv("B2CUDA_BATCH_THREADS")) : 0;
+  static int split = getenv("B2CUDA_BATCH_SPLIT") ? atoi(getenv("B2CUDA_BATCH_SPLIT")) : -1;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(k_batch_solve_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kWarpIslandsPerCta * sizeof(WarpIslandSlice)));
+    if (e != cudaSuccess) return e;
+    attr = true;
+  }
   const bool narrow = forced ? forced == 160 : (maxIslandConsSeen > 0 && maxIslandConsSeen <= 160);
-  if (narrow) k_batch_step<160, 4><<<worldCount, 160, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
-  else k_batch_step<256, 2><<<worldCount, 256, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
+  const bool useSplit = split < 0 ? narrow : (split != 0 && narrow);
+  if (useSplit) {
+    k_batch_step<160, 4, 1><<<worldCount, 160, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
+    k_batch_solve_warp<<<(worldCount + kWarpIslandsPerCta - 1) / kWarpIslandsPerCta, 32 * kWarpIslandsPerCta, kWarpIslandsPerCta * sizeof(WarpIslandSlice), stream>>>(worlds, worldCount, sp);
+    k_batch_step<64, 8, 2><<<worldCount, 64, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);   // FinalizeBodies of a small world: 64 threads, 8+ worlds per SM (134 -> see profiles/r02_summary.txt)
+  } else if (narrow) k_batch_step<160, 4, 0><<<worldCount, 160, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
+  else k_batch_step<256, 2, 0><<<worldCount, 256, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
   return cudaGetLastError();
 }
 __global__ void k_batch_zero_step(const WorldDev* worlds, int newEndIndex) { Scalars& s = *worlds[blockIdx.x].sc; s.beginCount = 0; s.hitCount = 0; s.endCount[newEndIndex] = 0; s.sensorBeginCount = 0; s.sensorEndCount[newEndIndex] = 0; }
