@@ -3,6 +3,7 @@
 // statistics reduced on the device, per-world reset from a snapshot taken at the first step.
 #include "b2c_host.cuh"
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 
 namespace b2c {
@@ -11,6 +12,7 @@ namespace b2c {
 
 cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, int* maxIslandConsDev, int maxIslandConsSeen, cudaStream_t stream);
 cudaError_t launchBatchZeroStep(const WorldDev* worlds, int worldCount, int newEndIndex, cudaStream_t stream);
+cudaError_t prepareBatchKernels();
 cudaError_t launchBatchStats(const WorldDev* worlds, int worldCount, int lastEndIndex, double* out, unsigned int* errOr, cudaStream_t stream);
 
 cudaStream_t batchStream(Batch* b) { return b->stream(); }
@@ -30,6 +32,7 @@ int Batch::init() {
   for (auto& e : timer_) CK(cudaEventCreate(&e));
   CK(cudaHostAlloc((void**)&mappedInt_, sizeof(int), cudaHostAllocMapped));
   CK(cudaHostGetDevicePointer((void**)&mappedIntDev_, mappedInt_, 0));
+  CK(prepareBatchKernels());
   CK(cudaHostAlloc((void**)&maxCons_, sizeof(int), cudaHostAllocMapped));
   *maxCons_ = 0;
   CK(cudaHostGetDevicePointer((void**)&maxConsDev_, maxCons_, 0));
@@ -49,6 +52,7 @@ Batch::~Batch() {
   for (World* w : worlds_) delete w;               // members free no device memory: it is the arena's
   for (void* c : chunks_) cudaFree(c);
   for (void* c : snapChunks_) cudaFree(c);
+  for (auto& c : graphs_) if (c.exec) cudaGraphExecDestroy(c.exec);
   if (dWorlds_) cudaFree(dWorlds_);
   if (dStats_) cudaFree(dStats_);
   if (hStats_) cudaFreeHost(hStats_);
@@ -167,7 +171,29 @@ int Batch::step(float timeStep, int subStepCount) {
     sp.enableWarmStarting = w0.enableWarmStarting; sp.enableContactSoftening = w0.enableContactSoftening; sp.enableContinuous = w0.enableContinuous;
     sp.enableSpeculative = w0.enableSpeculative; sp.enableSleep = 0; sp.endIndex = lastEnd;
     sp.clusterThreads = 0;
-    CK(launchBatchStep(dWorlds_, n, sp, endIndex_, maxConsDev_, *(volatile int*)maxCons_, stream_));   // the maximum may lag the running step: either CTA width is correct
+    const int maxCons = *(volatile int*)maxCons_;   // the maximum may lag the running step: either CTA width is correct
+    // The launches of a step are replayed as ONE CUDA-graph launch (captured per distinct step parameters / end-buffer parity / CTA
+    // width): with several ranks driving GPUs from one host the three kernels then run back to back whatever the host's launch latency is.
+    static const bool useGraph = !(getenv("B2CUDA_BATCH_GRAPH") && atoi(getenv("B2CUDA_BATCH_GRAPH")) == 0);
+    if (useGraph) {
+      StepGraphB* g = nullptr;
+      const int narrow = maxCons > 0 && maxCons <= 160;
+      for (auto& c : graphs_) if (c.endIndex == endIndex_ && c.narrow == narrow && c.n == n && memcmp(&c.sp, &sp, sizeof(sp)) == 0) { g = &c; break; }
+      if (!g) {
+        if (graphs_.size() >= 8) { for (auto& c : graphs_) cudaGraphExecDestroy(c.exec); graphs_.clear(); }
+        cudaGraph_t graph = nullptr;
+        CK(cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal));
+        cudaError_t le = launchBatchStep(dWorlds_, n, sp, endIndex_, maxConsDev_, maxCons, stream_);
+        cudaError_t ce = cudaStreamEndCapture(stream_, &graph);
+        if (le != cudaSuccess || ce != cudaSuccess) { if (graph) cudaGraphDestroy(graph); cudaGetLastError(); return fail(B2C_E_CUDA, std::string("batch step capture: ") + cudaGetErrorString(le != cudaSuccess ? le : ce)); }
+        StepGraphB c; c.sp = sp; c.endIndex = endIndex_; c.narrow = narrow; c.n = n; c.exec = nullptr;
+        cudaError_t ie = cudaGraphInstantiate(&c.exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ie != cudaSuccess) return fail(B2C_E_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ie));
+        graphs_.push_back(c); g = &graphs_.back();
+      }
+      CK(cudaGraphLaunch(g->exec, stream_));
+    } else CK(launchBatchStep(dWorlds_, n, sp, endIndex_, maxConsDev_, maxCons, stream_));
   }
   const bool zero = timeStep == 0.0f;
   for (World* w : worlds_) {                       // per-world host bookkeeping of World::step

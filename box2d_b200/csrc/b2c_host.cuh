@@ -274,6 +274,8 @@ class Batch {
   int endIndex_ = 0, stepCount_ = 0;
   double* dStats_ = nullptr; double* hStats_ = nullptr;
   cudaEvent_t timer_[2] = {nullptr, nullptr};
+  struct StepGraphB { StepParams sp; int endIndex, narrow, n; cudaGraphExec_t exec; };   // captured launches of one step
+  std::vector<StepGraphB> graphs_;
 };
 
 }  // namespace b2c

@@ -1918,17 +1918,14 @@ int World::getBodyMoveEvents(const B2CBodyMoveEvent** events, int* count) {
 // CTA width: 160 threads at 96 registers (4 worlds per SM) while every island's constraints fit 160 register lanes, else 256 threads
 // (2 worlds per SM). Measured on 8192 10-row pyramids (145 constraints each): 0.97 ms against 1.49 ms per step; narrower CTAs at
 // 80 / 72 / 64 registers spill and lose (1.14 - 1.17 ms). `maxIslandCons` is a mapped host int the kernel keeps a running maximum in.
+cudaError_t prepareBatchKernels() {                 // once per device, before the first launch (and outside any stream capture)
+  return cudaFuncSetAttribute(k_batch_solve_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kWarpIslandsPerCta * sizeof(WarpIslandSlice)));
+}
 // Three launches while every island fits a warp slice-sized CTA (see MODE above): measured on 8192 10-row pyramids against the one-launch
 // step (B2CUDA_BATCH_SPLIT=0 keeps one launch, =1 forces the split).
 cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepParams& sp, int newEndIndex, int* maxIslandConsDev, int maxIslandConsSeen, cudaStream_t stream) {
   static int forced = getenv("B2CUDA_BATCH_THREADS") ? atoi(getenv("B2CUDA_BATCH_THREADS")) : 0;
   static int split = getenv("B2CUDA_BATCH_SPLIT") ? atoi(getenv("B2CUDA_BATCH_SPLIT")) : -1;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(k_batch_solve_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kWarpIslandsPerCta * sizeof(WarpIslandSlice)));
-    if (e != cudaSuccess) return e;
-    attr = true;
-  }
   const bool narrow = forced ? forced == 160 : (maxIslandConsSeen > 0 && maxIslandConsSeen <= 160);
   const bool useSplit = split < 0 ? narrow : (split != 0 && narrow);
   if (useSplit) {
