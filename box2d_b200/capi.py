@@ -197,6 +197,7 @@ PROTOS = {
     "world_enable_continuous": [_W, C.c_int32],
     "world_enable_sleeping": [_W, C.c_int32],
     "world_set_contact_tuning": [_W, C.c_float, C.c_float, C.c_float],
+    "body_set_bullet": [_W, C.c_int32, C.c_int32],
     "world_step": [_W, C.c_float, C.c_int32],
     "world_synchronize": [_W],
     "world_destroy": [_W],
@@ -260,7 +261,6 @@ PRODUCT_ONLY.update({
     "body_wake_touching": ([_W, C.c_int32], C.c_int32),
     "body_disable": ([_W, C.c_int32], C.c_int32),
     "body_enable": ([_W, C.c_int32], C.c_int32),
-    "body_set_bullet": ([_W, C.c_int32, C.c_int32], C.c_int32),
 })
 NOALLOC_MAX_MOVE_EVENTS = 65536     # B2C_NOALLOC_MAX_MOVE_EVENTS
 

@@ -363,7 +363,6 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
     awakeOrder_.pop_back(); b.simIndex = -1;
   } else if (transfer == 2) { b.simIndex = newSim; awakeOrder_.push_back(bodyId); }
   d_.awakeCount = (int)awakeOrder_.size();
-  int parkedOverflow = 0;
   for (int jid : jids) {                            // :226-241 back into the graph when either body is dynamic now (fresh colour, appended)
     HJoint& j = joints_[jid];
     const HBody& bodyA = bodies_[j.bodyIdA]; const HBody& bodyB = bodies_[j.bodyIdB];
@@ -372,7 +371,6 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(stream_));
     const int color = *hJointColor_;
-    if (color == kOverflowIndex) { parkedOverflow++; continue; }
     colorJoints_[color].push_back(jid);
     j.inGraph = true; j.sim.colorIndex = color;
     k_joint_set_color<<<1, 1, 0, stream_>>>(d_, jid, color);
@@ -393,7 +391,6 @@ int World::setBodyType(int bodyId, int type) {   // BodyAPI.SetType api/Body.cs:
   k_body_mass_update<<<1, 1, 0, stream_>>>(d_, bodyId, b.type, b.invMass, b.invInertia, b.localCenter, b.minExtent, b.maxExtent);
   CK(cudaGetLastError());
   eventsFetched_ = false; bodiesFetched_ = false; movesFetched_ = false;
-  if (parkedOverflow) return fail(B2C_E_UNSUPPORTED, "body_set_type: a joint of this body would land in the overflow colour (more than 20 joints on a body); it stays parked and is not simulated");
   return B2C_OK;
 }
 void World::treeProxyRemoved(int type) {          // DestroyProxy: the leaf and, unless it was the root, its parent go back to the free list
@@ -407,8 +404,8 @@ int World::createBody(const B2CBodyDef& def, int* bodyId) {
     int rc = growBodies(bodyIds_.freeArray.empty() ? (int)bodies_.size() + 1 : 0, def.type != kStaticBody ? (int)awakeOrder_.size() + 1 : 0);
     if (rc) return rc;
   }
-  if (!def.isEnabled || def.isBullet || !(def.isAwake || !def.enableSleep))
-    return fail(B2C_E_UNSUPPORTED, "disabled / bullet / initially-asleep bodies are not supported");
+  if (!def.isEnabled || !(def.isAwake || !def.enableSleep))
+    return fail(B2C_E_UNSUPPORTED, "disabled / initially-asleep bodies are not supported");
   int id = bodyIds_.alloc();
   if (id == (int)bodies_.size()) bodies_.emplace_back();
   HBody& b = bodies_[id];
@@ -417,7 +414,7 @@ int World::createBody(const B2CBodyDef& def, int* bodyId) {
   b.generation = (uint16_t)(gen + 1);
   b.id = id; b.type = def.type; b.userData = def.userData; b.sleepThreshold = def.sleepThreshold; b.enableSleep = def.enableSleep != 0;
   b.flags = (def.lockLinearX ? kLockLinearX : 0) | (def.lockLinearY ? kLockLinearY : 0) | (def.lockAngularZ ? kLockAngularZ : 0) |
-            (def.allowFastRotation ? kAllowFastRotation : 0) | (def.type == kDynamicBody ? kDynamicFlag : 0);
+            (def.isBullet ? kIsBullet : 0) | (def.allowFastRotation ? kAllowFastRotation : 0) | (def.type == kDynamicBody ? kDynamicFlag : 0);   // api/Body.cs:42-62
   b.xf.p = mk(def.position.x, def.position.y); b.xf.q = mkRot(def.rotation.c, def.rotation.s);
   b.center = b.xf.p; b.center0 = b.xf.p; b.rot0 = b.xf.q; b.localCenter = mk(0, 0); b.force = mk(0, 0);
   b.linearDamping = def.linearDamping; b.angularDamping = def.angularDamping; b.gravityScale = def.gravityScale;
@@ -658,12 +655,10 @@ int World::createJoint(const B2CJointDef& def, int* jointId) {
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(stream_));
     deviceColor = *hJointColor_;
-    if (deviceColor == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   }
-  // the colour before anything is filed: a refused joint must leave id pool, body joint lists and colour masks untouched (assignJointColor
-  // sets no bit when it answers with the overflow colour)
+  // a body with joints in every colour it may use sends the next one to the overflow colour (no bit set, src/ConstraintGraph.cs:91-128):
+  // it is filed like any other and solved serially before the overflow contacts (src/Joint.cs:377-394)
   const int color = parked ? -1 : (onDevice_ ? deviceColor : assignJointColor(bodyA.id, bodyB.id, bodyA.type, bodyB.type));
-  if (color == kOverflowIndex) return fail(B2C_E_UNSUPPORTED, "joint landed in the overflow color (body with more than 20 joints); not supported");
   int id = jointIds_.alloc();
   if (id == (int)joints_.size()) joints_.emplace_back();
   HJoint& j = joints_[id];
@@ -1091,10 +1086,22 @@ int World::bodySetEnabled(int bodyId, bool enabled) {                 // api/Bod
   if (enabled) return B2C_OK;                                         // Enable on a body that is not in the disabled set returns at once (:757)
   return fail(B2C_E_UNSUPPORTED, "Body.Disable moves the body, its contacts and joints to the disabled solver set (api/Body.cs:721-752): the disabled set is not built");
 }
+__global__ void k_body_set_bullet(WorldDev d, int bodyId, int flag) {
+  const int sim = d.bodySim[bodyId];
+  uint32_t* f = sim < 0 ? &d.bodySimFlags[bodyId] : &d.simFlags[sim];
+  *f = flag ? (*f | kIsBullet) : (*f & ~(uint32_t)kIsBullet);
+  if (d.bodyOut) d.bodyOut[bodyId].flags = *f;      // the streamed read-back row of a static body is not rewritten by the step
+}
 int World::bodySetBullet(int bodyId, bool flag) {                     // api/Body.cs:835-842
   if (bodyId < 0 || bodyId >= (int)bodies_.size() || bodies_[bodyId].id != bodyId) return fail(B2C_E_INVALID, "bad body id");
-  if (!flag) return B2C_OK;                                           // no body carries the bit
-  return fail(B2C_E_UNSUPPORTED, "SetBullet(true): the bullet continuous stage (src/Solver.cs:728-738,1238-1272) is not built");
+  HBody& b = bodies_[bodyId];
+  b.flags = flag ? (b.flags | kIsBullet) : (b.flags & ~(uint32_t)kIsBullet);   // BodySim.flags only: Body.flags and BodyState.flags keep their bit
+  if (!onDevice_) return B2C_OK;
+  CK(cudaSetDevice(device_));
+  k_body_set_bullet<<<1, 1, 0, stream_>>>(d_, bodyId, flag ? 1 : 0);
+  CK(cudaGetLastError());
+  bodiesFetched_ = false;
+  return B2C_OK;
 }
 
 // BodyAPI.SetTransform after the upload: the same teleport as one device thread, ordered on the world's stream. The fat

@@ -1035,8 +1035,15 @@ __device__ __noinline__ void solveJointOther(const WorldDev& d, const StepParams
 __device__ __forceinline__ void warmStartJoint(const WorldDev& d, JointDev& j) {      // JointSim.WarmStart src/Joint.cs:131
   if (j.type == kRevoluteJoint) warmStartRevolute(d, j); else warmStartJointOther(d, j);
 }
-__device__ __forceinline__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {    // JointSim.Solve src/Joint.cs:132 + SolveJointsTask src/Solver.cs:180-198
+__device__ __forceinline__ void solveJointOnly(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {    // JointSim.Solve src/Joint.cs:132
   if (j.type == kRevoluteJoint) solveRevolute(d, sp, j, useBias); else solveJointOther(d, sp, j, useBias);
+}
+// Joints of the overflow colour (src/Joint.cs:377-394): one thread, array order, before the overflow contacts of the stage
+// (src/Solver.cs:633,648,669). The relax pass keeps useBias (Q4) and no joint event can come from here: only SolveJointsTask tests the thresholds.
+__device__ __noinline__ void ovJointsWarmStart(const WorldDev& d, int k0, int k1) { for (int k = k0; k < k1; k++) warmStartJoint(d, d.joints[d.jointSorted[k]]); }
+__device__ __noinline__ void ovJointsSolve(const WorldDev& d, const StepParams& sp, int k0, int k1) { for (int k = k0; k < k1; k++) solveJointOnly(d, sp, d.joints[d.jointSorted[k]], true); }
+__device__ __forceinline__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {    // JointSim.Solve src/Joint.cs:132 + SolveJointsTask src/Solver.cs:180-198
+  solveJointOnly(d, sp, j, useBias);
   if (useBias && (j.forceThreshold < FLT_MAX || j.torqueThreshold < FLT_MAX) && !d.jointEventFlag[j.jointId]) {   // src/Solver.cs:186-196
     float force, torque; jointReaction(j, sp.inv_h, &force, &torque);
     if (force >= j.forceThreshold || torque >= j.torqueThreshold) d.jointEventFlag[j.jointId] = 1;
@@ -1119,6 +1126,8 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   const int awake = s.bigBodyCount;               // bodies of grid-path islands (+ kinematic bodies some constraint reads)
   if (awake == 0 && activeCount == 0) return;     // everything lives in small islands / free bodies: no grid barrier at all
   const int nov = s.colLen[kOverflowIndex];                      // overflow colour: one thread, array order, before the colours of each stage (:633-670)
+  const int ovJ0 = d.jointColorStart[kOverflowIndex], ovJ1 = d.jointColorStart[kGraphColorCount];   // its joints come before its contacts
+  const bool anyOv = nov > 0 || ovJ1 > ovJ0;
   Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int myA = -1, myContact = -1;
   const BodyRows bs{d.st0, d.st1};
   if (CACHED) {
@@ -1132,14 +1141,14 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   for (int sub = 0; sub < sp.subStepCount; sub++) {
     for (int i = tid; i < awake; i += stride) integrateVelocity(d, sp, d.bigBodies[i]);
     grid.sync();
-    if (nov > 0) { if (tid == 0) ovWarmStart(d, nov); grid.sync(); }
+    if (anyOv) { if (tid == 0) { if (ovJ1 > ovJ0) ovJointsWarmStart(d, ovJ0, ovJ1); if (nov > 0) ovWarmStart(d, nov); } grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) warmStartJoint(d, d.joints[d.jointSorted[k]]);
       if (CACHED) { if (myA == a) warmStartLane(bs, c, c.indexA, c.indexB, I, J.z); }
       else for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) warmStartContact(d, t);
       grid.sync();
     }
-    if (nov > 0) { if (tid == 0) ovSolve(d, sp, nov, true); grid.sync(); }
+    if (anyOv) { if (tid == 0) { if (ovJ1 > ovJ0) ovJointsSolve(d, sp, ovJ0, ovJ1); if (nov > 0) ovSolve(d, sp, nov, true); } grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], true);
       if (CACHED) { if (myA == a) solveLane<true>(bs, sp, c, c.indexA, c.indexB, I, J); }
@@ -1148,7 +1157,7 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
     }
     for (int i = tid; i < awake; i += stride) integratePosition(d, sp, d.bigBodies[i]);
     grid.sync();
-    if (nov > 0) { if (tid == 0) ovSolve(d, sp, nov, true); grid.sync(); }      // Q4: the relax pass of the overflow colour keeps useBias
+    if (anyOv) { if (tid == 0) { if (ovJ1 > ovJ0) ovJointsSolve(d, sp, ovJ0, ovJ1); if (nov > 0) ovSolve(d, sp, nov, true); } grid.sync(); }      // Q4: the relax pass of the overflow colour keeps useBias
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], false);
       if (CACHED) { if (myA == a) solveLane<false>(bs, sp, c, c.indexA, c.indexB, I, J); }
@@ -1179,16 +1188,17 @@ namespace b2c {
 // ------------------------------------------------------------------------------------------------------------
 // Phase 3: FinalizeBodiesTask (src/Solver.cs:402-503) + refit (:1191-1237, src/DynamicTree.cs:482-505)
 // ------------------------------------------------------------------------------------------------------------
-// World.SolveContinuous (src/Solver.cs:315-401) for a non-bullet fast body: every shape of the body sweeps the static tree with the union
-// of its old and new boxes (DynamicTree.Query order: child2 first), ContinuousQueryCallback (:224-314) runs TimeOfImpact on every
-// candidate in that order with the running fraction as the sweep limit, and the smallest positive fraction wins. Returns that fraction
-// (1 = no hit). Sensor shapes in the static tree collect the visitors whose sweep reaches them before the hit (Sensor.hits).
+// World.SolveContinuous (src/Solver.cs:315-401): every shape of the fast body sweeps the static tree (a bullet: then the kinematic and the
+// dynamic tree, :342-346) with the union of its old and new boxes (DynamicTree.Query order: child2 first), ContinuousQueryCallback
+// (:224-314) runs TimeOfImpact on every candidate in that order with the running fraction as the sweep limit, and the smallest positive
+// fraction wins. Returns that fraction (1 = no hit). Sensor shapes collect the visitors whose sweep reaches them before the hit (Sensor.hits).
+// A query ends at the fast shape's own proxy (the callback returns false, :230): in the dynamic tree a bullet sees only what comes before itself.
 constexpr int kContinuousSensorHits = 8;
-__device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf xf2, const Sweep& sweep, uint32_t* simFlags) {
+__device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf xf2, const Sweep& sweep, uint32_t* simFlags, bool isBullet) {
   Scalars& sc = *d.sc;
   float fraction = 1.0f;
   int hitSensor[kContinuousSensorHits], hitVisitor[kContinuousSensorHits]; float hitFraction[kContinuousSensorHits]; int nSensorHits = 0;
-  const TreeDev& t = d.trees[kStaticBody];
+  const int treeCount = isBullet ? 3 : 1;              // kStaticBody = 0, kKinematicBody = 1, kDynamicBody = 2: the order of :341-346
   for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
     const ShapeDev& fastShape = d.shapes[sid];
     Box box1 = toBox(d.shapeAABB[sid]);
@@ -1196,9 +1206,11 @@ __device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf 
     d.shapeAABB[sid] = fromBox(box2);                    // raw AABB, no speculative margin (:337-339)
     if (fastShape.sensorIndex != -1) continue;
     const Box query = boxUnion(box1, box2);
+    const DistProxy proxyB = makeDistProxy(fastShape.geom);
+    for (int treeIndex = 0; treeIndex < treeCount; treeIndex++) {
+    const TreeDev& t = d.trees[treeIndex];
     int root = t.meta[0];
     if (t.meta[1] == 0 || root == -1) continue;
-    const DistProxy proxyB = makeDistProxy(fastShape.geom);
     int stack[kQueryStack]; int sp = 0;
     stack[sp++] = root;
     while (sp > 0) {
@@ -1215,11 +1227,18 @@ __device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf 
       const bool isSensor = shape.sensorIndex != -1;
       if (isSensor && (!(shape.flags & SF_SENSOR_EVENTS) || !(fastShape.flags & SF_SENSOR_EVENTS))) continue;
       if (!shouldShapesCollide(fastShape, shape)) continue;
-      if (d.bodySimFlags[shape.bodyId] & kIsBullet) continue;
+      const int otherSim = d.bodySim[shape.bodyId];
+      if ((otherSim < 0 ? d.bodySimFlags[shape.bodyId] : d.simFlags[otherSim]) & kIsBullet) continue;   // bullets do not stop each other (:241)
       if (!shouldBodiesCollide(d, bodyId, shape.bodyId)) continue;
       // (custom filter and chain segments cannot exist: refused at creation)
-      const float4 oxf = d.bodyXf[shape.bodyId]; const float2 oc = d.bodyCenter[shape.bodyId]; const float4 om = d.bodyMass[shape.bodyId];
-      Sweep sweepA; sweepA.localCenter = mk(om.z, om.w); sweepA.c1 = mk(oc.x, oc.y); sweepA.c2 = sweepA.c1; sweepA.q1 = mkRot(oxf.z, oxf.w); sweepA.q2 = sweepA.q1;   // BodySim.MakeSweep of a body at rest in the static set
+      Sweep sweepA;                                      // BodySim.MakeSweep src/Body.cs:172
+      if (otherSim < 0) {                                // a body at rest in the static set
+        const float4 oxf = d.bodyXf[shape.bodyId]; const float2 oc = d.bodyCenter[shape.bodyId]; const float4 om = d.bodyMass[shape.bodyId];
+        sweepA.localCenter = mk(om.z, om.w); sweepA.c1 = mk(oc.x, oc.y); sweepA.c2 = sweepA.c1; sweepA.q1 = mkRot(oxf.z, oxf.w); sweepA.q2 = sweepA.q1;
+      } else {                                           // an awake body, finalized (and, if fast, stopped) before the bullet stage: center0 == center
+        const float4 o0 = d.simPose0[otherSim], o1 = d.simPose[otherSim], ol = d.simLocal[otherSim];
+        sweepA.localCenter = mk(ol.x, ol.y); sweepA.c1 = mk(o0.x, o0.y); sweepA.c2 = mk(o1.x, o1.y); sweepA.q1 = mkRot(o0.z, o0.w); sweepA.q2 = mkRot(o1.z, o1.w);
+      }
       const DistProxy proxyA = makeDistProxy(shape.geom);
       bool throws = false;
       atomicAdd(&sc.toiCandidates, 1);
@@ -1243,6 +1262,7 @@ __device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf 
       }
       if (didHit) { *simFlags |= kHadTimeOfImpact; fraction = hit; }
     }
+    }
   }
   for (int k = 0; k < nSensorHits; k++) {                // :398-400, then src/Solver.cs:1276-1289
     if (!(hitFraction[k] < fraction)) continue;
@@ -1252,6 +1272,44 @@ __device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf 
     else atomicOr(&sc.errorFlags, (int)ERR_SENSOR_CAPACITY);
   }
   return fraction;
+}
+
+// SolveContinuous after the queries (:356-397): a hit stops the body at the time of impact and recomputes its shape boxes; without a hit the
+// raw boxes written by the sweep stay. Either way a box that left its fat box grows it (shape flagged, sim gets EnlargeBounds).
+// Returns the number of shapes flagged.
+__device__ __forceinline__ int continuousOutcome(const WorldDev& d, int i, int bodyId, const Sweep& sweep, float fraction, uint32_t& simFlags, Xf& xf, V2& center, Rot& q) {
+  int enlarged = 0;
+  if (fraction < 1.0f) {                             // :356-379 the body stops at the time of impact
+    q = nlerpRot(sweep.q1, sweep.q2, fraction);
+    center = lerp(sweep.c1, sweep.c2, fraction);
+    xf = mkXf(center - rotate(q, sweep.localCenter), q);
+    d.simPose[i] = make_float4(center.x, center.y, q.c, q.s);
+    d.bodyXf[bodyId] = make_float4(xf.p.x, xf.p.y, q.c, q.s);
+    d.bodyCenter[bodyId] = make_float2(center.x, center.y);
+    d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
+    for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+      Box aabb = boxGrow(geomAABB(d.shapes[sid].geom, xf), kSpeculativeDistance);
+      d.shapeAABB[sid] = fromBox(aabb);
+      if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
+        d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
+        d.shapes[sid].flags |= SF_ENLARGED;
+        simFlags |= kEnlargeBounds;
+        enlarged++;
+      }
+    }
+  } else {                                           // :380-397
+    d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
+    for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+      Box aabb = toBox(d.shapeAABB[sid]);
+      if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
+        d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
+        d.shapes[sid].flags |= SF_ENLARGED;
+        simFlags |= kEnlargeBounds;
+        enlarged++;
+      }
+    }
+  }
+  return enlarged;
 }
 
 __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int stride) {
@@ -1285,39 +1343,16 @@ __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int
     else d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
     int enlarged = 0;
     if (isFast) {
-      // SolveContinuous :315-401 (non-bullet body: static tree only)
-      float4 pose0 = d.simPose0[i];
-      Sweep sweep; sweep.localCenter = localCenter; sweep.c1 = mk(pose0.x, pose0.y); sweep.c2 = center; sweep.q1 = mkRot(pose0.z, pose0.w); sweep.q2 = q;   // BodySim.MakeSweep src/Body.cs:172
-      const float fraction = solveContinuous(d, bodyId, xf, sweep, &simFlags);
-      if (fraction < 1.0f) {                             // :356-379 the body stops at the time of impact
-        q = nlerpRot(sweep.q1, sweep.q2, fraction);
-        center = lerp(sweep.c1, sweep.c2, fraction);
-        xf = mkXf(center - rotate(q, localCenter), q);
-        d.simPose[i] = make_float4(center.x, center.y, q.c, q.s);
-        d.bodyXf[bodyId] = make_float4(xf.p.x, xf.p.y, q.c, q.s);
-        d.bodyCenter[bodyId] = make_float2(center.x, center.y);
-        d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
-        for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
-          Box aabb = boxGrow(geomAABB(d.shapes[sid].geom, xf), kSpeculativeDistance);
-          d.shapeAABB[sid] = fromBox(aabb);
-          if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
-            d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
-            d.shapes[sid].flags |= SF_ENLARGED;
-            simFlags |= kEnlargeBounds;
-            enlarged++;
-          }
-        }
-      } else {                                           // :380-397
-        d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
-        for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
-          Box aabb = toBox(d.shapeAABB[sid]);
-          if (!boxContains(toBox(d.shapeFat[sid]), aabb)) {
-            d.shapeFat[sid] = fromBox(boxGrow(aabb, kAABBMargin));
-            d.shapes[sid].flags |= SF_ENLARGED;
-            simFlags |= kEnlargeBounds;
-            enlarged++;
-          }
-        }
+      if (simFlags & kIsBullet) {
+        // a fast bullet waits for the bullet stage (:447-449): pose0 and the shape boxes stay, every shape is buffered as a move by the refit (:1210-1218)
+        atomicAdd(&d.sc->bulletCount, 1);
+        for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) enlarged++;
+      } else {
+        // SolveContinuous :315-401 (non-bullet body: static tree only)
+        float4 pose0 = d.simPose0[i];
+        Sweep sweep; sweep.localCenter = localCenter; sweep.c1 = mk(pose0.x, pose0.y); sweep.c2 = center; sweep.q1 = mkRot(pose0.z, pose0.w); sweep.q2 = q;   // BodySim.MakeSweep src/Body.cs:172
+        const float fraction = solveContinuous(d, bodyId, xf, sweep, &simFlags, false);
+        enlarged = continuousOutcome(d, i, bodyId, sweep, fraction, simFlags, xf, center, q);
       }
     } else {
       for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
@@ -1351,6 +1386,20 @@ __device__ __forceinline__ void atomicMaxF(float* addr, float v) {
   v = v + 0.0f;
   if (v >= 0.0f) atomicMax((int*)addr, __float_as_int(v)); else atomicMin((unsigned*)addr, __float_as_uint(v));
 }
+// DynamicTree.EnlargeProxy (src/DynamicTree.cs:482-505): the leaf takes the fat box, every ancestor grows to contain it and is flagged Enlarged
+__device__ __forceinline__ void enlargeLeaf(const TreeDev& t, int id, float4 fat) {
+  t.aabb[id] = fat;
+  for (int p = t.parent[id]; p != -1; p = t.parent[p]) {
+    float* a = (float*)&t.aabb[p];
+    const volatile float* av = a;                     // most ancestors already contain the box: test before the atomic
+    float4 cur = make_float4(av[0], av[1], av[2], av[3]);
+    if (fat.x < cur.x) atomicMinF(a + 0, fat.x);
+    if (fat.y < cur.y) atomicMinF(a + 1, fat.y);
+    if (fat.z > cur.z) atomicMaxF(a + 2, fat.z);
+    if (fat.w > cur.w) atomicMaxF(a + 3, fat.w);
+    if (!((*(volatile uint32_t*)&t.hf[p] >> 16) & NODE_ENLARGED)) atomicOr(&t.hf[p], (uint32_t)NODE_ENLARGED << 16);
+  }
+}
 // Enlarged bodies in ascending sim index, shapes in body list order: BroadPhase.EnlargeProxy + BufferMove (:1202-1233).
 // EnlargeProxy's result (ancestor boxes = union, every ancestor flagged Enlarged) does not depend on the order of the
 // calls, so it is applied with float atomics; the move array order is produced by the prefix sum.
@@ -1361,6 +1410,15 @@ __device__ void p_refit(const WorldDev& d, int tid, int stride) {
     int next = (i + 1 < n) ? d.bodyEnlargedCount[i + 1] + d.scanBlockSums[(i + 1) / (int)blockDim.x] : d.sc->moveCount;
     if (next == offset) continue;
     int bodyId = d.simBodyId[i];
+    if ((d.simFlags[i] & (kIsBullet | kIsFast)) == (kIsBullet | kIsFast)) {     // :1210-1218 a fast bullet: BufferMove only, the bullet stage enlarges
+      for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+        int key = d.shapes[sid].proxyKey;
+        if (offset < d.moveCapacity) d.moveArray[offset] = key;
+        offset++;
+        d.trees[key & 3].moved[key >> 2] = 1;
+      }
+      continue;
+    }
     for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
       ShapeDev& sh = d.shapes[sid];
       if (!(sh.flags & SF_ENLARGED)) continue;
@@ -1368,21 +1426,54 @@ __device__ void p_refit(const WorldDev& d, int tid, int stride) {
       int key = sh.proxyKey;
       const TreeDev& t = d.trees[key & 3];
       int id = key >> 2;
-      float4 fat = d.shapeFat[sid];
-      t.aabb[id] = fat;
       if (offset < d.moveCapacity) d.moveArray[offset] = key;
       offset++;
       t.moved[id] = 1;
-      for (int p = t.parent[id]; p != -1; p = t.parent[p]) {
-        float* a = (float*)&t.aabb[p];
-        const volatile float* av = a;                     // most ancestors already contain the box: test before the atomic
-        float4 cur = make_float4(av[0], av[1], av[2], av[3]);
-        if (fat.x < cur.x) atomicMinF(a + 0, fat.x);
-        if (fat.y < cur.y) atomicMinF(a + 1, fat.y);
-        if (fat.z > cur.z) atomicMaxF(a + 2, fat.z);
-        if (fat.w > cur.w) atomicMaxF(a + 3, fat.w);
-        if (!((*(volatile uint32_t*)&t.hf[p] >> 16) & NODE_ENLARGED)) atomicOr(&t.hf[p], (uint32_t)NODE_ENLARGED << 16);
+      enlargeLeaf(t, id, d.shapeFat[sid]);
+    }
+  }
+}
+
+// BulletBodyTask (src/Solver.cs:728-738): SolveContinuous for this step's fast bullets, after the refit (the dynamic tree holds the enlarged
+// boxes of everything else; every other awake body is at its end pose with center0 == center, so the bullets are independent of each other).
+__device__ void p_bullets(const WorldDev& d, int tid, int stride) {
+  const int n = d.awakeCount;
+  for (int i = tid; i < n; i += stride) {
+    uint32_t simFlags = d.simFlags[i];
+    if ((simFlags & (kIsBullet | kIsFast)) != (kIsBullet | kIsFast)) continue;
+    const int bodyId = d.simBodyId[i];
+    const float4 pose = d.simPose[i], pose0 = d.simPose0[i], loc = d.simLocal[i];
+    V2 center = mk(pose.x, pose.y); Rot q = mkRot(pose.z, pose.w);
+    Sweep sweep; sweep.localCenter = mk(loc.x, loc.y); sweep.c1 = mk(pose0.x, pose0.y); sweep.c2 = center; sweep.q1 = mkRot(pose0.z, pose0.w); sweep.q2 = q;
+    Xf xf = mkXf(center - rotate(q, sweep.localCenter), q);
+    const float fraction = solveContinuous(d, bodyId, xf, sweep, &simFlags, true);
+    continuousOutcome(d, i, bodyId, sweep, fraction, simFlags, xf, center, q);
+    d.simFlags[i] = simFlags;
+    if (fraction < 1.0f && d.moveOut) { d.moveOut[i].transform.p = {xf.p.x, xf.p.y}; d.moveOut[i].transform.q = {q.c, q.s}; }   // :366-367
+  }
+}
+// :1247-1269 the bullets' enlarged proxies grow in the dynamic tree (no BufferMove: the refit put every bullet shape in the move set)
+__device__ void p_bullet_enlarge(const WorldDev& d, int tid, int stride) {
+  const int n = d.awakeCount;
+  for (int i = tid; i < n; i += stride) {
+    uint32_t simFlags = d.simFlags[i];
+    if ((simFlags & (kIsBullet | kIsFast)) != (kIsBullet | kIsFast)) continue;
+    const int bodyId = d.simBodyId[i];
+    if (simFlags & kEnlargeBounds) {
+      simFlags &= ~(uint32_t)kEnlargeBounds;
+      d.simFlags[i] = simFlags;
+      const TreeDev& t = d.trees[kDynamicBody];
+      for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
+        ShapeDev& sh = d.shapes[sid];
+        if (!(sh.flags & SF_ENLARGED)) continue;
+        sh.flags &= ~SF_ENLARGED;
+        enlargeLeaf(t, sh.proxyKey >> 2, d.shapeFat[sid]);
       }
+    }
+    if (d.bodyOut) {                               // the bulk body read-back written by p_finalize, with the pose and flags of the bullet stage
+      const float4 pose = d.simPose[i], xf = d.bodyXf[bodyId];
+      B2CBodyRead& r = d.bodyOut[bodyId];
+      r.transform.p = {xf.x, xf.y}; r.transform.q = {xf.z, xf.w}; r.center = {pose.x, pose.y}; r.flags = simFlags;
     }
   }
 }
@@ -1660,9 +1751,15 @@ template <class S> __device__ void finalizePhase(const S& grid, const WorldDev& 
     gridScan<int>(grid, d.bodyEnlargedCount, d.scanBlockSums, d.awakeCount, &s.moveCount);
     p_refit(d, tid, stride);
     grid.sync();
+    if (s.bulletCount > 0) {                        // bullet stage :1238-1272 (uniform: counted by p_finalize before the barriers above; a fast
+      p_bullets(d, tid, stride);                    // bullet counts its shapes as enlarged, so the test lives in this branch and a step
+      grid.sync();                                  // without moves pays nothing for it)
+      p_bullet_enlarge(d, tid, stride);
+      grid.sync();
+    }
   } else if (tid == 0) s.moveCount = 0;
   phase_sensors(grid, d, sp.endIndex);              // World.OverlapSensors, api/World.cs:97-102 (before the end-event buffers trade places)
-  if (tid == 0) { s.enlargedShapeCount = 0; p_step_finish(d, newEndIndex); }
+  if (tid == 0) { s.enlargedShapeCount = 0; s.bulletCount = 0; p_step_finish(d, newEndIndex); }
 }
 __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp, int newEndIndex) {
   cg::grid_group g = cg::this_grid();

@@ -110,6 +110,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int rebuildLevels[3];
   int colLen[kGraphColorCount];         // GraphColor.contactSims.Count per colour (src/ConstraintGraph.cs:10-24); [kOverflowIndex] = contacts in the overflow colour
   int sensorParity, sensorBeginCount, sensorEndCount[2];   // src/Sensor.cs: which overlap buffer is overlaps2; sensor event counts (end events double-buffered like contact end events)
+  int bulletCount;                      // fast bullets of this step (StepContext.bulletBodyCount, src/Solver.cs:447-449)
   unsigned long long dbg[16];           // order-independent state checksums per phase (B2CUDA_DEBUG_CHECKSUMS=1; b2cuda_world_debug_checksums)
 };
 

@@ -265,6 +265,136 @@ def fast_rain(world, n=48, seed=5, walls="box"):
     return ground, strip, bodies
 
 
+def bullet_range(world, n=24, seed=7, targets="box"):
+    """Bullets (BodyDef.isBullet, src/Solver.cs:447-449,728-738,1238-1272): small fast bodies fired at thin DYNAMIC plates and a moving
+    kinematic plate, which only the bullet stage's sweep of the kinematic and dynamic trees can stop; every third projectile is not a
+    bullet (it stops at static shapes only and tunnels through the plates), two bullets cross each other's path (bullets ignore bullets),
+    one bullet is jointed to a plate with collideConnected off. targets="box": every target is a 4-point polygon (the port's cached-simplex
+    read stays in range); targets="round": dynamic circles, for which the C# code indexes past the proxy and throws.
+    Returns (ground, plates, projectiles)."""
+    sd = _shape_def(enableSensorEvents=1)
+    ground = world.CreateBody(api.default_body_def())
+    world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(30.0, 0.05, (0.0, -0.05)))
+    world.CreatePolygonShape(ground, sd, geo.MakeOffsetBox(0.05, 8.0, (16.0, 8.0)))
+    world.CreatePolygonShape(ground, _shape_def(isSensor=1, enableSensorEvents=1), geo.MakeOffsetBox(0.2, 8.0, (14.0, 8.0)))
+    plates = []
+    for k in range(6):                                  # thin upright dynamic plates, 0.08 m thick, standing on the ground
+        b = _dynamic_body(world, 4.0 + 1.5 * k, 1.5)
+        if targets == "box":
+            world.CreatePolygonShape(b, sd, geo.MakeBox(0.04, 1.5))
+        else:
+            world.CreateCircleShape(b, sd, geo.Circle((0.0, 0.0), 0.6))
+        plates.append(b)
+    bd = api.default_body_def()
+    bd.type = api.KINEMATIC_BODY
+    bd.position = api.Vec2(-3.0, 6.0)
+    bd.linearVelocity = api.Vec2(0.5, 0.0)
+    mover = world.CreateBody(bd)
+    world.CreatePolygonShape(mover, sd, geo.MakeBox(0.04, 2.0))
+    plates.append(mover)
+    shapes = [geo.MakeBox(0.08, 0.05), geo.Circle((0.0, 0.0), 0.07), geo.Capsule((-0.08, 0.0), (0.08, 0.0), 0.04), geo.MakeRoundedBox(0.05, 0.05, 0.02)]
+    state = seed
+    projectiles = []
+    for k in range(n):
+        state, y = _uniform(state, 0.4, 7.5)
+        state, vx = _uniform(state, 80.0, 260.0)
+        state, vy = _uniform(state, -15.0, 15.0)
+        state, w = _uniform(state, -30.0, 30.0)
+        b = _dynamic_body(world, -8.0 - 0.3 * k, y, linearVelocity=api.Vec2(vx, vy), angularVelocity=w, isBullet=0 if k % 3 == 2 else 1,
+                          gravityScale=0.2)
+        # (a projectile that is not a bullet is itself a target of the bullets: polygons only, or the C# code throws)
+        world.CreateShape(b, sd, shapes[k % len(shapes)] if k % 3 != 2 else shapes[0 if k % 2 else 3])
+        if k % 5 == 0:
+            world.CreatePolygonShape(b, sd, geo.MakeOffsetBox(0.03, 0.03, (0.0, 0.09)))
+        projectiles.append(b)
+    # two bullets on crossing paths
+    for sx in (-1.0, 1.0):
+        b = _dynamic_body(world, 1.0 + 2.0 * sx, 10.0, linearVelocity=api.Vec2(-120.0 * sx, 0.0), isBullet=1, gravityScale=0.0)
+        world.CreatePolygonShape(b, sd, geo.MakeBox(0.06, 0.06))
+        projectiles.append(b)
+    # a bullet tied to the first plate by a joint that switches their collision off: it flies through that plate and stops at the next
+    b = _dynamic_body(world, 2.5, 1.5, linearVelocity=api.Vec2(200.0, 0.0), isBullet=1, gravityScale=0.0)
+    world.CreatePolygonShape(b, sd, geo.MakeBox(0.05, 0.05))
+    jd = api.default_joint_def(api.capi.JOINT_DISTANCE)
+    jd.bodyIdA, jd.bodyIdB = plates[0], b
+    jd.length = 1.5
+    jd.enableSpring, jd.hertz, jd.dampingRatio = 1, 0.2, 0.0
+    jd.collideConnected = 0
+    world.CreateJoint(jd)
+    projectiles.append(b)
+    return ground, plates, projectiles
+
+
+def joint_hub(world, spokes=28, anchors=25):
+    """Joints in the overflow colour (src/ConstraintGraph.cs:91-128, src/Joint.cs:377-394): a dynamic hub with `spokes` joints to dynamic
+    satellites (a pair of dynamic bodies may use 20 colours: the rest overflow) and a second hub with `anchors` joints to the static ground
+    (22 colours). Plain revolutes, rigid and springy distance joints and velocity motors (the bit-exact types), thresholds on some of
+    them: an overflow joint never reports a joint event. The hubs' contacts find every colour taken and overflow as well.
+    Returns (hub, satellites, joint ids)."""
+    J = api.capi
+    sd = _shape_def()
+    ground = world.CreateBody(api.default_body_def())
+    world.CreateSegmentShape(ground, sd, geo.Segment((-30.0, 0.0), (30.0, 0.0)))
+
+    def jdef(t, a, b, pa, pb):
+        d = api.default_joint_def(t)
+        d.bodyIdA, d.bodyIdB = a, b
+        d.localFrameA.p = api.Vec2(float(f32(pa[0])), float(f32(pa[1])))
+        d.localFrameB.p = api.Vec2(float(f32(pb[0])), float(f32(pb[1])))
+        return d
+
+    joints = []
+    hub = _dynamic_body(world, 0.0, 4.0, angularVelocity=0.7)
+    world.CreatePolygonShape(hub, sd, geo.MakeBox(0.8, 0.8))
+    satellites = []
+    for k in range(spokes):
+        a = 2.0 * np.pi * k / spokes
+        cx, cy = 3.0 * np.cos(a), 3.0 * np.sin(a)
+        b = _dynamic_body(world, cx, 4.0 + cy)
+        if k % 2:
+            world.CreateCircleShape(b, sd, geo.Circle((0.0, 0.0), 0.25))
+        else:
+            world.CreatePolygonShape(b, sd, geo.MakeBox(0.2, 0.2))
+        satellites.append(b)
+        hx, hy = 0.7 * np.cos(a), 0.7 * np.sin(a)
+        kind = k % 4
+        if kind == 0:
+            d = jdef(J.JOINT_REVOLUTE, hub, b, (hx, hy), (hx - cx, hy - cy))
+            d.forceThreshold = 2.0
+        elif kind == 1:
+            d = jdef(J.JOINT_DISTANCE, hub, b, (hx, hy), (0.0, 0.0))
+            d.length = 2.3
+        elif kind == 2:
+            d = jdef(J.JOINT_DISTANCE, hub, b, (hx, hy), (0.0, 0.0))
+            d.length = 2.3
+            d.enableSpring, d.hertz, d.dampingRatio = 1, 2.0, 0.2
+            d.enableLimit, d.minLength, d.maxLength = 1, 1.5, 3.0
+        else:
+            d = jdef(J.JOINT_MOTOR, hub, b, (cx, cy), (0.0, 0.0))
+            d.linearVelocity, d.maxVelocityForce = api.Vec2(0.0, 0.0), 30.0
+            d.angularVelocity, d.maxVelocityTorque = 0.5, 2.0
+        d.collideConnected = 1 if k % 5 == 0 else 0
+        joints.append(world.CreateJoint(d))
+    # a second hub tied to the static ground body
+    hub2 = _dynamic_body(world, 12.0, 3.0)
+    world.CreatePolygonShape(hub2, sd, geo.MakeBox(1.0, 0.5))
+    for k in range(anchors):
+        x = 12.0 + (k - anchors / 2) * 0.4
+        if k % 3 == 0:
+            d = jdef(J.JOINT_REVOLUTE, ground, hub2, (12.0, 3.0 + 0.001 * k), (0.0, 0.001 * k))
+            d.forceThreshold = 1.0
+        else:
+            d = jdef(J.JOINT_DISTANCE, ground, hub2, (x, 8.0), ((k % 5 - 2) * 0.2, 0.0))
+            d.length = 5.0
+            d.enableSpring, d.hertz, d.dampingRatio = 1, 1.0 + 0.1 * k, 0.1
+        joints.append(world.CreateJoint(d))
+    # boxes dropped on both hubs: their contacts with a hub find its colours taken
+    for k in range(6):
+        b = _dynamic_body(world, -0.5 + 0.2 * k if k < 3 else 11.5 + 0.3 * (k - 3), 5.5 + 0.6 * (k % 3))
+        world.CreatePolygonShape(b, sd, geo.MakeBox(0.25, 0.25))
+    return hub, satellites, joints
+
+
 def overflow_plank(world, n=26):
     """A long dynamic plank resting on n small dynamic boxes: the plank needs more than the 20 dynamic colours, so some
     contacts land in the overflow colour (src/ConstraintGraph.cs:140) and are solved by the scalar overflow path."""

@@ -71,6 +71,7 @@ int32_t b2o_create_joint(World* w, const B2CJointDef* d, int32_t* jointId) {
 }
 int32_t b2o_joint_set_param(World* w, int32_t id, int32_t param, float v) { return w->JointSetParam(id, param, v) ? 0 : -1; }
 int32_t b2o_joint_enable(World* w, int32_t id, int32_t feature, int32_t flag) { return w->JointEnable(id, feature, flag != 0) ? 0 : -1; }
+int32_t b2o_body_set_bullet(World* w, int32_t id, int32_t flag) { if (id < 0 || id >= (int)w->bodies.size() || w->bodies[id].id != id) return -1; w->SetBullet(id, flag != 0); return 0; }
 int32_t b2o_joint_set_local_frame(World* w, int32_t id, int32_t which, B2CTransform f) { if (id < 0 || id >= (int)w->joints.size() || w->joints[id].jointId != id) return -1; w->JointSetLocalFrame(id, which, T(f)); return 0; }
 int32_t b2o_joint_set_collide_connected(World* w, int32_t id, int32_t flag) { if (id < 0 || id >= (int)w->joints.size() || w->joints[id].jointId != id) return -1; w->JointSetCollideConnected(id, flag != 0); return 0; }
 int32_t b2o_joint_set_limits(World* w, int32_t id, float lo, float hi) { return w->JointSetLimits(id, lo, hi) ? 0 : -1; }

@@ -41,7 +41,8 @@ void World::FinalizeBodies(StepContext& stepContext, BitSet& enlargedSimBitSet) 
       body.sleepTime = 0;
       if (body.type == kDynamicBody && enableContinuous && maxVelocity * stepContext.dt > 0.5f * sim.minExtent) {
         sim.flags |= kIsFast;
-        SolveContinuous(simIndex);      // bullets are rejected at creation
+        if (sim.flags & kIsBullet) bulletBodies.push_back(simIndex);     // :447-449 (one worker: ascending sim index)
+        else SolveContinuous(simIndex);
       } else { sim.center0 = sim.center; sim.rotation0 = sim.transform.q; }
     } else { sim.center0 = sim.center; sim.rotation0 = sim.transform.q; body.sleepTime += stepContext.dt; }
     Transform transform = sim.transform;
@@ -130,7 +131,9 @@ void World::Solve(StepContext& stepContext) {      // :739-1322
       BodySim& bodySim = awakeSet.bodySims[bodySimIndex];
       Body& body = bodies[bodySim.bodyId];
       int shapeId = body.headShapeId;
-      while (shapeId != -1) {
+      if ((bodySim.flags & (kIsBullet | kIsFast)) == (kIsBullet | kIsFast)) {     // :1210-1218 a fast bullet: its proxies are enlarged after the bullet stage
+        while (shapeId != -1) { Shape& shape = shapes[shapeId]; BufferMove(shape.proxyKey); shapeId = shape.nextShapeId; }
+      } else while (shapeId != -1) {
         Shape& shape = shapes[shapeId];
         if (shape.enlargedAABB) {
           trees[ProxyType(shape.proxyKey)].EnlargeProxy(ProxyId(shape.proxyKey), shape.fatAABB);   // src/BroadPhase.cs:96-104
@@ -142,6 +145,22 @@ void World::Solve(StepContext& stepContext) {      // :739-1322
       word &= word - 1;
     }
   }
+  // bullet stage :1238-1272: continuous collision of the fast bullets against all three trees, then their proxies are enlarged (no BufferMove:
+  // the refit above put them in the move set)
+  for (int simIndex : bulletBodies) SolveContinuous(simIndex);
+  for (int simIndex : bulletBodies) {
+    BodySim& bulletBodySim = awakeSet.bodySims[simIndex];
+    if (!(bulletBodySim.flags & kEnlargeBounds)) continue;
+    bulletBodySim.flags &= ~kEnlargeBounds;
+    Body& bulletBody = bodies[bulletBodySim.bodyId];
+    int shapeId = bulletBody.headShapeId;
+    while (shapeId != -1) {
+      Shape& shape = shapes[shapeId];
+      if (shape.enlargedAABB) { shape.enlargedAABB = false; trees[kDynamicBody].EnlargeProxy(ProxyId(shape.proxyKey), shape.fatAABB); }
+      shapeId = shape.nextShapeId;
+    }
+  }
+  bulletBodies.clear();
 }
 
 void World::Step(float timeStep, int subStepCount) {      // api/World.cs:31-113

@@ -21,7 +21,7 @@ World::World(const WorldDef& def) {      // src/World.cs:183-226, src/Constraint
 }
 
 int World::CreateBody(const BodyDef& def) {     // api/Body.cs:16-105
-  if (!def.isEnabled || def.isBullet || !(def.isAwake || !def.enableSleep)) { counters.unsupported++; lastError = "oracle: disabled/bullet/asleep bodies not restated"; }
+  if (!def.isEnabled || !(def.isAwake || !def.enableSleep)) { counters.unsupported++; lastError = "oracle: disabled/asleep bodies not restated"; }
   int setId = def.type == kStaticBody ? kStaticSet : kAwakeSet;
   int bodyId = bodyIdPool.AllocId();
   uint32_t lockFlags = (def.lockLinearX ? kLockLinearX : 0) | (def.lockLinearY ? kLockLinearY : 0) | (def.lockAngularZ ? kLockAngularZ : 0) |

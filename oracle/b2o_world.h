@@ -2,7 +2,7 @@
 // Data model of the reference world restricted to the rigid-body step path:
 // src/Body.cs, src/Shape.cs, src/Contact.cs, src/Joint.cs, src/joints/RevoluteJoint.cs,
 // src/ConstraintGraph.cs, src/SolverSet.cs (static + awake sets only), src/BroadPhase.cs.
-// Sensors: src/Sensor.cs (b2o_sensor.cpp). Not restated (asserted unused): islands/sleep, chains, bullets/TOI, particles.
+// Sensors: src/Sensor.cs (b2o_sensor.cpp). Continuous collision and bullets: b2o_continuous.inc. Not restated (asserted unused): islands/sleep, chains.
 #pragma once
 #include <vector>
 #include <unordered_set>
@@ -245,6 +245,7 @@ class World {
   void SetLinearDamping(int bodyId, float v);
   void SetAngularDamping(int bodyId, float v);
   void SetGravityScale(int bodyId, float v);
+  void SetBullet(int bodyId, bool flag) { BodySim& s = GetBodySim(bodies[bodyId]); if (flag) s.flags |= kIsBullet; else s.flags &= ~(uint32_t)kIsBullet; }   // api/Body.cs:835-842
   void Step(float timeStep, int subStepCount);
 
   // --- state ---
@@ -265,6 +266,7 @@ class World {
   bool enableSleep, enableWarmStarting = true, enableContactSoftening, enableContinuous, enableSpeculative = true;
   uint64_t stepIndex = 0;
   Counters counters;
+  std::vector<int> bulletBodies;           // StepContext.bulletBodies src/Solver.cs:447-449: sim indices of this step's fast bullets
   double profileMs[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // cumulative: step, pairs, collide, solve, solverStages
   std::vector<uint64_t> lastNewPairKeys;   // pair keys created by the last UpdateBroadPhasePairs, in creation order
   std::string lastError;

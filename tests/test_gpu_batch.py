@@ -24,6 +24,7 @@ def _builders():
     out.append(lambda w: scenes.bounce_mix(w, n=24, seed=2))
     out.append(lambda w: scenes.joint_grid(w, n=6))
     out.append(lambda w: scenes.fast_rain(w, n=30))             # continuous collision + sensors (a polygon strip) at CTA scope
+    out.append(lambda w: scenes.bullet_range(w, n=15))          # the bullet stage at CTA scope
     out.append(lambda w: None)                                  # an empty world inside a batch
     return out
 

@@ -1147,8 +1147,8 @@ def test_joint_local_frames_and_collide_connected_between_steps_bit_exact():
 
 
 def test_body_sleep_enable_bullet_surface_while_sleep_is_not_built():
-    """api/Body.cs:664-842: the calls that only wake or store succeed, the calls that need islands / the disabled set / the bullet
-    stage are refused loudly (B2C_E_UNSUPPORTED = -2), and none of them disturbs the simulation."""
+    """api/Body.cs:664-842: the calls that only wake or store succeed, the calls that need islands / the disabled set are refused
+    loudly (B2C_E_UNSUPPORTED = -2), and none of them disturbs the simulation (SetBullet: test_bullets_*)."""
     cuda = api.World(api.CudaBackend(), scenes.world_def())
     try:
         scenes.add_pyramid(cuda, 4)
@@ -1163,7 +1163,7 @@ def test_body_sleep_enable_bullet_surface_while_sleep_is_not_built():
         cuda.SetAwake(0, False)              # a static body: nothing to do
         cuda.EnableBody(b)
         cuda.SetBullet(b, False)
-        for call in (lambda: cuda.SetAwake(b, False), lambda: cuda.DisableBody(b), lambda: cuda.SetBullet(b, True)):
+        for call in (lambda: cuda.SetAwake(b, False), lambda: cuda.DisableBody(b)):
             with pytest.raises(api.B2Error, match="rc=-2"):
                 call()
         with pytest.raises(api.B2Error):
@@ -1302,3 +1302,106 @@ def test_continuous_parallel_motion_is_not_stopped():
         assert np.float32(w.ReadBodies()[1]["transform"]["p"]["x"]) == x
     finally:
         w.Destroy()
+
+
+def test_bullets_bit_exact():
+    """BodyDef.isBullet (src/Solver.cs:447-449, 728-738, 1210-1218, 1238-1272): fast bullets wait for the bullet stage, sweep the static,
+    kinematic and dynamic trees after the refit, stop at thin dynamic and kinematic plates (or tunnel where the port's cached-simplex read
+    derails the sweep), ignore each other and jointed bodies with collideConnected off; their shapes enter the move set in the refit and
+    their proxies grow after the stage. State, events, move counts and TOI candidate counts must equal the oracle's every step."""
+    res = parity.run_pair(lambda w: scenes.bullet_range(w, n=24), steps=45, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    assert res["toi"] > 300 and res["toi"] == res["toi_oracle"], res
+    res = parity.run_pair(lambda w: scenes.bullet_range(w, n=40, seed=31), steps=30, substeps=2, dt=1.0 / 30.0)
+    assert res["max_rel_err"] == 0.0 and res["toi"] == res["toi_oracle"]
+
+
+def test_bullet_move_events_and_set_bullet_between_steps():
+    """BodyAPI.SetBullet (api/Body.cs:835-842) flips BodySim.flags between steps; the body move events carry the pose the bullet stage
+    left (src/Solver.cs:366-367). Bullets are switched off and on while they fly; a static body takes the call without effect."""
+    from oracle_backend import OracleBackend
+    cuda = api.World(api.CudaBackend(), scenes.world_def())
+    orc = api.World(OracleBackend(), scenes.world_def())
+    try:
+        made = [scenes.bullet_range(w, n=24, seed=11) for w in (cuda, orc)]
+        assert made[0] == made[1]
+        ground, plates, proj = made[0]
+        had_toi = 0
+        for step in range(40):
+            for w in (cuda, orc):
+                if step == 2:
+                    for b in proj[::2]:
+                        w.SetBullet(b, False)
+                    w.SetBullet(ground, True)
+                if step == 5:
+                    for b in proj[::2]:
+                        w.SetBullet(b, True)
+                    w.SetBullet(proj[2], True)           # one that was never a bullet
+                    w.SetBullet(ground, False)
+                w.Step(1.0 / 60.0, 4)
+            a, b = cuda.GetBodyMoveEvents(), orc.GetBodyMoveEvents()
+            assert a.tobytes() == b.tobytes(), f"step {step}: body move events differ"
+            ra, rb = cuda.GetBodyEvents(), orc.GetBodyEvents()
+            assert ra.tobytes() == rb.tobytes(), f"step {step}: body read-back differs"
+            assert cuda.ReadBodies().tobytes() == orc.ReadBodies().tobytes(), f"step {step}"
+            assert cuda.ReadShapes().tobytes() == orc.ReadShapes().tobytes(), f"step {step}"
+            had_toi += int(np.count_nonzero(ra["flags"] & 0x40))
+            ca, co = cuda.GetCounters(), orc.GetCounters()
+            assert (ca.moveCount, ca.contactCount, ca.toiCandidates) == (co.moveCount, co.contactCount, co.toiCandidates)
+        assert had_toi > 0
+    finally:
+        cuda.Destroy()
+        orc.Destroy()
+
+
+def test_bullets_where_the_reference_throws():
+    """A bullet swept against a dynamic circle indexes past proxy A in the C# code (Distance.MakeSimplexFromCache): both sides report the
+    step as failed, in the same step."""
+    from oracle_backend import OracleBackend
+    failed = {}
+    for name, be in (("cuda", api.CudaBackend()), ("oracle", OracleBackend())):
+        w = api.World(be, scenes.world_def())
+        try:
+            scenes.bullet_range(w, targets="round")
+            failed[name] = None
+            for step in range(30):
+                try:
+                    w.Step(1.0 / 60.0, 4)
+                    w.GetCounters()
+                except api.B2Error as e:
+                    assert "throws" in str(e)
+                    failed[name] = step
+                    break
+        finally:
+            w.Destroy()
+    assert failed["cuda"] == failed["oracle"] and failed["cuda"] is not None, failed
+
+
+def test_overflow_joints_bit_exact():
+    """A body with more joints than colours (src/ConstraintGraph.cs:91-128): the surplus joints sit in the overflow colour and are prepared,
+    warm-started and solved serially before the overflow contacts of each stage (src/Joint.cs:377-394, src/Solver.cs:620,633,648,669),
+    relax keeps useBias, and they report no joint events. Joints are destroyed and created between steps, and a hub changes type and back."""
+    holder = {}
+
+    def build(w):
+        holder[w.backend.name] = scenes.joint_hub(w)
+
+    def mutate(w, step):
+        hub, sats, joints = holder[w.backend.name]
+        if step == 6:
+            w.DestroyJoint(joints[22])                      # an overflow joint
+            w.DestroyJoint(joints[3])                       # frees a colour of the hub: the next joint takes it
+        if step == 9:
+            for k in (3, 22):
+                d = api.default_joint_def(api.capi.JOINT_DISTANCE)
+                d.bodyIdA, d.bodyIdB = hub, sats[k]
+                d.length = 2.5
+                d.enableSpring, d.hertz, d.dampingRatio = 1, 3.0, 0.3
+                joints.append(w.CreateJoint(d))
+        if step == 14:
+            w.SetType(hub, api.KINEMATIC_BODY)              # hub joints stay in the graph (the satellites are dynamic) with fresh colours
+        if step == 20:
+            w.SetType(hub, api.DYNAMIC_BODY)
+
+    res = parity.run_pair(build, steps=60, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0 and res["max_overflow"] >= 11, res
