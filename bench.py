@@ -260,10 +260,10 @@ def b200_arm(args, rank, world_size, local_rank):
             for _ in range(n):
                 flush.zero_()
                 torch.cuda.synchronize()
+                w.TimerStart()                 # a CUDA event pair on the world's stream around the step's launches (TimerStop waits for the second)
                 w.Step(DT, SUBSTEPS)
-                w.Synchronize()
-            p = w.GetProfile()
-            step_ms += p.step * n
+                step_ms += w.TimerStop()
+            p = w.GetProfile()                 # phase and kernel times of the same steps: %globaltimer stamps the kernels write (no events between the kernels)
             for i, f in enumerate(phase_names):
                 phases[i] += getattr(p, f) * n
             done += n
@@ -341,6 +341,7 @@ def b200_arm(args, rank, world_size, local_rank):
                          "frac_is": "ALGORITHMIC bytes (SURVEY 8d per-constraint / per-body figures) over the measured copy peak; the lanes and body rows stay on chip, so physical DRAM traffic (`traffic`) is far below it and the kernel is bound by its barrier / dependent-issue chain, not by HBM",
                          "traffic": traffic, "traffic_source": traffic_src,
                          "algorithmic_bytes_per_launch": algo_bytes, "avg_launch_ms": avg_solver_ms,
+                         "avg_launch_ms_is": "end of k_step_front to start of k_finalize_phase, %globaltimer stamps the two kernels write on the world's stream during the timed steps (brackets the solver launch like an event pair, without the ~10 us per step that four cudaEventRecord calls cost); value / ms_per_step are CUDA-event pairs around each step",
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
             "e2e": {"value": total_units / (e2e_ms_max * 1e-3), "unit": "body-substeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(d2h),
                     "note": "Step(dt,substeps) has no per-step host input; scene uploaded once at the first step; each step reads back the body move events (transform + id of every awake body, the reference's GetBodyEvents payload) and the contact begin/end/hit events to host"},

@@ -117,8 +117,7 @@ void World::freeDevice() {
   hMoveEvents_ = nullptr;
   hBodyRead_ = nullptr;
   hostScalars_ = nullptr; hBegin_ = nullptr; hHit_ = nullptr; hJointEvents_ = nullptr;
-  for (auto& e : ev_) if (e) { cudaEventDestroy(e); e = nullptr; }
-  for (auto& g : graphs_) { if (g.exec) cudaGraphExecDestroy(g.exec); for (auto& e : g.ev) if (e) cudaEventDestroy(e); }
+  for (auto& g : graphs_) if (g.exec) cudaGraphExecDestroy(g.exec);
   graphs_.clear();
   for (auto& e : timer_) if (e) { cudaEventDestroy(e); e = nullptr; }
   if (stream_ && !batch_) cudaStreamDestroy(stream_);
@@ -1199,7 +1198,7 @@ int World::regrow(void** slot, size_t newCount, int fillByte) {
     cudaFree(old);
     for (void*& a : allocs_) if (a == old) a = p;
     *slot = p; r.count = newCount;
-    for (auto& g : graphs_) { if (g.exec) cudaGraphExecDestroy(g.exec); for (auto& e : g.ev) if (e) cudaEventDestroy(e); }
+    for (auto& g : graphs_) if (g.exec) cudaGraphExecDestroy(g.exec);
     graphs_.clear();                               // captured launches hold the old pointers
     return B2C_OK;
   }
@@ -1314,9 +1313,8 @@ int World::upload() {
   if (member) { stream_ = batchStream(batch_); if (!hostScalars_) hostScalars_ = (Scalars*)malloc(sizeof(Scalars)); }
   else {
     CK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
-    for (auto& e : ev_) CK(cudaEventCreate(&e));
     for (auto& e : timer_) CK(cudaEventCreate(&e));
-    CK(cudaHostAlloc((void**)&hostScalars_, sizeof(Scalars), cudaHostAllocDefault));
+    CK(cudaHostAlloc((void**)&hostScalars_, sizeof(Scalars), cudaHostAllocMapped));
   }
   memset(hostScalars_, 0, sizeof(Scalars));
   WorldDev& d = d_;
@@ -1470,6 +1468,8 @@ int World::upload() {
       for (int k = 0; k < 2; k++) CK(cudaHostGetDevicePointer((void**)&d.sensorEndEvents[k], hSensorEnd_[k], 0));
     } }
   DA(d.sc, Scalars, 1);
+  d.hostSc = nullptr;                              // the step's last warp keeps the pinned mirror current (a batch member is fetched on demand)
+  if (!member && cudaHostGetDevicePointer((void**)&d.hostSc, hostScalars_, 0) != cudaSuccess) { d.hostSc = nullptr; cudaGetLastError(); }
   int scanBlocks = std::max(std::max(std::max(contactCap, d.bigScratch), std::max(d.moveCapacity, capAwake)), capSensor_) / 64 + 2;   // chunk = block size of the scope, 64 at the narrowest (a batch world's finalize CTA)
   DA(d.scanBlockSums, int, scanBlocks); DA(d.scanBlockSums4, int4, scanBlocks);
   Scalars init; memset(&init, 0, sizeof(init));
@@ -2085,43 +2085,21 @@ int World::getJointEvents(const int** ids, int* count) {
   return B2C_OK;
 }
 
-int World::getProfile(B2CProfile* out) {       // averages over the steps since the previous call (events: at most kProfRing steps)
+int World::getProfile(B2CProfile* out) {       // averages over the steps since the previous call
+  // Every time is a difference of %globaltimer stamps taken by the step kernels themselves and summed on the device (Scalars::phaseAcc):
+  // no CUDA event is recorded in the stream of a step. Island solver = end of the front kernel to the start of the finalize kernel, whole
+  // step = start of the front kernel to the end of the finalize kernel (launch gaps between the kernels included, as an event pair would).
   memset(out, 0, sizeof(*out));
-  if (batch_) {                                // batch member: %globaltimer sums of this world's CTA (k_batch_step), no CUDA events
-    if (!onDevice_) return B2C_OK;
-    int rc = synchronize(); if (rc) return rc;
-    double ph[8]; const int n = stepCount_ - lastProfStep_ > 0 ? stepCount_ - lastProfStep_ : 1;
-    for (int k = 0; k < 8; k++) { ph[k] = (double)(hostScalars_->phaseAcc[k] - lastPhaseAcc_[k]) * 1e-6 / n; lastPhaseAcc_[k] = hostScalars_->phaseAcc[k]; }
-    lastProfStep_ = stepCount_;
-    out->pairs = (float)ph[0]; out->collide = (float)ph[1]; out->treeRebuild = (float)ph[4]; out->prepareConstraints = (float)ph[2];
-    out->solveConstraints = (float)(ph[3] + ph[5]); out->transforms = (float)ph[6]; out->refit = out->transforms;
-    out->solve = out->prepareConstraints + out->solveConstraints + out->transforms; out->step = (float)(ph[0] + ph[1] + ph[2] + ph[3] + ph[5] + ph[6]);
-    return B2C_OK;
-  }
-  if (!onDevice_ || profCount_ == 0) return B2C_OK;
+  if (!onDevice_) return B2C_OK;
   int rc = synchronize(); if (rc) return rc;
-  for (auto& g : graphs_) harvestGraph(g);
-  int n = profCount_ < kProfRing ? profCount_ : kProfRing;
-  double acc[4] = {0, 0, 0, 0};
-  if (graphMode_ == 1) {                 // steps were graph launches: event times were harvested per launch
-    n = profN_ > 0 ? profN_ : 1;
-    for (int j = 0; j < 4; j++) { acc[j] = profAcc_[j]; profAcc_[j] = 0; }
-    profN_ = 0;
-  } else for (int k = 0; k < n; k++) {
-    int slot = (profHead_ - 1 - k + 2 * kProfRing) % kProfRing;
-    cudaEvent_t* e = ev_ + slot * kProfEvents;
-    float ms;
-    for (int j = 0; j < 3; j++) { cudaEventElapsedTime(&ms, e[j], e[j + 1]); acc[j] += ms; }
-    cudaEventElapsedTime(&ms, e[0], e[3]); acc[3] += ms;
-  }
-  // sub-phases of the fused front kernel: %globaltimer sums kept on the device (ns), differenced against the previous call
-  double ph[5];
-  for (int k = 0; k < 5; k++) { ph[k] = (double)(hostScalars_->phaseAcc[k] - lastPhaseAcc_[k]) * 1e-6 / profCount_; lastPhaseAcc_[k] = hostScalars_->phaseAcc[k]; }
+  double ph[8]; const int n = stepCount_ - lastProfStep_ > 0 ? stepCount_ - lastProfStep_ : 1;
+  for (int k = 0; k < 8; k++) { ph[k] = (double)(hostScalars_->phaseAcc[k] - lastPhaseAcc_[k]) * 1e-6 / n; lastPhaseAcc_[k] = hostScalars_->phaseAcc[k]; }
+  lastProfStep_ = stepCount_;
   out->pairs = (float)ph[0]; out->collide = (float)ph[1]; out->treeRebuild = (float)ph[4]; out->prepareConstraints = (float)ph[2];
-  out->solveConstraints = (float)(ph[3] + acc[1] / n);          // grid-path solver + island solver kernel
-  out->transforms = (float)(acc[2] / n); out->refit = out->transforms;
-  out->solve = out->prepareConstraints + out->solveConstraints + out->transforms; out->step = (float)(acc[3] / n);
-  profCount_ = 0;
+  out->solveConstraints = (float)(ph[3] + ph[5]);          // grid-path solver + island solver kernel(s)
+  out->transforms = (float)ph[6]; out->refit = out->transforms;
+  out->solve = out->prepareConstraints + out->solveConstraints + out->transforms;
+  out->step = (float)(batch_ ? ph[0] + ph[1] + ph[2] + ph[3] + ph[5] + ph[6] : ph[7]);   // a batch world's CTA has no stamp 7 of its own meaning: its parts are summed
   return B2C_OK;
 }
 

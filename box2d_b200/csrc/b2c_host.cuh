@@ -208,18 +208,14 @@ class World {
   B2CContactTouchEvent *hBegin_ = nullptr, *hEnd_[2] = {nullptr, nullptr}; B2CContactHitEvent* hHit_ = nullptr; int* hJointEvents_ = nullptr;   // event arrays: mapped pinned host memory the kernels write into
   int hBeginN_ = 0, hEndN_ = 0, hHitN_ = 0, hJointN_ = 0;
   int lastEndIndex_ = 0;
-  static constexpr int kProfRing = 64, kProfEvents = 6;
-  cudaEvent_t ev_[kProfRing * kProfEvents] = {};
   cudaEvent_t timer_[2] = {};
-  int profHead_ = 0, profCount_ = 0, lastProfStep_ = 0;
+  int lastProfStep_ = 0;
   // One CUDA graph per distinct step configuration (parameters, end-event buffer parity, solver variant, streamed read-backs): a step is
   // then ONE launch, so the kernels run back to back whatever the host's launch latency is (matters with 8 ranks on one host).
-  struct StepGraph { std::vector<unsigned char> key; cudaGraphExec_t exec = nullptr; cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr}; bool pending = false; };
+  struct StepGraph { std::vector<unsigned char> key; cudaGraphExec_t exec = nullptr; };
   std::vector<StepGraph> graphs_;
   int graphMode_ = -1;          // -1 undecided (B2CUDA_GRAPH decides at the first step), 0 direct launches (default, or capture failed), 1 graphs
-  double profAcc_[4] = {0, 0, 0, 0}; int profN_ = 0;   // event times harvested from graph launches (ms)
-  int enqueueStep(const StepParams& sp, bool warpMode, bool clusterLaunch, int newEndIndex, cudaEvent_t* pe, bool external);
-  void harvestGraph(StepGraph& g);
+  int enqueueStep(const StepParams& sp, bool warpMode, bool clusterLaunch, int newEndIndex);
   unsigned long long lastPhaseAcc_[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   B2CProfile profile_{};
   bool profileValid_ = false;

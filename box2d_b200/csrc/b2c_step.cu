@@ -1040,8 +1040,16 @@ __device__ __forceinline__ void solveJointOnly(const WorldDev& d, const StepPara
 }
 // Joints of the overflow colour (src/Joint.cs:377-394): one thread, array order, before the overflow contacts of the stage
 // (src/Solver.cs:633,648,669). The relax pass keeps useBias (Q4) and no joint event can come from here: only SolveJointsTask tests the thresholds.
-__device__ __noinline__ void ovJointsWarmStart(const WorldDev& d, int k0, int k1) { for (int k = k0; k < k1; k++) warmStartJoint(d, d.joints[d.jointSorted[k]]); }
-__device__ __noinline__ void ovJointsSolve(const WorldDev& d, const StepParams& sp, int k0, int k1) { for (int k = k0; k < k1; k++) solveJointOnly(d, sp, d.joints[d.jointSorted[k]], true); }
+__device__ __noinline__ void ovWarmStartAll(const WorldDev& d) {
+  for (int k = d.jointColorStart[kOverflowIndex]; k < d.jointColorStart[kGraphColorCount]; k++) warmStartJoint(d, d.joints[d.jointSorted[k]]);
+  const int nc = d.sc->colLen[kOverflowIndex];
+  if (nc > 0) ovWarmStart(d, nc);
+}
+__device__ __noinline__ void ovSolveAll(const WorldDev& d, const StepParams& sp) {
+  for (int k = d.jointColorStart[kOverflowIndex]; k < d.jointColorStart[kGraphColorCount]; k++) solveJointOnly(d, sp, d.joints[d.jointSorted[k]], true);
+  const int nc = d.sc->colLen[kOverflowIndex];
+  if (nc > 0) ovSolve(d, sp, nc, true);
+}
 __device__ __forceinline__ void solveJoint(const WorldDev& d, const StepParams& sp, JointDev& j, bool useBias) {    // JointSim.Solve src/Joint.cs:132 + SolveJointsTask src/Solver.cs:180-198
   solveJointOnly(d, sp, j, useBias);
   if (useBias && (j.forceThreshold < FLT_MAX || j.torqueThreshold < FLT_MAX) && !d.jointEventFlag[j.jointId]) {   // src/Solver.cs:186-196
@@ -1125,9 +1133,8 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   const int tid = grid.tid(), stride = grid.size();
   const int awake = s.bigBodyCount;               // bodies of grid-path islands (+ kinematic bodies some constraint reads)
   if (awake == 0 && activeCount == 0) return;     // everything lives in small islands / free bodies: no grid barrier at all
-  const int nov = s.colLen[kOverflowIndex];                      // overflow colour: one thread, array order, before the colours of each stage (:633-670)
-  const int ovJ0 = d.jointColorStart[kOverflowIndex], ovJ1 = d.jointColorStart[kGraphColorCount];   // its joints come before its contacts
-  const bool anyOv = nov > 0 || ovJ1 > ovJ0;
+  // overflow colour: one thread, array order, before the colours of each stage (:633-670), its joints before its contacts
+  const int nov = s.colLen[kOverflowIndex] + d.jointColorStart[kGraphColorCount] - d.jointColorStart[kOverflowIndex];
   Lane c; float4 I = make_float4(0, 0, 0, 0), J = I; int myA = -1, myContact = -1;
   const BodyRows bs{d.st0, d.st1};
   if (CACHED) {
@@ -1141,14 +1148,14 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   for (int sub = 0; sub < sp.subStepCount; sub++) {
     for (int i = tid; i < awake; i += stride) integrateVelocity(d, sp, d.bigBodies[i]);
     grid.sync();
-    if (anyOv) { if (tid == 0) { if (ovJ1 > ovJ0) ovJointsWarmStart(d, ovJ0, ovJ1); if (nov > 0) ovWarmStart(d, nov); } grid.sync(); }
+    if (nov > 0) { if (tid == 0) ovWarmStartAll(d); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) warmStartJoint(d, d.joints[d.jointSorted[k]]);
       if (CACHED) { if (myA == a) warmStartLane(bs, c, c.indexA, c.indexB, I, J.z); }
       else for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) warmStartContact(d, t);
       grid.sync();
     }
-    if (anyOv) { if (tid == 0) { if (ovJ1 > ovJ0) ovJointsSolve(d, sp, ovJ0, ovJ1); if (nov > 0) ovSolve(d, sp, nov, true); } grid.sync(); }
+    if (nov > 0) { if (tid == 0) ovSolveAll(d, sp); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], true);
       if (CACHED) { if (myA == a) solveLane<true>(bs, sp, c, c.indexA, c.indexB, I, J); }
@@ -1157,7 +1164,7 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
     }
     for (int i = tid; i < awake; i += stride) integratePosition(d, sp, d.bigBodies[i]);
     grid.sync();
-    if (anyOv) { if (tid == 0) { if (ovJ1 > ovJ0) ovJointsSolve(d, sp, ovJ0, ovJ1); if (nov > 0) ovSolve(d, sp, nov, true); } grid.sync(); }      // Q4: the relax pass of the overflow colour keeps useBias
+    if (nov > 0) { if (tid == 0) ovSolveAll(d, sp); grid.sync(); }      // Q4: the relax pass of the overflow colour keeps useBias
     for (int a = 0; a < activeCount; a++) {
       for (int k = sJBegin[a] + tid; k < sJEnd[a]; k += stride) solveJoint(d, sp, d.joints[d.jointSorted[k]], false);
       if (CACHED) { if (myA == a) solveLane<false>(bs, sp, c, c.indexA, c.indexB, I, J); }
@@ -1168,7 +1175,7 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   // restitution: skipped entirely (like every AllZeroW group) when no touching contact has restitution (flag set by p_collide)
   if (s.anyRestitution) {
     if (CACHED) { if (myContact >= 0) writeLane(d, tid, c, I, J); grid.sync(); }      // restitution works on 8-lane groups of the planes
-    if (nov > 0) { if (tid == 0) ovRestitution(d, sp, nov); grid.sync(); }
+    if (nov > 0) { if (tid == 0) ovRestitution(d, sp, s.colLen[kOverflowIndex]); grid.sync(); }
     for (int a = 0; a < activeCount; a++) {
       for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) restitutionContact(d, sp, t);
       grid.sync();
@@ -1177,7 +1184,7 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
   if (CACHED && !s.anyRestitution) { if (myContact >= 0) storeImpulsesRegs(d, myContact, I, J, c.relVel1, c.relVel2); }
   else for (int a = 0; a < activeCount; a++)
     for (int t = sBegin[a] + tid; t < sEnd[a]; t += stride) storeImpulses(d, t);
-  for (int k = tid; k < nov; k += stride) ovStoreImpulses(d, k);
+  if (nov > 0) { const int nc = s.colLen[kOverflowIndex]; for (int k = tid; k < nc; k += stride) ovStoreImpulses(d, k); }
 }
 
 }  // namespace b2c
@@ -1194,6 +1201,7 @@ namespace b2c {
 // fraction wins. Returns that fraction (1 = no hit). Sensor shapes collect the visitors whose sweep reaches them before the hit (Sensor.hits).
 // A query ends at the fast shape's own proxy (the callback returns false, :230): in the dynamic tree a bullet sees only what comes before itself.
 constexpr int kContinuousSensorHits = 8;
+constexpr int kBulletStageBit = 1 << 30;            // in Scalars::enlargedShapeCount: this step has fast bullets (StepContext.bulletBodyCount > 0, src/Solver.cs:447-449,1238)
 __device__ __noinline__ float solveContinuous(const WorldDev& d, int bodyId, Xf xf2, const Sweep& sweep, uint32_t* simFlags, bool isBullet) {
   Scalars& sc = *d.sc;
   float fraction = 1.0f;
@@ -1345,7 +1353,7 @@ __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int
     if (isFast) {
       if (simFlags & kIsBullet) {
         // a fast bullet waits for the bullet stage (:447-449): pose0 and the shape boxes stay, every shape is buffered as a move by the refit (:1210-1218)
-        atomicAdd(&d.sc->bulletCount, 1);
+        atomicOr(&d.sc->enlargedShapeCount, kBulletStageBit);   // read back with the enlarged-shape count: one load decides both stages
         for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) enlarged++;
       } else {
         // SolveContinuous :315-401 (non-bullet body: static tree only)
@@ -1436,7 +1444,7 @@ __device__ void p_refit(const WorldDev& d, int tid, int stride) {
 
 // BulletBodyTask (src/Solver.cs:728-738): SolveContinuous for this step's fast bullets, after the refit (the dynamic tree holds the enlarged
 // boxes of everything else; every other awake body is at its end pose with center0 == center, so the bullets are independent of each other).
-__device__ void p_bullets(const WorldDev& d, int tid, int stride) {
+__device__ __noinline__ void p_bullets(const WorldDev& d, int tid, int stride) {
   const int n = d.awakeCount;
   for (int i = tid; i < n; i += stride) {
     uint32_t simFlags = d.simFlags[i];
@@ -1453,7 +1461,7 @@ __device__ void p_bullets(const WorldDev& d, int tid, int stride) {
   }
 }
 // :1247-1269 the bullets' enlarged proxies grow in the dynamic tree (no BufferMove: the refit put every bullet shape in the move set)
-__device__ void p_bullet_enlarge(const WorldDev& d, int tid, int stride) {
+__device__ __noinline__ void p_bullet_enlarge(const WorldDev& d, int tid, int stride) {
   const int n = d.awakeCount;
   for (int i = tid; i < n; i += stride) {
     uint32_t simFlags = d.simFlags[i];
@@ -1736,6 +1744,8 @@ __global__ void __launch_bounds__(kCoopThreads) k_solver_cluster(const __grid_co
 template <class S> __device__ void finalizePhase(const S& grid, const WorldDev& d, const StepParams& sp, int newEndIndex) {   // FinalizeBodies + refit
   const int tid = grid.tid(), stride = grid.size();
   Scalars& s = *d.sc;
+  unsigned long long t0 = 0;
+  if (tid == 0) t0 = globalTimer();
   if (d.debugChecksums == 1) { dbgBodies(d, 8); dbgContacts(d, 9); grid.sync(); }
   p_finalize(d, sp, tid, stride);
   if (s.anyHitShapes) {                           // hit events, ordered by (colour, position in the colour's array)
@@ -1747,11 +1757,12 @@ template <class S> __device__ void finalizePhase(const S& grid, const WorldDev& 
     p_hit_events<true>(d, sp, tid, stride, hitFlags, hitSums);
   }
   grid.sync();
-  if (s.enlargedShapeCount > 0) {
+  const int enlargedShapes = s.enlargedShapeCount;
+  if (enlargedShapes > 0) {
     gridScan<int>(grid, d.bodyEnlargedCount, d.scanBlockSums, d.awakeCount, &s.moveCount);
     p_refit(d, tid, stride);
     grid.sync();
-    if (s.bulletCount > 0) {                        // bullet stage :1238-1272 (uniform: counted by p_finalize before the barriers above; a fast
+    if (enlargedShapes & kBulletStageBit) {         // bullet stage :1238-1272 (uniform: flagged by p_finalize before the barriers above; a fast
       p_bullets(d, tid, stride);                    // bullet counts its shapes as enlarged, so the test lives in this branch and a step
       grid.sync();                                  // without moves pays nothing for it)
       p_bullet_enlarge(d, tid, stride);
@@ -1759,7 +1770,18 @@ template <class S> __device__ void finalizePhase(const S& grid, const WorldDev& 
     }
   } else if (tid == 0) s.moveCount = 0;
   phase_sensors(grid, d, sp.endIndex);              // World.OverlapSensors, api/World.cs:97-102 (before the end-event buffers trade places)
-  if (tid == 0) { s.enlargedShapeCount = 0; s.bulletCount = 0; p_step_finish(d, newEndIndex); }
+  if (tid < 32) {                                   // the first warp of the scope
+    if (tid == 0) {
+      s.enlargedShapeCount = 0; p_step_finish(d, newEndIndex);
+      const unsigned long long now = globalTimer();   // kernel-level times without CUDA events in the stream (each record costs ~2.5 us of device time)
+      s.phaseAcc[5] += t0 - s.phaseStamp[4]; s.phaseAcc[6] += now - t0; s.phaseAcc[7] += now - s.phaseStamp[0];
+    }
+    if (d.hostSc) {                                 // the step's scalars go to the host's pinned mirror from here: no copy node behind the kernel
+      __syncwarp();
+      const int4* src = reinterpret_cast<const int4*>(&s); int4* dst = reinterpret_cast<int4*>(d.hostSc);
+      for (int k = tid; k < (int)(sizeof(Scalars) / sizeof(int4)); k += 32) dst[k] = __ldcg(src + k);
+    }
+  }
 }
 __global__ void __launch_bounds__(kCoopThreads) k_finalize_phase(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp, int newEndIndex) {
   cg::grid_group g = cg::this_grid();
@@ -1805,10 +1827,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_batch_step(const WorldDev* __
     __syncthreads();
   }
   if (MODE != 1) {
-    unsigned long long t6 = 0;
-    if (threadIdx.x == 0) t6 = globalTimer();
-    finalizePhase(cta, d, sp, newEndIndex);
-    if (threadIdx.x == 0) { Scalars& s = *d.sc; s.phaseAcc[5] += t6 - s.phaseStamp[4]; s.phaseAcc[6] += globalTimer() - t6; }
+    finalizePhase(cta, d, sp, newEndIndex);       // (stamps the island-solver and finalize times itself)
   }
 }
 
@@ -1835,14 +1854,11 @@ static int gridFor(int n, int threads, int maxBlocks) {
 }
 
 // The launches of one step on the world's stream; captured into a CUDA graph (external = event-record nodes) or issued directly.
-int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch, int newEndIndex, cudaEvent_t* pe, bool external) {
+int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch, int newEndIndex) {
   WorldDev& d = d_;
   StepParams sp = spIn;
   const dim3 cgrid(coopBlocks_), cblock(kCoopThreads);
-  auto rec = [&](cudaEvent_t e) { return external ? cudaEventRecordWithFlags(e, stream_, cudaEventRecordExternal) : cudaEventRecord(e, stream_); };
-  CK(rec(pe[0]));
   { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
-  CK(rec(pe[1]));
   if (clusterLaunch) {
     cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(clusterCtas_); cfg.blockDim = dim3(kCoopThreads); cfg.stream = stream_;
     cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = clusterCtas_; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
@@ -1851,23 +1867,12 @@ int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch
   }
   if (warpMode) k_solver_islands_warp<<<coopBlocks_, 32 * kWarpIslandsPerCta, kWarpIslandsPerCta * sizeof(WarpIslandSlice), stream_>>>(d, sp);
   k_solver_islands<<<coopBlocks_ * 8, kIslandThreads, 0, stream_>>>(d, sp, (int)warpMode);
-  CK(rec(pe[2]));
   { void* args[] = {(void*)&d, (void*)&sp, (void*)&newEndIndex}; CK(cudaLaunchCooperativeKernel((void*)k_finalize_phase, cgrid, cblock, args, 0, stream_)); }
-  CK(rec(pe[3]));
-  CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
+  if (!d.hostSc) CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));   // (mapped mirror unavailable)
   if (streamMoves_ && !hMoveEventsDev_) CK(cudaMemcpyAsync(hMoveEvents_, dMoveEvents_, sizeof(B2CBodyMoveEvent) * (size_t)d.awakeCount, cudaMemcpyDeviceToHost, stream_));
   if (streamBodies_) CK(cudaMemcpyAsync(hBodyRead_, dBodyRead_, sizeof(B2CBodyRead) * (size_t)d.bodyCapacity, cudaMemcpyDeviceToHost, stream_));   // the caller reads body records every step: the copy rides behind the step
   return B2C_OK;
 }
-void World::harvestGraph(StepGraph& g) {          // event times of the graph's previous launch, if it has finished
-  if (!g.pending || cudaEventQuery(g.ev[3]) != cudaSuccess) { cudaGetLastError(); return; }
-  float ms;
-  for (int j = 0; j < 3; j++) if (cudaEventElapsedTime(&ms, g.ev[j], g.ev[j + 1]) == cudaSuccess) profAcc_[j] += ms;
-  if (cudaEventElapsedTime(&ms, g.ev[0], g.ev[3]) == cudaSuccess) profAcc_[3] += ms;
-  profN_++; g.pending = false;
-  cudaGetLastError();
-}
-
 int World::step(float timeStep, int subStepCount) {
   if (batch_) return fail(B2C_E_INVALID, "this world belongs to a batch: step it with b2cuda_batch_step");
   if (enableSleep) return fail(B2C_E_UNSUPPORTED, "enableSleep=true (islands/sleep, src/Island.cs) is not supported in this build; create the world with enableSleep=0");
@@ -1943,18 +1948,15 @@ int World::step(float timeStep, int subStepCount) {
     for (auto& c : graphs_) if (c.key == key) { g = &c; break; }
     if (!g) {
       if (graphs_.size() >= 8) {                    // parameters keep changing: drop the oldest
-        StepGraph& o = graphs_.front(); harvestGraph(o);
+        StepGraph& o = graphs_.front();
         if (o.exec) cudaGraphExecDestroy(o.exec);
-        for (auto& e : o.ev) if (e) cudaEventDestroy(e);
         graphs_.erase(graphs_.begin());
       }
       StepGraph ng; ng.key = key;
-      bool ok = true;
-      for (auto& e : ng.ev) ok = ok && cudaEventCreate(&e) == cudaSuccess;
       cudaGraph_t graph = nullptr;
-      ok = ok && cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+      bool ok = cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
       if (ok) {
-        int rc = enqueueStep(sp, warpMode, clusterLaunch, endIndex_, ng.ev, true);
+        int rc = enqueueStep(sp, warpMode, clusterLaunch, endIndex_);
         ok = cudaStreamEndCapture(stream_, &graph) == cudaSuccess && rc == B2C_OK && graph != nullptr;
       }
       ok = ok && cudaGraphInstantiate(&ng.exec, graph, 0) == cudaSuccess;
@@ -1962,22 +1964,17 @@ int World::step(float timeStep, int subStepCount) {
       if (ok) { graphs_.push_back(std::move(ng)); g = &graphs_.back(); }
       else {                                          // this driver cannot capture the sequence: direct launches from now on
         cudaGetLastError();
-        for (auto& e : ng.ev) if (e) cudaEventDestroy(e);
         if (ng.exec) cudaGraphExecDestroy(ng.exec);
         graphMode_ = 0;
       }
     }
     if (g) {
-      harvestGraph(*g);
       CK(cudaGraphLaunch(g->exec, stream_));
-      g->pending = true; profCount_++;
       launched = true;
     }
   }
   if (!launched) {
-    cudaEvent_t* pe = ev_ + (profHead_ % kProfRing) * kProfEvents;
-    int rc = enqueueStep(sp, warpMode, clusterLaunch, endIndex_, pe, false); if (rc) return rc;
-    profHead_ = (profHead_ + 1) % kProfRing; profCount_++;
+    int rc = enqueueStep(sp, warpMode, clusterLaunch, endIndex_); if (rc) return rc;
   }
   if (streamMoves_) movesFetched_ = true;
   if (streamBodies_) bodiesFetched_ = true;

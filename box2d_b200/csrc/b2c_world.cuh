@@ -101,7 +101,7 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int errorFlags, toiCandidates, jointEventCount, stepCount;
   int touchingCount, liveContactCount, rebuildLeafCount[3], colorRounds;
   int awakeCount, anyRestitution, anyContactFlag, anyHitShapes;
-  unsigned long long phaseStamp[8], phaseAcc[8];   // %globaltimer stamps inside k_step_front and their per-phase sums (ns)
+  unsigned long long phaseStamp[8], phaseAcc[8];   // %globaltimer stamps inside the step kernels and their per-phase sums (ns): 0 pairs, 1 collide, 2 prepare, 3 grid solver, 4 tree rebuild, 5 island solver kernels, 6 finalize, 7 whole step
   int islandCount, freeBodyCount, bigBodyCount, smallConStart;   // island partition of the awake set (b2c_islands.cuh)
   unsigned int contactStamp;   // contacts created so far (see cStamp)
   int clusterSolve;    // this step's grid-path constraints are solved by k_solver_cluster (one thread-block cluster) instead of the front kernel
@@ -110,9 +110,10 @@ struct Scalars {       // device scalars, mirrored to pinned host memory at the 
   int rebuildLevels[3];
   int colLen[kGraphColorCount];         // GraphColor.contactSims.Count per colour (src/ConstraintGraph.cs:10-24); [kOverflowIndex] = contacts in the overflow colour
   int sensorParity, sensorBeginCount, sensorEndCount[2];   // src/Sensor.cs: which overlap buffer is overlaps2; sensor event counts (end events double-buffered like contact end events)
-  int bulletCount;                      // fast bullets of this step (StepContext.bulletBodyCount, src/Solver.cs:447-449)
   unsigned long long dbg[16];           // order-independent state checksums per phase (B2CUDA_DEBUG_CHECKSUMS=1; b2cuda_world_debug_checksums)
 };
+
+static_assert(sizeof(Scalars) % 16 == 0, "Scalars is copied to the host mirror in 16-byte words");
 
 struct StepParams {    // src/Solver.cs:57-112 StepContext (scalars only)
   float dt, inv_dt, h, inv_h;
@@ -246,6 +247,7 @@ struct WorldDev {
   // --- finalize / refit scratch ---
   int* bodyEnlargedCount;   // per awake sim: enlarged shapes, then exclusive offsets
   Scalars* sc;
+  Scalars* hostSc;     // the host's pinned mirror of *sc, mapped: FinalizeBodies' last warp stores the step's scalars there (nullptr: batch member)
   // generic scan scratch
   int* scanBlockSums; int4* scanBlockSums4;
 };
