@@ -221,8 +221,7 @@ def b200_arm(args, rank, world_size, local_rank):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     w = api.World(api.CudaBackend(device=local_rank), scenes.world_def())
-    if world_size > 1:          # several ranks share one host: one graph launch per step keeps the kernels back to back under launch jitter
-        w.EnableGraphLaunch(True)
+    w.EnableGraphLaunch(True)   # b2cuda_world_enable_graph_launch: the step's three kernels replayed as one graph launch (back to back, free of host launch jitter)
     build_scene(w, args.workload, args.worlds, rank, world_size)
     flush = torch.empty(96 * 1024 * 1024, dtype=torch.float32, device="cuda")   # 384 MB > 126 MB L2
     K, W = args.steps, max(args.warmup, 3)
@@ -284,8 +283,7 @@ def b200_arm(args, rank, world_size, local_rank):
     warm_ms = median(warm_runs)
     barrier()
     # ---- timed region 3: end to end through the C-ABI with host buffers: step + bulk body read-back + contact events ----
-    if world_size > 1:
-        w.EnableGraphLaunch(False)             # a caller that reads results after every step is latency-bound: direct launches start ~7 us sooner
+    w.EnableGraphLaunch(False)                 # a caller that reads results after every step is latency-bound: direct launches start sooner than a graph launch
     for _ in range(max(3, min(W, 8))):         # untimed warm-up of the read-back path itself (first call packs all bodies, loads the kernel)
         w.Step(DT, SUBSTEPS)
         w.GetBodyMoveEvents(copy=False)
@@ -333,7 +331,8 @@ def b200_arm(args, rank, world_size, local_rank):
             "steps": K, "warmup": W, "ms_per_step": step_ms_max / K, "higher_is_better": True, "scaling": "strong" if args.workload == "batched_pyramids" else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(args.workload, bodies),
             "detail": {"bodies_per_gpu": bodies, "touching_contacts_per_gpu": touching, "parallelism": f"replicas x{world_size} (no data-path collective)",
-                       "launch": "cuda graph per step for value, direct launches for e2e" if world_size > 1 else "direct launches",
+                       "launch": "one cuda graph launch per step for value (b2cuda_world_enable_graph_launch), direct launches for e2e",
+                       "timer": "CUDA event pair on the world's stream around each step; b2cuda_world_timer_start holds the stream 60 us before its event so the step's launches are queued when the region opens (device time, not host enqueue latency)",
                        "repeats": repeats, "timed_step_ms_total": total_ms, "protocol": f"the {K}-step region repeated {repeats}x (>= {MIN_TIMED_S} s of step time or {MAX_REPEATS} regions); value, ms_per_step and phase_ms are the median region"},
             "value_l2_resident": total_units / (warm_ms_max * 1e-3), "ms_per_step_l2_resident": warm_ms_max / K,
             "phase_ms": dict(zip(("pairs", "collide", "color_sort_prepare", "solver_kernel", "finalize_refit", "tree_rebuild_in_collide"), [x / K for x in phases])),

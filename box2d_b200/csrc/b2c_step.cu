@@ -1320,6 +1320,26 @@ __device__ __forceinline__ int continuousOutcome(const WorldDev& d, int i, int b
   return enlarged;
 }
 
+// The fast branch of FinalizeBodies (:444-455), out of line so that the common path keeps its registers: a bullet only registers for the
+// bullet stage, any other fast body runs SolveContinuous against the static tree here. Returns the shapes to count for the refit.
+// Everything goes in and comes back by value: a pointer to a local of p_finalize would pin that local to the stack for the whole common path.
+struct FastBodyOut { int enlarged; uint32_t simFlags; Xf xf; V2 center; Rot q; };
+__device__ __noinline__ FastBodyOut finalizeFastBody(const WorldDev& d, int i, int bodyId, V2 localCenter, uint32_t simFlags, Xf xf, V2 center, Rot q) {
+  int enlarged = 0;
+  if (simFlags & kIsBullet) {
+    // a fast bullet waits for the bullet stage (:447-449): pose0 and the shape boxes stay, every shape is buffered as a move by the refit (:1210-1218)
+    atomicOr(&d.sc->enlargedShapeCount, kBulletStageBit);   // read back with the enlarged-shape count: one load decides both stages
+    for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) enlarged++;
+    return FastBodyOut{enlarged, simFlags, xf, center, q};
+  }
+  // SolveContinuous :315-401 (non-bullet body: static tree only)
+  float4 pose0 = d.simPose0[i];
+  Sweep sweep; sweep.localCenter = localCenter; sweep.c1 = mk(pose0.x, pose0.y); sweep.c2 = center; sweep.q1 = mkRot(pose0.z, pose0.w); sweep.q2 = q;   // BodySim.MakeSweep src/Body.cs:172
+  const float fraction = solveContinuous(d, bodyId, xf, sweep, &simFlags, false);
+  enlarged = continuousOutcome(d, i, bodyId, sweep, fraction, simFlags, xf, center, q);
+  return FastBodyOut{enlarged, simFlags, xf, center, q};
+}
+
 __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.awakeCount;
   for (int i = tid; i < n; i += stride) {
@@ -1351,17 +1371,8 @@ __device__ void p_finalize(const WorldDev& d, const StepParams& sp, int tid, int
     else d.simPose0[i] = make_float4(center.x, center.y, q.c, q.s);
     int enlarged = 0;
     if (isFast) {
-      if (simFlags & kIsBullet) {
-        // a fast bullet waits for the bullet stage (:447-449): pose0 and the shape boxes stay, every shape is buffered as a move by the refit (:1210-1218)
-        atomicOr(&d.sc->enlargedShapeCount, kBulletStageBit);   // read back with the enlarged-shape count: one load decides both stages
-        for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) enlarged++;
-      } else {
-        // SolveContinuous :315-401 (non-bullet body: static tree only)
-        float4 pose0 = d.simPose0[i];
-        Sweep sweep; sweep.localCenter = localCenter; sweep.c1 = mk(pose0.x, pose0.y); sweep.c2 = center; sweep.q1 = mkRot(pose0.z, pose0.w); sweep.q2 = q;   // BodySim.MakeSweep src/Body.cs:172
-        const float fraction = solveContinuous(d, bodyId, xf, sweep, &simFlags, false);
-        enlarged = continuousOutcome(d, i, bodyId, sweep, fraction, simFlags, xf, center, q);
-      }
+      const FastBodyOut o = finalizeFastBody(d, i, bodyId, localCenter, simFlags, xf, center, q);   // rare: kept out of line
+      enlarged = o.enlarged; simFlags = o.simFlags; xf = o.xf; center = o.center; q = o.q;
     } else {
       for (int sid = d.bodyHeadShape[bodyId]; sid != -1; sid = d.shapes[sid].nextShapeId) {
         Box aabb = boxGrow(geomAABB(d.shapes[sid].geom, xf), kSpeculativeDistance);
@@ -1887,6 +1898,11 @@ int World::step(float timeStep, int subStepCount) {
     k_zero_step<<<1, 1, 0, stream_>>>(d, endIndex_);
     CK(cudaMemcpyAsync(hostScalars_, d.sc, sizeof(Scalars), cudaMemcpyDeviceToHost, stream_));
     return B2C_OK;
+  }
+  { // contact rows three quarters full at the last step that reached the host: grow them before they overflow (src: List<T> growth)
+    const Scalars& hs = *hostScalars_;
+    const int used = std::max(std::max(hs.contactNext, hs.newPairCount), std::max(std::max(hs.beginCount, hs.hitCount), std::max(hs.endCount[0], hs.endCount[1])));
+    if (4LL * used > 3LL * d.contactCapacity) { int rc = growContacts(2 * d.contactCapacity); if (rc) return rc; }
   }
   StepParams sp;
   memset(&sp, 0, sizeof(sp));

@@ -396,11 +396,14 @@ int32_t b2cuda_batch_stats(B2CBatch* batch, B2CBatchStats* out, double* deviceDs
 int32_t b2cuda_batch_timer_start(B2CBatch* batch);
 int32_t b2cuda_batch_timer_stop(B2CBatch* batch, float* elapsedMs);
 /* (new, no reference counterpart) one CUDA-graph launch per step instead of one launch per kernel. The kernels then run back to back whatever
- * the host's launch latency is - use it when several processes drive GPUs from one host (bench.py does for world_size > 1) or when
- * steps are enqueued without reading results in between. Costs ~7 us of start latency per step, hence off by default (B2CUDA_GRAPH=1 also enables). */
+ * the host's launch latency is (many_pyramids: 0.068 against 0.074 ms per step) - use it when steps are enqueued without reading results in
+ * between, or when several processes drive GPUs from one host. The first kernel starts later than with direct launches, so a caller that
+ * synchronises after every step is better off without: off by default (B2CUDA_GRAPH=1 also enables). */
 int32_t b2cuda_world_enable_graph_launch(B2CWorld* world, int32_t flag);
 /* (new, no reference counterpart) device-time stopwatch on the world's own stream: CUDA events around whatever was
- * enqueued between the two calls; stop synchronises. Used by bench.py so timing does not depend on torch's stream. */
+ * enqueued between the two calls; stop synchronises. Used by bench.py so timing does not depend on torch's stream. start first
+ * holds the stream for 60 us (a spinning one-thread kernel) and records its event behind that, so the launches the caller enqueues
+ * next are already queued when the region opens: the region is device time and does not contain the host's enqueue latency. */
 int32_t b2cuda_world_timer_start(B2CWorld* world);
 int32_t b2cuda_world_timer_stop(B2CWorld* world, float* elapsedMs);
 

@@ -1405,3 +1405,27 @@ def test_overflow_joints_bit_exact():
 
     res = parity.run_pair(build, steps=60, mutate=mutate, verbose=True)
     assert res["max_rel_err"] == 0.0 and res["max_overflow"] >= 11, res
+
+
+def test_contact_rows_grow_between_steps():
+    """The reference's contact array, colour arrays, pair set and event lists grow without bound. Here the contact-sized device rows grow
+    (a) when shapes created between steps outgrow the first upload's reserve and (b) when a step leaves them three quarters full; ids, colour
+    array order, pending end events and every later step stay bit-exact."""
+    holder = {}
+
+    def build(w):
+        holder[w.backend.name] = scenes.add_pyramid(w, 3)
+
+    def mutate(w, step):
+        if step == 3:
+            scenes.add_pyramid(w, 30, origin=(60.0, 0.0))          # 465 bodies: 12 per shape passes the 4096 rows of the first upload
+        if step == 6:
+            w.DestroyBody(holder[w.backend.name][1][0])            # end events pending while ...
+            scenes.add_pyramid(w, 24, origin=(-60.0, 0.0))         # ... the rows grow again
+    res = parity.run_pair(build, steps=14, mutate=mutate, verbose=True)
+    assert res["max_rel_err"] == 0.0 and res["contacts"] > 1500, res
+
+    # (b): a fixed small reserve, contacts pile up gradually
+    wd = scenes.world_def(contactCapacity=160)
+    res = parity.run_pair(lambda w: scenes.mixed_drop(w, n=90, seed=5), steps=120, world_def=wd, full_every=10)
+    assert res["max_rel_err"] == 0.0 and res["contacts"] > 160, res
