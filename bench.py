@@ -204,7 +204,7 @@ def batched_record(args, rank, world_size, local_rank, dist, barrier):
     return {"workload": f"{args.worlds} independent 10-row pyramids (b2cuda_batch_*), world range split over {world_size} GPU(s)", "worlds": args.worlds,
             "worlds_per_gpu": n, "scaling": "strong", "steps": K, "warmup": W, "repeats": len(reps), "ms_per_step": ms_max / K,
             "world_steps_per_s": args.worlds * K / (ms_max * 1e-3), "body_substeps_per_s": v[0] * SUBSTEPS * K / (ms_max * 1e-3),
-            "e2e_world_steps_per_s": args.worlds * K / (e2e_max * 1e-3), "e2e_d2h_bytes_per_step": 64, "gpu_launches_per_step": 1,
+            "e2e_world_steps_per_s": args.worlds * K / (e2e_max * 1e-3), "e2e_d2h_bytes_per_step": 64, "gpu_launches_per_step": 3, "gpu_launches_note": "front, warp-per-world island solver, finalize: three kernels replayed as ONE cuda graph launch per step",
             "l2": "per-GPU working set (every world's own trees, contacts and solver arrays) exceeds the 126 MB L2 many times over",
             "dram_traffic_bytes_per_launch": (measured_traffic("batched_8192")[0] if (args.worlds == 8192 and world_size == 1) else None),
             "stats": {"awake_bodies": int(v[0]), "sum_v2": v[1], "touching_contacts": int(v[2]), "max_speed": v[5], "min_y": v[6]}}
