@@ -23,6 +23,26 @@ class B2Error(RuntimeError):
     pass
 
 
+_DTYPES = {}
+
+
+def _dt(ty):
+    """numpy dtype of a ctypes Structure, converted once (np.dtype(struct) costs ~25 us a call)."""
+    d = _DTYPES.get(ty)
+    if d is None:
+        d = _DTYPES[ty] = np.dtype(ty)
+    return d
+
+
+def _records(ptr, n, ty, copy):
+    """`n` records of ctypes type `ty` at `ptr` as a numpy structured array: a view of the library's buffer, or a copy."""
+    d = _dt(ty)
+    if n <= 0:
+        return np.zeros(0, dtype=d)
+    arr = np.frombuffer((C.c_uint8 * (n * d.itemsize)).from_address(C.cast(ptr, C.c_void_p).value), dtype=d)
+    return arr.copy() if copy else arr
+
+
 def default_world_def():
     """include/Types.cs:75-144"""
     d = WorldDef()
@@ -455,12 +475,7 @@ class World:
         nb, ne, nh = C.c_int32(), C.c_int32(), C.c_int32()
         self._check(self.fns["world_get_contact_events"](self.handle, C.byref(b), C.byref(nb), C.byref(e), C.byref(ne), C.byref(h), C.byref(nh)))
 
-        def grab(ptr, n, ty):
-            if n == 0:
-                return np.zeros(0, dtype=np.dtype(ty))
-            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ty * n)).contents).copy() if False else \
-                np.frombuffer(C.string_at(ptr, n * C.sizeof(ty)), dtype=np.dtype(ty)).copy()
-        return grab(b, nb.value, ContactTouchEvent), grab(e, ne.value, ContactTouchEvent), grab(h, nh.value, ContactHitEvent)
+        return _records(b, nb.value, ContactTouchEvent, True), _records(e, ne.value, ContactTouchEvent, True), _records(h, nh.value, ContactHitEvent, True)
 
     def GetSensorEvents(self):
         """WorldAPI.GetSensorEvents api/World.cs:289-299 -> (begin, end) numpy structured arrays of (sensor, visitor) shape references."""
@@ -469,9 +484,7 @@ class World:
         self._check(self.fns["world_get_sensor_events"](self.handle, C.byref(b), C.byref(nb), C.byref(e), C.byref(ne)))
 
         def grab(ptr, n):
-            if n == 0:
-                return np.zeros(0, dtype=np.dtype(capi.SensorEvent))
-            return np.frombuffer(C.string_at(ptr, n * C.sizeof(capi.SensorEvent)), dtype=np.dtype(capi.SensorEvent)).copy()
+            return _records(ptr, n, capi.SensorEvent, True)
         return grab(b, nb.value), grab(e, ne.value)
 
     def EnableSensorEvents(self, shape_id, flag):       # ShapeAPI.EnableSensorEvents api/Shape.cs:170
@@ -494,24 +507,20 @@ class World:
             buf = (ty * cap)()
             self._check(self.fns[name](self.handle, buf, cap, C.byref(n)))
             if n.value <= cap:
-                return np.frombuffer(buf, dtype=np.dtype(ty), count=n.value).copy()
+                return np.frombuffer(buf, dtype=_dt(ty), count=n.value).copy()
             cap = n.value
 
     def GetBodyEvents(self, copy=True):
         """WorldAPI.GetBodyEvents: one record per body id. copy=False returns a view of the library's pinned buffer (valid until the next Step)."""
         p, n = C.POINTER(BodyRead)(), C.c_int32()
         self._check(self.fns["world_get_body_events"](self.handle, C.byref(p), C.byref(n)))
-        arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value * C.sizeof(BodyRead),)).view(np.dtype(BodyRead))
-        return arr.copy() if copy else arr
+        return _records(p, n.value, BodyRead, copy)
 
     def GetBodyMoveEvents(self, copy=True):
         """WorldAPI.GetBodyEvents as the reference fills it: one (transform, bodyId, fellAsleep) per awake body, awake-set order."""
         p, n = C.POINTER(capi.BodyMoveEvent)(), C.c_int32()
         self._check(self.fns["world_get_body_move_events"](self.handle, C.byref(p), C.byref(n)))
-        if n.value == 0:
-            return np.zeros(0, dtype=np.dtype(capi.BodyMoveEvent))
-        arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value * C.sizeof(capi.BodyMoveEvent),)).view(np.dtype(capi.BodyMoveEvent))
-        return arr.copy() if copy else arr
+        return _records(p, n.value, capi.BodyMoveEvent, copy)
 
     def CopyBodyMoveEventsNoAlloc(self, out):
         """b2cuda_world_copy_body_move_events_noalloc: the move events into the caller's array `out` (numpy, dtype BodyMoveEvent) through
