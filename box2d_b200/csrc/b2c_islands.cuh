@@ -142,13 +142,17 @@ template <class S> __device__ void phase_islands(const S& grid, const WorldDev& 
     d.rootScan[i] = in;
   }
   grid.sync();
+  // grid-path bodies take their place in the body list in sim order (the 4th scan lane): neighbours in creation order stay neighbours,
+  // which is what lets the cluster solver keep most of a constraint's rows in its own CTA (b2c_cluster_dsm.cuh)
+  for (int i = tid; i < awake; i += stride) if (d.rootInfo[d.ufParent[i]] == -2) d.rootScan[i].w = 1;
+  grid.sync();
   gridScan4(grid, d.rootScan, d.scanBlockSums4, awake, d.rootScan + awake);
   // P6 layout of the grid-path color ranges (padded to 32) in front of the islands
   if (tid == 0) {
     int start = 0, touching = 0;
     for (int c = 0; c < kGraphColorCount; c++) { s.colorStart[c] = start; start += (s.colorCount[c] + 31) & ~31; touching += s.colorTotal[c]; }
     int4 tot = d.rootScan[awake];
-    s.smallConStart = start; s.islandCount = tot.x; s.constraintTotal = start + tot.z; s.touchingCount = touching;
+    s.smallConStart = start; s.islandCount = tot.x; s.constraintTotal = start + tot.z; s.touchingCount = touching; s.bigBodyCount = tot.w;
   }
   grid.sync();
   // P7 per island offsets
@@ -171,7 +175,7 @@ template <class S> __device__ void phase_islands(const S& grid, const WorldDev& 
   for (int i = tid; i < awake; i += stride) {
     int r = d.ufParent[i], info = d.rootInfo[r];
     if (info == -1) { d.freeBodies[atomicAdd(&s.freeBodyCount, 1)] = i; d.bodyLocal[i] = -1; }
-    else if (info == -2) { d.bigBodies[atomicAdd(&s.bigBodyCount, 1)] = i; d.bodyLocal[i] = -1; }
+    else if (info == -2) { const int k = d.rootScan[i].w + d.scanBlockSums4[i / (int)blockDim.x].w; d.bigBodies[k] = i; d.bodyLocal[i] = k; }   // slot in the grid-path body list, sim order (the cluster's shared-memory row)
     else { int k = atomicAdd(&d.rootBodyCount[r], 1); d.islandBodies[d.islandBodyStart[info] + k] = i; d.bodyLocal[i] = k; }
   }
   grid.sync();

@@ -616,6 +616,8 @@ struct BodyRows {
     b.v = mk(a.x, a.y); b.w = a.z; b.flags = fbits(a.w); b.dp = mk(c.x, c.y); b.dq = mkRot(c.z, c.w);
     return b;
   }
+  __device__ __forceinline__ BodyW loadA(int index) const { return load(index); }   // (the cluster's rows tell body A from body B: b2c_cluster_dsm.cuh)
+  __device__ __forceinline__ BodyW loadB(int index) const { return load(index); }
   __device__ __forceinline__ void store(int index, const BodyW& b) const {
     if (index >= 0 && (b.flags & kDynamicFlag)) st0[index] = make_float4(b.v.x, b.v.y, b.w, __uint_as_float(b.flags));
   }
@@ -721,8 +723,8 @@ __device__ void prepareContact(const WorldDev& d, const StepParams& sp, int t) {
 }
 
 // WarmStartContactsTask :686-744
-__device__ __forceinline__ void warmStartLane(const BodyRows& bs, const Lane& c, int ia, int ib, float4 I, float rollingImpulse) {
-  BodyW bA = bs.load(ia), bB = bs.load(ib);
+template <class Rows> __device__ __forceinline__ void warmStartLane(const Rows& bs, const Lane& c, int ia, int ib, float4 I, float rollingImpulse) {
+  BodyW bA = bs.loadA(ia), bB = bs.loadB(ib);
   float tangentX = c.n.y, tangentY = 0.0f - c.n.x;
   {
     float Px = I.x * c.n.x + I.y * tangentX, Py = I.x * c.n.y + I.y * tangentY;
@@ -785,9 +787,9 @@ __device__ __forceinline__ void solveFrictionPoint(BodyW& bA, BodyW& bB, const L
   applyP(bA, bB, c, rA, rB, impulse * tangentX, impulse * tangentY);
 }
 // SolveContactsTask :745-912 (useBias=true: Solve, false: Relax)
-template <bool USE_BIAS> __device__ __forceinline__ void solveLane(const BodyRows& bs, const StepParams& sp, const Lane& c, int ia, int ib, float4& I, float4& J) {
+template <bool USE_BIAS, class Rows> __device__ __forceinline__ void solveLane(const Rows& bs, const StepParams& sp, const Lane& c, int ia, int ib, float4& I, float4& J) {
   float contactSpeed = -sp.contactSpeed;
-  BodyW bA = bs.load(ia), bB = bs.load(ib);
+  BodyW bA = bs.loadA(ia), bB = bs.loadB(ib);
   float biasRate, massScale, impulseScale;
   if (USE_BIAS) { biasRate = c.massScale * c.biasRate; massScale = c.massScale; impulseScale = c.impulseScale; }
   else { biasRate = 0.0f; massScale = 1.0f; impulseScale = 0.0f; }
@@ -834,7 +836,7 @@ __device__ __forceinline__ void restitutionPoint(BodyW& bA, BodyW& bB, const Lan
   applyP(bA, bB, c, rA, rB, deltaImpulse * c.n.x, deltaImpulse * c.n.y);
 }
 __device__ __forceinline__ void restitutionLane(const BodyRows& bs, const StepParams& sp, const Lane& c, int ia, int ib, float4& I, float4& J) {
-  BodyW bA = bs.load(ia), bB = bs.load(ib);
+  BodyW bA = bs.loadA(ia), bB = bs.loadB(ib);
   bool restitutionMask = c.restitution == 0.0f;
   restitutionPoint(bA, bB, c, c.rA1, c.rB1, c.relVel1, I.x, J.x, sp.restitutionThreshold, restitutionMask);
   restitutionPoint(bA, bB, c, c.rA2, c.rB2, c.relVel2, I.z, J.y, sp.restitutionThreshold, restitutionMask);
@@ -1189,6 +1191,7 @@ template <bool CACHED, class Scope> __device__ void phase_solver_grid(const Scop
 
 }  // namespace b2c
 #include "b2c_islands.cuh"
+#include "b2c_cluster_dsm.cuh"
 #include "b2c_toi.cuh"
 namespace b2c {
 
@@ -1726,9 +1729,12 @@ template <class S> __device__ void stepFront(const S& grid, const WorldDev& d, c
   // a contact-only scene between 8 192 and 75 776 constraints keeps its lanes in the grid's registers, which beats the cheaper barrier.
   const bool clusterFits = s.smallConStart + gridJoints <= 12 * sp.clusterThreads && s.bigBodyCount <= 8 * sp.clusterThreads;
   const bool clusterWins = gridJoints > 0 || s.colLen[kOverflowIndex] > 0 || s.smallConStart <= sp.clusterThreads || s.smallConStart > grid.size();
-  const bool clusterPath = gridWork && sp.clusterThreads > 0 && clusterFits && clusterWins;
-  if (grid.tid() == 0) s.clusterSolve = clusterPath ? 1 : 0;
-  const bool cachedLanes = s.smallConStart <= (clusterPath ? sp.clusterThreads : grid.size());   // one grid-path constraint per thread: lanes stay in registers
+  // One large island of contacts that fits the cluster's shared memory: body rows in distributed shared memory, lanes in shared memory,
+  // no L2 round trip in a stage (b2c_cluster_dsm.cuh) - beats both the grid barrier and the plain cluster path.
+  const bool dsm = gridWork && sp.clusterThreads > 0 && dsmEligible(d, sp);
+  const bool clusterPath = gridWork && sp.clusterThreads > 0 && ((clusterFits && clusterWins) || dsm);
+  if (grid.tid() == 0) s.clusterSolve = dsm ? 2 : (clusterPath ? 1 : 0);
+  const bool cachedLanes = dsm || s.smallConStart <= (clusterPath ? sp.clusterThreads : grid.size());   // one grid-path constraint per thread: lanes stay in registers (dsm: built by the cluster kernel)
   if (gridWork) { phase_prepare(grid, d, sp, !cachedLanes); if (!cachedLanes) grid.sync(); }
   if (grid.tid() == 0) s.phaseStamp[3] = globalTimer();
   dbgLanes(d, 3, true); dbgBodies(d, 4); dbgColorConflicts(grid, d, 10);
@@ -1746,9 +1752,18 @@ __global__ void __launch_bounds__(kCoopThreads) k_step_front(const __grid_consta
 
 // The grid-path solver on one thread-block cluster (see clusterPath in stepFront). All CTAs of the cluster take the same path.
 __global__ void __launch_bounds__(kCoopThreads) k_solver_cluster(const __grid_constant__ WorldDev d, const __grid_constant__ StepParams sp) {
-  const Scalars& s = *d.sc;
+  extern __shared__ __align__(16) unsigned char dsmSmem[];
+  Scalars& s = *d.sc;
   if (!s.clusterSolve) return;
   ClusterScope cs;
+  if (s.clusterSolve == 2) {
+    if (phase_solver_dsm(cs, d, sp, dsmSmem)) return;
+    // one CTA would own more constraints than it has lanes: the plain cluster path, lanes in the global planes (stepFront skipped PrepareContacts)
+    for (int t = cs.tid(); t < s.smallConStart; t += cs.size()) if (d.sContact[t] >= 0) prepareContact(d, sp, t);
+    cs.sync();
+    phase_solver_grid<false>(cs, d, sp);
+    return;
+  }
   if (s.smallConStart <= cs.size()) phase_solver_grid<true>(cs, d, sp); else phase_solver_grid<false>(cs, d, sp);
 }
 
@@ -1872,6 +1887,7 @@ int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch
   { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
   if (clusterLaunch) {
     cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(clusterCtas_); cfg.blockDim = dim3(kCoopThreads); cfg.stream = stream_;
+    cfg.dynamicSmemBytes = clusterDsm_ ? kDsmSmemBytes : 0;
     cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = clusterCtas_; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
     cfg.attrs = &at; cfg.numAttrs = 1;
     CK(cudaLaunchKernelEx(&cfg, k_solver_cluster, d, sp));
@@ -1936,6 +1952,16 @@ int World::step(float timeStep, int subStepCount) {
         cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = size; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
         cfg.attrs = &at; cfg.numAttrs = 1;
         int n = 0;
+        // first choice: the cluster with the shared memory of the distributed-shared-memory solver (192 KB per CTA)
+        const char* de = getenv("B2CUDA_CLUSTER_DSM");
+        if ((!de || strcmp(de, "0")) && cudaFuncSetAttribute(k_solver_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDsmSmemBytes) == cudaSuccess) {
+          cfg.dynamicSmemBytes = kDsmSmemBytes;
+          cudaError_t oe = cudaOccupancyMaxActiveClusters(&n, k_solver_cluster, &cfg);
+          if (getenv("B2CUDA_VERBOSE")) fprintf(stderr, "b2cuda: cluster %d CTAs with %zu B of shared memory: %s, %d active clusters\n", size, kDsmSmemBytes, cudaGetErrorString(oe), n);
+          if (oe == cudaSuccess && n >= 1) { clusterCtas_ = size; clusterDsm_ = true; break; }
+          cfg.dynamicSmemBytes = 0;
+        } else if (getenv("B2CUDA_VERBOSE")) fprintf(stderr, "b2cuda: cluster kernel cannot take %zu B of dynamic shared memory: %s\n", kDsmSmemBytes, cudaGetErrorString(cudaGetLastError()));
+        cudaGetLastError();
         if (cudaOccupancyMaxActiveClusters(&n, k_solver_cluster, &cfg) == cudaSuccess && n >= 1) { clusterCtas_ = size; break; }
         cudaGetLastError();
       }
@@ -1949,6 +1975,9 @@ int World::step(float timeStep, int subStepCount) {
   // the front kernel takes the cluster path only when told the kernel follows, so a stale view costs speed, never correctness
   const bool clusterLaunch = clusterCtas_ > 0 && !d.debugChecksums && (hostScalars_->smallConStart > 0 || hostScalars_->bigBodyCount > 0 || d.jointColorStart[kGraphColorCount] > 0);
   sp.clusterThreads = clusterLaunch ? clusterCtas_ * kCoopThreads : 0;
+  sp.clusterDsm = clusterLaunch && clusterDsm_ ? 1 : 0;
+  if (stepCount_ == 100 && getenv("B2CUDA_VERBOSE")) fprintf(stderr, "b2cuda: step 100: cluster %d CTAs, dsm %d, launch %d; last step on the host: clusterSolve %d, grid-path constraints %d, bodies %d, islands %d, overflow %d, restitution %d\n",
+      clusterCtas_, (int)clusterDsm_, (int)clusterLaunch, hostScalars_->clusterSolve, hostScalars_->smallConStart, hostScalars_->bigBodyCount, hostScalars_->islandCount, hostScalars_->colLen[kOverflowIndex], hostScalars_->anyRestitution);
   lastEndIndex_ = endIndex_;
   endIndex_ = 1 - endIndex_;
   // Graph launches trade ~7 us of start latency for immunity to host launch jitter: off by default (a caller that synchronises every step is

@@ -124,6 +124,7 @@ struct StepParams {    // src/Solver.cs:57-112 StepContext (scalars only)
   int enableWarmStarting, enableContactSoftening, enableContinuous, enableSpeculative, enableSleep;
   int endIndex;        // which contactEndEvents buffer this step appends to
   int clusterThreads;  // > 0: k_solver_cluster follows the front kernel with this many threads (one cluster); 0: grid path only
+  int clusterDsm;      // the cluster kernel was launched with the shared memory of the distributed-shared-memory solver (b2c_cluster_dsm.cuh)
 };
 
 struct WorldDev;
