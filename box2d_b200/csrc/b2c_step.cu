@@ -1887,7 +1887,7 @@ int World::enqueueStep(const StepParams& spIn, bool warpMode, bool clusterLaunch
   { void* args[] = {(void*)&d, (void*)&sp}; CK(cudaLaunchCooperativeKernel((void*)k_step_front, cgrid, cblock, args, 0, stream_)); }
   if (clusterLaunch) {
     cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(clusterCtas_); cfg.blockDim = dim3(kCoopThreads); cfg.stream = stream_;
-    cfg.dynamicSmemBytes = clusterDsm_ ? kDsmSmemBytes : 0;
+    cfg.dynamicSmemBytes = sp.clusterDsm ? kDsmSmemBytes : 0;
     cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension; at.val.clusterDim.x = clusterCtas_; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
     cfg.attrs = &at; cfg.numAttrs = 1;
     CK(cudaLaunchKernelEx(&cfg, k_solver_cluster, d, sp));
@@ -1975,7 +1975,11 @@ int World::step(float timeStep, int subStepCount) {
   // the front kernel takes the cluster path only when told the kernel follows, so a stale view costs speed, never correctness
   const bool clusterLaunch = clusterCtas_ > 0 && !d.debugChecksums && (hostScalars_->smallConStart > 0 || hostScalars_->bigBodyCount > 0 || d.jointColorStart[kGraphColorCount] > 0);
   sp.clusterThreads = clusterLaunch ? clusterCtas_ * kCoopThreads : 0;
-  sp.clusterDsm = clusterLaunch && clusterDsm_ ? 1 : 0;
+  // The shared-memory solver's 216 KB leave the cluster kernel almost no L1, which the plain cluster path (joint records, lanes in global
+  // planes) lives on: ask for them only when the last step that reached the host looked eligible (the device decides for itself whether it is).
+  { const Scalars& hs = *hostScalars_;
+    sp.clusterDsm = clusterLaunch && clusterDsm_ && d.jointColorStart[kGraphColorCount] == 0 && hs.colLen[kOverflowIndex] == 0 && hs.anyRestitution == 0 &&
+                    hs.smallConStart > 0 && hs.smallConStart <= kDsmLanes * clusterCtas_ * kCoopThreads && hs.bigBodyCount <= kDsmRows * clusterCtas_ ? 1 : 0; }
   if (stepCount_ == 100 && getenv("B2CUDA_VERBOSE")) fprintf(stderr, "b2cuda: step 100: cluster %d CTAs, dsm %d, launch %d; last step on the host: clusterSolve %d, grid-path constraints %d, bodies %d, islands %d, overflow %d, restitution %d\n",
       clusterCtas_, (int)clusterDsm_, (int)clusterLaunch, hostScalars_->clusterSolve, hostScalars_->smallConStart, hostScalars_->bigBodyCount, hostScalars_->islandCount, hostScalars_->colLen[kOverflowIndex], hostScalars_->anyRestitution);
   lastEndIndex_ = endIndex_;
