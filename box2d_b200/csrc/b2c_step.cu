@@ -393,6 +393,7 @@ __device__ __forceinline__ void storePoint(const MPoint& p, float4* a, float4* b
   *c = make_float4(p.point.x, p.point.y, p.normalVelocity, __uint_as_float((p.id & 0xffffu) | (p.persisted << 16)));
 }
 
+__device__ __forceinline__ unsigned long long globalTimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 __device__ void p_collide(const WorldDev& d, const StepParams& sp, int tid, int stride) {
   int n = d.sc->contactNext;
@@ -527,9 +528,81 @@ __device__ void p_color_ops(const WorldDev& d) {
   __shared__ int sRemaining;
   int n = d.sc->opCount;
   if (n == 0) return;
+  int rounds = 0;
+  constexpr int kOwn = 8;                            // ops a thread keeps in registers (n <= kOwn * blockDim: no reload of ids / bodies / types per round)
+  if (n <= kOwn * (int)blockDim.x) {
+    // Every round costs three passes over the pending ops; with the op's contact id, bodies and body types in registers a pass is ONE
+    // memory round trip (the bodies' lowest pending op, then their colour masks) instead of a chain of five dependent loads.
+    int opId[kOwn], bx[kOwn], by[kOwn]; uint32_t st[kOwn];     // st: bit0 A dynamic, bit1 B dynamic, bit2 A static, bit3 B static, bit4 pending, bit5 done this round
+#pragma unroll
+    for (int i = 0; i < kOwn; i++) {
+      const int k = threadIdx.x + i * blockDim.x;
+      st[i] = 0;
+      if (k < n) {
+        d.opCol[k] = 0;
+        const int id = d.opList[k]; const int2 b = d.cBody[id];
+        const int tA = d.bodyType[b.x], tB = d.bodyType[b.y];
+        opId[i] = id; bx[i] = b.x; by[i] = b.y;
+        st[i] = (tA == kDynamicBody ? 1u : 0u) | (tB == kDynamicBody ? 2u : 0u) | (tA == kStaticBody ? 4u : 0u) | (tB == kStaticBody ? 8u : 0u) | 16u | ((uint32_t)(d.cColor[id] + 1) << 8);   // bits 8..: colour + 1 (0 = not in the graph: an add)
+      }
+    }
+    while (true) {
+      if (threadIdx.x == 0) sRemaining = 0;
+#pragma unroll
+      for (int i = 0; i < kOwn; i++) if (st[i] & 16u) {
+        const int k = threadIdx.x + i * blockDim.x;
+        if (st[i] & 1u) atomicMin(&d.bodyMinOp[bx[i]], k);
+        if (st[i] & 2u) atomicMin(&d.bodyMinOp[by[i]], k);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < kOwn; i++) if (st[i] & 16u) {
+        const int k = threadIdx.x + i * blockDim.x;
+        const bool dynA = st[i] & 1u, dynB = st[i] & 2u;
+        const int minA = dynA ? *(volatile int*)&d.bodyMinOp[bx[i]] : k, minB = dynB ? *(volatile int*)&d.bodyMinOp[by[i]] : k;
+        if (minA != k || minB != k) { sRemaining = 1; continue; }
+        const int id = opId[i];
+        const int color = (int)(st[i] >> 8) - 1;
+        if (color == -1) {                           // add
+          uint32_t mA = d.bodyColorMask[bx[i]], mB = d.bodyColorMask[by[i]];
+          int c = kOverflowIndex;
+          if (!(st[i] & 4u) && !(st[i] & 8u)) {
+            uint32_t freeBits = ~(mA | mB) & ((1u << kDynamicColorCount) - 1u);
+            if (freeBits) c = __ffs((int)freeBits) - 1;
+            if (c != kOverflowIndex) { if (dynA) mA |= 1u << c; if (dynB) mB |= 1u << c; }
+          } else if (dynA) {
+            uint32_t freeBits = ~mA & 0x007ffffeu;    // colors 22..1
+            if (freeBits) { c = 31 - __clz((int)freeBits); mA |= 1u << c; }
+          } else if (dynB) {
+            uint32_t freeBits = ~mB & 0x007ffffeu;
+            if (freeBits) { c = 31 - __clz((int)freeBits); mB |= 1u << c; }
+          }
+          if (dynA) d.bodyColorMask[bx[i]] = mA;
+          if (dynB) d.bodyColorMask[by[i]] = mB;
+          d.cColor[id] = c;
+          d.opCol[k] = (uint8_t)(0x40 | c);
+        } else {                                     // remove
+          d.opCol[k] = (uint8_t)(0x80 | color);
+          if (color != kOverflowIndex) {
+            if (dynA) d.bodyColorMask[bx[i]] &= ~(1u << color);
+            if (dynB) d.bodyColorMask[by[i]] &= ~(1u << color);
+          }
+          d.cColor[id] = -1;
+        }
+        st[i] = (st[i] & 15u) | 32u;
+      }
+      __syncthreads();
+      // every op that was pending in this round put its index on its bodies: take them all back (the ones that ran AND the ones that wait)
+#pragma unroll
+      for (int i = 0; i < kOwn; i++) if (st[i] & 48u) { d.bodyMinOp[bx[i]] = 0x7f7f7f7f; d.bodyMinOp[by[i]] = 0x7f7f7f7f; st[i] &= ~32u; }
+      rounds++;
+      __syncthreads();
+      if (sRemaining == 0) break;
+      __syncthreads();
+    }
+  } else {
   for (int k = threadIdx.x; k < n; k += blockDim.x) { d.opDone[k] = 0; d.opCol[k] = 0; }
   __syncthreads();
-  int rounds = 0;
   while (true) {
     if (threadIdx.x == 0) sRemaining = 0;
     for (int k = threadIdx.x; k < n; k += blockDim.x) {
@@ -587,7 +660,8 @@ __device__ void p_color_ops(const WorldDev& d) {
     if (sRemaining == 0) break;
     __syncthreads();
   }
-  if (threadIdx.x == 0) d.sc->colorRounds = rounds;
+  }
+  if (threadIdx.x == 0) { d.sc->colorRounds = rounds; if (d.debugChecksums == 2) d.sc->dbg[4] = globalTimer(); }
   __syncthreads();
   colReplayOps(d, n);
 }
@@ -1551,7 +1625,6 @@ namespace b2c {
 // Fused cooperative phase kernels: one launch per reference phase, grid.sync() between dependent sub-phases, and a
 // uniform early-out when the phase has nothing to do (no moved proxies / no contact state change / no enlarged proxy).
 // ------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned long long globalTimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 template <class S> __device__ void phase_broadphase(const S& grid, const WorldDev& d) {      // UpdateBroadPhasePairs + RebuildTrees
   const int tid = grid.tid(), stride = grid.size();
   Scalars& s = *d.sc;
@@ -1582,8 +1655,11 @@ template <class S> __device__ void phase_broadphase(const S& grid, const WorldDe
 template <class S> __device__ void phase_collide(const S& grid, const WorldDev& d, const StepParams& sp) {   // World.Collide
   const int tid = grid.tid(), stride = grid.size();
   Scalars& s = *d.sc;
+  const bool probe = d.debugChecksums == 2 && tid == 0;   // B2CUDA_DEBUG_CHECKSUMS=2: %globaltimer stamps of the sub-phases in dbg[0..5]
+  if (probe) s.dbg[0] = globalTimer();
   p_collide(d, sp, tid, stride);
   grid.sync();
+  if (probe) s.dbg[1] = globalTimer();
   if (s.anyContactFlag == 0) {                    // no begin / end / destroy anywhere: the serial pass is empty
     if (tid == 0) { s.beginCount = 0; s.opCount = 0; }      // endCount keeps the events DestroyContact appended since the last step
     return;
@@ -1591,9 +1667,11 @@ template <class S> __device__ void phase_collide(const S& grid, const WorldDev& 
   gridScan<int4>(grid, d.flagScan, d.scanBlockSums4, s.contactNext, d.flagScan + d.contactCapacity);
   p_contact_events(d, sp, tid, stride);
   grid.sync();
+  if (probe) s.dbg[2] = globalTimer();
   if (tid == 0) { p_events_finish(d, sp, d.flagScan + d.contactCapacity); s.anyContactFlag = 0; }
   grid.sync();
   if (grid.block() == 0) p_color_ops(d);
+  if (probe) { s.dbg[5] = globalTimer(); s.dbg[12] = (unsigned long long)s.opCount; s.dbg[13] = (unsigned long long)s.colorRounds; }
 }
 
 
