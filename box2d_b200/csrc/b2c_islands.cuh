@@ -25,12 +25,18 @@ __device__ __forceinline__ int ufFindReadOnly(const int* parent, int x) {
   while (p != x) { x = p; p = parent[x]; }
   return x;
 }
+__device__ __forceinline__ uint32_t ufPriority(int x) { return (uint32_t)x * 0x9E3779B1u; }     // odd multiplier: a bijection on 32 bits, no ties
 __device__ __forceinline__ void ufUnion(int* parent, int a, int b) {
   while (true) {
     a = ufFind(parent, a); b = ufFind(parent, b);
     if (a == b) return;
-    int hi = a > b ? a : b, lo = a > b ? b : a;
-    int old = atomicCAS(&parent[hi], hi, lo);    // hook the larger root under the smaller one
+    // hook the root of larger PRIORITY under the other. The priority is a bijective scramble of the index, not the index itself: bodies of
+    // a lattice are joined to their index neighbours, and hooking by index built parent chains hundreds of links long before any
+    // compression (tumbler: 189 us in this loop); with scrambled priorities the trees stay logarithmic. Any total order keeps the forest
+    // acyclic, and the root of a component (its minimum-priority member) is still independent of thread timing.
+    const bool aHigh = ufPriority(a) > ufPriority(b);
+    int hi = aHigh ? a : b, lo = aHigh ? b : a;
+    int old = atomicCAS(&parent[hi], hi, lo);
     if (old == hi) return;
   }
 }
@@ -68,12 +74,14 @@ template <class S> __device__ void gridScan4(const S& grid, int4* data, int4* su
 // Rebuilds the island partition and the constraint order [grid-path colors | island 0 | island 1 | ...] when the graph
 // changed this step; a no-op (one uniform branch) otherwise. Order inside one (group, color) bucket is arbitrary:
 // constraints of one color never share a writable body, so it does not influence any result.
+__device__ __forceinline__ unsigned long long globalTimerI() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 template <class S> __device__ void phase_islands(const S& grid, const WorldDev& d) {
   Scalars& s = *d.sc;
   if (!s.graphDirty) return;
   const int tid = grid.tid(), stride = grid.size();
   const int awake = d.awakeCount, nContacts = s.contactNext, nJoints = d.jointColorStart[kGraphColorCount];
   __shared__ int hist[kGraphColorCount];
+  if (d.debugChecksums == 3 && tid == 0) d.sc->dbg[6] = globalTimerI();
   // P0 init
   for (int i = tid; i < awake; i += stride) { d.ufParent[i] = i; d.rootBodyCount[i] = 0; d.rootConCount[i] = 0; d.kinematicUsed[i] = 0; }
   for (int i = tid; i < awake * kGraphColorCount; i += stride) d.rootColorCount[i] = 0;
@@ -92,9 +100,11 @@ template <class S> __device__ void phase_islands(const S& grid, const WorldDev& 
     if (simIsDynamic(d, a) && simIsDynamic(d, b)) ufUnion(d.ufParent, a, b);
   }
   grid.sync();
+  if (d.debugChecksums == 3 && tid == 0) d.sc->dbg[7] = globalTimerI();
   // P2 flatten + bodies per root
   for (int i = tid; i < awake; i += stride) { int r = ufFindReadOnly(d.ufParent, i); d.ufParent[i] = r; atomicAdd(&d.rootBodyCount[r], 1); }
   grid.sync();
+  if (d.debugChecksums == 3 && tid == 0) d.sc->dbg[8] = globalTimerI();
   // P3 constraints per root / color
   if (threadIdx.x < kGraphColorCount) hist[threadIdx.x] = 0;
   __syncthreads();
@@ -128,6 +138,7 @@ template <class S> __device__ void phase_islands(const S& grid, const WorldDev& 
   __syncthreads();
   if (threadIdx.x < kGraphColorCount && hist[threadIdx.x]) atomicAdd(&s.colorTotal[threadIdx.x], hist[threadIdx.x]);
   grid.sync();
+  if (d.debugChecksums == 3 && tid == 0) d.sc->dbg[9] = globalTimerI();
   // P4 classify roots
   for (int i = tid; i < awake; i += stride) {
     int4 in = make_int4(0, 0, 0, 0);
@@ -155,6 +166,7 @@ template <class S> __device__ void phase_islands(const S& grid, const WorldDev& 
     s.smallConStart = start; s.islandCount = tot.x; s.constraintTotal = start + tot.z; s.touchingCount = touching; s.bigBodyCount = tot.w;
   }
   grid.sync();
+  if (d.debugChecksums == 3 && tid == 0) d.sc->dbg[10] = globalTimerI();
   // P7 per island offsets
   const int smallConStart = s.smallConStart;
   for (int t = tid; t < smallConStart; t += stride) d.sContact[t] = -1;
@@ -179,6 +191,7 @@ template <class S> __device__ void phase_islands(const S& grid, const WorldDev& 
     else { int k = atomicAdd(&d.rootBodyCount[r], 1); d.islandBodies[d.islandBodyStart[info] + k] = i; d.bodyLocal[i] = k; }
   }
   grid.sync();
+  if (d.debugChecksums == 3 && tid == 0) d.sc->dbg[11] = globalTimerI();
   // P9 constraints -> slots
   for (int i = tid; i < nContacts; i += stride) {
     if (!(d.cFlags[i] & CF_TOUCHING)) { if (d.cFlags[i] & CF_ALIVE) d.cConstraint[i] = -1; continue; }

@@ -1799,6 +1799,7 @@ template <class S> __device__ void stepFront(const S& grid, const WorldDev& d, c
   const bool dirty = s.graphDirty != 0;
   phase_islands(grid, d);
   if (dirty) grid.sync();
+  if (d.debugChecksums == 3 && grid.tid() == 0) s.dbg[12] = globalTimer();
   const bool gridWork = s.smallConStart > 0 || d.jointColorStart[kGraphColorCount] > 0 || s.bigBodyCount > 0;
   // Scenes whose grid-path work is one cluster's worth are solved by k_solver_cluster (launched next when sp.clusterThreads > 0):
   // every colour stage is one barrier + one L2 round trip, so the cheaper barrier wins although 16 SMs do the work of 148.
