@@ -62,6 +62,8 @@ Batch::~Batch() {
   if (stream_) cudaStreamDestroy(stream_);
 }
 
+// Two arena chunks can be neighbours in the address space: a run of adjacent blocks must still end where a chunk begins (one copy, one allocation).
+bool Batch::isChunkBase(const void* p) const { return std::find(chunks_.begin(), chunks_.end(), p) != chunks_.end(); }
 void* Batch::arenaAlloc(size_t bytes) {
   bytes = (bytes + 255) & ~(size_t)255;
   if (bytes > chunkLeft_) {
@@ -111,7 +113,7 @@ int Batch::ensureUploaded() {
     // consecutive arena blocks are adjacent in memory (bump allocation) unless a chunk boundary fell between them: copy runs
     for (size_t k = 0; k < w.arenaBlocks_.size();) {
       char* runBegin = (char*)w.arenaBlocks_[k].first; size_t run = 0; size_t j = k;
-      while (j < w.arenaBlocks_.size() && (char*)w.arenaBlocks_[j].first == runBegin + run) { run += (w.arenaBlocks_[j].second + 255) & ~(size_t)255; j++; }
+      while (j < w.arenaBlocks_.size() && (char*)w.arenaBlocks_[j].first == runBegin + run && (j == k || !isChunkBase(w.arenaBlocks_[j].first))) { run += (w.arenaBlocks_[j].second + 255) & ~(size_t)255; j++; }
       CK(cudaMemcpyAsync(s.dev + off, runBegin, run, cudaMemcpyDeviceToDevice, stream_));
       off += run; k = j;
     }
@@ -131,7 +133,7 @@ int Batch::resetWorld(int index) {
   size_t off = 0;
   for (size_t k = 0; k < w.arenaBlocks_.size();) {
     char* runBegin = (char*)w.arenaBlocks_[k].first; size_t run = 0; size_t j = k;
-    while (j < w.arenaBlocks_.size() && (char*)w.arenaBlocks_[j].first == runBegin + run) { run += (w.arenaBlocks_[j].second + 255) & ~(size_t)255; j++; }
+    while (j < w.arenaBlocks_.size() && (char*)w.arenaBlocks_[j].first == runBegin + run && (j == k || !isChunkBase(w.arenaBlocks_[j].first))) { run += (w.arenaBlocks_[j].second + 255) & ~(size_t)255; j++; }
     CK(cudaMemcpyAsync(runBegin, s.dev + off, run, cudaMemcpyDeviceToDevice, stream_));
     off += run; k = j;
   }

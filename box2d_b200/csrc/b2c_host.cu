@@ -1304,7 +1304,7 @@ int World::growShapes(int minShapes) {
   const int c = std::max(minShapes, capShape_ + capShape_ / 2), extra = c - capShape_;
   RG(d.shapes, c); RG(d.shapeAABB, c); RG(d.shapeFat, c);
   const int m = d.moveCapacity + extra;              // every new shape may sit in the move buffer
-  RG(d.moveArray, m); RG(d.moveHitCount, m + 1); RG(d.moveBig, m); RG(d.moveHitBuf, (size_t)m * 4);
+  RG(d.moveArray, m); RG(d.moveHitCount, m + 1); RG(d.moveBig, m); RG(d.moveHitBuf, (size_t)m * kHitBuf);
   d.moveCapacity = m;
   capShape_ = c;
   return growScanScratch();
@@ -1486,7 +1486,7 @@ int World::upload() {
     d.debugChecksums = getenv("B2CUDA_DEBUG_CHECKSUMS") ? atoi(getenv("B2CUDA_DEBUG_CHECKSUMS")) : 0;
     if (const char* e = getenv("B2CUDA_ISLAND_MAX_BODIES")) { int v = atoi(e); if (v >= 0 && v <= kIslandMaxBodies) d.islandMaxBodies = v; }
     if (const char* e = getenv("B2CUDA_BIG_QUERY_VISITS")) { int v = atoi(e); if (v > 0) d.bigQueryVisits = v; }
-    DA(d.moveBig, int, d.moveCapacity); DA(d.moveHitBuf, int2, (size_t)d.moveCapacity * 4); DA(d.bigList, int, kMaxBigQueries); DA(d.bigSegStart, int, kMaxBigQueries + 1); DA(d.bigOff, int, kMaxBigQueries + 1);
+    DA(d.moveBig, int, d.moveCapacity); DA(d.moveHitBuf, int2, (size_t)d.moveCapacity * kHitBuf); DA(d.bigList, int, kMaxBigQueries); DA(d.bigSegStart, int, kMaxBigQueries + 1); DA(d.bigOff, int, kMaxBigQueries + 1);
     DA(d.bigScan, int, d.bigScratch); DA(d.bigFlag, uint8_t, d.bigScratch); DA(d.bigHits, int2, d.pairCapacity); }
   UP(d.moveArray, moveArray_);
   DA(d.cShape, int2, contactCap); DA(d.cBody, int2, contactCap); DA(d.cFlags, uint32_t, contactCap); DA(d.cColor, int, contactCap); DA(d.cGen, uint32_t, contactCap); DA(d.cStamp, uint32_t, contactCap);

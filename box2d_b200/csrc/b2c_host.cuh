@@ -253,6 +253,7 @@ class Batch {
   // used by member worlds
   cudaStream_t stream() { return stream_; }
   void* arenaAlloc(size_t bytes);
+  bool isChunkBase(const void* p) const;
   int* mappedInt(int** devPtr) { *devPtr = mappedIntDev_; return mappedInt_; }
   void markDirty(int index) { dirty_.push_back(index); }
  private:

@@ -194,7 +194,7 @@ __device__ __forceinline__ bool acceptPair(const WorldDev& d, int queryKey, int 
 // DynamicTree.Query (src/DynamicTree.cs:531-557): explicit stack, child1 pushed first so child2 is visited first.
 // BUDGET: give up (return -1) after kBigQueryVisits node visits — the query is then answered by the leaf sweep below.
 __device__ __forceinline__ void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
-constexpr int kHitBuf = 4;     // accepted hits kept from the count pass; queries with more re-traverse in the fill pass
+
 struct HitSink {               // where accepted hits of one query go
   int2* out; int outLast;      // FILL: movePairs and the query's last slot (hits are written in reverse)
   int2* buf;                   // count pass: first kHitBuf hits in hit order

@@ -93,6 +93,8 @@ struct OvConstraint {
   float friction, restitution, tangentSpeed, rollingResistance, rollingMass, rollingImpulse; Softness softness; int pointCount;
 };
 
+constexpr int kHitBuf = 8;     // accepted hits a pair query keeps from its count pass; a query with more walks the tree again in the fill pass (a full walk by one thread: ~100 us in a 20 000-leaf tree)
+
 struct Scalars {       // device scalars, mirrored to pinned host memory at the end of each step
   int moveCount, newPairCount, contactNext, contactFreeCount;
   int beginCount, endCount[2], hitCount;
