@@ -171,7 +171,7 @@ __device__ bool phase_solver_dsm(const ClusterScope& cs, const WorldDev& d, cons
     int off = 0;
     for (int a = 0; a < activeCount; a++) { sOff[a] = off; off += sHist[a]; }
     sOff[activeCount] = off;
-    if (off > kDsmLanes * kCoopThreads || myRows > kDsmRows) atomicExch(&s.clusterSolve, 3);      // more than this CTA has lanes or rows for
+    if (off > kDsmLanes * kCoopThreads || myRows > kDsmRows || sp.clusterDsm == 2) atomicExch(&s.clusterSolve, 3);      // more than this CTA has lanes or rows for (or the test switch)
   }
   cs.sync();
   if (*(volatile int*)&s.clusterSolve == 3) return false;

@@ -223,6 +223,7 @@ class World {
   int coopBlocks_ = 0;
   int clusterCtas_ = 0;   // CTAs of the solver cluster (16, 8 or 0 = off)
   bool clusterDsm_ = false;      // the cluster kernel can be launched with kDsmSmemBytes of dynamic shared memory per CTA
+  bool clusterDsmFallback_ = false;   // B2CUDA_CLUSTER_DSM=fallback
   B2CBodyRead* dBodyRead_ = nullptr; B2CBodyRead* hBodyRead_ = nullptr; bool bodiesFetched_ = false; bool streamBodies_ = false;
   B2CBodyMoveEvent* dMoveEvents_ = nullptr; B2CBodyMoveEvent* hMoveEvents_ = nullptr; B2CBodyMoveEvent* hMoveEventsDev_ = nullptr;   // device alias of the mapped host buffer
   bool movesFetched_ = false, streamMoves_ = false, lastStepDtZero_ = false;

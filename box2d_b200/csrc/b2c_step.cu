@@ -2033,6 +2033,7 @@ int World::step(float timeStep, int subStepCount) {
         int n = 0;
         // first choice: the cluster with the shared memory of the distributed-shared-memory solver (192 KB per CTA)
         const char* de = getenv("B2CUDA_CLUSTER_DSM");
+        clusterDsmFallback_ = de && !strcmp(de, "fallback");    // tests: every eligible step takes the solver's way out (a CTA short of lanes)
         if ((!de || strcmp(de, "0")) && cudaFuncSetAttribute(k_solver_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDsmSmemBytes) == cudaSuccess) {
           cfg.dynamicSmemBytes = kDsmSmemBytes;
           cudaError_t oe = cudaOccupancyMaxActiveClusters(&n, k_solver_cluster, &cfg);
@@ -2058,7 +2059,7 @@ int World::step(float timeStep, int subStepCount) {
   // planes) lives on: ask for them only when the last step that reached the host looked eligible (the device decides for itself whether it is).
   { const Scalars& hs = *hostScalars_;
     sp.clusterDsm = clusterLaunch && clusterDsm_ && d.jointColorStart[kGraphColorCount] == 0 && hs.colLen[kOverflowIndex] == 0 && hs.anyRestitution == 0 &&
-                    hs.smallConStart > 0 && hs.smallConStart <= kDsmLanes * clusterCtas_ * kCoopThreads && hs.bigBodyCount <= kDsmRows * clusterCtas_ ? 1 : 0; }
+                    hs.smallConStart > 0 && hs.smallConStart <= kDsmLanes * clusterCtas_ * kCoopThreads && hs.bigBodyCount <= kDsmRows * clusterCtas_ ? (clusterDsmFallback_ ? 2 : 1) : 0; }
   if (stepCount_ == 100 && getenv("B2CUDA_VERBOSE")) fprintf(stderr, "b2cuda: step 100: cluster %d CTAs, dsm %d, launch %d; last step on the host: clusterSolve %d, grid-path constraints %d, bodies %d, islands %d, overflow %d, restitution %d\n",
       clusterCtas_, (int)clusterDsm_, (int)clusterLaunch, hostScalars_->clusterSolve, hostScalars_->smallConStart, hostScalars_->bigBodyCount, hostScalars_->islandCount, hostScalars_->colLen[kOverflowIndex], hostScalars_->anyRestitution);
   lastEndIndex_ = endIndex_;

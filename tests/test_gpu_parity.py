@@ -402,6 +402,19 @@ def test_grid_barrier_solver_variant_bit_exact(scene, steps, monkeypatch):
     assert res["max_rel_err"] == 0.0
 
 
+@pytest.mark.parametrize("mode", ["0", "fallback"])
+def test_cluster_solver_without_its_shared_memory_variant_bit_exact(mode, monkeypatch):
+    """One large island of contacts is solved in the cluster's distributed shared memory by default (b2c_cluster_dsm.cuh; every other large-island
+    test runs that way). B2CUDA_CLUSTER_DSM=0 keeps the plain cluster path (lanes in global planes); =fallback makes every eligible step take the
+    shared-memory solver's way out (a CTA that would own more constraints than it has lanes: PrepareContacts inside the cluster kernel, then the
+    plain path). Both must give the reference's floats."""
+    monkeypatch.setenv("B2CUDA_CLUSTER_DSM", mode)
+    res = parity.run_pair(lambda w: scenes.large_pyramid(w, 40), steps=20, verbose=True)
+    assert res["max_rel_err"] == 0.0
+    res = parity.run_pair(lambda w: scenes.tumbler(w, n=600, half=6.0), steps=30)
+    assert res["max_rel_err"] == 0.0
+
+
 @pytest.mark.parametrize("scene", ["mixed", "zoo"])
 def test_graph_launch_path_bit_exact(scene, monkeypatch):
     """B2CUDA_GRAPH=1 / b2cuda_world_enable_graph_launch: a step is ONE CUDA-graph launch instead of one launch per kernel. Same results."""
