@@ -2154,7 +2154,7 @@ cudaError_t launchBatchStep(const WorldDev* worlds, int worldCount, const StepPa
   if (useSplit) {
     k_batch_step<160, 4, 1><<<worldCount, 160, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
     k_batch_solve_warp<<<(worldCount + kWarpIslandsPerCta - 1) / kWarpIslandsPerCta, 32 * kWarpIslandsPerCta, kWarpIslandsPerCta * sizeof(WarpIslandSlice), stream>>>(worlds, worldCount, sp);
-    k_batch_step<64, 8, 2><<<worldCount, 64, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);   // FinalizeBodies of a small world: 64 threads, 8+ worlds per SM (134 -> see profiles/r02_summary.txt)
+    k_batch_step<64, 12, 2><<<worldCount, 64, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);   // FinalizeBodies of a small world: 64 threads at 80 registers, 12 worlds per SM (a dependent body -> shape -> fat-box load chain per thread: more worlds in flight hide it; 8 per SM at 128 registers 0.864-0.898 ms, 12 at 80: 0.847-0.851, 16 at 64 spills: 0.87-0.88)
   } else if (narrow) k_batch_step<160, 4, 0><<<worldCount, 160, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
   else k_batch_step<256, 2, 0><<<worldCount, 256, 0, stream>>>(worlds, sp, newEndIndex, maxIslandConsDev);
   return cudaGetLastError();
